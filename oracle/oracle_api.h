@@ -1,0 +1,120 @@
+/* TEST INFRASTRUCTURE ONLY.  Plain-C interface of oracle/_ref/libswiftref_*.so:
+ * the harness that drives the reference's own operators
+ * (runner_do_hydro_sort, runner_dosub_{self,pair}1_density, runner_do_ghost,
+ * runner_dosub_{self,pair}2_force, runner_do_end_hydro_force, ...) on a cell
+ * tree described by flat arrays, in the order tests/test125cells.c:660-822
+ * calls them.  Shared by ref_harness.c, sph_oracle.c and the ctypes tests. */
+#ifndef ORACLE_API_H
+#define ORACLE_API_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* One cell of the tree (top-level or progeny).  Particles of a cell are the
+ * contiguous range [first, first+count) of the particle arrays, and a
+ * progeny's range lies inside its parent's (src/space_split.c). */
+typedef struct {
+  double loc[3];
+  double width[3];
+  int first;
+  int count;
+  int parent;     /* -1 at top level */
+  int progeny[8]; /* -1 where absent */
+  int depth;
+  int split;
+} oracle_cell;
+
+/* A hydro task after scheduler_splittask_hydro (src/scheduler.c:1154). */
+enum { ORACLE_TASK_SELF = 0, ORACLE_TASK_PAIR = 1, ORACLE_TASK_SUB_SELF = 2, ORACLE_TASK_SUB_PAIR = 3 };
+typedef struct {
+  int type;
+  int ci;
+  int cj; /* -1 for self tasks */
+} oracle_task;
+
+typedef struct {
+  double dim[3];
+  int periodic;
+  float eta_neighbours;  /* SPH:resolution_eta */
+  float h_tolerance;     /* SPH:h_tolerance */
+  float h_max;           /* SPH:h_max */
+  float h_min;
+  int max_smoothing_iterations;
+  float viscosity_alpha;
+  int max_active_bin;    /* particles with time_bin <= this are active */
+  int record_pairs;      /* log ordered pairs into the buffers below */
+  int scheme;            /* ORACLE_SCHEME_*; the ref harness ignores it (compile-time there) */
+} oracle_params;
+
+enum { ORACLE_SCHEME_MINIMAL = 0, ORACLE_SCHEME_PLANETARY = 1 };
+
+/* Tillotson material in INTERNAL units (src/equation_of_state/planetary/tillotson.h:43-143) */
+typedef struct {
+  float rho_0, a, b, A, B, u_0, u_iv, u_cv, alpha, beta, eta_min, eta_zero, P_min;
+  int mat_id;
+} oracle_til;
+
+typedef struct {
+  int n_til;
+  oracle_til til[8];
+  float idg_gamma[4]; /* planetary ideal gas gammas, mat_id 0..2 (planetary/ideal_gas.h) */
+} oracle_eos;
+
+/* Particle arrays (SoA, n entries; vectors are [n][3] row-major). */
+typedef struct {
+  int n;
+  /* inputs */
+  const double *x;
+  const float *v;
+  const float *mass;
+  const float *h;
+  const float *u;
+  const int *mat_id;            /* Planetary only, may be NULL */
+  const long long *id;
+  const signed char *time_bin;  /* may be NULL: all 1 */
+  /* stage 0: raw neighbour sums after the first density pass */
+  float *d_rho, *d_rho_dh, *d_wcount, *d_wcount_dh, *d_div_v, *d_rot_v;
+  /* stage 1: after the ghost */
+  float *g_h, *g_rho, *g_f, *g_pressure, *g_soundspeed, *g_balsara;
+  /* stage 2: after force + end_force */
+  float *f_a, *f_u_dt, *f_h_dt, *f_v_sig;
+  signed char *f_min_ngb_time_bin;
+} oracle_parts;
+
+/* Ordered (updated id, neighbour id) pairs.  loop 0: first density pass,
+ * loop 1: ghost redo passes (all sweeps concatenated), loop 2: force.
+ * count[] is always the true number, even beyond capacity. */
+typedef struct {
+  long long *pairs[3]; /* [capacity][2] each, may be NULL */
+  long long capacity[3];
+  long long count[3];
+  int ghost_sweeps;    /* number of redo density sweeps that had work */
+} oracle_pairlog;
+
+/* Runs sort -> density -> ghost -> force -> end_force with the REFERENCE's
+ * compiled operators.  Returns 0 on success. */
+int ref_run_step(const oracle_params *params, oracle_parts *parts,
+                 int ncells, const oracle_cell *cells, int ntasks,
+                 const oracle_task *tasks, oracle_pairlog *log);
+
+/* sizeof(struct part), offsetof checks for the INTEGRATION shim */
+int ref_sizeof_part(void);
+/* Planetary build only: the reference's own eos_init() result (internal units
+ * UnitMass 1e27 g, UnitLength 1e8 cm, UnitVelocity 1e8 cm/s as
+ * examples/Planetary/EarthImpact/earth_impact.yml:2-7). Returns 0 when compiled in. */
+int ref_get_eos(oracle_eos *out);
+
+/* ---- the plain-C restatement (oracle/sph_oracle.c) ---- */
+int oracle_build_tree(const oracle_params *prm, int n, const double *x, const float *h, int *order,
+                      oracle_cell **cells_out, int *ncells_out, int cdim_out[3]);
+int oracle_build_tasks(const oracle_params *prm, int ncells, const oracle_cell *cells, const int cdim[3],
+                       const float *h_sorted, oracle_task **tasks_out, int *ntasks_out);
+int oracle_run_step(const oracle_params *prm, const oracle_eos *eos, oracle_parts *parts, int ncells,
+                    const oracle_cell *cells, int ntasks, const oracle_task *tasks, oracle_pairlog *log);
+void oracle_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

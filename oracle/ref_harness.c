@@ -1,0 +1,292 @@
+/* TEST INFRASTRUCTURE ONLY -- never linked into or called by the product.
+ *
+ * Harness around the REFERENCE's own compiled hot-path operators (built from
+ * /root/reference/src by oracle/Makefile.ref into oracle/_ref/).  It receives
+ * particles, a cell tree and a task list as flat arrays, builds the reference's
+ * `struct cell` / `struct part` / `struct task` objects from them and runs
+ *   hydro_init_part -> runner_do_hydro_sort -> density tasks -> runner_do_ghost
+ *   -> force tasks -> runner_do_end_hydro_force
+ * calling the operators directly, single threaded, in the order
+ * tests/test125cells.c:660-822 does.  The ghost's redo
+ * passes see the density tasks through hand-made `struct link` lists, as
+ * engine_maketasks.c would have linked them (runner_ghost.c:1503-1546).
+ *
+ * This file contains no physics: every number it returns was computed by the
+ * reference's code. */
+#include <config.h>
+
+#include <float.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "active.h"
+#include "cell.h"
+#include "cosmology.h"
+#include "engine.h"
+#include "hydro.h"
+#include "hydro_properties.h"
+#include "physical_constants.h"
+#include "runner.h"
+#include "runner_doiact_hydro.h"
+#include "space.h"
+#include "task.h"
+#include "timeline.h"
+
+#include "oracle_api.h"
+
+/* ---- pair log ----------------------------------------------------------- */
+static oracle_pairlog *g_log = NULL;
+static int g_stage = 0; /* 0 density, 1 ghost redo, 2 force */
+
+void ref_record_pair(int loop, long long id_updated, long long id_other) {
+  if (g_log == NULL) return;
+  const int slot = (loop == 1) ? 2 : g_stage;
+  const long long k = g_log->count[slot]++;
+  if (g_log->pairs[slot] != NULL && k < g_log->capacity[slot]) {
+    g_log->pairs[slot][2 * k] = id_updated;
+    g_log->pairs[slot][2 * k + 1] = id_other;
+  }
+}
+
+int ref_sizeof_part(void) { return (int)sizeof(struct part); }
+
+/* ---- helpers ------------------------------------------------------------ */
+static void add_link(struct cell *c, struct task *t, struct link *pool,
+                     int *used) {
+  struct link *l = &pool[(*used)++];
+  l->t = t;
+  l->next = c->hydro.density;
+  c->hydro.density = l;
+}
+
+static int cell_has_active(const struct cell *c, const struct engine *e) {
+  for (int k = 0; k < c->hydro.count; k++)
+    if (c->hydro.parts[k].time_bin <= e->max_active_bin) return 1;
+  return 0;
+}
+
+int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
+                 const oracle_cell *cd, int ntasks, const oracle_task *td,
+                 oracle_pairlog *log) {
+  const int n = io->n;
+  const integertime_t ti_current = 8;
+
+  /* ---- particles ---- */
+  struct part *parts = NULL;
+  struct xpart *xparts = NULL;
+  if (posix_memalign((void **)&parts, part_align, (size_t)(n + 1) * sizeof(struct part)) != 0) return 1;
+  if (posix_memalign((void **)&xparts, xpart_align, (size_t)(n + 1) * sizeof(struct xpart)) != 0) return 1;
+  bzero(parts, (size_t)(n + 1) * sizeof(struct part));
+  bzero(xparts, (size_t)(n + 1) * sizeof(struct xpart));
+  for (int k = 0; k < n; k++) {
+    struct part *p = &parts[k];
+    for (int d = 0; d < 3; d++) {
+      p->x[d] = io->x[3 * k + d];
+      p->v[d] = io->v[3 * k + d];
+    }
+    p->mass = io->mass[k];
+    p->h = io->h[k];
+    p->u = io->u[k];
+#ifdef PLANETARY_SPH
+    p->mat_id = io->mat_id ? io->mat_id[k] : 0;
+#endif
+    hydro_first_init_part(p, &xparts[k]);
+    p->id = io->id[k];
+    p->time_bin = io->time_bin ? io->time_bin[k] : 1;
+    p->limiter_data.min_ngb_time_bin = num_time_bins + 1;
+  }
+
+  /* ---- engine & friends (as tests/test125cells.c:566-619) ---- */
+  struct space space;
+  bzero(&space, sizeof(space));
+  space.periodic = prm->periodic;
+  for (int d = 0; d < 3; d++) space.dim[d] = prm->dim[d];
+  hydro_space_init(&space.hs, &space);
+
+  struct phys_const prog_const;
+  bzero(&prog_const, sizeof(prog_const));
+  prog_const.const_vacuum_permeability = 1.0;
+
+  struct hydro_props hp;
+  bzero(&hp, sizeof(hp));
+  hydro_props_init_no_hydro(&hp);
+  hp.eta_neighbours = prm->eta_neighbours;
+  hp.h_tolerance = prm->h_tolerance;
+  hp.h_max = prm->h_max;
+  hp.h_min = prm->h_min;
+  hp.h_min_ratio = 0.f;
+  hp.max_smoothing_iterations = prm->max_smoothing_iterations;
+  hp.CFL_condition = 0.1f;
+  hp.viscosity.alpha = prm->viscosity_alpha;
+  hp.use_mass_weighted_num_ngb = 0;
+
+  struct cosmology cosmo;
+  cosmology_init_no_cosmo(&cosmo);
+
+  struct engine engine;
+  bzero(&engine, sizeof(engine));
+  engine.hydro_properties = &hp;
+  engine.physical_constants = &prog_const;
+  engine.s = &space;
+  engine.time = 0.1f;
+  engine.ti_current = ti_current;
+  engine.max_active_bin = prm->max_active_bin;
+  engine.nodeID = 0;
+  engine.cosmology = &cosmo;
+  engine.time_base = 1e-3;
+  engine.policy = engine_policy_hydro;
+  struct lightcone_array_props lcp;
+  bzero(&lcp, sizeof(lcp));
+  engine.lightcone_array_properties = &lcp;
+  struct pressure_floor_props pfloor;
+  bzero(&pfloor, sizeof(pfloor));
+  engine.pressure_floor_props = &pfloor;
+  space.e = &engine;
+
+  struct runner runner;
+  bzero(&runner, sizeof(runner));
+  runner.e = &engine;
+
+  /* ---- cells ---- */
+  struct cell *cells = NULL;
+  if (posix_memalign((void **)&cells, cell_align, (size_t)ncells * sizeof(struct cell)) != 0) return 1;
+  bzero(cells, (size_t)ncells * sizeof(struct cell));
+  for (int k = 0; k < ncells; k++) {
+    struct cell *c = &cells[k];
+    for (int d = 0; d < 3; d++) {
+      c->loc[d] = cd[k].loc[d];
+      c->width[d] = cd[k].width[d];
+    }
+    c->dmin = fmin(c->width[0], fmin(c->width[1], c->width[2]));
+    c->depth = cd[k].depth;
+    c->split = cd[k].split;
+    c->parent = cd[k].parent >= 0 ? &cells[cd[k].parent] : NULL;
+    for (int j = 0; j < 8; j++)
+      c->progeny[j] = cd[k].progeny[j] >= 0 ? &cells[cd[k].progeny[j]] : NULL;
+    c->hydro.parts = &parts[cd[k].first];
+    c->hydro.xparts = &xparts[cd[k].first];
+    c->hydro.count = cd[k].count;
+    float h_max = 0.f;
+    for (int j = 0; j < c->hydro.count; j++) h_max = max(h_max, c->hydro.parts[j].h);
+    c->hydro.h_max = h_max;
+    c->hydro.h_max_old = h_max;
+    c->hydro.h_max_active = h_max;
+    c->hydro.ti_old_part = ti_current;
+    c->hydro.ti_end_min = cell_has_active(c, &engine) ? ti_current : 2 * ti_current;
+    c->nodeID = 0;
+  }
+  for (int k = 0; k < ncells; k++) {
+    struct cell *top = &cells[k];
+    while (top->parent != NULL) top = top->parent;
+    cells[k].top = top;
+    cells[k].hydro.super = top;
+    cells[k].super = top;
+  }
+
+  /* ---- tasks and their links ---- */
+  struct task *tasks = (struct task *)calloc((size_t)ntasks + 1, sizeof(struct task));
+  struct link *links = (struct link *)calloc(2 * (size_t)ntasks + 2, sizeof(struct link));
+  int nlinks = 0;
+  for (int k = 0; k < ntasks; k++) {
+    struct task *t = &tasks[k];
+    t->ci = &cells[td[k].ci];
+    t->cj = td[k].cj >= 0 ? &cells[td[k].cj] : NULL;
+    t->subtype = task_subtype_density;
+    switch (td[k].type) {
+      case ORACLE_TASK_SELF: t->type = task_type_self; break;
+      case ORACLE_TASK_PAIR: t->type = task_type_pair; break;
+      case ORACLE_TASK_SUB_SELF: t->type = task_type_sub_self; break;
+      default: t->type = task_type_sub_pair; break;
+    }
+    add_link(t->ci, t, links, &nlinks);
+    if (t->cj != NULL) add_link(t->cj, t, links, &nlinks);
+  }
+
+  g_log = (prm->record_pairs && log) ? log : NULL;
+  if (log) {
+    log->count[0] = log->count[1] = log->count[2] = 0;
+    log->ghost_sweeps = 0;
+  }
+
+  /* ---- init + sort (all 13 axes on every top-level cell) ---- */
+  for (int k = 0; k < n; k++) hydro_init_part(&parts[k], &space.hs);
+  for (int k = 0; k < ncells; k++)
+    if (cells[k].parent == NULL && cells[k].hydro.count > 0)
+      runner_do_hydro_sort(&runner, &cells[k], 0x1FFF, 0, 0, 0);
+
+  /* ---- density ---- */
+  g_stage = 0;
+  for (int k = 0; k < ntasks; k++) {
+    struct task *t = &tasks[k];
+    switch (t->type) {
+      case task_type_self: runner_doself1_branch_density(&runner, t->ci); break;
+      case task_type_pair: runner_dopair1_branch_density(&runner, t->ci, t->cj); break;
+      case task_type_sub_self: runner_dosub_self1_density(&runner, t->ci, 0); break;
+      default: runner_dosub_pair1_density(&runner, t->ci, t->cj, 0); break;
+    }
+  }
+  for (int k = 0; k < n; k++) {
+    const struct part *p = &parts[k];
+    if (io->d_rho) io->d_rho[k] = p->rho;
+    if (io->d_rho_dh) io->d_rho_dh[k] = p->density.rho_dh;
+    if (io->d_wcount) io->d_wcount[k] = p->density.wcount;
+    if (io->d_wcount_dh) io->d_wcount_dh[k] = p->density.wcount_dh;
+    if (io->d_div_v) io->d_div_v[k] = p->density.div_v;
+    if (io->d_rot_v)
+      for (int d = 0; d < 3; d++) io->d_rot_v[3 * k + d] = p->density.rot_v[d];
+  }
+
+  /* ---- ghost ---- */
+  g_stage = 1;
+  for (int k = 0; k < ncells; k++)
+    if (cells[k].parent == NULL) runner_do_ghost(&runner, &cells[k], 0);
+  for (int k = 0; k < n; k++) {
+    const struct part *p = &parts[k];
+    if (io->g_h) io->g_h[k] = p->h;
+    if (io->g_rho) io->g_rho[k] = p->rho;
+    if (io->g_f) io->g_f[k] = p->force.f;
+    if (io->g_pressure) io->g_pressure[k] = p->force.pressure;
+    if (io->g_soundspeed) io->g_soundspeed[k] = p->force.soundspeed;
+    if (io->g_balsara) io->g_balsara[k] = p->force.balsara;
+  }
+
+  /* ---- force ---- */
+  g_stage = 2;
+  for (int k = 0; k < ntasks; k++) {
+    struct task *t = &tasks[k];
+    switch (t->type) {
+      case task_type_self: runner_doself2_branch_force(&runner, t->ci); break;
+      case task_type_pair: runner_dopair2_branch_force(&runner, t->ci, t->cj); break;
+      case task_type_sub_self: runner_dosub_self2_force(&runner, t->ci, 0); break;
+      default: runner_dosub_pair2_force(&runner, t->ci, t->cj, 0); break;
+    }
+  }
+  for (int k = 0; k < ncells; k++)
+    if (cells[k].parent == NULL) runner_do_end_hydro_force(&runner, &cells[k], 0);
+  for (int k = 0; k < n; k++) {
+    const struct part *p = &parts[k];
+    if (io->f_a)
+      for (int d = 0; d < 3; d++) io->f_a[3 * k + d] = p->a_hydro[d];
+    if (io->f_u_dt) io->f_u_dt[k] = p->u_dt;
+    if (io->f_h_dt) io->f_h_dt[k] = p->force.h_dt;
+    if (io->f_v_sig) io->f_v_sig[k] = p->force.v_sig;
+    if (io->f_min_ngb_time_bin) io->f_min_ngb_time_bin[k] = p->limiter_data.min_ngb_time_bin;
+  }
+
+  g_log = NULL;
+  for (int k = 0; k < ncells; k++) cell_free_hydro_sorts(&cells[k]);
+  free(links);
+  free(tasks);
+  free(cells);
+  free(parts);
+  free(xparts);
+  return 0;
+}
+
+/* The reference's eos_init() result, for the Planetary build (filled below). */
+#ifndef PLANETARY_SPH
+int ref_get_eos(oracle_eos *out) {
+  (void)out;
+  return 1;
+}
+#endif

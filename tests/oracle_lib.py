@@ -1,0 +1,208 @@
+"""ctypes bindings of the TEST-ONLY checkers: oracle/liboracle.so (plain-C
+restatement) and oracle/_ref/libswiftref_*.so (the reference's own compiled
+operators behind oracle/ref_harness.c).  Never imported by the product."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+
+
+class Cell(C.Structure):
+    _fields_ = [("loc", C.c_double * 3), ("width", C.c_double * 3), ("first", C.c_int), ("count", C.c_int),
+                ("parent", C.c_int), ("progeny", C.c_int * 8), ("depth", C.c_int), ("split", C.c_int)]
+
+
+class Task(C.Structure):
+    _fields_ = [("type", C.c_int), ("ci", C.c_int), ("cj", C.c_int)]
+
+
+class Params(C.Structure):
+    _fields_ = [("dim", C.c_double * 3), ("periodic", C.c_int), ("eta_neighbours", C.c_float),
+                ("h_tolerance", C.c_float), ("h_max", C.c_float), ("h_min", C.c_float),
+                ("max_smoothing_iterations", C.c_int), ("viscosity_alpha", C.c_float),
+                ("max_active_bin", C.c_int), ("record_pairs", C.c_int), ("scheme", C.c_int)]
+
+
+class Til(C.Structure):
+    _fields_ = [(k, C.c_float) for k in
+                ("rho_0", "a", "b", "A", "B", "u_0", "u_iv", "u_cv", "alpha", "beta", "eta_min", "eta_zero", "P_min")] \
+        + [("mat_id", C.c_int)]
+
+
+class Eos(C.Structure):
+    _fields_ = [("n_til", C.c_int), ("til", Til * 8), ("idg_gamma", C.c_float * 4)]
+
+
+_FP = C.POINTER(C.c_float)
+
+
+class Parts(C.Structure):
+    _fields_ = [("n", C.c_int), ("x", C.POINTER(C.c_double)), ("v", _FP), ("mass", _FP), ("h", _FP), ("u", _FP),
+                ("mat_id", C.POINTER(C.c_int)), ("id", C.POINTER(C.c_longlong)), ("time_bin", C.POINTER(C.c_byte)),
+                ("d_rho", _FP), ("d_rho_dh", _FP), ("d_wcount", _FP), ("d_wcount_dh", _FP), ("d_div_v", _FP),
+                ("d_rot_v", _FP),
+                ("g_h", _FP), ("g_rho", _FP), ("g_f", _FP), ("g_pressure", _FP), ("g_soundspeed", _FP),
+                ("g_balsara", _FP),
+                ("f_a", _FP), ("f_u_dt", _FP), ("f_h_dt", _FP), ("f_v_sig", _FP),
+                ("f_min_ngb_time_bin", C.POINTER(C.c_byte))]
+
+
+class PairLog(C.Structure):
+    _fields_ = [("pairs", C.POINTER(C.c_longlong) * 3), ("capacity", C.c_longlong * 3),
+                ("count", C.c_longlong * 3), ("ghost_sweeps", C.c_int)]
+
+
+OUT_FIELDS = {"d_rho": 1, "d_rho_dh": 1, "d_wcount": 1, "d_wcount_dh": 1, "d_div_v": 1, "d_rot_v": 3,
+              "g_h": 1, "g_rho": 1, "g_f": 1, "g_pressure": 1, "g_soundspeed": 1, "g_balsara": 1,
+              "f_a": 3, "f_u_dt": 1, "f_h_dt": 1, "f_v_sig": 1}
+
+_libs = {}
+
+
+def build_oracle():
+    subprocess.run(["make", "-C", ORACLE_DIR, "liboracle.so"], check=True, capture_output=True)
+
+
+def oracle():
+    if "oracle" not in _libs:
+        path = os.path.join(ORACLE_DIR, "liboracle.so")
+        if not os.path.exists(path):
+            build_oracle()
+        lib = C.CDLL(path)
+        lib.oracle_build_tree.restype = C.c_int
+        lib.oracle_build_tasks.restype = C.c_int
+        lib.oracle_run_step.restype = C.c_int
+        lib.oracle_free.argtypes = [C.c_void_p]
+        _libs["oracle"] = lib
+    return _libs["oracle"]
+
+
+def ref_available(variant="minimal"):
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libswiftref_%s.so" % variant))
+
+
+def ref(variant="minimal"):
+    key = "ref_" + variant
+    if key not in _libs:
+        lib = C.CDLL(os.path.join(ORACLE_DIR, "_ref", "libswiftref_%s.so" % variant))
+        lib.ref_run_step.restype = C.c_int
+        lib.ref_get_eos.restype = C.c_int
+        _libs[key] = lib
+    return _libs[key]
+
+
+def make_params(dim=(1.0, 1.0, 1.0), periodic=True, eta=1.2348, h_tolerance=1e-4, h_max=1e10, h_min=0.0,
+                max_iter=30, alpha=0.8, max_active_bin=56, record=False, scheme=0):
+    p = Params()
+    p.dim[:] = dim
+    p.periodic = int(periodic)
+    p.eta_neighbours = eta
+    p.h_tolerance = h_tolerance
+    p.h_max = h_max
+    p.h_min = h_min
+    p.max_smoothing_iterations = max_iter
+    p.viscosity_alpha = alpha
+    p.max_active_bin = max_active_bin
+    p.record_pairs = int(record)
+    p.scheme = scheme
+    return p
+
+
+def build_tree_and_tasks(prm, x, h):
+    """Returns (order, cells ndarray-of-struct ctypes array, cdim, tasks ctypes array)."""
+    lib = oracle()
+    n = len(h)
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    h = np.ascontiguousarray(h, dtype=np.float32)
+    order = np.empty(n, dtype=np.int32)
+    cells_p = C.POINTER(Cell)()
+    ncells = C.c_int()
+    cdim = (C.c_int * 3)()
+    rc = lib.oracle_build_tree(C.byref(prm), n, x.ctypes.data_as(C.c_void_p), h.ctypes.data_as(C.c_void_p),
+                               order.ctypes.data_as(C.c_void_p), C.byref(cells_p), C.byref(ncells), cdim)
+    if rc != 0:
+        raise RuntimeError("oracle_build_tree failed rc=%d" % rc)
+    cells = (Cell * ncells.value)()
+    C.memmove(cells, cells_p, C.sizeof(Cell) * ncells.value)
+    lib.oracle_free(cells_p)
+    hs = np.ascontiguousarray(h[order])
+    tasks_p = C.POINTER(Task)()
+    ntasks = C.c_int()
+    lib.oracle_build_tasks(C.byref(prm), ncells.value, cells, cdim, hs.ctypes.data_as(C.c_void_p),
+                           C.byref(tasks_p), C.byref(ntasks))
+    tasks = (Task * max(ntasks.value, 1))()
+    C.memmove(tasks, tasks_p, C.sizeof(Task) * ntasks.value)
+    lib.oracle_free(tasks_p)
+    return order, cells, tuple(cdim), tasks, ntasks.value
+
+
+def run_step(which, prm, ic, cells, tasks, ntasks, record=False, pair_capacity=None, eos=None, variant="minimal"):
+    """ic: dict with x[n,3] f64, v[n,3], mass, h, u (f32), id (i64), optional mat_id, time_bin -- already in CELL ORDER.
+    which: 'oracle' or 'ref'.  Returns dict of outputs (+ 'pairs', 'counts', 'ghost_sweeps')."""
+    n = len(ic["h"])
+    keep = []
+
+    def arr(a, dt):
+        a = np.ascontiguousarray(a, dtype=dt)
+        keep.append(a)
+        return a
+
+    P = Parts()
+    P.n = n
+    x = arr(ic["x"], np.float64)
+    P.x = x.ctypes.data_as(C.POINTER(C.c_double))
+    for k in ("v", "mass", "h", "u"):
+        a = arr(ic[k], np.float32)
+        setattr(P, k, a.ctypes.data_as(_FP))
+    ids = arr(ic["id"], np.int64)
+    P.id = ids.ctypes.data_as(C.POINTER(C.c_longlong))
+    if ic.get("mat_id") is not None:
+        m = arr(ic["mat_id"], np.int32)
+        P.mat_id = m.ctypes.data_as(C.POINTER(C.c_int))
+    if ic.get("time_bin") is not None:
+        tb = arr(ic["time_bin"], np.int8)
+        P.time_bin = tb.ctypes.data_as(C.POINTER(C.c_byte))
+    out = {}
+    for k, w in OUT_FIELDS.items():
+        out[k] = np.zeros((n, w) if w > 1 else n, dtype=np.float32)
+        setattr(P, k, out[k].ctypes.data_as(_FP))
+    out["f_min_ngb_time_bin"] = np.zeros(n, dtype=np.int8)
+    P.f_min_ngb_time_bin = out["f_min_ngb_time_bin"].ctypes.data_as(C.POINTER(C.c_byte))
+    log = PairLog()
+    bufs = []
+    prm.record_pairs = int(record)
+    if record:
+        cap = pair_capacity or (n * 400)
+        for s in range(3):
+            b = np.zeros((cap, 2), dtype=np.int64)
+            bufs.append(b)
+            log.pairs[s] = b.ctypes.data_as(C.POINTER(C.c_longlong))
+            log.capacity[s] = cap
+    ncells = len(cells)
+    if which == "oracle":
+        e = eos if eos is not None else Eos()
+        rc = oracle().oracle_run_step(C.byref(prm), C.byref(e), C.byref(P), ncells, cells, ntasks, tasks, C.byref(log))
+    else:
+        rc = ref(variant).ref_run_step(C.byref(prm), C.byref(P), ncells, cells, ntasks, tasks, C.byref(log))
+    if rc != 0:
+        raise RuntimeError("%s run_step rc=%d" % (which, rc))
+    out["counts"] = [int(log.count[s]) for s in range(3)]
+    out["ghost_sweeps"] = int(log.ghost_sweeps)
+    if record:
+        out["pairs"] = []
+        for s in range(3):
+            assert log.count[s] <= log.capacity[s], "pair buffer too small"
+            out["pairs"].append(bufs[s][:log.count[s]].copy())
+    return out
+
+
+def sorted_pairs(p):
+    """Canonical (lexicographically sorted) copy of an [m,2] pair list."""
+    if len(p) == 0:
+        return p
+    idx = np.lexsort((p[:, 1], p[:, 0]))
+    return p[idx]
