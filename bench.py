@@ -1,0 +1,260 @@
+#!/usr/bin/env python
+"""Benchmark of the SPH neighbour-loop hot path (density + ghost + force).
+
+metric : ordered SPH pair interactions per second over one density+ghost+force
+         step, whole job.
+value  : device-timed, particles resident in HBM (CUDA events around the step).
+e2e    : the same step through the public C ABI with HOST buffers: H2D of the
+         step's particle state and D2H of its results inside the timed region.
+--impl reference : the reference's own CPU operators (oracle/_ref, compiled from
+         /root/reference; the plain-C oracle port when that is absent) on all
+         host cores, on bounded samples of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "sph_pair_interactions_per_sec"
+UNIT = "interactions/s"
+FLOP_DENSITY, FLOP_FORCE = 66, 122  # algorithmic flop per ordered interaction
+
+
+def workload(args):
+    side = args.side
+    return {"workload": "periodic uniform-random box %d^3 (%d particles), ~48 neighbours, density+ghost+force, "
+                        "Minimal SPH + ideal gas" % (side, side ** 3),
+            "side": side, "seed": 42,
+            "l2": "inputs (>=180 B/particle resident) exceed the 126 MB L2 for side >= 96; no explicit flush",
+            "sort_in_step": True}
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nme, val in zip(names, f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------- CPU arm
+def _cpu_worker(argtuple):
+    side, seed, use_ref = argtuple
+    import oracle_lib as ol
+    from swift_subtask_dev_b200 import ics
+    ic = ics.uniform_random(side ** 3, seed=seed)
+    prm = ol.make_params()
+    order, cells, cdim, tasks, nt = ol.build_tree_and_tasks(prm, ic["x"], ic["h"])
+    icc = ics.permute(ic, order)
+    t0 = time.perf_counter()
+    o = ol.run_step("ref" if use_ref else "oracle", prm, icc, cells, tasks, nt, record=False)
+    dt = time.perf_counter() - t0
+    return sum(o["counts"]), dt
+
+
+def cpu_arm(sample_side, nproc, reps=1):
+    """Reference CPU operators on `nproc` host processes, each stepping its own
+    sample_side^3 sample of the workload.  Returns (interactions/s aggregate, description)."""
+    import multiprocessing as mp
+    import oracle_lib as ol
+    use_ref = ol.ref_available("minimal")
+    if not use_ref:
+        ol.build_oracle()
+    jobs = [(sample_side, 1000 + k, use_ref) for k in range(nproc * reps)]
+    t0 = time.perf_counter()
+    with mp.get_context("fork").Pool(nproc) as pool:
+        res = pool.map(_cpu_worker, jobs, chunksize=1)
+    wall = time.perf_counter() - t0
+    total = sum(r[0] for r in res)
+    # tree building / IC generation are outside the operators: use the summed operator time per process
+    busy = max(sum(r[1] for r in res[k::nproc]) for k in range(nproc))
+    return total / busy, {"kind": "reference" if use_ref else "port", "cores": nproc,
+                          "sample": "%d independent %d^3 uniform-random periodic boxes (one per process), "
+                                    "sort+density+ghost+force by the reference's runner_* operators, single "
+                                    "thread each" % (nproc * reps, sample_side),
+                          "wall_s": wall, "interactions": total}
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+# --------------------------------------------------------------------------- main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--side", type=int, default=256, help="particles per box side (BASELINE configs[1]: 256)")
+    ap.add_argument("--cpu-side", type=int, default=64)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    cfg = workload(args)
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        nproc = host_cores()
+        for _ in range(max(args.warmup, 0) and 1):
+            cpu_arm(32, nproc)
+        t0 = time.perf_counter()
+        vals = []
+        for _ in range(args.steps):
+            v, desc = cpu_arm(args.cpu_side, nproc)
+            vals.append(v)
+        dt = time.perf_counter() - t0
+        v = float(np.mean(vals))
+        desc["value"] = v
+        desc["unit"] = UNIT
+        print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+                          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                          "data": "synthetic", "config": cfg, "cpu_baseline": desc,
+                          "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return 0
+
+    import torch
+    from swift_subtask_dev_b200 import HydroBackend, ics, make_params
+    if world > 1:
+        from swift_subtask_dev_b200 import multi
+        return multi.bench_multi(args, cfg, METRIC, UNIT)
+
+    torch.cuda.set_device(0)
+    ic = ics.uniform_random(args.side ** 3, seed=cfg["seed"])
+    n = len(ic["h"])
+    be = HydroBackend(make_params())
+    t0 = time.perf_counter()
+    be.build(ic)
+    build_s = time.perf_counter() - t0
+
+    for _ in range(args.warmup):
+        be.step()
+    sampler = ClockSampler(0)
+    sampler.start()
+    torch.cuda.synchronize()
+    times, phase = [], {"sort_ms": 0.0, "density_ms": 0.0, "ghost_ms": 0.0, "force_ms": 0.0}
+    launches = 0
+    for _ in range(args.steps):
+        be.step()
+        t = be.timings()
+        times.append(t["total_ms"])
+        for k in phase:
+            phase[k] += t[k]
+        launches += be.counters()["n_kernel_launches"]
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    cnt = be.counters()
+    inter = cnt["n_density"] + cnt["n_density_redo"] + cnt["n_force"]
+    ms = float(np.mean(times))
+    value = inter / (ms * 1e-3)
+
+    # ---- end to end through the C ABI with host buffers
+    e2e_times = []
+    h2d = n * (24 + 12 + 4 + 4 + 4)
+    d2h = n * 4 * (1 + 1 + 1 + 1 + 1 + 1 + 3 + 1 + 1 + 1) + n
+    for k in range(max(1, min(args.steps, 2)) + 1):
+        t0 = time.perf_counter()
+        be.update_particles(ic)
+        be.step()
+        be.results()
+        dt = time.perf_counter() - t0
+        if k > 0:
+            e2e_times.append(dt)
+    e2e_value = inter / float(np.mean(e2e_times))
+
+    # ---- roofline of the dominant kernel (FP32 CUDA-core bound, BASELINE.md "Roofline")
+    dom = max(("density_ms", "ghost_ms", "force_ms"), key=lambda k: phase[k])
+    flops = {"density_ms": FLOP_DENSITY * cnt["n_density"], "ghost_ms": FLOP_DENSITY * cnt["n_density_redo"],
+             "force_ms": FLOP_FORCE * cnt["n_force"]}[dom]
+    kern_ms = phase[dom] / args.steps
+    achieved = flops / (kern_ms * 1e-3) / 1e12
+    sm_mhz = clocks.get("sm_mhz") or 1965.0
+    peak_nominal = 148 * 128 * 2 * 1965e6 / 1e12
+    roofline = {"bound": "fp32", "kernel": {"density_ms": "k_density<0>", "ghost_ms": "k_density<1> (ghost redo sweeps)",
+                                             "force_ms": "k_force"}[dom],
+                "achieved": achieved, "peak": peak_nominal, "unit": "TFLOP/s", "frac": achieved / peak_nominal,
+                "peak_source": "148 SMs x 128 lanes x 2 x 1965 MHz (MEASURED_PEAKS.json has no FP32 entry)",
+                "peak_at_observed_clock": 148 * 128 * 2 * sm_mhz * 1e6 / 1e12, "traffic": None,
+                "hbm_step": {"achieved_gbs": 223.0 * n / (ms * 1e-3) / 1e9, "peak_gbs": 6540.8,
+                             "note": "223 B/particle/step algorithmic (SURVEY 8(d)) over the whole step"}}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": cfg, "clocks": clocks, "gpu_launches": launches,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "roofline": roofline,
+            "detail": {"n_particles": n, "interactions_per_step": inter, "n_density": cnt["n_density"],
+                       "n_density_redo": cnt["n_density_redo"], "n_force": cnt["n_force"],
+                       "ghost_sweeps": cnt["ghost_sweeps"], "phase_ms": {k: v / args.steps for k, v in phase.items()},
+                       "build_s": build_s, "leaf_interactions": cnt["n_leaf_interactions"]}}
+    if not args.no_cpu:
+        nproc = host_cores()
+        v, desc = cpu_arm(args.cpu_side, nproc)
+        desc["value"] = v
+        desc["unit"] = UNIT
+        line["cpu_baseline"] = desc
+    print(json.dumps(line))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,210 @@
+/* swift_cuda.h -- C ABI of the B200-native SPH neighbour-loop backend.
+ *
+ * This is the whole drop-in boundary: plain pointers and sizes, no C++ or
+ * torch types.  It replaces, for one (sub-)step of a two-loop SPH scheme
+ * (Minimal or Planetary), the reference's task subgraph
+ *
+ *   sort -> density(self/pair/sub) -> ghost -> force(self/pair/sub) -> end_force
+ *
+ * i.e. the operators declared in
+ *   src/runner_doiact_hydro.h:168-191   runner_do{self,pair}{1,2}_branch_{density,force},
+ *                                       runner_dosub_{self,pair}{1,2}_{density,force},
+ *                                       runner_do{self,pair}_subset_branch_density,
+ *                                       runner_dosub_subset_density
+ *   src/runner.h:94-119                 runner_do_ghost, runner_do_hydro_sort,
+ *                                       runner_do_end_hydro_force
+ * and called from src/runner_main.c:196-204, 246-254, 294-302, 340-348,
+ * 386-394, 417-418, 455-456.  INTEGRATION.md shows the C shim a SWIFT
+ * maintainer adds in src/cuda/ to route those tasks here.
+ *
+ * Error convention: every function returns 0 on success, non-zero on failure;
+ * swift_cuda_last_error() gives the message.  (The reference aborts through
+ * error(), src/error.h:42-78; the shim turns a non-zero status into error().)
+ * There is no CPU fallback: without a CUDA device every compute entry fails. */
+#ifndef SWIFT_CUDA_H
+#define SWIFT_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SWIFT_CUDA_ABI_VERSION 1
+
+enum { SWIFT_CUDA_SCHEME_MINIMAL = 0, SWIFT_CUDA_SCHEME_PLANETARY = 1 };
+
+/* Tillotson material, INTERNAL units -- a copy of the reference's
+ * struct Til_params after convert_units_Til
+ * (src/equation_of_state/planetary/tillotson.h:43-143). */
+typedef struct {
+  float rho_0, a, b, A, B, u_0, u_iv, u_cv, alpha, beta, eta_min, eta_zero, P_min;
+  int mat_id;
+} swift_cuda_til;
+
+/* Run-time scalars the operators read through r->e:
+ * e->s->dim/periodic, e->hydro_properties->{eta_neighbours, h_tolerance, h_max,
+ * h_min, max_smoothing_iterations, viscosity.alpha}, e->max_active_bin,
+ * e->cosmology->{a, H}. */
+typedef struct {
+  double dim[3];
+  int periodic;
+  float eta_neighbours;
+  float h_tolerance;
+  float h_max;
+  float h_min;
+  int max_smoothing_iterations;
+  float viscosity_alpha;
+  int max_active_bin;
+  int scheme;      /* SWIFT_CUDA_SCHEME_* */
+  float cosmo_a;   /* 1 without cosmology */
+  float cosmo_H;   /* 0 without cosmology */
+  int n_til;
+  swift_cuda_til til[8];
+  float idg_gamma[4]; /* planetary ideal-gas gammas for mat_id 0..3 */
+} swift_cuda_params;
+
+/* One cell of the caller's tree: struct cell {loc, width, hydro.parts - parts,
+ * hydro.count, parent, progeny, depth, split} (src/cell.h:354). */
+typedef struct {
+  double loc[3];
+  double width[3];
+  int first;
+  int count;
+  int parent;
+  int progeny[8];
+  int depth;
+  int split;
+} swift_cuda_cell;
+
+/* One hydro task as left by scheduler_splittask_hydro (src/scheduler.c:1154):
+ * type 0 self, 1 pair, 2 sub_self, 3 sub_pair. */
+typedef struct {
+  int type;
+  int ci;
+  int cj;
+} swift_cuda_task;
+
+/* Particle arrays, host memory, n entries each ([n][3] row-major for x, v).
+ * Field meaning as struct part (src/hydro/Minimal/hydro_part.h:98-189). */
+typedef struct {
+  int64_t n;
+  const double *x;
+  const float *v;
+  const float *mass;
+  const float *h;
+  const float *u;
+  const int32_t *mat_id;  /* Planetary only; may be NULL */
+  const int8_t *time_bin; /* may be NULL: all particles in bin 1 */
+  const int64_t *id;      /* may be NULL: ids are the input positions */
+} swift_cuda_parts_in;
+
+/* Results, host memory, written in the caller's particle order; any pointer
+ * may be NULL.  a[n][3]. */
+typedef struct {
+  float *h;          /* p->h after the ghost */
+  float *rho;        /* p->rho */
+  float *pressure;   /* p->force.pressure */
+  float *soundspeed; /* p->force.soundspeed */
+  float *f;          /* p->force.f (grad-h term) */
+  float *balsara;    /* p->force.balsara */
+  float *a;          /* p->a_hydro */
+  float *u_dt;       /* p->u_dt */
+  float *h_dt;       /* p->force.h_dt after hydro_end_force */
+  float *v_sig;      /* p->force.v_sig */
+  int8_t *min_ngb_time_bin; /* p->limiter_data.min_ngb_time_bin */
+  /* raw neighbour sums of the FIRST density pass (before hydro_end_density) */
+  float *d_rho, *d_rho_dh, *d_wcount, *d_wcount_dh, *d_div_v, *d_rot_v;
+} swift_cuda_parts_out;
+
+/* Integer work counters of the last step (BASELINE.md "Metric"). */
+typedef struct {
+  long long n_density;      /* ordered hits of the first density pass */
+  long long n_density_redo; /* ordered hits of all ghost redo sweeps */
+  long long n_force;        /* ordered hits of the force loop */
+  int ghost_sweeps;         /* redo sweeps that had work */
+  int ghost_unconverged;    /* particles left unconverged (error if > 0) */
+  long long n_leaf_interactions; /* direct self + pair cell interactions */
+  long long n_sort_entries;      /* sort entries built */
+  int n_kernel_launches;         /* kernels launched by the last step */
+} swift_cuda_counters;
+
+/* Device timings of the last step, milliseconds (CUDA events). */
+typedef struct {
+  float sort_ms, density_ms, ghost_ms, force_ms, total_ms;
+} swift_cuda_timings;
+
+typedef struct swift_cuda_ctx swift_cuda_ctx;
+
+int swift_cuda_abi_version(void);
+const char *swift_cuda_last_error(void);
+
+/* Context on CUDA device `device`. */
+int swift_cuda_create(const swift_cuda_params *params, int device, swift_cuda_ctx **out);
+void swift_cuda_destroy(swift_cuda_ctx *ctx);
+
+/* (A) Library-built tree: bins the particles into the top-level grid and
+ * octree exactly as space_regrid / space_split do (src/space_regrid.c:120-301,
+ * src/space_split.c:199-262), creates and splits the hydro tasks
+ * (src/engine_maketasks.c:4060-4182, src/scheduler.c:1154-1378), packs the
+ * particles to the device in cell order.  Role of cache.h / space_rebuild. */
+int swift_cuda_build_from_particles(swift_cuda_ctx *ctx, const swift_cuda_parts_in *parts);
+
+/* (B) Caller-built tree (the drop-in path): particles are already in cell
+ * order (a cell's particles are [first, first+count)), `cells` and `tasks`
+ * describe the caller's struct cell tree and density task list. */
+int swift_cuda_build_from_cells(swift_cuda_ctx *ctx, const swift_cuda_parts_in *parts, int ncells,
+                                const swift_cuda_cell *cells, int ntasks, const swift_cuda_task *tasks);
+
+/* Refresh particle state (x, v, h, u, time_bin) after a drift with the tree
+ * unchanged; same order as the build call. */
+int swift_cuda_update_particles(swift_cuda_ctx *ctx, const swift_cuda_parts_in *parts);
+
+/* One density -> ghost -> force -> end_force pass on the device.  `do_sort`
+ * rebuilds the 13-axis sorts first (runner_do_hydro_sort). */
+int swift_cuda_step(swift_cuda_ctx *ctx, int do_sort);
+
+/* Operator-level entry points (same phases, separately callable; used by the
+ * per-task shims and the parity tests). */
+int swift_cuda_do_sort(swift_cuda_ctx *ctx);
+int swift_cuda_do_density(swift_cuda_ctx *ctx);
+int swift_cuda_do_ghost(swift_cuda_ctx *ctx);
+int swift_cuda_do_force(swift_cuda_ctx *ctx);
+
+int swift_cuda_get_results(swift_cuda_ctx *ctx, const swift_cuda_parts_out *out);
+int swift_cuda_get_counters(swift_cuda_ctx *ctx, swift_cuda_counters *out);
+int swift_cuda_get_timings(swift_cuda_ctx *ctx, swift_cuda_timings *out);
+
+/* Tree introspection (library-built tree): sizes, then copies. */
+int swift_cuda_get_tree_size(swift_cuda_ctx *ctx, int *ncells, int *ntasks, int cdim[3]);
+int swift_cuda_get_tree(swift_cuda_ctx *ctx, swift_cuda_cell *cells, swift_cuda_task *tasks, int32_t *order);
+
+/* Host-only planning (no GPU needed): the tree, task list and flattened
+ * interaction count the library would build for these particles.  Arrays are
+ * malloc'ed by the library; release with swift_cuda_host_free.  `order` has n
+ * entries (caller-allocated). */
+int swift_cuda_host_plan(const swift_cuda_params *params, const swift_cuda_parts_in *parts,
+                         swift_cuda_cell **cells, int *ncells, swift_cuda_task **tasks, int *ntasks,
+                         int32_t *order, int cdim[3], long long *n_interactions, long long *n_items);
+void swift_cuda_host_free(void *p);
+
+/* Test hook: record ordered (updated id, neighbour id) pairs of the next
+ * phases into device buffers of `capacity` pairs per loop
+ * (0 first density pass, 1 redo sweeps, 2 force); fetch copies them out. */
+int swift_cuda_record_pairs(swift_cuda_ctx *ctx, long long capacity);
+int swift_cuda_fetch_pairs(swift_cuda_ctx *ctx, int loop, long long *pairs, long long capacity, long long *count);
+
+/* Multi-GPU: device pointers of the packed halo buffers so a
+ * host can move them with NCCL send/recv (phase 0: xv before density, phase 1:
+ * rho after the ghost).  See swift_subtask_dev_b200/halo.py. */
+int swift_cuda_halo_pack(swift_cuda_ctx *ctx, int phase, const int32_t *d_index, int64_t count, void *d_buffer,
+                         void *stream);
+int swift_cuda_halo_unpack(swift_cuda_ctx *ctx, int phase, const int32_t *d_index, int64_t count,
+                           const void *d_buffer, void *stream);
+size_t swift_cuda_halo_bytes_per_particle(int phase);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SWIFT_CUDA_H */

@@ -36,13 +36,14 @@
 
 /* ---- pair log ----------------------------------------------------------- */
 static oracle_pairlog *g_log = NULL;
+static int g_store = 0;
 static int g_stage = 0; /* 0 density, 1 ghost redo, 2 force */
 
 void ref_record_pair(int loop, long long id_updated, long long id_other) {
   if (g_log == NULL) return;
   const int slot = (loop == 1) ? 2 : g_stage;
   const long long k = g_log->count[slot]++;
-  if (g_log->pairs[slot] != NULL && k < g_log->capacity[slot]) {
+  if (g_store && g_log->pairs[slot] != NULL && k < g_log->capacity[slot]) {
     g_log->pairs[slot][2 * k] = id_updated;
     g_log->pairs[slot][2 * k + 1] = id_other;
   }
@@ -202,7 +203,8 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
     if (t->cj != NULL) add_link(t->cj, t, links, &nlinks);
   }
 
-  g_log = (prm->record_pairs && log) ? log : NULL;
+  g_log = log;
+  g_store = prm->record_pairs;
   if (log) {
     log->count[0] = log->count[1] = log->count[2] = 0;
     log->ghost_sweeps = 0;

@@ -1,0 +1,311 @@
+"""Python host-side mirror of the C ABI in include/swift_cuda.h (ctypes).
+
+The product is the shared library `libswiftcuda.so` (hand-written sm_100a
+kernels + C++ host tree/work-list builder).  This module only marshals numpy
+arrays into it; the operator names follow the reference's runner surface
+(src/runner_doiact_hydro.h:168-191, src/runner.h:94-119).  There is no CPU
+fallback: a missing library or GPU raises.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(_HERE)
+LIB_PATH = os.path.join(_HERE, "libswiftcuda.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+SCHEME_MINIMAL, SCHEME_PLANETARY = 0, 1
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared", "-fmad=false"]
+
+
+def build_library(verbose=False, force=False):
+    """Compiles the CUDA backend in-tree with nvcc for sm_100a."""
+    srcs = [os.path.join(CSRC, f) for f in ("swift_cuda.cu", "host_tree.cpp")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.cuh", "device_types.cuh", "host_tree.hpp")] + \
+        [os.path.join(ROOT, "include", "swift_cuda.h")]
+    if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
+        return LIB_PATH
+    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + srcs
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(r.stderr)
+    return LIB_PATH
+
+
+class Til(C.Structure):
+    _fields_ = [(k, C.c_float) for k in
+                ("rho_0", "a", "b", "A", "B", "u_0", "u_iv", "u_cv", "alpha", "beta", "eta_min", "eta_zero", "P_min")] \
+        + [("mat_id", C.c_int)]
+
+
+class Params(C.Structure):
+    _fields_ = [("dim", C.c_double * 3), ("periodic", C.c_int), ("eta_neighbours", C.c_float),
+                ("h_tolerance", C.c_float), ("h_max", C.c_float), ("h_min", C.c_float),
+                ("max_smoothing_iterations", C.c_int), ("viscosity_alpha", C.c_float),
+                ("max_active_bin", C.c_int), ("scheme", C.c_int), ("cosmo_a", C.c_float), ("cosmo_H", C.c_float),
+                ("n_til", C.c_int), ("til", Til * 8), ("idg_gamma", C.c_float * 4)]
+
+
+class Cell(C.Structure):
+    _fields_ = [("loc", C.c_double * 3), ("width", C.c_double * 3), ("first", C.c_int), ("count", C.c_int),
+                ("parent", C.c_int), ("progeny", C.c_int * 8), ("depth", C.c_int), ("split", C.c_int)]
+
+
+class Task(C.Structure):
+    _fields_ = [("type", C.c_int), ("ci", C.c_int), ("cj", C.c_int)]
+
+
+_FP = C.POINTER(C.c_float)
+
+
+class PartsIn(C.Structure):
+    _fields_ = [("n", C.c_int64), ("x", C.POINTER(C.c_double)), ("v", _FP), ("mass", _FP), ("h", _FP), ("u", _FP),
+                ("mat_id", C.POINTER(C.c_int32)), ("time_bin", C.POINTER(C.c_int8)), ("id", C.POINTER(C.c_int64))]
+
+
+OUT_FIELDS = [("h", 1), ("rho", 1), ("pressure", 1), ("soundspeed", 1), ("f", 1), ("balsara", 1), ("a", 3),
+              ("u_dt", 1), ("h_dt", 1), ("v_sig", 1)]
+OUT_FIRST = [("d_rho", 1), ("d_rho_dh", 1), ("d_wcount", 1), ("d_wcount_dh", 1), ("d_div_v", 1), ("d_rot_v", 3)]
+
+
+class PartsOut(C.Structure):
+    # field order must match swift_cuda_parts_out
+    _fields_ = [("h", _FP), ("rho", _FP), ("pressure", _FP), ("soundspeed", _FP), ("f", _FP), ("balsara", _FP),
+                ("a", _FP), ("u_dt", _FP), ("h_dt", _FP), ("v_sig", _FP), ("min_ngb_time_bin", C.POINTER(C.c_int8)),
+                ("d_rho", _FP), ("d_rho_dh", _FP), ("d_wcount", _FP), ("d_wcount_dh", _FP), ("d_div_v", _FP),
+                ("d_rot_v", _FP)]
+
+
+class Counters(C.Structure):
+    _fields_ = [("n_density", C.c_longlong), ("n_density_redo", C.c_longlong), ("n_force", C.c_longlong),
+                ("ghost_sweeps", C.c_int), ("ghost_unconverged", C.c_int), ("n_leaf_interactions", C.c_longlong),
+                ("n_sort_entries", C.c_longlong), ("n_kernel_launches", C.c_int)]
+
+
+class Timings(C.Structure):
+    _fields_ = [("sort_ms", C.c_float), ("density_ms", C.c_float), ("ghost_ms", C.c_float), ("force_ms", C.c_float),
+                ("total_ms", C.c_float)]
+
+
+EXPORTS = ["swift_cuda_abi_version", "swift_cuda_last_error", "swift_cuda_create", "swift_cuda_destroy",
+           "swift_cuda_build_from_particles", "swift_cuda_build_from_cells", "swift_cuda_update_particles",
+           "swift_cuda_step", "swift_cuda_do_sort", "swift_cuda_do_density", "swift_cuda_do_ghost",
+           "swift_cuda_do_force", "swift_cuda_get_results", "swift_cuda_get_counters", "swift_cuda_get_timings",
+           "swift_cuda_get_tree_size", "swift_cuda_get_tree", "swift_cuda_record_pairs", "swift_cuda_fetch_pairs",
+           "swift_cuda_halo_pack", "swift_cuda_halo_unpack", "swift_cuda_halo_bytes_per_particle",
+           "swift_cuda_host_plan", "swift_cuda_host_free"]
+
+_lib = None
+
+
+def load_library():
+    """dlopens the backend; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libswiftcuda.so is missing: run __graft_entry__.build() (no CPU fallback exists)")
+        lib = C.CDLL(LIB_PATH)
+        lib.swift_cuda_last_error.restype = C.c_char_p
+        lib.swift_cuda_halo_bytes_per_particle.restype = C.c_size_t
+        lib.swift_cuda_halo_pack.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        lib.swift_cuda_halo_unpack.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        lib.swift_cuda_destroy.argtypes = [C.c_void_p]
+        lib.swift_cuda_record_pairs.argtypes = [C.c_void_p, C.c_longlong]
+        lib.swift_cuda_fetch_pairs.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_longlong, C.c_void_p]
+        _lib = lib
+    return _lib
+
+
+class SwiftCudaError(RuntimeError):
+    pass
+
+
+def host_plan(params, ic):
+    """Host-only (no GPU): the tree, tasks and work-list size the library builds for `ic`."""
+    lib = load_library()
+    lib.swift_cuda_host_free.argtypes = [C.c_void_p]
+    n = len(ic["h"])
+    x = np.ascontiguousarray(ic["x"], dtype=np.float64)
+    h = np.ascontiguousarray(ic["h"], dtype=np.float32)
+    P = PartsIn()
+    P.n = n
+    P.x = x.ctypes.data_as(C.POINTER(C.c_double))
+    P.h = h.ctypes.data_as(_FP)
+    cells_p, tasks_p = C.POINTER(Cell)(), C.POINTER(Task)()
+    nc, nt = C.c_int(), C.c_int()
+    cdim = (C.c_int * 3)()
+    ni, nitems = C.c_longlong(), C.c_longlong()
+    order = np.zeros(n, dtype=np.int32)
+    rc = lib.swift_cuda_host_plan(C.byref(params), C.byref(P), C.byref(cells_p), C.byref(nc), C.byref(tasks_p),
+                                  C.byref(nt), order.ctypes.data_as(C.c_void_p), cdim, C.byref(ni), C.byref(nitems))
+    if rc != 0:
+        raise SwiftCudaError(lib.swift_cuda_last_error().decode())
+    cells = (Cell * max(nc.value, 1))()
+    C.memmove(cells, cells_p, C.sizeof(Cell) * nc.value)
+    tasks = (Task * max(nt.value, 1))()
+    C.memmove(tasks, tasks_p, C.sizeof(Task) * nt.value)
+    lib.swift_cuda_host_free(cells_p)
+    lib.swift_cuda_host_free(tasks_p)
+    return {"cells": cells, "ncells": nc.value, "tasks": tasks, "ntasks": nt.value, "cdim": tuple(cdim),
+            "order": order, "n_interactions": ni.value, "n_items": nitems.value}
+
+
+def make_params(dim=(1.0, 1.0, 1.0), periodic=True, eta=1.2348, h_tolerance=1e-4, h_max=1e10, h_min=0.0,
+                max_iter=30, alpha=0.8, max_active_bin=56, scheme=SCHEME_MINIMAL, til=(), idg_gamma=(5. / 3.,) * 4):
+    p = Params()
+    p.dim[:] = dim
+    p.periodic = int(periodic)
+    p.eta_neighbours = eta
+    p.h_tolerance = h_tolerance
+    p.h_max = h_max
+    p.h_min = h_min
+    p.max_smoothing_iterations = max_iter
+    p.viscosity_alpha = alpha
+    p.max_active_bin = max_active_bin
+    p.scheme = scheme
+    p.cosmo_a = 1.0
+    p.cosmo_H = 0.0
+    p.n_til = len(til)
+    for k, t in enumerate(til):
+        p.til[k] = t
+    p.idg_gamma[:] = idg_gamma
+    return p
+
+
+class HydroBackend:
+    """One GPU's SPH neighbour-loop engine.  Usage:
+        be = HydroBackend(params); be.build(ic); be.step(); out = be.results()
+    """
+
+    def __init__(self, params, device=0):
+        self.lib = load_library()
+        self.params = params
+        self.ctx = C.c_void_p()
+        self._keep = []
+        self._check(self.lib.swift_cuda_create(C.byref(params), int(device), C.byref(self.ctx)))
+        self.n = 0
+
+    def _check(self, rc):
+        if rc != 0:
+            raise SwiftCudaError(self.lib.swift_cuda_last_error().decode())
+
+    def close(self):
+        if self.ctx:
+            self.lib.swift_cuda_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _parts_in(self, ic):
+        keep = []
+
+        def arr(a, dt):
+            a = np.ascontiguousarray(a, dtype=dt)
+            keep.append(a)
+            return a
+        P = PartsIn()
+        P.n = len(ic["h"])
+        P.x = arr(ic["x"], np.float64).ctypes.data_as(C.POINTER(C.c_double))
+        for k in ("v", "mass", "h", "u"):
+            setattr(P, k, arr(ic[k], np.float32).ctypes.data_as(_FP))
+        if ic.get("mat_id") is not None:
+            P.mat_id = arr(ic["mat_id"], np.int32).ctypes.data_as(C.POINTER(C.c_int32))
+        if ic.get("time_bin") is not None:
+            P.time_bin = arr(ic["time_bin"], np.int8).ctypes.data_as(C.POINTER(C.c_int8))
+        if ic.get("id") is not None:
+            P.id = arr(ic["id"], np.int64).ctypes.data_as(C.POINTER(C.c_int64))
+        return P, keep
+
+    # ---- building (role of space_rebuild + cache packing) ----
+    def build(self, ic):
+        P, keep = self._parts_in(ic)
+        self.n = P.n
+        self._check(self.lib.swift_cuda_build_from_particles(self.ctx, C.byref(P)))
+
+    def build_from_cells(self, ic, cells, tasks, ntasks=None):
+        """ic already in cell order; cells/tasks: ctypes arrays of Cell/Task (or layout-compatible)."""
+        P, keep = self._parts_in(ic)
+        self.n = P.n
+        nt = len(tasks) if ntasks is None else ntasks
+        self._check(self.lib.swift_cuda_build_from_cells(self.ctx, C.byref(P), len(cells), cells, nt, tasks))
+
+    def update_particles(self, ic):
+        P, keep = self._parts_in(ic)
+        self._check(self.lib.swift_cuda_update_particles(self.ctx, C.byref(P)))
+
+    # ---- operators ----
+    def step(self, do_sort=True):
+        """sort -> density -> ghost -> force -> end_force."""
+        self._check(self.lib.swift_cuda_step(self.ctx, int(do_sort)))
+
+    def runner_do_hydro_sort(self):
+        self._check(self.lib.swift_cuda_do_sort(self.ctx))
+
+    def runner_do_density(self):
+        """All runner_do{self,pair}1_branch_density / runner_dosub_*1_density tasks."""
+        self._check(self.lib.swift_cuda_do_density(self.ctx))
+
+    def runner_do_ghost(self):
+        self._check(self.lib.swift_cuda_do_ghost(self.ctx))
+
+    def runner_do_force(self):
+        """All runner_do{self,pair}2_branch_force tasks + runner_do_end_hydro_force."""
+        self._check(self.lib.swift_cuda_do_force(self.ctx))
+
+    # ---- results ----
+    def results(self, first_pass=False):
+        n = self.n
+        out = {}
+        P = PartsOut()
+        fields = OUT_FIELDS + (OUT_FIRST if first_pass else [])
+        for k, w in fields:
+            out[k] = np.zeros((n, w) if w > 1 else n, dtype=np.float32)
+            setattr(P, k, out[k].ctypes.data_as(_FP))
+        out["min_ngb_time_bin"] = np.zeros(n, dtype=np.int8)
+        P.min_ngb_time_bin = out["min_ngb_time_bin"].ctypes.data_as(C.POINTER(C.c_int8))
+        self._check(self.lib.swift_cuda_get_results(self.ctx, C.byref(P)))
+        return out
+
+    def counters(self):
+        c = Counters()
+        self._check(self.lib.swift_cuda_get_counters(self.ctx, C.byref(c)))
+        return {k: getattr(c, k) for k, _ in Counters._fields_}
+
+    def timings(self):
+        t = Timings()
+        self._check(self.lib.swift_cuda_get_timings(self.ctx, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in Timings._fields_}
+
+    def tree(self):
+        nc, nt = C.c_int(), C.c_int()
+        cdim = (C.c_int * 3)()
+        self._check(self.lib.swift_cuda_get_tree_size(self.ctx, C.byref(nc), C.byref(nt), cdim))
+        cells = (Cell * max(nc.value, 1))()
+        tasks = (Task * max(nt.value, 1))()
+        order = np.zeros(self.n, dtype=np.int32)
+        self._check(self.lib.swift_cuda_get_tree(self.ctx, cells, tasks, order.ctypes.data_as(C.c_void_p)))
+        return {"cells": cells, "ncells": nc.value, "tasks": tasks, "ntasks": nt.value, "cdim": tuple(cdim),
+                "order": order}
+
+    # ---- test hook ----
+    def record_pairs(self, capacity):
+        self._check(self.lib.swift_cuda_record_pairs(self.ctx, int(capacity)))
+
+    def fetch_pairs(self, loop, capacity):
+        cnt = C.c_longlong()
+        self._check(self.lib.swift_cuda_fetch_pairs(self.ctx, loop, None, 0, C.byref(cnt)))
+        buf = np.zeros((max(cnt.value, 1), 2), dtype=np.int64)
+        self._check(self.lib.swift_cuda_fetch_pairs(self.ctx, loop, buf.ctypes.data_as(C.c_void_p), cnt.value,
+                                                    C.byref(cnt)))
+        return buf[:cnt.value]

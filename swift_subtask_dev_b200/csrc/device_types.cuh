@@ -1,0 +1,90 @@
+// Device-side data layout of the SPH backend (SoA particle caches in HBM, the
+// role of src/cache.h in the reference) and the numeric constants of
+// src/kernel_hydro.h / src/dimension.h / src/adiabatic_index.h.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/swift_cuda.h"
+#include "host_tree.hpp"
+
+namespace swiftcuda {
+
+// Numeric constants, evaluated ON THE HOST with the reference's own expressions
+// (src/kernel_hydro.h:52-53, 205-241; cubic spline, 3D) and uploaded, so that
+// device and CPU use the same bits.
+struct Consts {
+  float gamma;          // kernel_gamma
+  float gamma2;         // kernel_gamma2
+  float gamma_inv;      // kernel_gamma_inv
+  float kconst;         // kernel_constant
+  float ginv_dim;       // kernel_gamma_inv_dim
+  float ginv_dim_p1;    // kernel_gamma_inv_dim_plus_one
+  float kroot;          // kernel_root
+  float eta_dim;        // pow_dimension(eta_neighbours)
+  float h_tol, h_max, h_min;
+  float alpha, beta;    // viscosity alpha, const_viscosity_beta
+  float a, H;           // cosmology
+  int max_active_bin;
+  int scheme;
+  int max_iter;
+  int n_til;
+  swift_cuda_til til[8];
+  float idg_gamma[4];
+  double axis[13][3];   // runner_shift
+};
+
+struct CellDev {
+  double loc[3];
+  int first;
+  int count;
+};
+
+// Everything a kernel needs, passed by value.
+struct Dev {
+  int64_t n;
+  int ncells;
+  int n_icells;
+  // particles, cell order
+  const double *x, *y, *z;
+  float4 *vm;          // vx, vy, vz, mass
+  float *h;
+  const float *u;
+  const int8_t *time_bin;
+  const int32_t *mat_id;
+  const int64_t *id;
+  // density sums
+  float4 *dens0;       // rho, rho_dh, wcount, wcount_dh
+  float4 *dens1;       // div_v, rot_v[3]
+  // force inputs (after ghost)
+  float4 *fin;         // rho, pressure, grad-h f, soundspeed
+  float *balsara;
+  // force outputs
+  float4 *acc;         // a_hydro[3], u_dt
+  float *h_dt;
+  float *v_sig;
+  int *min_bin;
+  // ghost state
+  float *left, *right;
+  uint8_t *gstate;     // 0 idle/inactive, 1 pending, 2 redo this sweep, 3 done
+  // tree
+  const CellDev *cells;
+  float *cell_hmax;        // current c->hydro.h_max
+  const float *cell_hmax_old;  // value at build (h_max_old)
+  const int32_t *icells;
+  const int32_t *item_begin;
+  const Item *items;
+  // sorts
+  const int64_t *sort_lookup;  // [ncells*13]
+  float *sort_d;
+  int32_t *sort_i;
+  // counters: [0] density, [1] redo, [2] force
+  unsigned long long *hits;
+  int *redo_count;         // [max_iter+1]
+  // pair recording (test hook)
+  long long *rec_pairs[3];
+  unsigned long long *rec_count;  // [3]
+  long long rec_capacity;
+};
+
+}  // namespace swiftcuda

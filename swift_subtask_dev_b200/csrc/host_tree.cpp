@@ -1,0 +1,514 @@
+// See host_tree.hpp for what this reproduces and the reference lines.
+#include "host_tree.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <thread>
+
+namespace swiftcuda {
+
+// runner_shift, src/sort_part.h:42-56 (unit vectors of the 13 pair axes)
+const double kAxis[13][3] = {
+    {5.773502691896258e-01, 5.773502691896258e-01, 5.773502691896258e-01},
+    {7.071067811865475e-01, 7.071067811865475e-01, 0.0},
+    {5.773502691896258e-01, 5.773502691896258e-01, -5.773502691896258e-01},
+    {7.071067811865475e-01, 0.0, 7.071067811865475e-01},
+    {1.0, 0.0, 0.0},
+    {7.071067811865475e-01, 0.0, -7.071067811865475e-01},
+    {5.773502691896258e-01, -5.773502691896258e-01, 5.773502691896258e-01},
+    {7.071067811865475e-01, -7.071067811865475e-01, 0.0},
+    {5.773502691896258e-01, -5.773502691896258e-01, -5.773502691896258e-01},
+    {0.0, 7.071067811865475e-01, 7.071067811865475e-01},
+    {0.0, 1.0, 0.0},
+    {0.0, 7.071067811865475e-01, -7.071067811865475e-01},
+    {0.0, 0.0, 1.0},
+};
+
+// sid_scale, src/sort_part.h:93-95
+static const float kSidScale[13] = {0.1897f, 0.4025f, 0.1897f, 0.4025f, 0.5788f, 0.4025f, 0.1897f,
+                                    0.4025f, 0.1897f, 0.4025f, 0.5788f, 0.4025f, 0.5788f};
+
+namespace {
+
+// A direction code packs the sign of the cell offset per axis as base-3 digits
+// (x most significant).  Codes 0..12 are the "flipped" half: the pair is
+// stored with the cells swapped so that cj always lies in the positive
+// half-space; the sort axis of code k and of 26-k is the same
+// (sortlistID / runner_flip, src/sort_part.h:58-90).
+inline bool code_is_flipped(int code) { return code < 13; }
+inline int code_to_sid(int code) { return code < 13 ? code : (code == 13 ? 0 : 26 - code); }
+inline bool sid_is_corner(int sid) { return sid == 0 || sid == 2 || sid == 6 || sid == 8; }
+
+struct PairGeom {
+  int ci, cj, sid;
+  double shift[3];
+};
+
+// space_getsid on cell indices.
+PairGeom orient_pair(const swift_cuda_params &prm, const std::vector<swift_cuda_cell> &cells, int a, int b) {
+  PairGeom g;
+  double dx[3];
+  int code = 0;
+  for (int k = 0; k < 3; k++) {
+    dx[k] = cells[b].loc[k] - cells[a].loc[k];
+    if (prm.periodic && dx[k] < -prm.dim[k] / 2)
+      g.shift[k] = prm.dim[k];
+    else if (prm.periodic && dx[k] > prm.dim[k] / 2)
+      g.shift[k] = -prm.dim[k];
+    else
+      g.shift[k] = 0.0;
+    dx[k] += g.shift[k];
+    code = 3 * code + ((dx[k] < 0.0) ? 0 : ((dx[k] > 0.0) ? 2 : 1));
+  }
+  if (code_is_flipped(code)) {
+    g.ci = b;
+    g.cj = a;
+    for (int k = 0; k < 3; k++) g.shift[k] = -g.shift[k];
+  } else {
+    g.ci = a;
+    g.cj = b;
+  }
+  g.sid = code_to_sid(code);
+  return g;
+}
+
+// Octant pairs (of ci, of cj) that touch across a pair of direction `sid`:
+// role of cell_split_pairs (src/cell.c:62).  Octant k has bit 4|2|1 set when it
+// is the upper half along x|y|z (src/space_split.c:223-225).
+struct OctPairs {
+  int n;
+  int pi[16], pj[16];
+};
+OctPairs make_oct_pairs(int sid) {
+  OctPairs o;
+  o.n = 0;
+  const int code = 26 - sid;
+  const int dir[3] = {code / 9 - 1, (code / 3) % 3 - 1, code % 3 - 1};
+  for (int a = 0; a < 8; a++)
+    for (int b = 0; b < 8; b++) {
+      bool touch = true;
+      for (int d = 0; d < 3; d++) {
+        const int ba = (a >> (2 - d)) & 1, bb = (b >> (2 - d)) & 1;
+        const int off = 2 * dir[d] + bb - ba;
+        touch &= (off >= -1 && off <= 1);
+      }
+      if (touch) {
+        o.pi[o.n] = a;
+        o.pj[o.n] = b;
+        o.n++;
+      }
+    }
+  return o;
+}
+const OctPairs &oct_pairs(int sid) {
+  static OctPairs table[13];
+  static bool init = false;
+  if (!init) {
+    for (int s = 0; s < 13; s++) table[s] = make_oct_pairs(s);
+    init = true;
+  }
+  return table[sid];
+}
+
+inline double cell_dmin(const swift_cuda_cell &c) { return std::min(c.width[0], std::min(c.width[1], c.width[2])); }
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// Tree
+// ---------------------------------------------------------------------------
+namespace {
+struct SplitCtx {
+  const double *x;
+  std::vector<swift_cuda_cell> *cells;
+  int32_t *order;
+  int32_t *scratch;
+};
+
+inline int octant_of(const double *p, const double pivot[3]) {
+  return (p[0] >= pivot[0]) * 4 + (p[1] >= pivot[1]) * 2 + (p[2] >= pivot[2]);
+}
+
+swift_cuda_cell blank_cell() {
+  swift_cuda_cell c;
+  std::memset(&c, 0, sizeof(c));
+  c.parent = -1;
+  for (int k = 0; k < 8; k++) c.progeny[k] = -1;
+  return c;
+}
+
+// Splits one top-level cell into `local` (indices relative to local[0] = the top cell).
+void split_top(const double *x, int32_t *order, int32_t *scratch, std::vector<swift_cuda_cell> &local) {
+  // explicit stack, depth-first, children appended as they are created
+  std::vector<int> stack;
+  stack.push_back(0);
+  while (!stack.empty()) {
+    const int ci = stack.back();
+    stack.pop_back();
+    const swift_cuda_cell c = local[ci];
+    if (c.count <= kSplitSize) continue;
+    const double pivot[3] = {c.loc[0] + c.width[0] / 2, c.loc[1] + c.width[1] / 2, c.loc[2] + c.width[2] / 2};
+    int bucket[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int k = 0; k < c.count; k++) bucket[octant_of(&x[3 * (size_t)order[c.first + k]], pivot)]++;
+    int start[9];
+    start[0] = 0;
+    for (int k = 0; k < 8; k++) start[k + 1] = start[k] + bucket[k];
+    int fill[8];
+    for (int k = 0; k < 8; k++) fill[k] = start[k];
+    for (int k = 0; k < c.count; k++) {
+      const int32_t o = order[c.first + k];
+      scratch[c.first + fill[octant_of(&x[3 * (size_t)o], pivot)]++] = o;
+    }
+    std::memcpy(&order[c.first], &scratch[c.first], sizeof(int32_t) * (size_t)c.count);
+    local[ci].split = 1;
+    for (int k = 0; k < 8; k++) {
+      if (bucket[k] == 0) continue;  // empty progeny are recycled (space_split.c:246-249)
+      swift_cuda_cell p = blank_cell();
+      for (int d = 0; d < 3; d++) {
+        p.loc[d] = c.loc[d];
+        p.width[d] = c.width[d] / 2;
+      }
+      if (k & 4) p.loc[0] += p.width[0];
+      if (k & 2) p.loc[1] += p.width[1];
+      if (k & 1) p.loc[2] += p.width[2];
+      p.first = c.first + start[k];
+      p.count = bucket[k];
+      p.parent = ci;
+      p.depth = c.depth + 1;
+      const int pi = (int)local.size();
+      local.push_back(p);
+      local[ci].progeny[k] = pi;
+      stack.push_back(pi);
+    }
+  }
+}
+}  // namespace
+
+int build_tree(const swift_cuda_params &prm, int64_t n, const double *x, const float *h, Tree &tree) {
+  float h_max = 0.f;
+  for (int64_t k = 0; k < n; k++) h_max = std::max(h_max, h[k]);
+  h_max = std::min(h_max, prm.h_max);
+  const double dmax = std::max(prm.dim[0], std::max(prm.dim[1], prm.dim[2]));
+  const double cell_min = 0.99 * dmax / kMaxTopCells;  // src/space.c:1160
+  int cdim[3];
+  double width[3], iwidth[3];
+  for (int d = 0; d < 3; d++) {
+    cdim[d] = (int)std::floor(prm.dim[d] / std::fmax(h_max * kKernelGamma * kSpaceStretch, cell_min));
+    if (cdim[d] < 1) return 1;
+    if (prm.periodic && cdim[d] < 3) return 2;
+    width[d] = prm.dim[d] / cdim[d];
+    iwidth[d] = 1.0 / width[d];
+    tree.cdim[d] = cdim[d];
+  }
+  const int ntop = cdim[0] * cdim[1] * cdim[2];
+
+  // counting sort of the particles into the top-level cells
+  std::vector<int32_t> top_of(n);
+  std::vector<int64_t> start(ntop + 1, 0);
+  for (int64_t k = 0; k < n; k++) {
+    int idx[3];
+    for (int d = 0; d < 3; d++) {
+      idx[d] = (int)(x[3 * k + d] * iwidth[d]);
+      idx[d] = std::min(std::max(idx[d], 0), cdim[d] - 1);
+    }
+    top_of[k] = (idx[0] * cdim[1] + idx[1]) * cdim[2] + idx[2];
+    start[top_of[k] + 1]++;
+  }
+  for (int c = 0; c < ntop; c++) start[c + 1] += start[c];
+  tree.order.resize(n);
+  {
+    std::vector<int64_t> fill(start.begin(), start.end() - 1);
+    for (int64_t k = 0; k < n; k++) tree.order[fill[top_of[k]]++] = (int32_t)k;
+  }
+  top_of.clear();
+  top_of.shrink_to_fit();
+
+  // split every top-level cell independently (threads), then concatenate
+  std::vector<std::vector<swift_cuda_cell>> locals(ntop);
+  std::vector<int32_t> scratch(n);
+  auto work = [&](int t, int nt) {
+    for (int c = t; c < ntop; c += nt) {
+      swift_cuda_cell top = blank_cell();
+      const int i = c / (cdim[1] * cdim[2]), j = (c / cdim[2]) % cdim[1], k = c % cdim[2];
+      top.loc[0] = i * width[0];
+      top.loc[1] = j * width[1];
+      top.loc[2] = k * width[2];
+      for (int d = 0; d < 3; d++) top.width[d] = width[d];
+      top.first = (int)start[c];
+      top.count = (int)(start[c + 1] - start[c]);
+      locals[c].push_back(top);
+      split_top(x, tree.order.data(), scratch.data(), locals[c]);
+    }
+  };
+  const int nt = (int)std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+  if (n < 200000 || nt == 1) {
+    work(0, 1);
+  } else {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nt; t++) th.emplace_back(work, t, nt);
+    for (auto &t : th) t.join();
+  }
+  // top-level cells first (indices 0..ntop-1, as s->cells_top), progeny after
+  size_t total = 0;
+  for (auto &l : locals) total += l.size();
+  tree.cells.assign(total, blank_cell());
+  std::vector<int> base(ntop);
+  int next = ntop;
+  for (int c = 0; c < ntop; c++) {
+    base[c] = next - 1;  // local index j>=1 maps to base+j
+    next += (int)locals[c].size() - 1;
+  }
+  for (int c = 0; c < ntop; c++) {
+    auto remap = [&](int j) { return j < 0 ? -1 : (j == 0 ? c : base[c] + j); };
+    for (size_t j = 0; j < locals[c].size(); j++) {
+      swift_cuda_cell cell = locals[c][j];
+      cell.parent = (j == 0) ? -1 : remap(cell.parent);
+      for (int k = 0; k < 8; k++) cell.progeny[k] = remap(cell.progeny[k]);
+      tree.cells[remap((int)j)] = cell;
+    }
+  }
+  return 0;
+}
+
+void compute_cell_hmax(Tree &tree, const float *h) {
+  const size_t nc = tree.cells.size();
+  tree.h_max.assign(nc, 0.f);
+  // leaves from particles, parents from children (children have larger indices than
+  // their parent in both the library tree and any top-down numbered tree; fall back
+  // to a direct scan otherwise)
+  for (size_t c = nc; c-- > 0;) {
+    const swift_cuda_cell &cell = tree.cells[c];
+    float m = 0.f;
+    bool from_children = cell.split;
+    if (from_children)
+      for (int k = 0; k < 8; k++)
+        if (cell.progeny[k] >= 0 && (size_t)cell.progeny[k] <= c) from_children = false;
+    if (from_children) {
+      for (int k = 0; k < 8; k++)
+        if (cell.progeny[k] >= 0) m = std::max(m, tree.h_max[cell.progeny[k]]);
+    } else {
+      for (int k = 0; k < cell.count; k++) m = std::max(m, h[cell.first + k]);
+    }
+    tree.h_max[c] = m;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Tasks
+// ---------------------------------------------------------------------------
+namespace {
+struct TaskBuilder {
+  const swift_cuda_params &prm;
+  Tree &tree;
+  // cell_can_split_{self,pair}_hydro_task, src/cell.h:899-931
+  bool can_split(int c) const {
+    const swift_cuda_cell &cell = tree.cells[c];
+    return cell.split && (kSpaceStretch * kKernelGamma * tree.h_max[c] < 0.5f * cell_dmin(cell));
+  }
+  void add(int type, int ci, int cj) { tree.tasks.push_back(swift_cuda_task{type, ci, cj}); }
+
+  void split_self(int c) {
+    if (tree.cells[c].count == 0) return;
+    if (!can_split(c)) {
+      add(0, c, -1);
+      return;
+    }
+    if (tree.cells[c].count < kSubSizeSelf) {
+      add(2, c, -1);
+      return;
+    }
+    const int *pr = tree.cells[c].progeny;
+    for (int k = 0; k < 8; k++)
+      if (pr[k] >= 0) split_self(pr[k]);
+    for (int j = 0; j < 8; j++)
+      for (int k = j + 1; k < 8; k++)
+        if (pr[j] >= 0 && pr[k] >= 0) split_pair(pr[j], pr[k]);
+  }
+  void split_pair(int a, int b) {
+    if (tree.cells[a].count == 0 || tree.cells[b].count == 0) return;
+    const PairGeom g = orient_pair(prm, tree.cells, a, b);
+    if (!(can_split(g.ci) && can_split(g.cj))) {
+      add(1, g.ci, g.cj);
+      return;
+    }
+    const int ni = tree.cells[g.ci].count, nj = tree.cells[g.cj].count;
+    const bool small = ni * kSidScale[g.sid] < kSubSizePair / nj;  // src/scheduler.c:1307-1308
+    if (small && !sid_is_corner(g.sid)) {
+      add(3, g.ci, g.cj);
+      return;
+    }
+    const OctPairs &op = oct_pairs(g.sid);
+    for (int k = 0; k < op.n; k++) {
+      const int pa = tree.cells[g.ci].progeny[op.pi[k]], pb = tree.cells[g.cj].progeny[op.pj[k]];
+      if (pa >= 0 && pb >= 0) split_pair(pa, pb);
+    }
+  }
+};
+}  // namespace
+
+void build_tasks(const swift_cuda_params &prm, Tree &tree) {
+  tree.tasks.clear();
+  TaskBuilder tb{prm, tree};
+  const int *cdim = tree.cdim;
+  for (int i = 0; i < cdim[0]; i++)
+    for (int j = 0; j < cdim[1]; j++)
+      for (int k = 0; k < cdim[2]; k++) {
+        const int cid = (i * cdim[1] + j) * cdim[2] + k;
+        if (tree.cells[cid].count == 0) continue;
+        tb.split_self(cid);
+        for (int ii = -1; ii <= 1; ii++) {
+          int iii = i + ii;
+          if (!prm.periodic && (iii < 0 || iii >= cdim[0])) continue;
+          iii = (iii + cdim[0]) % cdim[0];
+          for (int jj = -1; jj <= 1; jj++) {
+            int jjj = j + jj;
+            if (!prm.periodic && (jjj < 0 || jjj >= cdim[1])) continue;
+            jjj = (jjj + cdim[1]) % cdim[1];
+            for (int kk = -1; kk <= 1; kk++) {
+              int kkk = k + kk;
+              if (!prm.periodic && (kkk < 0 || kkk >= cdim[2])) continue;
+              kkk = (kkk + cdim[2]) % cdim[2];
+              const int cjd = (iii * cdim[1] + jjj) * cdim[2] + kkk;
+              if (cid >= cjd || tree.cells[cjd].count == 0) continue;
+              tb.split_pair(cid, cjd);
+            }
+          }
+        }
+      }
+}
+
+// ---------------------------------------------------------------------------
+// Work lists
+// ---------------------------------------------------------------------------
+namespace {
+struct Flattener {
+  const swift_cuda_params &prm;
+  const Tree &tree;
+  const std::vector<uint8_t> &active;
+  std::vector<std::vector<Item>> per_cell;
+  int64_t n_interactions = 0;
+
+  // cell_can_recurse_in_{pair,self}_hydro_task, src/cell.h:761-782 (dx_max_part_old = 0 after a rebuild)
+  bool recurse_pair(int c) const {
+    const swift_cuda_cell &cell = tree.cells[c];
+    return cell.split && ((kKernelGamma * tree.h_max[c] + 0.f) < 0.5f * cell_dmin(cell));
+  }
+  bool recurse_self(int c) const {
+    const swift_cuda_cell &cell = tree.cells[c];
+    return cell.split && (kKernelGamma * tree.h_max[c] < 0.5f * cell_dmin(cell));
+  }
+
+  void direct_self(int c) {
+    if (tree.cells[c].count == 0 || !active[c]) return;
+    Item it;
+    std::memset(&it, 0, sizeof(it));
+    it.partner = c;
+    it.sid = -1;
+    it.role = kRoleSelf;
+    for (int d = 0; d < 3; d++) it.org[d] = tree.cells[c].loc[d];
+    per_cell[c].push_back(it);
+    n_interactions++;
+  }
+  void direct_pair(int a, int b) {
+    if (tree.cells[a].count == 0 || tree.cells[b].count == 0) return;
+    if (!active[a] && !active[b]) return;
+    const PairGeom g = orient_pair(prm, tree.cells, a, b);
+    Item it;
+    std::memset(&it, 0, sizeof(it));
+    it.sid = g.sid;
+    double rshift = 0.0;
+    for (int k = 0; k < 3; k++) {
+      it.shift[k] = g.shift[k];
+      rshift += g.shift[k] * kAxis[g.sid][k];
+      it.org[k] = tree.cells[g.cj].loc[k];
+    }
+    it.rshift = rshift;
+    if (active[g.ci]) {
+      it.partner = g.cj;
+      it.role = kRoleLeft;
+      per_cell[g.ci].push_back(it);
+    }
+    if (active[g.cj]) {
+      it.partner = g.ci;
+      it.role = kRoleRight;
+      per_cell[g.cj].push_back(it);
+    }
+    n_interactions++;
+  }
+  void sub_pair(int a, int b) {
+    if (!active[a] && !active[b]) return;
+    if (tree.cells[a].count == 0 || tree.cells[b].count == 0) return;
+    const PairGeom g = orient_pair(prm, tree.cells, a, b);
+    if (recurse_pair(g.ci) && recurse_pair(g.cj)) {
+      const OctPairs &op = oct_pairs(g.sid);
+      for (int k = 0; k < op.n; k++) {
+        const int pa = tree.cells[g.ci].progeny[op.pi[k]], pb = tree.cells[g.cj].progeny[op.pj[k]];
+        if (pa >= 0 && pb >= 0) sub_pair(pa, pb);
+      }
+    } else {
+      direct_pair(g.ci, g.cj);
+    }
+  }
+  void sub_self(int c) {
+    if (tree.cells[c].count == 0 || !active[c]) return;
+    if (recurse_self(c)) {
+      const int *pr = tree.cells[c].progeny;
+      for (int k = 0; k < 8; k++)
+        if (pr[k] >= 0) {
+          sub_self(pr[k]);
+          for (int j = k + 1; j < 8; j++)
+            if (pr[j] >= 0) sub_pair(pr[k], pr[j]);
+        }
+    } else {
+      direct_self(c);
+    }
+  }
+};
+}  // namespace
+
+void build_worklists(const swift_cuda_params &prm, const Tree &tree, const std::vector<uint8_t> &cell_active,
+                     WorkLists &wl) {
+  Flattener f{prm, tree, cell_active, {}, 0};
+  f.per_cell.resize(tree.cells.size());
+  for (const swift_cuda_task &t : tree.tasks) {
+    switch (t.type) {
+      case 0: f.direct_self(t.ci); break;
+      case 1: f.direct_pair(t.ci, t.cj); break;
+      case 2: f.sub_self(t.ci); break;
+      default: f.sub_pair(t.ci, t.cj); break;
+    }
+  }
+  wl = WorkLists();
+  wl.n_interactions = f.n_interactions;
+  const size_t nc = tree.cells.size();
+  wl.sort_lookup.assign(nc * 13, -1);
+  wl.item_begin.push_back(0);
+  for (size_t c = 0; c < nc; c++) {
+    if (f.per_cell[c].empty()) continue;
+    wl.icells.push_back((int32_t)c);
+    // self first, then pairs by axis: partners that share an axis reuse the same sorted segment
+    std::stable_sort(f.per_cell[c].begin(), f.per_cell[c].end(),
+                     [](const Item &a, const Item &b) { return a.sid < b.sid; });
+    for (const Item &it : f.per_cell[c]) {
+      wl.items.push_back(it);
+      if (it.role != kRoleSelf) {
+        // both cells of a pair need their sorted list along sid
+        for (int which = 0; which < 2; which++) {
+          const int cell = which ? it.partner : (int)c;
+          int64_t &slot = wl.sort_lookup[(size_t)cell * 13 + it.sid];
+          if (slot < 0) {
+            slot = wl.n_sort_entries;
+            wl.sort_cells.push_back(cell);
+            wl.sort_sids.push_back(it.sid);
+            wl.sort_offset.push_back(wl.n_sort_entries);
+            wl.n_sort_entries += tree.cells[cell].count;
+          }
+        }
+      }
+    }
+    wl.item_begin.push_back((int32_t)wl.items.size());
+  }
+}
+
+}  // namespace swiftcuda

@@ -1,0 +1,76 @@
+// Host side of the backend: cell tree, hydro task list and the flattened
+// per-cell interaction lists the kernels consume.  Plain C++17, no CUDA.
+//
+// What it reproduces (decisions only, no physics):
+//   space_regrid            src/space_regrid.c:120-127, 220, 297-301   top-level grid
+//   space_split_recursive   src/space_split.c:199-262, cell_split.c:72-110  octree, 400 parts / leaf
+//   engine_make_hydroloop_tasks_mapper  src/engine_maketasks.c:4060-4182   self + 26-neighbour pair tasks
+//   scheduler_splittask_hydro           src/scheduler.c:1154-1378          push tasks down / make sub tasks
+//   DOSUB_SELF1/DOSUB_PAIR1             src/runner_doiact_functions_hydro.h:2524-2617  run-time recursion
+//   space_getsid                        src/space_getsid.h:46-84           sid, shift, which cell is "cj"
+#pragma once
+#include <cstdint>
+#include <vector>
+
+#include "../../include/swift_cuda.h"
+
+namespace swiftcuda {
+
+constexpr int kSplitSize = 400;          // space_splitsize_default, src/space.h:49
+constexpr int kMaxTopCells = 12;         // space_max_top_level_cells_default, src/space.h:64
+constexpr int kSubSizeSelf = 32000;      // space_subsize_self_hydro_default
+constexpr int kSubSizePair = 256000000;  // space_subsize_pair_hydro_default
+constexpr float kSpaceStretch = 1.10f;   // space_stretch, src/space.h:65
+constexpr float kKernelGamma = (float)(1.825742);  // src/kernel_hydro.h:52
+
+enum Role : int { kRoleLeft = 0, kRoleRight = 1, kRoleSelf = 2 };
+
+// One side of a direct cell interaction, seen from the cell that gets updated.
+struct Item {
+  int partner;      // cell index of the other cell (== own cell for self)
+  int sid;          // sort axis 0..12 (unused for self)
+  int role;         // kRoleLeft: this cell is "ci"; kRoleRight: this cell is "cj"; kRoleSelf
+  int pad;
+  double shift[3];  // space_getsid shift AFTER the flip (applies to ci)
+  double rshift;    // shift . runner_shift[sid]
+  double org[3];    // loc of the pair's "cj" cell: frame origin of DOPAIR1/2
+};
+
+struct Tree {
+  std::vector<swift_cuda_cell> cells;
+  std::vector<swift_cuda_task> tasks;
+  std::vector<int32_t> order;  // order[k] = caller index of the particle at cell-order slot k
+  std::vector<float> h_max;    // per cell, from the particles' h at build time (c->hydro.h_max_old)
+  int cdim[3] = {0, 0, 0};
+};
+
+struct WorkLists {
+  std::vector<int32_t> icells;       // cells that own at least one item
+  std::vector<int32_t> item_begin;   // [icells.size()+1] offsets into items
+  std::vector<Item> items;
+  std::vector<int32_t> sort_cells;   // (cell, sid) segments to sort: cell
+  std::vector<int32_t> sort_sids;    //                              sid
+  std::vector<int64_t> sort_offset;  // start of each segment in the flat sort arrays
+  std::vector<int64_t> sort_lookup;  // [ncells*13] segment start or -1
+  int64_t n_sort_entries = 0;
+  int64_t n_interactions = 0;        // direct self + pair interactions
+};
+
+extern const double kAxis[13][3];
+
+// Builds grid + octree; fills tree.cells / order / cdim / h_max.  Returns 0, or
+// an error code (1: empty grid, 2: periodic box with fewer than 3 cells).
+int build_tree(const swift_cuda_params &prm, int64_t n, const double *x, const float *h, Tree &tree);
+
+// Computes tree.h_max from particle h (cell order).
+void compute_cell_hmax(Tree &tree, const float *h_cell_order);
+
+// Creates and splits the hydro tasks for tree.cells.
+void build_tasks(const swift_cuda_params &prm, Tree &tree);
+
+// Replays the run-time recursion of every task and groups the resulting direct
+// interactions by updated cell.  `active[c]` != 0 when cell c holds an active particle.
+void build_worklists(const swift_cuda_params &prm, const Tree &tree, const std::vector<uint8_t> &cell_active,
+                     WorkLists &wl);
+
+}  // namespace swiftcuda

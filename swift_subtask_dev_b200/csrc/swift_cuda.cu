@@ -1,0 +1,707 @@
+// C ABI of the backend (include/swift_cuda.h): context, device buffers, the
+// launch sequence of one density -> ghost -> force step.  No CPU fallback: every
+// compute entry needs a CUDA device and fails loudly without one.
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+
+using namespace swiftcuda;
+
+static thread_local std::string g_err;
+static int fail(const std::string &m) {
+  g_err = m;
+  return 1;
+}
+#define CK(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess)                                                                    \
+      return fail(std::string(#call) + ": " + cudaGetErrorString(e_) + " (" + __FILE__ + ":" + \
+                  std::to_string(__LINE__) + ")");                                            \
+  } while (0)
+
+struct swift_cuda_ctx {
+  swift_cuda_params prm;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[6] = {};
+  Tree tree;
+  WorkLists wl;
+  Dev dev;
+  int64_t n = 0;
+  bool built = false;
+  std::vector<void *> allocs;
+  // device-only helpers
+  int32_t *d_seg_cell = nullptr, *d_seg_sid = nullptr;
+  int64_t *d_seg_off = nullptr, *d_scratch_off = nullptr;
+  unsigned long long *d_scratch = nullptr;
+  int n_seg = 0;
+  swift_cuda_counters counters = {};
+  swift_cuda_timings timings = {};
+  long long rec_capacity = 0;
+  std::vector<float> d_first_pass;  // unused
+  float4 *d_dens0_first = nullptr, *d_dens1_first = nullptr;  // snapshot of the first-pass sums
+};
+
+template <typename T>
+static int dmalloc(swift_cuda_ctx *c, T **p, size_t count) {
+  void *q = nullptr;
+  CK(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T)));
+  c->allocs.push_back(q);
+  *p = reinterpret_cast<T *>(q);
+  return 0;
+}
+template <typename T>
+static int upload(swift_cuda_ctx *c, T **p, const T *src, size_t count) {
+  if (dmalloc(c, p, count)) return 1;
+  if (count) CK(cudaMemcpyAsync(*p, src, count * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  return 0;
+}
+
+static void free_device(swift_cuda_ctx *c) {
+  for (void *p : c->allocs) cudaFree(p);
+  c->allocs.clear();
+  c->built = false;
+}
+
+extern "C" {
+
+int swift_cuda_abi_version(void) { return SWIFT_CUDA_ABI_VERSION; }
+const char *swift_cuda_last_error(void) { return g_err.c_str(); }
+
+int swift_cuda_create(const swift_cuda_params *params, int device, swift_cuda_ctx **out) {
+  if (!params || !out) return fail("swift_cuda_create: null argument");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail("swift_cuda_create: no CUDA device (this backend has no CPU fallback)");
+  if (device < 0 || device >= ndev) return fail("swift_cuda_create: bad device index");
+  CK(cudaSetDevice(device));
+  swift_cuda_ctx *c = new swift_cuda_ctx();
+  c->prm = *params;
+  c->device = device;
+  CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  for (auto &e : c->ev) CK(cudaEventCreate(&e));
+  std::memset(&c->dev, 0, sizeof(Dev));
+  *out = c;
+  return 0;
+}
+
+void swift_cuda_destroy(swift_cuda_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  free_device(c);
+  for (auto &e : c->ev)
+    if (e) cudaEventDestroy(e);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+}  // extern "C"
+
+static int upload_consts(swift_cuda_ctx *c) {
+  const swift_cuda_params &p = c->prm;
+  Consts k;
+  std::memset(&k, 0, sizeof(k));
+  // src/kernel_hydro.h:52-53, 205-241 -- same expressions, evaluated by the host compiler
+  const float kg = (float)(1.825742);
+  k.gamma = kg;
+  k.gamma2 = (float)(kg * kg);
+  k.gamma_inv = (float)(1. / kg);
+  k.kconst = (float)(16. * 0.31830988618379067154);  // 16 * M_1_PI
+  k.ginv_dim = (float)(1. / (kg * kg * kg));
+  k.ginv_dim_p1 = (float)(1. / (kg * kg * kg * kg));
+  k.kroot = (float)(0.5f) * k.kconst * k.ginv_dim;
+  k.eta_dim = p.eta_neighbours * p.eta_neighbours * p.eta_neighbours;
+  k.h_tol = p.h_tolerance;
+  k.h_max = p.h_max;
+  k.h_min = p.h_min;
+  k.alpha = p.viscosity_alpha;
+  k.beta = p.scheme == SWIFT_CUDA_SCHEME_PLANETARY ? 4.f : 3.f;  // hydro_parameters.h:51 of each scheme
+  k.a = p.cosmo_a;
+  k.H = p.cosmo_H;
+  k.max_active_bin = p.max_active_bin;
+  k.scheme = p.scheme;
+  k.max_iter = p.max_smoothing_iterations;
+  k.n_til = p.n_til;
+  for (int i = 0; i < 8; i++) k.til[i] = p.til[i];
+  for (int i = 0; i < 4; i++) k.idg_gamma[i] = p.idg_gamma[i];
+  for (int s = 0; s < 13; s++)
+    for (int d = 0; d < 3; d++) k.axis[s][d] = kAxis[s][d];
+  CK(cudaMemcpyToSymbolAsync(kc, &k, sizeof(k), 0, cudaMemcpyHostToDevice, c->stream));
+  return 0;
+}
+
+// Packs the caller's particles to the device in cell order (tree.order) and
+// uploads the tree, work lists and sort segment tables.
+static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
+  const int64_t n = in->n;
+  c->n = n;
+  Dev &d = c->dev;
+  const std::vector<int32_t> &ord = c->tree.order;
+  std::vector<double> x(n), y(n), z(n);
+  std::vector<float4> vm(n);
+  std::vector<float> h(n), u(n);
+  std::vector<int8_t> tb(n);
+  std::vector<int32_t> mat(n);
+  std::vector<int64_t> id(n);
+  for (int64_t k = 0; k < n; k++) {
+    const int64_t s = ord.empty() ? k : ord[k];
+    x[k] = in->x[3 * s];
+    y[k] = in->x[3 * s + 1];
+    z[k] = in->x[3 * s + 2];
+    vm[k] = make_float4(in->v[3 * s], in->v[3 * s + 1], in->v[3 * s + 2], in->mass[s]);
+    h[k] = in->h[s];
+    u[k] = in->u[s];
+    tb[k] = in->time_bin ? in->time_bin[s] : (int8_t)1;
+    mat[k] = in->mat_id ? in->mat_id[s] : 0;
+    id[k] = in->id ? in->id[s] : s;
+  }
+  d.n = n;
+  double *dx, *dy, *dz;
+  if (upload(c, &dx, x.data(), n) || upload(c, &dy, y.data(), n) || upload(c, &dz, z.data(), n)) return 1;
+  d.x = dx; d.y = dy; d.z = dz;
+  if (upload(c, &d.vm, vm.data(), n) || upload(c, &d.h, h.data(), n)) return 1;
+  float *du; int8_t *dtb; int32_t *dmat; int64_t *did;
+  if (upload(c, &du, u.data(), n) || upload(c, &dtb, tb.data(), n) || upload(c, &dmat, mat.data(), n) ||
+      upload(c, &did, id.data(), n))
+    return 1;
+  d.u = du; d.time_bin = dtb; d.mat_id = dmat; d.id = did;
+  if (dmalloc(c, &d.dens0, n) || dmalloc(c, &d.dens1, n) || dmalloc(c, &d.fin, n) || dmalloc(c, &d.balsara, n) ||
+      dmalloc(c, &d.acc, n) || dmalloc(c, &d.h_dt, n) || dmalloc(c, &d.v_sig, n) || dmalloc(c, &d.min_bin, n) ||
+      dmalloc(c, &d.left, n) || dmalloc(c, &d.right, n) || dmalloc(c, &d.gstate, n) ||
+      dmalloc(c, &c->d_dens0_first, n) || dmalloc(c, &c->d_dens1_first, n))
+    return 1;
+  CK(cudaMemsetAsync(d.fin, 0, n * sizeof(float4), c->stream));
+  CK(cudaMemsetAsync(d.balsara, 0, n * sizeof(float), c->stream));
+  CK(cudaMemsetAsync(d.acc, 0, n * sizeof(float4), c->stream));
+  CK(cudaMemsetAsync(d.h_dt, 0, n * sizeof(float), c->stream));
+  CK(cudaMemsetAsync(d.v_sig, 0, n * sizeof(float), c->stream));
+
+  // tree
+  const size_t nc = c->tree.cells.size();
+  std::vector<CellDev> cells(nc);
+  for (size_t k = 0; k < nc; k++) {
+    for (int a = 0; a < 3; a++) cells[k].loc[a] = c->tree.cells[k].loc[a];
+    cells[k].first = c->tree.cells[k].first;
+    cells[k].count = c->tree.cells[k].count;
+  }
+  d.ncells = (int)nc;
+  CellDev *dcells; float *dhm_old;
+  if (upload(c, &dcells, cells.data(), nc) || upload(c, &d.cell_hmax, c->tree.h_max.data(), nc) ||
+      upload(c, &dhm_old, c->tree.h_max.data(), nc))
+    return 1;
+  d.cells = dcells; d.cell_hmax_old = dhm_old;
+
+  // work lists
+  const WorkLists &wl = c->wl;
+  d.n_icells = (int)wl.icells.size();
+  int32_t *dic, *dib; Item *dit; int64_t *dsl;
+  if (upload(c, &dic, wl.icells.data(), wl.icells.size()) || upload(c, &dib, wl.item_begin.data(), wl.item_begin.size()) ||
+      upload(c, &dit, wl.items.data(), wl.items.size()) || upload(c, &dsl, wl.sort_lookup.data(), wl.sort_lookup.size()))
+    return 1;
+  d.icells = dic; d.item_begin = dib; d.items = dit; d.sort_lookup = dsl;
+  if (dmalloc(c, &d.sort_d, (size_t)wl.n_sort_entries) || dmalloc(c, &d.sort_i, (size_t)wl.n_sort_entries)) return 1;
+  c->n_seg = (int)wl.sort_cells.size();
+  std::vector<int64_t> scratch_off(c->n_seg, 0);
+  int64_t scratch_total = 0;
+  for (int s = 0; s < c->n_seg; s++) {
+    const int cnt = c->tree.cells[wl.sort_cells[s]].count;
+    int npad = 1;
+    while (npad < cnt) npad <<= 1;
+    if (npad > kSortSmem) {
+      scratch_off[s] = scratch_total;
+      scratch_total += npad;
+    }
+  }
+  if (upload(c, &c->d_seg_cell, wl.sort_cells.data(), wl.sort_cells.size()) ||
+      upload(c, &c->d_seg_sid, wl.sort_sids.data(), wl.sort_sids.size()) ||
+      upload(c, &c->d_seg_off, wl.sort_offset.data(), wl.sort_offset.size()) ||
+      upload(c, &c->d_scratch_off, scratch_off.data(), scratch_off.size()) ||
+      dmalloc(c, &c->d_scratch, (size_t)scratch_total))
+    return 1;
+  if (dmalloc(c, &d.hits, 3) || dmalloc(c, &d.redo_count, (size_t)c->prm.max_smoothing_iterations + 2) ||
+      dmalloc(c, &d.rec_count, 3))
+    return 1;
+  CK(cudaMemsetAsync(d.rec_count, 0, 3 * sizeof(unsigned long long), c->stream));
+  d.rec_capacity = 0;
+  for (int k = 0; k < 3; k++) d.rec_pairs[k] = nullptr;
+  if (upload_consts(c)) return 1;
+  CK(cudaStreamSynchronize(c->stream));
+  c->built = true;
+  return 0;
+}
+
+static void cells_active(const swift_cuda_ctx *c, const swift_cuda_parts_in *in, std::vector<uint8_t> &act) {
+  const size_t nc = c->tree.cells.size();
+  act.assign(nc, 1);
+  if (!in->time_bin) return;
+  const std::vector<int32_t> &ord = c->tree.order;
+  for (size_t k = 0; k < nc; k++) {
+    const swift_cuda_cell &cell = c->tree.cells[k];
+    uint8_t a = 0;
+    for (int j = 0; j < cell.count && !a; j++) {
+      const int64_t s = ord.empty() ? (cell.first + j) : ord[cell.first + j];
+      a = in->time_bin[s] <= c->prm.max_active_bin;
+    }
+    act[k] = a;
+  }
+}
+
+extern "C" {
+
+int swift_cuda_build_from_particles(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
+  if (!c || !in || !in->x || !in->v || !in->mass || !in->h || !in->u) return fail("build: null argument");
+  CK(cudaSetDevice(c->device));
+  free_device(c);
+  c->tree = Tree();
+  const int rc = build_tree(c->prm, in->n, in->x, in->h, c->tree);
+  if (rc == 1) return fail("build: top-level grid has a zero dimension");
+  if (rc == 2) return fail("build: periodic box needs at least 3 top-level cells per dimension (h_max too large)");
+  std::vector<float> hs(in->n);
+  for (int64_t k = 0; k < in->n; k++) hs[k] = in->h[c->tree.order[k]];
+  compute_cell_hmax(c->tree, hs.data());
+  build_tasks(c->prm, c->tree);
+  std::vector<uint8_t> act;
+  cells_active(c, in, act);
+  build_worklists(c->prm, c->tree, act, c->wl);
+  return pack_and_upload(c, in);
+}
+
+int swift_cuda_build_from_cells(swift_cuda_ctx *c, const swift_cuda_parts_in *in, int ncells,
+                                const swift_cuda_cell *cells, int ntasks, const swift_cuda_task *tasks) {
+  if (!c || !in || !cells || (!tasks && ntasks > 0)) return fail("build_from_cells: null argument");
+  CK(cudaSetDevice(c->device));
+  free_device(c);
+  c->tree = Tree();
+  c->tree.cells.assign(cells, cells + ncells);
+  c->tree.tasks.assign(tasks, tasks + ntasks);
+  for (int k = 0; k < ncells; k++)
+    if (cells[k].first < 0 || (int64_t)cells[k].first + cells[k].count > in->n)
+      return fail("build_from_cells: cell particle range outside the particle arrays");
+  compute_cell_hmax(c->tree, in->h);
+  std::vector<uint8_t> act;
+  cells_active(c, in, act);
+  build_worklists(c->prm, c->tree, act, c->wl);
+  return pack_and_upload(c, in);
+}
+
+int swift_cuda_update_particles(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
+  if (!c || !c->built) return fail("update_particles: context not built");
+  if (in->n != c->n) return fail("update_particles: particle count changed; rebuild");
+  CK(cudaSetDevice(c->device));
+  const int64_t n = c->n;
+  const std::vector<int32_t> &ord = c->tree.order;
+  std::vector<double> x(n), y(n), z(n);
+  std::vector<float4> vm(n);
+  std::vector<float> h(n), u(n);
+  for (int64_t k = 0; k < n; k++) {
+    const int64_t s = ord.empty() ? k : ord[k];
+    x[k] = in->x[3 * s]; y[k] = in->x[3 * s + 1]; z[k] = in->x[3 * s + 2];
+    vm[k] = make_float4(in->v[3 * s], in->v[3 * s + 1], in->v[3 * s + 2], in->mass[s]);
+    h[k] = in->h[s];
+    u[k] = in->u[s];
+  }
+  Dev &d = c->dev;
+  CK(cudaMemcpyAsync((void *)d.x, x.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync((void *)d.y, y.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync((void *)d.z, z.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(d.vm, vm.data(), n * 16, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(d.h, h.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync((void *)d.u, u.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
+  // cell h_max follows the particles (c->hydro.h_max after a drift)
+  std::vector<float> hs(h);
+  compute_cell_hmax(c->tree, hs.data());
+  CK(cudaMemcpyAsync(d.cell_hmax, c->tree.h_max.data(), c->tree.h_max.size() * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync((void *)d.cell_hmax_old, c->tree.h_max.data(), c->tree.h_max.size() * 4, cudaMemcpyHostToDevice,
+                     c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// ---- phases ----------------------------------------------------------------
+static int launch_sort(swift_cuda_ctx *c) {
+  if (c->n_seg > 0)
+    k_sort<<<c->n_seg, 256, 0, c->stream>>>(c->dev, c->d_seg_cell, c->d_seg_sid, c->d_seg_off, c->d_scratch,
+                                            c->d_scratch_off);
+  c->counters.n_kernel_launches += 1;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+static int launch_density(swift_cuda_ctx *c) {
+  Dev &d = c->dev;
+  const int nb = (int)((c->n + 255) / 256);
+  CK(cudaMemsetAsync(d.hits, 0, 3 * sizeof(unsigned long long), c->stream));
+  CK(cudaMemsetAsync(d.redo_count, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
+  CK(cudaMemcpyAsync(d.cell_hmax, d.cell_hmax_old, (size_t)d.ncells * sizeof(float), cudaMemcpyDeviceToDevice,
+                     c->stream));
+  k_init_step<<<nb, 256, 0, c->stream>>>(d);
+  if (d.n_icells > 0) k_density<0><<<d.n_icells, kBlock, 0, c->stream>>>(d, 0);
+  c->counters.n_kernel_launches += 2;
+  CK(cudaGetLastError());
+  // keep the raw first-pass sums for inspection (parity tests)
+  CK(cudaMemcpyAsync(c->d_dens0_first, d.dens0, c->n * sizeof(float4), cudaMemcpyDeviceToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->d_dens1_first, d.dens1, c->n * sizeof(float4), cudaMemcpyDeviceToDevice, c->stream));
+  return 0;
+}
+
+static int launch_ghost(swift_cuda_ctx *c) {
+  Dev &d = c->dev;
+  const int nb = (int)((c->n + 255) / 256);
+  // Fixed launch sequence, no host round trip: every kernel looks at the device-side
+  // redo counter of the sweep before and leaves at once when nothing is pending.
+  for (int sweep = 0; sweep < c->prm.max_smoothing_iterations; sweep++) {
+    k_ghost<<<nb, 256, 0, c->stream>>>(d, sweep);
+    if (d.n_icells > 0) k_density<1><<<d.n_icells, kBlock, 0, c->stream>>>(d, sweep);
+    c->counters.n_kernel_launches += 2;
+  }
+  k_cell_hmax<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d);
+  c->counters.n_kernel_launches += 1;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+static int launch_force(swift_cuda_ctx *c) {
+  Dev &d = c->dev;
+  const int nb = (int)((c->n + 255) / 256);
+  if (d.n_icells > 0) {
+    if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY)
+      k_force<SWIFT_CUDA_SCHEME_PLANETARY><<<d.n_icells, kBlock, 0, c->stream>>>(d);
+    else
+      k_force<SWIFT_CUDA_SCHEME_MINIMAL><<<d.n_icells, kBlock, 0, c->stream>>>(d);
+  }
+  k_end_force<<<nb, 256, 0, c->stream>>>(d);
+  c->counters.n_kernel_launches += 2;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+static int finish_counters(swift_cuda_ctx *c) {
+  Dev &d = c->dev;
+  unsigned long long hits[3];
+  std::vector<int> redo((size_t)c->prm.max_smoothing_iterations + 2);
+  CK(cudaMemcpyAsync(hits, d.hits, sizeof(hits), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(redo.data(), d.redo_count, redo.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  c->counters.n_density = (long long)hits[0];
+  c->counters.n_density_redo = (long long)hits[1];
+  c->counters.n_force = (long long)hits[2];
+  int sweeps = 0;
+  for (int s = 0; s < c->prm.max_smoothing_iterations; s++)
+    if (redo[s] > 0) sweeps = s + 1;
+  c->counters.ghost_sweeps = sweeps;
+  const int last = c->prm.max_smoothing_iterations - 1;
+  c->counters.ghost_unconverged = last >= 0 ? redo[last] : 0;
+  c->counters.n_leaf_interactions = c->wl.n_interactions;
+  c->counters.n_sort_entries = c->wl.n_sort_entries;
+  return 0;
+}
+
+#define NEED_BUILT(c)                                         \
+  if (!(c) || !(c)->built) return fail("context not built"); \
+  CK(cudaSetDevice((c)->device));
+
+int swift_cuda_do_sort(swift_cuda_ctx *c) {
+  NEED_BUILT(c);
+  if (launch_sort(c)) return 1;
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+int swift_cuda_do_density(swift_cuda_ctx *c) {
+  NEED_BUILT(c);
+  if (launch_density(c)) return 1;
+  return finish_counters(c);
+}
+int swift_cuda_do_ghost(swift_cuda_ctx *c) {
+  NEED_BUILT(c);
+  if (launch_ghost(c)) return 1;
+  if (finish_counters(c)) return 1;
+  if (c->counters.ghost_unconverged > 0)
+    return fail("Smoothing length failed to converge on " + std::to_string(c->counters.ghost_unconverged) +
+                " particles.");
+  return 0;
+}
+int swift_cuda_do_force(swift_cuda_ctx *c) {
+  NEED_BUILT(c);
+  if (launch_force(c)) return 1;
+  return finish_counters(c);
+}
+
+int swift_cuda_step(swift_cuda_ctx *c, int do_sort) {
+  NEED_BUILT(c);
+  c->counters.n_kernel_launches = 0;
+  CK(cudaEventRecord(c->ev[0], c->stream));
+  if (do_sort && launch_sort(c)) return 1;
+  CK(cudaEventRecord(c->ev[1], c->stream));
+  if (launch_density(c)) return 1;
+  CK(cudaEventRecord(c->ev[2], c->stream));
+  if (launch_ghost(c)) return 1;
+  CK(cudaEventRecord(c->ev[3], c->stream));
+  if (launch_force(c)) return 1;
+  CK(cudaEventRecord(c->ev[4], c->stream));
+  if (finish_counters(c)) return 1;
+  CK(cudaEventElapsedTime(&c->timings.sort_ms, c->ev[0], c->ev[1]));
+  CK(cudaEventElapsedTime(&c->timings.density_ms, c->ev[1], c->ev[2]));
+  CK(cudaEventElapsedTime(&c->timings.ghost_ms, c->ev[2], c->ev[3]));
+  CK(cudaEventElapsedTime(&c->timings.force_ms, c->ev[3], c->ev[4]));
+  CK(cudaEventElapsedTime(&c->timings.total_ms, c->ev[0], c->ev[4]));
+  if (c->counters.ghost_unconverged > 0)
+    return fail("Smoothing length failed to converge on " + std::to_string(c->counters.ghost_unconverged) +
+                " particles.");
+  return 0;
+}
+
+// ---- results ---------------------------------------------------------------
+int swift_cuda_get_results(swift_cuda_ctx *c, const swift_cuda_parts_out *out) {
+  NEED_BUILT(c);
+  const int64_t n = c->n;
+  Dev &d = c->dev;
+  const std::vector<int32_t> &ord = c->tree.order;
+  auto slot = [&](int64_t k) -> int64_t { return ord.empty() ? k : ord[k]; };
+  std::vector<float4> b4(n);
+  std::vector<float> b1(n);
+  CK(cudaStreamSynchronize(c->stream));
+  if (out->h) {
+    CK(cudaMemcpy(b1.data(), d.h, n * 4, cudaMemcpyDeviceToHost));
+    for (int64_t k = 0; k < n; k++) out->h[slot(k)] = b1[k];
+  }
+  if (out->rho || out->pressure || out->f || out->soundspeed) {
+    CK(cudaMemcpy(b4.data(), d.fin, n * 16, cudaMemcpyDeviceToHost));
+    for (int64_t k = 0; k < n; k++) {
+      const int64_t s = slot(k);
+      if (out->rho) out->rho[s] = b4[k].x;
+      if (out->pressure) out->pressure[s] = b4[k].y;
+      if (out->f) out->f[s] = b4[k].z;
+      if (out->soundspeed) out->soundspeed[s] = b4[k].w;
+    }
+  }
+  if (out->balsara) {
+    CK(cudaMemcpy(b1.data(), d.balsara, n * 4, cudaMemcpyDeviceToHost));
+    for (int64_t k = 0; k < n; k++) out->balsara[slot(k)] = b1[k];
+  }
+  if (out->a || out->u_dt) {
+    CK(cudaMemcpy(b4.data(), d.acc, n * 16, cudaMemcpyDeviceToHost));
+    for (int64_t k = 0; k < n; k++) {
+      const int64_t s = slot(k);
+      if (out->a) {
+        out->a[3 * s] = b4[k].x;
+        out->a[3 * s + 1] = b4[k].y;
+        out->a[3 * s + 2] = b4[k].z;
+      }
+      if (out->u_dt) out->u_dt[s] = b4[k].w;
+    }
+  }
+  if (out->h_dt) {
+    CK(cudaMemcpy(b1.data(), d.h_dt, n * 4, cudaMemcpyDeviceToHost));
+    for (int64_t k = 0; k < n; k++) out->h_dt[slot(k)] = b1[k];
+  }
+  if (out->v_sig) {
+    CK(cudaMemcpy(b1.data(), d.v_sig, n * 4, cudaMemcpyDeviceToHost));
+    for (int64_t k = 0; k < n; k++) out->v_sig[slot(k)] = b1[k];
+  }
+  if (out->min_ngb_time_bin) {
+    std::vector<int> bi(n);
+    CK(cudaMemcpy(bi.data(), d.min_bin, n * 4, cudaMemcpyDeviceToHost));
+    for (int64_t k = 0; k < n; k++) out->min_ngb_time_bin[slot(k)] = (int8_t)bi[k];
+  }
+  if (out->d_rho || out->d_rho_dh || out->d_wcount || out->d_wcount_dh) {
+    CK(cudaMemcpy(b4.data(), c->d_dens0_first, n * 16, cudaMemcpyDeviceToHost));
+    for (int64_t k = 0; k < n; k++) {
+      const int64_t s = slot(k);
+      if (out->d_rho) out->d_rho[s] = b4[k].x;
+      if (out->d_rho_dh) out->d_rho_dh[s] = b4[k].y;
+      if (out->d_wcount) out->d_wcount[s] = b4[k].z;
+      if (out->d_wcount_dh) out->d_wcount_dh[s] = b4[k].w;
+    }
+  }
+  if (out->d_div_v || out->d_rot_v) {
+    CK(cudaMemcpy(b4.data(), c->d_dens1_first, n * 16, cudaMemcpyDeviceToHost));
+    for (int64_t k = 0; k < n; k++) {
+      const int64_t s = slot(k);
+      if (out->d_div_v) out->d_div_v[s] = b4[k].x;
+      if (out->d_rot_v) {
+        out->d_rot_v[3 * s] = b4[k].y;
+        out->d_rot_v[3 * s + 1] = b4[k].z;
+        out->d_rot_v[3 * s + 2] = b4[k].w;
+      }
+    }
+  }
+  return 0;
+}
+
+int swift_cuda_get_counters(swift_cuda_ctx *c, swift_cuda_counters *out) {
+  if (!c || !out) return fail("get_counters: null argument");
+  *out = c->counters;
+  return 0;
+}
+int swift_cuda_get_timings(swift_cuda_ctx *c, swift_cuda_timings *out) {
+  if (!c || !out) return fail("get_timings: null argument");
+  *out = c->timings;
+  return 0;
+}
+
+int swift_cuda_get_tree_size(swift_cuda_ctx *c, int *ncells, int *ntasks, int cdim[3]) {
+  if (!c) return fail("get_tree_size: null context");
+  if (ncells) *ncells = (int)c->tree.cells.size();
+  if (ntasks) *ntasks = (int)c->tree.tasks.size();
+  if (cdim)
+    for (int k = 0; k < 3; k++) cdim[k] = c->tree.cdim[k];
+  return 0;
+}
+int swift_cuda_get_tree(swift_cuda_ctx *c, swift_cuda_cell *cells, swift_cuda_task *tasks, int32_t *order) {
+  if (!c) return fail("get_tree: null context");
+  if (cells) std::memcpy(cells, c->tree.cells.data(), c->tree.cells.size() * sizeof(swift_cuda_cell));
+  if (tasks) std::memcpy(tasks, c->tree.tasks.data(), c->tree.tasks.size() * sizeof(swift_cuda_task));
+  if (order) std::memcpy(order, c->tree.order.data(), c->tree.order.size() * sizeof(int32_t));
+  return 0;
+}
+
+// ---- host-only planning ------------------------------------------------------
+int swift_cuda_host_plan(const swift_cuda_params *params, const swift_cuda_parts_in *in, swift_cuda_cell **cells,
+                         int *ncells, swift_cuda_task **tasks, int *ntasks, int32_t *order, int cdim[3],
+                         long long *n_interactions, long long *n_items) {
+  if (!params || !in) return fail("host_plan: null argument");
+  Tree tree;
+  const int rc = build_tree(*params, in->n, in->x, in->h, tree);
+  if (rc) return fail("host_plan: cannot build the top-level grid (code " + std::to_string(rc) + ")");
+  std::vector<float> hs(in->n);
+  for (int64_t k = 0; k < in->n; k++) hs[k] = in->h[tree.order[k]];
+  compute_cell_hmax(tree, hs.data());
+  build_tasks(*params, tree);
+  std::vector<uint8_t> act(tree.cells.size(), 1);
+  WorkLists wl;
+  build_worklists(*params, tree, act, wl);
+  if (cells) {
+    *cells = (swift_cuda_cell *)malloc(sizeof(swift_cuda_cell) * std::max<size_t>(tree.cells.size(), 1));
+    std::memcpy(*cells, tree.cells.data(), sizeof(swift_cuda_cell) * tree.cells.size());
+  }
+  if (tasks) {
+    *tasks = (swift_cuda_task *)malloc(sizeof(swift_cuda_task) * std::max<size_t>(tree.tasks.size(), 1));
+    std::memcpy(*tasks, tree.tasks.data(), sizeof(swift_cuda_task) * tree.tasks.size());
+  }
+  if (ncells) *ncells = (int)tree.cells.size();
+  if (ntasks) *ntasks = (int)tree.tasks.size();
+  if (order) std::memcpy(order, tree.order.data(), sizeof(int32_t) * tree.order.size());
+  if (cdim)
+    for (int k = 0; k < 3; k++) cdim[k] = tree.cdim[k];
+  if (n_interactions) *n_interactions = wl.n_interactions;
+  if (n_items) *n_items = (long long)wl.items.size();
+  return 0;
+}
+void swift_cuda_host_free(void *p) { free(p); }
+
+// ---- pair recording (test hook) ---------------------------------------------
+int swift_cuda_record_pairs(swift_cuda_ctx *c, long long capacity) {
+  NEED_BUILT(c);
+  Dev &d = c->dev;
+  if (capacity > 0 && d.rec_pairs[0] == nullptr) {
+    for (int k = 0; k < 3; k++)
+      if (dmalloc(c, &d.rec_pairs[k], (size_t)capacity * 2)) return 1;
+    c->rec_capacity = capacity;
+  }
+  d.rec_capacity = capacity > 0 ? c->rec_capacity : 0;
+  CK(cudaMemsetAsync(d.rec_count, 0, 3 * sizeof(unsigned long long), c->stream));
+  return 0;
+}
+int swift_cuda_fetch_pairs(swift_cuda_ctx *c, int loop, long long *pairs, long long capacity, long long *count) {
+  NEED_BUILT(c);
+  if (loop < 0 || loop > 2) return fail("fetch_pairs: loop must be 0, 1 or 2");
+  Dev &d = c->dev;
+  unsigned long long cnt[3];
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaMemcpy(cnt, d.rec_count, sizeof(cnt), cudaMemcpyDeviceToHost));
+  if (count) *count = (long long)cnt[loop];
+  if ((long long)cnt[loop] > c->rec_capacity) return fail("fetch_pairs: device pair buffer overflowed");
+  if (pairs) {
+    const long long m = std::min<long long>(capacity, (long long)cnt[loop]);
+    if (m > 0) CK(cudaMemcpy(pairs, d.rec_pairs[loop], (size_t)m * 2 * sizeof(long long), cudaMemcpyDeviceToHost));
+  }
+  return 0;
+}
+
+// ---- halo buffers (multi-GPU) -------------------------------------------------
+}  // extern "C"
+
+namespace swiftcuda {
+// phase 0 "xv": x, y, z (f64), vx, vy, vz, m, h (f32) = 44 B; phase 1 "rho": h, rho, P, f, c, balsara = 24 B
+struct HaloXV {
+  double x, y, z;
+  float vx, vy, vz, m, h;
+  float pad;
+};
+struct HaloRho {
+  float h, rho, P, f, c, bal;
+};
+__global__ void k_halo_pack_xv(Dev d, const int32_t *idx, int64_t n, HaloXV *buf) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t p = idx[k];
+  const float4 vm = d.vm[p];
+  HaloXV r = {d.x[p], d.y[p], d.z[p], vm.x, vm.y, vm.z, vm.w, d.h[p], 0.f};
+  buf[k] = r;
+}
+__global__ void k_halo_unpack_xv(Dev d, const int32_t *idx, int64_t n, const HaloXV *buf) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t p = idx[k];
+  const HaloXV r = buf[k];
+  const_cast<double *>(d.x)[p] = r.x;
+  const_cast<double *>(d.y)[p] = r.y;
+  const_cast<double *>(d.z)[p] = r.z;
+  d.vm[p] = make_float4(r.vx, r.vy, r.vz, r.m);
+  d.h[p] = r.h;
+}
+__global__ void k_halo_pack_rho(Dev d, const int32_t *idx, int64_t n, HaloRho *buf) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t p = idx[k];
+  const float4 f = d.fin[p];
+  HaloRho r = {d.h[p], f.x, f.y, f.z, f.w, d.balsara[p]};
+  buf[k] = r;
+}
+__global__ void k_halo_unpack_rho(Dev d, const int32_t *idx, int64_t n, const HaloRho *buf) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t p = idx[k];
+  const HaloRho r = buf[k];
+  d.h[p] = r.h;
+  d.fin[p] = make_float4(r.rho, r.P, r.f, r.c);
+  d.balsara[p] = r.bal;
+}
+}  // namespace swiftcuda
+
+extern "C" {
+
+size_t swift_cuda_halo_bytes_per_particle(int phase) { return phase == 0 ? sizeof(HaloXV) : sizeof(HaloRho); }
+
+int swift_cuda_halo_pack(swift_cuda_ctx *c, int phase, const int32_t *d_index, int64_t count, void *d_buffer,
+                         void *stream) {
+  NEED_BUILT(c);
+  if (count <= 0) return 0;
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  const int nb = (int)((count + 255) / 256);
+  if (phase == 0)
+    k_halo_pack_xv<<<nb, 256, 0, s>>>(c->dev, d_index, count, (HaloXV *)d_buffer);
+  else
+    k_halo_pack_rho<<<nb, 256, 0, s>>>(c->dev, d_index, count, (HaloRho *)d_buffer);
+  CK(cudaGetLastError());
+  return 0;
+}
+int swift_cuda_halo_unpack(swift_cuda_ctx *c, int phase, const int32_t *d_index, int64_t count,
+                           const void *d_buffer, void *stream) {
+  NEED_BUILT(c);
+  if (count <= 0) return 0;
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  const int nb = (int)((count + 255) / 256);
+  if (phase == 0)
+    k_halo_unpack_xv<<<nb, 256, 0, s>>>(c->dev, d_index, count, (const HaloXV *)d_buffer);
+  else
+    k_halo_unpack_rho<<<nb, 256, 0, s>>>(c->dev, d_index, count, (const HaloRho *)d_buffer);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"
