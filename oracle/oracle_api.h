@@ -80,6 +80,10 @@ typedef struct {
   /* stage 2: after force + end_force */
   float *f_a, *f_u_dt, *f_h_dt, *f_v_sig;
   signed char *f_min_ngb_time_bin;
+  /* optional inputs: the state INACTIVE particles carry over from their last
+   * active step (p->rho, p->force.{pressure, f, soundspeed, balsara}); the
+   * force loop of their active neighbours reads it.  NULL: zeros. */
+  const float *in_rho, *in_pressure, *in_f, *in_soundspeed, *in_balsara;
 } oracle_parts;
 
 /* Ordered (updated id, neighbour id) pairs.  loop 0: first density pass,

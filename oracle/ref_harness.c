@@ -50,6 +50,9 @@ void ref_record_pair(int loop, long long id_updated, long long id_other) {
 }
 
 int ref_sizeof_part(void) { return (int)sizeof(struct part); }
+#ifdef PLANETARY_SPH
+static void ref_planetary_eos_init(void);
+#endif
 
 /* ---- helpers ------------------------------------------------------------ */
 static void add_link(struct cell *c, struct task *t, struct link *pool,
@@ -203,6 +206,9 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
     if (t->cj != NULL) add_link(t->cj, t, links, &nlinks);
   }
 
+#ifdef PLANETARY_SPH
+  ref_planetary_eos_init();
+#endif
   g_log = log;
   g_store = prm->record_pairs;
   if (log) {
@@ -211,7 +217,20 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
   }
 
   /* ---- init + sort (all 13 axes on every top-level cell) ---- */
-  for (int k = 0; k < n; k++) hydro_init_part(&parts[k], &space.hs);
+  /* only active particles are re-initialised (src/cell_drift.c:342); inactive ones keep
+   * the state of their last active step, given by the caller */
+  for (int k = 0; k < n; k++) {
+    struct part *p = &parts[k];
+    if (part_is_active(p, &engine)) {
+      hydro_init_part(p, &space.hs);
+    } else {
+      p->rho = io->in_rho ? io->in_rho[k] : 0.f;
+      p->force.pressure = io->in_pressure ? io->in_pressure[k] : 0.f;
+      p->force.f = io->in_f ? io->in_f[k] : 0.f;
+      p->force.soundspeed = io->in_soundspeed ? io->in_soundspeed[k] : 0.f;
+      p->force.balsara = io->in_balsara ? io->in_balsara[k] : 0.f;
+    }
+  }
   for (int k = 0; k < ncells; k++)
     if (cells[k].parent == NULL && cells[k].hydro.count > 0)
       runner_do_hydro_sort(&runner, &cells[k], 0x1FFF, 0, 0, 0);
@@ -285,8 +304,53 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
   return 0;
 }
 
-/* The reference's eos_init() result, for the Planetary build (filled below). */
-#ifndef PLANETARY_SPH
+/* ---- planetary equation of state ------------------------------------------ */
+#ifdef PLANETARY_SPH
+#include "equation_of_state.h"
+#include "units.h"
+
+/* Fills the reference's global `eos` with its own setters and unit conversion
+ * (set_idg_def, set_Til_*, convert_units_Til: what eos_init does for
+ * EoS:planetary_use_idg_def / _Til_iron / _Til_granite / _Til_water /
+ * _Til_basalt = 1, src/equation_of_state/planetary/equation_of_state.h:1599-1627)
+ * in the internal units of examples/Planetary/EarthImpact/earth_impact.yml:2-7. */
+static int g_eos_ready = 0;
+static void ref_planetary_eos_init(void) {
+  if (g_eos_ready) return;
+  struct unit_system us;
+  units_init(&us, 1e27, 1e8, 1.0, 1.0, 1.0); /* mass g, length cm, time s (velocity 1e8 cm/s) */
+  bzero(&eos, sizeof(eos));
+  set_idg_def(&eos.idg_def, eos_planetary_id_idg_def);
+  set_Til_iron(&eos.Til_iron, eos_planetary_id_Til_iron);
+  convert_units_Til(&eos.Til_iron, &us);
+  set_Til_granite(&eos.Til_granite, eos_planetary_id_Til_granite);
+  convert_units_Til(&eos.Til_granite, &us);
+  set_Til_water(&eos.Til_water, eos_planetary_id_Til_water);
+  convert_units_Til(&eos.Til_water, &us);
+  set_Til_basalt(&eos.Til_basalt, eos_planetary_id_Til_basalt);
+  convert_units_Til(&eos.Til_basalt, &us);
+  g_eos_ready = 1;
+}
+
+static void copy_til(oracle_til *o, const struct Til_params *m) {
+  o->rho_0 = m->rho_0; o->a = m->a; o->b = m->b; o->A = m->A; o->B = m->B;
+  o->u_0 = m->u_0; o->u_iv = m->u_iv; o->u_cv = m->u_cv; o->alpha = m->alpha; o->beta = m->beta;
+  o->eta_min = m->eta_min; o->eta_zero = m->eta_zero; o->P_min = m->P_min;
+  o->mat_id = (int)m->mat_id;
+}
+
+int ref_get_eos(oracle_eos *out) {
+  ref_planetary_eos_init();
+  bzero(out, sizeof(*out));
+  out->n_til = 4;
+  copy_til(&out->til[0], &eos.Til_iron);
+  copy_til(&out->til[1], &eos.Til_granite);
+  copy_til(&out->til[2], &eos.Til_water);
+  copy_til(&out->til[3], &eos.Til_basalt);
+  for (int k = 0; k < 4; k++) out->idg_gamma[k] = eos.idg_def.gamma;
+  return 0;
+}
+#else
 int ref_get_eos(oracle_eos *out) {
   (void)out;
   return 1;

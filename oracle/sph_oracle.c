@@ -330,10 +330,10 @@ static void eos_eval(const octx *c, const opart *p, float *P, float *cs) {
   }
   const int type = p->mat_id / 100;
   if (type == 0) {
-    /* planetary/ideal_gas.h: P = (gamma-1) u rho, c = sqrt(gamma (gamma-1) u) */
+    /* planetary/ideal_gas.h:132-136, 161-165: P = (gamma-1) u rho, c = sqrt(u gamma (gamma-1)) */
     const float g = c->eos->idg_gamma[p->mat_id % 100];
     *P = (g - 1.f) * p->u * p->rho;
-    *cs = sqrtf(g * (g - 1.f) * p->u);
+    *cs = sqrtf(p->u * g * (g - 1.f));
     return;
   }
   const oracle_til *m = NULL;
@@ -1441,7 +1441,17 @@ int oracle_run_step(const oracle_params *prm, const oracle_eos *eos, oracle_part
     p->id = io->id[k];
     p->time_bin = io->time_bin ? io->time_bin[k] : 1;
     p->min_ngb_time_bin = NUM_TIME_BINS + 1;
-    init_part(p);
+    /* only active particles are re-initialised (src/cell_drift.c:342); the others keep
+     * what their last active step left in struct part */
+    if (part_active(&c, p)) {
+      init_part(p);
+    } else {
+      p->rho = io->in_rho ? io->in_rho[k] : 0.f;
+      p->pressure = io->in_pressure ? io->in_pressure[k] : 0.f;
+      p->f = io->in_f ? io->in_f[k] : 0.f;
+      p->soundspeed = io->in_soundspeed ? io->in_soundspeed[k] : 0.f;
+      p->balsara = io->in_balsara ? io->in_balsara[k] : 0.f;
+    }
   }
   for (int k = 0; k < ncells; k++) {
     ocell *o = &c.cells[k];

@@ -82,9 +82,55 @@ def clustered(n, nclumps=64, seed=7, box=1.0, frac_background=0.3):
     return ic
 
 
+def two_body_impact(n, seed=5, r_target=6.4, r_impactor=3.0):
+    """Config 3 shape: a target and an impactor, each a Tillotson iron core
+    (mat_id 100) inside a granite mantle (mat_id 101), on a jittered lattice in
+    a NON-periodic box; internal units of examples/Planetary/EarthImpact
+    (1e27 g, 1e8 cm, 1e8 cm/s).  Free surfaces, a density jump at the
+    core-mantle boundary, and internal energies spread over the condensed,
+    hybrid and expanded Tillotson branches.  Returns the usual dict plus
+    "dim" (box size) and "h_max"."""
+    rng = np.random.default_rng(seed)
+    vol = 4.0 / 3.0 * np.pi * (r_target ** 3 + r_impactor ** 3)
+    delta = (vol / n) ** (1.0 / 3.0)
+    box = 4.0 * (r_target + r_impactor)
+    c_t = np.array([0.40 * box, 0.5 * box, 0.5 * box])
+    c_i = c_t + np.array([r_target + r_impactor + 2.0 * delta, 0.3 * r_target, 0.0])
+    xs, mats, vs = [], [], []
+    for centre, radius, vel in ((c_t, r_target, 0.0), (c_i, r_impactor, -0.01)):
+        m = int(np.ceil(radius / delta)) + 1
+        g = np.arange(-m, m + 1) * delta
+        p = np.stack(np.meshgrid(g, g, g, indexing="ij"), axis=-1).reshape(-1, 3)
+        p = p + rng.uniform(-0.5, 0.5, p.shape) * 0.2 * delta
+        r = np.linalg.norm(p, axis=1)
+        keep = r < radius
+        p, r = p[keep], r[keep]
+        xs.append(p + centre)
+        mats.append(np.where(r < 0.55 * radius, 100, 101).astype(np.int32))
+        v = np.zeros((len(p), 3), dtype=np.float32)
+        v[:, 0] = vel
+        vs.append(v)
+    x = np.concatenate(xs)
+    mat = np.concatenate(mats)
+    v = np.concatenate(vs) + rng.uniform(-1e-4, 1e-4, (len(x), 3)).astype(np.float32)
+    nn = len(x)
+    rho0 = np.where(mat == 100, 7.8e-3, 2.68e-3)
+    mass = (rho0 * delta ** 3 * rng.uniform(0.8, 1.25, nn)).astype(np.float32)
+    u = np.exp(rng.uniform(np.log(1e-7), np.log(3e-5), nn)).astype(np.float32)
+    h0 = np.float32(ETA * delta)
+    ic = {"x": np.ascontiguousarray(x, dtype=np.float64), "v": np.ascontiguousarray(v, dtype=np.float32),
+          "mass": mass, "h": np.full(nn, h0, dtype=np.float32), "u": u,
+          "id": np.arange(1, nn + 1, dtype=np.int64), "mat_id": mat, "time_bin": None,
+          "dim": (box, box, box), "h_max": float(1.3 * h0)}
+    return ic
+
+
 def permute(ic, order):
     """Reorders every per-particle array with `order` (cell order)."""
     out = {}
     for k, a in ic.items():
-        out[k] = None if a is None else np.ascontiguousarray(a[order])
+        if isinstance(a, np.ndarray):
+            out[k] = np.ascontiguousarray(a[order])
+        elif a is None:
+            out[k] = None
     return out

@@ -48,7 +48,8 @@ class Parts(C.Structure):
                 ("g_h", _FP), ("g_rho", _FP), ("g_f", _FP), ("g_pressure", _FP), ("g_soundspeed", _FP),
                 ("g_balsara", _FP),
                 ("f_a", _FP), ("f_u_dt", _FP), ("f_h_dt", _FP), ("f_v_sig", _FP),
-                ("f_min_ngb_time_bin", C.POINTER(C.c_byte))]
+                ("f_min_ngb_time_bin", C.POINTER(C.c_byte)),
+                ("in_rho", _FP), ("in_pressure", _FP), ("in_f", _FP), ("in_soundspeed", _FP), ("in_balsara", _FP)]
 
 
 class PairLog(C.Structure):
@@ -93,6 +94,35 @@ def ref(variant="minimal"):
         lib.ref_get_eos.restype = C.c_int
         _libs[key] = lib
     return _libs[key]
+
+
+def ref_eos():
+    """The reference's own Tillotson / ideal-gas parameters in internal units
+    (needs the compiled planetary reference)."""
+    e = Eos()
+    rc = ref("planetary").ref_get_eos(C.byref(e))
+    if rc != 0:
+        raise RuntimeError("ref_get_eos failed")
+    return e
+
+
+def eos_from_json(path=os.path.join(ROOT, "tests", "golden", "eos_planetary.json")):
+    """The same parameters from the committed fixture (GPU box: no reference there)."""
+    import json
+    with open(path) as f:
+        d = json.load(f)
+    e = Eos()
+    e.n_til = len(d["til"])
+    for k, t in enumerate(d["til"]):
+        for name, _ in Til._fields_:
+            setattr(e.til[k], name, t[name])
+    e.idg_gamma[:] = d["idg_gamma"]
+    return e
+
+
+def eos_to_dict(e):
+    return {"til": [{name: getattr(e.til[k], name) for name, _ in Til._fields_} for k in range(e.n_til)],
+            "idg_gamma": list(e.idg_gamma)}
 
 
 def make_params(dim=(1.0, 1.0, 1.0), periodic=True, eta=1.2348, h_tolerance=1e-4, h_max=1e10, h_min=0.0,
@@ -166,6 +196,9 @@ def run_step(which, prm, ic, cells, tasks, ntasks, record=False, pair_capacity=N
     if ic.get("time_bin") is not None:
         tb = arr(ic["time_bin"], np.int8)
         P.time_bin = tb.ctypes.data_as(C.POINTER(C.c_byte))
+    for k in ("in_rho", "in_pressure", "in_f", "in_soundspeed", "in_balsara"):
+        if ic.get(k) is not None:
+            setattr(P, k, arr(ic[k], np.float32).ctypes.data_as(_FP))
     out = {}
     for k, w in OUT_FIELDS.items():
         out[k] = np.zeros((n, w) if w > 1 else n, dtype=np.float32)
