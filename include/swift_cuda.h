@@ -98,6 +98,11 @@ typedef struct {
   const int32_t *mat_id;  /* Planetary only; may be NULL */
   const int8_t *time_bin; /* may be NULL: all particles in bin 1 */
   const int64_t *id;      /* may be NULL: ids are the input positions */
+  /* State that INACTIVE particles (time_bin > max_active_bin) carry over from
+   * their last active step and that the force loop of their active neighbours
+   * reads: p->rho, p->force.{pressure, f, soundspeed, balsara}.  Each may be
+   * NULL (zeros); ignored for active particles, which get theirs from the ghost. */
+  const float *rho, *pressure, *f, *soundspeed, *balsara;
 } swift_cuda_parts_in;
 
 /* Results, host memory, written in the caller's particle order; any pointer
@@ -161,9 +166,18 @@ int swift_cuda_build_from_cells(swift_cuda_ctx *ctx, const swift_cuda_parts_in *
  * unchanged; same order as the build call. */
 int swift_cuda_update_particles(swift_cuda_ctx *ctx, const swift_cuda_parts_in *parts);
 
-/* One density -> ghost -> force -> end_force pass on the device.  `do_sort`
- * rebuilds the 13-axis sorts first (runner_do_hydro_sort). */
-int swift_cuda_step(swift_cuda_ctx *ctx, int do_sort);
+/* Puts the device copy of the particle state (h and the cells' h_max) back to
+ * what the last build / update call uploaded, without touching host memory:
+ * repeats a step from the same initial smoothing lengths. */
+int swift_cuda_restore_particles(swift_cuda_ctx *ctx);
+
+/* One density -> ghost -> force -> end_force pass on the device.
+ * flags: SWIFT_CUDA_STEP_SORT rebuilds the 13-axis sorts first
+ * (runner_do_hydro_sort); SWIFT_CUDA_STEP_RESTORE first puts h back to the
+ * values of the last build / update call (device-side, inside the timed
+ * region), so that a repeated step does the work of the first one. */
+enum { SWIFT_CUDA_STEP_SORT = 1, SWIFT_CUDA_STEP_RESTORE = 2 };
+int swift_cuda_step(swift_cuda_ctx *ctx, int flags);
 
 /* Operator-level entry points (same phases, separately callable; used by the
  * per-task shims and the parity tests). */
@@ -175,6 +189,10 @@ int swift_cuda_do_force(swift_cuda_ctx *ctx);
 int swift_cuda_get_results(swift_cuda_ctx *ctx, const swift_cuda_parts_out *out);
 int swift_cuda_get_counters(swift_cuda_ctx *ctx, swift_cuda_counters *out);
 int swift_cuda_get_timings(swift_cuda_ctx *ctx, swift_cuda_timings *out);
+
+/* Sustained FP32 FMA rate of the context's GPU in TFLOP/s (microbenchmark;
+ * the roofline denominator of the pair kernels).  < 0 on error. */
+double swift_cuda_measure_fp32_peak(swift_cuda_ctx *ctx);
 
 /* Tree introspection (library-built tree): sizes, then copies. */
 int swift_cuda_get_tree_size(swift_cuda_ctx *ctx, int *ncells, int *ntasks, int cdim[3]);

@@ -67,7 +67,8 @@ _FP = C.POINTER(C.c_float)
 
 class PartsIn(C.Structure):
     _fields_ = [("n", C.c_int64), ("x", C.POINTER(C.c_double)), ("v", _FP), ("mass", _FP), ("h", _FP), ("u", _FP),
-                ("mat_id", C.POINTER(C.c_int32)), ("time_bin", C.POINTER(C.c_int8)), ("id", C.POINTER(C.c_int64))]
+                ("mat_id", C.POINTER(C.c_int32)), ("time_bin", C.POINTER(C.c_int8)), ("id", C.POINTER(C.c_int64)),
+                ("rho", _FP), ("pressure", _FP), ("f", _FP), ("soundspeed", _FP), ("balsara", _FP)]
 
 
 OUT_FIELDS = [("h", 1), ("rho", 1), ("pressure", 1), ("soundspeed", 1), ("f", 1), ("balsara", 1), ("a", 3),
@@ -96,8 +97,10 @@ class Timings(C.Structure):
 
 EXPORTS = ["swift_cuda_abi_version", "swift_cuda_last_error", "swift_cuda_create", "swift_cuda_destroy",
            "swift_cuda_build_from_particles", "swift_cuda_build_from_cells", "swift_cuda_update_particles",
+           "swift_cuda_restore_particles",
            "swift_cuda_step", "swift_cuda_do_sort", "swift_cuda_do_density", "swift_cuda_do_ghost",
            "swift_cuda_do_force", "swift_cuda_get_results", "swift_cuda_get_counters", "swift_cuda_get_timings",
+           "swift_cuda_measure_fp32_peak",
            "swift_cuda_get_tree_size", "swift_cuda_get_tree", "swift_cuda_record_pairs", "swift_cuda_fetch_pairs",
            "swift_cuda_halo_pack", "swift_cuda_halo_unpack", "swift_cuda_halo_bytes_per_particle",
            "swift_cuda_host_plan", "swift_cuda_host_free"]
@@ -225,6 +228,9 @@ class HydroBackend:
             P.time_bin = arr(ic["time_bin"], np.int8).ctypes.data_as(C.POINTER(C.c_int8))
         if ic.get("id") is not None:
             P.id = arr(ic["id"], np.int64).ctypes.data_as(C.POINTER(C.c_int64))
+        for k in ("rho", "pressure", "f", "soundspeed", "balsara"):
+            if ic.get("in_" + k) is not None:
+                setattr(P, k, arr(ic["in_" + k], np.float32).ctypes.data_as(_FP))
         return P, keep
 
     # ---- building (role of space_rebuild + cache packing) ----
@@ -244,10 +250,19 @@ class HydroBackend:
         P, keep = self._parts_in(ic)
         self._check(self.lib.swift_cuda_update_particles(self.ctx, C.byref(P)))
 
+    def restore_particles(self):
+        """Device-side reset of h to the values of the last build/update (no host traffic)."""
+        self._check(self.lib.swift_cuda_restore_particles(self.ctx))
+
     # ---- operators ----
-    def step(self, do_sort=True):
-        """sort -> density -> ghost -> force -> end_force."""
-        self._check(self.lib.swift_cuda_step(self.ctx, int(do_sort)))
+    def step(self, do_sort=True, restore=False):
+        """sort -> density -> ghost -> force -> end_force.  restore: start from the h of the last build/update."""
+        self._check(self.lib.swift_cuda_step(self.ctx, (1 if do_sort else 0) | (2 if restore else 0)))
+
+    def measure_fp32_peak(self):
+        self.lib.swift_cuda_measure_fp32_peak.restype = C.c_double
+        self.lib.swift_cuda_measure_fp32_peak.argtypes = [C.c_void_p]
+        return float(self.lib.swift_cuda_measure_fp32_peak(self.ctx))
 
     def runner_do_hydro_sort(self):
         self._check(self.lib.swift_cuda_do_sort(self.ctx))

@@ -38,13 +38,17 @@ struct CellDev {
   double loc[3];
   int first;
   int count;
+  float width;   // largest edge (bounds the f32 error of the conservative candidate cull)
+  int pad;
 };
 
 // Everything a kernel needs, passed by value.
 struct Dev {
   int64_t n;
   int ncells;
-  int n_icells;
+  int n_leaves;
+  int n_units;
+  double dim[3];
   // particles, cell order
   const double *x, *y, *z;
   float4 *vm;          // vx, vy, vz, mass
@@ -58,7 +62,7 @@ struct Dev {
   float4 *dens1;       // div_v, rot_v[3]
   // force inputs (after ghost)
   float4 *fin;         // rho, pressure, grad-h f, soundspeed
-  float *balsara;
+  float4 *hb;          // h, balsara, time_bin (int bits), unused: the rest of a force neighbour
   // force outputs
   float4 *acc;         // a_hydro[3], u_dt
   float *h_dt;
@@ -71,9 +75,13 @@ struct Dev {
   const CellDev *cells;
   float *cell_hmax;        // current c->hydro.h_max
   const float *cell_hmax_old;  // value at build (h_max_old)
-  const int32_t *icells;
-  const int32_t *item_begin;
-  const Item *items;
+  const int32_t *leaves;       // [n_leaves] cell index
+  const int32_t *item_begin;   // [n_leaves+1]
+  const Item *items;           // first density pass + force
+  const int32_t *redo_begin;   // [n_leaves+1]
+  const Item *redo_items;      // ghost redo passes
+  const int32_t *unit_leaf;    // [n_units] warp unit -> leaf slot
+  const int32_t *unit_off;     //           -> first particle inside the leaf
   // sorts
   const int64_t *sort_lookup;  // [ncells*13]
   float *sort_d;

@@ -382,12 +382,30 @@ void build_tasks(const swift_cuda_params &prm, Tree &tree) {
 // Work lists
 // ---------------------------------------------------------------------------
 namespace {
+
+struct SeqItem {
+  Item it;
+  int64_t seq;  // position in the reference's (single-threaded) execution order
+};
+
+inline int8_t shift_code(const swift_cuda_params &prm, const double shift[3]) {
+  int code = 0, mul = 1;
+  for (int k = 0; k < 3; k++) {
+    const int s = shift[k] > 0.0 ? 1 : (shift[k] < 0.0 ? -1 : 0);
+    code += (s + 1) * mul;
+    mul *= 3;
+  }
+  (void)prm;
+  return (int8_t)code;
+}
+
 struct Flattener {
   const swift_cuda_params &prm;
   const Tree &tree;
   const std::vector<uint8_t> &active;
-  std::vector<std::vector<Item>> per_cell;
+  std::vector<std::vector<SeqItem>> per_cell;
   int64_t n_interactions = 0;
+  int64_t seq = 0;
 
   // cell_can_recurse_in_{pair,self}_hydro_task, src/cell.h:761-782 (dx_max_part_old = 0 after a rebuild)
   bool recurse_pair(int c) const {
@@ -399,43 +417,45 @@ struct Flattener {
     return cell.split && (kKernelGamma * tree.h_max[c] < 0.5f * cell_dmin(cell));
   }
 
-  void direct_self(int c) {
-    if (tree.cells[c].count == 0 || !active[c]) return;
+  static Item blank() {
     Item it;
     std::memset(&it, 0, sizeof(it));
+    return it;
+  }
+
+  void direct_self(int c) {
+    if (tree.cells[c].count == 0 || !active[c]) return;
+    Item it = blank();
     it.partner = c;
+    it.own = c;
+    it.kind = kSelf;
     it.sid = -1;
-    it.role = kRoleSelf;
-    for (int d = 0; d < 3; d++) it.org[d] = tree.cells[c].loc[d];
-    per_cell[c].push_back(it);
+    it.shift = 13;
+    per_cell[c].push_back(SeqItem{it, seq++});
     n_interactions++;
   }
   void direct_pair(int a, int b) {
     if (tree.cells[a].count == 0 || tree.cells[b].count == 0) return;
     if (!active[a] && !active[b]) return;
     const PairGeom g = orient_pair(prm, tree.cells, a, b);
-    Item it;
-    std::memset(&it, 0, sizeof(it));
-    it.sid = g.sid;
-    double rshift = 0.0;
-    for (int k = 0; k < 3; k++) {
-      it.shift[k] = g.shift[k];
-      rshift += g.shift[k] * kAxis[g.sid][k];
-      it.org[k] = tree.cells[g.cj].loc[k];
-    }
-    it.rshift = rshift;
+    Item it = blank();
+    it.sid = (int8_t)g.sid;
+    it.shift = shift_code(prm, g.shift);
     if (active[g.ci]) {
+      it.own = g.ci;
       it.partner = g.cj;
-      it.role = kRoleLeft;
-      per_cell[g.ci].push_back(it);
+      it.kind = kPairLeft;
+      per_cell[g.ci].push_back(SeqItem{it, seq++});
     }
     if (active[g.cj]) {
+      it.own = g.cj;
       it.partner = g.ci;
-      it.role = kRoleRight;
-      per_cell[g.cj].push_back(it);
+      it.kind = kPairRight;
+      per_cell[g.cj].push_back(SeqItem{it, seq++});
     }
     n_interactions++;
   }
+  // DOSUB_PAIR1/2, src/runner_doiact_functions_hydro.h:2524-2586, 2630-2692
   void sub_pair(int a, int b) {
     if (!active[a] && !active[b]) return;
     if (tree.cells[a].count == 0 || tree.cells[b].count == 0) return;
@@ -450,6 +470,7 @@ struct Flattener {
       direct_pair(g.ci, g.cj);
     }
   }
+  // DOSUB_SELF1/2, :2587-2617, 2693-2719
   void sub_self(int c) {
     if (tree.cells[c].count == 0 || !active[c]) return;
     if (recurse_self(c)) {
@@ -465,49 +486,184 @@ struct Flattener {
     }
   }
 };
+
+// The order in which runner_do_ghost (src/runner_ghost.c:1503-1546) re-runs the
+// density loop for the unconverged particles of one leaf: the leaf and then
+// each of its parents, every density task linked to that cell newest first,
+// each expanded by DOSUB_SUBSET (src/runner_doiact_functions_hydro.h:2721-2805).
+struct RedoBuilder {
+  const swift_cuda_params &prm;
+  const Tree &tree;
+  const std::vector<uint8_t> &active;
+  const std::vector<std::vector<int32_t>> &cell_tasks;  // tasks touching a cell, creation order
+  const Flattener &fl;
+  int leaf = -1;
+  std::vector<Item> *out = nullptr;
+
+  bool holds_leaf(int c) const {
+    const swift_cuda_cell &a = tree.cells[c], &l = tree.cells[leaf];
+    return l.first >= a.first && l.first < a.first + a.count;
+  }
+  void self_subset(int c) {
+    Item it = Flattener::blank();
+    it.partner = c;
+    it.own = c;
+    it.kind = kSubSelf;
+    it.sid = -1;
+    it.shift = 13;
+    out->push_back(it);
+  }
+  // DOPAIR_SUBSET_BRANCH, :884-937 (wraps without looking at s->periodic)
+  void pair_subset_branch(int ci, int cj) {
+    if (tree.cells[cj].count == 0) return;
+    double shift[3] = {0.0, 0.0, 0.0};
+    int code = 0;
+    for (int k = 0; k < 3; k++) {
+      const double dx = tree.cells[cj].loc[k] - tree.cells[ci].loc[k];
+      if (dx < -prm.dim[k] / 2)
+        shift[k] = prm.dim[k];
+      else if (dx > prm.dim[k] / 2)
+        shift[k] = -prm.dim[k];
+      const double w = dx + shift[k];
+      code = 3 * code + ((w < 0) ? 0 : ((w > 0) ? 2 : 1));
+    }
+    Item it = Flattener::blank();
+    it.partner = cj;
+    it.own = ci;
+    it.kind = code_is_flipped(code) ? kSubPairFlip : kSubPair;
+    it.sid = (int8_t)code_to_sid(code);
+    it.shift = shift_code(prm, shift);
+    out->push_back(it);
+  }
+  void sub_subset(int ci, int cj) {
+    if (!active[ci] && (cj < 0 || !active[cj])) return;
+    if (tree.cells[ci].count == 0 || (cj >= 0 && tree.cells[cj].count == 0)) return;
+    int sub = -1;
+    if (tree.cells[ci].split)
+      for (int k = 0; k < 8; k++) {
+        const int p = tree.cells[ci].progeny[k];
+        if (p >= 0 && holds_leaf(p)) {
+          sub = p;
+          break;
+        }
+      }
+    if (cj < 0) {
+      if (fl.recurse_self(ci)) {
+        sub_subset(sub, -1);
+        for (int j = 0; j < 8; j++) {
+          const int p = tree.cells[ci].progeny[j];
+          if (p != sub && p >= 0) sub_subset(sub, p);
+        }
+      } else {
+        self_subset(ci);
+      }
+    } else {
+      if (fl.recurse_pair(ci) && fl.recurse_pair(cj)) {
+        const PairGeom g = orient_pair(prm, tree.cells, ci, cj);
+        const OctPairs &op = oct_pairs(g.sid);
+        for (int k = 0; k < op.n; k++) {
+          const int pa = tree.cells[g.ci].progeny[op.pi[k]], pb = tree.cells[g.cj].progeny[op.pj[k]];
+          if (pa == sub && sub >= 0 && pb >= 0) sub_subset(pa, pb);
+          if (pa >= 0 && pb == sub && sub >= 0) sub_subset(pb, pa);
+        }
+      } else if (active[ci] || active[cj]) {
+        pair_subset_branch(ci, cj);
+      }
+    }
+  }
+  void build(int leaf_cell, std::vector<Item> &dst) {
+    leaf = leaf_cell;
+    out = &dst;
+    for (int fi = leaf; fi >= 0; fi = tree.cells[fi].parent) {
+      const std::vector<int32_t> &tl = cell_tasks[fi];
+      for (size_t l = tl.size(); l-- > 0;) {
+        const swift_cuda_task &t = tree.tasks[tl[l]];
+        const int other = t.cj >= 0 ? (t.ci == fi ? t.cj : t.ci) : -1;
+        switch (t.type) {
+          case 0: self_subset(fi); break;
+          case 1: pair_subset_branch(fi, other); break;
+          case 2: sub_subset(fi, -1); break;
+          default: sub_subset(fi, other); break;
+        }
+      }
+    }
+  }
+};
 }  // namespace
 
 void build_worklists(const swift_cuda_params &prm, const Tree &tree, const std::vector<uint8_t> &cell_active,
                      WorkLists &wl) {
-  Flattener f{prm, tree, cell_active, {}, 0};
-  f.per_cell.resize(tree.cells.size());
-  for (const swift_cuda_task &t : tree.tasks) {
-    switch (t.type) {
-      case 0: f.direct_self(t.ci); break;
-      case 1: f.direct_pair(t.ci, t.cj); break;
-      case 2: f.sub_self(t.ci); break;
-      default: f.sub_pair(t.ci, t.cj); break;
+  Flattener f{prm, tree, cell_active, {}, 0, 0};
+  const size_t nc = tree.cells.size();
+  f.per_cell.resize(nc);
+  std::vector<std::vector<int32_t>> cell_tasks(nc);
+  for (size_t t = 0; t < tree.tasks.size(); t++) {
+    const swift_cuda_task &tk = tree.tasks[t];
+    cell_tasks[tk.ci].push_back((int32_t)t);
+    if (tk.cj >= 0) cell_tasks[tk.cj].push_back((int32_t)t);
+    switch (tk.type) {
+      case 0: f.direct_self(tk.ci); break;
+      case 1: f.direct_pair(tk.ci, tk.cj); break;
+      case 2: f.sub_self(tk.ci); break;
+      default: f.sub_pair(tk.ci, tk.cj); break;
     }
   }
   wl = WorkLists();
   wl.n_interactions = f.n_interactions;
-  const size_t nc = tree.cells.size();
   wl.sort_lookup.assign(nc * 13, -1);
+  auto need_sort = [&](int cell, int sid) {
+    int64_t &slot = wl.sort_lookup[(size_t)cell * 13 + sid];
+    if (slot < 0) {
+      slot = wl.n_sort_entries;
+      wl.sort_cells.push_back(cell);
+      wl.sort_sids.push_back(sid);
+      wl.sort_offset.push_back(wl.n_sort_entries);
+      wl.n_sort_entries += tree.cells[cell].count;
+    }
+  };
+  RedoBuilder rb{prm, tree, cell_active, cell_tasks, f};
   wl.item_begin.push_back(0);
+  wl.redo_begin.push_back(0);
+  std::vector<const std::vector<SeqItem> *> chain;
+  std::vector<SeqItem> merged;
   for (size_t c = 0; c < nc; c++) {
-    if (f.per_cell[c].empty()) continue;
-    wl.icells.push_back((int32_t)c);
-    // self first, then pairs by axis: partners that share an axis reuse the same sorted segment
-    std::stable_sort(f.per_cell[c].begin(), f.per_cell[c].end(),
-                     [](const Item &a, const Item &b) { return a.sid < b.sid; });
-    for (const Item &it : f.per_cell[c]) {
-      wl.items.push_back(it);
-      if (it.role != kRoleSelf) {
-        // both cells of a pair need their sorted list along sid
-        for (int which = 0; which < 2; which++) {
-          const int cell = which ? it.partner : (int)c;
-          int64_t &slot = wl.sort_lookup[(size_t)cell * 13 + it.sid];
-          if (slot < 0) {
-            slot = wl.n_sort_entries;
-            wl.sort_cells.push_back(cell);
-            wl.sort_sids.push_back(it.sid);
-            wl.sort_offset.push_back(wl.n_sort_entries);
-            wl.n_sort_entries += tree.cells[cell].count;
-          }
-        }
+    const swift_cuda_cell &cell = tree.cells[c];
+    if (cell.split || cell.count == 0 || !cell_active[c]) continue;
+    // every interaction that updates this leaf's particles: its own and its ancestors', in execution order
+    chain.clear();
+    for (int a = (int)c; a >= 0; a = tree.cells[a].parent)
+      if (!f.per_cell[a].empty()) chain.push_back(&f.per_cell[a]);
+    const size_t before = wl.items.size();
+    if (chain.size() == 1) {
+      for (const SeqItem &si : *chain[0]) wl.items.push_back(si.it);
+    } else if (chain.size() > 1) {
+      merged.clear();
+      for (auto *v : chain) merged.insert(merged.end(), v->begin(), v->end());
+      std::sort(merged.begin(), merged.end(), [](const SeqItem &a, const SeqItem &b) { return a.seq < b.seq; });
+      for (const SeqItem &si : merged) wl.items.push_back(si.it);
+    }
+    const size_t rbefore = wl.redo_items.size();
+    rb.build((int)c, wl.redo_items);
+    if (wl.items.size() == before && wl.redo_items.size() == rbefore) continue;
+    for (size_t k = before; k < wl.items.size(); k++) {
+      const Item &it = wl.items[k];
+      if (it.kind != kSelf) {
+        need_sort(it.own, it.sid);
+        need_sort(it.partner, it.sid);
       }
     }
+    for (size_t k = rbefore; k < wl.redo_items.size(); k++) {
+      const Item &it = wl.redo_items[k];
+      if (it.kind != kSubSelf) need_sort(it.partner, it.sid);
+    }
+    const int32_t slot = (int32_t)wl.leaves.size();
+    wl.leaves.push_back((int32_t)c);
     wl.item_begin.push_back((int32_t)wl.items.size());
+    wl.redo_begin.push_back((int32_t)wl.redo_items.size());
+    for (int off = 0; off < cell.count; off += 32) {
+      wl.unit_leaf.push_back(slot);
+      wl.unit_off.push_back(off);
+    }
   }
 }
 

@@ -23,17 +23,28 @@ constexpr int kSubSizePair = 256000000;  // space_subsize_pair_hydro_default
 constexpr float kSpaceStretch = 1.10f;   // space_stretch, src/space.h:65
 constexpr float kKernelGamma = (float)(1.825742);  // src/kernel_hydro.h:52
 
-enum Role : int { kRoleLeft = 0, kRoleRight = 1, kRoleSelf = 2 };
+// Kinds of direct cell interaction, seen from the particles that get updated.
+enum Kind : int {
+  kSelf = 0,       // DOSELF1 / DOSELF2 inside cell `own` (f64 position differences)
+  kPairLeft = 1,   // DOPAIR1 / DOPAIR2, the updated particles lie in the pair's "ci"
+  kPairRight = 2,  // ... in the pair's "cj"
+  kSubSelf = 3,    // DOSELF_SUBSET inside cell `own` (f32 cell-relative positions)
+  kSubPair = 4,    // DOPAIR_SUBSET against `partner`, walked upwards from its first sorted particle
+  kSubPairFlip = 5 // DOPAIR_SUBSET, flipped: walked downwards from the last one
+};
 
-// One side of a direct cell interaction, seen from the cell that gets updated.
+// One direct cell interaction in the list of a leaf cell.  The updated
+// particles are those of the LEAF; `own` is the leaf or the ancestor of it at
+// whose level the reference evaluates the interaction (its loc is the frame
+// origin, its h_max enters the sorted-axis cuts).  16 bytes.
 struct Item {
-  int partner;      // cell index of the other cell (== own cell for self)
-  int sid;          // sort axis 0..12 (unused for self)
-  int role;         // kRoleLeft: this cell is "ci"; kRoleRight: this cell is "cj"; kRoleSelf
-  int pad;
-  double shift[3];  // space_getsid shift AFTER the flip (applies to ci)
-  double rshift;    // shift . runner_shift[sid]
-  double org[3];    // loc of the pair's "cj" cell: frame origin of DOPAIR1/2
+  int32_t partner;  // the other cell (== own for the self kinds)
+  int32_t own;
+  int8_t kind;      // Kind
+  int8_t sid;       // sort axis 0..12 (pairs)
+  int8_t shift;     // periodic shift of ci: (sx+1) + 3 (sy+1) + 9 (sz+1), s in {-1,0,1} box lengths
+  int8_t pad0;
+  int32_t pad1;
 };
 
 struct Tree {
@@ -45,9 +56,13 @@ struct Tree {
 };
 
 struct WorkLists {
-  std::vector<int32_t> icells;       // cells that own at least one item
-  std::vector<int32_t> item_begin;   // [icells.size()+1] offsets into items
-  std::vector<Item> items;
+  std::vector<int32_t> leaves;       // leaf cells (split == 0) that hold active particles and have work
+  std::vector<int32_t> item_begin;   // [leaves+1] offsets into items
+  std::vector<Item> items;           // first density pass and force loop, in the reference's task order
+  std::vector<int32_t> redo_begin;   // [leaves+1] offsets into redo_items
+  std::vector<Item> redo_items;      // ghost redo passes, in the order runner_do_ghost walks the task links
+  std::vector<int32_t> unit_leaf;    // warp units: index into leaves ...
+  std::vector<int32_t> unit_off;     // ... and first particle of the unit inside the leaf (32 per unit)
   std::vector<int32_t> sort_cells;   // (cell, sid) segments to sort: cell
   std::vector<int32_t> sort_sids;    //                              sid
   std::vector<int64_t> sort_offset;  // start of each segment in the flat sort arrays

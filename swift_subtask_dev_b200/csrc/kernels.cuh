@@ -17,9 +17,12 @@ namespace swiftcuda {
 
 __constant__ Consts kc;
 
-constexpr int kBlock = 128;     // threads per CTA of the pair kernels
-constexpr int kTile = 128;      // partner particles staged per shared-memory tile
+constexpr int kWarps = 4;        // warps per CTA of the neighbour-loop kernels (each warp works alone)
+constexpr int kBlock = 32 * kWarps;
+constexpr int kQ = 8;            // slots per lane of the deferred-hit queue (power of two)
 constexpr int kNumTimeBins = 56;
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kDpFlag = 0x40000000;  // queue entry: dx must be recomputed from the f64 positions
 
 // ---------------------------------------------------------------------------
 // small helpers
@@ -98,9 +101,11 @@ struct ForceAcc {
 
 struct ForceI {  // per-i quantities hoisted out of the neighbour loop
   float h, hi_inv, hid_inv, m, rho, P, f, c, bal, vx, vy, vz;
+  float Pr2;  // P / rho^2
 };
 struct ForceJ {
   float h, m, rho, P, f, c, bal, vx, vy, vz;
+  float Pr2;  // P / rho^2, formed once per particle by the ghost
   int bin;
 };
 
@@ -126,8 +131,8 @@ __device__ __forceinline__ void iact_force(ForceAcc &a, float r2, float dx, floa
   const float wj_dr = hjd_inv * wj_dx;
   const float f_ij = 1.f - pi.f / pj.m;
   const float f_ji = 1.f - pj.f / pi.m;
-  const float P_over_rho2_i = pi.P / (pi.rho * pi.rho) * f_ij;
-  const float P_over_rho2_j = pj.P / (pj.rho * pj.rho) * f_ji;
+  const float P_over_rho2_i = pi.Pr2 * f_ij;  // pressure / (rho * rho) * f, :281-282
+  const float P_over_rho2_j = pj.Pr2 * f_ji;
   float dvdr = (pi.vx - pj.vx) * dx + (pi.vy - pj.vy) * dy + (pi.vz - pj.vz) * dz;
   float dvdr_visc, visc, v_sig;
   const float rho_ij = 0.5f * (pi.rho + pj.rho);
@@ -254,223 +259,328 @@ __global__ void k_init_step(Dev d) {
   d.left[p] = 0.f;
   d.right[p] = kc.h_max;
   d.min_bin[p] = kNumTimeBins + 1;
+  if (active) {
+    d.acc[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+    d.h_dt[p] = 0.f;
+  }
 }
 
 // ---------------------------------------------------------------------------
-// K3/K5: density.  One CTA per updated cell; a thread owns one particle i of
-// the cell and keeps its eight neighbour sums in registers across all of the
-// cell's interactions; partner particles are staged through shared memory in
-// sorted-axis order and walked with the reference's early exit.
-// MODE 0: first pass (DOSELF1/DOPAIR1 arithmetic, every active particle).
-// MODE 1: ghost redo (DOSELF_SUBSET/DOPAIR_SUBSET arithmetic, gstate == 2 only).
+// Neighbour-loop machinery shared by K3 (density), K5 (ghost redo) and K6 (force)
+//
+// Work decomposition.  A warp owns up to 32 particles of ONE leaf cell, one per
+// lane, and walks that leaf's list of direct cell interactions in the order
+// the reference's single-threaded runner executes them.  For every interaction
+// the partner cell's particles are staged 32 at a time into a warp-private
+// shared-memory tile (already sorted along the pair axis, positions already in
+// the pair's frame), every lane tests every staged candidate against its own
+// sorted-axis cut and r2 < h^2 gamma^2 (FP32, one broadcast LDS.128 per
+// candidate), and pushes the hits into a per-lane FIFO in shared memory.  The
+// interaction body (runner_iact_nonsym_*) runs only when a lane's FIFO is about
+// to overflow, so that most lanes have a hit to work on: the divergence of
+// "one lane hits, 31 wait" is gone.  Hits are consumed in FIFO order into
+// register accumulators, so every particle sums its neighbours in exactly the
+// order the reference does: the results are bit-identical to the oracle.
 // ---------------------------------------------------------------------------
-struct TileJ {
-  double x[kTile], y[kTile], z[kTile];  // absolute positions (self, subset pair)
-  float fx[kTile], fy[kTile], fz[kTile];  // frame-relative positions (pair, subset self)
-  float d[kTile];                       // sort key
-  float4 vm[kTile];
-  long long id[kTile];
-  int idx[kTile];
+struct WarpTile {
+  float4 pos[32];     // frame-relative position of the candidate, sort key in w
+  float4 aux[32];     // force only: per-candidate thresholds (see k_force)
+  int idx[32];        // particle index of the candidate
+  int sel[64];        // redo: compaction of the flagged particles of a leaf
+  float4 q[kQ][32];   // deferred hits: dx, dy, dz, candidate index (or kDpFlag form)
 };
 
+__device__ __forceinline__ float next_down(float f) {
+  // f finite; largest float < f
+  if (f == 0.f) return -FLT_TRUE_MIN;
+  int b = __float_as_int(f);
+  return __int_as_float(f > 0.f ? b - 1 : b + 1);
+}
+__device__ __forceinline__ float next_up(float f) {
+  if (f == 0.f) return FLT_TRUE_MIN;
+  int b = __float_as_int(f);
+  return __int_as_float(f > 0.f ? b + 1 : b - 1);
+}
+// largest float t with (double)t < y   ("sort.d < di" with a double di)
+__device__ __forceinline__ float thr_lt(double y) {
+  if (!(y > -(double)FLT_MAX)) return -INFINITY;
+  if (y > (double)FLT_MAX) return FLT_MAX;
+  float t = __double2float_rd(y);
+  if ((double)t == y) t = next_down(t);
+  return t;
+}
+// smallest float t with (double)t > y   ("sort.d > dj" with a double dj)
+__device__ __forceinline__ float thr_gt(double y) {
+  if (!(y < (double)FLT_MAX)) return INFINITY;
+  if (y < -(double)FLT_MAX) return -FLT_MAX;
+  float t = __double2float_ru(y);
+  if ((double)t == y) t = next_up(t);
+  return t;
+}
+// smallest float t with RN((double)t - rs) > y   ("sort.d - rshift > dj")
+__device__ __forceinline__ float thr_gt_shift(double rs, double y) {
+  if (rs == 0.0) return thr_gt(y);
+  float t = __double2float_rn(__dadd_rn(y, rs));
+  if (!(fabsf(t) < FLT_MAX)) return t > 0.f ? INFINITY : -FLT_MAX;
+  for (int k = 0; k < 4; k++) {
+    const float tm = next_down(t);
+    if (__dsub_rn((double)tm, rs) > y) t = tm; else break;
+  }
+  for (int k = 0; k < 4; k++) {
+    if (!(__dsub_rn((double)t, rs) > y)) t = next_up(t); else break;
+  }
+  return t;
+}
+
+__device__ __forceinline__ float warp_max(float v) {
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(kFull, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_min(float v) {
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(kFull, v, o));
+  return v;
+}
+
+// periodic shift of an item along axis k, in box lengths {-1, 0, 1}
+__device__ __forceinline__ double item_shift(const Dev &d, int code, int k) {
+  const int s = (k == 0 ? code % 3 : (k == 1 ? (code / 3) % 3 : code / 9)) - 1;
+  return (double)s * d.dim[k];
+}
+// rshift = sum_k shift[k] * runner_shift[sid][k], accumulated from 0 in k order as the reference does
+__device__ __forceinline__ double item_rshift(const double sh[3], int sid) {
+  double r = __dmul_rn(sh[0], kc.axis[sid][0]);
+  r = __dadd_rn(r, __dmul_rn(sh[1], kc.axis[sid][1]));
+  r = __dadd_rn(r, __dmul_rn(sh[2], kc.axis[sid][2]));
+  return r;
+}
+
+// conservative FP32 cull threshold for pairs whose exact dx needs the f64 positions:
+// every true hit (exact r2 < hg2) has an approximate r2 below this.
+__device__ __forceinline__ float cull_thr(float hg2, float e) {
+  return hg2 * 1.000002f + 3.5f * sqrtf(hg2) * e + 3.f * e * e;
+}
+
+// ---------------------------------------------------------------------------
+// K3 / K5: density.
+// MODE 0: first pass, DOSELF1 / DOPAIR1 arithmetic, every active particle;
+//         one warp per 32-particle unit of a leaf.
+// MODE 1: ghost redo sweep, DOSELF_SUBSET / DOPAIR_SUBSET arithmetic, only the
+//         particles the ghost flagged (gstate == 2); one warp per leaf, which
+//         first compacts the flagged particles into full groups of 32.
+// ---------------------------------------------------------------------------
 template <int MODE>
 __global__ void __launch_bounds__(kBlock) k_density(Dev d, int sweep) {
   if (MODE == 1 && d.redo_count[sweep] == 0) return;
-  __shared__ TileJ t;
-  __shared__ int s_list[kBlock];
-  __shared__ int s_nlist;
-  const int A = d.icells[blockIdx.x];
-  const CellDev cA = d.cells[A];
-  const int ib = d.item_begin[blockIdx.x], ie = d.item_begin[blockIdx.x + 1];
+  __shared__ WarpTile tiles[kWarps];
+  WarpTile &ws = tiles[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  const int wid = blockIdx.x * kWarps + (threadIdx.x >> 5);
+  if (wid >= (MODE == 0 ? d.n_units : d.n_leaves)) return;
+  const int slot = MODE == 0 ? d.unit_leaf[wid] : wid;
+  const CellDev cL = d.cells[d.leaves[slot]];
+  const Item *__restrict__ items = MODE == 0 ? d.items : d.redo_items;
+  const int ib = (MODE == 0 ? d.item_begin : d.redo_begin)[slot];
+  const int ie = (MODE == 0 ? d.item_begin : d.redo_begin)[slot + 1];
   const bool rec = d.rec_capacity > 0;
-  const int loop = MODE;
   unsigned long long nhits = 0;
+  int scan = 0, nsel = 0;
+  bool first = true;
 
-  for (int chunk = 0; chunk < cA.count; chunk += kBlock) {
-    // which particle does this thread own in this chunk?
-    int li = chunk + threadIdx.x;
-    bool mine = li < cA.count;
+  while (true) {
+    // ---- which particle does this lane own in this round?
+    int p = -1;
     if (MODE == 0) {
-      if (mine) mine = d.time_bin[cA.first + li] <= kc.max_active_bin;
+      if (!first) break;
+      first = false;
+      const int li = d.unit_off[wid] + lane;
+      if (li < cL.count && d.time_bin[cL.first + li] <= kc.max_active_bin) p = cL.first + li;
     } else {
-      // compact the flagged particles of this chunk so that the CTA can leave early
-      if (threadIdx.x == 0) s_nlist = 0;
-      __syncthreads();
-      if (mine && d.gstate[cA.first + li] == 2) s_list[atomicAdd(&s_nlist, 1)] = li;
-      __syncthreads();
-      const int nl = s_nlist;
-      if (nl == 0) {
-        __syncthreads();
-        continue;
+      while (nsel < 32 && scan < cL.count) {
+        const int li = scan + lane;
+        const bool f = li < cL.count && d.gstate[cL.first + li] == 2;
+        const unsigned b = __ballot_sync(kFull, f);
+        if (f) ws.sel[nsel + __popc(b & ((1u << lane) - 1u))] = cL.first + li;
+        nsel += __popc(b);
+        scan += 32;
       }
-      mine = threadIdx.x < nl;
-      li = mine ? s_list[threadIdx.x] : 0;
-      __syncthreads();
+      __syncwarp();
+      if (nsel == 0) break;
+      const int take = min(nsel, 32);
+      if (lane < take) p = ws.sel[lane];
+      const int carry = (lane + 32 < nsel) ? ws.sel[lane + 32] : 0;
+      __syncwarp();
+      ws.sel[lane] = carry;
+      nsel -= take;
+      __syncwarp();
     }
-    const int64_t pi = cA.first + (mine ? li : 0);
-    const double xi = d.x[pi], yi = d.y[pi], zi = d.z[pi];
-    const float hi = d.h[pi];
+    if (!__any_sync(kFull, p >= 0)) continue;
+
+    const bool mine = p >= 0;
+    const int pp = mine ? p : cL.first;
+    const double xi = d.x[pp], yi = d.y[pp], zi = d.z[pp];
+    const float hi = d.h[pp];
     const float hig2 = sq_gamma2(hi);
     const float hi_inv = 1.f / hi;
-    const float4 vmi = d.vm[pi];
-    const long long idi = rec ? d.id[pi] : 0;
+    const float hig = __fmul_rn(hi, kc.gamma);
+    const float4 vmi = d.vm[pp];
+    const long long idi = rec ? d.id[pp] : 0;
     DensAcc acc;
     acc.zero();
+    int qhead = 0, qcnt = 0;
+
+    // one deferred hit -> runner_iact_nonsym_density
+    auto consume = [&](const float4 e) {
+      const int w = __float_as_int(e.w);
+      const int j = w & (kDpFlag - 1);
+      float dx, dy, dz;
+      if (w & kDpFlag) {
+        const int code = __float_as_int(e.x);
+        dx = dsub_f(__dsub_rn(xi, item_shift(d, code, 0)), d.x[j]);
+        dy = dsub_f(__dsub_rn(yi, item_shift(d, code, 1)), d.y[j]);
+        dz = dsub_f(__dsub_rn(zi, item_shift(d, code, 2)), d.z[j]);
+      } else {
+        dx = e.x; dy = e.y; dz = e.z;
+      }
+      const float r2 = dist2(dx, dy, dz);
+      if (r2 < hig2) {
+        iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, d.vm[j]);
+        nhits++;
+        if (rec) record_pair(d, MODE, idi, d.id[j]);
+      }
+    };
+    auto drain_round = [&]() {
+      if (qcnt > 0) {
+        const float4 e = ws.q[qhead][lane];
+        qhead = (qhead + 1) & (kQ - 1);
+        qcnt--;
+        consume(e);
+      }
+    };
 
     for (int it = ib; it < ie; it++) {
-      const Item item = d.items[it];
+      const Item item = items[it];
+      const CellDev cA = d.cells[item.own];
       const CellDev cB = d.cells[item.partner];
-      if (item.role == kRoleSelf) {
-        // ---- own cell ----
-        float pfx = 0.f, pfy = 0.f, pfz = 0.f;
-        if (MODE == 1) {
-          pfx = dsub_f(xi, cA.loc[0]);
-          pfy = dsub_f(yi, cA.loc[1]);
-          pfz = dsub_f(zi, cA.loc[2]);
+      const int kind = item.kind;
+      const int sid = item.sid;
+      const bool sorted = !(kind == kSelf || kind == kSubSelf);
+      const bool desc = (kind == kPairRight || kind == kSubPairFlip);
+      const bool dp = (kind == kSelf || kind == kSubPair || kind == kSubPairFlip);
+      const int64_t segB = sorted ? d.sort_lookup[(int64_t)item.partner * 13 + sid] : 0;
+      double sh[3] = {0.0, 0.0, 0.0};
+      if (sorted) {
+        sh[0] = item_shift(d, item.shift, 0);
+        sh[1] = item_shift(d, item.shift, 1);
+        sh[2] = item_shift(d, item.shift, 2);
+      }
+      // frame origin of the staged candidates (fo) and of this lane's particle (fl)
+      double fo[3], fl[3];
+      double px = xi, py = yi, pz = zi;
+      float lo = INFINITY, hi_cut = -INFINITY;  // lane's window on the candidates' sort keys (empty)
+      float thr = hig2;
+      if (kind == kSelf || kind == kSubSelf) {
+        for (int k = 0; k < 3; k++) fo[k] = fl[k] = cA.loc[k];
+        if (mine) { lo = -INFINITY; hi_cut = INFINITY; }
+        if (kind == kSelf) thr = cull_thr(hig2, 4e-7f * cA.width);
+      } else if (kind == kPairLeft) {
+        // this leaf's particles are "pi" of DOPAIR1 loop 1 (:1122-1216): frame cj.loc + shift
+        for (int k = 0; k < 3; k++) { fo[k] = cB.loc[k]; fl[k] = __dadd_rn(cB.loc[k], sh[k]); }
+        if (mine) {
+          const double rshift = item_rshift(sh, sid);
+          const float d_me = sort_key(xi, yi, zi, sid);
+          const double dj_min = (double)d.sort_d[segB];
+          const double hi_max = __dsub_rn((double)__fmul_rn(d.cell_hmax[item.own], kc.gamma), rshift);
+          const double di = __dsub_rn((double)__fadd_rn(d_me, hig), rshift);
+          if ((__dadd_rn((double)d_me, hi_max) > dj_min) && !(di < dj_min)) { lo = -INFINITY; hi_cut = thr_lt(di); }
         }
-        for (int base = 0; base < cB.count; base += kTile) {
-          const int nt = min(kTile, cB.count - base);
-          __syncthreads();
-          for (int k = threadIdx.x; k < nt; k += kBlock) {
-            const int64_t pj = cB.first + base + k;
-            const double xj = d.x[pj], yj = d.y[pj], zj = d.z[pj];
-            if (MODE == 0) {
-              t.x[k] = xj; t.y[k] = yj; t.z[k] = zj;
-            } else {
-              t.fx[k] = dsub_f(xj, cA.loc[0]);
-              t.fy[k] = dsub_f(yj, cA.loc[1]);
-              t.fz[k] = dsub_f(zj, cA.loc[2]);
-            }
-            t.vm[k] = d.vm[pj];
-            if (rec) t.id[k] = d.id[pj];
-          }
-          __syncthreads();
-          if (mine) {
-            for (int k = 0; k < nt; k++) {
-              if (base + k == li) continue;
-              float dx, dy, dz;
-              if (MODE == 0) {
-                dx = dsub_f(xi, t.x[k]); dy = dsub_f(yi, t.y[k]); dz = dsub_f(zi, t.z[k]);
-              } else {
-                dx = __fsub_rn(pfx, t.fx[k]); dy = __fsub_rn(pfy, t.fy[k]); dz = __fsub_rn(pfz, t.fz[k]);
-              }
-              const float r2 = dist2(dx, dy, dz);
-              if (r2 < hig2) {
-                iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, t.vm[k]);
-                nhits++;
-                if (rec) record_pair(d, loop, idi, t.id[k]);
-              }
-            }
+      } else if (kind == kPairRight) {
+        // this leaf's particles are "pj" of DOPAIR1 loop 2 (:1222-1316): frame cj.loc (their own cell)
+        for (int k = 0; k < 3; k++) { fo[k] = __dadd_rn(cA.loc[k], sh[k]); fl[k] = cA.loc[k]; }
+        if (mine) {
+          const double rshift = item_rshift(sh, sid);
+          const float d_me = sort_key(xi, yi, zi, sid);
+          const double di_max = __dsub_rn((double)d.sort_d[segB + cB.count - 1], rshift);
+          const double hj_max = (double)__fmul_rn(d.cell_hmax[item.own], kc.gamma);
+          const double dj = __dadd_rn((double)__fsub_rn(d_me, hig), rshift);
+          if ((__dsub_rn((double)d_me, hj_max) < di_max) && !(__dsub_rn(dj, rshift) > di_max)) {
+            lo = thr_gt(dj);
+            hi_cut = INFINITY;
           }
         }
       } else {
-        // ---- pair ----
-        const int sid = item.sid;
-        const int64_t segB = d.sort_lookup[(int64_t)item.partner * 13 + sid];
-        const int64_t segA = d.sort_lookup[(int64_t)A * 13 + sid];
-        const bool left = item.role == kRoleLeft;
-        const float d_me = sort_key(xi, yi, zi, sid);
-        // frame origins: particles of ci are taken relative to cj.loc + shift, those of cj relative to cj.loc
-        const double oix = __dadd_rn(item.org[0], item.shift[0]), oiy = __dadd_rn(item.org[1], item.shift[1]),
-                     oiz = __dadd_rn(item.org[2], item.shift[2]);
-        float pfx, pfy, pfz;
-        double cut;           // di (left) / dj (right) / subset di
-        double px = 0, py = 0, pz = 0;
-        bool skip = !mine;
-        if (MODE == 0) {
-          if (left) {
-            pfx = dsub_f(xi, oix); pfy = dsub_f(yi, oiy); pfz = dsub_f(zi, oiz);
-            const double dj_min = (double)d.sort_d[segB];
-            const double hi_max = __dsub_rn((double)__fmul_rn(d.cell_hmax[A], kc.gamma), item.rshift);
-            if (!(__dadd_rn((double)d_me, hi_max) > dj_min)) skip = true;
-            cut = __dsub_rn((double)__fadd_rn(d_me, __fmul_rn(hi, kc.gamma)), item.rshift);
-            if (cut < dj_min) skip = true;
-          } else {
-            pfx = dsub_f(xi, item.org[0]); pfy = dsub_f(yi, item.org[1]); pfz = dsub_f(zi, item.org[2]);
-            const double di_max = __dsub_rn((double)d.sort_d[segB + cB.count - 1], item.rshift);
-            const double hj_max = (double)__fmul_rn(d.cell_hmax[A], kc.gamma);
-            if (!(__dsub_rn((double)d_me, hj_max) < di_max)) skip = true;
-            cut = __dadd_rn((double)__fsub_rn(d_me, __fmul_rn(hi, kc.gamma)), item.rshift);
-            if (__dsub_rn(cut, item.rshift) > di_max) skip = true;
-          }
-        } else {
-          // DOPAIR_SUBSET: shift seen from this cell; "flipped" == this cell is the right one
-          const double sgn = left ? 1.0 : -1.0;
-          px = __dsub_rn(xi, sgn * item.shift[0]);
-          py = __dsub_rn(yi, sgn * item.shift[1]);
-          pz = __dsub_rn(zi, sgn * item.shift[2]);
-          const double proj0 = __dmul_rn(px, kc.axis[sid][0]), proj1 = __dmul_rn(py, kc.axis[sid][1]),
-                       proj2 = __dmul_rn(pz, kc.axis[sid][2]);
-          const float hg = left ? __fmul_rn(hi, kc.gamma) : __fmul_rn(-hi, kc.gamma);
-          cut = __dadd_rn(__dadd_rn(__dadd_rn((double)hg, proj0), proj1), proj2);
-          pfx = pfy = pfz = 0.f;
+        // DOPAIR_SUBSET (:745-770, 794-838): pix = x - shift in f64, dx = (float)(pix - pj.x)
+        px = __dsub_rn(xi, sh[0]); py = __dsub_rn(yi, sh[1]); pz = __dsub_rn(zi, sh[2]);
+        for (int k = 0; k < 3; k++) fo[k] = fl[k] = cB.loc[k];
+        thr = cull_thr(hig2, 8e-7f * fmaxf(cA.width, cB.width));
+        if (mine) {
+          const float hg = (kind == kSubPair) ? __fadd_rn(hig, 0.f) : __fsub_rn(-hig, 0.f);
+          const double cut = __dadd_rn(__dadd_rn(__dadd_rn((double)hg, __dmul_rn(px, kc.axis[sid][0])),
+                                                 __dmul_rn(py, kc.axis[sid][1])),
+                                       __dmul_rn(pz, kc.axis[sid][2]));
+          if (kind == kSubPair) { lo = -INFINITY; hi_cut = thr_lt(cut); }
+          else { lo = thr_gt(cut); hi_cut = INFINITY; }
         }
-        (void)segA;
-        // walk the partner's sorted list from the interface outwards
-        int done = skip;
-        for (int base = 0; base < cB.count; base += kTile) {
-          const int nt = min(kTile, cB.count - base);
-          if (__syncthreads_and(done)) break;
-          for (int k = threadIdx.x; k < nt; k += kBlock) {
-            const int e = left ? (base + k) : (cB.count - 1 - base - k);
-            const int lj = d.sort_i[segB + e];
-            const int64_t pj = cB.first + lj;
-            t.d[k] = d.sort_d[segB + e];
-            const double xj = d.x[pj], yj = d.y[pj], zj = d.z[pj];
-            if (MODE == 0) {
-              if (left) {  // partner is cj
-                t.fx[k] = dsub_f(xj, item.org[0]); t.fy[k] = dsub_f(yj, item.org[1]); t.fz[k] = dsub_f(zj, item.org[2]);
-              } else {     // partner is ci
-                t.fx[k] = dsub_f(xj, oix); t.fy[k] = dsub_f(yj, oiy); t.fz[k] = dsub_f(zj, oiz);
-              }
+      }
+      const float pfx = dsub_f(px, fl[0]), pfy = dsub_f(py, fl[1]), pfz = dsub_f(pz, fl[2]);
+      const float wlim = desc ? warp_min(lo) : warp_max(hi_cut);
+      if (desc ? (wlim == INFINITY) : (wlim == -INFINITY)) continue;  // no lane takes part
+      const int shiftbits = item.shift;
+
+      for (int base = 0; base < cB.count; base += 32) {
+        const int nt = min(32, cB.count - base);
+        __syncwarp();
+        {
+          const float qnan = __int_as_float(0x7fc00000);
+          float4 c = make_float4(qnan, qnan, qnan, qnan);  // padding: never in a window, never a hit
+          int j = 0;
+          if (lane < nt) {
+            float dk = 0.f;
+            if (sorted) {
+              const int e = desc ? (cB.count - 1 - base - lane) : (base + lane);
+              j = cB.first + d.sort_i[segB + e];
+              dk = d.sort_d[segB + e];
             } else {
-              t.x[k] = xj; t.y[k] = yj; t.z[k] = zj;
+              j = cB.first + base + lane;
             }
-            t.vm[k] = d.vm[pj];
-            if (rec) t.id[k] = d.id[pj];
+            c = make_float4(dsub_f(d.x[j], fo[0]), dsub_f(d.y[j], fo[1]), dsub_f(d.z[j], fo[2]), dk);
           }
-          __syncthreads();
-          if (!done) {
-            for (int k = 0; k < nt; k++) {
-              const double dk = (double)t.d[k];
-              if (left ? !(dk < cut) : !(dk > cut)) {
-                done = 1;
-                break;
-              }
-              float dx, dy, dz;
-              if (MODE == 0) {
-                dx = __fsub_rn(pfx, t.fx[k]); dy = __fsub_rn(pfy, t.fy[k]); dz = __fsub_rn(pfz, t.fz[k]);
-              } else {
-                dx = dsub_f(px, t.x[k]); dy = dsub_f(py, t.y[k]); dz = dsub_f(pz, t.z[k]);
-              }
-              const float r2 = dist2(dx, dy, dz);
-              if (r2 < hig2) {
-                iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, t.vm[k]);
-                nhits++;
-                if (rec) record_pair(d, loop, idi, t.id[k]);
+          ws.pos[lane] = c;
+          ws.idx[lane] = j;
+        }
+        __syncwarp();
+        if (sorted) {
+          const float first_key = ws.pos[0].w;
+          if (desc ? !(first_key >= wlim) : !(first_key <= wlim)) break;
+        }
+        for (int k0 = 0; k0 < nt; k0 += 4) {
+          while (__any_sync(kFull, qcnt > kQ - 4)) drain_round();
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int k = k0 + u;
+            const float4 c = ws.pos[k];
+            const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
+            const float r2 = dist2(dx, dy, dz);
+            if (c.w >= lo && c.w <= hi_cut && r2 < thr) {
+              const int j = ws.idx[k];
+              if (j != pp) {
+                ws.q[(qhead + qcnt) & (kQ - 1)][lane] =
+                    dp ? make_float4(__int_as_float(shiftbits), 0.f, 0.f, __int_as_float(j | kDpFlag))
+                       : make_float4(dx, dy, dz, __int_as_float(j));
+                qcnt++;
               }
             }
           }
         }
-        __syncthreads();
       }
     }
+    while (__any_sync(kFull, qcnt > 0)) drain_round();
     if (mine) {
-      float *o0 = reinterpret_cast<float *>(&d.dens0[pi]);
-      float *o1 = reinterpret_cast<float *>(&d.dens1[pi]);
-      atomicAdd(o0 + 0, acc.rho);
-      atomicAdd(o0 + 1, acc.rho_dh);
-      atomicAdd(o0 + 2, acc.wcount);
-      atomicAdd(o0 + 3, acc.wcount_dh);
-      atomicAdd(o1 + 0, acc.div_v);
-      atomicAdd(o1 + 1, acc.rx);
-      atomicAdd(o1 + 2, acc.ry);
-      atomicAdd(o1 + 3, acc.rz);
+      d.dens0[p] = make_float4(acc.rho, acc.rho_dh, acc.wcount, acc.wcount_dh);
+      d.dens1[p] = make_float4(acc.div_v, acc.rx, acc.ry, acc.rz);
     }
-    __syncthreads();
   }
-  const unsigned long long tot = block_sum(nhits);
-  if (threadIdx.x == 0 && tot) atomicAdd(&d.hits[MODE], tot);
+  for (int o = 16; o > 0; o >>= 1) nhits += __shfl_down_sync(kFull, nhits, o);
+  if (lane == 0 && nhits) atomicAdd(&d.hits[MODE], nhits);
 }
 
 // ---------------------------------------------------------------------------
@@ -554,7 +664,7 @@ __device__ __forceinline__ void eos_eval(float rho, float u, int mat_id, float &
   if (mat_id / 100 == 0) {
     const float g = kc.idg_gamma[mat_id % 100 & 3];
     P = (g - 1.f) * u * rho;
-    cs = sqrtf(g * (g - 1.f) * u);
+    cs = sqrtf(u * g * (g - 1.f));  // planetary/ideal_gas.h:161-165
     return;
   }
   int m = 0;
@@ -562,6 +672,25 @@ __device__ __forceinline__ void eos_eval(float rho, float u, int mat_id, float &
     if (kc.til[k].mat_id == mat_id) m = k;
   P = til_pressure(rho, u, kc.til[m]);
   cs = til_soundspeed(rho, u, kc.til[m]);
+}
+
+// cbrtf as glibc 2.39 computes it (sysdeps/ieee754/flt-32/s_cbrtf.c: frexp, a quadratic
+// seed, one Halley step in double, a table of 2^(k/3)), so that the rare bisection step of
+// the ghost gives the same bits as the oracle on the host.  CUDA's cbrtf differs in the last ulp.
+__device__ float cbrtf_glibc(float x) {
+  const double factor[5] = {1.0 / 1.5874010519681994748, 1.0 / 1.2599210498948731648, 1.0, 1.2599210498948731648,
+                            1.5874010519681994748};
+  int xe;
+  const float xm = frexpf(fabsf(x), &xe);
+  if (xe == 0 && (x == 0.f || !isfinite(x))) return x + x;
+  const float u = (float)__dadd_rn(
+      0.492659620528969547,
+      __dmul_rn(__dsub_rn(0.697570460207922770, __dmul_rn(0.191502161678719066, (double)xm)), (double)xm));
+  const float t2 = __fmul_rn(__fmul_rn(u, u), u);
+  const double num = __dmul_rn((double)u, __dadd_rn((double)t2, __dmul_rn(2.0, (double)xm)));
+  const double den = __dadd_rn(__dmul_rn(2.0, (double)t2), (double)xm);
+  const float ym = (float)__dmul_rn(__ddiv_rn(num, den), factor[2 + xe % 3]);
+  return ldexpf(x > 0.f ? ym : -ym, xe / 3);
 }
 
 __global__ void k_ghost(Dev d, int sweep) {
@@ -625,7 +754,7 @@ __global__ void k_ghost(Dev d, int sweep) {
   }
   if (!finish && fabsf(h_new - h_old) > kc.h_tol * h_old) {
     if ((h_new == left && h_old == right) || (h_old == left && h_new == right))
-      h = cbrtf(0.5f * (left * left * left + right * right * right));
+      h = cbrtf_glibc(0.5f * (left * left * left + right * right * right));
     else
       h = h_new;
     if (h < kc.h_max && h > kc.h_min) {
@@ -678,7 +807,8 @@ __global__ void k_ghost(Dev d, int sweep) {
     balsara = kc.alpha * abs_div / (abs_div + curl_v + 0.0001f * fac_Balsara_eps * soundspeed * (1.f / h));
   d.h[p] = h;
   d.fin[p] = make_float4(s0.x, pressure, grad_h_term, soundspeed);
-  d.balsara[p] = balsara;
+  // the rest of what a force neighbour needs, with P / rho^2 formed as runner_iact_force does (:281-282)
+  d.hb[p] = make_float4(h, balsara, __int_as_float((int)d.time_bin[p]), pressure / (s0.x * s0.x));
   d.acc[p] = make_float4(0.f, 0.f, 0.f, 0.f);
   d.h_dt[p] = 0.f;
   d.v_sig[p] = planetary ? soundspeed : 2.f * soundspeed;
@@ -699,207 +829,271 @@ __global__ void k_cell_hmax(Dev d) {
 }
 
 // ---------------------------------------------------------------------------
-// K6: force.  Same decomposition as K3.  A pair (L in ci, R in cj) interacts
-// when loop 1 of DOPAIR2 takes it (r2 < hL^2 g^2 inside L's sorted range) or
-// loop 2 does (r2 < hR^2 g^2, r2 >= hL^2 g^2, inside R's sorted range).
+// K6: force.  Same warp-per-unit walk as K3.  A pair (L in ci, R in cj)
+// interacts when loop 1 of DOPAIR2 takes it (:1528-1737: r2 < hL^2 g^2 with R
+// inside L's sorted range) or loop 2 does (:1741-1952: r2 < hR^2 g^2 and
+// r2 >= hL^2 g^2 with L inside R's range).  The reference applies all loop-1
+// updates of a pair before any loop-2 update, so each pair item is walked in
+// two phases and the hits of both go through the same FIFO.
+//   tile.aux per candidate:  x = h^2 gamma^2 of the candidate (self: its cull threshold)
+//                            y = candidate is cj: its "dj" of loop 2, +inf if loop 2 skips it
+//                            z = candidate is ci: largest sort key of a cj particle inside its
+//                                loop-1 range, -inf if loop 1 skips it
 // ---------------------------------------------------------------------------
-struct TileF {
-  double x[kTile], y[kTile], z[kTile];
-  float fx[kTile], fy[kTile], fz[kTile];
-  float d[kTile];
-  float4 vm[kTile];
-  float4 fin[kTile];
-  float h[kTile], bal[kTile];
-  int bin[kTile];
-  long long id[kTile];
-};
-
-struct PairCuts {  // per (pair, direction) constants of DOPAIR2, all f64 as in the reference
-  double rshift, dj_min, di_max, hi_max_g, hj_max_g;
-};
-
-// loop 1 (:1528-1737): L is the "pi" of the loop, R a particle of cj in L's range
-__device__ __forceinline__ bool force_loop1(const PairCuts &c, float dL, float hL, float dR, float r2, float hLg2) {
-  if (!(__dsub_rn(__dadd_rn((double)dL, c.hi_max_g), c.rshift) > c.dj_min)) return false;
-  const double di = __dsub_rn((double)__fadd_rn(dL, __fmul_rn(hL, kc.gamma)), c.rshift);
-  if (di < c.dj_min) return false;
-  if (!((double)dR < di)) return false;
-  return r2 < hLg2;
-}
-// loop 2 (:1741-1952): R is the "pj" of the loop, L a particle of ci in R's range
-__device__ __forceinline__ bool force_loop2(const PairCuts &c, float dL, float dR, float hR, float r2, float hLg2,
-                                            float hRg2) {
-  const double rhs = __dsub_rn(c.di_max, c.rshift);
-  if (!(__dsub_rn((double)dR, c.hj_max_g) < rhs)) return false;
-  const double dj = (double)__fsub_rn(dR, __fmul_rn(hR, kc.gamma));
-  if (dj > rhs) return false;
-  if (!(__dsub_rn((double)dL, c.rshift) > dj)) return false;
-  return (r2 < hRg2) && (r2 >= hLg2);
-}
-
 template <int SCHEME>
 __global__ void __launch_bounds__(kBlock) k_force(Dev d) {
-  __shared__ TileF t;
-  const int A = d.icells[blockIdx.x];
-  const CellDev cA = d.cells[A];
-  const int ib = d.item_begin[blockIdx.x], ie = d.item_begin[blockIdx.x + 1];
+  __shared__ WarpTile tiles[kWarps];
+  WarpTile &ws = tiles[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  const int wid = blockIdx.x * kWarps + (threadIdx.x >> 5);
+  if (wid >= d.n_units) return;
+  const int slot = d.unit_leaf[wid];
+  const CellDev cL = d.cells[d.leaves[slot]];
+  const int ib = d.item_begin[slot], ie = d.item_begin[slot + 1];
   const bool rec = d.rec_capacity > 0;
   unsigned long long nhits = 0;
 
-  for (int chunk = 0; chunk < cA.count; chunk += kBlock) {
-    const int li = chunk + threadIdx.x;
-    bool mine = li < cA.count;
-    if (mine) mine = d.time_bin[cA.first + li] <= kc.max_active_bin;
-    const int64_t pi = cA.first + (mine ? li : 0);
-    const double xi = d.x[pi], yi = d.y[pi], zi = d.z[pi];
-    ForceI me;
-    {
-      const float4 vmi = d.vm[pi];
-      const float4 fi = d.fin[pi];
-      me.h = d.h[pi];
-      me.hi_inv = 1.0f / me.h;
-      const float hi2 = me.hi_inv * me.hi_inv;
-      me.hid_inv = hi2 * hi2;
-      me.m = vmi.w; me.vx = vmi.x; me.vy = vmi.y; me.vz = vmi.z;
-      me.rho = fi.x; me.P = fi.y; me.f = fi.z; me.c = fi.w;
-      me.bal = d.balsara[pi];
-    }
-    const float hig2 = sq_gamma2(me.h);
-    const long long idi = rec ? d.id[pi] : 0;
-    ForceAcc acc;
-    acc.ax = acc.ay = acc.az = acc.u_dt = acc.h_dt = 0.f;
-    acc.v_sig = 0.f;  // combined with the stored value by max at the end
-    acc.min_bin = kNumTimeBins + 1;
-
-    for (int it = ib; it < ie; it++) {
-      const Item item = d.items[it];
-      const CellDev cB = d.cells[item.partner];
-      const bool self = item.role == kRoleSelf;
-      const bool left = item.role == kRoleLeft;
-      const int sid = self ? 0 : item.sid;
-      const int64_t segB = self ? 0 : d.sort_lookup[(int64_t)item.partner * 13 + sid];
-      const int64_t segA = self ? 0 : d.sort_lookup[(int64_t)A * 13 + sid];
-      float d_me = 0.f, pfx = 0.f, pfy = 0.f, pfz = 0.f;
-      double oix = 0, oiy = 0, oiz = 0;
-      PairCuts pc;
-      double bound = 0;  // conservative end of the walk along the partner's sorted list
-      if (!self) {
-        d_me = sort_key(xi, yi, zi, sid);
-        oix = __dadd_rn(item.org[0], item.shift[0]);
-        oiy = __dadd_rn(item.org[1], item.shift[1]);
-        oiz = __dadd_rn(item.org[2], item.shift[2]);
-        pc.rshift = item.rshift;
-        const float hmaxA = d.cell_hmax[A], hmaxB = d.cell_hmax[item.partner];
-        if (left) {  // A = ci, B = cj
-          pfx = dsub_f(xi, oix); pfy = dsub_f(yi, oiy); pfz = dsub_f(zi, oiz);
-          pc.dj_min = (double)d.sort_d[segB];
-          pc.di_max = (double)d.sort_d[segA + cA.count - 1];
-          pc.hi_max_g = __dmul_rn((double)hmaxA, (double)kc.gamma);
-          pc.hj_max_g = __dmul_rn((double)hmaxB, (double)kc.gamma);
-          const double hmx = (double)fmaxf(me.h, hmaxB) * (double)kc.gamma * 1.000001 + 1e-30;
-          bound = (double)d_me - pc.rshift + hmx + 4.0 * fabs((double)d_me) * 1.2e-7;
-        } else {     // A = cj, B = ci
-          pfx = dsub_f(xi, item.org[0]); pfy = dsub_f(yi, item.org[1]); pfz = dsub_f(zi, item.org[2]);
-          pc.dj_min = (double)d.sort_d[segA];
-          pc.di_max = (double)d.sort_d[segB + cB.count - 1];
-          pc.hi_max_g = __dmul_rn((double)hmaxB, (double)kc.gamma);
-          pc.hj_max_g = __dmul_rn((double)hmaxA, (double)kc.gamma);
-          const double hmx = (double)fmaxf(me.h, hmaxB) * (double)kc.gamma * 1.000001 + 1e-30;
-          bound = (double)d_me + pc.rshift - hmx - 4.0 * fabs((double)d_me) * 1.2e-7;
-        }
-      }
-      int done = !mine;
-      for (int base = 0; base < cB.count; base += kTile) {
-        const int nt = min(kTile, cB.count - base);
-        if (__syncthreads_and(done)) break;
-        for (int k = threadIdx.x; k < nt; k += kBlock) {
-          int lj;
-          if (self) {
-            lj = base + k;
-          } else {
-            const int e = left ? (base + k) : (cB.count - 1 - base - k);
-            lj = d.sort_i[segB + e];
-            t.d[k] = d.sort_d[segB + e];
-          }
-          const int64_t pj = cB.first + lj;
-          const double xj = d.x[pj], yj = d.y[pj], zj = d.z[pj];
-          if (self) {
-            t.x[k] = xj; t.y[k] = yj; t.z[k] = zj;
-            t.d[k] = __int_as_float(lj);
-          } else if (left) {
-            t.fx[k] = dsub_f(xj, item.org[0]); t.fy[k] = dsub_f(yj, item.org[1]); t.fz[k] = dsub_f(zj, item.org[2]);
-          } else {
-            t.fx[k] = dsub_f(xj, oix); t.fy[k] = dsub_f(yj, oiy); t.fz[k] = dsub_f(zj, oiz);
-          }
-          t.vm[k] = d.vm[pj];
-          t.fin[k] = d.fin[pj];
-          t.h[k] = d.h[pj];
-          t.bal[k] = d.balsara[pj];
-          t.bin[k] = d.time_bin[pj];
-          if (rec) t.id[k] = d.id[pj];
-        }
-        __syncthreads();
-        if (!done) {
-          for (int k = 0; k < nt; k++) {
-            float dx, dy, dz, r2;
-            bool hit;
-            const float hj = t.h[k];
-            if (self) {
-              if (base + k == li) continue;
-              dx = dsub_f(xi, t.x[k]); dy = dsub_f(yi, t.y[k]); dz = dsub_f(zi, t.z[k]);
-              r2 = dist2(dx, dy, dz);
-              hit = (r2 < hig2) || (r2 < sq_gamma2(hj));
-            } else {
-              const float dk = t.d[k];
-              if (left ? !((double)dk < bound) : !((double)dk > bound)) {
-                done = 1;
-                break;
-              }
-              dx = __fsub_rn(pfx, t.fx[k]); dy = __fsub_rn(pfy, t.fy[k]); dz = __fsub_rn(pfz, t.fz[k]);
-              r2 = dist2(dx, dy, dz);
-              const float hjg2 = sq_gamma2(hj);
-              if (left)
-                hit = force_loop1(pc, d_me, me.h, dk, r2, hig2) || force_loop2(pc, d_me, dk, hj, r2, hig2, hjg2);
-              else
-                hit = force_loop1(pc, dk, hj, d_me, r2, hjg2) || force_loop2(pc, dk, d_me, me.h, r2, hjg2, hig2);
-            }
-            if (hit) {
-              ForceJ pj;
-              const float4 vmj = t.vm[k];
-              const float4 fj = t.fin[k];
-              pj.h = hj; pj.m = vmj.w; pj.vx = vmj.x; pj.vy = vmj.y; pj.vz = vmj.z;
-              pj.rho = fj.x; pj.P = fj.y; pj.f = fj.z; pj.c = fj.w;
-              pj.bal = t.bal[k]; pj.bin = t.bin[k];
-              iact_force<SCHEME>(acc, r2, dx, dy, dz, me, pj);
-              nhits++;
-              if (rec) record_pair(d, 2, idi, t.id[k]);
-            }
-          }
-        }
-      }
-      __syncthreads();
-    }
-    if (mine) {
-      float *o = reinterpret_cast<float *>(&d.acc[pi]);
-      atomicAdd(o + 0, acc.ax);
-      atomicAdd(o + 1, acc.ay);
-      atomicAdd(o + 2, acc.az);
-      atomicAdd(o + 3, acc.u_dt);
-      atomicAdd(&d.h_dt[pi], acc.h_dt);
-      if (acc.v_sig > 0.f) atomicMax(reinterpret_cast<int *>(&d.v_sig[pi]), __float_as_int(acc.v_sig));
-      atomicMin(&d.min_bin[pi], acc.min_bin);
-    }
-    __syncthreads();
+  int p = -1;
+  {
+    const int li = d.unit_off[wid] + lane;
+    if (li < cL.count && d.time_bin[cL.first + li] <= kc.max_active_bin) p = cL.first + li;
   }
-  const unsigned long long tot = block_sum(nhits);
-  if (threadIdx.x == 0 && tot) atomicAdd(&d.hits[2], tot);
-}
+  if (!__any_sync(kFull, p >= 0)) return;
+  const bool mine = p >= 0;
+  const int pp = mine ? p : cL.first;
+  const double xi = d.x[pp], yi = d.y[pp], zi = d.z[pp];
+  ForceI me;
+  {
+    const float4 vmi = d.vm[pp];
+    const float4 fi = d.fin[pp];
+    const float4 hbi = d.hb[pp];
+    me.h = hbi.x;
+    me.hi_inv = 1.0f / me.h;
+    const float hi2 = me.hi_inv * me.hi_inv;
+    me.hid_inv = hi2 * hi2;
+    me.m = vmi.w; me.vx = vmi.x; me.vy = vmi.y; me.vz = vmi.z;
+    me.rho = fi.x; me.P = fi.y; me.f = fi.z; me.c = fi.w;
+    me.bal = hbi.y;
+    me.Pr2 = hbi.w;
+  }
+  const float hig2 = sq_gamma2(me.h);
+  const float hig = __fmul_rn(me.h, kc.gamma);
+  const long long idi = rec ? d.id[pp] : 0;
+  ForceAcc acc;
+  {
+    const float4 a0 = d.acc[pp];
+    acc.ax = a0.x; acc.ay = a0.y; acc.az = a0.z; acc.u_dt = a0.w;
+    acc.h_dt = d.h_dt[pp];
+    acc.v_sig = d.v_sig[pp];
+    acc.min_bin = d.min_bin[pp];
+  }
+  int qhead = 0, qcnt = 0;
 
-// runner_do_end_hydro_force (src/runner_others.c:618-690): hydro_end_force, Minimal/hydro.h:878-882
-__global__ void k_end_force(Dev d) {
-  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (p >= d.n) return;
-  if (d.time_bin[p] <= kc.max_active_bin) d.h_dt[p] *= d.h[p] * 0.3333333333f;
+  auto consume = [&](const float4 e) {
+    const int w = __float_as_int(e.w);
+    const int j = w & (kDpFlag - 1);
+    const float4 hbj = d.hb[j];
+    float dx, dy, dz;
+    bool hit = true;
+    if (w & kDpFlag) {  // own cell: f64 position difference (:2349-2353, 2416-2420)
+      dx = dsub_f(xi, d.x[j]); dy = dsub_f(yi, d.y[j]); dz = dsub_f(zi, d.z[j]);
+      const float r2e = dist2(dx, dy, dz);
+      hit = (r2e < hig2) || (r2e < sq_gamma2(hbj.x));
+    } else {
+      dx = e.x; dy = e.y; dz = e.z;
+    }
+    if (hit) {
+      const float r2 = dist2(dx, dy, dz);
+      const float4 vmj = d.vm[j];
+      const float4 fj = d.fin[j];
+      ForceJ pj;
+      pj.h = hbj.x; pj.bal = hbj.y; pj.bin = __float_as_int(hbj.z); pj.Pr2 = hbj.w;
+      pj.m = vmj.w; pj.vx = vmj.x; pj.vy = vmj.y; pj.vz = vmj.z;
+      pj.rho = fj.x; pj.P = fj.y; pj.f = fj.z; pj.c = fj.w;
+      iact_force<SCHEME>(acc, r2, dx, dy, dz, me, pj);
+      nhits++;
+      if (rec) record_pair(d, 2, idi, d.id[j]);
+    }
+  };
+  auto drain_round = [&]() {
+    if (qcnt > 0) {
+      const float4 e = ws.q[qhead][lane];
+      qhead = (qhead + 1) & (kQ - 1);
+      qcnt--;
+      consume(e);
+    }
+  };
+  auto push = [&](const float4 e) {
+    ws.q[(qhead + qcnt) & (kQ - 1)][lane] = e;
+    qcnt++;
+  };
+
+  for (int it = ib; it < ie; it++) {
+    const Item item = d.items[it];
+    const CellDev cA = d.cells[item.own];
+    const CellDev cB = d.cells[item.partner];
+    const int kind = item.kind;
+    const int sid = item.sid;
+
+    if (kind == kSelf) {
+      // ---- DOSELF2 (:2337-2471): every other particle of the cell, index order
+      const float e = 4e-7f * cA.width;
+      const float pfx = dsub_f(xi, cA.loc[0]), pfy = dsub_f(yi, cA.loc[1]), pfz = dsub_f(zi, cA.loc[2]);
+      const float thr_i = mine ? cull_thr(hig2, e) : -INFINITY;
+      for (int base = 0; base < cB.count; base += 32) {
+        const int nt = min(32, cB.count - base);
+        __syncwarp();
+        {
+          const float qnan = __int_as_float(0x7fc00000);
+          float4 c = make_float4(qnan, qnan, qnan, qnan);  // padding: never a hit
+          float4 a = make_float4(-INFINITY, 0.f, 0.f, 0.f);
+          int j = 0;
+          if (lane < nt) {
+            j = cB.first + base + lane;
+            c = make_float4(dsub_f(d.x[j], cA.loc[0]), dsub_f(d.y[j], cA.loc[1]), dsub_f(d.z[j], cA.loc[2]), 0.f);
+            a.x = cull_thr(sq_gamma2(d.hb[j].x), e);
+          }
+          ws.pos[lane] = c; ws.aux[lane] = a; ws.idx[lane] = j;
+        }
+        __syncwarp();
+        for (int k0 = 0; k0 < nt; k0 += 4) {
+          while (__any_sync(kFull, qcnt > kQ - 4)) drain_round();
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int k = k0 + u;
+            const float4 c = ws.pos[k];
+            const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
+            const float r2 = dist2(dx, dy, dz);
+            if (mine && (r2 < thr_i || r2 < ws.aux[k].x)) {
+              const int j = ws.idx[k];
+              if (j != pp) push(make_float4(0.f, 0.f, 0.f, __int_as_float(j | kDpFlag)));
+            }
+          }
+        }
+      }
+      continue;
+    }
+
+    // ---- DOPAIR2
+    const bool left = kind == kPairLeft;  // this leaf's cell is the pair's ci
+    const int64_t segB = d.sort_lookup[(int64_t)item.partner * 13 + sid];
+    const int64_t segA = d.sort_lookup[(int64_t)item.own * 13 + sid];
+    double sh[3] = {item_shift(d, item.shift, 0), item_shift(d, item.shift, 1), item_shift(d, item.shift, 2)};
+    const double rshift = item_rshift(sh, sid);
+    const float hmaxA = d.cell_hmax[item.own], hmaxB = d.cell_hmax[item.partner];
+    // frame: ci particles relative to cj.loc + shift, cj particles relative to cj.loc (:1480-1482)
+    double fo[3], fl[3];
+    for (int k = 0; k < 3; k++) {
+      if (left) { fo[k] = cB.loc[k]; fl[k] = __dadd_rn(cB.loc[k], sh[k]); }
+      else { fo[k] = __dadd_rn(cA.loc[k], sh[k]); fl[k] = cA.loc[k]; }
+    }
+    const float pfx = dsub_f(xi, fl[0]), pfy = dsub_f(yi, fl[1]), pfz = dsub_f(zi, fl[2]);
+    const float d_me = sort_key(xi, yi, zi, sid);
+    // constants of the pair, as the reference forms them (f64)
+    const double dj_min = (double)d.sort_d[left ? segB : segA];                       // first of cj
+    const double di_max = (double)d.sort_d[left ? (segA + cA.count - 1) : (segB + cB.count - 1)];  // last of ci
+    const double hi_max_g = __dmul_rn((double)(left ? hmaxA : hmaxB), (double)kc.gamma);
+    const double hj_max_g = __dmul_rn((double)(left ? hmaxB : hmaxA), (double)kc.gamma);
+    const double rhs2 = __dsub_rn(di_max, rshift);
+    const float hmaxBg = __fmul_rn(hmaxB, kc.gamma);
+
+    // lane-side cuts of the two phases
+    float cut1, cut2, bound1, bound2;
+    if (left) {
+      // phase 1: I am pi of loop 1; candidates R ascending while (double)dR < di
+      const double di = __dsub_rn((double)__fadd_rn(d_me, hig), rshift);
+      const bool ok1 = mine && (__dsub_rn(__dadd_rn((double)d_me, hi_max_g), rshift) > dj_min) && !(di < dj_min);
+      cut1 = ok1 ? thr_lt(di) : -INFINITY;
+      bound1 = cut1;
+      // phase 2: I am a pi inside R's loop-2 range: (double)d_me - rshift > dj(R)
+      cut2 = mine ? thr_lt(__dsub_rn((double)d_me, rshift)) : -INFINITY;
+      bound2 = -INFINITY;
+      if (mine) {
+        bound2 = cut2 + hmaxBg * 1.000001f + 1e-30f;
+        bound2 = bound2 + fabsf(bound2) * 2e-7f;
+      }
+    } else {
+      // phase 1: I am a pj inside L's loop-1 range: (double)d_me < di(L); candidates L descending
+      cut1 = mine ? d_me : INFINITY;
+      float b = (float)((double)d_me + rshift) - hmaxBg * 1.000001f - 1e-30f;
+      b = b - fabsf(b) * 2e-7f - fabsf((float)rshift) * 2e-7f;
+      bound1 = mine ? b : INFINITY;
+      // phase 2: I am pj of loop 2; candidates L descending while (double)dL - rshift > dj
+      const float djf = __fsub_rn(d_me, hig);
+      const bool ok2 = mine && (__dsub_rn((double)d_me, hj_max_g) < rhs2) && !((double)djf > rhs2);
+      cut2 = ok2 ? thr_gt_shift(rshift, (double)djf) : INFINITY;
+      bound2 = cut2;
+    }
+
+    for (int phase = 0; phase < 2; phase++) {
+      const float wlim = left ? warp_max(phase == 0 ? bound1 : bound2) : warp_min(phase == 0 ? bound1 : bound2);
+      if (left ? (wlim == -INFINITY) : (wlim == INFINITY)) continue;
+      for (int base = 0; base < cB.count; base += 32) {
+        const int nt = min(32, cB.count - base);
+        __syncwarp();
+        {
+          const float qnan = __int_as_float(0x7fc00000);
+          float4 c = make_float4(qnan, qnan, qnan, qnan);  // padding: never in a window, never a hit
+          float4 a = make_float4(0.f, INFINITY, -INFINITY, 0.f);
+          int j = 0;
+          if (lane < nt) {
+            const int e = left ? (base + lane) : (cB.count - 1 - base - lane);
+            j = cB.first + d.sort_i[segB + e];
+            const float dk = d.sort_d[segB + e];
+            c = make_float4(dsub_f(d.x[j], fo[0]), dsub_f(d.y[j], fo[1]), dsub_f(d.z[j], fo[2]), dk);
+            const float hj = d.hb[j].x;
+            const float hjg = __fmul_rn(hj, kc.gamma);
+            a.x = sq_gamma2(hj);
+            if (left) {
+              // candidate is R in cj: loop 2 outer conditions (:1741-1760)
+              const float djf = __fsub_rn(dk, hjg);
+              const bool ok = (__dsub_rn((double)dk, hj_max_g) < rhs2) && !((double)djf > rhs2);
+              a.y = ok ? djf : INFINITY;
+            } else {
+              // candidate is L in ci: loop 1 outer conditions (:1528-1545)
+              const double di = __dsub_rn((double)__fadd_rn(dk, hjg), rshift);
+              const bool ok = (__dsub_rn(__dadd_rn((double)dk, hi_max_g), rshift) > dj_min) && !(di < dj_min);
+              a.z = ok ? thr_lt(di) : -INFINITY;
+            }
+          }
+          ws.pos[lane] = c; ws.aux[lane] = a; ws.idx[lane] = j;
+        }
+        __syncwarp();
+        {
+          const float first_key = ws.pos[0].w;
+          if (left ? !(first_key <= wlim) : !(first_key >= wlim)) break;
+        }
+        for (int k0 = 0; k0 < nt; k0 += 4) {
+          while (__any_sync(kFull, qcnt > kQ - 4)) drain_round();
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int k = k0 + u;
+            const float4 c = ws.pos[k];
+            const float4 a = ws.aux[k];
+            const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
+            const float r2 = dist2(dx, dy, dz);
+            bool hit;
+            if (left) {
+              hit = (phase == 0) ? (c.w <= cut1 && r2 < hig2) : (a.y <= cut2 && r2 < a.x && r2 >= hig2);
+            } else {
+              hit = (phase == 0) ? (cut1 <= a.z && r2 < a.x) : (c.w >= cut2 && r2 < hig2 && r2 >= a.x);
+            }
+            if (hit) push(make_float4(dx, dy, dz, __int_as_float(ws.idx[k])));
+          }
+        }
+      }
+    }
+  }
+  while (__any_sync(kFull, qcnt > 0)) drain_round();
+  if (mine) {
+    d.acc[p] = make_float4(acc.ax, acc.ay, acc.az, acc.u_dt);
+    // hydro_end_force (Minimal/hydro.h:878-882), the whole of runner_do_end_hydro_force for these schemes
+    d.h_dt[p] = acc.h_dt * (me.h * 0.3333333333f);
+    d.v_sig[p] = acc.v_sig;
+    d.min_bin[p] = acc.min_bin;
+  }
+  for (int o = 16; o > 0; o >>= 1) nhits += __shfl_down_sync(kFull, nhits, o);
+  if (lane == 0 && nhits) atomicAdd(&d.hits[2], nhits);
 }
 
 }  // namespace swiftcuda

@@ -42,8 +42,8 @@ struct swift_cuda_ctx {
   swift_cuda_counters counters = {};
   swift_cuda_timings timings = {};
   long long rec_capacity = 0;
-  std::vector<float> d_first_pass;  // unused
   float4 *d_dens0_first = nullptr, *d_dens1_first = nullptr;  // snapshot of the first-pass sums
+  float *d_h0 = nullptr;     // h as last uploaded (swift_cuda_restore_particles)
 };
 
 template <typename T>
@@ -134,48 +134,71 @@ static int upload_consts(swift_cuda_ctx *c) {
   return 0;
 }
 
+// Host-side gather of the caller's particle arrays into cell order (tree.order).
+struct Packed {
+  std::vector<double> x, y, z;
+  std::vector<float4> vm, fin, hb;
+  std::vector<float> h, u;
+  std::vector<int8_t> tb;
+  std::vector<int32_t> mat;
+  std::vector<int64_t> id;
+};
+static void gather_particles(const swift_cuda_ctx *c, const swift_cuda_parts_in *in, Packed &P, bool with_static) {
+  const int64_t n = in->n;
+  const std::vector<int32_t> &ord = c->tree.order;
+  P.x.resize(n); P.y.resize(n); P.z.resize(n);
+  P.vm.resize(n); P.fin.resize(n); P.hb.resize(n); P.h.resize(n); P.u.resize(n); P.tb.resize(n);
+  if (with_static) { P.mat.resize(n); P.id.resize(n); }
+  for (int64_t k = 0; k < n; k++) {
+    const int64_t s = ord.empty() ? k : ord[k];
+    P.x[k] = in->x[3 * s];
+    P.y[k] = in->x[3 * s + 1];
+    P.z[k] = in->x[3 * s + 2];
+    P.vm[k] = make_float4(in->v[3 * s], in->v[3 * s + 1], in->v[3 * s + 2], in->mass[s]);
+    P.h[k] = in->h[s];
+    P.u[k] = in->u[s];
+    P.tb[k] = in->time_bin ? in->time_bin[s] : (int8_t)1;
+    // carried state of inactive particles (struct part: rho, force.{pressure, f, soundspeed, balsara})
+    const float rho = in->rho ? in->rho[s] : 0.f, P_ = in->pressure ? in->pressure[s] : 0.f;
+    P.fin[k] = make_float4(rho, P_, in->f ? in->f[s] : 0.f, in->soundspeed ? in->soundspeed[s] : 0.f);
+    int bin_bits = (int)P.tb[k];
+    float binf;
+    std::memcpy(&binf, &bin_bits, sizeof(float));
+    const float rho2 = rho * rho;
+    P.hb[k] = make_float4(P.h[k], in->balsara ? in->balsara[s] : 0.f, binf, P_ / rho2);
+    if (with_static) {
+      P.mat[k] = in->mat_id ? in->mat_id[s] : 0;
+      P.id[k] = in->id ? in->id[s] : s;
+    }
+  }
+}
+
 // Packs the caller's particles to the device in cell order (tree.order) and
 // uploads the tree, work lists and sort segment tables.
 static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
   const int64_t n = in->n;
   c->n = n;
   Dev &d = c->dev;
-  const std::vector<int32_t> &ord = c->tree.order;
-  std::vector<double> x(n), y(n), z(n);
-  std::vector<float4> vm(n);
-  std::vector<float> h(n), u(n);
-  std::vector<int8_t> tb(n);
-  std::vector<int32_t> mat(n);
-  std::vector<int64_t> id(n);
-  for (int64_t k = 0; k < n; k++) {
-    const int64_t s = ord.empty() ? k : ord[k];
-    x[k] = in->x[3 * s];
-    y[k] = in->x[3 * s + 1];
-    z[k] = in->x[3 * s + 2];
-    vm[k] = make_float4(in->v[3 * s], in->v[3 * s + 1], in->v[3 * s + 2], in->mass[s]);
-    h[k] = in->h[s];
-    u[k] = in->u[s];
-    tb[k] = in->time_bin ? in->time_bin[s] : (int8_t)1;
-    mat[k] = in->mat_id ? in->mat_id[s] : 0;
-    id[k] = in->id ? in->id[s] : s;
-  }
+  Packed P;
+  gather_particles(c, in, P, true);
   d.n = n;
+  for (int k = 0; k < 3; k++) d.dim[k] = c->prm.dim[k];
   double *dx, *dy, *dz;
-  if (upload(c, &dx, x.data(), n) || upload(c, &dy, y.data(), n) || upload(c, &dz, z.data(), n)) return 1;
+  if (upload(c, &dx, P.x.data(), n) || upload(c, &dy, P.y.data(), n) || upload(c, &dz, P.z.data(), n)) return 1;
   d.x = dx; d.y = dy; d.z = dz;
-  if (upload(c, &d.vm, vm.data(), n) || upload(c, &d.h, h.data(), n)) return 1;
+  if (upload(c, &d.vm, P.vm.data(), n) || upload(c, &d.h, P.h.data(), n) || upload(c, &c->d_h0, P.h.data(), n) ||
+      upload(c, &d.fin, P.fin.data(), n) || upload(c, &d.hb, P.hb.data(), n))
+    return 1;
   float *du; int8_t *dtb; int32_t *dmat; int64_t *did;
-  if (upload(c, &du, u.data(), n) || upload(c, &dtb, tb.data(), n) || upload(c, &dmat, mat.data(), n) ||
-      upload(c, &did, id.data(), n))
+  if (upload(c, &du, P.u.data(), n) || upload(c, &dtb, P.tb.data(), n) || upload(c, &dmat, P.mat.data(), n) ||
+      upload(c, &did, P.id.data(), n))
     return 1;
   d.u = du; d.time_bin = dtb; d.mat_id = dmat; d.id = did;
-  if (dmalloc(c, &d.dens0, n) || dmalloc(c, &d.dens1, n) || dmalloc(c, &d.fin, n) || dmalloc(c, &d.balsara, n) ||
+  if (dmalloc(c, &d.dens0, n) || dmalloc(c, &d.dens1, n) ||
       dmalloc(c, &d.acc, n) || dmalloc(c, &d.h_dt, n) || dmalloc(c, &d.v_sig, n) || dmalloc(c, &d.min_bin, n) ||
       dmalloc(c, &d.left, n) || dmalloc(c, &d.right, n) || dmalloc(c, &d.gstate, n) ||
       dmalloc(c, &c->d_dens0_first, n) || dmalloc(c, &c->d_dens1_first, n))
     return 1;
-  CK(cudaMemsetAsync(d.fin, 0, n * sizeof(float4), c->stream));
-  CK(cudaMemsetAsync(d.balsara, 0, n * sizeof(float), c->stream));
   CK(cudaMemsetAsync(d.acc, 0, n * sizeof(float4), c->stream));
   CK(cudaMemsetAsync(d.h_dt, 0, n * sizeof(float), c->stream));
   CK(cudaMemsetAsync(d.v_sig, 0, n * sizeof(float), c->stream));
@@ -184,9 +207,12 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
   const size_t nc = c->tree.cells.size();
   std::vector<CellDev> cells(nc);
   for (size_t k = 0; k < nc; k++) {
-    for (int a = 0; a < 3; a++) cells[k].loc[a] = c->tree.cells[k].loc[a];
-    cells[k].first = c->tree.cells[k].first;
-    cells[k].count = c->tree.cells[k].count;
+    const swift_cuda_cell &sc = c->tree.cells[k];
+    for (int a = 0; a < 3; a++) cells[k].loc[a] = sc.loc[a];
+    cells[k].first = sc.first;
+    cells[k].count = sc.count;
+    cells[k].width = (float)std::max(sc.width[0], std::max(sc.width[1], sc.width[2]));
+    cells[k].pad = 0;
   }
   d.ncells = (int)nc;
   CellDev *dcells; float *dhm_old;
@@ -195,14 +221,23 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
     return 1;
   d.cells = dcells; d.cell_hmax_old = dhm_old;
 
+
   // work lists
   const WorkLists &wl = c->wl;
-  d.n_icells = (int)wl.icells.size();
-  int32_t *dic, *dib; Item *dit; int64_t *dsl;
-  if (upload(c, &dic, wl.icells.data(), wl.icells.size()) || upload(c, &dib, wl.item_begin.data(), wl.item_begin.size()) ||
-      upload(c, &dit, wl.items.data(), wl.items.size()) || upload(c, &dsl, wl.sort_lookup.data(), wl.sort_lookup.size()))
+  d.n_leaves = (int)wl.leaves.size();
+  d.n_units = (int)wl.unit_leaf.size();
+  int32_t *dlv, *dib, *drb, *dul, *duo; Item *dit, *drt; int64_t *dsl;
+  if (upload(c, &dlv, wl.leaves.data(), wl.leaves.size()) ||
+      upload(c, &dib, wl.item_begin.data(), wl.item_begin.size()) ||
+      upload(c, &dit, wl.items.data(), wl.items.size()) ||
+      upload(c, &drb, wl.redo_begin.data(), wl.redo_begin.size()) ||
+      upload(c, &drt, wl.redo_items.data(), wl.redo_items.size()) ||
+      upload(c, &dul, wl.unit_leaf.data(), wl.unit_leaf.size()) ||
+      upload(c, &duo, wl.unit_off.data(), wl.unit_off.size()) ||
+      upload(c, &dsl, wl.sort_lookup.data(), wl.sort_lookup.size()))
     return 1;
-  d.icells = dic; d.item_begin = dib; d.items = dit; d.sort_lookup = dsl;
+  d.leaves = dlv; d.item_begin = dib; d.items = dit; d.redo_begin = drb; d.redo_items = drt;
+  d.unit_leaf = dul; d.unit_off = duo; d.sort_lookup = dsl;
   if (dmalloc(c, &d.sort_d, (size_t)wl.n_sort_entries) || dmalloc(c, &d.sort_i, (size_t)wl.n_sort_entries)) return 1;
   c->n_seg = (int)wl.sort_cells.size();
   std::vector<int64_t> scratch_off(c->n_seg, 0);
@@ -290,35 +325,81 @@ int swift_cuda_build_from_cells(swift_cuda_ctx *c, const swift_cuda_parts_in *in
 
 int swift_cuda_update_particles(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
   if (!c || !c->built) return fail("update_particles: context not built");
-  if (in->n != c->n) return fail("update_particles: particle count changed; rebuild");
+  if (!in || in->n != c->n) return fail("update_particles: particle count changed; rebuild");
   CK(cudaSetDevice(c->device));
   const int64_t n = c->n;
-  const std::vector<int32_t> &ord = c->tree.order;
-  std::vector<double> x(n), y(n), z(n);
-  std::vector<float4> vm(n);
-  std::vector<float> h(n), u(n);
-  for (int64_t k = 0; k < n; k++) {
-    const int64_t s = ord.empty() ? k : ord[k];
-    x[k] = in->x[3 * s]; y[k] = in->x[3 * s + 1]; z[k] = in->x[3 * s + 2];
-    vm[k] = make_float4(in->v[3 * s], in->v[3 * s + 1], in->v[3 * s + 2], in->mass[s]);
-    h[k] = in->h[s];
-    u[k] = in->u[s];
-  }
+  Packed P;
+  gather_particles(c, in, P, false);
   Dev &d = c->dev;
-  CK(cudaMemcpyAsync((void *)d.x, x.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync((void *)d.y, y.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync((void *)d.z, z.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(d.vm, vm.data(), n * 16, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(d.h, h.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync((void *)d.u, u.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync((void *)d.x, P.x.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync((void *)d.y, P.y.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync((void *)d.z, P.z.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(d.vm, P.vm.data(), n * 16, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(d.h, P.h.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->d_h0, P.h.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync((void *)d.u, P.u.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync((void *)d.time_bin, P.tb.data(), n, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(d.fin, P.fin.data(), n * 16, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(d.hb, P.hb.data(), n * 16, cudaMemcpyHostToDevice, c->stream));
   // cell h_max follows the particles (c->hydro.h_max after a drift)
-  std::vector<float> hs(h);
-  compute_cell_hmax(c->tree, hs.data());
+  compute_cell_hmax(c->tree, P.h.data());
   CK(cudaMemcpyAsync(d.cell_hmax, c->tree.h_max.data(), c->tree.h_max.size() * 4, cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemcpyAsync((void *)d.cell_hmax_old, c->tree.h_max.data(), c->tree.h_max.size() * 4, cudaMemcpyHostToDevice,
                      c->stream));
   CK(cudaStreamSynchronize(c->stream));
   return 0;
+}
+
+int swift_cuda_restore_particles(swift_cuda_ctx *c) {
+  if (!c || !c->built) return fail("restore_particles: context not built");
+  CK(cudaSetDevice(c->device));
+  CK(cudaMemcpyAsync(c->dev.h, c->d_h0, c->n * sizeof(float), cudaMemcpyDeviceToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->dev.cell_hmax, c->dev.cell_hmax_old, (size_t)c->dev.ncells * sizeof(float),
+                     cudaMemcpyDeviceToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// Sustained FP32 FMA rate of this GPU (the roofline denominator of the pair kernels; the
+// driver-written MEASURED_PEAKS.json has no FP32 entry).  Returns TFLOP/s, < 0 on error.
+namespace swiftcuda {
+__global__ void k_fma_peak(float *out, int iters) {
+  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f,
+        a6 = a0 + 6.f, a7 = a0 + 7.f;
+  const float b = 0.999f, c = 1e-3f;
+  for (int i = 0; i < iters; i++) {
+    a0 = __fmaf_rn(a0, b, c); a1 = __fmaf_rn(a1, b, c); a2 = __fmaf_rn(a2, b, c); a3 = __fmaf_rn(a3, b, c);
+    a4 = __fmaf_rn(a4, b, c); a5 = __fmaf_rn(a5, b, c); a6 = __fmaf_rn(a6, b, c); a7 = __fmaf_rn(a7, b, c);
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+}  // namespace swiftcuda
+
+double swift_cuda_measure_fp32_peak(swift_cuda_ctx *c) {
+  if (!c) return -1.0;
+  if (cudaSetDevice(c->device) != cudaSuccess) return -1.0;
+  const int blocks = 148 * 16, threads = 256, iters = 1 << 16;
+  float *buf = nullptr;
+  if (cudaMalloc(&buf, (size_t)blocks * threads * sizeof(float)) != cudaSuccess) return -1.0;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  k_fma_peak<<<blocks, threads, 0, c->stream>>>(buf, 1 << 10);  // warm-up
+  float best = 1e30f;
+  for (int r = 0; r < 3; r++) {
+    cudaEventRecord(e0, c->stream);
+    k_fma_peak<<<blocks, threads, 0, c->stream>>>(buf, iters);
+    cudaEventRecord(e1, c->stream);
+    cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    best = std::min(best, ms);
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(buf);
+  if (cudaGetLastError() != cudaSuccess) return -1.0;
+  return 2.0 * 8.0 * (double)iters * blocks * threads / (best * 1e-3) / 1e12;
 }
 
 // ---- phases ----------------------------------------------------------------
@@ -339,7 +420,7 @@ static int launch_density(swift_cuda_ctx *c) {
   CK(cudaMemcpyAsync(d.cell_hmax, d.cell_hmax_old, (size_t)d.ncells * sizeof(float), cudaMemcpyDeviceToDevice,
                      c->stream));
   k_init_step<<<nb, 256, 0, c->stream>>>(d);
-  if (d.n_icells > 0) k_density<0><<<d.n_icells, kBlock, 0, c->stream>>>(d, 0);
+  if (d.n_units > 0) k_density<0><<<(d.n_units + kWarps - 1) / kWarps, kBlock, 0, c->stream>>>(d, 0);
   c->counters.n_kernel_launches += 2;
   CK(cudaGetLastError());
   // keep the raw first-pass sums for inspection (parity tests)
@@ -355,7 +436,7 @@ static int launch_ghost(swift_cuda_ctx *c) {
   // redo counter of the sweep before and leaves at once when nothing is pending.
   for (int sweep = 0; sweep < c->prm.max_smoothing_iterations; sweep++) {
     k_ghost<<<nb, 256, 0, c->stream>>>(d, sweep);
-    if (d.n_icells > 0) k_density<1><<<d.n_icells, kBlock, 0, c->stream>>>(d, sweep);
+    if (d.n_leaves > 0) k_density<1><<<(d.n_leaves + kWarps - 1) / kWarps, kBlock, 0, c->stream>>>(d, sweep);
     c->counters.n_kernel_launches += 2;
   }
   k_cell_hmax<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d);
@@ -366,15 +447,15 @@ static int launch_ghost(swift_cuda_ctx *c) {
 
 static int launch_force(swift_cuda_ctx *c) {
   Dev &d = c->dev;
-  const int nb = (int)((c->n + 255) / 256);
-  if (d.n_icells > 0) {
+  // runner_do_end_hydro_force is the epilogue of the force kernel
+  if (d.n_units > 0) {
+    const int nb = (d.n_units + kWarps - 1) / kWarps;
     if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY)
-      k_force<SWIFT_CUDA_SCHEME_PLANETARY><<<d.n_icells, kBlock, 0, c->stream>>>(d);
+      k_force<SWIFT_CUDA_SCHEME_PLANETARY><<<nb, kBlock, 0, c->stream>>>(d);
     else
-      k_force<SWIFT_CUDA_SCHEME_MINIMAL><<<d.n_icells, kBlock, 0, c->stream>>>(d);
+      k_force<SWIFT_CUDA_SCHEME_MINIMAL><<<nb, kBlock, 0, c->stream>>>(d);
   }
-  k_end_force<<<nb, 256, 0, c->stream>>>(d);
-  c->counters.n_kernel_launches += 2;
+  c->counters.n_kernel_launches += 1;
   CK(cudaGetLastError());
   return 0;
 }
@@ -430,11 +511,14 @@ int swift_cuda_do_force(swift_cuda_ctx *c) {
   return finish_counters(c);
 }
 
-int swift_cuda_step(swift_cuda_ctx *c, int do_sort) {
+int swift_cuda_step(swift_cuda_ctx *c, int flags) {
   NEED_BUILT(c);
   c->counters.n_kernel_launches = 0;
   CK(cudaEventRecord(c->ev[0], c->stream));
-  if (do_sort && launch_sort(c)) return 1;
+  if (flags & SWIFT_CUDA_STEP_RESTORE) {
+    CK(cudaMemcpyAsync(c->dev.h, c->d_h0, c->n * sizeof(float), cudaMemcpyDeviceToDevice, c->stream));
+  }
+  if ((flags & SWIFT_CUDA_STEP_SORT) && launch_sort(c)) return 1;
   CK(cudaEventRecord(c->ev[1], c->stream));
   if (launch_density(c)) return 1;
   CK(cudaEventRecord(c->ev[2], c->stream));
@@ -479,8 +563,8 @@ int swift_cuda_get_results(swift_cuda_ctx *c, const swift_cuda_parts_out *out) {
     }
   }
   if (out->balsara) {
-    CK(cudaMemcpy(b1.data(), d.balsara, n * 4, cudaMemcpyDeviceToHost));
-    for (int64_t k = 0; k < n; k++) out->balsara[slot(k)] = b1[k];
+    CK(cudaMemcpy(b4.data(), d.hb, n * 16, cudaMemcpyDeviceToHost));
+    for (int64_t k = 0; k < n; k++) out->balsara[slot(k)] = b4[k].y;
   }
   if (out->a || out->u_dt) {
     CK(cudaMemcpy(b4.data(), d.acc, n * 16, cudaMemcpyDeviceToHost));
@@ -659,7 +743,7 @@ __global__ void k_halo_pack_rho(Dev d, const int32_t *idx, int64_t n, HaloRho *b
   if (k >= n) return;
   const int64_t p = idx[k];
   const float4 f = d.fin[p];
-  HaloRho r = {d.h[p], f.x, f.y, f.z, f.w, d.balsara[p]};
+  HaloRho r = {d.h[p], f.x, f.y, f.z, f.w, d.hb[p].y};
   buf[k] = r;
 }
 __global__ void k_halo_unpack_rho(Dev d, const int32_t *idx, int64_t n, const HaloRho *buf) {
@@ -669,7 +753,7 @@ __global__ void k_halo_unpack_rho(Dev d, const int32_t *idx, int64_t n, const Ha
   const HaloRho r = buf[k];
   d.h[p] = r.h;
   d.fin[p] = make_float4(r.rho, r.P, r.f, r.c);
-  d.balsara[p] = r.bal;
+  d.hb[p] = make_float4(r.h, r.bal, __int_as_float((int)d.time_bin[p]), r.P / (r.rho * r.rho));
 }
 }  // namespace swiftcuda
 
