@@ -81,7 +81,8 @@ struct Dev {
   const int32_t *redo_begin;   // [n_leaves+1]
   const Item *redo_items;      // ghost redo passes
   const int32_t *unit_leaf;    // [n_units] warp unit -> leaf slot
-  const int32_t *unit_off;     //           -> first particle inside the leaf
+  const int32_t *unit_begin;   // [n_leaves+1] first unit of a leaf
+  const int32_t *lane_part;    // [n_units*32] particle of each lane, or -1
   // sorts
   const int64_t *sort_lookup;  // [ncells*13]
   float *sort_d;

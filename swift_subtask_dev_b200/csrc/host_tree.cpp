@@ -660,10 +660,55 @@ void build_worklists(const swift_cuda_params &prm, const Tree &tree, const std::
     wl.leaves.push_back((int32_t)c);
     wl.item_begin.push_back((int32_t)wl.items.size());
     wl.redo_begin.push_back((int32_t)wl.redo_items.size());
-    for (int off = 0; off < cell.count; off += 32) {
-      wl.unit_leaf.push_back(slot);
-      wl.unit_off.push_back(off);
+    wl.unit_begin.push_back((int32_t)wl.unit_leaf.size());
+    for (int off = 0; off < cell.count; off += 32) wl.unit_leaf.push_back(slot);
+  }
+  wl.unit_begin.push_back((int32_t)wl.unit_leaf.size());
+}
+
+namespace {
+inline uint32_t spread3(uint32_t v) {  // 10 bits -> every third bit
+  v &= 0x3ff;
+  v = (v | (v << 16)) & 0x030000ff;
+  v = (v | (v << 8)) & 0x0300f00f;
+  v = (v | (v << 4)) & 0x030c30c3;
+  v = (v | (v << 2)) & 0x09249249;
+  return v;
+}
+}  // namespace
+
+void assign_lanes(const Tree &tree, const double *x, WorkLists &wl) {
+  const size_t nl = wl.leaves.size();
+  wl.lane_part.assign(wl.unit_leaf.size() * 32, -1);
+  const std::vector<int32_t> &ord = tree.order;
+  auto work = [&](size_t t, size_t nt) {
+    std::vector<std::pair<uint32_t, int32_t>> keys;
+    for (size_t s = t; s < nl; s += nt) {
+      const swift_cuda_cell &cell = tree.cells[wl.leaves[s]];
+      keys.resize(cell.count);
+      for (int k = 0; k < cell.count; k++) {
+        const int64_t slot = (int64_t)cell.first + k;
+        const int64_t src = ord.empty() ? slot : ord[slot];
+        uint32_t q[3];
+        for (int d = 0; d < 3; d++) {
+          double u = (x[3 * src + d] - cell.loc[d]) / cell.width[d];
+          u = u < 0.0 ? 0.0 : (u > 0.999999 ? 0.999999 : u);
+          q[d] = (uint32_t)(u * 1024.0);
+        }
+        keys[k] = {(spread3(q[0]) << 2) | (spread3(q[1]) << 1) | spread3(q[2]), (int32_t)slot};
+      }
+      std::sort(keys.begin(), keys.end());
+      int32_t *dst = &wl.lane_part[(size_t)wl.unit_begin[s] * 32];
+      for (int k = 0; k < cell.count; k++) dst[k] = keys[k].second;
     }
+  };
+  const size_t nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+  if (nl < 2000 || nt == 1) {
+    work(0, 1);
+  } else {
+    std::vector<std::thread> th;
+    for (size_t t = 0; t < nt; t++) th.emplace_back(work, t, nt);
+    for (auto &t : th) t.join();
   }
 }
 

@@ -61,8 +61,11 @@ struct WorkLists {
   std::vector<Item> items;           // first density pass and force loop, in the reference's task order
   std::vector<int32_t> redo_begin;   // [leaves+1] offsets into redo_items
   std::vector<Item> redo_items;      // ghost redo passes, in the order runner_do_ghost walks the task links
-  std::vector<int32_t> unit_leaf;    // warp units: index into leaves ...
-  std::vector<int32_t> unit_off;     // ... and first particle of the unit inside the leaf (32 per unit)
+  std::vector<int32_t> unit_leaf;    // warp units (32 lanes): index into leaves
+  std::vector<int32_t> unit_begin;   // [leaves+1] first unit of each leaf
+  std::vector<int32_t> lane_part;    // [units*32] particle owned by each lane (cell-order index) or -1; the
+                                     // particles of a leaf are dealt out in Morton order so that the lanes
+                                     // of a warp are spatial neighbours (same candidates, same hit rate)
   std::vector<int32_t> sort_cells;   // (cell, sid) segments to sort: cell
   std::vector<int32_t> sort_sids;    //                              sid
   std::vector<int64_t> sort_offset;  // start of each segment in the flat sort arrays
@@ -87,5 +90,9 @@ void build_tasks(const swift_cuda_params &prm, Tree &tree);
 // interactions by updated cell.  `active[c]` != 0 when cell c holds an active particle.
 void build_worklists(const swift_cuda_params &prm, const Tree &tree, const std::vector<uint8_t> &cell_active,
                      WorkLists &wl);
+
+// Fills wl.lane_part from the particle positions (cell order, [n][3] gathered through `order`
+// when it is not empty).
+void assign_lanes(const Tree &tree, const double *x, WorkLists &wl);
 
 }  // namespace swiftcuda

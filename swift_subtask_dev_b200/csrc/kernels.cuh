@@ -19,7 +19,7 @@ __constant__ Consts kc;
 
 constexpr int kWarps = 4;        // warps per CTA of the neighbour-loop kernels (each warp works alone)
 constexpr int kBlock = 32 * kWarps;
-constexpr int kQ = 8;            // slots per lane of the deferred-hit queue (power of two)
+constexpr int kQ = 16;           // slots per lane of the deferred-hit queue (power of two)
 constexpr int kNumTimeBins = 56;
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int kDpFlag = 0x40000000;  // queue entry: dx must be recomputed from the f64 positions
@@ -392,14 +392,17 @@ __global__ void __launch_bounds__(kBlock) k_density(Dev d, int sweep) {
     if (MODE == 0) {
       if (!first) break;
       first = false;
-      const int li = d.unit_off[wid] + lane;
-      if (li < cL.count && d.time_bin[cL.first + li] <= kc.max_active_bin) p = cL.first + li;
+      const int q = d.lane_part[(int64_t)wid * 32 + lane];
+      if (q >= 0 && d.time_bin[q] <= kc.max_active_bin) p = q;
     } else {
-      while (nsel < 32 && scan < cL.count) {
-        const int li = scan + lane;
-        const bool f = li < cL.count && d.gstate[cL.first + li] == 2;
+      // the leaf's particles in lane (Morton) order
+      const int64_t lp0 = (int64_t)d.unit_begin[slot] * 32;
+      const int nlp = (d.unit_begin[slot + 1] - d.unit_begin[slot]) * 32;
+      while (nsel < 32 && scan < nlp) {
+        const int q = d.lane_part[lp0 + scan + lane];
+        const bool f = q >= 0 && d.gstate[q] == 2;
         const unsigned b = __ballot_sync(kFull, f);
-        if (f) ws.sel[nsel + __popc(b & ((1u << lane) - 1u))] = cL.first + li;
+        if (f) ws.sel[nsel + __popc(b & ((1u << lane) - 1u))] = q;
         nsel += __popc(b);
         scan += 32;
       }
@@ -855,8 +858,8 @@ __global__ void __launch_bounds__(kBlock) k_force(Dev d) {
 
   int p = -1;
   {
-    const int li = d.unit_off[wid] + lane;
-    if (li < cL.count && d.time_bin[cL.first + li] <= kc.max_active_bin) p = cL.first + li;
+    const int q = d.lane_part[(int64_t)wid * 32 + lane];
+    if (q >= 0 && d.time_bin[q] <= kc.max_active_bin) p = q;
   }
   if (!__any_sync(kFull, p >= 0)) return;
   const bool mine = p >= 0;

@@ -226,18 +226,19 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
   const WorkLists &wl = c->wl;
   d.n_leaves = (int)wl.leaves.size();
   d.n_units = (int)wl.unit_leaf.size();
-  int32_t *dlv, *dib, *drb, *dul, *duo; Item *dit, *drt; int64_t *dsl;
+  int32_t *dlv, *dib, *drb, *dul, *duo, *dlp; Item *dit, *drt; int64_t *dsl;
   if (upload(c, &dlv, wl.leaves.data(), wl.leaves.size()) ||
       upload(c, &dib, wl.item_begin.data(), wl.item_begin.size()) ||
       upload(c, &dit, wl.items.data(), wl.items.size()) ||
       upload(c, &drb, wl.redo_begin.data(), wl.redo_begin.size()) ||
       upload(c, &drt, wl.redo_items.data(), wl.redo_items.size()) ||
       upload(c, &dul, wl.unit_leaf.data(), wl.unit_leaf.size()) ||
-      upload(c, &duo, wl.unit_off.data(), wl.unit_off.size()) ||
+      upload(c, &duo, wl.unit_begin.data(), wl.unit_begin.size()) ||
+      upload(c, &dlp, wl.lane_part.data(), wl.lane_part.size()) ||
       upload(c, &dsl, wl.sort_lookup.data(), wl.sort_lookup.size()))
     return 1;
   d.leaves = dlv; d.item_begin = dib; d.items = dit; d.redo_begin = drb; d.redo_items = drt;
-  d.unit_leaf = dul; d.unit_off = duo; d.sort_lookup = dsl;
+  d.unit_leaf = dul; d.unit_begin = duo; d.lane_part = dlp; d.sort_lookup = dsl;
   if (dmalloc(c, &d.sort_d, (size_t)wl.n_sort_entries) || dmalloc(c, &d.sort_i, (size_t)wl.n_sort_entries)) return 1;
   c->n_seg = (int)wl.sort_cells.size();
   std::vector<int64_t> scratch_off(c->n_seg, 0);
@@ -302,6 +303,7 @@ int swift_cuda_build_from_particles(swift_cuda_ctx *c, const swift_cuda_parts_in
   std::vector<uint8_t> act;
   cells_active(c, in, act);
   build_worklists(c->prm, c->tree, act, c->wl);
+  assign_lanes(c->tree, in->x, c->wl);
   return pack_and_upload(c, in);
 }
 
@@ -320,6 +322,7 @@ int swift_cuda_build_from_cells(swift_cuda_ctx *c, const swift_cuda_parts_in *in
   std::vector<uint8_t> act;
   cells_active(c, in, act);
   build_worklists(c->prm, c->tree, act, c->wl);
+  assign_lanes(c->tree, in->x, c->wl);
   return pack_and_upload(c, in);
 }
 
