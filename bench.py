@@ -217,13 +217,23 @@ def main():
     # ---- end to end through the C ABI with host buffers: H2D of the step's particle state,
     # the step, D2H of every result field, all inside the timed region
     e2e_times = []
-    h2d = n * (24 + 16 + 4 + 4 + 1 + 16 + 16)
-    d2h = n * 4 * (1 + 4 + 1 + 4 + 1 + 1 + 1)
+    h2d = n * (24 + 12 + 4 + 4 + 4)            # x, v, mass, h, u from pinned host memory
+    d2h = n * (4 * (6 + 3 + 3) + 1)            # h, rho, P, c, f, balsara, a[3], u_dt, h_dt, v_sig, min_ngb_time_bin
+    ic_pin = {}
+    keep = []
+    for k, a in ic.items():
+        if isinstance(a, np.ndarray):
+            t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+            keep.append(t)
+            ic_pin[k] = t.numpy()
+        else:
+            ic_pin[k] = a
+    out_pin = be.alloc_results(pinned=True)
     for k in range(max(1, min(args.steps, 2)) + 1):
         t0 = time.perf_counter()
-        be.update_particles(ic)
+        be.update_particles(ic_pin)
         be.step()
-        be.results()
+        be.results(out=out_pin)
         dt = time.perf_counter() - t0
         if k > 0:
             e2e_times.append(dt)

@@ -279,15 +279,30 @@ class HydroBackend:
         self._check(self.lib.swift_cuda_do_force(self.ctx))
 
     # ---- results ----
-    def results(self, first_pass=False):
+    def alloc_results(self, first_pass=False, pinned=False):
+        """Output arrays for results(out=...); pinned=True allocates page-locked host memory (torch)."""
         n = self.n
+        fields = OUT_FIELDS + (OUT_FIRST if first_pass else []) + [("min_ngb_time_bin", 1)]
         out = {}
-        P = PartsOut()
-        fields = OUT_FIELDS + (OUT_FIRST if first_pass else [])
         for k, w in fields:
-            out[k] = np.zeros((n, w) if w > 1 else n, dtype=np.float32)
-            setattr(P, k, out[k].ctypes.data_as(_FP))
-        out["min_ngb_time_bin"] = np.zeros(n, dtype=np.int8)
+            dt = np.int8 if k == "min_ngb_time_bin" else np.float32
+            shape = (n, w) if w > 1 else (n,)
+            if pinned:
+                import torch
+                t = torch.empty(shape, dtype=torch.int8 if dt == np.int8 else torch.float32, pin_memory=True)
+                out[k] = t.numpy()
+                self._keep.append(t)
+            else:
+                out[k] = np.zeros(shape, dtype=dt)
+        return out
+
+    def results(self, first_pass=False, out=None):
+        if out is None:
+            out = self.alloc_results(first_pass)
+        P = PartsOut()
+        for k, w in OUT_FIELDS + OUT_FIRST:
+            if k in out:
+                setattr(P, k, out[k].ctypes.data_as(_FP))
         P.min_ngb_time_bin = out["min_ngb_time_bin"].ctypes.data_as(C.POINTER(C.c_int8))
         self._check(self.lib.swift_cuda_get_results(self.ctx, C.byref(P)))
         return out

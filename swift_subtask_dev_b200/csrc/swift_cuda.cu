@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "kernels.cuh"
+#include "pack.cuh"
 
 using namespace swiftcuda;
 
@@ -44,6 +45,14 @@ struct swift_cuda_ctx {
   long long rec_capacity = 0;
   float4 *d_dens0_first = nullptr, *d_dens1_first = nullptr;  // snapshot of the first-pass sums
   float *d_h0 = nullptr;     // h as last uploaded (swift_cuda_restore_particles)
+  // caller-order staging on the device (K1 pack / K7 unpack)
+  double *s_x = nullptr;
+  float *s_v = nullptr, *s_mass = nullptr, *s_h = nullptr, *s_u = nullptr, *s_carry[5] = {};
+  int8_t *s_tb = nullptr;
+  int32_t *s_mat = nullptr, *s_order = nullptr;
+  int64_t *s_id = nullptr;
+  float *s_out = nullptr;    // 20 floats per particle
+  int8_t *s_out_bin = nullptr;
 };
 
 template <typename T>
@@ -134,66 +143,79 @@ static int upload_consts(swift_cuda_ctx *c) {
   return 0;
 }
 
-// Host-side gather of the caller's particle arrays into cell order (tree.order).
-struct Packed {
-  std::vector<double> x, y, z;
-  std::vector<float4> vm, fin, hb;
-  std::vector<float> h, u;
-  std::vector<int8_t> tb;
-  std::vector<int32_t> mat;
-  std::vector<int64_t> id;
-};
-static void gather_particles(const swift_cuda_ctx *c, const swift_cuda_parts_in *in, Packed &P, bool with_static) {
-  const int64_t n = in->n;
-  const std::vector<int32_t> &ord = c->tree.order;
-  P.x.resize(n); P.y.resize(n); P.z.resize(n);
-  P.vm.resize(n); P.fin.resize(n); P.hb.resize(n); P.h.resize(n); P.u.resize(n); P.tb.resize(n);
-  if (with_static) { P.mat.resize(n); P.id.resize(n); }
-  for (int64_t k = 0; k < n; k++) {
-    const int64_t s = ord.empty() ? k : ord[k];
-    P.x[k] = in->x[3 * s];
-    P.y[k] = in->x[3 * s + 1];
-    P.z[k] = in->x[3 * s + 2];
-    P.vm[k] = make_float4(in->v[3 * s], in->v[3 * s + 1], in->v[3 * s + 2], in->mass[s]);
-    P.h[k] = in->h[s];
-    P.u[k] = in->u[s];
-    P.tb[k] = in->time_bin ? in->time_bin[s] : (int8_t)1;
-    // carried state of inactive particles (struct part: rho, force.{pressure, f, soundspeed, balsara})
-    const float rho = in->rho ? in->rho[s] : 0.f, P_ = in->pressure ? in->pressure[s] : 0.f;
-    P.fin[k] = make_float4(rho, P_, in->f ? in->f[s] : 0.f, in->soundspeed ? in->soundspeed[s] : 0.f);
-    int bin_bits = (int)P.tb[k];
-    float binf;
-    std::memcpy(&binf, &bin_bits, sizeof(float));
-    const float rho2 = rho * rho;
-    P.hb[k] = make_float4(P.h[k], in->balsara ? in->balsara[s] : 0.f, binf, P_ / rho2);
-    if (with_static) {
-      P.mat[k] = in->mat_id ? in->mat_id[s] : 0;
-      P.id[k] = in->id ? in->id[s] : s;
-    }
+// Copies the caller's arrays to the device as they are and permutes them into the cell-ordered
+// SoA layout there (k_pack).  with_static: also mat_id / id / the order table (build only).
+static int upload_and_pack(swift_cuda_ctx *c, const swift_cuda_parts_in *in, bool with_static) {
+  const int64_t n = c->n;
+  Dev &d = c->dev;
+  cudaStream_t st = c->stream;
+  RawIn r;
+  std::memset(&r, 0, sizeof(r));
+  CK(cudaMemcpyAsync(c->s_x, in->x, n * 24, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(c->s_v, in->v, n * 12, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(c->s_mass, in->mass, n * 4, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(c->s_h, in->h, n * 4, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(c->s_u, in->u, n * 4, cudaMemcpyHostToDevice, st));
+  r.x = c->s_x; r.v = c->s_v; r.mass = c->s_mass; r.h = c->s_h; r.u = c->s_u;
+  if (in->time_bin) {
+    CK(cudaMemcpyAsync(c->s_tb, in->time_bin, n, cudaMemcpyHostToDevice, st));
+    r.time_bin = c->s_tb;
   }
+  const float *carry[5] = {in->rho, in->pressure, in->f, in->soundspeed, in->balsara};
+  const float **rc[5] = {&r.rho, &r.pressure, &r.f, &r.soundspeed, &r.balsara};
+  for (int k = 0; k < 5; k++)
+    if (carry[k]) {
+      if (!c->s_carry[k] && dmalloc(c, &c->s_carry[k], (size_t)n)) return 1;
+      CK(cudaMemcpyAsync(c->s_carry[k], carry[k], n * 4, cudaMemcpyHostToDevice, st));
+      *rc[k] = c->s_carry[k];
+    }
+  if (with_static) {
+    if (in->mat_id) {
+      CK(cudaMemcpyAsync(c->s_mat, in->mat_id, n * 4, cudaMemcpyHostToDevice, st));
+      r.mat_id = c->s_mat;
+    }
+    if (in->id) {
+      CK(cudaMemcpyAsync(c->s_id, in->id, n * 8, cudaMemcpyHostToDevice, st));
+      r.id = c->s_id;
+    }
+    if (!c->tree.order.empty())
+      CK(cudaMemcpyAsync(c->s_order, c->tree.order.data(), n * 4, cudaMemcpyHostToDevice, st));
+  }
+  r.order = c->tree.order.empty() ? nullptr : c->s_order;
+  PackDst o;
+  o.x = const_cast<double *>(d.x); o.y = const_cast<double *>(d.y); o.z = const_cast<double *>(d.z);
+  o.vm = d.vm; o.fin = d.fin; o.hb = d.hb; o.h = d.h; o.h0 = c->d_h0; o.u = const_cast<float *>(d.u);
+  o.time_bin = const_cast<int8_t *>(d.time_bin);
+  o.mat_id = const_cast<int32_t *>(d.mat_id);
+  o.id = const_cast<int64_t *>(d.id);
+  if (n > 0) k_pack<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, r, o, with_static ? 1 : 0);
+  CK(cudaGetLastError());
+  return 0;
 }
 
-// Packs the caller's particles to the device in cell order (tree.order) and
-// uploads the tree, work lists and sort segment tables.
+// Allocates the device arrays, packs the particles (device side) and uploads the tree, work
+// lists and sort segment tables.
 static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
   const int64_t n = in->n;
   c->n = n;
   Dev &d = c->dev;
-  Packed P;
-  gather_particles(c, in, P, true);
   d.n = n;
   for (int k = 0; k < 3; k++) d.dim[k] = c->prm.dim[k];
   double *dx, *dy, *dz;
-  if (upload(c, &dx, P.x.data(), n) || upload(c, &dy, P.y.data(), n) || upload(c, &dz, P.z.data(), n)) return 1;
-  d.x = dx; d.y = dy; d.z = dz;
-  if (upload(c, &d.vm, P.vm.data(), n) || upload(c, &d.h, P.h.data(), n) || upload(c, &c->d_h0, P.h.data(), n) ||
-      upload(c, &d.fin, P.fin.data(), n) || upload(c, &d.hb, P.hb.data(), n))
-    return 1;
   float *du; int8_t *dtb; int32_t *dmat; int64_t *did;
-  if (upload(c, &du, P.u.data(), n) || upload(c, &dtb, P.tb.data(), n) || upload(c, &dmat, P.mat.data(), n) ||
-      upload(c, &did, P.id.data(), n))
+  if (dmalloc(c, &dx, n) || dmalloc(c, &dy, n) || dmalloc(c, &dz, n) || dmalloc(c, &d.vm, n) || dmalloc(c, &d.h, n) ||
+      dmalloc(c, &c->d_h0, n) || dmalloc(c, &d.fin, n) || dmalloc(c, &d.hb, n) || dmalloc(c, &du, n) ||
+      dmalloc(c, &dtb, n) || dmalloc(c, &dmat, n) || dmalloc(c, &did, n))
     return 1;
-  d.u = du; d.time_bin = dtb; d.mat_id = dmat; d.id = did;
+  d.x = dx; d.y = dy; d.z = dz; d.u = du; d.time_bin = dtb; d.mat_id = dmat; d.id = did;
+  if (dmalloc(c, &c->s_x, (size_t)n * 3) || dmalloc(c, &c->s_v, (size_t)n * 3) || dmalloc(c, &c->s_mass, n) ||
+      dmalloc(c, &c->s_h, n) || dmalloc(c, &c->s_u, n) || dmalloc(c, &c->s_tb, n) || dmalloc(c, &c->s_mat, n) ||
+      dmalloc(c, &c->s_id, n) || dmalloc(c, &c->s_order, n))
+    return 1;
+  for (int k = 0; k < 5; k++) c->s_carry[k] = nullptr;
+  c->s_out = nullptr;
+  c->s_out_bin = nullptr;
+  if (upload_and_pack(c, in, true)) return 1;
   if (dmalloc(c, &d.dens0, n) || dmalloc(c, &d.dens1, n) ||
       dmalloc(c, &d.acc, n) || dmalloc(c, &d.h_dt, n) || dmalloc(c, &d.v_sig, n) || dmalloc(c, &d.min_bin, n) ||
       dmalloc(c, &d.left, n) || dmalloc(c, &d.right, n) || dmalloc(c, &d.gstate, n) ||
@@ -329,26 +351,15 @@ int swift_cuda_build_from_cells(swift_cuda_ctx *c, const swift_cuda_parts_in *in
 int swift_cuda_update_particles(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
   if (!c || !c->built) return fail("update_particles: context not built");
   if (!in || in->n != c->n) return fail("update_particles: particle count changed; rebuild");
+  if (!in->x || !in->v || !in->mass || !in->h || !in->u) return fail("update_particles: null argument");
   CK(cudaSetDevice(c->device));
-  const int64_t n = c->n;
-  Packed P;
-  gather_particles(c, in, P, false);
-  Dev &d = c->dev;
-  CK(cudaMemcpyAsync((void *)d.x, P.x.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync((void *)d.y, P.y.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync((void *)d.z, P.z.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(d.vm, P.vm.data(), n * 16, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(d.h, P.h.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(c->d_h0, P.h.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync((void *)d.u, P.u.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync((void *)d.time_bin, P.tb.data(), n, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(d.fin, P.fin.data(), n * 16, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(d.hb, P.hb.data(), n * 16, cudaMemcpyHostToDevice, c->stream));
+  if (upload_and_pack(c, in, false)) return 1;
   // cell h_max follows the particles (c->hydro.h_max after a drift)
-  compute_cell_hmax(c->tree, P.h.data());
-  CK(cudaMemcpyAsync(d.cell_hmax, c->tree.h_max.data(), c->tree.h_max.size() * 4, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync((void *)d.cell_hmax_old, c->tree.h_max.data(), c->tree.h_max.size() * 4, cudaMemcpyHostToDevice,
-                     c->stream));
+  Dev &d = c->dev;
+  if (d.ncells > 0)
+    k_cell_hmax_init<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d, d.cell_hmax,
+                                                                         const_cast<float *>(d.cell_hmax_old));
+  CK(cudaGetLastError());
   CK(cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -544,78 +555,35 @@ int swift_cuda_step(swift_cuda_ctx *c, int flags) {
 // ---- results ---------------------------------------------------------------
 int swift_cuda_get_results(swift_cuda_ctx *c, const swift_cuda_parts_out *out) {
   NEED_BUILT(c);
+  if (!out) return fail("get_results: null argument");
   const int64_t n = c->n;
   Dev &d = c->dev;
-  const std::vector<int32_t> &ord = c->tree.order;
-  auto slot = [&](int64_t k) -> int64_t { return ord.empty() ? k : ord[k]; };
-  std::vector<float4> b4(n);
-  std::vector<float> b1(n);
+  if (!c->s_out) {
+    if (dmalloc(c, &c->s_out, (size_t)n * 20) || dmalloc(c, &c->s_out_bin, (size_t)n)) return 1;
+  }
+  // K7: scatter to caller order on the device, then one copy per requested field
+  struct Field { float *host; int width; float **dev; };
+  RawOut r;
+  std::memset(&r, 0, sizeof(r));
+  Field fields[] = {{out->h, 1, &r.h}, {out->rho, 1, &r.rho}, {out->pressure, 1, &r.pressure},
+                    {out->soundspeed, 1, &r.soundspeed}, {out->f, 1, &r.f}, {out->balsara, 1, &r.balsara},
+                    {out->a, 3, &r.a}, {out->u_dt, 1, &r.u_dt}, {out->h_dt, 1, &r.h_dt}, {out->v_sig, 1, &r.v_sig},
+                    {out->d_rho, 1, &r.d_rho}, {out->d_rho_dh, 1, &r.d_rho_dh}, {out->d_wcount, 1, &r.d_wcount},
+                    {out->d_wcount_dh, 1, &r.d_wcount_dh}, {out->d_div_v, 1, &r.d_div_v}, {out->d_rot_v, 3, &r.d_rot_v}};
+  int64_t off = 0;
+  for (Field &f : fields) {
+    if (f.host) *f.dev = c->s_out + off;
+    off += (int64_t)f.width * n;
+  }
+  if (out->min_ngb_time_bin) r.min_bin = c->s_out_bin;
+  r.order = c->tree.order.empty() ? nullptr : c->s_order;
+  if (n > 0) k_unpack<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(d, r, c->d_dens0_first, c->d_dens1_first);
+  CK(cudaGetLastError());
+  for (Field &f : fields)
+    if (f.host) CK(cudaMemcpyAsync(f.host, *f.dev, (size_t)f.width * n * 4, cudaMemcpyDeviceToHost, c->stream));
+  if (out->min_ngb_time_bin)
+    CK(cudaMemcpyAsync(out->min_ngb_time_bin, c->s_out_bin, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
-  if (out->h) {
-    CK(cudaMemcpy(b1.data(), d.h, n * 4, cudaMemcpyDeviceToHost));
-    for (int64_t k = 0; k < n; k++) out->h[slot(k)] = b1[k];
-  }
-  if (out->rho || out->pressure || out->f || out->soundspeed) {
-    CK(cudaMemcpy(b4.data(), d.fin, n * 16, cudaMemcpyDeviceToHost));
-    for (int64_t k = 0; k < n; k++) {
-      const int64_t s = slot(k);
-      if (out->rho) out->rho[s] = b4[k].x;
-      if (out->pressure) out->pressure[s] = b4[k].y;
-      if (out->f) out->f[s] = b4[k].z;
-      if (out->soundspeed) out->soundspeed[s] = b4[k].w;
-    }
-  }
-  if (out->balsara) {
-    CK(cudaMemcpy(b4.data(), d.hb, n * 16, cudaMemcpyDeviceToHost));
-    for (int64_t k = 0; k < n; k++) out->balsara[slot(k)] = b4[k].y;
-  }
-  if (out->a || out->u_dt) {
-    CK(cudaMemcpy(b4.data(), d.acc, n * 16, cudaMemcpyDeviceToHost));
-    for (int64_t k = 0; k < n; k++) {
-      const int64_t s = slot(k);
-      if (out->a) {
-        out->a[3 * s] = b4[k].x;
-        out->a[3 * s + 1] = b4[k].y;
-        out->a[3 * s + 2] = b4[k].z;
-      }
-      if (out->u_dt) out->u_dt[s] = b4[k].w;
-    }
-  }
-  if (out->h_dt) {
-    CK(cudaMemcpy(b1.data(), d.h_dt, n * 4, cudaMemcpyDeviceToHost));
-    for (int64_t k = 0; k < n; k++) out->h_dt[slot(k)] = b1[k];
-  }
-  if (out->v_sig) {
-    CK(cudaMemcpy(b1.data(), d.v_sig, n * 4, cudaMemcpyDeviceToHost));
-    for (int64_t k = 0; k < n; k++) out->v_sig[slot(k)] = b1[k];
-  }
-  if (out->min_ngb_time_bin) {
-    std::vector<int> bi(n);
-    CK(cudaMemcpy(bi.data(), d.min_bin, n * 4, cudaMemcpyDeviceToHost));
-    for (int64_t k = 0; k < n; k++) out->min_ngb_time_bin[slot(k)] = (int8_t)bi[k];
-  }
-  if (out->d_rho || out->d_rho_dh || out->d_wcount || out->d_wcount_dh) {
-    CK(cudaMemcpy(b4.data(), c->d_dens0_first, n * 16, cudaMemcpyDeviceToHost));
-    for (int64_t k = 0; k < n; k++) {
-      const int64_t s = slot(k);
-      if (out->d_rho) out->d_rho[s] = b4[k].x;
-      if (out->d_rho_dh) out->d_rho_dh[s] = b4[k].y;
-      if (out->d_wcount) out->d_wcount[s] = b4[k].z;
-      if (out->d_wcount_dh) out->d_wcount_dh[s] = b4[k].w;
-    }
-  }
-  if (out->d_div_v || out->d_rot_v) {
-    CK(cudaMemcpy(b4.data(), c->d_dens1_first, n * 16, cudaMemcpyDeviceToHost));
-    for (int64_t k = 0; k < n; k++) {
-      const int64_t s = slot(k);
-      if (out->d_div_v) out->d_div_v[s] = b4[k].x;
-      if (out->d_rot_v) {
-        out->d_rot_v[3 * s] = b4[k].y;
-        out->d_rot_v[3 * s + 1] = b4[k].z;
-        out->d_rot_v[3 * s + 2] = b4[k].w;
-      }
-    }
-  }
   return 0;
 }
 
