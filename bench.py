@@ -178,7 +178,7 @@ def main():
     from swift_subtask_dev_b200 import HydroBackend, ics, make_params
     if world > 1:
         from swift_subtask_dev_b200 import multi
-        return multi.bench_multi(args, cfg, METRIC, UNIT)
+        return multi.bench_multi(args, cfg, METRIC, UNIT, sampler_cls=ClockSampler)
 
     torch.cuda.set_device(0)
     ic = ics.uniform_random(args.side ** 3, seed=cfg["seed"])

@@ -143,6 +143,9 @@ typedef struct {
 typedef struct swift_cuda_ctx swift_cuda_ctx;
 
 int swift_cuda_abi_version(void);
+/* sizeof of the ABI structs as compiled into the library, for binding checks:
+ * 0 params, 1 cell, 2 task, 3 parts_in, 4 parts_out, 5 counters, 6 timings, 7 til. */
+size_t swift_cuda_sizeof(int which);
 const char *swift_cuda_last_error(void);
 
 /* Context on CUDA device `device`. */
@@ -221,6 +224,17 @@ int swift_cuda_halo_pack(swift_cuda_ctx *ctx, int phase, const int32_t *d_index,
 int swift_cuda_halo_unpack(swift_cuda_ctx *ctx, int phase, const int32_t *d_index, int64_t count,
                            const void *d_buffer, void *stream);
 size_t swift_cuda_halo_bytes_per_particle(int phase);
+/* d_index entries are positions in the library's cell order: cell_order_slot =
+ * inverse of the `order` table swift_cuda_get_tree returns. */
+
+/* mask[k] = 1 (caller order, n bytes) when particle k lies in a cell that an
+ * interaction of an active leaf reads: what a rank must keep fresh in its halo. */
+int swift_cuda_get_touched(swift_cuda_ctx *ctx, uint8_t *mask);
+
+/* Recomputes every cell's h_max from the device copy of h.  after_ghost = 0:
+ * from scratch, also h_max_old (after an xv refresh); 1: raise to cover the
+ * current h (after a rho refresh), as runner_do_ghost leaves it. */
+int swift_cuda_refresh_cell_hmax(swift_cuda_ctx *ctx, int after_ghost);
 
 #ifdef __cplusplus
 }

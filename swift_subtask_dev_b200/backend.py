@@ -95,7 +95,7 @@ class Timings(C.Structure):
                 ("total_ms", C.c_float)]
 
 
-EXPORTS = ["swift_cuda_abi_version", "swift_cuda_last_error", "swift_cuda_create", "swift_cuda_destroy",
+EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error", "swift_cuda_create", "swift_cuda_destroy",
            "swift_cuda_build_from_particles", "swift_cuda_build_from_cells", "swift_cuda_update_particles",
            "swift_cuda_restore_particles",
            "swift_cuda_step", "swift_cuda_do_sort", "swift_cuda_do_density", "swift_cuda_do_ghost",
@@ -103,6 +103,7 @@ EXPORTS = ["swift_cuda_abi_version", "swift_cuda_last_error", "swift_cuda_create
            "swift_cuda_measure_fp32_peak",
            "swift_cuda_get_tree_size", "swift_cuda_get_tree", "swift_cuda_record_pairs", "swift_cuda_fetch_pairs",
            "swift_cuda_halo_pack", "swift_cuda_halo_unpack", "swift_cuda_halo_bytes_per_particle",
+           "swift_cuda_get_touched", "swift_cuda_refresh_cell_hmax",
            "swift_cuda_host_plan", "swift_cuda_host_free"]
 
 _lib = None
@@ -116,6 +117,7 @@ def load_library():
             raise RuntimeError("libswiftcuda.so is missing: run __graft_entry__.build() (no CPU fallback exists)")
         lib = C.CDLL(LIB_PATH)
         lib.swift_cuda_last_error.restype = C.c_char_p
+        lib.swift_cuda_sizeof.restype = C.c_size_t
         lib.swift_cuda_halo_bytes_per_particle.restype = C.c_size_t
         lib.swift_cuda_halo_pack.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
         lib.swift_cuda_halo_unpack.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
@@ -327,6 +329,26 @@ class HydroBackend:
         self._check(self.lib.swift_cuda_get_tree(self.ctx, cells, tasks, order.ctypes.data_as(C.c_void_p)))
         return {"cells": cells, "ncells": nc.value, "tasks": tasks, "ntasks": nt.value, "cdim": tuple(cdim),
                 "order": order}
+
+    # ---- multi-GPU support ----
+    def touched_mask(self):
+        m = np.zeros(self.n, dtype=np.uint8)
+        self._check(self.lib.swift_cuda_get_touched(self.ctx, m.ctypes.data_as(C.c_void_p)))
+        return m.astype(bool)
+
+    def refresh_cell_hmax(self, after_ghost):
+        self._check(self.lib.swift_cuda_refresh_cell_hmax(self.ctx, int(after_ghost)))
+
+    def halo_bytes(self, phase):
+        return int(self.lib.swift_cuda_halo_bytes_per_particle(int(phase)))
+
+    def halo_pack(self, phase, index_ptr, count, buffer_ptr, stream=0):
+        self._check(self.lib.swift_cuda_halo_pack(self.ctx, int(phase), C.c_void_p(index_ptr), C.c_int64(count),
+                                                  C.c_void_p(buffer_ptr), C.c_void_p(stream)))
+
+    def halo_unpack(self, phase, index_ptr, count, buffer_ptr, stream=0):
+        self._check(self.lib.swift_cuda_halo_unpack(self.ctx, int(phase), C.c_void_p(index_ptr), C.c_int64(count),
+                                                    C.c_void_p(buffer_ptr), C.c_void_p(stream)))
 
     # ---- test hook ----
     def record_pairs(self, capacity):

@@ -79,6 +79,19 @@ static void free_device(swift_cuda_ctx *c) {
 extern "C" {
 
 int swift_cuda_abi_version(void) { return SWIFT_CUDA_ABI_VERSION; }
+size_t swift_cuda_sizeof(int which) {
+  switch (which) {
+    case 0: return sizeof(swift_cuda_params);
+    case 1: return sizeof(swift_cuda_cell);
+    case 2: return sizeof(swift_cuda_task);
+    case 3: return sizeof(swift_cuda_parts_in);
+    case 4: return sizeof(swift_cuda_parts_out);
+    case 5: return sizeof(swift_cuda_counters);
+    case 6: return sizeof(swift_cuda_timings);
+    case 7: return sizeof(swift_cuda_til);
+    default: return 0;
+  }
+}
 const char *swift_cuda_last_error(void) { return g_err.c_str(); }
 
 int swift_cuda_create(const swift_cuda_params *params, int device, swift_cuda_ctx **out) {
@@ -674,6 +687,43 @@ int swift_cuda_fetch_pairs(swift_cuda_ctx *c, int loop, long long *pairs, long l
     const long long m = std::min<long long>(capacity, (long long)cnt[loop]);
     if (m > 0) CK(cudaMemcpy(pairs, d.rec_pairs[loop], (size_t)m * 2 * sizeof(long long), cudaMemcpyDeviceToHost));
   }
+  return 0;
+}
+
+// Marks (caller order) every particle that lies in a cell some interaction of an ACTIVE leaf
+// reads: the set a multi-GPU rank has to keep fresh in its halo.
+int swift_cuda_get_touched(swift_cuda_ctx *c, uint8_t *mask) {
+  if (!c || !mask) return fail("get_touched: null argument");
+  const int64_t n = (int64_t)(c->tree.order.empty() ? c->n : (int64_t)c->tree.order.size());
+  std::vector<uint8_t> cell_mark(c->tree.cells.size(), 0);
+  for (const Item &it : c->wl.items) cell_mark[it.partner] = cell_mark[it.own] = 1;
+  for (const Item &it : c->wl.redo_items) cell_mark[it.partner] = cell_mark[it.own] = 1;
+  std::memset(mask, 0, (size_t)n);
+  for (size_t k = 0; k < cell_mark.size(); k++) {
+    if (!cell_mark[k]) continue;
+    const swift_cuda_cell &cell = c->tree.cells[k];
+    for (int j = 0; j < cell.count; j++) {
+      const int64_t slot = (int64_t)cell.first + j;
+      mask[c->tree.order.empty() ? slot : c->tree.order[slot]] = 1;
+    }
+  }
+  return 0;
+}
+
+// c->hydro.h_max of every cell from the device copy of h: after_ghost = 0 sets it (and h_max_old)
+// from scratch (after an xv halo refresh), 1 raises it to cover the current h (after a rho refresh).
+int swift_cuda_refresh_cell_hmax(swift_cuda_ctx *c, int after_ghost) {
+  NEED_BUILT(c);
+  Dev &d = c->dev;
+  if (d.ncells > 0) {
+    const int nb = (d.ncells * 32 + 255) / 256;
+    if (after_ghost)
+      k_cell_hmax<<<nb, 256, 0, c->stream>>>(d);
+    else
+      k_cell_hmax_init<<<nb, 256, 0, c->stream>>>(d, d.cell_hmax, const_cast<float *>(d.cell_hmax_old));
+  }
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(c->stream));
   return 0;
 }
 

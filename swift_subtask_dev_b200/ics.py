@@ -125,6 +125,43 @@ def two_body_impact(n, seed=5, r_target=6.4, r_impactor=3.0):
     return ic
 
 
+def top_grid(dim, h_max, max_top=12, stretch=1.1, gamma=1.825742):
+    """cdim of the top-level grid the reference (and the library) builds: src/space_regrid.c:120-127."""
+    dmax = max(dim)
+    cell_min = 0.99 * dmax / max_top
+    return tuple(int(np.floor(d / max(np.float32(h_max) * np.float32(gamma) * np.float32(stretch), cell_min)))
+                 for d in dim)
+
+
+def cell_block_random(cells, cdim, dim, per_cell, seed=42, h=None):
+    """Config 4 shape, generated cell by cell: `per_cell` uniform-random particles in each
+    top-level cell listed in `cells` (flat indices, x-major as the reference numbers them), each
+    cell seeded by its own index, so any process generates the same particles for the same cell.
+    ids are cell * 2^24 + k.  Returns the usual dict plus "cell" (top-level cell of each particle)."""
+    cells = np.asarray(cells, dtype=np.int64)
+    width = np.array([dim[k] / cdim[k] for k in range(3)])
+    n = len(cells) * per_cell
+    x = np.empty((n, 3), dtype=np.float64)
+    v = np.empty((n, 3), dtype=np.float32)
+    for q, c in enumerate(cells):
+        rng = np.random.default_rng([seed, int(c)])
+        i, j, k = c // (cdim[1] * cdim[2]), (c // cdim[2]) % cdim[1], c % cdim[2]
+        lo = np.array([i, j, k]) * width
+        u = rng.random((per_cell, 3))
+        xx = lo + u * width
+        # keep every particle strictly inside its cell after rounding
+        xx = np.minimum(xx, np.nextafter(lo + width, lo))
+        x[q * per_cell:(q + 1) * per_cell] = xx
+        v[q * per_cell:(q + 1) * per_cell] = rng.uniform(-0.05, 0.05, (per_cell, 3))
+    ntot_density = per_cell / float(np.prod(width))
+    h0 = np.float32(ETA / ntot_density ** (1.0 / 3.0)) if h is None else np.float32(h)
+    ic = {"x": x, "v": v, "mass": np.full(n, 1.0 / ntot_density, dtype=np.float32),
+          "h": np.full(n, h0, dtype=np.float32), "u": np.ones(n, dtype=np.float32),
+          "id": (np.repeat(cells, per_cell) << 24) + np.tile(np.arange(per_cell, dtype=np.int64), len(cells)),
+          "mat_id": None, "time_bin": None, "cell": np.repeat(cells, per_cell)}
+    return ic
+
+
 def permute(ic, order):
     """Reorders every per-particle array with `order` (cell order)."""
     out = {}

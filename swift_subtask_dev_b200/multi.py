@@ -1,0 +1,381 @@
+"""Multi-GPU driver of the SPH neighbour-loop path: spatial decomposition of the
+top-level cell grid with halo refresh between the phases.
+
+Role in the reference: partition_initial_partition (src/partition.c:1914-1950,
+grid of ranks over the top-level cells), engine_makeproxies
+(src/engine_proxy.c:41), and the send/recv tasks of
+engine_addtasks_send_hydro / _recv_hydro (src/engine_maketasks.c:141-324,
+567-): `xv` before the density loop, `rho` after the ghost.
+
+One process per GPU.  Every rank holds the particles of the top-level cells it
+owns (ACTIVE) plus the particles of the neighbouring ranks' adjacent top-level
+cells (its halo, INACTIVE on this rank: they are read by the loops, never
+updated; reference rule, src/scheduler.c:1275, tests/testHydroMPIrules.c).  Only
+the halo particles that an interaction of an owned leaf actually reads
+(swift_cuda_get_touched) are refreshed: packed on the owner's GPU
+(swift_cuda_halo_pack: 48 B `xv`, 24 B `rho` per particle instead of the
+reference's 128-byte struct part), moved with NCCL send/recv over NVLink, and
+unpacked on the receiver's GPU.  There is no collective on the data path.
+The results of the owned particles are bit-identical to a single-GPU run.
+"""
+import numpy as np
+
+from . import ics
+from .backend import HydroBackend, make_params
+
+
+# --------------------------------------------------------------------------- partition
+class Partition:
+    """gx x gy x gz blocks of top-level cells; nodeID = ix + gx (iy + gy iz) as
+    partition_initial_partition's INITPART_GRID."""
+
+    def __init__(self, cdim, grid, periodic=True):
+        self.cdim = tuple(int(c) for c in cdim)
+        self.grid = tuple(int(g) for g in grid)
+        self.periodic = periodic
+        for c, g in zip(self.cdim, self.grid):
+            if c % g != 0:
+                raise ValueError("grid %s does not divide the top-level cells %s" % (grid, cdim))
+        self.nranks = self.grid[0] * self.grid[1] * self.grid[2]
+        ijk = np.stack(np.meshgrid(*[np.arange(c) for c in self.cdim], indexing="ij"), axis=-1).reshape(-1, 3)
+        blk = [ijk[:, d] // (self.cdim[d] // self.grid[d]) for d in range(3)]
+        self.ijk = ijk
+        self.owner = (blk[0] + self.grid[0] * (blk[1] + self.grid[1] * blk[2])).astype(np.int32)
+
+    def flat(self, i, j, k):
+        return (i * self.cdim[1] + j) * self.cdim[2] + k
+
+    def owned_cells(self, rank):
+        return np.nonzero(self.owner == rank)[0]
+
+    def halo_cells(self, rank):
+        """Foreign top-level cells adjacent (26 neighbours, periodic wrap) to a cell of `rank`."""
+        own = self.owned_cells(rank)
+        out = set()
+        for c in own:
+            i, j, k = self.ijk[c]
+            for di in (-1, 0, 1):
+                for dj in (-1, 0, 1):
+                    for dk in (-1, 0, 1):
+                        n = [i + di, j + dj, k + dk]
+                        ok = True
+                        for d in range(3):
+                            if n[d] < 0 or n[d] >= self.cdim[d]:
+                                if self.periodic:
+                                    n[d] %= self.cdim[d]
+                                else:
+                                    ok = False
+                        if ok:
+                            f = self.flat(*n)
+                            if self.owner[f] != rank:
+                                out.add(int(f))
+        return np.array(sorted(out), dtype=np.int64)
+
+
+def grid_for(nranks):
+    return {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[nranks]
+
+
+def local_particles(part, rank, dim, per_cell, seed=42):
+    """Owned + halo particles of `rank`, cell by cell in the order of the global cell index (so
+    that the particles of a cell come in the same relative order on every rank and in a
+    single-GPU run).  time_bin 1 = owned (active), 2 = halo (inactive with max_active_bin = 1)."""
+    own = part.owned_cells(rank)
+    halo = part.halo_cells(rank)
+    cells = np.sort(np.concatenate([own, halo]))
+    ic = ics.cell_block_random(cells, part.cdim, dim, per_cell, seed=seed)
+    is_own = part.owner[ic["cell"]] == rank
+    ic["time_bin"] = np.where(is_own, 1, 2).astype(np.int8)
+    ic["owner"] = part.owner[ic["cell"]]
+    return ic
+
+
+# --------------------------------------------------------------------------- transports
+def plan_recv(ic, need):
+    """{peer: (ids, caller indices)} of the halo particles flagged in `need`, ids ascending."""
+    out = {}
+    for peer in np.unique(ic["owner"][need]):
+        sel = np.nonzero(need & (ic["owner"] == peer))[0]
+        sel = sel[np.argsort(ic["id"][sel])]
+        out[int(peer)] = (ic["id"][sel], sel)
+    return out
+
+
+def match_send(ic, is_own, wanted):
+    """{peer: caller indices} of my owned particles in the order of the ids each peer asked for."""
+    my_ids = ic["id"]
+    srt = np.argsort(my_ids)
+    out = {}
+    for peer, ids in wanted.items():
+        pos = srt[np.searchsorted(my_ids[srt], ids)]
+        if not (np.array_equal(my_ids[pos], ids) and is_own[pos].all()):
+            raise ValueError("rank %d asked for particles this rank does not own" % peer)
+        out[int(peer)] = pos
+    return out
+
+
+class NcclTransport:
+    """torch.distributed: NCCL send/recv for the halo buffers, a gloo group for the set-up lists."""
+
+    def __init__(self):
+        import torch.distributed as dist
+        self.dist = dist
+        self.rank = dist.get_rank()
+        self.nranks = dist.get_world_size()
+        self.setup_group = dist.new_group(backend="gloo") if dist.get_backend() != "gloo" else None
+
+    def all_to_all_objects(self, objs):
+        """objs: {peer: object}; returns {src: object} (one-off, host side)."""
+        out = [None] * self.nranks
+        send = [objs.get(p) for p in range(self.nranks)]
+        gathered = [None] * self.nranks
+        self.dist.all_gather_object(gathered, send, group=self.setup_group)
+        for src in range(self.nranks):
+            out[src] = gathered[src][self.rank]
+        return {src: o for src, o in enumerate(out) if o is not None and src != self.rank}
+
+    def exchange(self, send, recv):
+        """send / recv: {peer: cuda uint8 tensor}.  Grouped point-to-point, no collective."""
+        dist = self.dist
+        ops = []
+        for peer in sorted(set(send) | set(recv)):
+            if peer in recv and recv[peer].numel():
+                ops.append(dist.P2POp(dist.irecv, recv[peer], peer))
+            if peer in send and send[peer].numel():
+                ops.append(dist.P2POp(dist.isend, send[peer], peer))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+
+
+# --------------------------------------------------------------------------- one rank
+class RankState:
+    """The backend of one rank plus its halo plan."""
+
+    def __init__(self, rank, part, dim, per_cell, seed=42, device=0, params_kw=None):
+        import torch
+        self.torch = torch
+        self.rank = rank
+        self.part = part
+        self.device = device
+        self.ic = local_particles(part, rank, dim, per_cell, seed=seed)
+        kw = dict(dim=dim, periodic=part.periodic, max_active_bin=1)
+        kw.update(params_kw or {})
+        self.be = HydroBackend(make_params(**kw), device=device)
+        self.be.build(self.ic)
+        tree = self.be.tree()
+        assert tuple(tree["cdim"]) == tuple(part.cdim), (tree["cdim"], part.cdim)
+        order = tree["order"]
+        self.slot_of = np.empty(len(order), dtype=np.int64)   # caller index -> cell-order slot
+        self.slot_of[order] = np.arange(len(order))
+        touched = self.be.touched_mask()
+        self.is_own = self.ic["time_bin"] == 1
+        need = touched & ~self.is_own
+        # what I need from each peer: ids, sorted, and where they live on my device
+        self.recv_ids, self.recv_idx = {}, {}
+        for peer, (ids, sel) in plan_recv(self.ic, need).items():
+            self.recv_ids[peer] = ids
+            self.recv_idx[peer] = self._dev_index(self.slot_of[sel])
+        self.send_idx = {}
+        self.bufs = {}
+
+    def _dev_index(self, slots):
+        return self.torch.as_tensor(np.ascontiguousarray(slots, dtype=np.int32), device="cuda:%d" % self.device)
+
+    def set_send_lists(self, wanted):
+        """wanted: {peer: sorted ids the peer needs from me}."""
+        for peer, pos in match_send(self.ic, self.is_own, wanted).items():
+            self.send_idx[peer] = self._dev_index(self.slot_of[pos])
+
+    def buffers(self, phase):
+        if phase not in self.bufs:
+            nb = self.be.halo_bytes(phase)
+            dev = "cuda:%d" % self.device
+            send = {p: self.torch.empty(len(ix) * nb, dtype=self.torch.uint8, device=dev)
+                    for p, ix in self.send_idx.items()}
+            recv = {p: self.torch.empty(len(ix) * nb, dtype=self.torch.uint8, device=dev)
+                    for p, ix in self.recv_idx.items()}
+            self.bufs[phase] = (send, recv)
+        return self.bufs[phase]
+
+    def pack(self, phase):
+        send, _ = self.buffers(phase)
+        st = self.torch.cuda.current_stream(self.device).cuda_stream
+        for p, ix in self.send_idx.items():
+            self.be.halo_pack(phase, ix.data_ptr(), len(ix), send[p].data_ptr(), st)
+        return send
+
+    def unpack(self, phase):
+        _, recv = self.buffers(phase)
+        st = self.torch.cuda.current_stream(self.device).cuda_stream
+        for p, ix in self.recv_idx.items():
+            self.be.halo_unpack(phase, ix.data_ptr(), len(ix), recv[p].data_ptr(), st)
+        self.torch.cuda.current_stream(self.device).synchronize()
+        self.be.refresh_cell_hmax(after_ghost=(phase == 1))
+
+    def halo_bytes_per_step(self):
+        return sum(len(ix) for ix in self.send_idx.values()) * (self.be.halo_bytes(0) + self.be.halo_bytes(1))
+
+    def owned_results(self):
+        out = self.be.results()
+        sel = self.is_own
+        res = {k: v[sel] for k, v in out.items()}
+        res["id"] = self.ic["id"][sel]
+        return res
+
+
+def step_ranks_local(states):
+    """One density -> ghost -> force step of all ranks living in this process (LocalTransport)."""
+    def move(phase):
+        for s in states:
+            s.pack(phase)
+        for s in states:
+            s.torch.cuda.current_stream(s.device).synchronize()
+        for s in states:
+            _, recv = s.buffers(phase)
+            for peer, buf in recv.items():
+                buf.copy_(states[peer].buffers(phase)[0][s.rank])
+        for s in states:
+            s.unpack(phase)
+    for s in states:
+        s.be.restore_particles()
+    move(0)
+    for s in states:
+        s.be.runner_do_hydro_sort()
+        s.be.runner_do_density()
+        s.be.runner_do_ghost()
+    move(1)
+    for s in states:
+        s.be.runner_do_force()
+
+
+def setup_local(nranks, dim, cdim, per_cell, seed=42, periodic=True, params_kw=None):
+    part = Partition(cdim, grid_for(nranks), periodic)
+    states = [RankState(r, part, dim, per_cell, seed=seed, device=0, params_kw=params_kw) for r in range(nranks)]
+    for s in states:
+        s.set_send_lists({r.rank: r.recv_ids[s.rank] for r in states if s.rank in r.recv_ids})
+    return part, states
+
+
+# --------------------------------------------------------------------------- torchrun entry
+def step_rank_nccl(state, transport):
+    """One step of this process's rank: xv halo, sort + density + ghost, rho halo, force."""
+    be = state.be
+    be.restore_particles()
+    send = state.pack(0)
+    _, recv = state.buffers(0)
+    transport.exchange(send, recv)
+    state.unpack(0)
+    be.runner_do_hydro_sort()
+    be.runner_do_density()
+    be.runner_do_ghost()
+    send = state.pack(1)
+    _, recv = state.buffers(1)
+    transport.exchange(send, recv)
+    state.unpack(1)
+    be.runner_do_force()
+
+
+def bench_multi(args, cfg, metric, unit, sampler_cls=None):
+    """bench.py under torchrun: weak scaling, `side`^3 particles per GPU (BASELINE config 4 at 8 GPUs:
+    512^3 over 2 x 2 x 2)."""
+    import json
+    import os
+    import time
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ["RANK"])
+    world = int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    tr = NcclTransport()
+    grid = grid_for(world)
+    dim = tuple(float(g) for g in grid)
+    side = args.side
+    h0 = ics.ETA / side
+    cdim = ics.top_grid(dim, h0)
+    part = Partition(cdim, grid, periodic=True)
+    per_cell = int(round(side ** 3 * world / float(np.prod(cdim))))
+    t0 = time.perf_counter()
+    st = RankState(rank, part, dim, per_cell, seed=cfg["seed"], device=local)
+    wanted = tr.all_to_all_objects({p: ids for p, ids in st.recv_ids.items()})
+    st.set_send_lists(wanted)
+    build_s = time.perf_counter() - t0
+    n_own = int(st.is_own.sum())
+
+    def barrier():
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_rank_nccl(st, tr)
+    sampler = None
+    if rank == 0 and sampler_cls is not None:
+        sampler = sampler_cls(local)
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_rank_nccl(st, tr)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_dev = e0.elapsed_time(e1) / args.steps
+    ms_wall = 1e3 * (time.perf_counter() - t0) / args.steps
+    clocks = sampler.stop() if sampler is not None else None
+    cnt = st.be.counters()
+    inter = cnt["n_density"] + cnt["n_density_redo"] + cnt["n_force"]
+    # end to end: H2D of this rank's particle state from pinned host memory, the step, D2H of the results
+    ic_pin, keep = {}, []
+    for k, a in st.ic.items():
+        if isinstance(a, np.ndarray) and k not in ("cell", "owner"):
+            tt = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+            keep.append(tt)
+            ic_pin[k] = tt.numpy()
+        elif a is None:
+            ic_pin[k] = None
+    out_pin = st.be.alloc_results(pinned=True)
+    nloc = len(st.ic["h"])
+    e2e_s = []
+    for k in range(3):
+        barrier()
+        t1 = time.perf_counter()
+        st.be.update_particles(ic_pin)
+        step_rank_nccl(st, tr)
+        st.be.results(out=out_pin)
+        torch.cuda.synchronize()
+        if k > 0:
+            e2e_s.append(time.perf_counter() - t1)
+    e2e_ms = 1e3 * float(np.mean(e2e_s))
+    t = torch.tensor([max(ms_dev, ms_wall), float(inter), float(n_own), float(st.halo_bytes_per_step()), e2e_ms,
+                      float(nloc)], dtype=torch.float64, device="cuda")
+    tmax = t.clone()
+    dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    tsum = t.clone()
+    dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+    ms = float(tmax[0])
+    if rank == 0:
+        cfg = dict(cfg)
+        cfg["workload"] = ("periodic uniform-random box, %d particles per top-level cell, %s top-level cells over a "
+                           "%dx%dx%d GPU grid (%d^3 particles per GPU), density+ghost+force, Minimal SPH + ideal gas"
+                           % (per_cell, "x".join(map(str, cdim)), grid[0], grid[1], grid[2], side))
+        cfg["parallelism"] = "spatial %dx%dx%d, NCCL send/recv halo (xv 48 B, rho 24 B per particle)" % grid
+        nloc_tot = int(tsum[5])
+        line = {"metric": metric, "value": float(tsum[1]) / (ms * 1e-3), "unit": unit, "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+                "clocks": clocks,
+                "gpu_launches": (2 * st.be.params.max_smoothing_iterations + 5 + 4 * len(st.send_idx))
+                * args.steps * world,
+                "e2e": {"value": float(tsum[1]) / (float(tmax[4]) * 1e-3), "unit": unit,
+                        "h2d_bytes_per_step": nloc_tot * 49, "d2h_bytes_per_step": nloc_tot * 49},
+                "detail": {"n_particles_owned_total": int(tsum[2]), "interactions_per_step": int(tsum[1]),
+                           "halo_bytes_per_step_total": int(tsum[3]), "build_s": build_s,
+                           "ms_device_events_rank0": ms_dev, "ms_wall_rank0": ms_wall}}
+        print(json.dumps(line))
+    dist.barrier()
+    dist.destroy_process_group()
+    return 0

@@ -1,0 +1,94 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads, exports every
+symbol include/swift_cuda.h declares, its structs match the ctypes mirror, it
+refuses to compute without a GPU, and its host-side tree / task builder makes
+the same decisions as the oracle's restatement of space_split /
+scheduler_splittask_hydro."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from swift_subtask_dev_b200 import backend as be
+from swift_subtask_dev_b200 import ics, make_params
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "swift_cuda.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(swift_cuda_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = be.load_library()
+    syms = _declared_symbols()
+    assert len(syms) >= 25
+    for name in syms:
+        assert hasattr(lib, name), "libswiftcuda.so does not export %s" % name
+    assert sorted(be.EXPORTS) == syms, "backend.EXPORTS and include/swift_cuda.h disagree"
+    assert lib.swift_cuda_abi_version() == 1
+
+
+def test_struct_layouts_match_ctypes_mirror():
+    lib = be.load_library()
+    for which, cls in enumerate([be.Params, be.Cell, be.Task, be.PartsIn, be.PartsOut, be.Counters, be.Timings,
+                                 be.Til]):
+        assert lib.swift_cuda_sizeof(which) == C.sizeof(cls), cls.__name__
+    # the oracle's tree structs are layout-compatible (tests memmove between them)
+    assert C.sizeof(ol.Cell) == C.sizeof(be.Cell) and C.sizeof(ol.Task) == C.sizeof(be.Task)
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(be.SwiftCudaError) as e:
+        be.HydroBackend(make_params())
+    assert "no CUDA device" in str(e.value)
+
+
+CASES = [
+    ("uniform64k", lambda: ics.uniform_random(40 ** 3, seed=3), dict(periodic=True)),
+    ("uniform_split", lambda: ics.uniform_random(96 ** 3, seed=5), dict(periodic=True)),
+    ("open_box", lambda: ics.uniform_random(30 ** 3, seed=7), dict(periodic=False)),
+    ("clustered", lambda: ics.clustered(60000, nclumps=16, seed=3), dict(periodic=True)),
+]
+
+
+@pytest.mark.parametrize("name,make,kw", CASES, ids=[c[0] for c in CASES])
+def test_host_plan_matches_oracle_tree_and_tasks(name, make, kw):
+    ic = make()
+    plan = be.host_plan(make_params(**kw), ic)
+    order, cells, cdim, tasks, nt = ol.build_tree_and_tasks(ol.make_params(**kw), ic["x"], ic["h"])
+    assert plan["cdim"] == tuple(cdim)
+    assert plan["ncells"] == len(cells) and plan["ntasks"] == nt
+    # the two builders may number the progeny differently: compare by (first, count, depth)
+    def key(c):
+        return (c.first, c.count, c.depth)
+
+    def canon(cs, n):
+        return sorted((key(cs[k]), tuple(cs[k].loc), tuple(cs[k].width), cs[k].split,
+                       key(cs[cs[k].parent]) if cs[k].parent >= 0 else None,
+                       tuple(key(cs[p]) if p >= 0 else None for p in cs[k].progeny)) for k in range(n))
+    assert canon(plan["cells"], plan["ncells"]) == canon(cells, len(cells)), "cells differ"
+
+    def canon_tasks(ts, n, cs):
+        return sorted((ts[k].type, key(cs[ts[k].ci]), key(cs[ts[k].cj]) if ts[k].cj >= 0 else None)
+                      for k in range(n))
+    assert canon_tasks(plan["tasks"], nt, plan["cells"]) == canon_tasks(tasks, nt, cells), "task lists differ"
+    # same particles in every leaf
+    for k in range(0, len(cells), max(1, len(cells) // 200)):
+        c = cells[k]
+        assert set(plan["order"][c.first:c.first + c.count]) == set(order[c.first:c.first + c.count])
+    assert plan["n_interactions"] > 0 and plan["n_items"] >= plan["n_interactions"]
+
+
+def test_host_plan_rejects_too_large_h_in_periodic_box():
+    ic = ics.uniform_random(1000, seed=1)
+    ic["h"][:] = 0.3  # 1.1 * gamma * h > box / 3
+    with pytest.raises(be.SwiftCudaError):
+        be.host_plan(make_params(periodic=True), ic)
