@@ -74,6 +74,10 @@ struct Dev {
   // tree
   const CellDev *cells;
   float *cell_hmax;        // current c->hydro.h_max
+  const int32_t *cell_parent;  // -1 for a top-level cell
+  const uint8_t *cell_split;   // 0: leaf
+  float *cell_box;         // [ncells][6] bounding box of the cell's particles relative to loc (lo xyz, hi xyz)
+  uint32_t *cell_box_u;    // the same while it is being reduced (order-preserving integer images)
   const float *cell_hmax_old;  // value at build (h_max_old)
   const int32_t *leaves;       // [n_leaves] cell index
   const int32_t *item_begin;   // [n_leaves+1]
@@ -87,6 +91,10 @@ struct Dev {
   const int64_t *sort_lookup;  // [ncells*13]
   float *sort_d;
   int32_t *sort_i;
+  // persistent kernels: per-warp FIFO of deferred hits [n_qwarps][kQD][32], unit counters
+  // [0] first density pass, [1 + sweep] redo sweeps, [1 + max_iter] force
+  float4 *gq;
+  int *work_ctr;
   // counters: [0] density, [1] redo, [2] force
   unsigned long long *hits;
   int *redo_count;         // [max_iter+1]

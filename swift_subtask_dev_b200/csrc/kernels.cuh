@@ -19,7 +19,6 @@ __constant__ Consts kc;
 
 constexpr int kWarps = 4;        // warps per CTA of the neighbour-loop kernels (each warp works alone)
 constexpr int kBlock = 32 * kWarps;
-constexpr int kQ = 16;           // slots per lane of the deferred-hit queue (power of two)
 constexpr int kNumTimeBins = 56;
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int kDpFlag = 0x40000000;  // queue entry: dx must be recomputed from the f64 positions
@@ -268,26 +267,38 @@ __global__ void k_init_step(Dev d) {
 // ---------------------------------------------------------------------------
 // Neighbour-loop machinery shared by K3 (density), K5 (ghost redo) and K6 (force)
 //
-// Work decomposition.  A warp owns up to 32 particles of ONE leaf cell, one per
-// lane, and walks that leaf's list of direct cell interactions in the order
-// the reference's single-threaded runner executes them.  For every interaction
-// the partner cell's particles are staged 32 at a time into a warp-private
-// shared-memory tile (already sorted along the pair axis, positions already in
-// the pair's frame), every lane tests every staged candidate against its own
-// sorted-axis cut and r2 < h^2 gamma^2 (FP32, one broadcast LDS.128 per
-// candidate), and pushes the hits into a per-lane FIFO in shared memory.  The
-// interaction body (runner_iact_nonsym_*) runs only when a lane's FIFO is about
-// to overflow, so that most lanes have a hit to work on: the divergence of
-// "one lane hits, 31 wait" is gone.  Hits are consumed in FIFO order into
-// register accumulators, so every particle sums its neighbours in exactly the
-// order the reference does: the results are bit-identical to the oracle.
+// Work decomposition.  The kernels are PERSISTENT: the grid is one resident
+// wave of CTAs and every warp draws units from a device-side counter.  A unit
+// is up to 32 particles of ONE leaf cell, one per lane (spatial neighbours:
+// Morton order inside the leaf).  The warp walks that leaf's list of direct
+// cell interactions in the order the reference's single-threaded runner
+// executes them.  For every interaction:
+//   1. skip it when the bounding box of the partner cell's particles cannot
+//      reach the box of the unit's particles (each grown by its search radius);
+//   2. stage the partner's particles 32 at a time in sorted-axis order, one per
+//      lane, already converted to the pair's f32 frame, and keep only those
+//      inside the unit's box and inside the union of the lanes' sort-key
+//      windows; survivors are compacted, IN ORDER, into a warp-private
+//      shared-memory ring;
+//   3. every lane tests every surviving candidate against its own sorted-axis
+//      cut and r2 < h^2 gamma^2 (FP32, one broadcast LDS.128 per candidate) and
+//      appends its hits to a per-lane FIFO in global memory (L2 resident, kQD
+//      entries deep: deep enough for ALL the hits of a particle in the
+//      benchmark configurations).
+// The interaction body (runner_iact_nonsym_*) runs when the walk is over (or
+// when a FIFO is about to overflow), with every lane busy, consuming the hits
+// in FIFO order into register accumulators: every particle sums its
+// neighbours in exactly the order the reference does, so the results are
+// bit-identical to the oracle.
 // ---------------------------------------------------------------------------
+constexpr int kQD = 128;    // deferred hits per lane
+constexpr int kTile = 64;   // ring of staged candidates per warp (two 32-candidate tiles)
+constexpr int kSide = 4;    // force: loop-2 hits of one pair kept aside per lane
+
 struct WarpTile {
-  float4 pos[32];     // frame-relative position of the candidate, sort key in w
-  float4 aux[32];     // force only: per-candidate thresholds (see k_force)
-  int idx[32];        // particle index of the candidate
+  float4 pos[kTile];  // frame-relative position of the candidate, sort key in w
+  int idx[kTile];     // particle index of the candidate
   int sel[64];        // redo: compaction of the flagged particles of a leaf
-  float4 q[kQ][32];   // deferred hits: dx, dy, dz, candidate index (or kDpFlag form)
 };
 
 __device__ __forceinline__ float next_down(float f) {
@@ -332,19 +343,24 @@ __device__ __forceinline__ float thr_gt_shift(double rs, double y) {
   return t;
 }
 
-__device__ __forceinline__ float warp_max(float v) {
-  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(kFull, v, o));
-  return v;
-}
+// warp-wide min / max in one instruction (redux.sync f32: sm_100a)
 __device__ __forceinline__ float warp_min(float v) {
-  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(kFull, v, o));
-  return v;
+  float r;
+  asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+}
+__device__ __forceinline__ float warp_max(float v) {
+  float r;
+  asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
 }
 
 // periodic shift of an item along axis k, in box lengths {-1, 0, 1}
+__device__ __forceinline__ int item_shift_i(int code, int k) {
+  return (k == 0 ? code % 3 : (k == 1 ? (code / 3) % 3 : code / 9)) - 1;
+}
 __device__ __forceinline__ double item_shift(const Dev &d, int code, int k) {
-  const int s = (k == 0 ? code % 3 : (k == 1 ? (code / 3) % 3 : code / 9)) - 1;
-  return (double)s * d.dim[k];
+  return (double)item_shift_i(code, k) * d.dim[k];
 }
 // rshift = sum_k shift[k] * runner_shift[sid][k], accumulated from 0 in k order as the reference does
 __device__ __forceinline__ double item_rshift(const double sh[3], int sid) {
@@ -360,13 +376,42 @@ __device__ __forceinline__ float cull_thr(float hg2, float e) {
   return hg2 * 1.000002f + 3.5f * sqrtf(hg2) * e + 3.f * e * e;
 }
 
+// Box of a unit's particles (each grown by its search radius), given in the frame of the
+// leaf (ulo/uhi, f32) -> the same box in the frame the candidates of an item are staged in.
+// ol = (leaf origin) - (what is subtracted from a lane's position) - (lane frame origin).
+// The margin covers every f32 rounding between the two frames (8 ulp of the magnitudes).
+struct StageBox {
+  float lo[3], hi[3];
+};
+__device__ __forceinline__ void stage_box(const float ulo[3], const float uhi[3], const double ol[3], float slack,
+                                          StageBox &b) {
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    const double m = 1e-6 * (fabs(ol[k]) + (double)fabsf(ulo[k]) + (double)fabsf(uhi[k])) + (double)slack;
+    b.lo[k] = __double2float_rd((double)ulo[k] + ol[k] - m);
+    b.hi[k] = __double2float_ru((double)uhi[k] + ol[k] + m);
+  }
+}
+// can a particle of cell cb (bounding box of its particles relative to its loc: bb[0..5]) lie in b?
+// og = cb.loc - (frame origin of the staged candidates)
+__device__ __forceinline__ bool box_reaches_cell(const StageBox &b, const float *__restrict__ bb, const double og[3]) {
+  bool r = true;
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    const double lo = (double)bb[k] + og[k], hi = (double)bb[3 + k] + og[k];
+    const double m = 1e-6 * (fabs(og[k]) + fabs(lo) + fabs(hi));
+    r = r && ((double)b.hi[k] >= lo - m) && ((double)b.lo[k] <= hi + m);
+  }
+  return r;
+}
+
 // ---------------------------------------------------------------------------
 // K3 / K5: density.
 // MODE 0: first pass, DOSELF1 / DOPAIR1 arithmetic, every active particle;
-//         one warp per 32-particle unit of a leaf.
+//         a unit is 32 particles of a leaf.
 // MODE 1: ghost redo sweep, DOSELF_SUBSET / DOPAIR_SUBSET arithmetic, only the
-//         particles the ghost flagged (gstate == 2); one warp per leaf, which
-//         first compacts the flagged particles into full groups of 32.
+//         particles the ghost flagged (gstate == 2); a unit is a leaf, whose
+//         flagged particles the warp first compacts into full groups of 32.
 // ---------------------------------------------------------------------------
 template <int MODE>
 __global__ void __launch_bounds__(kBlock) k_density(Dev d, int sweep) {
@@ -374,212 +419,292 @@ __global__ void __launch_bounds__(kBlock) k_density(Dev d, int sweep) {
   __shared__ WarpTile tiles[kWarps];
   WarpTile &ws = tiles[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
-  const int wid = blockIdx.x * kWarps + (threadIdx.x >> 5);
-  if (wid >= (MODE == 0 ? d.n_units : d.n_leaves)) return;
-  const int slot = MODE == 0 ? d.unit_leaf[wid] : wid;
-  const CellDev cL = d.cells[d.leaves[slot]];
+  const unsigned lt_mask = (1u << lane) - 1u;
+  float4 *const gq = d.gq + (size_t)(blockIdx.x * kWarps + (threadIdx.x >> 5)) * (kQD * 32) + lane;
+  const int total = MODE == 0 ? d.n_units : d.n_leaves;
+  int *const work = d.work_ctr + (MODE == 0 ? 0 : 1 + sweep);
   const Item *__restrict__ items = MODE == 0 ? d.items : d.redo_items;
-  const int ib = (MODE == 0 ? d.item_begin : d.redo_begin)[slot];
-  const int ie = (MODE == 0 ? d.item_begin : d.redo_begin)[slot + 1];
   const bool rec = d.rec_capacity > 0;
+  const float qnan = __int_as_float(0x7fc00000);
   unsigned long long nhits = 0;
-  int scan = 0, nsel = 0;
-  bool first = true;
 
   while (true) {
-    // ---- which particle does this lane own in this round?
-    int p = -1;
-    if (MODE == 0) {
-      if (!first) break;
-      first = false;
-      const int q = d.lane_part[(int64_t)wid * 32 + lane];
-      if (q >= 0 && d.time_bin[q] <= kc.max_active_bin) p = q;
-    } else {
-      // the leaf's particles in lane (Morton) order
-      const int64_t lp0 = (int64_t)d.unit_begin[slot] * 32;
-      const int nlp = (d.unit_begin[slot + 1] - d.unit_begin[slot]) * 32;
-      while (nsel < 32 && scan < nlp) {
-        const int q = d.lane_part[lp0 + scan + lane];
-        const bool f = q >= 0 && d.gstate[q] == 2;
-        const unsigned b = __ballot_sync(kFull, f);
-        if (f) ws.sel[nsel + __popc(b & ((1u << lane) - 1u))] = q;
-        nsel += __popc(b);
-        scan += 32;
-      }
-      __syncwarp();
-      if (nsel == 0) break;
-      const int take = min(nsel, 32);
-      if (lane < take) p = ws.sel[lane];
-      const int carry = (lane + 32 < nsel) ? ws.sel[lane + 32] : 0;
-      __syncwarp();
-      ws.sel[lane] = carry;
-      nsel -= take;
-      __syncwarp();
-    }
-    if (!__any_sync(kFull, p >= 0)) continue;
+    int wid = 0;
+    if (lane == 0) wid = atomicAdd(work, 1);
+    wid = __shfl_sync(kFull, wid, 0);
+    if (wid >= total) break;
+    const int slot = MODE == 0 ? d.unit_leaf[wid] : wid;
+    const CellDev cL = d.cells[d.leaves[slot]];
+    const int ib = (MODE == 0 ? d.item_begin : d.redo_begin)[slot];
+    const int ie = (MODE == 0 ? d.item_begin : d.redo_begin)[slot + 1];
+    int scan = 0, nsel = 0;
+    bool first = true;
 
-    const bool mine = p >= 0;
-    const int pp = mine ? p : cL.first;
-    const double xi = d.x[pp], yi = d.y[pp], zi = d.z[pp];
-    const float hi = d.h[pp];
-    const float hig2 = sq_gamma2(hi);
-    const float hi_inv = 1.f / hi;
-    const float hig = __fmul_rn(hi, kc.gamma);
-    const float4 vmi = d.vm[pp];
-    const long long idi = rec ? d.id[pp] : 0;
-    DensAcc acc;
-    acc.zero();
-    int qhead = 0, qcnt = 0;
-
-    // one deferred hit -> runner_iact_nonsym_density
-    auto consume = [&](const float4 e) {
-      const int w = __float_as_int(e.w);
-      const int j = w & (kDpFlag - 1);
-      float dx, dy, dz;
-      if (w & kDpFlag) {
-        const int code = __float_as_int(e.x);
-        dx = dsub_f(__dsub_rn(xi, item_shift(d, code, 0)), d.x[j]);
-        dy = dsub_f(__dsub_rn(yi, item_shift(d, code, 1)), d.y[j]);
-        dz = dsub_f(__dsub_rn(zi, item_shift(d, code, 2)), d.z[j]);
+    while (true) {
+      // ---- which particle does this lane own in this round?
+      int p = -1;
+      if (MODE == 0) {
+        if (!first) break;
+        first = false;
+        const int q = d.lane_part[(int64_t)wid * 32 + lane];
+        if (q >= 0 && d.time_bin[q] <= kc.max_active_bin) p = q;
       } else {
-        dx = e.x; dy = e.y; dz = e.z;
-      }
-      const float r2 = dist2(dx, dy, dz);
-      if (r2 < hig2) {
-        iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, d.vm[j]);
-        nhits++;
-        if (rec) record_pair(d, MODE, idi, d.id[j]);
-      }
-    };
-    auto drain_round = [&]() {
-      if (qcnt > 0) {
-        const float4 e = ws.q[qhead][lane];
-        qhead = (qhead + 1) & (kQ - 1);
-        qcnt--;
-        consume(e);
-      }
-    };
-
-    for (int it = ib; it < ie; it++) {
-      const Item item = items[it];
-      const CellDev cA = d.cells[item.own];
-      const CellDev cB = d.cells[item.partner];
-      const int kind = item.kind;
-      const int sid = item.sid;
-      const bool sorted = !(kind == kSelf || kind == kSubSelf);
-      const bool desc = (kind == kPairRight || kind == kSubPairFlip);
-      const bool dp = (kind == kSelf || kind == kSubPair || kind == kSubPairFlip);
-      const int64_t segB = sorted ? d.sort_lookup[(int64_t)item.partner * 13 + sid] : 0;
-      double sh[3] = {0.0, 0.0, 0.0};
-      if (sorted) {
-        sh[0] = item_shift(d, item.shift, 0);
-        sh[1] = item_shift(d, item.shift, 1);
-        sh[2] = item_shift(d, item.shift, 2);
-      }
-      // frame origin of the staged candidates (fo) and of this lane's particle (fl)
-      double fo[3], fl[3];
-      double px = xi, py = yi, pz = zi;
-      float lo = INFINITY, hi_cut = -INFINITY;  // lane's window on the candidates' sort keys (empty)
-      float thr = hig2;
-      if (kind == kSelf || kind == kSubSelf) {
-        for (int k = 0; k < 3; k++) fo[k] = fl[k] = cA.loc[k];
-        if (mine) { lo = -INFINITY; hi_cut = INFINITY; }
-        if (kind == kSelf) thr = cull_thr(hig2, 4e-7f * cA.width);
-      } else if (kind == kPairLeft) {
-        // this leaf's particles are "pi" of DOPAIR1 loop 1 (:1122-1216): frame cj.loc + shift
-        for (int k = 0; k < 3; k++) { fo[k] = cB.loc[k]; fl[k] = __dadd_rn(cB.loc[k], sh[k]); }
-        if (mine) {
-          const double rshift = item_rshift(sh, sid);
-          const float d_me = sort_key(xi, yi, zi, sid);
-          const double dj_min = (double)d.sort_d[segB];
-          const double hi_max = __dsub_rn((double)__fmul_rn(d.cell_hmax[item.own], kc.gamma), rshift);
-          const double di = __dsub_rn((double)__fadd_rn(d_me, hig), rshift);
-          if ((__dadd_rn((double)d_me, hi_max) > dj_min) && !(di < dj_min)) { lo = -INFINITY; hi_cut = thr_lt(di); }
-        }
-      } else if (kind == kPairRight) {
-        // this leaf's particles are "pj" of DOPAIR1 loop 2 (:1222-1316): frame cj.loc (their own cell)
-        for (int k = 0; k < 3; k++) { fo[k] = __dadd_rn(cA.loc[k], sh[k]); fl[k] = cA.loc[k]; }
-        if (mine) {
-          const double rshift = item_rshift(sh, sid);
-          const float d_me = sort_key(xi, yi, zi, sid);
-          const double di_max = __dsub_rn((double)d.sort_d[segB + cB.count - 1], rshift);
-          const double hj_max = (double)__fmul_rn(d.cell_hmax[item.own], kc.gamma);
-          const double dj = __dadd_rn((double)__fsub_rn(d_me, hig), rshift);
-          if ((__dsub_rn((double)d_me, hj_max) < di_max) && !(__dsub_rn(dj, rshift) > di_max)) {
-            lo = thr_gt(dj);
-            hi_cut = INFINITY;
-          }
-        }
-      } else {
-        // DOPAIR_SUBSET (:745-770, 794-838): pix = x - shift in f64, dx = (float)(pix - pj.x)
-        px = __dsub_rn(xi, sh[0]); py = __dsub_rn(yi, sh[1]); pz = __dsub_rn(zi, sh[2]);
-        for (int k = 0; k < 3; k++) fo[k] = fl[k] = cB.loc[k];
-        thr = cull_thr(hig2, 8e-7f * fmaxf(cA.width, cB.width));
-        if (mine) {
-          const float hg = (kind == kSubPair) ? __fadd_rn(hig, 0.f) : __fsub_rn(-hig, 0.f);
-          const double cut = __dadd_rn(__dadd_rn(__dadd_rn((double)hg, __dmul_rn(px, kc.axis[sid][0])),
-                                                 __dmul_rn(py, kc.axis[sid][1])),
-                                       __dmul_rn(pz, kc.axis[sid][2]));
-          if (kind == kSubPair) { lo = -INFINITY; hi_cut = thr_lt(cut); }
-          else { lo = thr_gt(cut); hi_cut = INFINITY; }
-        }
-      }
-      const float pfx = dsub_f(px, fl[0]), pfy = dsub_f(py, fl[1]), pfz = dsub_f(pz, fl[2]);
-      const float wlim = desc ? warp_min(lo) : warp_max(hi_cut);
-      if (desc ? (wlim == INFINITY) : (wlim == -INFINITY)) continue;  // no lane takes part
-      const int shiftbits = item.shift;
-
-      for (int base = 0; base < cB.count; base += 32) {
-        const int nt = min(32, cB.count - base);
-        __syncwarp();
-        {
-          const float qnan = __int_as_float(0x7fc00000);
-          float4 c = make_float4(qnan, qnan, qnan, qnan);  // padding: never in a window, never a hit
-          int j = 0;
-          if (lane < nt) {
-            float dk = 0.f;
-            if (sorted) {
-              const int e = desc ? (cB.count - 1 - base - lane) : (base + lane);
-              j = cB.first + d.sort_i[segB + e];
-              dk = d.sort_d[segB + e];
-            } else {
-              j = cB.first + base + lane;
-            }
-            c = make_float4(dsub_f(d.x[j], fo[0]), dsub_f(d.y[j], fo[1]), dsub_f(d.z[j], fo[2]), dk);
-          }
-          ws.pos[lane] = c;
-          ws.idx[lane] = j;
+        // the leaf's particles in lane (Morton) order
+        const int64_t lp0 = (int64_t)d.unit_begin[slot] * 32;
+        const int nlp = (d.unit_begin[slot + 1] - d.unit_begin[slot]) * 32;
+        while (nsel < 32 && scan < nlp) {
+          const int q = d.lane_part[lp0 + scan + lane];
+          const bool f = q >= 0 && d.gstate[q] == 2;
+          const unsigned b = __ballot_sync(kFull, f);
+          if (f) ws.sel[nsel + __popc(b & lt_mask)] = q;
+          nsel += __popc(b);
+          scan += 32;
         }
         __syncwarp();
-        if (sorted) {
-          const float first_key = ws.pos[0].w;
-          if (desc ? !(first_key >= wlim) : !(first_key <= wlim)) break;
-        }
-        for (int k0 = 0; k0 < nt; k0 += 4) {
-          while (__any_sync(kFull, qcnt > kQ - 4)) drain_round();
+        if (nsel == 0) break;
+        const int take = min(nsel, 32);
+        if (lane < take) p = ws.sel[lane];
+        const int carry = (lane + 32 < nsel) ? ws.sel[lane + 32] : 0;
+        __syncwarp();
+        ws.sel[lane] = carry;
+        nsel -= take;
+        __syncwarp();
+      }
+      if (!__any_sync(kFull, p >= 0)) continue;
+
+      const bool mine = p >= 0;
+      const int pp = mine ? p : cL.first;
+      const double xi = d.x[pp], yi = d.y[pp], zi = d.z[pp];
+      const float hi = d.h[pp];
+      const float hig2 = sq_gamma2(hi);
+      const float hi_inv = 1.f / hi;
+      const float hig = __fmul_rn(hi, kc.gamma);
+      const float4 vmi = d.vm[pp];
+      const long long idi = rec ? d.id[pp] : 0;
+      DensAcc acc;
+      acc.zero();
+      int qcnt = 0;
+
+      // box of the unit's particles, each grown by its search radius, in the leaf's frame
+      float ulo[3], uhi[3];
+      {
+        const float l[3] = {dsub_f(xi, cL.loc[0]), dsub_f(yi, cL.loc[1]), dsub_f(zi, cL.loc[2])};
+        const float ru = hig * 1.0001f;
 #pragma unroll
-          for (int u = 0; u < 4; u++) {
-            const int k = k0 + u;
-            const float4 c = ws.pos[k];
-            const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
-            const float r2 = dist2(dx, dy, dz);
-            if (c.w >= lo && c.w <= hi_cut && r2 < thr) {
-              const int j = ws.idx[k];
-              if (j != pp) {
-                ws.q[(qhead + qcnt) & (kQ - 1)][lane] =
-                    dp ? make_float4(__int_as_float(shiftbits), 0.f, 0.f, __int_as_float(j | kDpFlag))
-                       : make_float4(dx, dy, dz, __int_as_float(j));
-                qcnt++;
+        for (int k = 0; k < 3; k++) {
+          ulo[k] = warp_min(mine ? l[k] - ru : INFINITY);
+          uhi[k] = warp_max(mine ? l[k] + ru : -INFINITY);
+        }
+      }
+
+      // one deferred hit -> runner_iact_nonsym_density
+      auto consume = [&](const float4 e) {
+        const int w = __float_as_int(e.w);
+        const int j = w & (kDpFlag - 1);
+        float dx, dy, dz;
+        if (w & kDpFlag) {
+          // e.xyz: periodic shift of the item in box lengths (-1, 0, 1)
+          dx = dsub_f(__dsub_rn(xi, __dmul_rn((double)e.x, d.dim[0])), d.x[j]);
+          dy = dsub_f(__dsub_rn(yi, __dmul_rn((double)e.y, d.dim[1])), d.y[j]);
+          dz = dsub_f(__dsub_rn(zi, __dmul_rn((double)e.z, d.dim[2])), d.z[j]);
+        } else {
+          dx = e.x; dy = e.y; dz = e.z;
+        }
+        const float r2 = dist2(dx, dy, dz);
+        if (r2 < hig2) {
+          iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, d.vm[j]);
+          nhits++;
+          if (rec) record_pair(d, MODE, idi, d.id[j]);
+        }
+      };
+      auto drain_all = [&]() {
+        const int m = __reduce_max_sync(kFull, qcnt);
+        float4 e = qcnt > 0 ? gq[0] : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < m; r++) {
+          const float4 en = (r + 1 < qcnt) ? gq[(r + 1) * 32] : make_float4(0.f, 0.f, 0.f, 0.f);
+          if (r < qcnt) consume(e);
+          e = en;
+        }
+        qcnt = 0;
+      };
+
+      for (int it = ib; it < ie; it++) {
+        const Item item = items[it];
+        const CellDev cA = d.cells[item.own];
+        const CellDev cB = d.cells[item.partner];
+        const int kind = item.kind;
+        const int sid = item.sid;
+        const bool sorted = !(kind == kSelf || kind == kSubSelf);
+        const bool desc = (kind == kPairRight || kind == kSubPairFlip);
+        const bool dp = (kind == kSelf || kind == kSubPair || kind == kSubPairFlip);
+        double sh[3] = {0.0, 0.0, 0.0};
+        float shf[3] = {0.f, 0.f, 0.f};
+        if (sorted) {
+#pragma unroll
+          for (int k = 0; k < 3; k++) {
+            const int s = item_shift_i(item.shift, k);
+            shf[k] = (float)s;
+            sh[k] = (double)s * d.dim[k];
+          }
+        }
+        // frame origin of the staged candidates (fo) and of this lane's particle (fl);
+        // sub: what DOPAIR_SUBSET takes off the lane's position first
+        double fo[3], fl[3], sub[3] = {0.0, 0.0, 0.0};
+        float slack = 0.f;
+        if (kind == kSelf || kind == kSubSelf) {
+#pragma unroll
+          for (int k = 0; k < 3; k++) fo[k] = fl[k] = cA.loc[k];
+          if (kind == kSelf) slack = 1e-6f * cA.width;
+        } else if (kind == kPairLeft) {
+#pragma unroll
+          for (int k = 0; k < 3; k++) { fo[k] = cB.loc[k]; fl[k] = __dadd_rn(cB.loc[k], sh[k]); }
+        } else if (kind == kPairRight) {
+#pragma unroll
+          for (int k = 0; k < 3; k++) { fo[k] = __dadd_rn(cA.loc[k], sh[k]); fl[k] = cA.loc[k]; }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 3; k++) { fo[k] = fl[k] = cB.loc[k]; sub[k] = sh[k]; }
+          slack = 2e-6f * fmaxf(cA.width, cB.width);
+        }
+        StageBox sb;
+        {
+          double ol[3], og[3];
+#pragma unroll
+          for (int k = 0; k < 3; k++) {
+            ol[k] = cL.loc[k] - sub[k] - fl[k];
+            og[k] = cB.loc[k] - fo[k];
+          }
+          stage_box(ulo, uhi, ol, slack, sb);
+          if (!box_reaches_cell(sb, d.cell_box + (int64_t)item.partner * 6, og)) continue;
+        }
+
+        const int64_t segB = sorted ? d.sort_lookup[(int64_t)item.partner * 13 + sid] : 0;
+        double px = xi, py = yi, pz = zi;
+        float lo = INFINITY, hi_cut = -INFINITY;  // lane's window on the candidates' sort keys (empty)
+        float thr = hig2;
+        if (kind == kSelf || kind == kSubSelf) {
+          if (mine) { lo = -INFINITY; hi_cut = INFINITY; }
+          if (kind == kSelf) thr = cull_thr(hig2, 4e-7f * cA.width);
+        } else if (kind == kPairLeft) {
+          // this leaf's particles are "pi" of DOPAIR1 loop 1 (:1122-1216): frame cj.loc + shift
+          if (mine) {
+            const double rshift = item_rshift(sh, sid);
+            const float d_me = sort_key(xi, yi, zi, sid);
+            const double dj_min = (double)d.sort_d[segB];
+            const double hi_max = __dsub_rn((double)__fmul_rn(d.cell_hmax[item.own], kc.gamma), rshift);
+            const double di = __dsub_rn((double)__fadd_rn(d_me, hig), rshift);
+            if ((__dadd_rn((double)d_me, hi_max) > dj_min) && !(di < dj_min)) { lo = -INFINITY; hi_cut = thr_lt(di); }
+          }
+        } else if (kind == kPairRight) {
+          // this leaf's particles are "pj" of DOPAIR1 loop 2 (:1222-1316): frame cj.loc (their own cell)
+          if (mine) {
+            const double rshift = item_rshift(sh, sid);
+            const float d_me = sort_key(xi, yi, zi, sid);
+            const double di_max = __dsub_rn((double)d.sort_d[segB + cB.count - 1], rshift);
+            const double hj_max = (double)__fmul_rn(d.cell_hmax[item.own], kc.gamma);
+            const double dj = __dadd_rn((double)__fsub_rn(d_me, hig), rshift);
+            if ((__dsub_rn((double)d_me, hj_max) < di_max) && !(__dsub_rn(dj, rshift) > di_max)) {
+              lo = thr_gt(dj);
+              hi_cut = INFINITY;
+            }
+          }
+        } else {
+          // DOPAIR_SUBSET (:745-770, 794-838): pix = x - shift in f64, dx = (float)(pix - pj.x)
+          px = __dsub_rn(xi, sh[0]); py = __dsub_rn(yi, sh[1]); pz = __dsub_rn(zi, sh[2]);
+          thr = cull_thr(hig2, 8e-7f * fmaxf(cA.width, cB.width));
+          if (mine) {
+            const float hg = (kind == kSubPair) ? __fadd_rn(hig, 0.f) : __fsub_rn(-hig, 0.f);
+            const double cut = __dadd_rn(__dadd_rn(__dadd_rn((double)hg, __dmul_rn(px, kc.axis[sid][0])),
+                                                   __dmul_rn(py, kc.axis[sid][1])),
+                                         __dmul_rn(pz, kc.axis[sid][2]));
+            if (kind == kSubPair) { lo = -INFINITY; hi_cut = thr_lt(cut); }
+            else { lo = thr_gt(cut); hi_cut = INFINITY; }
+          }
+        }
+        // union of the lanes' windows: what is worth staging at all
+        const float wlo = warp_min(lo), whi = warp_max(hi_cut);
+        if (!(wlo <= whi)) continue;  // no lane takes part
+        const float pfx = dsub_f(px, fl[0]), pfy = dsub_f(py, fl[1]), pfz = dsub_f(pz, fl[2]);
+
+        // every lane against the staged candidates [st, st + n) of the ring; n a multiple of 4
+        auto test = [&](int st, int n) {
+          if (__any_sync(kFull, qcnt > kQD - n)) drain_all();
+          for (int k0 = 0; k0 < n; k0 += 4) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+              const int k = (st + k0 + u) & (kTile - 1);
+              const float4 c = ws.pos[k];
+              const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
+              const float r2 = dist2(dx, dy, dz);
+              if (c.w >= lo && c.w <= hi_cut && r2 < thr) {
+                const int j = ws.idx[k];
+                if (j != pp) {
+                  gq[qcnt * 32] = dp ? make_float4(shf[0], shf[1], shf[2], __int_as_float(j | kDpFlag))
+                                     : make_float4(dx, dy, dz, __int_as_float(j));
+                  qcnt++;
+                }
               }
             }
           }
+        };
+
+        int st = 0, ntile = 0, base = 0;
+        bool done = false;
+        while (true) {
+          if (base < cB.count) {
+            const int nt = min(32, cB.count - base);
+            float dk = 0.f;
+            int j = 0;
+            bool keep = lane < nt;
+            if (sorted) {
+              const int e = desc ? (cB.count - 1 - base - lane) : (base + lane);
+              if (keep) dk = d.sort_d[segB + e];
+              const float k0 = __shfl_sync(kFull, dk, 0);
+              if (desc ? !(k0 >= wlo) : !(k0 <= whi)) done = true;  // sorted axis: nothing further on can hit
+              keep = keep && !done && dk >= wlo && dk <= whi;
+              if (keep) j = cB.first + d.sort_i[segB + e];
+            } else {
+              j = cB.first + base + lane;
+            }
+            float4 c = make_float4(qnan, qnan, qnan, qnan);
+            if (keep) {
+              c = make_float4(dsub_f(d.x[j], fo[0]), dsub_f(d.y[j], fo[1]), dsub_f(d.z[j], fo[2]), dk);
+              keep = c.x >= sb.lo[0] && c.x <= sb.hi[0] && c.y >= sb.lo[1] && c.y <= sb.hi[1] && c.z >= sb.lo[2] &&
+                     c.z <= sb.hi[2];
+            }
+            const unsigned b = __ballot_sync(kFull, keep);
+            if (keep) {
+              const int s = (st + ntile + __popc(b & lt_mask)) & (kTile - 1);
+              ws.pos[s] = c;
+              ws.idx[s] = j;
+            }
+            ntile += __popc(b);
+            base += 32;
+          } else {
+            done = true;
+          }
+          int n = 0;
+          if (ntile >= 32) {
+            n = 32;
+          } else if (done && ntile > 0) {
+            n = (ntile + 3) & ~3;
+            if (lane < n - ntile) ws.pos[(st + ntile + lane) & (kTile - 1)] = make_float4(qnan, qnan, qnan, qnan);
+          }
+          if (n > 0) {
+            __syncwarp();
+            test(st, n);
+            st = (st + 32) & (kTile - 1);
+            ntile = max(ntile - 32, 0);
+          }
+          if (done && ntile == 0) break;
         }
+        __syncwarp();
       }
-    }
-    while (__any_sync(kFull, qcnt > 0)) drain_round();
-    if (mine) {
-      d.dens0[p] = make_float4(acc.rho, acc.rho_dh, acc.wcount, acc.wcount_dh);
-      d.dens1[p] = make_float4(acc.div_v, acc.rx, acc.ry, acc.rz);
+      drain_all();
+      if (mine) {
+        d.dens0[p] = make_float4(acc.rho, acc.rho_dh, acc.wcount, acc.wcount_dh);
+        d.dens1[p] = make_float4(acc.div_v, acc.rx, acc.ry, acc.rz);
+      }
     }
   }
   for (int o = 16; o > 0; o >>= 1) nhits += __shfl_down_sync(kFull, nhits, o);
@@ -831,269 +956,414 @@ __global__ void k_cell_hmax(Dev d) {
   if (lane == 0) d.cell_hmax[c] = m;
 }
 
+// Bounding box of every cell's particles, f32 relative to the cell's loc (what the
+// neighbour-loop kernels use to skip cell pairs and candidates out of reach; particles may
+// have drifted out of their cell, so the cell geometry itself is not used).  One warp per
+// LEAF folds its particles and pushes the box up through its ancestors with atomics on
+// order-preserving integer images of the floats.  cell_box: [ncells][6] = lo xyz, hi xyz.
+__global__ void k_cell_box_init(Dev d) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= d.ncells * 6) return;
+  d.cell_box_u[i] = float_to_ordered((i % 6) < 3 ? INFINITY : -INFINITY);
+}
+__global__ void k_cell_box(Dev d) {
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (c >= d.ncells || d.cell_split[c]) return;  // leaves only
+  const CellDev cell = d.cells[c];
+  if (cell.count == 0) return;
+  double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int k = lane; k < cell.count; k += 32) {
+    const double p[3] = {d.x[cell.first + k], d.y[cell.first + k], d.z[cell.first + k]};
+#pragma unroll
+    for (int a = 0; a < 3; a++) { lo[a] = fmin(lo[a], p[a]); hi[a] = fmax(hi[a], p[a]); }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++)
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[a] = fmin(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+      hi[a] = fmax(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+    }
+  if (lane >= 6) return;
+  const int a = lane % 3;
+  const bool is_hi = lane >= 3;
+  const double v = is_hi ? (a == 0 ? hi[0] : a == 1 ? hi[1] : hi[2]) : (a == 0 ? lo[0] : a == 1 ? lo[1] : lo[2]);
+  for (int q = c; q >= 0; q = d.cell_parent[q]) {
+    const double rel = v - d.cells[q].loc[a];
+    if (is_hi) atomicMax(&d.cell_box_u[(int64_t)q * 6 + lane], float_to_ordered(__double2float_ru(rel)));
+    else atomicMin(&d.cell_box_u[(int64_t)q * 6 + lane], float_to_ordered(__double2float_rd(rel)));
+  }
+}
+__global__ void k_cell_box_finish(Dev d) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= d.ncells * 6) return;
+  d.cell_box[i] = ordered_to_float(d.cell_box_u[i]);
+}
+
 // ---------------------------------------------------------------------------
-// K6: force.  Same warp-per-unit walk as K3.  A pair (L in ci, R in cj)
-// interacts when loop 1 of DOPAIR2 takes it (:1528-1737: r2 < hL^2 g^2 with R
-// inside L's sorted range) or loop 2 does (:1741-1952: r2 < hR^2 g^2 and
-// r2 >= hL^2 g^2 with L inside R's range).  The reference applies all loop-1
-// updates of a pair before any loop-2 update, so each pair item is walked in
-// two phases and the hits of both go through the same FIFO.
+// K6: force.  Same persistent warp-per-unit walk as K3.  A pair (L in ci, R in
+// cj) interacts when loop 1 of DOPAIR2 takes it (:1528-1737: r2 < hL^2 g^2
+// with R inside L's sorted range) or loop 2 does (:1741-1952: r2 < hR^2 g^2
+// and r2 >= hL^2 g^2 with L inside R's range).  The reference applies all
+// loop-1 updates of a pair before any loop-2 update.  The candidates of a pair
+// are walked ONCE: loop-1 hits go straight to the lane's FIFO, the (few)
+// loop-2 hits wait in a small per-lane side list in shared memory and are
+// appended when the pair is finished.  Should a side list overflow (kSide
+// loop-2 hits of one lane in one pair: only with strongly varying h), the side
+// lists are dropped and the pair is walked a second time for loop 2 alone.
 //   tile.aux per candidate:  x = h^2 gamma^2 of the candidate (self: its cull threshold)
 //                            y = candidate is cj: its "dj" of loop 2, +inf if loop 2 skips it
 //                            z = candidate is ci: largest sort key of a cj particle inside its
 //                                loop-1 range, -inf if loop 1 skips it
 // ---------------------------------------------------------------------------
+struct ForceTile {
+  float4 pos[kTile];
+  float4 aux[kTile];
+  int idx[kTile];
+  float4 side[kSide][32];
+};
+
 template <int SCHEME>
 __global__ void __launch_bounds__(kBlock) k_force(Dev d) {
-  __shared__ WarpTile tiles[kWarps];
-  WarpTile &ws = tiles[threadIdx.x >> 5];
+  __shared__ ForceTile tiles[kWarps];
+  ForceTile &ws = tiles[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
-  const int wid = blockIdx.x * kWarps + (threadIdx.x >> 5);
-  if (wid >= d.n_units) return;
-  const int slot = d.unit_leaf[wid];
-  const CellDev cL = d.cells[d.leaves[slot]];
-  const int ib = d.item_begin[slot], ie = d.item_begin[slot + 1];
+  const unsigned lt_mask = (1u << lane) - 1u;
+  float4 *const gq = d.gq + (size_t)(blockIdx.x * kWarps + (threadIdx.x >> 5)) * (kQD * 32) + lane;
+  int *const work = d.work_ctr + 1 + kc.max_iter;
   const bool rec = d.rec_capacity > 0;
+  const float qnan = __int_as_float(0x7fc00000);
   unsigned long long nhits = 0;
 
-  int p = -1;
-  {
-    const int q = d.lane_part[(int64_t)wid * 32 + lane];
-    if (q >= 0 && d.time_bin[q] <= kc.max_active_bin) p = q;
-  }
-  if (!__any_sync(kFull, p >= 0)) return;
-  const bool mine = p >= 0;
-  const int pp = mine ? p : cL.first;
-  const double xi = d.x[pp], yi = d.y[pp], zi = d.z[pp];
-  ForceI me;
-  {
-    const float4 vmi = d.vm[pp];
-    const float4 fi = d.fin[pp];
-    const float4 hbi = d.hb[pp];
-    me.h = hbi.x;
-    me.hi_inv = 1.0f / me.h;
-    const float hi2 = me.hi_inv * me.hi_inv;
-    me.hid_inv = hi2 * hi2;
-    me.m = vmi.w; me.vx = vmi.x; me.vy = vmi.y; me.vz = vmi.z;
-    me.rho = fi.x; me.P = fi.y; me.f = fi.z; me.c = fi.w;
-    me.bal = hbi.y;
-    me.Pr2 = hbi.w;
-  }
-  const float hig2 = sq_gamma2(me.h);
-  const float hig = __fmul_rn(me.h, kc.gamma);
-  const long long idi = rec ? d.id[pp] : 0;
-  ForceAcc acc;
-  {
-    const float4 a0 = d.acc[pp];
-    acc.ax = a0.x; acc.ay = a0.y; acc.az = a0.z; acc.u_dt = a0.w;
-    acc.h_dt = d.h_dt[pp];
-    acc.v_sig = d.v_sig[pp];
-    acc.min_bin = d.min_bin[pp];
-  }
-  int qhead = 0, qcnt = 0;
+  while (true) {
+    int wid = 0;
+    if (lane == 0) wid = atomicAdd(work, 1);
+    wid = __shfl_sync(kFull, wid, 0);
+    if (wid >= d.n_units) break;
+    const int slot = d.unit_leaf[wid];
+    const CellDev cL = d.cells[d.leaves[slot]];
+    const int ib = d.item_begin[slot], ie = d.item_begin[slot + 1];
 
-  auto consume = [&](const float4 e) {
-    const int w = __float_as_int(e.w);
-    const int j = w & (kDpFlag - 1);
-    const float4 hbj = d.hb[j];
-    float dx, dy, dz;
-    bool hit = true;
-    if (w & kDpFlag) {  // own cell: f64 position difference (:2349-2353, 2416-2420)
-      dx = dsub_f(xi, d.x[j]); dy = dsub_f(yi, d.y[j]); dz = dsub_f(zi, d.z[j]);
-      const float r2e = dist2(dx, dy, dz);
-      hit = (r2e < hig2) || (r2e < sq_gamma2(hbj.x));
-    } else {
-      dx = e.x; dy = e.y; dz = e.z;
+    int p = -1;
+    {
+      const int q = d.lane_part[(int64_t)wid * 32 + lane];
+      if (q >= 0 && d.time_bin[q] <= kc.max_active_bin) p = q;
     }
-    if (hit) {
-      const float r2 = dist2(dx, dy, dz);
-      const float4 vmj = d.vm[j];
-      const float4 fj = d.fin[j];
-      ForceJ pj;
-      pj.h = hbj.x; pj.bal = hbj.y; pj.bin = __float_as_int(hbj.z); pj.Pr2 = hbj.w;
-      pj.m = vmj.w; pj.vx = vmj.x; pj.vy = vmj.y; pj.vz = vmj.z;
-      pj.rho = fj.x; pj.P = fj.y; pj.f = fj.z; pj.c = fj.w;
-      iact_force<SCHEME>(acc, r2, dx, dy, dz, me, pj);
-      nhits++;
-      if (rec) record_pair(d, 2, idi, d.id[j]);
+    if (!__any_sync(kFull, p >= 0)) continue;
+    const bool mine = p >= 0;
+    const int pp = mine ? p : cL.first;
+    const double xi = d.x[pp], yi = d.y[pp], zi = d.z[pp];
+    ForceI me;
+    {
+      const float4 vmi = d.vm[pp];
+      const float4 fi = d.fin[pp];
+      const float4 hbi = d.hb[pp];
+      me.h = hbi.x;
+      me.hi_inv = 1.0f / me.h;
+      const float hi2 = me.hi_inv * me.hi_inv;
+      me.hid_inv = hi2 * hi2;
+      me.m = vmi.w; me.vx = vmi.x; me.vy = vmi.y; me.vz = vmi.z;
+      me.rho = fi.x; me.P = fi.y; me.f = fi.z; me.c = fi.w;
+      me.bal = hbi.y;
+      me.Pr2 = hbi.w;
     }
-  };
-  auto drain_round = [&]() {
-    if (qcnt > 0) {
-      const float4 e = ws.q[qhead][lane];
-      qhead = (qhead + 1) & (kQ - 1);
-      qcnt--;
-      consume(e);
+    const float hig2 = sq_gamma2(me.h);
+    const float hig = __fmul_rn(me.h, kc.gamma);
+    const long long idi = rec ? d.id[pp] : 0;
+    ForceAcc acc;
+    {
+      const float4 a0 = d.acc[pp];
+      acc.ax = a0.x; acc.ay = a0.y; acc.az = a0.z; acc.u_dt = a0.w;
+      acc.h_dt = d.h_dt[pp];
+      acc.v_sig = d.v_sig[pp];
+      acc.min_bin = d.min_bin[pp];
     }
-  };
-  auto push = [&](const float4 e) {
-    ws.q[(qhead + qcnt) & (kQ - 1)][lane] = e;
-    qcnt++;
-  };
+    int qcnt = 0;
 
-  for (int it = ib; it < ie; it++) {
-    const Item item = d.items[it];
-    const CellDev cA = d.cells[item.own];
-    const CellDev cB = d.cells[item.partner];
-    const int kind = item.kind;
-    const int sid = item.sid;
-
-    if (kind == kSelf) {
-      // ---- DOSELF2 (:2337-2471): every other particle of the cell, index order
-      const float e = 4e-7f * cA.width;
-      const float pfx = dsub_f(xi, cA.loc[0]), pfy = dsub_f(yi, cA.loc[1]), pfz = dsub_f(zi, cA.loc[2]);
-      const float thr_i = mine ? cull_thr(hig2, e) : -INFINITY;
-      for (int base = 0; base < cB.count; base += 32) {
-        const int nt = min(32, cB.count - base);
-        __syncwarp();
-        {
-          const float qnan = __int_as_float(0x7fc00000);
-          float4 c = make_float4(qnan, qnan, qnan, qnan);  // padding: never a hit
-          float4 a = make_float4(-INFINITY, 0.f, 0.f, 0.f);
-          int j = 0;
-          if (lane < nt) {
-            j = cB.first + base + lane;
-            c = make_float4(dsub_f(d.x[j], cA.loc[0]), dsub_f(d.y[j], cA.loc[1]), dsub_f(d.z[j], cA.loc[2]), 0.f);
-            a.x = cull_thr(sq_gamma2(d.hb[j].x), e);
-          }
-          ws.pos[lane] = c; ws.aux[lane] = a; ws.idx[lane] = j;
-        }
-        __syncwarp();
-        for (int k0 = 0; k0 < nt; k0 += 4) {
-          while (__any_sync(kFull, qcnt > kQ - 4)) drain_round();
+    // boxes of the unit's particles in the leaf's frame: bare positions (u0), and grown by
+    // each particle's own search radius (uH)
+    float u0lo[3], u0hi[3], uHlo[3], uHhi[3];
+    {
+      const float l[3] = {dsub_f(xi, cL.loc[0]), dsub_f(yi, cL.loc[1]), dsub_f(zi, cL.loc[2])};
+      const float ru = hig * 1.0001f;
 #pragma unroll
-          for (int u = 0; u < 4; u++) {
-            const int k = k0 + u;
-            const float4 c = ws.pos[k];
-            const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
-            const float r2 = dist2(dx, dy, dz);
-            if (mine && (r2 < thr_i || r2 < ws.aux[k].x)) {
-              const int j = ws.idx[k];
-              if (j != pp) push(make_float4(0.f, 0.f, 0.f, __int_as_float(j | kDpFlag)));
-            }
-          }
-        }
+      for (int k = 0; k < 3; k++) {
+        u0lo[k] = warp_min(mine ? l[k] : INFINITY);
+        u0hi[k] = warp_max(mine ? l[k] : -INFINITY);
+        uHlo[k] = warp_min(mine ? l[k] - ru : INFINITY);
+        uHhi[k] = warp_max(mine ? l[k] + ru : -INFINITY);
       }
-      continue;
     }
 
-    // ---- DOPAIR2
-    const bool left = kind == kPairLeft;  // this leaf's cell is the pair's ci
-    const int64_t segB = d.sort_lookup[(int64_t)item.partner * 13 + sid];
-    const int64_t segA = d.sort_lookup[(int64_t)item.own * 13 + sid];
-    double sh[3] = {item_shift(d, item.shift, 0), item_shift(d, item.shift, 1), item_shift(d, item.shift, 2)};
-    const double rshift = item_rshift(sh, sid);
-    const float hmaxA = d.cell_hmax[item.own], hmaxB = d.cell_hmax[item.partner];
-    // frame: ci particles relative to cj.loc + shift, cj particles relative to cj.loc (:1480-1482)
-    double fo[3], fl[3];
-    for (int k = 0; k < 3; k++) {
-      if (left) { fo[k] = cB.loc[k]; fl[k] = __dadd_rn(cB.loc[k], sh[k]); }
-      else { fo[k] = __dadd_rn(cA.loc[k], sh[k]); fl[k] = cA.loc[k]; }
-    }
-    const float pfx = dsub_f(xi, fl[0]), pfy = dsub_f(yi, fl[1]), pfz = dsub_f(zi, fl[2]);
-    const float d_me = sort_key(xi, yi, zi, sid);
-    // constants of the pair, as the reference forms them (f64)
-    const double dj_min = (double)d.sort_d[left ? segB : segA];                       // first of cj
-    const double di_max = (double)d.sort_d[left ? (segA + cA.count - 1) : (segB + cB.count - 1)];  // last of ci
-    const double hi_max_g = __dmul_rn((double)(left ? hmaxA : hmaxB), (double)kc.gamma);
-    const double hj_max_g = __dmul_rn((double)(left ? hmaxB : hmaxA), (double)kc.gamma);
-    const double rhs2 = __dsub_rn(di_max, rshift);
-    const float hmaxBg = __fmul_rn(hmaxB, kc.gamma);
-
-    // lane-side cuts of the two phases
-    float cut1, cut2, bound1, bound2;
-    if (left) {
-      // phase 1: I am pi of loop 1; candidates R ascending while (double)dR < di
-      const double di = __dsub_rn((double)__fadd_rn(d_me, hig), rshift);
-      const bool ok1 = mine && (__dsub_rn(__dadd_rn((double)d_me, hi_max_g), rshift) > dj_min) && !(di < dj_min);
-      cut1 = ok1 ? thr_lt(di) : -INFINITY;
-      bound1 = cut1;
-      // phase 2: I am a pi inside R's loop-2 range: (double)d_me - rshift > dj(R)
-      cut2 = mine ? thr_lt(__dsub_rn((double)d_me, rshift)) : -INFINITY;
-      bound2 = -INFINITY;
-      if (mine) {
-        bound2 = cut2 + hmaxBg * 1.000001f + 1e-30f;
-        bound2 = bound2 + fabsf(bound2) * 2e-7f;
+    auto consume = [&](const float4 e) {
+      const int w = __float_as_int(e.w);
+      const int j = w & (kDpFlag - 1);
+      const float4 hbj = d.hb[j];
+      float dx, dy, dz;
+      bool hit = true;
+      if (w & kDpFlag) {  // own cell: f64 position difference (:2349-2353, 2416-2420)
+        dx = dsub_f(xi, d.x[j]); dy = dsub_f(yi, d.y[j]); dz = dsub_f(zi, d.z[j]);
+        const float r2e = dist2(dx, dy, dz);
+        hit = (r2e < hig2) || (r2e < sq_gamma2(hbj.x));
+      } else {
+        dx = e.x; dy = e.y; dz = e.z;
       }
-    } else {
-      // phase 1: I am a pj inside L's loop-1 range: (double)d_me < di(L); candidates L descending
-      cut1 = mine ? d_me : INFINITY;
-      float b = (float)((double)d_me + rshift) - hmaxBg * 1.000001f - 1e-30f;
-      b = b - fabsf(b) * 2e-7f - fabsf((float)rshift) * 2e-7f;
-      bound1 = mine ? b : INFINITY;
-      // phase 2: I am pj of loop 2; candidates L descending while (double)dL - rshift > dj
-      const float djf = __fsub_rn(d_me, hig);
-      const bool ok2 = mine && (__dsub_rn((double)d_me, hj_max_g) < rhs2) && !((double)djf > rhs2);
-      cut2 = ok2 ? thr_gt_shift(rshift, (double)djf) : INFINITY;
-      bound2 = cut2;
-    }
+      if (hit) {
+        const float r2 = dist2(dx, dy, dz);
+        const float4 vmj = d.vm[j];
+        const float4 fj = d.fin[j];
+        ForceJ pj;
+        pj.h = hbj.x; pj.bal = hbj.y; pj.bin = __float_as_int(hbj.z); pj.Pr2 = hbj.w;
+        pj.m = vmj.w; pj.vx = vmj.x; pj.vy = vmj.y; pj.vz = vmj.z;
+        pj.rho = fj.x; pj.P = fj.y; pj.f = fj.z; pj.c = fj.w;
+        iact_force<SCHEME>(acc, r2, dx, dy, dz, me, pj);
+        nhits++;
+        if (rec) record_pair(d, 2, idi, d.id[j]);
+      }
+    };
+    auto drain_all = [&]() {
+      const int m = __reduce_max_sync(kFull, qcnt);
+      float4 e = qcnt > 0 ? gq[0] : make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r = 0; r < m; r++) {
+        const float4 en = (r + 1 < qcnt) ? gq[(r + 1) * 32] : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < qcnt) consume(e);
+        e = en;
+      }
+      qcnt = 0;
+    };
 
-    for (int phase = 0; phase < 2; phase++) {
-      const float wlim = left ? warp_max(phase == 0 ? bound1 : bound2) : warp_min(phase == 0 ? bound1 : bound2);
-      if (left ? (wlim == -INFINITY) : (wlim == INFINITY)) continue;
-      for (int base = 0; base < cB.count; base += 32) {
-        const int nt = min(32, cB.count - base);
-        __syncwarp();
-        {
-          const float qnan = __int_as_float(0x7fc00000);
-          float4 c = make_float4(qnan, qnan, qnan, qnan);  // padding: never in a window, never a hit
-          float4 a = make_float4(0.f, INFINITY, -INFINITY, 0.f);
-          int j = 0;
-          if (lane < nt) {
-            const int e = left ? (base + lane) : (cB.count - 1 - base - lane);
-            j = cB.first + d.sort_i[segB + e];
-            const float dk = d.sort_d[segB + e];
-            c = make_float4(dsub_f(d.x[j], fo[0]), dsub_f(d.y[j], fo[1]), dsub_f(d.z[j], fo[2]), dk);
-            const float hj = d.hb[j].x;
-            const float hjg = __fmul_rn(hj, kc.gamma);
-            a.x = sq_gamma2(hj);
-            if (left) {
-              // candidate is R in cj: loop 2 outer conditions (:1741-1760)
-              const float djf = __fsub_rn(dk, hjg);
-              const bool ok = (__dsub_rn((double)dk, hj_max_g) < rhs2) && !((double)djf > rhs2);
-              a.y = ok ? djf : INFINITY;
-            } else {
-              // candidate is L in ci: loop 1 outer conditions (:1528-1545)
-              const double di = __dsub_rn((double)__fadd_rn(dk, hjg), rshift);
-              const bool ok = (__dsub_rn(__dadd_rn((double)dk, hi_max_g), rshift) > dj_min) && !(di < dj_min);
-              a.z = ok ? thr_lt(di) : -INFINITY;
-            }
-          }
-          ws.pos[lane] = c; ws.aux[lane] = a; ws.idx[lane] = j;
-        }
-        __syncwarp();
-        {
-          const float first_key = ws.pos[0].w;
-          if (left ? !(first_key <= wlim) : !(first_key >= wlim)) break;
-        }
-        for (int k0 = 0; k0 < nt; k0 += 4) {
-          while (__any_sync(kFull, qcnt > kQ - 4)) drain_round();
+    for (int it = ib; it < ie; it++) {
+      const Item item = d.items[it];
+      const CellDev cA = d.cells[item.own];
+      const CellDev cB = d.cells[item.partner];
+      const int kind = item.kind;
+      const int sid = item.sid;
+      const bool self = kind == kSelf;
+      const bool left = kind == kPairLeft;  // this leaf's cell is the pair's ci
+      const float hmaxA = d.cell_hmax[item.own], hmaxB = d.cell_hmax[item.partner];
+      const float hmaxBg = __fmul_rn(hmaxB, kc.gamma);
+
+      double sh[3] = {0.0, 0.0, 0.0};
+      if (!self) {
 #pragma unroll
-          for (int u = 0; u < 4; u++) {
-            const int k = k0 + u;
-            const float4 c = ws.pos[k];
-            const float4 a = ws.aux[k];
-            const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
-            const float r2 = dist2(dx, dy, dz);
-            bool hit;
-            if (left) {
-              hit = (phase == 0) ? (c.w <= cut1 && r2 < hig2) : (a.y <= cut2 && r2 < a.x && r2 >= hig2);
-            } else {
-              hit = (phase == 0) ? (cut1 <= a.z && r2 < a.x) : (c.w >= cut2 && r2 < hig2 && r2 >= a.x);
-            }
-            if (hit) push(make_float4(dx, dy, dz, __int_as_float(ws.idx[k])));
+        for (int k = 0; k < 3; k++) sh[k] = item_shift(d, item.shift, k);
+      }
+      // frame: ci particles relative to cj.loc + shift, cj particles relative to cj.loc (:1480-1482);
+      // DOSELF2 (:2337-2471): relative to the cell
+      double fo[3], fl[3];
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        if (self) { fo[k] = fl[k] = cA.loc[k]; }
+        else if (left) { fo[k] = cB.loc[k]; fl[k] = __dadd_rn(cB.loc[k], sh[k]); }
+        else { fo[k] = __dadd_rn(cA.loc[k], sh[k]); fl[k] = cA.loc[k]; }
+      }
+      // a hit needs r < max(H of the lane, H of the candidate): box of the lanes for this item
+      StageBox sb;
+      {
+        float blo[3], bhi[3];
+        const float rb = hmaxBg * 1.0001f;
+        double ol[3], og[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          blo[k] = fminf(uHlo[k], u0lo[k] - rb);
+          bhi[k] = fmaxf(uHhi[k], u0hi[k] + rb);
+          ol[k] = cL.loc[k] - fl[k];
+          og[k] = cB.loc[k] - fo[k];
+        }
+        stage_box(blo, bhi, ol, self ? 1e-6f * cA.width : 0.f, sb);
+        if (!box_reaches_cell(sb, d.cell_box + (int64_t)item.partner * 6, og)) continue;
+      }
+      const float pfx = dsub_f(xi, fl[0]), pfy = dsub_f(yi, fl[1]), pfz = dsub_f(zi, fl[2]);
+
+      // lane-side cuts of the two loops, and what bounds the walk along the sorted axis
+      float cut1 = 0.f, cut2 = 0.f, bound1 = 0.f, bound2 = 0.f, thr_i = 0.f;
+      int64_t segB = 0;
+      double rshift = 0.0, dj_min = 0.0, hi_max_g = 0.0, hj_max_g = 0.0, rhs2 = 0.0;
+      const float e_self = 4e-7f * cA.width;
+      if (self) {
+        thr_i = mine ? cull_thr(hig2, e_self) : -INFINITY;
+      } else {
+        segB = d.sort_lookup[(int64_t)item.partner * 13 + sid];
+        const int64_t segA = d.sort_lookup[(int64_t)item.own * 13 + sid];
+        rshift = item_rshift(sh, sid);
+        const float d_me = sort_key(xi, yi, zi, sid);
+        // constants of the pair, as the reference forms them (f64)
+        dj_min = (double)d.sort_d[left ? segB : segA];                                            // first of cj
+        const double di_max = (double)d.sort_d[left ? (segA + cA.count - 1) : (segB + cB.count - 1)];  // last of ci
+        hi_max_g = __dmul_rn((double)(left ? hmaxA : hmaxB), (double)kc.gamma);
+        hj_max_g = __dmul_rn((double)(left ? hmaxB : hmaxA), (double)kc.gamma);
+        rhs2 = __dsub_rn(di_max, rshift);
+        if (left) {
+          // loop 1: I am pi; candidates R ascending while (double)dR < di
+          const double di = __dsub_rn((double)__fadd_rn(d_me, hig), rshift);
+          const bool ok1 = mine && (__dsub_rn(__dadd_rn((double)d_me, hi_max_g), rshift) > dj_min) && !(di < dj_min);
+          cut1 = ok1 ? thr_lt(di) : -INFINITY;
+          bound1 = cut1;
+          // loop 2: I am a pi inside R's range: (double)d_me - rshift > dj(R)
+          cut2 = mine ? thr_lt(__dsub_rn((double)d_me, rshift)) : -INFINITY;
+          bound2 = -INFINITY;
+          if (mine) {
+            bound2 = cut2 + hmaxBg * 1.000001f + 1e-30f;
+            bound2 = bound2 + fabsf(bound2) * 2e-7f;
           }
+        } else {
+          // loop 1: I am a pj inside L's range: (double)d_me < di(L); candidates L descending
+          cut1 = mine ? d_me : INFINITY;
+          float b = (float)((double)d_me + rshift) - hmaxBg * 1.000001f - 1e-30f;
+          b = b - fabsf(b) * 2e-7f - fabsf((float)rshift) * 2e-7f;
+          bound1 = mine ? b : INFINITY;
+          // loop 2: I am pj; candidates L descending while (double)dL - rshift > dj
+          const float djf = __fsub_rn(d_me, hig);
+          const bool ok2 = mine && (__dsub_rn((double)d_me, hj_max_g) < rhs2) && !((double)djf > rhs2);
+          cut2 = ok2 ? thr_gt_shift(rshift, (double)djf) : INFINITY;
+          bound2 = cut2;
+        }
+      }
+
+      // pass 0: both loops in one walk (loop-2 hits to the side list);
+      // pass 1: only after a side-list overflow, loop 2 alone
+      int scnt = 0;
+      bool sovf = false;
+      for (int pass = 0; pass < 2; pass++) {
+        float wlim;  // how far along the sorted axis some lane can still hit
+        if (self) wlim = 0.f;
+        else if (left) wlim = warp_max(pass == 0 ? fmaxf(bound1, bound2) : bound2);
+        else wlim = warp_min(pass == 0 ? fminf(bound1, bound2) : bound2);
+        if (!self && (left ? (wlim == -INFINITY) : (wlim == INFINITY))) break;
+
+        auto test = [&](int st, int n) {
+          if (__any_sync(kFull, qcnt > kQD - n - kSide)) drain_all();
+          for (int k0 = 0; k0 < n; k0 += 4) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+              const int k = (st + k0 + u) & (kTile - 1);
+              const float4 c = ws.pos[k];
+              const float4 a = ws.aux[k];
+              const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
+              const float r2 = dist2(dx, dy, dz);
+              if (self) {
+                if (r2 < thr_i || (mine && r2 < a.x)) {
+                  const int j = ws.idx[k];
+                  if (j != pp) {
+                    gq[qcnt * 32] = make_float4(0.f, 0.f, 0.f, __int_as_float(j | kDpFlag));
+                    qcnt++;
+                  }
+                }
+              } else {
+                bool h1, h2;
+                if (left) {
+                  h1 = c.w <= cut1 && r2 < hig2;
+                  h2 = a.y <= cut2 && r2 < a.x && r2 >= hig2;
+                } else {
+                  h1 = cut1 <= a.z && r2 < a.x;
+                  h2 = c.w >= cut2 && r2 < hig2 && r2 >= a.x;
+                }
+                if (pass == 0 ? h1 : h2) {
+                  gq[qcnt * 32] = make_float4(dx, dy, dz, __int_as_float(ws.idx[k]));
+                  qcnt++;
+                } else if (pass == 0 && h2) {
+                  if (scnt < kSide) ws.side[scnt][lane] = make_float4(dx, dy, dz, __int_as_float(ws.idx[k]));
+                  else sovf = true;
+                  scnt++;
+                }
+              }
+            }
+          }
+        };
+
+        int st = 0, ntile = 0, base = 0;
+        bool done = false;
+        while (true) {
+          if (base < cB.count) {
+            const int nt = min(32, cB.count - base);
+            float dk = 0.f;
+            int j = 0;
+            bool keep = lane < nt;
+            if (self) {
+              j = cB.first + base + lane;
+            } else {
+              const int e = left ? (base + lane) : (cB.count - 1 - base - lane);
+              if (keep) dk = d.sort_d[segB + e];
+              const float k0 = __shfl_sync(kFull, dk, 0);
+              if (left ? !(k0 <= wlim) : !(k0 >= wlim)) done = true;  // sorted axis: nothing further on can hit
+              keep = keep && !done && (left ? (dk <= wlim) : (dk >= wlim));
+              if (keep) j = cB.first + d.sort_i[segB + e];
+            }
+            float4 c = make_float4(qnan, qnan, qnan, qnan);
+            float4 a = make_float4(0.f, INFINITY, -INFINITY, 0.f);
+            if (keep) {
+              c = make_float4(dsub_f(d.x[j], fo[0]), dsub_f(d.y[j], fo[1]), dsub_f(d.z[j], fo[2]), dk);
+              keep = c.x >= sb.lo[0] && c.x <= sb.hi[0] && c.y >= sb.lo[1] && c.y <= sb.hi[1] && c.z >= sb.lo[2] &&
+                     c.z <= sb.hi[2];
+            }
+            if (keep) {
+              const float hj = d.hb[j].x;
+              const float hjg = __fmul_rn(hj, kc.gamma);
+              a.x = sq_gamma2(hj);
+              if (self) {
+                a.x = cull_thr(a.x, e_self);
+              } else if (left) {
+                // candidate is R in cj: loop 2 outer conditions (:1741-1760)
+                const float djf = __fsub_rn(dk, hjg);
+                const bool ok = (__dsub_rn((double)dk, hj_max_g) < rhs2) && !((double)djf > rhs2);
+                a.y = ok ? djf : INFINITY;
+              } else {
+                // candidate is L in ci: loop 1 outer conditions (:1528-1545)
+                const double di = __dsub_rn((double)__fadd_rn(dk, hjg), rshift);
+                const bool ok = (__dsub_rn(__dadd_rn((double)dk, hi_max_g), rshift) > dj_min) && !(di < dj_min);
+                a.z = ok ? thr_lt(di) : -INFINITY;
+              }
+            }
+            const unsigned b = __ballot_sync(kFull, keep);
+            if (keep) {
+              const int s = (st + ntile + __popc(b & lt_mask)) & (kTile - 1);
+              ws.pos[s] = c;
+              ws.aux[s] = a;
+              ws.idx[s] = j;
+            }
+            ntile += __popc(b);
+            base += 32;
+          } else {
+            done = true;
+          }
+          int n = 0;
+          if (ntile >= 32) {
+            n = 32;
+          } else if (done && ntile > 0) {
+            n = (ntile + 3) & ~3;
+            if (lane < n - ntile) ws.pos[(st + ntile + lane) & (kTile - 1)] = make_float4(qnan, qnan, qnan, qnan);
+          }
+          if (n > 0) {
+            __syncwarp();
+            test(st, n);
+            st = (st + 32) & (kTile - 1);
+            ntile = max(ntile - 32, 0);
+          }
+          if (done && ntile == 0) break;
+        }
+        __syncwarp();
+        if (self) break;
+        if (pass == 0) {
+          if (!__any_sync(kFull, sovf)) {
+            // the pair's loop-2 hits follow its loop-1 hits
+            for (int s = 0; s < scnt; s++) {
+              gq[qcnt * 32] = ws.side[s][lane];
+              qcnt++;
+            }
+            break;
+          }
+          scnt = 0;
         }
       }
     }
-  }
-  while (__any_sync(kFull, qcnt > 0)) drain_round();
-  if (mine) {
-    d.acc[p] = make_float4(acc.ax, acc.ay, acc.az, acc.u_dt);
-    // hydro_end_force (Minimal/hydro.h:878-882), the whole of runner_do_end_hydro_force for these schemes
-    d.h_dt[p] = acc.h_dt * (me.h * 0.3333333333f);
-    d.v_sig[p] = acc.v_sig;
-    d.min_bin[p] = acc.min_bin;
+    drain_all();
+    if (mine) {
+      d.acc[p] = make_float4(acc.ax, acc.ay, acc.az, acc.u_dt);
+      // hydro_end_force (Minimal/hydro.h:878-882), the whole of runner_do_end_hydro_force for these schemes
+      d.h_dt[p] = acc.h_dt * (me.h * 0.3333333333f);
+      d.v_sig[p] = acc.v_sig;
+      d.min_bin[p] = acc.min_bin;
+    }
   }
   for (int o = 16; o > 0; o >>= 1) nhits += __shfl_down_sync(kFull, nhits, o);
   if (lane == 0 && nhits) atomicAdd(&d.hits[2], nhits);

@@ -45,6 +45,7 @@ struct swift_cuda_ctx {
   long long rec_capacity = 0;
   float4 *d_dens0_first = nullptr, *d_dens1_first = nullptr;  // snapshot of the first-pass sums
   float *d_h0 = nullptr;     // h as last uploaded (swift_cuda_restore_particles)
+  int grid_density = 0, grid_redo = 0, grid_force = 0;  // persistent grids: one resident wave of CTAs
   // caller-order staging on the device (K1 pack / K7 unpack)
   double *s_x = nullptr;
   float *s_v = nullptr, *s_mass = nullptr, *s_h = nullptr, *s_u = nullptr, *s_carry[5] = {};
@@ -255,6 +256,19 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
       upload(c, &dhm_old, c->tree.h_max.data(), nc))
     return 1;
   d.cells = dcells; d.cell_hmax_old = dhm_old;
+  {
+    std::vector<int32_t> par(nc);
+    std::vector<uint8_t> spl(nc);
+    for (size_t k = 0; k < nc; k++) {
+      par[k] = c->tree.cells[k].parent;
+      spl[k] = c->tree.cells[k].split ? 1 : 0;
+    }
+    int32_t *dpar; uint8_t *dspl;
+    if (upload(c, &dpar, par.data(), nc) || upload(c, &dspl, spl.data(), nc) || dmalloc(c, &d.cell_box, nc * 6) ||
+        dmalloc(c, &d.cell_box_u, nc * 6))
+      return 1;
+    d.cell_parent = dpar; d.cell_split = dspl;
+  }
 
 
   // work lists
@@ -298,6 +312,29 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
     return 1;
   CK(cudaMemsetAsync(d.rec_count, 0, 3 * sizeof(unsigned long long), c->stream));
   d.rec_capacity = 0;
+  {
+    // persistent neighbour-loop kernels: one resident wave of CTAs, one hit FIFO per warp
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, c->device));
+    int o0 = 0, o1 = 0, o2 = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o0, k_density<0>, kBlock, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, k_density<1>, kBlock, 0));
+    if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY)
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, k_force<SWIFT_CUDA_SCHEME_PLANETARY>, kBlock, 0));
+    else
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, k_force<SWIFT_CUDA_SCHEME_MINIMAL>, kBlock, 0));
+    const int sms = prop.multiProcessorCount;
+    auto grid_for = [&](int occ, int work_units) {
+      const int want = (work_units + kWarps - 1) / kWarps;
+      return std::max(1, std::min(want, sms * std::max(occ, 1)));
+    };
+    c->grid_density = grid_for(o0, d.n_units);
+    c->grid_redo = grid_for(o1, d.n_leaves);
+    c->grid_force = grid_for(o2, d.n_units);
+    const size_t qwarps = (size_t)std::max(c->grid_density, std::max(c->grid_redo, c->grid_force)) * kWarps;
+    if (dmalloc(c, &d.gq, qwarps * kQD * 32) || dmalloc(c, &d.work_ctr, (size_t)c->prm.max_smoothing_iterations + 2))
+      return 1;
+  }
   for (int k = 0; k < 3; k++) d.rec_pairs[k] = nullptr;
   if (upload_consts(c)) return 1;
   CK(cudaStreamSynchronize(c->stream));
@@ -439,6 +476,18 @@ static int launch_sort(swift_cuda_ctx *c) {
   return 0;
 }
 
+// bounding boxes of the cells' particles (positions may have moved since the tree was built)
+static int launch_cell_box(swift_cuda_ctx *c) {
+  Dev &d = c->dev;
+  if (d.ncells == 0) return 0;
+  k_cell_box_init<<<(d.ncells * 6 + 255) / 256, 256, 0, c->stream>>>(d);
+  k_cell_box<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d);
+  k_cell_box_finish<<<(d.ncells * 6 + 255) / 256, 256, 0, c->stream>>>(d);
+  c->counters.n_kernel_launches += 3;
+  CK(cudaGetLastError());
+  return 0;
+}
+
 static int launch_density(swift_cuda_ctx *c) {
   Dev &d = c->dev;
   const int nb = (int)((c->n + 255) / 256);
@@ -446,8 +495,10 @@ static int launch_density(swift_cuda_ctx *c) {
   CK(cudaMemsetAsync(d.redo_count, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
   CK(cudaMemcpyAsync(d.cell_hmax, d.cell_hmax_old, (size_t)d.ncells * sizeof(float), cudaMemcpyDeviceToDevice,
                      c->stream));
+  CK(cudaMemsetAsync(d.work_ctr, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
+  if (launch_cell_box(c)) return 1;
   k_init_step<<<nb, 256, 0, c->stream>>>(d);
-  if (d.n_units > 0) k_density<0><<<(d.n_units + kWarps - 1) / kWarps, kBlock, 0, c->stream>>>(d, 0);
+  if (d.n_units > 0) k_density<0><<<c->grid_density, kBlock, 0, c->stream>>>(d, 0);
   c->counters.n_kernel_launches += 2;
   CK(cudaGetLastError());
   // keep the raw first-pass sums for inspection (parity tests)
@@ -463,7 +514,7 @@ static int launch_ghost(swift_cuda_ctx *c) {
   // redo counter of the sweep before and leaves at once when nothing is pending.
   for (int sweep = 0; sweep < c->prm.max_smoothing_iterations; sweep++) {
     k_ghost<<<nb, 256, 0, c->stream>>>(d, sweep);
-    if (d.n_leaves > 0) k_density<1><<<(d.n_leaves + kWarps - 1) / kWarps, kBlock, 0, c->stream>>>(d, sweep);
+    if (d.n_leaves > 0) k_density<1><<<c->grid_redo, kBlock, 0, c->stream>>>(d, sweep);
     c->counters.n_kernel_launches += 2;
   }
   k_cell_hmax<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d);
@@ -475,8 +526,9 @@ static int launch_ghost(swift_cuda_ctx *c) {
 static int launch_force(swift_cuda_ctx *c) {
   Dev &d = c->dev;
   // runner_do_end_hydro_force is the epilogue of the force kernel
+  CK(cudaMemsetAsync(d.work_ctr + 1 + c->prm.max_smoothing_iterations, 0, sizeof(int), c->stream));
   if (d.n_units > 0) {
-    const int nb = (d.n_units + kWarps - 1) / kWarps;
+    const int nb = c->grid_force;
     if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY)
       k_force<SWIFT_CUDA_SCHEME_PLANETARY><<<nb, kBlock, 0, c->stream>>>(d);
     else
