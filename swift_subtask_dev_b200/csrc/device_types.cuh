@@ -42,6 +42,11 @@ struct CellDev {
   int pad;
 };
 
+struct __align__(8) SortEnt {
+  float d;
+  int32_t i;
+};
+
 // Everything a kernel needs, passed by value.
 struct Dev {
   int64_t n;
@@ -89,8 +94,7 @@ struct Dev {
   const int32_t *lane_part;    // [n_units*32] particle of each lane, or -1
   // sorts
   const int64_t *sort_lookup;  // [ncells*13]
-  float *sort_d;
-  int32_t *sort_i;
+  SortEnt *sort;           // struct sort_entry (src/sort_part.h:34-41): key d, index i inside the cell
   // persistent kernels: per-warp FIFO of deferred hits [n_qwarps][kQD][32], unit counters
   // [0] first density pass, [1 + sweep] redo sweeps, [1 + max_iter] force
   float4 *gq;

@@ -19,6 +19,13 @@ __constant__ Consts kc;
 
 constexpr int kWarps = 4;        // warps per CTA of the neighbour-loop kernels (each warp works alone)
 constexpr int kBlock = 32 * kWarps;
+// resident CTAs per SM the neighbour-loop kernels are compiled for (register cap = 65536 / (kBlock * n))
+#ifndef SWIFT_MINB_DENSITY
+#define SWIFT_MINB_DENSITY 4
+#endif
+#ifndef SWIFT_MINB_FORCE
+#define SWIFT_MINB_FORCE 4
+#endif
 constexpr int kNumTimeBins = 56;
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int kDpFlag = 0x40000000;  // queue entry: dx must be recomputed from the f64 positions
@@ -240,8 +247,10 @@ __global__ void __launch_bounds__(256) k_sort(Dev d, const int32_t *seg_cell, co
   const int64_t off = seg_off[seg];
   for (int k = threadIdx.x; k < n; k += blockDim.x) {
     const unsigned long long key = keys[k];
-    d.sort_d[off + k] = ordered_to_float((uint32_t)(key >> 32));
-    d.sort_i[off + k] = (int32_t)(key & 0xffffffffu);
+    SortEnt se;
+    se.d = ordered_to_float((uint32_t)(key >> 32));
+    se.i = (int32_t)(key & 0xffffffffu);
+    d.sort[off + k] = se;
   }
 }
 
@@ -387,9 +396,10 @@ __device__ __forceinline__ void stage_box(const float ulo[3], const float uhi[3]
                                           StageBox &b) {
 #pragma unroll
   for (int k = 0; k < 3; k++) {
-    const double m = 1e-6 * (fabs(ol[k]) + (double)fabsf(ulo[k]) + (double)fabsf(uhi[k])) + (double)slack;
-    b.lo[k] = __double2float_rd((double)ulo[k] + ol[k] - m);
-    b.hi[k] = __double2float_ru((double)uhi[k] + ol[k] + m);
+    const float o = (float)ol[k];
+    const float m = 2e-6f * (fabsf(o) + fabsf(ulo[k]) + fabsf(uhi[k])) + slack;
+    b.lo[k] = ulo[k] + o - m;
+    b.hi[k] = uhi[k] + o + m;
   }
 }
 // can a particle of cell cb (bounding box of its particles relative to its loc: bb[0..5]) lie in b?
@@ -398,9 +408,10 @@ __device__ __forceinline__ bool box_reaches_cell(const StageBox &b, const float 
   bool r = true;
 #pragma unroll
   for (int k = 0; k < 3; k++) {
-    const double lo = (double)bb[k] + og[k], hi = (double)bb[3 + k] + og[k];
-    const double m = 1e-6 * (fabs(og[k]) + fabs(lo) + fabs(hi));
-    r = r && ((double)b.hi[k] >= lo - m) && ((double)b.lo[k] <= hi + m);
+    const float o = (float)og[k];
+    const float lo = bb[k] + o, hi = bb[3 + k] + o;
+    const float m = 2e-6f * (fabsf(o) + fabsf(lo) + fabsf(hi));
+    r = r && (b.hi[k] >= lo - m) && (b.lo[k] <= hi + m);
   }
   return r;
 }
@@ -414,7 +425,7 @@ __device__ __forceinline__ bool box_reaches_cell(const StageBox &b, const float 
 //         flagged particles the warp first compacts into full groups of 32.
 // ---------------------------------------------------------------------------
 template <int MODE>
-__global__ void __launch_bounds__(kBlock) k_density(Dev d, int sweep) {
+__global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, int sweep) {
   if (MODE == 1 && d.redo_count[sweep] == 0) return;
   __shared__ WarpTile tiles[kWarps];
   WarpTile &ws = tiles[threadIdx.x >> 5];
@@ -497,33 +508,51 @@ __global__ void __launch_bounds__(kBlock) k_density(Dev d, int sweep) {
         }
       }
 
-      // one deferred hit -> runner_iact_nonsym_density
-      auto consume = [&](const float4 e) {
+      // one deferred hit -> runner_iact_nonsym_density; vmj (and the f64 position of j when the
+      // difference must be taken in f64) were gathered one round ahead
+      auto consume = [&](const float4 e, const float4 vmj, double xj, double yj, double zj) {
         const int w = __float_as_int(e.w);
-        const int j = w & (kDpFlag - 1);
         float dx, dy, dz;
         if (w & kDpFlag) {
           // e.xyz: periodic shift of the item in box lengths (-1, 0, 1)
-          dx = dsub_f(__dsub_rn(xi, __dmul_rn((double)e.x, d.dim[0])), d.x[j]);
-          dy = dsub_f(__dsub_rn(yi, __dmul_rn((double)e.y, d.dim[1])), d.y[j]);
-          dz = dsub_f(__dsub_rn(zi, __dmul_rn((double)e.z, d.dim[2])), d.z[j]);
+          dx = dsub_f(__dsub_rn(xi, __dmul_rn((double)e.x, d.dim[0])), xj);
+          dy = dsub_f(__dsub_rn(yi, __dmul_rn((double)e.y, d.dim[1])), yj);
+          dz = dsub_f(__dsub_rn(zi, __dmul_rn((double)e.z, d.dim[2])), zj);
         } else {
           dx = e.x; dy = e.y; dz = e.z;
         }
         const float r2 = dist2(dx, dy, dz);
         if (r2 < hig2) {
-          iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, d.vm[j]);
+          iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, vmj);
           nhits++;
-          if (rec) record_pair(d, MODE, idi, d.id[j]);
+          if (rec) record_pair(d, MODE, idi, d.id[w & (kDpFlag - 1)]);
         }
       };
+      // software pipeline over the FIFO: entry r+2 is being read, the gathers of entry r+1 are in
+      // flight, entry r is consumed
       auto drain_all = [&]() {
         const int m = __reduce_max_sync(kFull, qcnt);
-        float4 e = qcnt > 0 ? gq[0] : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        auto gather = [&](const float4 e, bool ok, float4 &v, double &x, double &y, double &z) {
+          if (ok) {
+            const int w = __float_as_int(e.w);
+            const int j = w & (kDpFlag - 1);
+            v = d.vm[j];
+            if (w & kDpFlag) { x = d.x[j]; y = d.y[j]; z = d.z[j]; }
+          }
+        };
+        float4 e0 = qcnt > 0 ? gq[0] : z4;
+        float4 e1 = qcnt > 1 ? gq[32] : z4;
+        float4 v0 = z4;
+        double x0 = 0.0, y0 = 0.0, z0 = 0.0;
+        gather(e0, qcnt > 0, v0, x0, y0, z0);
         for (int r = 0; r < m; r++) {
-          const float4 en = (r + 1 < qcnt) ? gq[(r + 1) * 32] : make_float4(0.f, 0.f, 0.f, 0.f);
-          if (r < qcnt) consume(e);
-          e = en;
+          const float4 e2 = (r + 2 < qcnt) ? gq[(r + 2) * 32] : z4;
+          float4 v1 = z4;
+          double x1 = 0.0, y1 = 0.0, z1 = 0.0;
+          gather(e1, r + 1 < qcnt, v1, x1, y1, z1);
+          if (r < qcnt) consume(e0, v0, x0, y0, z0);
+          e0 = e1; e1 = e2; v0 = v1; x0 = x1; y0 = y1; z0 = z1;
         }
         qcnt = 0;
       };
@@ -590,7 +619,7 @@ __global__ void __launch_bounds__(kBlock) k_density(Dev d, int sweep) {
           if (mine) {
             const double rshift = item_rshift(sh, sid);
             const float d_me = sort_key(xi, yi, zi, sid);
-            const double dj_min = (double)d.sort_d[segB];
+            const double dj_min = (double)d.sort[segB].d;
             const double hi_max = __dsub_rn((double)__fmul_rn(d.cell_hmax[item.own], kc.gamma), rshift);
             const double di = __dsub_rn((double)__fadd_rn(d_me, hig), rshift);
             if ((__dadd_rn((double)d_me, hi_max) > dj_min) && !(di < dj_min)) { lo = -INFINITY; hi_cut = thr_lt(di); }
@@ -600,7 +629,7 @@ __global__ void __launch_bounds__(kBlock) k_density(Dev d, int sweep) {
           if (mine) {
             const double rshift = item_rshift(sh, sid);
             const float d_me = sort_key(xi, yi, zi, sid);
-            const double di_max = __dsub_rn((double)d.sort_d[segB + cB.count - 1], rshift);
+            const double di_max = __dsub_rn((double)d.sort[segB + cB.count - 1].d, rshift);
             const double hj_max = (double)__fmul_rn(d.cell_hmax[item.own], kc.gamma);
             const double dj = __dadd_rn((double)__fsub_rn(d_me, hig), rshift);
             if ((__dsub_rn((double)d_me, hj_max) < di_max) && !(__dsub_rn(dj, rshift) > di_max)) {
@@ -650,21 +679,27 @@ __global__ void __launch_bounds__(kBlock) k_density(Dev d, int sweep) {
 
         int st = 0, ntile = 0, base = 0;
         bool done = false;
+        // this lane's sort entry of a staging round, read one round ahead
+        auto load_se = [&](int b) {
+          SortEnt se;
+          se.d = 0.f;
+          se.i = b + lane;  // unsorted: index order
+          if (sorted && b + lane < cB.count) se = d.sort[segB + (desc ? (cB.count - 1 - b - lane) : (b + lane))];
+          return se;
+        };
+        SortEnt se_next = load_se(0);
         while (true) {
           if (base < cB.count) {
             const int nt = min(32, cB.count - base);
-            float dk = 0.f;
-            int j = 0;
+            const SortEnt se = se_next;
+            if (base + 32 < cB.count) se_next = load_se(base + 32);
+            const float dk = se.d;
+            const int j = cB.first + se.i;
             bool keep = lane < nt;
             if (sorted) {
-              const int e = desc ? (cB.count - 1 - base - lane) : (base + lane);
-              if (keep) dk = d.sort_d[segB + e];
               const float k0 = __shfl_sync(kFull, dk, 0);
               if (desc ? !(k0 >= wlo) : !(k0 <= whi)) done = true;  // sorted axis: nothing further on can hit
               keep = keep && !done && dk >= wlo && dk <= whi;
-              if (keep) j = cB.first + d.sort_i[segB + e];
-            } else {
-              j = cB.first + base + lane;
             }
             float4 c = make_float4(qnan, qnan, qnan, qnan);
             if (keep) {
@@ -1024,7 +1059,7 @@ struct ForceTile {
 };
 
 template <int SCHEME>
-__global__ void __launch_bounds__(kBlock) k_force(Dev d) {
+__global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
   __shared__ ForceTile tiles[kWarps];
   ForceTile &ws = tiles[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
@@ -1095,14 +1130,15 @@ __global__ void __launch_bounds__(kBlock) k_force(Dev d) {
       }
     }
 
-    auto consume = [&](const float4 e) {
+    // one deferred hit -> runner_iact_nonsym_force; the three float4 of j (and its f64 position for
+    // an own-cell pair) were gathered one round ahead
+    auto consume = [&](const float4 e, const float4 hbj, const float4 vmj, const float4 fj, double xj, double yj,
+                       double zj) {
       const int w = __float_as_int(e.w);
-      const int j = w & (kDpFlag - 1);
-      const float4 hbj = d.hb[j];
       float dx, dy, dz;
       bool hit = true;
       if (w & kDpFlag) {  // own cell: f64 position difference (:2349-2353, 2416-2420)
-        dx = dsub_f(xi, d.x[j]); dy = dsub_f(yi, d.y[j]); dz = dsub_f(zi, d.z[j]);
+        dx = dsub_f(xi, xj); dy = dsub_f(yi, yj); dz = dsub_f(zi, zj);
         const float r2e = dist2(dx, dy, dz);
         hit = (r2e < hig2) || (r2e < sq_gamma2(hbj.x));
       } else {
@@ -1110,24 +1146,42 @@ __global__ void __launch_bounds__(kBlock) k_force(Dev d) {
       }
       if (hit) {
         const float r2 = dist2(dx, dy, dz);
-        const float4 vmj = d.vm[j];
-        const float4 fj = d.fin[j];
         ForceJ pj;
         pj.h = hbj.x; pj.bal = hbj.y; pj.bin = __float_as_int(hbj.z); pj.Pr2 = hbj.w;
         pj.m = vmj.w; pj.vx = vmj.x; pj.vy = vmj.y; pj.vz = vmj.z;
         pj.rho = fj.x; pj.P = fj.y; pj.f = fj.z; pj.c = fj.w;
         iact_force<SCHEME>(acc, r2, dx, dy, dz, me, pj);
         nhits++;
-        if (rec) record_pair(d, 2, idi, d.id[j]);
+        if (rec) record_pair(d, 2, idi, d.id[w & (kDpFlag - 1)]);
       }
     };
+    // software pipeline over the FIFO: entry r+2 is being read, the gathers of entry r+1 are in
+    // flight, entry r is consumed
     auto drain_all = [&]() {
       const int m = __reduce_max_sync(kFull, qcnt);
-      float4 e = qcnt > 0 ? gq[0] : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      auto gather = [&](const float4 e, bool ok, float4 &hb, float4 &v, float4 &f, double &x, double &y, double &z) {
+        if (ok) {
+          const int w = __float_as_int(e.w);
+          const int j = w & (kDpFlag - 1);
+          hb = d.hb[j];
+          v = d.vm[j];
+          f = d.fin[j];
+          if (w & kDpFlag) { x = d.x[j]; y = d.y[j]; z = d.z[j]; }
+        }
+      };
+      float4 e0 = qcnt > 0 ? gq[0] : z4;
+      float4 e1 = qcnt > 1 ? gq[32] : z4;
+      float4 hb0 = z4, v0 = z4, f0 = z4;
+      double x0 = 0.0, y0 = 0.0, z0 = 0.0;
+      gather(e0, qcnt > 0, hb0, v0, f0, x0, y0, z0);
       for (int r = 0; r < m; r++) {
-        const float4 en = (r + 1 < qcnt) ? gq[(r + 1) * 32] : make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < qcnt) consume(e);
-        e = en;
+        const float4 e2 = (r + 2 < qcnt) ? gq[(r + 2) * 32] : z4;
+        float4 hb1 = z4, v1 = z4, f1 = z4;
+        double x1 = 0.0, y1 = 0.0, z1 = 0.0;
+        gather(e1, r + 1 < qcnt, hb1, v1, f1, x1, y1, z1);
+        if (r < qcnt) consume(e0, hb0, v0, f0, x0, y0, z0);
+        e0 = e1; e1 = e2; hb0 = hb1; v0 = v1; f0 = f1; x0 = x1; y0 = y1; z0 = z1;
       }
       qcnt = 0;
     };
@@ -1188,8 +1242,8 @@ __global__ void __launch_bounds__(kBlock) k_force(Dev d) {
         rshift = item_rshift(sh, sid);
         const float d_me = sort_key(xi, yi, zi, sid);
         // constants of the pair, as the reference forms them (f64)
-        dj_min = (double)d.sort_d[left ? segB : segA];                                            // first of cj
-        const double di_max = (double)d.sort_d[left ? (segA + cA.count - 1) : (segB + cB.count - 1)];  // last of ci
+        dj_min = (double)d.sort[left ? segB : segA].d;                                            // first of cj
+        const double di_max = (double)d.sort[left ? (segA + cA.count - 1) : (segB + cB.count - 1)].d;  // last of ci
         hi_max_g = __dmul_rn((double)(left ? hmaxA : hmaxB), (double)kc.gamma);
         hj_max_g = __dmul_rn((double)(left ? hmaxB : hmaxA), (double)kc.gamma);
         rhs2 = __dsub_rn(di_max, rshift);
@@ -1273,21 +1327,27 @@ __global__ void __launch_bounds__(kBlock) k_force(Dev d) {
 
         int st = 0, ntile = 0, base = 0;
         bool done = false;
+        // this lane's sort entry of a staging round, read one round ahead
+        auto load_se = [&](int b) {
+          SortEnt se;
+          se.d = 0.f;
+          se.i = b + lane;  // own cell: index order
+          if (!self && b + lane < cB.count) se = d.sort[segB + (left ? (b + lane) : (cB.count - 1 - b - lane))];
+          return se;
+        };
+        SortEnt se_next = load_se(0);
         while (true) {
           if (base < cB.count) {
             const int nt = min(32, cB.count - base);
-            float dk = 0.f;
-            int j = 0;
+            const SortEnt se = se_next;
+            if (base + 32 < cB.count) se_next = load_se(base + 32);
+            const float dk = se.d;
+            const int j = cB.first + se.i;
             bool keep = lane < nt;
-            if (self) {
-              j = cB.first + base + lane;
-            } else {
-              const int e = left ? (base + lane) : (cB.count - 1 - base - lane);
-              if (keep) dk = d.sort_d[segB + e];
+            if (!self) {
               const float k0 = __shfl_sync(kFull, dk, 0);
               if (left ? !(k0 <= wlim) : !(k0 >= wlim)) done = true;  // sorted axis: nothing further on can hit
               keep = keep && !done && (left ? (dk <= wlim) : (dk >= wlim));
-              if (keep) j = cB.first + d.sort_i[segB + e];
             }
             float4 c = make_float4(qnan, qnan, qnan, qnan);
             float4 a = make_float4(0.f, INFINITY, -INFINITY, 0.f);

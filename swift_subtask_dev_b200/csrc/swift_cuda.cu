@@ -288,7 +288,7 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
     return 1;
   d.leaves = dlv; d.item_begin = dib; d.items = dit; d.redo_begin = drb; d.redo_items = drt;
   d.unit_leaf = dul; d.unit_begin = duo; d.lane_part = dlp; d.sort_lookup = dsl;
-  if (dmalloc(c, &d.sort_d, (size_t)wl.n_sort_entries) || dmalloc(c, &d.sort_i, (size_t)wl.n_sort_entries)) return 1;
+  if (dmalloc(c, &d.sort, (size_t)wl.n_sort_entries)) return 1;
   c->n_seg = (int)wl.sort_cells.size();
   std::vector<int64_t> scratch_off(c->n_seg, 0);
   int64_t scratch_total = 0;
