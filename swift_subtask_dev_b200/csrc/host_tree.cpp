@@ -667,13 +667,36 @@ void build_worklists(const swift_cuda_params &prm, const Tree &tree, const std::
 }
 
 namespace {
-inline uint32_t spread3(uint32_t v) {  // 10 bits -> every third bit
-  v &= 0x3ff;
-  v = (v | (v << 16)) & 0x030000ff;
-  v = (v | (v << 8)) & 0x0300f00f;
-  v = (v | (v << 4)) & 0x030c30c3;
-  v = (v | (v << 2)) & 0x09249249;
-  return v;
+struct LanePoint {
+  float p[3];
+  int32_t slot;
+};
+// Deals n particles out to `nunits` warp units (32 lanes each) by recursive bisection along the
+// longest axis of their bounding box: every unit is a compact box of ~n / nunits particles, so the
+// candidates one unit has to look at are few (the unit's box grown by the search radius).
+void split_units(LanePoint *a, int n, int nunits, int32_t *dst) {
+  if (nunits == 1) {
+    for (int k = 0; k < n; k++) dst[k] = a[k].slot;
+    return;
+  }
+  const int ul = nunits / 2, ur = nunits - ul;
+  int nl = (int)((int64_t)n * ul / nunits);
+  nl = std::max(nl, n - 32 * ur);
+  nl = std::min(nl, 32 * ul);
+  float lo[3] = {a[0].p[0], a[0].p[1], a[0].p[2]}, hi[3] = {a[0].p[0], a[0].p[1], a[0].p[2]};
+  for (int k = 1; k < n; k++)
+    for (int d = 0; d < 3; d++) {
+      lo[d] = std::min(lo[d], a[k].p[d]);
+      hi[d] = std::max(hi[d], a[k].p[d]);
+    }
+  int ax = 0;
+  for (int d = 1; d < 3; d++)
+    if (hi[d] - lo[d] > hi[ax] - lo[ax]) ax = d;
+  std::nth_element(a, a + nl, a + n, [ax](const LanePoint &u, const LanePoint &v) {
+    return u.p[ax] < v.p[ax] || (u.p[ax] == v.p[ax] && u.slot < v.slot);
+  });
+  split_units(a, nl, ul, dst);
+  split_units(a + nl, n - nl, ur, dst + (size_t)ul * 32);
 }
 }  // namespace
 
@@ -682,24 +705,19 @@ void assign_lanes(const Tree &tree, const double *x, WorkLists &wl) {
   wl.lane_part.assign(wl.unit_leaf.size() * 32, -1);
   const std::vector<int32_t> &ord = tree.order;
   auto work = [&](size_t t, size_t nt) {
-    std::vector<std::pair<uint32_t, int32_t>> keys;
+    std::vector<LanePoint> pts;
     for (size_t s = t; s < nl; s += nt) {
       const swift_cuda_cell &cell = tree.cells[wl.leaves[s]];
-      keys.resize(cell.count);
+      if (cell.count == 0) continue;
+      pts.resize(cell.count);
       for (int k = 0; k < cell.count; k++) {
         const int64_t slot = (int64_t)cell.first + k;
         const int64_t src = ord.empty() ? slot : ord[slot];
-        uint32_t q[3];
-        for (int d = 0; d < 3; d++) {
-          double u = (x[3 * src + d] - cell.loc[d]) / cell.width[d];
-          u = u < 0.0 ? 0.0 : (u > 0.999999 ? 0.999999 : u);
-          q[d] = (uint32_t)(u * 1024.0);
-        }
-        keys[k] = {(spread3(q[0]) << 2) | (spread3(q[1]) << 1) | spread3(q[2]), (int32_t)slot};
+        for (int d = 0; d < 3; d++) pts[k].p[d] = (float)(x[3 * src + d] - cell.loc[d]);
+        pts[k].slot = (int32_t)slot;
       }
-      std::sort(keys.begin(), keys.end());
-      int32_t *dst = &wl.lane_part[(size_t)wl.unit_begin[s] * 32];
-      for (int k = 0; k < cell.count; k++) dst[k] = keys[k].second;
+      const int nunits = wl.unit_begin[s + 1] - wl.unit_begin[s];
+      split_units(pts.data(), cell.count, nunits, &wl.lane_part[(size_t)wl.unit_begin[s] * 32]);
     }
   };
   const size_t nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));

@@ -514,10 +514,15 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
         const int w = __float_as_int(e.w);
         float dx, dy, dz;
         if (w & kDpFlag) {
-          // e.xyz: periodic shift of the item in box lengths (-1, 0, 1)
-          dx = dsub_f(__dsub_rn(xi, __dmul_rn((double)e.x, d.dim[0])), xj);
-          dy = dsub_f(__dsub_rn(yi, __dmul_rn((double)e.y, d.dim[1])), yj);
-          dz = dsub_f(__dsub_rn(zi, __dmul_rn((double)e.z, d.dim[2])), zj);
+          if (MODE == 0) {
+            // own cell (DOSELF1): no periodic shift
+            dx = dsub_f(xi, xj); dy = dsub_f(yi, yj); dz = dsub_f(zi, zj);
+          } else {
+            // e.xyz: periodic shift of the item in box lengths (-1, 0, 1)
+            dx = dsub_f(__dsub_rn(xi, __dmul_rn((double)e.x, d.dim[0])), xj);
+            dy = dsub_f(__dsub_rn(yi, __dmul_rn((double)e.y, d.dim[1])), yj);
+            dz = dsub_f(__dsub_rn(zi, __dmul_rn((double)e.z, d.dim[2])), zj);
+          }
         } else {
           dx = e.x; dy = e.y; dz = e.z;
         }
@@ -655,26 +660,34 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
         if (!(wlo <= whi)) continue;  // no lane takes part
         const float pfx = dsub_f(px, fl[0]), pfy = dsub_f(py, fl[1]), pfz = dsub_f(pz, fl[2]);
 
-        // every lane against the staged candidates [st, st + n) of the ring; n a multiple of 4
+        // every lane against the staged candidates [st, st + n) of the ring (st is 0 or 32: no wrap);
+        // n a multiple of 4.  The distance is formed with FMAs and compared with a threshold a few ulp
+        // wider: the exact r2 < h^2 gamma^2 of the reference is redone when the hit is consumed.
+        const float thr_c = thr * 1.000001f;
+        const int flagbits = dp ? kDpFlag : 0;
         auto test = [&](int st, int n) {
           if (__any_sync(kFull, qcnt > kQD - n)) drain_all();
+          const float4 *__restrict__ tp = ws.pos + st;
+          const int *__restrict__ ti = ws.idx + st;
+          float4 *qp = gq + qcnt * 32;
           for (int k0 = 0; k0 < n; k0 += 4) {
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-              const int k = (st + k0 + u) & (kTile - 1);
-              const float4 c = ws.pos[k];
+              const float4 c = tp[k0 + u];
               const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
-              const float r2 = dist2(dx, dy, dz);
-              if (c.w >= lo && c.w <= hi_cut && r2 < thr) {
-                const int j = ws.idx[k];
+              const float r2c = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+              if (c.w >= lo && c.w <= hi_cut && r2c < thr_c) {
+                const int j = ti[k0 + u];
                 if (j != pp) {
-                  gq[qcnt * 32] = dp ? make_float4(shf[0], shf[1], shf[2], __int_as_float(j | kDpFlag))
-                                     : make_float4(dx, dy, dz, __int_as_float(j));
-                  qcnt++;
+                  if (MODE == 0) *qp = make_float4(dx, dy, dz, __int_as_float(j | flagbits));
+                  else *qp = dp ? make_float4(shf[0], shf[1], shf[2], __int_as_float(j | kDpFlag))
+                                : make_float4(dx, dy, dz, __int_as_float(j));
+                  qp += 32;
                 }
               }
             }
           }
+          qcnt = (int)(qp - gq) >> 5;
         };
 
         int st = 0, ntile = 0, base = 0;
@@ -1287,20 +1300,23 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
 
         auto test = [&](int st, int n) {
           if (__any_sync(kFull, qcnt > kQD - n - kSide)) drain_all();
+          const float4 *__restrict__ tp = ws.pos + st;  // st is 0 or 32: no wrap inside a tile
+          const float4 *__restrict__ ta = ws.aux + st;
+          const int *__restrict__ ti = ws.idx + st;
+          float4 *qp = gq + qcnt * 32;
           for (int k0 = 0; k0 < n; k0 += 4) {
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-              const int k = (st + k0 + u) & (kTile - 1);
-              const float4 c = ws.pos[k];
-              const float4 a = ws.aux[k];
+              const float4 c = tp[k0 + u];
+              const float4 a = ta[k0 + u];
               const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
               const float r2 = dist2(dx, dy, dz);
               if (self) {
                 if (r2 < thr_i || (mine && r2 < a.x)) {
-                  const int j = ws.idx[k];
+                  const int j = ti[k0 + u];
                   if (j != pp) {
-                    gq[qcnt * 32] = make_float4(0.f, 0.f, 0.f, __int_as_float(j | kDpFlag));
-                    qcnt++;
+                    *qp = make_float4(0.f, 0.f, 0.f, __int_as_float(j | kDpFlag));
+                    qp += 32;
                   }
                 }
               } else {
@@ -1313,16 +1329,17 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
                   h2 = c.w >= cut2 && r2 < hig2 && r2 >= a.x;
                 }
                 if (pass == 0 ? h1 : h2) {
-                  gq[qcnt * 32] = make_float4(dx, dy, dz, __int_as_float(ws.idx[k]));
-                  qcnt++;
+                  *qp = make_float4(dx, dy, dz, __int_as_float(ti[k0 + u]));
+                  qp += 32;
                 } else if (pass == 0 && h2) {
-                  if (scnt < kSide) ws.side[scnt][lane] = make_float4(dx, dy, dz, __int_as_float(ws.idx[k]));
+                  if (scnt < kSide) ws.side[scnt][lane] = make_float4(dx, dy, dz, __int_as_float(ti[k0 + u]));
                   else sovf = true;
                   scnt++;
                 }
               }
             }
           }
+          qcnt = (int)(qp - gq) >> 5;
         };
 
         int st = 0, ntile = 0, base = 0;
