@@ -199,7 +199,7 @@ __device__ __forceinline__ unsigned long long block_sum(unsigned long long v) {
 // (order-preserving key bits << 32 | local index) in shared memory, or in a
 // global scratch area for cells above kSortSmem particles.
 // ---------------------------------------------------------------------------
-constexpr int kSortSmem = 4096;
+constexpr int kSortSmem = 1024;
 
 __device__ __forceinline__ uint32_t float_to_ordered(float f) {
   const uint32_t b = __float_as_uint(f);
@@ -219,6 +219,38 @@ __global__ void __launch_bounds__(256) k_sort(Dev d, const int32_t *seg_cell, co
   const int n = c.count;
   int npad = 1;
   while (npad < n) npad <<= 1;
+  if (npad <= 256) {
+    // The common case (a leaf of <= 256 particles): one element per thread, compare-exchange
+    // through warp shuffles for strides < 32 and through shared memory only for strides >= 32
+    // (6 of the 36 stages), so almost no block-wide barriers.
+    const int t = threadIdx.x;
+    unsigned long long key = ~0ULL;
+    if (t < n) {
+      const int64_t p = c.first + t;
+      key = ((unsigned long long)float_to_ordered(sort_key(d.x[p], d.y[p], d.z[p], sid)) << 32) | (unsigned)t;
+    }
+    for (int size = 2; size <= npad; size <<= 1)
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        unsigned long long other;
+        if (stride >= 32) {
+          __syncthreads();
+          skeys[t] = key;
+          __syncthreads();
+          other = skeys[t ^ stride];
+        } else {
+          other = __shfl_xor_sync(0xffffffffu, key, stride);
+        }
+        const bool up = (t & size) == 0, lower = (t & stride) == 0;
+        key = (lower == up) ? (key < other ? key : other) : (key < other ? other : key);
+      }
+    if (t < n) {
+      SortEnt se;
+      se.d = ordered_to_float((uint32_t)(key >> 32));
+      se.i = (int32_t)(key & 0xffffffffu);
+      d.sort[seg_off[seg] + t] = se;
+    }
+    return;
+  }
   unsigned long long *keys = (npad <= kSortSmem) ? skeys : (scratch + scratch_off[seg]);
   for (int k = threadIdx.x; k < npad; k += blockDim.x) {
     unsigned long long key = ~0ULL;
