@@ -4,8 +4,8 @@
 metric : ordered SPH pair interactions per second over one density+ghost+force
          step, whole job.
 value  : device-timed, particles resident in HBM (CUDA events around the step).
-e2e    : the same step through the public C ABI with HOST buffers: H2D of the
-         step's particle state and D2H of its results inside the timed region.
+e2e    : the same step through the public C ABI with HOST buffers (swift_cuda_step_io):
+         H2D of the step's particle state and D2H of its results inside the timed region.
 --impl reference : the reference's own CPU operators (oracle/_ref, compiled from
          /root/reference; the plain-C oracle port when that is absent) on all
          host cores, on bounded samples of the same workload.
@@ -231,9 +231,7 @@ def main():
     out_pin = be.alloc_results(pinned=True)
     for k in range(max(1, min(args.steps, 2)) + 1):
         t0 = time.perf_counter()
-        be.update_particles(ic_pin)
-        be.step()
-        be.results(out=out_pin)
+        be.step_io(ic_pin, out_pin)   # upload + sort + density + ghost + force + download, one C-ABI call
         dt = time.perf_counter() - t0
         if k > 0:
             e2e_times.append(dt)

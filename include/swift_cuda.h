@@ -182,6 +182,14 @@ int swift_cuda_restore_particles(swift_cuda_ctx *ctx);
 enum { SWIFT_CUDA_STEP_SORT = 1, SWIFT_CUDA_STEP_RESTORE = 2 };
 int swift_cuda_step(swift_cuda_ctx *ctx, int flags);
 
+/* swift_cuda_update_particles + swift_cuda_step + swift_cuda_get_results as ONE call, with the
+ * transfers overlapped with the kernels (host buffers should be page-locked for that): the
+ * positions are uploaded first and the sorts start while v, m, h, u are still on the bus; what
+ * the ghost leaves (h, rho, P, c, f, balsara) is copied out while the force loop runs.  Same
+ * results, bit for bit, as the three separate calls. */
+int swift_cuda_step_io(swift_cuda_ctx *ctx, const swift_cuda_parts_in *parts, int flags,
+                       const swift_cuda_parts_out *out);
+
 /* Operator-level entry points (same phases, separately callable; used by the
  * per-task shims and the parity tests). */
 int swift_cuda_do_sort(swift_cuda_ctx *ctx);

@@ -99,7 +99,7 @@ class Timings(C.Structure):
 EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error", "swift_cuda_create", "swift_cuda_destroy",
            "swift_cuda_build_from_particles", "swift_cuda_build_from_cells", "swift_cuda_update_particles",
            "swift_cuda_restore_particles",
-           "swift_cuda_step", "swift_cuda_do_sort", "swift_cuda_do_density", "swift_cuda_do_ghost",
+           "swift_cuda_step", "swift_cuda_step_io", "swift_cuda_do_sort", "swift_cuda_do_density", "swift_cuda_do_ghost",
            "swift_cuda_do_force", "swift_cuda_get_results", "swift_cuda_get_counters", "swift_cuda_get_timings",
            "swift_cuda_measure_fp32_peak",
            "swift_cuda_get_tree_size", "swift_cuda_get_tree", "swift_cuda_record_pairs", "swift_cuda_fetch_pairs",
@@ -261,6 +261,18 @@ class HydroBackend:
     def step(self, do_sort=True, restore=False):
         """sort -> density -> ghost -> force -> end_force.  restore: start from the h of the last build/update."""
         self._check(self.lib.swift_cuda_step(self.ctx, (1 if do_sort else 0) | (2 if restore else 0)))
+
+    def step_io(self, ic, out, do_sort=True):
+        """update_particles + step + results as one call, transfers overlapped with the kernels
+        (swift_cuda_step_io); `ic` and `out` should live in page-locked host memory."""
+        P, keep = self._parts_in(ic)
+        O = PartsOut()
+        for k, w in OUT_FIELDS + OUT_FIRST:
+            if k in out:
+                setattr(O, k, out[k].ctypes.data_as(_FP))
+        O.min_ngb_time_bin = out["min_ngb_time_bin"].ctypes.data_as(C.POINTER(C.c_int8))
+        self._check(self.lib.swift_cuda_step_io(self.ctx, C.byref(P), 1 if do_sort else 0, C.byref(O)))
+        return out
 
     def measure_fp32_peak(self):
         self.lib.swift_cuda_measure_fp32_peak.restype = C.c_double

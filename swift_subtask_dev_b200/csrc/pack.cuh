@@ -39,13 +39,18 @@ struct PackDst {  // mutable views of the Dev arrays k_pack fills
   int64_t *id;
 };
 
-__global__ void k_pack(int64_t n, RawIn in, PackDst o, int with_static) {
+// what: 1 = positions, 2 = everything else, 3 = both (the overlapped step uploads and packs the
+// positions first so that the sorts can start while the other fields are still on the bus)
+__global__ void k_pack(int64_t n, RawIn in, PackDst o, int with_static, int what) {
   const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (k >= n) return;
   const int64_t s = in.order ? in.order[k] : k;
-  o.x[k] = in.x[3 * s];
-  o.y[k] = in.x[3 * s + 1];
-  o.z[k] = in.x[3 * s + 2];
+  if (what & 1) {
+    o.x[k] = in.x[3 * s];
+    o.y[k] = in.x[3 * s + 1];
+    o.z[k] = in.x[3 * s + 2];
+  }
+  if (!(what & 2)) return;
   o.vm[k] = make_float4(in.v[3 * s], in.v[3 * s + 1], in.v[3 * s + 2], in.mass[s]);
   const float h = in.h[s];
   o.h[k] = h;

@@ -28,6 +28,8 @@ struct swift_cuda_ctx {
   swift_cuda_params prm;
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t io = nullptr;      // copy stream of swift_cuda_step_io
+  cudaEvent_t io_ev[4] = {};
   cudaEvent_t ev[6] = {};
   Tree tree;
   WorkLists wl;
@@ -107,6 +109,8 @@ int swift_cuda_create(const swift_cuda_params *params, int device, swift_cuda_ct
   c->device = device;
   CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   for (auto &e : c->ev) CK(cudaEventCreate(&e));
+  CK(cudaStreamCreateWithFlags(&c->io, cudaStreamNonBlocking));
+  for (auto &e : c->io_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   std::memset(&c->dev, 0, sizeof(Dev));
   *out = c;
   return 0;
@@ -119,6 +123,9 @@ void swift_cuda_destroy(swift_cuda_ctx *c) {
   for (auto &e : c->ev)
     if (e) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
+  for (auto &e : c->io_ev)
+    if (e) cudaEventDestroy(e);
+  if (c->io) cudaStreamDestroy(c->io);
   delete c;
 }
 
@@ -202,7 +209,7 @@ static int upload_and_pack(swift_cuda_ctx *c, const swift_cuda_parts_in *in, boo
   o.time_bin = const_cast<int8_t *>(d.time_bin);
   o.mat_id = const_cast<int32_t *>(d.mat_id);
   o.id = const_cast<int64_t *>(d.id);
-  if (n > 0) k_pack<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, r, o, with_static ? 1 : 0);
+  if (n > 0) k_pack<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, r, o, with_static ? 1 : 0, 3);
   CK(cudaGetLastError());
   return 0;
 }
@@ -618,37 +625,128 @@ int swift_cuda_step(swift_cuda_ctx *c, int flags) {
 }
 
 // ---- results ---------------------------------------------------------------
-int swift_cuda_get_results(swift_cuda_ctx *c, const swift_cuda_parts_out *out) {
-  NEED_BUILT(c);
-  if (!out) return fail("get_results: null argument");
+// K7 for a subset of the fields: scatter to caller order on the device (stream `ks`), then one
+// copy per requested field on stream `cs` (after event `ready` when the streams differ).
+// which: 1 = what the ghost leaves (h, rho, P, c, f, balsara, first-pass sums), 2 = what the force
+// loop leaves (a, u_dt, h_dt, v_sig, min_ngb_time_bin).
+static int enqueue_results(swift_cuda_ctx *c, const swift_cuda_parts_out *out, int which, cudaStream_t ks,
+                           cudaStream_t cs, cudaEvent_t ready) {
   const int64_t n = c->n;
   Dev &d = c->dev;
   if (!c->s_out) {
     if (dmalloc(c, &c->s_out, (size_t)n * 20) || dmalloc(c, &c->s_out_bin, (size_t)n)) return 1;
   }
-  // K7: scatter to caller order on the device, then one copy per requested field
-  struct Field { float *host; int width; float **dev; };
+  struct Field { float *host; int width; float **dev; int phase; };
   RawOut r;
   std::memset(&r, 0, sizeof(r));
-  Field fields[] = {{out->h, 1, &r.h}, {out->rho, 1, &r.rho}, {out->pressure, 1, &r.pressure},
-                    {out->soundspeed, 1, &r.soundspeed}, {out->f, 1, &r.f}, {out->balsara, 1, &r.balsara},
-                    {out->a, 3, &r.a}, {out->u_dt, 1, &r.u_dt}, {out->h_dt, 1, &r.h_dt}, {out->v_sig, 1, &r.v_sig},
-                    {out->d_rho, 1, &r.d_rho}, {out->d_rho_dh, 1, &r.d_rho_dh}, {out->d_wcount, 1, &r.d_wcount},
-                    {out->d_wcount_dh, 1, &r.d_wcount_dh}, {out->d_div_v, 1, &r.d_div_v}, {out->d_rot_v, 3, &r.d_rot_v}};
+  Field fields[] = {{out->h, 1, &r.h, 1}, {out->rho, 1, &r.rho, 1}, {out->pressure, 1, &r.pressure, 1},
+                    {out->soundspeed, 1, &r.soundspeed, 1}, {out->f, 1, &r.f, 1}, {out->balsara, 1, &r.balsara, 1},
+                    {out->a, 3, &r.a, 2}, {out->u_dt, 1, &r.u_dt, 2}, {out->h_dt, 1, &r.h_dt, 2},
+                    {out->v_sig, 1, &r.v_sig, 2},
+                    {out->d_rho, 1, &r.d_rho, 1}, {out->d_rho_dh, 1, &r.d_rho_dh, 1}, {out->d_wcount, 1, &r.d_wcount, 1},
+                    {out->d_wcount_dh, 1, &r.d_wcount_dh, 1}, {out->d_div_v, 1, &r.d_div_v, 1},
+                    {out->d_rot_v, 3, &r.d_rot_v, 1}};
   int64_t off = 0;
   for (Field &f : fields) {
-    if (f.host) *f.dev = c->s_out + off;
+    if (f.host && (f.phase & which)) *f.dev = c->s_out + off;
     off += (int64_t)f.width * n;
   }
-  if (out->min_ngb_time_bin) r.min_bin = c->s_out_bin;
+  const bool bin = out->min_ngb_time_bin && (which & 2);
+  if (bin) r.min_bin = c->s_out_bin;
   r.order = c->tree.order.empty() ? nullptr : c->s_order;
-  if (n > 0) k_unpack<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(d, r, c->d_dens0_first, c->d_dens1_first);
+  if (n > 0) k_unpack<<<(unsigned)((n + 255) / 256), 256, 0, ks>>>(d, r, c->d_dens0_first, c->d_dens1_first);
   CK(cudaGetLastError());
+  if (cs != ks) {
+    CK(cudaEventRecord(ready, ks));
+    CK(cudaStreamWaitEvent(cs, ready, 0));
+  }
   for (Field &f : fields)
-    if (f.host) CK(cudaMemcpyAsync(f.host, *f.dev, (size_t)f.width * n * 4, cudaMemcpyDeviceToHost, c->stream));
-  if (out->min_ngb_time_bin)
-    CK(cudaMemcpyAsync(out->min_ngb_time_bin, c->s_out_bin, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    if (f.host && (f.phase & which))
+      CK(cudaMemcpyAsync(f.host, *f.dev, (size_t)f.width * n * 4, cudaMemcpyDeviceToHost, cs));
+  if (bin) CK(cudaMemcpyAsync(out->min_ngb_time_bin, c->s_out_bin, (size_t)n, cudaMemcpyDeviceToHost, cs));
+  return 0;
+}
+
+int swift_cuda_get_results(swift_cuda_ctx *c, const swift_cuda_parts_out *out) {
+  NEED_BUILT(c);
+  if (!out) return fail("get_results: null argument");
+  if (enqueue_results(c, out, 3, c->stream, c->stream, nullptr)) return 1;
   CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// update_particles + step + get_results as ONE call with the transfers overlapped with the kernels:
+// the positions go up first and the sorts start while v, m, h, u are still on the bus; what the
+// ghost leaves (h, rho, P, c, f, balsara) goes down while the force loop runs.
+int swift_cuda_step_io(swift_cuda_ctx *c, const swift_cuda_parts_in *in, int flags, const swift_cuda_parts_out *out) {
+  NEED_BUILT(c);
+  if (!in || !out) return fail("step_io: null argument");
+  if (in->n != c->n) return fail("step_io: particle count changed; rebuild");
+  if (!in->x || !in->v || !in->mass || !in->h || !in->u) return fail("step_io: null argument");
+  const int64_t n = c->n;
+  Dev &d = c->dev;
+  c->counters.n_kernel_launches = 0;
+  RawIn r;
+  std::memset(&r, 0, sizeof(r));
+  // io stream: positions, then the rest
+  CK(cudaMemcpyAsync(c->s_x, in->x, n * 24, cudaMemcpyHostToDevice, c->io));
+  CK(cudaEventRecord(c->io_ev[0], c->io));
+  CK(cudaMemcpyAsync(c->s_v, in->v, n * 12, cudaMemcpyHostToDevice, c->io));
+  CK(cudaMemcpyAsync(c->s_mass, in->mass, n * 4, cudaMemcpyHostToDevice, c->io));
+  CK(cudaMemcpyAsync(c->s_h, in->h, n * 4, cudaMemcpyHostToDevice, c->io));
+  CK(cudaMemcpyAsync(c->s_u, in->u, n * 4, cudaMemcpyHostToDevice, c->io));
+  r.x = c->s_x; r.v = c->s_v; r.mass = c->s_mass; r.h = c->s_h; r.u = c->s_u;
+  if (in->time_bin) {
+    CK(cudaMemcpyAsync(c->s_tb, in->time_bin, n, cudaMemcpyHostToDevice, c->io));
+    r.time_bin = c->s_tb;
+  }
+  const float *carry[5] = {in->rho, in->pressure, in->f, in->soundspeed, in->balsara};
+  const float **rc[5] = {&r.rho, &r.pressure, &r.f, &r.soundspeed, &r.balsara};
+  for (int k = 0; k < 5; k++)
+    if (carry[k]) {
+      if (!c->s_carry[k] && dmalloc(c, &c->s_carry[k], (size_t)n)) return 1;
+      CK(cudaMemcpyAsync(c->s_carry[k], carry[k], n * 4, cudaMemcpyHostToDevice, c->io));
+      *rc[k] = c->s_carry[k];
+    }
+  CK(cudaEventRecord(c->io_ev[1], c->io));
+  r.order = c->tree.order.empty() ? nullptr : c->s_order;
+  PackDst o;
+  o.x = const_cast<double *>(d.x); o.y = const_cast<double *>(d.y); o.z = const_cast<double *>(d.z);
+  o.vm = d.vm; o.fin = d.fin; o.hb = d.hb; o.h = d.h; o.h0 = c->d_h0; o.u = const_cast<float *>(d.u);
+  o.time_bin = const_cast<int8_t *>(d.time_bin);
+  o.mat_id = const_cast<int32_t *>(d.mat_id);
+  o.id = const_cast<int64_t *>(d.id);
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  // compute stream
+  CK(cudaEventRecord(c->ev[0], c->stream));
+  CK(cudaStreamWaitEvent(c->stream, c->io_ev[0], 0));
+  if (n > 0) k_pack<<<nb, 256, 0, c->stream>>>(n, r, o, 0, 1);
+  if ((flags & SWIFT_CUDA_STEP_SORT) && launch_sort(c)) return 1;
+  CK(cudaStreamWaitEvent(c->stream, c->io_ev[1], 0));
+  if (n > 0) k_pack<<<nb, 256, 0, c->stream>>>(n, r, o, 0, 2);
+  if (d.ncells > 0)
+    k_cell_hmax_init<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d, d.cell_hmax,
+                                                                         const_cast<float *>(d.cell_hmax_old));
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(c->ev[1], c->stream));
+  if (launch_density(c)) return 1;
+  CK(cudaEventRecord(c->ev[2], c->stream));
+  if (launch_ghost(c)) return 1;
+  if (enqueue_results(c, out, 1, c->stream, c->io, c->io_ev[2])) return 1;
+  CK(cudaEventRecord(c->ev[3], c->stream));
+  if (launch_force(c)) return 1;
+  CK(cudaEventRecord(c->ev[4], c->stream));
+  if (enqueue_results(c, out, 2, c->stream, c->stream, nullptr)) return 1;
+  if (finish_counters(c)) return 1;
+  CK(cudaStreamSynchronize(c->io));
+  CK(cudaEventElapsedTime(&c->timings.sort_ms, c->ev[0], c->ev[1]));
+  CK(cudaEventElapsedTime(&c->timings.density_ms, c->ev[1], c->ev[2]));
+  CK(cudaEventElapsedTime(&c->timings.ghost_ms, c->ev[2], c->ev[3]));
+  CK(cudaEventElapsedTime(&c->timings.force_ms, c->ev[3], c->ev[4]));
+  CK(cudaEventElapsedTime(&c->timings.total_ms, c->ev[0], c->ev[4]));
+  if (c->counters.ghost_unconverged > 0)
+    return fail("Smoothing length failed to converge on " + std::to_string(c->counters.ghost_unconverged) +
+                " particles.");
   return 0;
 }
 

@@ -105,3 +105,23 @@ def test_second_step_is_bit_identical():
     for k in a:
         assert np.array_equal(a[k], b[k]), k
     assert ca["n_density_redo"] == cb["n_density_redo"] and ca["n_force"] == cb["n_force"]
+
+
+def test_step_io_matches_separate_calls():
+    """swift_cuda_step_io (overlapped upload / step / download) gives the bits of the three separate calls."""
+    from swift_subtask_dev_b200 import HydroBackend, make_params
+    ic = ics.uniform_random(40000, seed=21)
+    be = HydroBackend(make_params())
+    be.build(ic)
+    be.update_particles(ic)
+    be.step()
+    a = be.results()
+    ca = be.counters()
+    out = be.alloc_results()
+    be.step_io(ic, out)
+    cb = be.counters()
+    be.close()
+    for k in a:
+        assert np.array_equal(a[k], out[k]), k
+    assert [ca[k] for k in ("n_density", "n_density_redo", "n_force")] == \
+           [cb[k] for k in ("n_density", "n_density_redo", "n_force")]
