@@ -237,12 +237,14 @@ def main():
             e2e_times.append(dt)
     e2e_value = inter / float(np.mean(e2e_times))
 
-    # ---- roofline of the dominant kernel: FP32 CUDA-core bound, algorithmic flops
-    # = 66 per density interaction, 122 per force interaction; tests that miss are not credited
-    dom = max(("density_ms", "ghost_ms", "force_ms"), key=lambda k: phase[k])
-    flops = {"density_ms": FLOP_DENSITY * cnt["n_density"], "ghost_ms": FLOP_DENSITY * cnt["n_density_redo"],
-             "force_ms": FLOP_FORCE * cnt["n_force"]}[dom]
-    kern_ms = phase[dom] / args.steps
+    # ---- roofline of the dominant kernel: the single launch that takes longest (k_force; the ghost
+    # phase is longer in total but is five launches of k_density<1>).  FP32 CUDA-core bound (SURVEY.md
+    # 8(d)): algorithmic flops = 66 per density interaction, 122 per force interaction; candidate tests
+    # that miss are not credited.  kernel_ms = CUDA events on the library's stream around that launch.
+    per_launch = {"k_density<0>": (phase["density_ms"] / args.steps, FLOP_DENSITY * cnt["n_density"]),
+                  "k_force": (phase["force_ms"] / args.steps, FLOP_FORCE * cnt["n_force"])}
+    dom = max(per_launch, key=lambda k: per_launch[k][0])
+    kern_ms, flops = per_launch[dom]
     achieved = flops / (kern_ms * 1e-3) / 1e12
     fp32_measured = be.measure_fp32_peak()
     peak_nominal = 148 * 128 * 2 * 1965e6 / 1e12
@@ -254,13 +256,30 @@ def main():
     except Exception:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6400.0))
-    roofline = {"bound": "fp32", "kernel": {"density_ms": "k_density<0>",
-                                             "ghost_ms": "k_density<1> + k_ghost (redo sweeps)",
-                                             "force_ms": "k_force"}[dom],
+    # dram bytes of that kernel per launch, from the committed `ncu --set full` capture of this command
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            tj = json.load(f)
+        if tj.get("side") == args.side:
+            traffic = tj["dram_bytes_per_launch"].get(dom)
+    except Exception:
+        pass
+    redo_ms = phase["ghost_ms"] / args.steps
+    roofline = {"bound": "fp32", "kernel": dom,
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "peak_source": "FMA microbenchmark run by this bench on this GPU (MEASURED_PEAKS.json has no FP32 "
                                "entry); nominal 148 SMs x 128 lanes x 2 x 1965 MHz = %.1f" % peak_nominal,
-                "kernel_ms": kern_ms, "traffic": None,
+                "kernel_ms": kern_ms, "traffic": traffic,
+                "note": "bound is the FP32 CUDA-core issue rate (SURVEY 8(d): ~40 flop/B, no dense contraction: "
+                        "neither 'hbm' nor 'tensor'); achieved counts only the 122 (66) algorithmic flop of "
+                        "interactions that hit",
+                "other_kernels": {"k_density<0>": {"ms": per_launch["k_density<0>"][0],
+                                                   "tflops": per_launch["k_density<0>"][1] /
+                                                   (per_launch["k_density<0>"][0] * 1e-3) / 1e12},
+                                  "k_density<1> x %d sweeps + k_ghost" % cnt["ghost_sweeps"]:
+                                      {"ms": redo_ms,
+                                       "tflops": FLOP_DENSITY * cnt["n_density_redo"] / (redo_ms * 1e-3) / 1e12}},
                 "hbm_step": {"achieved_gbs": 223.0 * n / (ms * 1e-3) / 1e9, "peak_gbs": hbm_peak,
                              "frac": 223.0 * n / (ms * 1e-3) / 1e9 / hbm_peak,
                              "note": "223 B/particle/step algorithmic (SURVEY 8(d)) over the whole step; "

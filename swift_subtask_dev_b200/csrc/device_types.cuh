@@ -42,6 +42,10 @@ struct CellDev {
   int pad;
 };
 
+struct __align__(16) PosD {
+  double x, y, z, pad;
+};
+
 struct __align__(8) SortEnt {
   float d;
   int32_t i;
@@ -55,7 +59,7 @@ struct Dev {
   int n_units;
   double dim[3];
   // particles, cell order
-  const double *x, *y, *z;
+  const PosD *pos;     // x, y, z f64 in one 32-byte record: a gather touches ONE sector
   float4 *vm;          // vx, vy, vz, mass
   float *h;
   const float *u;

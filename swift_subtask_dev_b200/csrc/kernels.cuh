@@ -39,6 +39,14 @@ __device__ __forceinline__ float dist2(float dx, float dy, float dz) {
   return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
 }
 
+// the f64 position of particle j: one 16-byte and one 8-byte load from the same sector
+__device__ __forceinline__ void load_pos(const PosD *__restrict__ pos, int64_t j, double &x, double &y, double &z) {
+  const double2 xy = *reinterpret_cast<const double2 *>(&pos[j].x);
+  x = xy.x;
+  y = xy.y;
+  z = pos[j].z;
+}
+
 // (float)(a - b) with the subtraction in f64
 __device__ __forceinline__ float dsub_f(double a, double b) { return __double2float_rn(__dsub_rn(a, b)); }
 
@@ -227,7 +235,9 @@ __global__ void __launch_bounds__(256) k_sort(Dev d, const int32_t *seg_cell, co
     unsigned long long key = ~0ULL;
     if (t < n) {
       const int64_t p = c.first + t;
-      key = ((unsigned long long)float_to_ordered(sort_key(d.x[p], d.y[p], d.z[p], sid)) << 32) | (unsigned)t;
+      double px, py, pz;
+      load_pos(d.pos, p, px, py, pz);
+      key = ((unsigned long long)float_to_ordered(sort_key(px, py, pz, sid)) << 32) | (unsigned)t;
     }
     for (int size = 2; size <= npad; size <<= 1)
       for (int stride = size >> 1; stride > 0; stride >>= 1) {
@@ -256,7 +266,9 @@ __global__ void __launch_bounds__(256) k_sort(Dev d, const int32_t *seg_cell, co
     unsigned long long key = ~0ULL;
     if (k < n) {
       const int64_t p = c.first + k;
-      const float dk = sort_key(d.x[p], d.y[p], d.z[p], sid);
+      double px, py, pz;
+      load_pos(d.pos, p, px, py, pz);
+      const float dk = sort_key(px, py, pz, sid);
       key = ((unsigned long long)float_to_ordered(dk) << 32) | (unsigned)k;
     }
     keys[k] = key;
@@ -517,7 +529,8 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
 
       const bool mine = p >= 0;
       const int pp = mine ? p : cL.first;
-      const double xi = d.x[pp], yi = d.y[pp], zi = d.z[pp];
+      double xi, yi, zi;
+      load_pos(d.pos, pp, xi, yi, zi);
       const float hi = d.h[pp];
       const float hig2 = sq_gamma2(hi);
       const float hi_inv = 1.f / hi;
@@ -575,7 +588,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
             const int w = __float_as_int(e.w);
             const int j = w & (kDpFlag - 1);
             v = d.vm[j];
-            if (w & kDpFlag) { x = d.x[j]; y = d.y[j]; z = d.z[j]; }
+            if (w & kDpFlag) load_pos(d.pos, j, x, y, z);
           }
         };
         float4 e0 = qcnt > 0 ? gq[0] : z4;
@@ -748,7 +761,9 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
             }
             float4 c = make_float4(qnan, qnan, qnan, qnan);
             if (keep) {
-              c = make_float4(dsub_f(d.x[j], fo[0]), dsub_f(d.y[j], fo[1]), dsub_f(d.z[j], fo[2]), dk);
+              double xj, yj, zj;
+              load_pos(d.pos, j, xj, yj, zj);
+              c = make_float4(dsub_f(xj, fo[0]), dsub_f(yj, fo[1]), dsub_f(zj, fo[2]), dk);
               keep = c.x >= sb.lo[0] && c.x <= sb.hi[0] && c.y >= sb.lo[1] && c.y <= sb.hi[1] && c.z >= sb.lo[2] &&
                      c.z <= sb.hi[2];
             }
@@ -1054,7 +1069,8 @@ __global__ void k_cell_box(Dev d) {
   if (cell.count == 0) return;
   double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
   for (int k = lane; k < cell.count; k += 32) {
-    const double p[3] = {d.x[cell.first + k], d.y[cell.first + k], d.z[cell.first + k]};
+    double p[3];
+    load_pos(d.pos, cell.first + k, p[0], p[1], p[2]);
 #pragma unroll
     for (int a = 0; a < 3; a++) { lo[a] = fmin(lo[a], p[a]); hi[a] = fmax(hi[a], p[a]); }
   }
@@ -1132,7 +1148,8 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
     if (!__any_sync(kFull, p >= 0)) continue;
     const bool mine = p >= 0;
     const int pp = mine ? p : cL.first;
-    const double xi = d.x[pp], yi = d.y[pp], zi = d.z[pp];
+    double xi, yi, zi;
+    load_pos(d.pos, pp, xi, yi, zi);
     ForceI me;
     {
       const float4 vmi = d.vm[pp];
@@ -1212,7 +1229,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
           hb = d.hb[j];
           v = d.vm[j];
           f = d.fin[j];
-          if (w & kDpFlag) { x = d.x[j]; y = d.y[j]; z = d.z[j]; }
+          if (w & kDpFlag) load_pos(d.pos, j, x, y, z);
         }
       };
       float4 e0 = qcnt > 0 ? gq[0] : z4;
@@ -1401,7 +1418,9 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
             float4 c = make_float4(qnan, qnan, qnan, qnan);
             float4 a = make_float4(0.f, INFINITY, -INFINITY, 0.f);
             if (keep) {
-              c = make_float4(dsub_f(d.x[j], fo[0]), dsub_f(d.y[j], fo[1]), dsub_f(d.z[j], fo[2]), dk);
+              double xj, yj, zj;
+              load_pos(d.pos, j, xj, yj, zj);
+              c = make_float4(dsub_f(xj, fo[0]), dsub_f(yj, fo[1]), dsub_f(zj, fo[2]), dk);
               keep = c.x >= sb.lo[0] && c.x <= sb.hi[0] && c.y >= sb.lo[1] && c.y <= sb.hi[1] && c.z >= sb.lo[2] &&
                      c.z <= sb.hi[2];
             }

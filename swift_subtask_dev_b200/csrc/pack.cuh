@@ -31,7 +31,7 @@ struct RawOut {
 };
 
 struct PackDst {  // mutable views of the Dev arrays k_pack fills
-  double *x, *y, *z;
+  PosD *pos;
   float4 *vm, *fin, *hb;
   float *h, *h0, *u;
   int8_t *time_bin;
@@ -46,9 +46,9 @@ __global__ void k_pack(int64_t n, RawIn in, PackDst o, int with_static, int what
   if (k >= n) return;
   const int64_t s = in.order ? in.order[k] : k;
   if (what & 1) {
-    o.x[k] = in.x[3 * s];
-    o.y[k] = in.x[3 * s + 1];
-    o.z[k] = in.x[3 * s + 2];
+    PosD q;
+    q.x = in.x[3 * s]; q.y = in.x[3 * s + 1]; q.z = in.x[3 * s + 2]; q.pad = 0.0;
+    o.pos[k] = q;
   }
   if (!(what & 2)) return;
   o.vm[k] = make_float4(in.v[3 * s], in.v[3 * s + 1], in.v[3 * s + 2], in.mass[s]);

@@ -204,7 +204,7 @@ static int upload_and_pack(swift_cuda_ctx *c, const swift_cuda_parts_in *in, boo
   }
   r.order = c->tree.order.empty() ? nullptr : c->s_order;
   PackDst o;
-  o.x = const_cast<double *>(d.x); o.y = const_cast<double *>(d.y); o.z = const_cast<double *>(d.z);
+  o.pos = const_cast<PosD *>(d.pos);
   o.vm = d.vm; o.fin = d.fin; o.hb = d.hb; o.h = d.h; o.h0 = c->d_h0; o.u = const_cast<float *>(d.u);
   o.time_bin = const_cast<int8_t *>(d.time_bin);
   o.mat_id = const_cast<int32_t *>(d.mat_id);
@@ -222,13 +222,13 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
   Dev &d = c->dev;
   d.n = n;
   for (int k = 0; k < 3; k++) d.dim[k] = c->prm.dim[k];
-  double *dx, *dy, *dz;
+  PosD *dpos;
   float *du; int8_t *dtb; int32_t *dmat; int64_t *did;
-  if (dmalloc(c, &dx, n) || dmalloc(c, &dy, n) || dmalloc(c, &dz, n) || dmalloc(c, &d.vm, n) || dmalloc(c, &d.h, n) ||
+  if (dmalloc(c, &dpos, n) || dmalloc(c, &d.vm, n) || dmalloc(c, &d.h, n) ||
       dmalloc(c, &c->d_h0, n) || dmalloc(c, &d.fin, n) || dmalloc(c, &d.hb, n) || dmalloc(c, &du, n) ||
       dmalloc(c, &dtb, n) || dmalloc(c, &dmat, n) || dmalloc(c, &did, n))
     return 1;
-  d.x = dx; d.y = dy; d.z = dz; d.u = du; d.time_bin = dtb; d.mat_id = dmat; d.id = did;
+  d.pos = dpos; d.u = du; d.time_bin = dtb; d.mat_id = dmat; d.id = did;
   if (dmalloc(c, &c->s_x, (size_t)n * 3) || dmalloc(c, &c->s_v, (size_t)n * 3) || dmalloc(c, &c->s_mass, n) ||
       dmalloc(c, &c->s_h, n) || dmalloc(c, &c->s_u, n) || dmalloc(c, &c->s_tb, n) || dmalloc(c, &c->s_mat, n) ||
       dmalloc(c, &c->s_id, n) || dmalloc(c, &c->s_order, n))
@@ -711,7 +711,7 @@ int swift_cuda_step_io(swift_cuda_ctx *c, const swift_cuda_parts_in *in, int fla
   CK(cudaEventRecord(c->io_ev[1], c->io));
   r.order = c->tree.order.empty() ? nullptr : c->s_order;
   PackDst o;
-  o.x = const_cast<double *>(d.x); o.y = const_cast<double *>(d.y); o.z = const_cast<double *>(d.z);
+  o.pos = const_cast<PosD *>(d.pos);
   o.vm = d.vm; o.fin = d.fin; o.hb = d.hb; o.h = d.h; o.h0 = c->d_h0; o.u = const_cast<float *>(d.u);
   o.time_bin = const_cast<int8_t *>(d.time_bin);
   o.mat_id = const_cast<int32_t *>(d.mat_id);
@@ -895,7 +895,8 @@ __global__ void k_halo_pack_xv(Dev d, const int32_t *idx, int64_t n, HaloXV *buf
   if (k >= n) return;
   const int64_t p = idx[k];
   const float4 vm = d.vm[p];
-  HaloXV r = {d.x[p], d.y[p], d.z[p], vm.x, vm.y, vm.z, vm.w, d.h[p], 0.f};
+  const PosD q = d.pos[p];
+  HaloXV r = {q.x, q.y, q.z, vm.x, vm.y, vm.z, vm.w, d.h[p], 0.f};
   buf[k] = r;
 }
 __global__ void k_halo_unpack_xv(Dev d, const int32_t *idx, int64_t n, const HaloXV *buf) {
@@ -903,9 +904,9 @@ __global__ void k_halo_unpack_xv(Dev d, const int32_t *idx, int64_t n, const Hal
   if (k >= n) return;
   const int64_t p = idx[k];
   const HaloXV r = buf[k];
-  const_cast<double *>(d.x)[p] = r.x;
-  const_cast<double *>(d.y)[p] = r.y;
-  const_cast<double *>(d.z)[p] = r.z;
+  PosD q;
+  q.x = r.x; q.y = r.y; q.z = r.z; q.pad = 0.0;
+  const_cast<PosD *>(d.pos)[p] = q;
   d.vm[p] = make_float4(r.vx, r.vy, r.vz, r.m);
   d.h[p] = r.h;
 }
