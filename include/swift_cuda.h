@@ -169,6 +169,12 @@ int swift_cuda_build_from_cells(swift_cuda_ctx *ctx, const swift_cuda_parts_in *
  * unchanged; same order as the build call. */
 int swift_cuda_update_particles(swift_cuda_ctx *ctx, const swift_cuda_parts_in *parts);
 
+/* Multi-GPU hosts: only the first `count` particles (caller order) are moved by the host <->
+ * device copies of swift_cuda_update_particles / swift_cuda_get_results / swift_cuda_step_io; the
+ * others (halo copies, refreshed over NVLink by the halo entries below) keep their device state.
+ * count < 0: all particles again.  Reset by a build call. */
+int swift_cuda_set_transfer_count(swift_cuda_ctx *ctx, int64_t count);
+
 /* Puts the device copy of the particle state (h and the cells' h_max) back to
  * what the last build / update call uploaded, without touching host memory:
  * repeats a step from the same initial smoothing lengths. */

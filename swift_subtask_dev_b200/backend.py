@@ -98,7 +98,7 @@ class Timings(C.Structure):
 
 EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error", "swift_cuda_create", "swift_cuda_destroy",
            "swift_cuda_build_from_particles", "swift_cuda_build_from_cells", "swift_cuda_update_particles",
-           "swift_cuda_restore_particles",
+           "swift_cuda_restore_particles", "swift_cuda_set_transfer_count",
            "swift_cuda_step", "swift_cuda_step_io", "swift_cuda_do_sort", "swift_cuda_do_density", "swift_cuda_do_ghost",
            "swift_cuda_do_force", "swift_cuda_get_results", "swift_cuda_get_counters", "swift_cuda_get_timings",
            "swift_cuda_measure_fp32_peak",
@@ -252,6 +252,10 @@ class HydroBackend:
     def update_particles(self, ic):
         P, keep = self._parts_in(ic)
         self._check(self.lib.swift_cuda_update_particles(self.ctx, C.byref(P)))
+
+    def set_transfer_count(self, count):
+        """Only the first `count` particles (caller order) travel in update_particles / results / step_io."""
+        self._check(self.lib.swift_cuda_set_transfer_count(self.ctx, C.c_int64(int(count))))
 
     def restore_particles(self):
         """Device-side reset of h to the values of the last build/update (no host traffic)."""

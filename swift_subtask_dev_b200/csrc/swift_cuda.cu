@@ -35,6 +35,7 @@ struct swift_cuda_ctx {
   WorkLists wl;
   Dev dev;
   int64_t n = 0;
+  int64_t n_io = -1;   // swift_cuda_set_transfer_count: particles moved by the host<->device copies (-1: all)
   bool built = false;
   std::vector<void *> allocs;
   // device-only helpers
@@ -168,18 +169,19 @@ static int upload_consts(swift_cuda_ctx *c) {
 // SoA layout there (k_pack).  with_static: also mat_id / id / the order table (build only).
 static int upload_and_pack(swift_cuda_ctx *c, const swift_cuda_parts_in *in, bool with_static) {
   const int64_t n = c->n;
+  const int64_t m = (with_static || c->n_io < 0) ? n : c->n_io;  // particles on the bus
   Dev &d = c->dev;
   cudaStream_t st = c->stream;
   RawIn r;
   std::memset(&r, 0, sizeof(r));
-  CK(cudaMemcpyAsync(c->s_x, in->x, n * 24, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(c->s_v, in->v, n * 12, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(c->s_mass, in->mass, n * 4, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(c->s_h, in->h, n * 4, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(c->s_u, in->u, n * 4, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(c->s_x, in->x, m * 24, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(c->s_v, in->v, m * 12, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(c->s_mass, in->mass, m * 4, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(c->s_h, in->h, m * 4, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(c->s_u, in->u, m * 4, cudaMemcpyHostToDevice, st));
   r.x = c->s_x; r.v = c->s_v; r.mass = c->s_mass; r.h = c->s_h; r.u = c->s_u;
   if (in->time_bin) {
-    CK(cudaMemcpyAsync(c->s_tb, in->time_bin, n, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(c->s_tb, in->time_bin, m, cudaMemcpyHostToDevice, st));
     r.time_bin = c->s_tb;
   }
   const float *carry[5] = {in->rho, in->pressure, in->f, in->soundspeed, in->balsara};
@@ -187,7 +189,7 @@ static int upload_and_pack(swift_cuda_ctx *c, const swift_cuda_parts_in *in, boo
   for (int k = 0; k < 5; k++)
     if (carry[k]) {
       if (!c->s_carry[k] && dmalloc(c, &c->s_carry[k], (size_t)n)) return 1;
-      CK(cudaMemcpyAsync(c->s_carry[k], carry[k], n * 4, cudaMemcpyHostToDevice, st));
+      CK(cudaMemcpyAsync(c->s_carry[k], carry[k], m * 4, cudaMemcpyHostToDevice, st));
       *rc[k] = c->s_carry[k];
     }
   if (with_static) {
@@ -219,6 +221,7 @@ static int upload_and_pack(swift_cuda_ctx *c, const swift_cuda_parts_in *in, boo
 static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
   const int64_t n = in->n;
   c->n = n;
+  c->n_io = -1;
   Dev &d = c->dev;
   d.n = n;
   for (int k = 0; k < 3; k++) d.dim[k] = c->prm.dim[k];
@@ -418,6 +421,13 @@ int swift_cuda_update_particles(swift_cuda_ctx *c, const swift_cuda_parts_in *in
                                                                          const_cast<float *>(d.cell_hmax_old));
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int swift_cuda_set_transfer_count(swift_cuda_ctx *c, int64_t count) {
+  if (!c || !c->built) return fail("set_transfer_count: context not built");
+  if (count > c->n) return fail("set_transfer_count: more than the particles of the context");
+  c->n_io = count < 0 ? -1 : count;
   return 0;
 }
 
@@ -651,6 +661,7 @@ static int enqueue_results(swift_cuda_ctx *c, const swift_cuda_parts_out *out, i
     if (f.host && (f.phase & which)) *f.dev = c->s_out + off;
     off += (int64_t)f.width * n;
   }
+  const int64_t m = c->n_io < 0 ? n : c->n_io;  // particles on the bus
   const bool bin = out->min_ngb_time_bin && (which & 2);
   if (bin) r.min_bin = c->s_out_bin;
   r.order = c->tree.order.empty() ? nullptr : c->s_order;
@@ -662,8 +673,8 @@ static int enqueue_results(swift_cuda_ctx *c, const swift_cuda_parts_out *out, i
   }
   for (Field &f : fields)
     if (f.host && (f.phase & which))
-      CK(cudaMemcpyAsync(f.host, *f.dev, (size_t)f.width * n * 4, cudaMemcpyDeviceToHost, cs));
-  if (bin) CK(cudaMemcpyAsync(out->min_ngb_time_bin, c->s_out_bin, (size_t)n, cudaMemcpyDeviceToHost, cs));
+      CK(cudaMemcpyAsync(f.host, *f.dev, (size_t)f.width * m * 4, cudaMemcpyDeviceToHost, cs));
+  if (bin) CK(cudaMemcpyAsync(out->min_ngb_time_bin, c->s_out_bin, (size_t)m, cudaMemcpyDeviceToHost, cs));
   return 0;
 }
 
@@ -684,20 +695,21 @@ int swift_cuda_step_io(swift_cuda_ctx *c, const swift_cuda_parts_in *in, int fla
   if (in->n != c->n) return fail("step_io: particle count changed; rebuild");
   if (!in->x || !in->v || !in->mass || !in->h || !in->u) return fail("step_io: null argument");
   const int64_t n = c->n;
+  const int64_t m = c->n_io < 0 ? n : c->n_io;  // particles on the bus
   Dev &d = c->dev;
   c->counters.n_kernel_launches = 0;
   RawIn r;
   std::memset(&r, 0, sizeof(r));
   // io stream: positions, then the rest
-  CK(cudaMemcpyAsync(c->s_x, in->x, n * 24, cudaMemcpyHostToDevice, c->io));
+  CK(cudaMemcpyAsync(c->s_x, in->x, m * 24, cudaMemcpyHostToDevice, c->io));
   CK(cudaEventRecord(c->io_ev[0], c->io));
-  CK(cudaMemcpyAsync(c->s_v, in->v, n * 12, cudaMemcpyHostToDevice, c->io));
-  CK(cudaMemcpyAsync(c->s_mass, in->mass, n * 4, cudaMemcpyHostToDevice, c->io));
-  CK(cudaMemcpyAsync(c->s_h, in->h, n * 4, cudaMemcpyHostToDevice, c->io));
-  CK(cudaMemcpyAsync(c->s_u, in->u, n * 4, cudaMemcpyHostToDevice, c->io));
+  CK(cudaMemcpyAsync(c->s_v, in->v, m * 12, cudaMemcpyHostToDevice, c->io));
+  CK(cudaMemcpyAsync(c->s_mass, in->mass, m * 4, cudaMemcpyHostToDevice, c->io));
+  CK(cudaMemcpyAsync(c->s_h, in->h, m * 4, cudaMemcpyHostToDevice, c->io));
+  CK(cudaMemcpyAsync(c->s_u, in->u, m * 4, cudaMemcpyHostToDevice, c->io));
   r.x = c->s_x; r.v = c->s_v; r.mass = c->s_mass; r.h = c->s_h; r.u = c->s_u;
   if (in->time_bin) {
-    CK(cudaMemcpyAsync(c->s_tb, in->time_bin, n, cudaMemcpyHostToDevice, c->io));
+    CK(cudaMemcpyAsync(c->s_tb, in->time_bin, m, cudaMemcpyHostToDevice, c->io));
     r.time_bin = c->s_tb;
   }
   const float *carry[5] = {in->rho, in->pressure, in->f, in->soundspeed, in->balsara};
@@ -705,7 +717,7 @@ int swift_cuda_step_io(swift_cuda_ctx *c, const swift_cuda_parts_in *in, int fla
   for (int k = 0; k < 5; k++)
     if (carry[k]) {
       if (!c->s_carry[k] && dmalloc(c, &c->s_carry[k], (size_t)n)) return 1;
-      CK(cudaMemcpyAsync(c->s_carry[k], carry[k], n * 4, cudaMemcpyHostToDevice, c->io));
+      CK(cudaMemcpyAsync(c->s_carry[k], carry[k], m * 4, cudaMemcpyHostToDevice, c->io));
       *rc[k] = c->s_carry[k];
     }
   CK(cudaEventRecord(c->io_ev[1], c->io));
