@@ -147,6 +147,9 @@ def main():
     ap.add_argument("--side", type=int, default=256, help="particles per box side (BASELINE configs[1]: 256)")
     ap.add_argument("--cpu-side", type=int, default=64)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--workload", default="uniform", choices=["uniform", "clustered"],
+                    help="uniform: BASELINE configs[1] / [3] (default, the metric's config); clustered: configs[4] "
+                         "shape, side^3 particles in TOTAL over ~10^3 clumps + background")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -181,7 +184,12 @@ def main():
         return multi.bench_multi(args, cfg, METRIC, UNIT, sampler_cls=ClockSampler)
 
     torch.cuda.set_device(0)
-    ic = ics.uniform_random(args.side ** 3, seed=cfg["seed"])
+    if args.workload == "clustered":
+        ic = ics.clustered(args.side ** 3, nclumps=1000, seed=7)
+        cfg["workload"] = ("clustered periodic box (1000 Plummer clumps + 30 %% uniform background), %d^3 particles, "
+                           "density+ghost+force, Minimal SPH + ideal gas" % args.side)
+    else:
+        ic = ics.uniform_random(args.side ** 3, seed=cfg["seed"])
     n = len(ic["h"])
     be = HydroBackend(make_params())
     t0 = time.perf_counter()

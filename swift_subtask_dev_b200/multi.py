@@ -29,18 +29,68 @@ class Partition:
     """gx x gy x gz blocks of top-level cells; nodeID = ix + gx (iy + gy iz) as
     partition_initial_partition's INITPART_GRID."""
 
-    def __init__(self, cdim, grid, periodic=True):
+    def __init__(self, cdim, grid, periodic=True, weights=None):
+        """weights=None: equal blocks (the grid must divide cdim).  weights = cost of every top-level
+        cell (flat, x-major): the cuts of the gx x gy x gz blocks are moved so that every block
+        carries the same cost (recursive bisection: x, then y inside each x slab, then z inside
+        each column) -- the role of the reference's weighted repartition (src/partition.c:419-530,
+        1382: METIS vertex weights from particle counts / task costs) for the clustered config."""
         self.cdim = tuple(int(c) for c in cdim)
         self.grid = tuple(int(g) for g in grid)
         self.periodic = periodic
-        for c, g in zip(self.cdim, self.grid):
-            if c % g != 0:
-                raise ValueError("grid %s does not divide the top-level cells %s" % (grid, cdim))
         self.nranks = self.grid[0] * self.grid[1] * self.grid[2]
         ijk = np.stack(np.meshgrid(*[np.arange(c) for c in self.cdim], indexing="ij"), axis=-1).reshape(-1, 3)
-        blk = [ijk[:, d] // (self.cdim[d] // self.grid[d]) for d in range(3)]
         self.ijk = ijk
+        if weights is None:
+            for c, g in zip(self.cdim, self.grid):
+                if c % g != 0:
+                    raise ValueError("grid %s does not divide the top-level cells %s" % (grid, cdim))
+            blk = [ijk[:, d] // (self.cdim[d] // self.grid[d]) for d in range(3)]
+        else:
+            w = np.asarray(weights, dtype=np.float64).reshape(self.cdim)
+            blk = self._weighted_blocks(w)
         self.owner = (blk[0] + self.grid[0] * (blk[1] + self.grid[1] * blk[2])).astype(np.int32)
+
+    @staticmethod
+    def _cuts(w1d, parts):
+        """Block index of every slice of a 1-D cost profile: `parts` contiguous blocks of equal cost,
+        each at least one slice wide."""
+        n = len(w1d)
+        if parts > n:
+            raise ValueError("more blocks than top-level cells along an axis")
+        cum = np.cumsum(w1d)
+        total = cum[-1] if cum[-1] > 0 else 1.0
+        idx = np.zeros(n, dtype=np.int64)
+        start = 0
+        for b in range(parts - 1):
+            target = total * (b + 1) / parts
+            end = int(np.searchsorted(cum, target, side="left")) + 1   # first `end` slices reach the target
+            if end - 1 > start and target - cum[end - 2] < cum[end - 1] - target:
+                end -= 1                                               # the nearer of the two cuts
+            end = min(max(end, start + 1), n - (parts - 1 - b))
+            idx[end:] = b + 1
+            start = end
+        return idx
+
+    def _weighted_blocks(self, w):
+        gx, gy, gz = self.grid
+        cx, cy, cz = self.cdim
+        bi = np.zeros(self.cdim, dtype=np.int64)
+        bj = np.zeros(self.cdim, dtype=np.int64)
+        bk = np.zeros(self.cdim, dtype=np.int64)
+        ix = self._cuts(w.sum(axis=(1, 2)), gx)
+        for a in range(gx):
+            sx = ix == a
+            iy = self._cuts(w[sx].sum(axis=(0, 2)), gy)
+            for b in range(gy):
+                sy = iy == b
+                sub = w[np.ix_(sx, sy, np.ones(cz, dtype=bool))]
+                iz = self._cuts(sub.sum(axis=(0, 1)), gz)
+                m = np.ix_(sx, sy, np.ones(cz, dtype=bool))
+                bi[m] = a
+                bj[m] = b
+                bk[m] = iz[None, None, :]
+        return [bi.reshape(-1), bj.reshape(-1), bk.reshape(-1)]
 
     def flat(self, i, j, k):
         return (i * self.cdim[1] + j) * self.cdim[2] + k
@@ -90,6 +140,34 @@ def local_particles(part, rank, dim, per_cell, seed=42):
     ic["time_bin"] = np.where(is_own, 1, 2).astype(np.int8)
     ic["owner"] = part.owner[ic["cell"]]
     return ic
+
+
+def top_cell_of(x, cdim, dim):
+    """Flat top-level cell of every position, with the library's own arithmetic
+    (host_tree.cpp: idx = (int)(x * (1 / width)), clamped)."""
+    idx = []
+    for d in range(3):
+        iw = 1.0 / (dim[d] / cdim[d])
+        idx.append(np.clip((x[:, d] * iw).astype(np.int64), 0, cdim[d] - 1))
+    return (idx[0] * cdim[1] + idx[1]) * cdim[2] + idx[2]
+
+
+def local_particles_from(ic, part, rank, dim):
+    """The same for an arbitrary particle set `ic` (every rank holds or generates the whole set):
+    the particles of the rank's own top-level cells first, then those of its halo cells, each group
+    in the order of the global arrays."""
+    cell = top_cell_of(ic["x"], part.cdim, dim)
+    own_mask = part.owner[cell] == rank
+    halo_cells = part.halo_cells(rank)
+    is_halo = np.zeros(int(np.prod(part.cdim)), dtype=bool)
+    is_halo[halo_cells] = True
+    sel = np.concatenate([np.nonzero(own_mask)[0], np.nonzero(is_halo[cell] & ~own_mask)[0]])
+    out = {k: (np.ascontiguousarray(a[sel]) if isinstance(a, np.ndarray) and len(a) == len(cell) else a)
+           for k, a in ic.items()}
+    out["cell"] = cell[sel]
+    out["owner"] = part.owner[out["cell"]]
+    out["time_bin"] = np.where(out["owner"] == rank, 1, 2).astype(np.int8)
+    return out
 
 
 # --------------------------------------------------------------------------- transports
@@ -154,13 +232,15 @@ class NcclTransport:
 class RankState:
     """The backend of one rank plus its halo plan."""
 
-    def __init__(self, rank, part, dim, per_cell, seed=42, device=0, params_kw=None):
+    def __init__(self, rank, part, dim, per_cell, seed=42, device=0, params_kw=None, ic=None):
+        """ic=None: the uniform per-cell generator (config 4); else the rank's particles as
+        local_particles_from gives them."""
         import torch
         self.torch = torch
         self.rank = rank
         self.part = part
         self.device = device
-        self.ic = local_particles(part, rank, dim, per_cell, seed=seed)
+        self.ic = local_particles(part, rank, dim, per_cell, seed=seed) if ic is None else ic
         kw = dict(dim=dim, periodic=part.periodic, max_active_bin=1)
         kw.update(params_kw or {})
         self.be = HydroBackend(make_params(**kw), device=device)
@@ -251,9 +331,15 @@ def step_ranks_local(states):
         s.be.runner_do_force()
 
 
-def setup_local(nranks, dim, cdim, per_cell, seed=42, periodic=True, params_kw=None):
-    part = Partition(cdim, grid_for(nranks), periodic)
-    states = [RankState(r, part, dim, per_cell, seed=seed, device=0, params_kw=params_kw) for r in range(nranks)]
+def setup_local(nranks, dim, cdim, per_cell, seed=42, periodic=True, params_kw=None, ic=None, weighted=False):
+    """All ranks in this process on device 0 (tests).  ic: a whole particle set to be split (config 5
+    shape), weighted: balance the particle counts of the blocks."""
+    weights = None
+    if ic is not None and weighted:
+        weights = np.bincount(top_cell_of(ic["x"], cdim, dim), minlength=int(np.prod(cdim)))
+    part = Partition(cdim, grid_for(nranks), periodic, weights=weights)
+    states = [RankState(r, part, dim, per_cell, seed=seed, device=0, params_kw=params_kw,
+                        ic=None if ic is None else local_particles_from(ic, part, r, dim)) for r in range(nranks)]
     for s in states:
         s.set_send_lists({r.rank: r.recv_ids[s.rank] for r in states if s.rank in r.recv_ids})
     return part, states
@@ -293,14 +379,28 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     tr = NcclTransport()
     grid = grid_for(world)
-    dim = tuple(float(g) for g in grid)
     side = args.side
-    h0 = ics.ETA / side
-    cdim = ics.top_grid(dim, h0)
-    part = Partition(cdim, grid, periodic=True)
-    per_cell = int(round(side ** 3 * world / float(np.prod(cdim))))
+    clustered = getattr(args, "workload", "uniform") == "clustered"
     t0 = time.perf_counter()
-    st = RankState(rank, part, dim, per_cell, seed=cfg["seed"], device=local)
+    if clustered:
+        # BASELINE configs[4]: ONE clustered box of side^3 particles split over the ranks (strong
+        # scaling), blocks weighted by particle count; every rank generates the same seeded set
+        dim = (1.0, 1.0, 1.0)
+        gic = ics.clustered(side ** 3, nclumps=1000, seed=7)
+        gic["id"] = np.arange(1, len(gic["h"]) + 1, dtype=np.int64)
+        cdim = ics.top_grid(dim, float(gic["h"].max()))
+        weights = np.bincount(top_cell_of(gic["x"], cdim, dim), minlength=int(np.prod(cdim)))
+        part = Partition(cdim, grid, periodic=True, weights=weights)
+        per_cell = 0
+        st = RankState(rank, part, dim, per_cell, device=local, ic=local_particles_from(gic, part, rank, dim))
+        del gic
+    else:
+        dim = tuple(float(g) for g in grid)
+        h0 = ics.ETA / side
+        cdim = ics.top_grid(dim, h0)
+        part = Partition(cdim, grid, periodic=True)
+        per_cell = int(round(side ** 3 * world / float(np.prod(cdim))))
+        st = RankState(rank, part, dim, per_cell, seed=cfg["seed"], device=local)
     wanted = tr.all_to_all_objects({p: ids for p, ids in st.recv_ids.items()})
     st.set_send_lists(wanted)
     build_s = time.perf_counter() - t0
@@ -365,14 +465,20 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
     ms = float(tmax[0])
     if rank == 0:
         cfg = dict(cfg)
-        cfg["workload"] = ("periodic uniform-random box, %d particles per top-level cell, %s top-level cells over a "
-                           "%dx%dx%d GPU grid (%d^3 particles per GPU), density+ghost+force, Minimal SPH + ideal gas"
-                           % (per_cell, "x".join(map(str, cdim)), grid[0], grid[1], grid[2], side))
+        if clustered:
+            cfg["workload"] = ("clustered periodic box (1000 Plummer clumps + 30 %% uniform background), %d^3 "
+                               "particles in TOTAL, %s top-level cells in %dx%dx%d blocks of equal particle count, "
+                               "density+ghost+force, Minimal SPH + ideal gas"
+                               % (side, "x".join(map(str, cdim)), grid[0], grid[1], grid[2]))
+        else:
+            cfg["workload"] = ("periodic uniform-random box, %d particles per top-level cell, %s top-level cells "
+                               "over a %dx%dx%d GPU grid (%d^3 particles per GPU), density+ghost+force, Minimal SPH "
+                               "+ ideal gas" % (per_cell, "x".join(map(str, cdim)), grid[0], grid[1], grid[2], side))
         cfg["parallelism"] = "spatial %dx%dx%d, NCCL send/recv halo (xv 48 B, rho 24 B per particle)" % grid
         nloc_tot = int(tsum[5])
         line = {"metric": metric, "value": float(tsum[1]) / (ms * 1e-3), "unit": unit, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+                "scaling": "strong" if clustered else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
                 "clocks": clocks,
                 "gpu_launches": (2 * st.be.params.max_smoothing_iterations + 5 + 4 * len(st.send_idx))
                 * args.steps * world,
@@ -380,6 +486,7 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
                         "h2d_bytes_per_step": int(tsum[2]) * 49, "d2h_bytes_per_step": int(tsum[2]) * 49},
                 "detail": {"n_particles_owned_total": int(tsum[2]), "interactions_per_step": int(tsum[1]),
                            "halo_bytes_per_step_total": int(tsum[3]), "build_s": build_s,
+                           "load_imbalance_interactions_max_over_mean": float(tmax[1]) * world / float(tsum[1]),
                            "ms_device_events_rank0": ms_dev, "ms_wall_rank0": ms_wall}}
         print(json.dumps(line))
     dist.barrier()

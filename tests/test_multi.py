@@ -130,3 +130,65 @@ def test_ranks_reproduce_single_gpu_run_bit_exactly(nranks):
         assert s.halo_bytes_per_step() > 0
         s.be.close()
     assert tot == cref["n_density"] + cref["n_density_redo"] + cref["n_force"]
+
+
+def test_weighted_partition_balances_a_clustered_box():
+    """Cost-weighted blocks (role of the reference's weighted repartition) on a clumpy particle set:
+    every cell owned once, blocks are boxes, the heaviest rank is lighter than with equal blocks."""
+    cdim, dim = (12, 12, 12), (1.0, 1.0, 1.0)
+    ic = ics.clustered(200000, nclumps=6, seed=3)
+    cell = multi.top_cell_of(ic["x"], cdim, dim)
+    w = np.bincount(cell, minlength=int(np.prod(cdim)))
+    for n in (2, 4, 8):
+        eq = multi.Partition(cdim, multi.grid_for(n))
+        wt = multi.Partition(cdim, multi.grid_for(n), weights=w)
+        assert set(np.unique(wt.owner)) == set(range(n))
+        le = np.bincount(eq.owner, weights=w, minlength=n)
+        lw = np.bincount(wt.owner, weights=w, minlength=n)
+        assert lw.max() <= le.max()
+        for r in range(n):   # a block is a box of cells
+            ijk = wt.ijk[wt.owner == r]
+            ext = ijk.max(axis=0) - ijk.min(axis=0) + 1
+            assert int(np.prod(ext)) == len(ijk)
+    assert lw.max() / lw.mean() < 1.5 < le.max() / le.mean()
+    # every particle is owned by exactly one rank, and a rank's own particles come first
+    part = multi.Partition(cdim, multi.grid_for(4), weights=w)
+    owned = 0
+    for r in range(4):
+        loc = multi.local_particles_from(ic, part, r, dim)
+        own = loc["time_bin"] == 1
+        n_own = int(own.sum())
+        assert own[:n_own].all() and not own[n_own:].any()
+        assert (part.owner[loc["cell"]][own] == r).all()
+        owned += n_own
+    assert owned == len(ic["h"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nranks,weighted", [(2, False), (4, True)])
+def test_clustered_ranks_reproduce_single_gpu_run_bit_exactly(nranks, weighted):
+    """BASELINE configs[4] shape (clustered, deep tree) split over ranks: owned results bit-identical to
+    one context on the whole box, with equal and with cost-weighted blocks."""
+    from swift_subtask_dev_b200 import HydroBackend, make_params
+    dim = (1.0, 1.0, 1.0)
+    ic = ics.clustered(300000, nclumps=12, seed=5)
+    ic["id"] = np.arange(1, len(ic["h"]) + 1, dtype=np.int64)
+    be = HydroBackend(make_params(dim=dim, periodic=True))
+    be.build(ic)
+    cdim = tuple(be.tree()["cdim"])
+    be.step()
+    ref = be.results()
+    cref = be.counters()
+    be.close()
+    part, states = multi.setup_local(nranks, dim, cdim, 0, ic=ic, weighted=weighted)
+    multi.step_ranks_local(states)
+    tot = 0
+    for s in states:
+        r = s.owned_results()
+        idx = r["id"] - 1
+        for k in ref:
+            assert np.array_equal(r[k], ref[k][idx]), (s.rank, k)
+        c = s.be.counters()
+        tot += c["n_density"] + c["n_density_redo"] + c["n_force"]
+        s.be.close()
+    assert tot == cref["n_density"] + cref["n_density_redo"] + cref["n_force"]
