@@ -10,6 +10,7 @@
 //   sort key  src/runner_sort.c:377-387
 #pragma once
 #include <cfloat>
+#include <type_traits>
 
 #include "device_types.cuh"
 
@@ -396,6 +397,13 @@ __device__ __forceinline__ float thr_gt_shift(double rs, double y) {
   return t;
 }
 
+// 16-byte store under a predicate: no branch, no reconvergence point in the candidate tests
+__device__ __forceinline__ void st_pred(float4 *p, float x, float y, float z, float w, bool pred) {
+  asm volatile("{ .reg .pred q; setp.ne.b32 q, %5, 0; @q st.global.v4.f32 [%0], {%1, %2, %3, %4}; }" ::"l"(p), "f"(x),
+               "f"(y), "f"(z), "f"(w), "r"((int)pred)
+               : "memory");
+}
+
 // warp-wide min / max in one instruction (redux.sync f32: sm_100a)
 __device__ __forceinline__ float warp_min(float v) {
   float r;
@@ -710,8 +718,10 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
         // wider: the exact r2 < h^2 gamma^2 of the reference is redone when the hit is consumed.
         const float thr_c = thr * 1.000001f;
         const int flagbits = dp ? kDpFlag : 0;
-        auto test = [&](int st, int n) {
-          if (__any_sync(kFull, qcnt > kQD - n)) drain_all();
+        // SHIFTED (redo sweeps, pairs across the cell boundary): the entry carries the periodic shift
+        // instead of dx, which the body takes again from the f64 positions
+        auto test_impl = [&](auto shifted_c, int st, int n) {
+          constexpr bool SHIFTED = decltype(shifted_c)::value;
           const float4 *__restrict__ tp = ws.pos + st;
           const int *__restrict__ ti = ws.idx + st;
           float4 *qp = gq + qcnt * 32;
@@ -721,18 +731,20 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
               const float4 c = tp[k0 + u];
               const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
               const float r2c = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
-              if (c.w >= lo && c.w <= hi_cut && r2c < thr_c) {
-                const int j = ti[k0 + u];
-                if (j != pp) {
-                  if (MODE == 0) *qp = make_float4(dx, dy, dz, __int_as_float(j | flagbits));
-                  else *qp = dp ? make_float4(shf[0], shf[1], shf[2], __int_as_float(j | kDpFlag))
-                                : make_float4(dx, dy, dz, __int_as_float(j));
-                  qp += 32;
-                }
-              }
+              const int j = ti[k0 + u];
+              const bool push = c.w >= lo && c.w <= hi_cut && r2c < thr_c && j != pp;
+              // straight-line: the store and the FIFO advance are predicated, not branched over
+              if (SHIFTED) st_pred(qp, shf[0], shf[1], shf[2], __int_as_float(j | kDpFlag), push);
+              else st_pred(qp, dx, dy, dz, __int_as_float(j | flagbits), push);
+              qp += push ? 32 : 0;
             }
           }
           qcnt = (int)(qp - gq) >> 5;
+        };
+        auto test = [&](int st, int n) {
+          if (__any_sync(kFull, qcnt > kQD - n)) drain_all();
+          if (MODE == 1 && dp) test_impl(std::true_type{}, st, n);
+          else test_impl(std::false_type{}, st, n);
         };
 
         int st = 0, ntile = 0, base = 0;
@@ -1347,8 +1359,10 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
         else wlim = warp_min(pass == 0 ? fminf(bound1, bound2) : bound2);
         if (!self && (left ? (wlim == -INFINITY) : (wlim == INFINITY))) break;
 
-        auto test = [&](int st, int n) {
-          if (__any_sync(kFull, qcnt > kQD - n - kSide)) drain_all();
+        // KIND 0: own cell, 1: this leaf is the pair's ci, 2: the pair's cj.  Straight-line tests: the
+        // FIFO store and its advance are predicated; only the rare loop-2 side push is a branch.
+        auto test_impl = [&](auto kind_c, int st, int n) {
+          constexpr int KIND = decltype(kind_c)::value;
           const float4 *__restrict__ tp = ws.pos + st;  // st is 0 or 32: no wrap inside a tile
           const float4 *__restrict__ ta = ws.aux + st;
           const int *__restrict__ ti = ws.idx + st;
@@ -1358,30 +1372,27 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
             for (int u = 0; u < 4; u++) {
               const float4 c = tp[k0 + u];
               const float4 a = ta[k0 + u];
+              const int j = ti[k0 + u];
               const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
               const float r2 = dist2(dx, dy, dz);
-              if (self) {
-                if (r2 < thr_i || (mine && r2 < a.x)) {
-                  const int j = ti[k0 + u];
-                  if (j != pp) {
-                    *qp = make_float4(0.f, 0.f, 0.f, __int_as_float(j | kDpFlag));
-                    qp += 32;
-                  }
-                }
+              if (KIND == 0) {
+                const bool push = (r2 < thr_i || (mine && r2 < a.x)) && j != pp;
+                st_pred(qp, 0.f, 0.f, 0.f, __int_as_float(j | kDpFlag), push);
+                qp += push ? 32 : 0;
               } else {
                 bool h1, h2;
-                if (left) {
+                if (KIND == 1) {
                   h1 = c.w <= cut1 && r2 < hig2;
                   h2 = a.y <= cut2 && r2 < a.x && r2 >= hig2;
                 } else {
                   h1 = cut1 <= a.z && r2 < a.x;
                   h2 = c.w >= cut2 && r2 < hig2 && r2 >= a.x;
                 }
-                if (pass == 0 ? h1 : h2) {
-                  *qp = make_float4(dx, dy, dz, __int_as_float(ti[k0 + u]));
-                  qp += 32;
-                } else if (pass == 0 && h2) {
-                  if (scnt < kSide) ws.side[scnt][lane] = make_float4(dx, dy, dz, __int_as_float(ti[k0 + u]));
+                const bool push = pass == 0 ? h1 : h2;
+                st_pred(qp, dx, dy, dz, __int_as_float(j), push);
+                qp += push ? 32 : 0;
+                if (pass == 0 && h2) {
+                  if (scnt < kSide) ws.side[scnt][lane] = make_float4(dx, dy, dz, __int_as_float(j));
                   else sovf = true;
                   scnt++;
                 }
@@ -1389,6 +1400,12 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
             }
           }
           qcnt = (int)(qp - gq) >> 5;
+        };
+        auto test = [&](int st, int n) {
+          if (__any_sync(kFull, qcnt > kQD - n - kSide)) drain_all();
+          if (self) test_impl(std::integral_constant<int, 0>{}, st, n);
+          else if (left) test_impl(std::integral_constant<int, 1>{}, st, n);
+          else test_impl(std::integral_constant<int, 2>{}, st, n);
         };
 
         int st = 0, ntile = 0, base = 0;
