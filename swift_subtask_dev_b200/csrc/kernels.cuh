@@ -1129,6 +1129,7 @@ struct ForceTile {
   float4 aux[kTile];
   int idx[kTile];
   float4 side[kSide][32];
+  float box[12];      // the unit's boxes (leaf frame): u0 lo/hi, uH lo/hi -- warp-uniform, kept out of the registers
 };
 
 template <int SCHEME>
@@ -1191,18 +1192,19 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
 
     // boxes of the unit's particles in the leaf's frame: bare positions (u0), and grown by
     // each particle's own search radius (uH)
-    float u0lo[3], u0hi[3], uHlo[3], uHhi[3];
+    float *const u0lo = ws.box, *const u0hi = ws.box + 3, *const uHlo = ws.box + 6, *const uHhi = ws.box + 9;
+    __syncwarp();
     {
       const float l[3] = {dsub_f(xi, cL.loc[0]), dsub_f(yi, cL.loc[1]), dsub_f(zi, cL.loc[2])};
       const float ru = hig * 1.0001f;
 #pragma unroll
       for (int k = 0; k < 3; k++) {
-        u0lo[k] = warp_min(mine ? l[k] : INFINITY);
-        u0hi[k] = warp_max(mine ? l[k] : -INFINITY);
-        uHlo[k] = warp_min(mine ? l[k] - ru : INFINITY);
-        uHhi[k] = warp_max(mine ? l[k] + ru : -INFINITY);
+        const float a0 = warp_min(mine ? l[k] : INFINITY), a1 = warp_max(mine ? l[k] : -INFINITY);
+        const float a2 = warp_min(mine ? l[k] - ru : INFINITY), a3 = warp_max(mine ? l[k] + ru : -INFINITY);
+        if (lane == 0) { u0lo[k] = a0; u0hi[k] = a1; uHlo[k] = a2; uHhi[k] = a3; }
       }
     }
+    __syncwarp();
 
     // one deferred hit -> runner_iact_nonsym_force; the three float4 of j (and its f64 position for
     // an own-cell pair) were gathered one round ahead
