@@ -229,37 +229,35 @@ __global__ void __launch_bounds__(256) k_sort(Dev d, const int32_t *seg_cell, co
   int npad = 1;
   while (npad < n) npad <<= 1;
   if (npad <= 256) {
-    // The common case (a leaf of <= 256 particles): one element per thread, compare-exchange
-    // through warp shuffles for strides < 32 and through shared memory only for strides >= 32
-    // (6 of the 36 stages), so almost no block-wide barriers.
+    // The common case (a leaf of <= 256 particles): rank sort.  Every thread counts the keys below
+    // its own (four per 16-byte broadcast load) and writes its entry at that rank: ~3x fewer
+    // instructions than a 36-stage bitonic network on 256 slots, one barrier.  Equal keys (rare)
+    // are ordered by index, as sorting (key << 32 | index) does.
+    uint32_t *sk = reinterpret_cast<uint32_t *>(skeys);
     const int t = threadIdx.x;
-    unsigned long long key = ~0ULL;
+    uint32_t ku = 0xffffffffu;
     if (t < n) {
-      const int64_t p = c.first + t;
       double px, py, pz;
-      load_pos(d.pos, p, px, py, pz);
-      key = ((unsigned long long)float_to_ordered(sort_key(px, py, pz, sid)) << 32) | (unsigned)t;
+      load_pos(d.pos, c.first + t, px, py, pz);
+      ku = float_to_ordered(sort_key(px, py, pz, sid));
     }
-    for (int size = 2; size <= npad; size <<= 1)
-      for (int stride = size >> 1; stride > 0; stride >>= 1) {
-        unsigned long long other;
-        if (stride >= 32) {
-          __syncthreads();
-          skeys[t] = key;
-          __syncthreads();
-          other = skeys[t ^ stride];
-        } else {
-          other = __shfl_xor_sync(0xffffffffu, key, stride);
-        }
-        const bool up = (t & size) == 0, lower = (t & stride) == 0;
-        key = (lower == up) ? (key < other ? key : other) : (key < other ? other : key);
-      }
-    if (t < n) {
-      SortEnt se;
-      se.d = ordered_to_float((uint32_t)(key >> 32));
-      se.i = (int32_t)(key & 0xffffffffu);
-      d.sort[seg_off[seg] + t] = se;
+    sk[t] = ku;  // slots n .. 255: 0xffffffff, below nothing
+    __syncthreads();
+    if (t >= n) return;
+    int lt = 0, eq = 0;
+    const int n4 = (n + 3) & ~3;
+    for (int k = 0; k < n4; k += 4) {
+      const uint4 v = *reinterpret_cast<const uint4 *>(&sk[k]);
+      lt += (v.x < ku) + (v.y < ku) + (v.z < ku) + (v.w < ku);
+      eq += (v.x == ku) + (v.y == ku) + (v.z == ku) + (v.w == ku);
     }
+    int rank = lt;
+    if (eq > 1)
+      for (int k = 0; k < t; k++) rank += (sk[k] == ku);
+    SortEnt se;
+    se.d = ordered_to_float(ku);
+    se.i = t;
+    d.sort[seg_off[seg] + rank] = se;
     return;
   }
   unsigned long long *keys = (npad <= kSortSmem) ? skeys : (scratch + scratch_off[seg]);
