@@ -482,7 +482,11 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
   const int lane = threadIdx.x & 31;
   const unsigned lt_mask = (1u << lane) - 1u;
   float4 *const gq = d.gq + (size_t)(blockIdx.x * kWarps + (threadIdx.x >> 5)) * (kQD * 32) + lane;
-  const int total = MODE == 0 ? d.n_units : d.n_leaves;
+  // redo sweeps: while most particles are still flagged (the first sweeps) a warp takes a 32-particle
+  // unit as the first pass does (5x more leaves in flight would not fit the L2); once the flagged
+  // particles are few, a warp takes a whole leaf and compacts them into full groups of 32
+  const bool by_unit = MODE == 0 || (long long)d.redo_count[sweep] * 2 > d.n;
+  const int total = by_unit ? d.n_units : d.n_leaves;
   int *const work = d.work_ctr + (MODE == 0 ? 0 : 1 + sweep);
   const Item *__restrict__ items = MODE == 0 ? d.items : d.redo_items;
   const bool rec = d.rec_capacity > 0;
@@ -494,7 +498,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
     if (lane == 0) wid = atomicAdd(work, 1);
     wid = __shfl_sync(kFull, wid, 0);
     if (wid >= total) break;
-    const int slot = MODE == 0 ? d.unit_leaf[wid] : wid;
+    const int slot = by_unit ? d.unit_leaf[wid] : wid;
     const CellDev cL = d.cells[d.leaves[slot]];
     const int ib = (MODE == 0 ? d.item_begin : d.redo_begin)[slot];
     const int ie = (MODE == 0 ? d.item_begin : d.redo_begin)[slot + 1];
@@ -504,11 +508,15 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
     while (true) {
       // ---- which particle does this lane own in this round?
       int p = -1;
-      if (MODE == 0) {
+      if (by_unit) {
         if (!first) break;
         first = false;
         const int q = d.lane_part[(int64_t)wid * 32 + lane];
-        if (q >= 0 && d.time_bin[q] <= kc.max_active_bin) p = q;
+        if (MODE == 0) {
+          if (q >= 0 && d.time_bin[q] <= kc.max_active_bin) p = q;
+        } else {
+          if (q >= 0 && d.gstate[q] == 2) p = q;
+        }
       } else {
         // the leaf's particles in lane (Morton) order
         const int64_t lp0 = (int64_t)d.unit_begin[slot] * 32;

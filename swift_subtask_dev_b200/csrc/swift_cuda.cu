@@ -339,7 +339,7 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
       return std::max(1, std::min(want, sms * std::max(occ, 1)));
     };
     c->grid_density = grid_for(o0, d.n_units);
-    c->grid_redo = grid_for(o1, d.n_leaves);
+    c->grid_redo = grid_for(o1, d.n_units);
     c->grid_force = grid_for(o2, d.n_units);
     const size_t qwarps = (size_t)std::max(c->grid_density, std::max(c->grid_redo, c->grid_force)) * kWarps;
     if (dmalloc(c, &d.gq, qwarps * kQD * 32) || dmalloc(c, &d.work_ctr, (size_t)c->prm.max_smoothing_iterations + 2))
