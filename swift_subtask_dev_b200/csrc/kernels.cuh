@@ -397,7 +397,7 @@ __device__ __forceinline__ float thr_gt_shift(double rs, double y) {
 
 // 16-byte store under a predicate: no branch, no reconvergence point in the candidate tests
 __device__ __forceinline__ void st_pred(float4 *p, float x, float y, float z, float w, bool pred) {
-  asm volatile("{ .reg .pred q; setp.ne.b32 q, %5, 0; @q st.global.v4.f32 [%0], {%1, %2, %3, %4}; }" ::"l"(p), "f"(x),
+  asm volatile("{ .reg .pred q; setp.ne.b32 q, %5, 0; @q st.global.cs.v4.f32 [%0], {%1, %2, %3, %4}; }" ::"l"(p), "f"(x),
                "f"(y), "f"(z), "f"(w), "r"((int)pred)
                : "memory");
 }
@@ -605,13 +605,13 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
             if (w & kDpFlag) load_pos(d.pos, j, x, y, z);
           }
         };
-        float4 e0 = qcnt > 0 ? gq[0] : z4;
-        float4 e1 = qcnt > 1 ? gq[32] : z4;
+        float4 e0 = qcnt > 0 ? __ldcs(&gq[0]) : z4;
+        float4 e1 = qcnt > 1 ? __ldcs(&gq[32]) : z4;
         float4 v0 = z4;
         double x0 = 0.0, y0 = 0.0, z0 = 0.0;
         gather(e0, qcnt > 0, v0, x0, y0, z0);
         for (int r = 0; r < m; r++) {
-          const float4 e2 = (r + 2 < qcnt) ? gq[(r + 2) * 32] : z4;
+          const float4 e2 = (r + 2 < qcnt) ? __ldcs(&gq[(r + 2) * 32]) : z4;
           float4 v1 = z4;
           double x1 = 0.0, y1 = 0.0, z1 = 0.0;
           gather(e1, r + 1 < qcnt, v1, x1, y1, z1);
@@ -1252,13 +1252,13 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
           if (w & kDpFlag) load_pos(d.pos, j, x, y, z);
         }
       };
-      float4 e0 = qcnt > 0 ? gq[0] : z4;
-      float4 e1 = qcnt > 1 ? gq[32] : z4;
+      float4 e0 = qcnt > 0 ? __ldcs(&gq[0]) : z4;
+      float4 e1 = qcnt > 1 ? __ldcs(&gq[32]) : z4;
       float4 hb0 = z4, v0 = z4, f0 = z4;
       double x0 = 0.0, y0 = 0.0, z0 = 0.0;
       gather(e0, qcnt > 0, hb0, v0, f0, x0, y0, z0);
       for (int r = 0; r < m; r++) {
-        const float4 e2 = (r + 2 < qcnt) ? gq[(r + 2) * 32] : z4;
+        const float4 e2 = (r + 2 < qcnt) ? __ldcs(&gq[(r + 2) * 32]) : z4;
         float4 hb1 = z4, v1 = z4, f1 = z4;
         double x1 = 0.0, y1 = 0.0, z1 = 0.0;
         gather(e1, r + 1 < qcnt, hb1, v1, f1, x1, y1, z1);
