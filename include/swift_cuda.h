@@ -144,7 +144,8 @@ typedef struct swift_cuda_ctx swift_cuda_ctx;
 
 int swift_cuda_abi_version(void);
 /* sizeof of the ABI structs as compiled into the library, for binding checks:
- * 0 params, 1 cell, 2 task, 3 parts_in, 4 parts_out, 5 counters, 6 timings, 7 til. */
+ * 0 params, 1 cell, 2 task, 3 parts_in, 4 parts_out, 5 counters, 6 timings, 7 til, 8 integrator,
+ * 9 state_out. */
 size_t swift_cuda_sizeof(int which);
 const char *swift_cuda_last_error(void);
 
@@ -249,6 +250,57 @@ int swift_cuda_get_touched(swift_cuda_ctx *ctx, uint8_t *mask);
  * from scratch, also h_max_old (after an xv refresh); 1: raise to cover the
  * current h (after a rho refresh), as runner_do_ghost leaves it. */
 int swift_cuda_refresh_cell_hmax(swift_cuda_ctx *ctx, int after_ghost);
+
+/* ---- Time integration on the device -------------------
+ * The step either side of the neighbour loops, so that the particles stay resident in HBM across
+ * steps and only snapshots cross the bus.  Replaces, for gas particles without gravity, cosmology,
+ * cooling or the time-step limiter:
+ *   runner_do_drift_part -> cell_drift_part   src/cell_drift.c:145-380  (drift_part, src/drift.h:143-233,
+ *                                             hydro_predict_extra, src/hydro/<scheme>/hydro.h)
+ *   runner_do_kick1 / runner_do_kick2         src/runner_time_integration.c:87-220, 359-500 (kick_part,
+ *                                             src/kick.h:215-279, hydro_kick_extra, hydro_reset_predicted_values)
+ *   runner_do_timestep                        src/runner_time_integration.c:637-1000 (get_part_timestep,
+ *                                             make_integer_timestep, src/timestep.h:45-82, 141-222)
+ * Engine-step order (src/engine.c, engine_step), with every particle drifted at every step
+ * (engine_policy_drift_all):
+ *   set_time(ti_current, get_max_active_bin(ti_current)); drift(ti_old); step(SORT); kick(2); timestep; kick(1)
+ * The context must have been built with every cell in the work lists (max_active_bin = 56 at the build:
+ * which particles are active then changes per step on the device only). */
+typedef struct {
+  float cfl_condition;           /* hydro_props->CFL_condition */
+  float log_max_h_change;        /* hydro_props->log_max_h_change */
+  float minimal_internal_energy; /* hydro_props->minimal_internal_energy */
+  double dt_min, dt_max;         /* e->dt_min, e->dt_max */
+  double time_base;              /* e->time_base */
+} swift_cuda_integrator;
+
+/* The whole per-particle state, host memory, caller order; any pointer may be NULL. */
+typedef struct {
+  double *x;                     /* p->x */
+  float *v, *v_full;             /* p->v (predicted), xp->v_full */
+  float *u, *u_full;             /* p->u (predicted), xp->u_full */
+  float *h, *rho, *pressure, *soundspeed, *v_sig;
+  float *a, *u_dt, *h_dt;
+  float *x_diff, *x_diff_sort;   /* xp->x_diff, xp->x_diff_sort */
+  int8_t *time_bin, *min_ngb_time_bin;
+} swift_cuda_state_out;
+
+/* hydro_first_init_part: v_full = v, u_full = u, x_diff = x_diff_sort = 0 from the uploaded particles. */
+int swift_cuda_integrator_init(swift_cuda_ctx *ctx, const swift_cuda_integrator *p);
+/* e->ti_current and e->max_active_bin of the step that starts. */
+int swift_cuda_set_time(swift_cuda_ctx *ctx, long long ti_current, int max_active_bin);
+/* Drifts every particle from ti_old to ti_current, refreshes the cells' h_max; dx_max[0] = largest
+ * |x_diff| (c->hydro.dx_max_part over all cells), dx_max[1] = largest |x_diff_sort|: what the host's
+ * rebuild / re-sort criterion reads.  dx_max may be NULL. */
+int swift_cuda_drift(swift_cuda_ctx *ctx, long long ti_old, float dx_max[2]);
+/* which = 1: runner_do_kick1 (particles starting a step); 2: runner_do_kick2 (particles ending one). */
+int swift_cuda_kick(swift_cuda_ctx *ctx, int which);
+/* New time bins of the active particles.  ti_end_min: the next ti_current; updated: particles that got a
+ * new step.  Fails ("wants a time-step below dt_min", as the reference's error()) when one does. */
+int swift_cuda_timestep(swift_cuda_ctx *ctx, long long *ti_end_min, long long *updated);
+/* Zeroes x_diff_sort (after a re-sort) and/or x_diff (after a rebuild): what = 1 sort, 2 both. */
+int swift_cuda_reset_offsets(swift_cuda_ctx *ctx, int what);
+int swift_cuda_get_state(swift_cuda_ctx *ctx, const swift_cuda_state_out *out);
 
 #ifdef __cplusplus
 }

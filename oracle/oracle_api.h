@@ -84,6 +84,10 @@ typedef struct {
    * active step (p->rho, p->force.{pressure, f, soundspeed, balsara}); the
    * force loop of their active neighbours reads it.  NULL: zeros. */
   const float *in_rho, *in_pressure, *in_f, *in_soundspeed, *in_balsara;
+  /* optional: the smoothing lengths at the last rebuild, from which c->hydro.h_max_old is taken (it
+   * decides how deep the sub-tasks recurse and stays fixed between rebuilds, src/space_split.c).
+   * NULL: the current h (a step right after a rebuild). */
+  const float *in_h_build;
 } oracle_parts;
 
 /* Ordered (updated id, neighbour id) pairs.  loop 0: first density pass,
@@ -117,6 +121,51 @@ int oracle_build_tasks(const oracle_params *prm, int ncells, const oracle_cell *
 int oracle_run_step(const oracle_params *prm, const oracle_eos *eos, oracle_parts *parts, int ncells,
                     const oracle_cell *cells, int ntasks, const oracle_task *tasks, oracle_pairlog *log);
 void oracle_free(void *p);
+
+/* ---- time integration either side of the path --------
+ * drift (src/drift.h:143-233 inside the particle loop of src/cell_drift.c:233-340),
+ * kick (src/kick.h:215-279 as called by src/runner_time_integration.c:141-180, 412-457),
+ * time-step (src/timestep.h:45-82, 141-222; src/runner_time_integration.c:696-745),
+ * without cosmology, gravity, cooling, limiter.  All arrays have n entries ([n][3] vectors). */
+typedef struct {
+  int scheme;                    /* ORACLE_SCHEME_* (the ref harness ignores it) */
+  float cfl_condition;           /* hydro_props->CFL_condition */
+  float log_max_h_change;        /* hydro_props->log_max_h_change */
+  float minimal_internal_energy; /* hydro_props->minimal_internal_energy */
+  float h_max, h_min;            /* hydro_props->h_max / h_min (cell_drift.c:303-304) */
+  double dt_min, dt_max;         /* e->dt_min, e->dt_max */
+  double time_base;              /* e->time_base; time_base_inv = 1 / time_base */
+  int max_active_bin;            /* e->max_active_bin */
+  long long ti_current;          /* e->ti_current */
+} oracle_iparams;
+
+typedef struct {
+  int n;
+  double *x;
+  float *v, *v_full;             /* p->v (predicted), xp->v_full */
+  float *u, *u_full;             /* p->u (predicted), xp->u_full */
+  float *h, *rho, *pressure, *soundspeed, *v_sig;
+  float *a, *u_dt, *h_dt;        /* p->a_hydro, p->u_dt, p->force.h_dt */
+  float *x_diff, *x_diff_sort;   /* xp->x_diff, xp->x_diff_sort */
+  signed char *time_bin;
+  const signed char *min_ngb_time_bin;
+  const int *mat_id;             /* Planetary only, may be NULL */
+} oracle_istate;
+
+/* every particle drifts from ti_old to ip->ti_current (dt = (ti_current - ti_old) * time_base, the
+ * non-cosmological branch of cell_drift.c:232-236): drift_part + the h clamp; dx_max[0] =
+ * c->hydro.dx_max_part, dx_max[1] = c->hydro.dx_max_sort of a cell holding all particles */
+int ref_drift(const oracle_iparams *ip, oracle_istate *s, long long ti_old, float dx_max[2]);
+int oracle_drift(const oracle_iparams *ip, const oracle_eos *eos, oracle_istate *s, long long ti_old,
+                 float dx_max[2]);
+/* which = 1: runner_do_kick1 (starting particles, first half step of their bin);
+ * which = 2: runner_do_kick2 (active particles, second half) + hydro_reset_predicted_values */
+int ref_kick(const oracle_iparams *ip, oracle_istate *s, int which);
+int oracle_kick(const oracle_iparams *ip, const oracle_eos *eos, oracle_istate *s, int which);
+/* runner_do_timestep on the active particles: new time_bin; ti_end_min = min(ti_current + new step),
+ * updated = particles that got a new step.  Returns 2 when a particle wants a step below dt_min. */
+int ref_timestep(const oracle_iparams *ip, oracle_istate *s, long long *ti_end_min, long long *updated);
+int oracle_timestep(const oracle_iparams *ip, oracle_istate *s, long long *ti_end_min, long long *updated);
 
 #ifdef __cplusplus
 }

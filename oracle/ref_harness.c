@@ -170,10 +170,13 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
     c->hydro.parts = &parts[cd[k].first];
     c->hydro.xparts = &xparts[cd[k].first];
     c->hydro.count = cd[k].count;
-    float h_max = 0.f;
-    for (int j = 0; j < c->hydro.count; j++) h_max = max(h_max, c->hydro.parts[j].h);
+    float h_max = 0.f, h_max_old = 0.f;
+    for (int j = 0; j < c->hydro.count; j++) {
+      h_max = max(h_max, c->hydro.parts[j].h);
+      h_max_old = max(h_max_old, io->in_h_build ? io->in_h_build[cd[k].first + j] : c->hydro.parts[j].h);
+    }
     c->hydro.h_max = h_max;
-    c->hydro.h_max_old = h_max;
+    c->hydro.h_max_old = h_max_old;
     c->hydro.h_max_active = h_max;
     c->hydro.ti_old_part = ti_current;
     c->hydro.ti_end_min = cell_has_active(c, &engine) ? ti_current : 2 * ti_current;
@@ -301,6 +304,181 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
   free(cells);
   free(parts);
   free(xparts);
+  return 0;
+}
+
+/* ---- time integration ---------------------------------- */
+/* The reference's own cell_drift_part / runner_do_kick1 / runner_do_kick2 / runner_do_timestep run
+ * on ONE fake leaf cell holding all particles (these tasks are per particle: the cell only
+ * carries the loop and the min/max reductions). */
+#include "cell.h"
+#include "entropy_floor.h"
+
+typedef struct {
+  struct space space;
+  struct hydro_props hp;
+  struct cosmology cosmo;
+  struct phys_const pc;
+  struct engine engine;
+  struct lightcone_array_props lcp;
+  struct pressure_floor_props pfloor;
+  struct entropy_floor_properties efloor;
+  struct runner runner;
+  struct cell cell;
+  struct part *parts;
+  struct xpart *xparts;
+} ienv;
+
+static ienv *ienv_make(const oracle_iparams *ip, const oracle_istate *s) {
+  ienv *v = NULL;
+  if (posix_memalign((void **)&v, 128, sizeof(ienv)) != 0) return NULL;
+  bzero(v, sizeof(*v));
+  const int n = s->n;
+  if (posix_memalign((void **)&v->parts, part_align, (size_t)(n + 1) * sizeof(struct part)) != 0) return NULL;
+  if (posix_memalign((void **)&v->xparts, xpart_align, (size_t)(n + 1) * sizeof(struct xpart)) != 0) return NULL;
+  bzero(v->parts, (size_t)(n + 1) * sizeof(struct part));
+  bzero(v->xparts, (size_t)(n + 1) * sizeof(struct xpart));
+  v->space.periodic = 1; /* nobody is removed for leaving the box (cell_drift.c:274) */
+  for (int d = 0; d < 3; d++) v->space.dim[d] = 1.0;
+  hydro_space_init(&v->space.hs, &v->space);
+  v->pc.const_vacuum_permeability = 1.0;
+  hydro_props_init_no_hydro(&v->hp);
+  v->hp.CFL_condition = ip->cfl_condition;
+  v->hp.log_max_h_change = ip->log_max_h_change;
+  v->hp.minimal_internal_energy = ip->minimal_internal_energy;
+  v->hp.h_max = ip->h_max;
+  v->hp.h_min = ip->h_min;
+  cosmology_init_no_cosmo(&v->cosmo);
+  struct engine *e = &v->engine;
+  e->hydro_properties = &v->hp;
+  e->physical_constants = &v->pc;
+  e->s = &v->space;
+  e->cosmology = &v->cosmo;
+  e->lightcone_array_properties = &v->lcp;
+  e->pressure_floor_props = &v->pfloor;
+  e->entropy_floor = &v->efloor;
+  e->policy = engine_policy_hydro;
+  e->time_base = ip->time_base;
+  e->time_base_inv = 1.0 / ip->time_base;
+  e->dt_min = ip->dt_min;
+  e->dt_max = ip->dt_max;
+  e->dt_max_RMS_displacement = FLT_MAX;
+  e->ti_current = ip->ti_current;
+  e->max_active_bin = ip->max_active_bin;
+  e->nodeID = 0;
+  v->space.e = e;
+  v->runner.e = e;
+#ifdef PLANETARY_SPH
+  ref_planetary_eos_init();
+#endif
+  for (int k = 0; k < n; k++) {
+    struct part *p = &v->parts[k];
+    struct xpart *xp = &v->xparts[k];
+    for (int d = 0; d < 3; d++) {
+      p->x[d] = s->x[3 * k + d];
+      p->v[d] = s->v[3 * k + d];
+      xp->v_full[d] = s->v_full[3 * k + d];
+      p->a_hydro[d] = s->a[3 * k + d];
+      xp->x_diff[d] = s->x_diff[3 * k + d];
+      xp->x_diff_sort[d] = s->x_diff_sort[3 * k + d];
+    }
+    p->u = s->u[k];
+    xp->u_full = s->u_full[k];
+    p->h = s->h[k];
+    p->rho = s->rho[k];
+    p->force.pressure = s->pressure[k];
+    p->force.soundspeed = s->soundspeed[k];
+    p->force.v_sig = s->v_sig[k];
+    p->u_dt = s->u_dt[k];
+    p->force.h_dt = s->h_dt[k];
+    p->time_bin = s->time_bin[k];
+    p->limiter_data.min_ngb_time_bin = s->min_ngb_time_bin ? s->min_ngb_time_bin[k] : num_time_bins + 1;
+    p->limiter_data.wakeup = time_bin_not_awake;
+    p->mass = 1.f;
+    p->id = k;
+#ifdef PLANETARY_SPH
+    p->mat_id = s->mat_id ? s->mat_id[k] : 0;
+#endif
+  }
+  struct cell *c = &v->cell;
+  c->hydro.parts = v->parts;
+  c->hydro.xparts = v->xparts;
+  c->hydro.count = n;
+  c->split = 0;
+  c->nodeID = 0;
+  c->top = c;
+  c->super = c;
+  c->hydro.super = c;
+  c->width[0] = c->width[1] = c->width[2] = 1.0;
+  c->dmin = 1.0;
+  return v;
+}
+
+static void ienv_store(ienv *v, oracle_istate *s) {
+  for (int k = 0; k < s->n; k++) {
+    const struct part *p = &v->parts[k];
+    const struct xpart *xp = &v->xparts[k];
+    for (int d = 0; d < 3; d++) {
+      s->x[3 * k + d] = p->x[d];
+      s->v[3 * k + d] = p->v[d];
+      s->v_full[3 * k + d] = xp->v_full[d];
+      s->a[3 * k + d] = p->a_hydro[d];
+      s->x_diff[3 * k + d] = xp->x_diff[d];
+      s->x_diff_sort[3 * k + d] = xp->x_diff_sort[d];
+    }
+    s->u[k] = p->u;
+    s->u_full[k] = xp->u_full;
+    s->h[k] = p->h;
+    s->rho[k] = p->rho;
+    s->pressure[k] = p->force.pressure;
+    s->soundspeed[k] = p->force.soundspeed;
+    s->v_sig[k] = p->force.v_sig;
+    s->u_dt[k] = p->u_dt;
+    s->h_dt[k] = p->force.h_dt;
+    s->time_bin[k] = p->time_bin;
+  }
+  free(v->parts);
+  free(v->xparts);
+  free(v);
+}
+
+int ref_drift(const oracle_iparams *ip, oracle_istate *s, long long ti_old, float dx_max[2]) {
+  ienv *v = ienv_make(ip, s);
+  if (v == NULL) return 1;
+  /* nobody is "active" during the drift itself: cell_drift.c:342 would otherwise zero the density
+   * sums of the active particles (hydro_init_part), which the caller does at the start of the step */
+  v->engine.max_active_bin = -1;
+  v->cell.hydro.ti_old_part = ti_old;
+  cell_drift_part(&v->cell, &v->engine, /*force=*/1, NULL);
+  dx_max[0] = v->cell.hydro.dx_max_part;
+  dx_max[1] = v->cell.hydro.dx_max_sort;
+  ienv_store(v, s);
+  return 0;
+}
+
+int ref_kick(const oracle_iparams *ip, oracle_istate *s, int which) {
+  ienv *v = ienv_make(ip, s);
+  if (v == NULL) return 1;
+  /* make the cell pass cell_is_starting_hydro / cell_is_active_hydro (src/active.h) */
+  v->cell.hydro.ti_beg_max = ip->ti_current;
+  v->cell.hydro.ti_end_min = ip->ti_current;
+  v->space.periodic = 0; /* no mesh-gravity kick (runner_time_integration.c:125: e->mesh is not set up) */
+  if (which == 1)
+    runner_do_kick1(&v->runner, &v->cell, 0);
+  else
+    runner_do_kick2(&v->runner, &v->cell, 0);
+  ienv_store(v, s);
+  return 0;
+}
+
+int ref_timestep(const oracle_iparams *ip, oracle_istate *s, long long *ti_end_min, long long *updated) {
+  ienv *v = ienv_make(ip, s);
+  if (v == NULL) return 1;
+  v->cell.hydro.ti_end_min = ip->ti_current;
+  runner_do_timestep(&v->runner, &v->cell, 0);
+  *ti_end_min = v->cell.hydro.ti_end_min;
+  *updated = v->cell.hydro.updated;
+  ienv_store(v, s);
   return 0;
 }
 

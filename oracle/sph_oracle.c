@@ -1466,13 +1466,15 @@ int oracle_run_step(const oracle_params *prm, const oracle_eos *eos, oracle_part
     o->depth = cd[k].depth;
     o->split = cd[k].split;
     for (int j = 0; j < 8; j++) o->progeny[j] = cd[k].progeny[j];
-    float hm = 0.f;
+    float hm = 0.f, hm_old = 0.f;
     int act = 0;
     for (int j = 0; j < o->count; j++) {
       hm = fmax_f(hm, c.parts[o->first + j].h);
+      hm_old = fmax_f(hm_old, io->in_h_build ? io->in_h_build[o->first + j] : c.parts[o->first + j].h);
       act |= part_active(&c, &c.parts[o->first + j]);
     }
-    o->h_max = o->h_max_old = o->h_max_active = hm;
+    o->h_max = o->h_max_active = hm;
+    o->h_max_old = hm_old;
     o->active = act;
   }
   for (int t = 0; t < ntasks; t++) {
@@ -1547,4 +1549,194 @@ int oracle_run_step(const oracle_params *prm, const oracle_eos *eos, oracle_part
   free(c.cells);
   free(c.parts);
   return ghost_failed ? 3 : 0;
+}
+
+/* ------------------------------------------------------------------------ */
+/* Time integration either side of the path              */
+/* ------------------------------------------------------------------------ */
+#define NUM_TIME_BINS 56                 /* src/timeline.h:36 */
+#define MAX_NR_TIMESTEPS (1LL << (NUM_TIME_BINS + 1))
+#define MAX_DELTA_BIN 2                  /* time_bin_neighbour_max_delta_bin, timeline.h:51 */
+
+/* src/timeline.h:59-63, 78-83, 107-114, 126-138 */
+static inline long long int_timestep(int bin) { return bin <= 0 ? 0 : 1LL << (bin + 1); }
+static inline int time_bin_of(long long dti) { return 62 - __builtin_clzll((unsigned long long)dti); }
+static inline long long int_time_begin(long long ti_current, int bin) {
+  const long long dti = int_timestep(bin);
+  return dti == 0 ? 0 : dti * ((ti_current - 1) / dti);
+}
+static inline long long int_time_end(long long ti_current, int bin) {
+  const long long dti = int_timestep(bin);
+  if (dti == 0) return 0;
+  const long long mod = ti_current % dti;
+  return mod == 0 ? ti_current : ti_current - mod + dti;
+}
+
+/* src/approx_math.h:35-37 */
+static inline float approx_expf(float x) { return 1.f + x * (1.f + x * (0.5f + x * (1.f / 6.f + 1.f / 24.f * x))); }
+
+static void ieos(const oracle_iparams *ip, const oracle_eos *eos, float rho, float u, int mat_id, float *P, float *cs) {
+  oracle_params prm;
+  memset(&prm, 0, sizeof(prm));
+  prm.scheme = ip->scheme;
+  octx c;
+  memset(&c, 0, sizeof(c));
+  c.prm = &prm;
+  c.eos = eos;
+  opart p;
+  memset(&p, 0, sizeof(p));
+  p.rho = rho;
+  p.u = u;
+  p.mat_id = mat_id;
+  eos_eval(&c, &p, P, cs);
+}
+
+/* drift_part (src/drift.h:186-214) with hydro_predict_extra (Minimal/hydro.h:815-866,
+ * Planetary/hydro.h:823-870), then the tail of the particle loop of cell_drift_part
+ * (src/cell_drift.c:303-318, 359-360). */
+int oracle_drift(const oracle_iparams *ip, const oracle_eos *eos, oracle_istate *s, long long ti_old,
+                 float dx_max[2]) {
+  const double dt = (double)(ip->ti_current - ti_old) * ip->time_base; /* drift, kick_hydro and therm alike */
+  const int planetary = ip->scheme == ORACLE_SCHEME_PLANETARY;
+  float dx2_max = 0.f, dx2_max_sort = 0.f;
+  for (int k = 0; k < s->n; k++) {
+    for (int d = 0; d < 3; d++) {
+      s->x[3 * k + d] += s->v_full[3 * k + d] * dt;
+      s->v[3 * k + d] += s->a[3 * k + d] * dt;
+    }
+    const float dt_drift = dt, dt_therm = dt;
+    float u = s->u[k];
+    u += s->u_dt[k] * dt_therm;
+    const float min_u = ip->minimal_internal_energy / 1.0; /* cosmo->a_factor_internal_energy = 1 */
+    if (planetary) u = u > min_u ? u : min_u;
+    const float h_inv = 1.f / s->h[k];
+    const float w1 = s->h_dt[k] * h_inv * dt_drift;
+    if (fabsf(w1) < 0.2f)
+      s->h[k] *= approx_expf(w1);
+    else
+      s->h[k] *= expf(w1);
+    const float w2 = -3.f * w1; /* hydro_dimension */
+    if (fabsf(w2) < 0.2f)
+      s->rho[k] *= approx_expf(w2);
+    else
+      s->rho[k] *= expf(w2);
+    if (!planetary) {
+      /* entropy floor "none": floor_A = 0, floor_u = 0 * rho^(gamma-1) / (gamma-1) = 0 */
+      const float floor_u = 0.f;
+      u = u > floor_u ? u : floor_u;
+      u = u > min_u ? u : min_u;
+    }
+    s->u[k] = u;
+    float P, cs;
+    ieos(ip, eos, s->rho[k], u, s->mat_id ? s->mat_id[k] : 0, &P, &cs);
+    s->pressure[k] = P;
+    s->soundspeed[k] = cs;
+    const float two_cs = 2.f * cs;
+    s->v_sig[k] = s->v_sig[k] > two_cs ? s->v_sig[k] : two_cs;
+    for (int d = 0; d < 3; d++) {
+      const float dx = s->v_full[3 * k + d] * dt;
+      s->x_diff[3 * k + d] -= dx;
+      s->x_diff_sort[3 * k + d] -= dx;
+    }
+    /* cell_drift.c:303-304 */
+    s->h[k] = s->h[k] < ip->h_max ? s->h[k] : ip->h_max;
+    s->h[k] = s->h[k] > ip->h_min ? s->h[k] : ip->h_min;
+    const float *xd = &s->x_diff[3 * k], *xs = &s->x_diff_sort[3 * k];
+    const float dx2 = xd[0] * xd[0] + xd[1] * xd[1] + xd[2] * xd[2];
+    dx2_max = dx2_max > dx2 ? dx2_max : dx2;
+    const float dx2s = xs[0] * xs[0] + xs[1] * xs[1] + xs[2] * xs[2];
+    dx2_max_sort = dx2_max_sort > dx2s ? dx2_max_sort : dx2s;
+  }
+  dx_max[0] = sqrtf(dx2_max);
+  dx_max[1] = sqrtf(dx2_max_sort);
+  return 0;
+}
+
+/* kick_part (src/kick.h:244-278) with hydro_kick_extra (Minimal/hydro.h:901-930, Planetary/hydro.h:904-925),
+ * driven as runner_do_kick1 / runner_do_kick2 do (src/runner_time_integration.c:141-180, 412-457);
+ * kick2 ends with hydro_reset_predicted_values (Minimal/hydro.h:771-796, Planetary/hydro.h:778-803). */
+int oracle_kick(const oracle_iparams *ip, const oracle_eos *eos, oracle_istate *s, int which) {
+  const int planetary = ip->scheme == ORACLE_SCHEME_PLANETARY;
+  for (int k = 0; k < s->n; k++) {
+    const int bin = s->time_bin[k];
+    if (bin > ip->max_active_bin) continue; /* part_is_starting / part_is_active */
+    const long long ti_step = int_timestep(bin);
+    long long ti_begin;
+    if (which == 1)
+      ti_begin = int_time_begin(ip->ti_current + 1, bin);
+    else
+      ti_begin = int_time_begin(ip->ti_current, bin) + ti_step / 2;
+    const long long ti_end = ti_begin + ti_step / 2;
+    const double dt = (double)(ti_end - ti_begin) * ip->time_base;
+    for (int d = 0; d < 3; d++) s->v_full[3 * k + d] += s->a[3 * k + d] * dt;
+    const float dt_therm = dt;
+    const float delta_u = s->u_dt[k] * dt_therm;
+    const float ua = s->u_full[k] + delta_u, ub = 0.5f * s->u_full[k];
+    s->u_full[k] = ua > ub ? ua : ub;
+    const float min_u = ip->minimal_internal_energy / 1.0;
+    const float floor_u = 0.f;
+    const float energy_min = planetary ? min_u : (min_u > floor_u ? min_u : floor_u);
+    if (s->u_full[k] < energy_min) {
+      s->u_full[k] = energy_min;
+      s->u_dt[k] = 0.f;
+    }
+    if (which == 2) {
+      for (int d = 0; d < 3; d++) s->v[3 * k + d] = s->v_full[3 * k + d];
+      s->u[k] = s->u_full[k];
+      float P, cs;
+      ieos(ip, eos, s->rho[k], s->u[k], s->mat_id ? s->mat_id[k] : 0, &P, &cs);
+      s->pressure[k] = P;
+      s->soundspeed[k] = cs;
+      const float two_cs = 2.f * cs;
+      s->v_sig[k] = s->v_sig[k] > two_cs ? s->v_sig[k] : two_cs;
+    }
+  }
+  return 0;
+}
+
+/* get_part_timestep + make_integer_timestep (src/timestep.h:45-82, 141-222) for the active particles,
+ * the sync point of the others, as runner_do_timestep does (src/runner_time_integration.c:696-745, 790-800). */
+int oracle_timestep(const oracle_iparams *ip, oracle_istate *s, long long *ti_end_min_out, long long *updated_out) {
+  const double time_base_inv = 1.0 / ip->time_base;
+  long long ti_end_min = MAX_NR_TIMESTEPS, updated = 0;
+  int status = 0;
+  for (int k = 0; k < s->n; k++) {
+    const int old_bin = s->time_bin[k];
+    if (old_bin > ip->max_active_bin) {
+      const long long ti_end = int_time_end(ip->ti_current, old_bin);
+      ti_end_min = ti_end < ti_end_min ? ti_end : ti_end_min;
+      continue;
+    }
+    /* hydro_compute_timestep (Minimal/hydro.h:440-452): cosmo->a and a_factor_sound_speed are doubles (= 1) */
+    const float dt_cfl = 2.f * K_GAMMA * ip->cfl_condition * 1.0 * s->h[k] / (1.0 * s->v_sig[k]);
+    float new_dt = dt_cfl;
+    const float dt_h_change =
+        (s->h_dt[k] != 0.0f) ? fabsf(ip->log_max_h_change * s->h[k] / s->h_dt[k]) : FLT_MAX;
+    new_dt = new_dt < dt_h_change ? new_dt : dt_h_change;
+    new_dt = new_dt < FLT_MAX ? new_dt : FLT_MAX; /* dt_max_RMS_displacement */
+    new_dt *= 1.0;                                /* cosmology->time_step_factor */
+    new_dt = (double)new_dt < ip->dt_max ? (double)new_dt : ip->dt_max;
+    if (new_dt < ip->dt_min) status = 2;
+    long long new_dti = (long long)(new_dt * time_base_inv);
+    int new_bin = (signed char)time_bin_of(new_dti);
+    const int ngb = (s->min_ngb_time_bin ? s->min_ngb_time_bin[k] : NUM_TIME_BINS + 1) + MAX_DELTA_BIN;
+    new_bin = (signed char)(new_bin < ngb ? new_bin : ngb);
+    new_dti = int_timestep(new_bin);
+    const long long current_dti = int_timestep(old_bin);
+    const long long ti_end = int_time_end(ip->ti_current, old_bin);
+    if (old_bin > 0) new_dti = new_dti < 2 * current_dti ? new_dti : 2 * current_dti;
+    long long dti_timeline = MAX_NR_TIMESTEPS;
+    while (new_dti < dti_timeline) dti_timeline /= 2LL;
+    new_dti = dti_timeline;
+    if (new_dti > current_dti) {
+      if ((MAX_NR_TIMESTEPS - ti_end) % new_dti > 0) new_dti = current_dti;
+    }
+    s->time_bin[k] = (signed char)time_bin_of(new_dti);
+    updated++;
+    const long long t = ip->ti_current + new_dti;
+    ti_end_min = t < ti_end_min ? t : ti_end_min;
+  }
+  *ti_end_min_out = ti_end_min;
+  *updated_out = updated;
+  return status;
 }

@@ -96,6 +96,22 @@ class Timings(C.Structure):
                 ("total_ms", C.c_float)]
 
 
+class Integrator(C.Structure):
+    # field order must match swift_cuda_integrator
+    _fields_ = [("cfl_condition", C.c_float), ("log_max_h_change", C.c_float), ("minimal_internal_energy", C.c_float),
+                ("dt_min", C.c_double), ("dt_max", C.c_double), ("time_base", C.c_double)]
+
+
+STATE_FIELDS = [("x", 3), ("v", 3), ("v_full", 3), ("u", 1), ("u_full", 1), ("h", 1), ("rho", 1), ("pressure", 1),
+                ("soundspeed", 1), ("v_sig", 1), ("a", 3), ("u_dt", 1), ("h_dt", 1), ("x_diff", 3), ("x_diff_sort", 3)]
+
+
+class StateOut(C.Structure):
+    # field order must match swift_cuda_state_out
+    _fields_ = [("x", C.POINTER(C.c_double))] + [(k, _FP) for k, _ in STATE_FIELDS[1:]] + \
+               [("time_bin", C.POINTER(C.c_int8)), ("min_ngb_time_bin", C.POINTER(C.c_int8))]
+
+
 EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error", "swift_cuda_create", "swift_cuda_destroy",
            "swift_cuda_build_from_particles", "swift_cuda_build_from_cells", "swift_cuda_update_particles",
            "swift_cuda_restore_particles", "swift_cuda_set_transfer_count",
@@ -105,7 +121,9 @@ EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error
            "swift_cuda_get_tree_size", "swift_cuda_get_tree", "swift_cuda_record_pairs", "swift_cuda_fetch_pairs",
            "swift_cuda_halo_pack", "swift_cuda_halo_unpack", "swift_cuda_halo_bytes_per_particle",
            "swift_cuda_get_touched", "swift_cuda_refresh_cell_hmax",
-           "swift_cuda_host_plan", "swift_cuda_host_free"]
+           "swift_cuda_host_plan", "swift_cuda_host_free",
+           "swift_cuda_integrator_init", "swift_cuda_set_time", "swift_cuda_drift", "swift_cuda_kick",
+           "swift_cuda_timestep", "swift_cuda_reset_offsets", "swift_cuda_get_state"]
 
 _lib = None
 
@@ -125,6 +143,11 @@ def load_library():
         lib.swift_cuda_destroy.argtypes = [C.c_void_p]
         lib.swift_cuda_record_pairs.argtypes = [C.c_void_p, C.c_longlong]
         lib.swift_cuda_fetch_pairs.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_longlong, C.c_void_p]
+        lib.swift_cuda_set_time.argtypes = [C.c_void_p, C.c_longlong, C.c_int]
+        lib.swift_cuda_drift.argtypes = [C.c_void_p, C.c_longlong, C.c_void_p]
+        lib.swift_cuda_kick.argtypes = [C.c_void_p, C.c_int]
+        lib.swift_cuda_timestep.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.swift_cuda_reset_offsets.argtypes = [C.c_void_p, C.c_int]
         _lib = lib
     return _lib
 
@@ -296,6 +319,51 @@ class HydroBackend:
     def runner_do_force(self):
         """All runner_do{self,pair}2_branch_force tasks + runner_do_end_hydro_force."""
         self._check(self.lib.swift_cuda_do_force(self.ctx))
+
+    # ---- time integration (SURVEY.md 8(f) N3): the particles stay on the device across steps ----
+    def integrator_init(self, cfl_condition, log_max_h_change, minimal_internal_energy, dt_min, dt_max, time_base,
+                        **_ignored):
+        """hydro_first_init_part on the device copy; the constants of e->hydro_properties / e->dt_* / e->time_base."""
+        p = Integrator(cfl_condition, log_max_h_change, minimal_internal_energy, dt_min, dt_max, time_base)
+        self._check(self.lib.swift_cuda_integrator_init(self.ctx, C.byref(p)))
+
+    def set_time(self, ti_current, max_active_bin):
+        self._check(self.lib.swift_cuda_set_time(self.ctx, ti_current, max_active_bin))
+
+    def drift(self, ti_old):
+        """runner_do_drift_part on every particle up to the current time; returns (dx_max_part, dx_max_sort)."""
+        dx = (C.c_float * 2)()
+        self._check(self.lib.swift_cuda_drift(self.ctx, ti_old, dx))
+        return float(dx[0]), float(dx[1])
+
+    def kick(self, which):
+        """which = 1: runner_do_kick1, 2: runner_do_kick2 (+ hydro_reset_predicted_values)."""
+        self._check(self.lib.swift_cuda_kick(self.ctx, which))
+
+    def timestep(self):
+        """runner_do_timestep; returns (ti_end_min, updated)."""
+        t, u = C.c_longlong(0), C.c_longlong(0)
+        self._check(self.lib.swift_cuda_timestep(self.ctx, C.byref(t), C.byref(u)))
+        return t.value, u.value
+
+    def reset_offsets(self, what=1):
+        self._check(self.lib.swift_cuda_reset_offsets(self.ctx, what))
+
+    def state(self):
+        """Every per-particle field of the device state, caller order."""
+        n = self.n
+        out = {k: np.zeros((n, w) if w > 1 else n, dtype=np.float64 if k == "x" else np.float32)
+               for k, w in STATE_FIELDS}
+        out["time_bin"] = np.zeros(n, dtype=np.int8)
+        out["min_ngb_time_bin"] = np.zeros(n, dtype=np.int8)
+        S = StateOut()
+        S.x = out["x"].ctypes.data_as(C.POINTER(C.c_double))
+        for k, _ in STATE_FIELDS[1:]:
+            setattr(S, k, out[k].ctypes.data_as(_FP))
+        S.time_bin = out["time_bin"].ctypes.data_as(C.POINTER(C.c_int8))
+        S.min_ngb_time_bin = out["min_ngb_time_bin"].ctypes.data_as(C.POINTER(C.c_int8))
+        self._check(self.lib.swift_cuda_get_state(self.ctx, C.byref(S)))
+        return out
 
     # ---- results ----
     def alloc_results(self, first_pass=False, pinned=False):

@@ -1,0 +1,311 @@
+// Time integration either side of the neighbour loops: drift, kick and time-step
+// as per-particle kernels on the SoA state the loops already keep in HBM, so that the particles stay
+// resident on the device across steps.  Restates, per particle,
+//   drift_part                      src/drift.h:143-233   (+ hydro_predict_extra, Minimal/hydro.h:815-866,
+//                                                           Planetary/hydro.h:823-870; tail of the loop of
+//                                                           cell_drift_part, src/cell_drift.c:303-318)
+//   kick_part                       src/kick.h:215-279    (+ hydro_kick_extra, Minimal/hydro.h:901-930,
+//                                                           Planetary/hydro.h:904-925) as driven by
+//   runner_do_kick1 / runner_do_kick2   src/runner_time_integration.c:141-180, 412-457
+//                                   (kick2 ends with hydro_reset_predicted_values, Minimal/hydro.h:771-796)
+//   runner_do_timestep              src/runner_time_integration.c:696-745, 790-800 with get_part_timestep and
+//                                   make_integer_timestep (src/timestep.h:45-82, 141-222)
+// without cosmology (a = 1), gravity, cooling or the time-step limiter.  All three are HBM-bound streaming
+// kernels (one thread per particle, 16-byte vector accesses); arithmetic is in the reference's types
+// and operand order, products with the double time steps in f64, so the results are bit-identical.
+#pragma once
+#include "kernels.cuh"
+
+namespace swiftcuda {
+
+constexpr int kMaxDeltaBin = 2;  // time_bin_neighbour_max_delta_bin, src/timeline.h:51
+constexpr long long kMaxNrTimesteps = 1LL << (kNumTimeBins + 1);
+
+struct IntegPrm {
+  float cfl, log_max_h_change, min_u;
+  double dt_min, dt_max, time_base, time_base_inv;
+  long long ti_current;
+};
+
+struct IntegDev {
+  float4 *vu_full;        // xp->v_full[3], xp->u_full
+  float4 *xdiff;          // xp->x_diff[3]
+  float4 *xdiff_sort;     // xp->x_diff_sort[3]
+  unsigned *dx2_max;      // [2] bit images of the (non-negative) maxima of |x_diff|^2, |x_diff_sort|^2
+  unsigned long long *ti_end_min;
+  unsigned long long *updated;
+  int *too_small;         // particles that want a step below dt_min
+};
+
+// src/timeline.h:59-63, 78-83, 107-114, 126-138
+__device__ __forceinline__ long long int_timestep(int bin) { return bin <= 0 ? 0 : 1LL << (bin + 1); }
+__device__ __forceinline__ int time_bin_of(long long dti) { return 62 - __clzll(dti); }
+__device__ __forceinline__ long long int_time_begin(long long ti_current, int bin) {
+  const long long dti = int_timestep(bin);
+  return dti == 0 ? 0 : dti * ((ti_current - 1) / dti);
+}
+__device__ __forceinline__ long long int_time_end(long long ti_current, int bin) {
+  const long long dti = int_timestep(bin);
+  if (dti == 0) return 0;
+  const long long mod = ti_current % dti;
+  return mod == 0 ? ti_current : ti_current - mod + dti;
+}
+
+// src/approx_math.h:35-37
+__device__ __forceinline__ float approx_expf(float x) {
+  const float c = __fadd_rn(1.f / 6.f, __fmul_rn(1.f / 24.f, x));
+  const float b = __fadd_rn(0.5f, __fmul_rn(x, c));
+  const float a = __fadd_rn(1.f, __fmul_rn(x, b));
+  return __fadd_rn(1.f, __fmul_rn(x, a));
+}
+
+// expf as glibc >= 2.27 computes it (sysdeps/ieee754/flt-32/e_expf.c with the 32-entry table of
+// exp2f_data.c: x * 32 / ln2 = k + r, 2^(k/32) from the table, a cubic in r, all in double, one
+// rounding to float).  The reference calls libm's expf when a drift changes h by more than ~20 %
+// (|w| >= 0.2); CUDA's expf differs from it in the last bit for ~1 argument in 10.
+__device__ const unsigned long long kExp2fTab[32] = {
+      0x3ff0000000000000ULL, 0x3fefd9b0d3158574ULL, 0x3fefb5586cf9890fULL, 0x3fef9301d0125b51ULL,
+      0x3fef72b83c7d517bULL, 0x3fef54873168b9aaULL, 0x3fef387a6e756238ULL, 0x3fef1e9df51fdee1ULL,
+      0x3fef06fe0a31b715ULL, 0x3feef1a7373aa9cbULL, 0x3feedea64c123422ULL, 0x3feece086061892dULL,
+      0x3feebfdad5362a27ULL, 0x3feeb42b569d4f82ULL, 0x3feeab07dd485429ULL, 0x3feea47eb03a5585ULL,
+      0x3feea09e667f3bcdULL, 0x3fee9f75e8ec5f74ULL, 0x3feea11473eb0187ULL, 0x3feea589994cce13ULL,
+      0x3feeace5422aa0dbULL, 0x3feeb737b0cdc5e5ULL, 0x3feec49182a3f090ULL, 0x3feed503b23e255dULL,
+      0x3feee89f995ad3adULL, 0x3feeff76f2fb5e47ULL, 0x3fef199bdd85529cULL, 0x3fef3720dcef9069ULL,
+      0x3fef5818dcfba487ULL, 0x3fef7c97337b9b5fULL, 0x3fefa4afa2a490daULL, 0x3fefd0765b6e4540ULL};
+__device__ float expf_glibc(float x) {
+  if (!(fabsf(x) < 88.f)) return expf(x);  // overflow, underflow, inf, nan: not reached by a drift
+  const double inv_ln2_n = 0x1.71547652b82fep+0 * 32.0, shift = 0x1.8p+52;
+  const double c0 = 0x1.c6af84b912394p-5 / 32.0 / 32.0 / 32.0, c1 = 0x1.ebfce50fac4f3p-3 / 32.0 / 32.0,
+               c2 = 0x1.62e42ff0c52d6p-1 / 32.0;
+  const double z = __dmul_rn(inv_ln2_n, (double)x);
+  double kd = __dadd_rn(z, shift);
+  const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
+  kd = __dsub_rn(kd, shift);
+  const double r = __dsub_rn(z, kd);
+  const double s = __longlong_as_double((long long)(kExp2fTab[ki & 31] + (ki << 47)));
+  const double zz = __dadd_rn(__dmul_rn(c0, r), c1);
+  const double r2 = __dmul_rn(r, r);
+  double y = __dadd_rn(__dmul_rn(c2, r), 1.0);
+  y = __dadd_rn(__dmul_rn(zz, r2), y);
+  return (float)__dmul_rn(y, s);
+}
+
+// v += a * dt with a float accumulator and a double dt: (float)((double)v + (double)a * dt)
+__device__ __forceinline__ float kick_f(float v, float a, double dt) {
+  return (float)__dadd_rn((double)v, __dmul_rn((double)a, dt));
+}
+
+// hydro_first_init_part (Minimal/hydro.h:983-995): v_full = v, u_full = u; offsets since the last rebuild = 0
+__global__ void k_integ_init(Dev d, IntegDev g) {
+  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p >= d.n) return;
+  const float4 vm = d.vm[p];
+  g.vu_full[p] = make_float4(vm.x, vm.y, vm.z, d.u[p]);
+  g.xdiff[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+  g.xdiff_sort[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// Every particle from ti_old to ti_current (engine_policy_drift_all).  dt = (ti_current - ti_old) *
+// time_base is at once dt_drift, dt_kick_hydro and dt_therm (cell_drift.c:232-236, no cosmology).
+__global__ void k_drift(Dev d, IntegDev g, IntegPrm ip, double dt) {
+  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  float dx2 = 0.f, dx2s = 0.f;
+  if (p < d.n) {
+    const bool planetary = kc.scheme == SWIFT_CUDA_SCHEME_PLANETARY;
+    const float4 vf = g.vu_full[p];
+    PosD *pos = const_cast<PosD *>(d.pos);
+    PosD q = pos[p];
+    q.x = __dadd_rn(q.x, __dmul_rn((double)vf.x, dt));
+    q.y = __dadd_rn(q.y, __dmul_rn((double)vf.y, dt));
+    q.z = __dadd_rn(q.z, __dmul_rn((double)vf.z, dt));
+    pos[p] = q;
+    const float4 acc = d.acc[p];  // a_hydro, u_dt
+    float4 vm = d.vm[p];
+    vm.x = kick_f(vm.x, acc.x, dt);
+    vm.y = kick_f(vm.y, acc.y, dt);
+    vm.z = kick_f(vm.z, acc.z, dt);
+    d.vm[p] = vm;
+    // hydro_predict_extra
+    const float dtf = (float)dt;
+    float *up = const_cast<float *>(d.u);
+    float u = __fadd_rn(up[p], __fmul_rn(acc.w, dtf));
+    if (planetary) u = u > ip.min_u ? u : ip.min_u;
+    float h = d.h[p];
+    const float h_inv = 1.f / h;
+    const float w1 = __fmul_rn(__fmul_rn(d.h_dt[p], h_inv), dtf);
+    h = __fmul_rn(h, fabsf(w1) < 0.2f ? approx_expf(w1) : expf_glibc(w1));
+    float4 fin = d.fin[p];  // rho, P, f, c
+    const float w2 = __fmul_rn(-3.f, w1);
+    fin.x = __fmul_rn(fin.x, fabsf(w2) < 0.2f ? approx_expf(w2) : expf_glibc(w2));
+    if (!planetary) {
+      u = u > 0.f ? u : 0.f;  // entropy floor "none": floor_u = 0
+      u = u > ip.min_u ? u : ip.min_u;
+    }
+    up[p] = u;
+    float P, cs;
+    eos_eval(fin.x, u, planetary ? d.mat_id[p] : 0, P, cs);
+    fin.y = P;
+    fin.w = cs;
+    d.fin[p] = fin;
+    const float two_cs = __fmul_rn(2.f, cs);
+    const float vs = d.v_sig[p];
+    d.v_sig[p] = vs > two_cs ? vs : two_cs;
+    // offsets since the last rebuild / sort
+    const float ox = (float)__dmul_rn((double)vf.x, dt), oy = (float)__dmul_rn((double)vf.y, dt),
+                oz = (float)__dmul_rn((double)vf.z, dt);
+    float4 xd = g.xdiff[p], xs = g.xdiff_sort[p];
+    xd.x = __fsub_rn(xd.x, ox); xd.y = __fsub_rn(xd.y, oy); xd.z = __fsub_rn(xd.z, oz);
+    xs.x = __fsub_rn(xs.x, ox); xs.y = __fsub_rn(xs.y, oy); xs.z = __fsub_rn(xs.z, oz);
+    g.xdiff[p] = xd;
+    g.xdiff_sort[p] = xs;
+    // cell_drift.c:303-304
+    h = h < kc.h_max ? h : kc.h_max;
+    h = h > kc.h_min ? h : kc.h_min;
+    d.h[p] = h;
+    float4 hb = d.hb[p];  // the force neighbour record follows: h, balsara, time_bin, P / rho^2
+    hb.x = h;
+    hb.w = P / (fin.x * fin.x);
+    d.hb[p] = hb;
+    dx2 = __fadd_rn(__fadd_rn(__fmul_rn(xd.x, xd.x), __fmul_rn(xd.y, xd.y)), __fmul_rn(xd.z, xd.z));
+    dx2s = __fadd_rn(__fadd_rn(__fmul_rn(xs.x, xs.x), __fmul_rn(xs.y, xs.y)), __fmul_rn(xs.z, xs.z));
+  }
+  // max over the block, then one atomic each (non-negative floats order like their bit images)
+  for (int o = 16; o > 0; o >>= 1) {
+    dx2 = fmaxf(dx2, __shfl_xor_sync(0xffffffffu, dx2, o));
+    dx2s = fmaxf(dx2s, __shfl_xor_sync(0xffffffffu, dx2s, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (dx2 > 0.f) atomicMax(&g.dx2_max[0], __float_as_uint(dx2));
+    if (dx2s > 0.f) atomicMax(&g.dx2_max[1], __float_as_uint(dx2s));
+  }
+}
+
+// which = 1: first half-kick of the step that starts now (runner_do_kick1, starting particles);
+// which = 2: second half-kick of the step that ends now (runner_do_kick2, active particles), then
+// hydro_reset_predicted_values.
+__global__ void k_kick(Dev d, IntegDev g, IntegPrm ip, int which) {
+  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p >= d.n) return;
+  const int bin = d.time_bin[p];
+  if (bin > kc.max_active_bin) return;
+  const bool planetary = kc.scheme == SWIFT_CUDA_SCHEME_PLANETARY;
+  const long long ti_step = int_timestep(bin);
+  const long long ti_begin =
+      which == 1 ? int_time_begin(ip.ti_current + 1, bin) : int_time_begin(ip.ti_current, bin) + ti_step / 2;
+  const long long ti_end = ti_begin + ti_step / 2;
+  const double dt = __dmul_rn((double)(ti_end - ti_begin), ip.time_base);
+  float4 acc = d.acc[p];
+  float4 vf = g.vu_full[p];
+  vf.x = kick_f(vf.x, acc.x, dt);
+  vf.y = kick_f(vf.y, acc.y, dt);
+  vf.z = kick_f(vf.z, acc.z, dt);
+  // hydro_kick_extra
+  const float delta_u = __fmul_rn(acc.w, (float)dt);
+  const float ua = __fadd_rn(vf.w, delta_u), ub = __fmul_rn(0.5f, vf.w);
+  vf.w = ua > ub ? ua : ub;
+  const float energy_min = planetary ? ip.min_u : (ip.min_u > 0.f ? ip.min_u : 0.f);
+  if (vf.w < energy_min) {
+    vf.w = energy_min;
+    acc.w = 0.f;
+    d.acc[p] = acc;
+  }
+  g.vu_full[p] = vf;
+  if (which == 2) {
+    float4 vm = d.vm[p];
+    vm.x = vf.x; vm.y = vf.y; vm.z = vf.z;
+    d.vm[p] = vm;
+    const_cast<float *>(d.u)[p] = vf.w;
+    float4 fin = d.fin[p];
+    float P, cs;
+    eos_eval(fin.x, vf.w, planetary ? d.mat_id[p] : 0, P, cs);
+    fin.y = P;
+    fin.w = cs;
+    d.fin[p] = fin;
+    float4 hb = d.hb[p];
+    hb.w = P / (fin.x * fin.x);
+    d.hb[p] = hb;
+    const float two_cs = __fmul_rn(2.f, cs);
+    const float vs = d.v_sig[p];
+    d.v_sig[p] = vs > two_cs ? vs : two_cs;
+  }
+}
+
+// New time bin of every active particle; the next sync point of the run.
+__global__ void k_timestep(Dev d, IntegDev g, IntegPrm ip) {
+  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  long long t_end = kMaxNrTimesteps;
+  int upd = 0;
+  if (p < d.n) {
+    const int old_bin = d.time_bin[p];
+    if (old_bin > kc.max_active_bin) {
+      t_end = int_time_end(ip.ti_current, old_bin);
+    } else {
+      const float h = d.h[p];
+      // hydro_compute_timestep: cosmo->a and a_factor_sound_speed are doubles (= 1)
+      const float front = __fmul_rn(__fmul_rn(2.f, kc.gamma), ip.cfl);
+      const float dt_cfl = (float)__ddiv_rn(__dmul_rn((double)front, (double)h), (double)d.v_sig[p]);
+      const float h_dt = d.h_dt[p];
+      const float dt_h_change = (h_dt != 0.0f) ? fabsf(__fmul_rn(ip.log_max_h_change, h) / h_dt) : 3.402823466e+38f;
+      float new_dt = dt_cfl < dt_h_change ? dt_cfl : dt_h_change;
+      new_dt = (double)new_dt < ip.dt_max ? new_dt : (float)ip.dt_max;
+      if ((double)new_dt < ip.dt_min) atomicAdd(g.too_small, 1);
+      // make_integer_timestep
+      long long new_dti = (long long)__dmul_rn((double)new_dt, ip.time_base_inv);
+      int new_bin = (signed char)time_bin_of(new_dti);
+      const int ngb = d.min_bin[p] + kMaxDeltaBin;
+      new_bin = (signed char)(new_bin < ngb ? new_bin : ngb);
+      new_dti = int_timestep(new_bin);
+      const long long current_dti = int_timestep(old_bin);
+      const long long ti_end = int_time_end(ip.ti_current, old_bin);
+      if (old_bin > 0) new_dti = new_dti < 2 * current_dti ? new_dti : 2 * current_dti;
+      long long dti_timeline = kMaxNrTimesteps;
+      while (new_dti < dti_timeline) dti_timeline /= 2LL;
+      new_dti = dti_timeline;
+      if (new_dti > current_dti) {
+        if ((kMaxNrTimesteps - ti_end) % new_dti > 0) new_dti = current_dti;
+      }
+      const int bin = time_bin_of(new_dti);
+      const_cast<int8_t *>(d.time_bin)[p] = (int8_t)bin;
+      float4 hb = d.hb[p];
+      hb.z = __int_as_float(bin);
+      d.hb[p] = hb;
+      upd = 1;
+      t_end = ip.ti_current + new_dti;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const long long other = __shfl_xor_sync(0xffffffffu, t_end, o);
+    t_end = other < t_end ? other : t_end;
+  }
+  const unsigned b = __ballot_sync(0xffffffffu, upd);
+  if ((threadIdx.x & 31) == 0) {
+    atomicMin(g.ti_end_min, (unsigned long long)t_end);
+    if (b) atomicAdd(g.updated, (unsigned long long)__popc(b));
+  }
+}
+
+// State inspection: scatter `width` floats per particle from a strided source to caller order.
+__global__ void k_scatter_f32(int64_t n, const int32_t *order, const float *src, int src_stride, int width,
+                              float *dst) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t s = order ? order[k] : k;
+  for (int c = 0; c < width; c++) dst[s * width + c] = src[k * src_stride + c];
+}
+__global__ void k_scatter_pos(int64_t n, const int32_t *order, const PosD *src, double *dst) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t s = order ? order[k] : k;
+  const PosD q = src[k];
+  dst[3 * s] = q.x; dst[3 * s + 1] = q.y; dst[3 * s + 2] = q.z;
+}
+__global__ void k_scatter_bins(int64_t n, const int32_t *order, const int8_t *tb, const int *min_bin, int8_t *dst_tb,
+                               int8_t *dst_min) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t s = order ? order[k] : k;
+  dst_tb[s] = tb[k];
+  dst_min[s] = (int8_t)min_bin[k];
+}
+
+}  // namespace swiftcuda

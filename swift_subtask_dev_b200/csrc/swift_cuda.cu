@@ -1,6 +1,7 @@
 // C ABI of the backend (include/swift_cuda.h): context, device buffers, the
 // launch sequence of one density -> ghost -> force step.  No CPU fallback: every
 // compute entry needs a CUDA device and fails loudly without one.
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -8,6 +9,7 @@
 
 #include "kernels.cuh"
 #include "pack.cuh"
+#include "integrate.cuh"
 
 using namespace swiftcuda;
 
@@ -57,6 +59,11 @@ struct swift_cuda_ctx {
   int64_t *s_id = nullptr;
   float *s_out = nullptr;    // 20 floats per particle
   int8_t *s_out_bin = nullptr;
+  // time integration (swift_cuda_integrator_init)
+  bool all_cells_active = false;   // every cell is in the work lists
+  bool integ_on = false;
+  IntegDev integ = {};
+  IntegPrm iprm = {};
 };
 
 template <typename T>
@@ -93,6 +100,8 @@ size_t swift_cuda_sizeof(int which) {
     case 5: return sizeof(swift_cuda_counters);
     case 6: return sizeof(swift_cuda_timings);
     case 7: return sizeof(swift_cuda_til);
+    case 8: return sizeof(swift_cuda_integrator);
+    case 9: return sizeof(swift_cuda_state_out);
     default: return 0;
   }
 }
@@ -384,6 +393,8 @@ int swift_cuda_build_from_particles(swift_cuda_ctx *c, const swift_cuda_parts_in
   build_tasks(c->prm, c->tree);
   std::vector<uint8_t> act;
   cells_active(c, in, act);
+  c->all_cells_active = std::find(act.begin(), act.end(), (uint8_t)0) == act.end();
+  c->integ_on = false;
   build_worklists(c->prm, c->tree, act, c->wl);
   assign_lanes(c->tree, in->x, c->wl);
   return pack_and_upload(c, in);
@@ -403,6 +414,8 @@ int swift_cuda_build_from_cells(swift_cuda_ctx *c, const swift_cuda_parts_in *in
   compute_cell_hmax(c->tree, in->h);
   std::vector<uint8_t> act;
   cells_active(c, in, act);
+  c->all_cells_active = std::find(act.begin(), act.end(), (uint8_t)0) == act.end();
+  c->integ_on = false;
   build_worklists(c->prm, c->tree, act, c->wl);
   assign_lanes(c->tree, in->x, c->wl);
   return pack_and_upload(c, in);
@@ -969,6 +982,166 @@ int swift_cuda_halo_unpack(swift_cuda_ctx *c, int phase, const int32_t *d_index,
   else
     k_halo_unpack_rho<<<nb, 256, 0, s>>>(c->dev, d_index, count, (const HaloRho *)d_buffer);
   CK(cudaGetLastError());
+  return 0;
+}
+
+// ---- time integration (integrate.cuh) ---------------------
+#define NEED_INTEG(c)  \
+  NEED_BUILT(c);       \
+  if (!(c)->integ_on) return fail("swift_cuda_integrator_init has not been called on this context");
+
+int swift_cuda_integrator_init(swift_cuda_ctx *c, const swift_cuda_integrator *p) {
+  NEED_BUILT(c);
+  if (!p) return fail("integrator_init: null argument");
+  if (!c->all_cells_active)
+    return fail("integrator_init: build the context with every particle active (max_active_bin = 56), so that "
+                "every cell is in the work lists; the active set then changes per step on the device");
+  if (!(p->time_base > 0.0)) return fail("integrator_init: time_base must be positive");
+  IntegDev &g = c->integ;
+  const int64_t n = c->n;
+  if (dmalloc(c, &g.vu_full, (size_t)n) || dmalloc(c, &g.xdiff, (size_t)n) || dmalloc(c, &g.xdiff_sort, (size_t)n) ||
+      dmalloc(c, &g.dx2_max, 2) || dmalloc(c, &g.ti_end_min, 1) || dmalloc(c, &g.updated, 1) ||
+      dmalloc(c, &g.too_small, 1))
+    return 1;
+  c->iprm.cfl = p->cfl_condition;
+  c->iprm.log_max_h_change = p->log_max_h_change;
+  c->iprm.min_u = (float)((double)p->minimal_internal_energy / 1.0);  // / cosmo->a_factor_internal_energy
+  c->iprm.dt_min = p->dt_min;
+  c->iprm.dt_max = p->dt_max;
+  c->iprm.time_base = p->time_base;
+  c->iprm.time_base_inv = 1.0 / p->time_base;
+  c->iprm.ti_current = 0;
+  if (n > 0) k_integ_init<<<(int)((n + 255) / 256), 256, 0, c->stream>>>(c->dev, g);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(c->stream));
+  c->integ_on = true;
+  return 0;
+}
+
+int swift_cuda_set_time(swift_cuda_ctx *c, long long ti_current, int max_active_bin) {
+  NEED_INTEG(c);
+  c->iprm.ti_current = ti_current;
+  c->prm.max_active_bin = max_active_bin;
+  if (upload_consts(c)) return 1;
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int swift_cuda_drift(swift_cuda_ctx *c, long long ti_old, float dx_max[2]) {
+  NEED_INTEG(c);
+  if (ti_old > c->iprm.ti_current) return fail("drift: attempt to drift to the past");
+  Dev &d = c->dev;
+  const double dt = (double)(c->iprm.ti_current - ti_old) * c->iprm.time_base;
+  CK(cudaMemsetAsync(c->integ.dx2_max, 0, 2 * sizeof(unsigned), c->stream));
+  if (c->n > 0) k_drift<<<(int)((c->n + 255) / 256), 256, 0, c->stream>>>(d, c->integ, c->iprm, dt);
+  // c->hydro.h_max follows the particles (cell_drift.c:318, 367)
+  if (d.ncells > 0)
+    k_cell_hmax_init<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d, d.cell_hmax,
+                                                                         const_cast<float *>(d.cell_hmax_old));
+  CK(cudaGetLastError());
+  float dx2[2] = {0.f, 0.f};
+  CK(cudaMemcpyAsync(dx2, c->integ.dx2_max, sizeof(dx2), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if (dx_max) {
+    dx_max[0] = sqrtf(dx2[0]);  // cell_drift.c:359-360
+    dx_max[1] = sqrtf(dx2[1]);
+  }
+  return 0;
+}
+
+int swift_cuda_kick(swift_cuda_ctx *c, int which) {
+  NEED_INTEG(c);
+  if (which != 1 && which != 2) return fail("kick: which must be 1 (kick1) or 2 (kick2)");
+  if (c->n > 0) k_kick<<<(int)((c->n + 255) / 256), 256, 0, c->stream>>>(c->dev, c->integ, c->iprm, which);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int swift_cuda_timestep(swift_cuda_ctx *c, long long *ti_end_min, long long *updated) {
+  NEED_INTEG(c);
+  const unsigned long long big = (unsigned long long)kMaxNrTimesteps;
+  CK(cudaMemcpyAsync(c->integ.ti_end_min, &big, sizeof(big), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemsetAsync(c->integ.updated, 0, sizeof(unsigned long long), c->stream));
+  CK(cudaMemsetAsync(c->integ.too_small, 0, sizeof(int), c->stream));
+  if (c->n > 0) k_timestep<<<(int)((c->n + 255) / 256), 256, 0, c->stream>>>(c->dev, c->integ, c->iprm);
+  CK(cudaGetLastError());
+  unsigned long long t = 0, u = 0;
+  int small = 0;
+  CK(cudaMemcpyAsync(&t, c->integ.ti_end_min, sizeof(t), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(&u, c->integ.updated, sizeof(u), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(&small, c->integ.too_small, sizeof(small), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if (ti_end_min) *ti_end_min = (long long)t;
+  if (updated) *updated = (long long)u;
+  if (small > 0)
+    return fail(std::to_string(small) + " particle(s) want a time-step below dt_min (" +
+                std::to_string(c->iprm.dt_min) + ")");
+  return 0;
+}
+
+int swift_cuda_reset_offsets(swift_cuda_ctx *c, int what) {
+  NEED_INTEG(c);
+  CK(cudaMemsetAsync(c->integ.xdiff_sort, 0, (size_t)c->n * sizeof(float4), c->stream));
+  if (what >= 2) CK(cudaMemsetAsync(c->integ.xdiff, 0, (size_t)c->n * sizeof(float4), c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int swift_cuda_get_state(swift_cuda_ctx *c, const swift_cuda_state_out *o) {
+  NEED_INTEG(c);
+  if (!o) return fail("get_state: null argument");
+  const int64_t n = c->n;
+  if (n == 0) return 0;
+  Dev &d = c->dev;
+  const IntegDev &g = c->integ;
+  void *tmp = nullptr;  // inspection path: one scratch buffer, fields one after the other
+  CK(cudaMalloc(&tmp, (size_t)n * 3 * sizeof(double)));
+  const int32_t *order = c->tree.order.empty() ? nullptr : c->s_order;
+  const int nb = (int)((n + 255) / 256);
+  int rc = 0;
+  auto f32 = [&](float *host, const void *src, int stride, int width) {
+    if (!host || rc) return;
+    k_scatter_f32<<<nb, 256, 0, c->stream>>>(n, order, (const float *)src, stride, width, (float *)tmp);
+    if (cudaMemcpyAsync(host, tmp, (size_t)n * width * sizeof(float), cudaMemcpyDeviceToHost, c->stream) !=
+            cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess)
+      rc = 1;
+  };
+  if (o->x) {
+    k_scatter_pos<<<nb, 256, 0, c->stream>>>(n, order, d.pos, (double *)tmp);
+    if (cudaMemcpyAsync(o->x, tmp, (size_t)n * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream) !=
+            cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess)
+      rc = 1;
+  }
+  f32(o->v, d.vm, 4, 3);
+  f32(o->v_full, g.vu_full, 4, 3);
+  f32(o->u, d.u, 1, 1);
+  f32(o->u_full, (const float *)g.vu_full + 3, 4, 1);
+  f32(o->h, d.h, 1, 1);
+  f32(o->rho, d.fin, 4, 1);
+  f32(o->pressure, (const float *)d.fin + 1, 4, 1);
+  f32(o->soundspeed, (const float *)d.fin + 3, 4, 1);
+  f32(o->v_sig, d.v_sig, 1, 1);
+  f32(o->a, d.acc, 4, 3);
+  f32(o->u_dt, (const float *)d.acc + 3, 4, 1);
+  f32(o->h_dt, d.h_dt, 1, 1);
+  f32(o->x_diff, g.xdiff, 4, 3);
+  f32(o->x_diff_sort, g.xdiff_sort, 4, 3);
+  if (!rc && (o->time_bin || o->min_ngb_time_bin)) {
+    int8_t *tb = (int8_t *)tmp, *mb = tb + n;
+    k_scatter_bins<<<nb, 256, 0, c->stream>>>(n, order, d.time_bin, d.min_bin, tb, mb);
+    if (o->time_bin && cudaMemcpyAsync(o->time_bin, tb, (size_t)n, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess)
+      rc = 1;
+    if (o->min_ngb_time_bin &&
+        cudaMemcpyAsync(o->min_ngb_time_bin, mb, (size_t)n, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess)
+      rc = 1;
+    if (cudaStreamSynchronize(c->stream) != cudaSuccess) rc = 1;
+  }
+  const cudaError_t e = cudaGetLastError();
+  cudaFree(tmp);
+  if (rc || e != cudaSuccess) return fail(std::string("get_state: ") + cudaGetErrorString(e));
   return 0;
 }
 

@@ -49,7 +49,8 @@ class Parts(C.Structure):
                 ("g_balsara", _FP),
                 ("f_a", _FP), ("f_u_dt", _FP), ("f_h_dt", _FP), ("f_v_sig", _FP),
                 ("f_min_ngb_time_bin", C.POINTER(C.c_byte)),
-                ("in_rho", _FP), ("in_pressure", _FP), ("in_f", _FP), ("in_soundspeed", _FP), ("in_balsara", _FP)]
+                ("in_rho", _FP), ("in_pressure", _FP), ("in_f", _FP), ("in_soundspeed", _FP), ("in_balsara", _FP),
+                ("in_h_build", _FP)]
 
 
 class PairLog(C.Structure):
@@ -196,7 +197,7 @@ def run_step(which, prm, ic, cells, tasks, ntasks, record=False, pair_capacity=N
     if ic.get("time_bin") is not None:
         tb = arr(ic["time_bin"], np.int8)
         P.time_bin = tb.ctypes.data_as(C.POINTER(C.c_byte))
-    for k in ("in_rho", "in_pressure", "in_f", "in_soundspeed", "in_balsara"):
+    for k in ("in_rho", "in_pressure", "in_f", "in_soundspeed", "in_balsara", "in_h_build"):
         if ic.get(k) is not None:
             setattr(P, k, arr(ic[k], np.float32).ctypes.data_as(_FP))
     out = {}

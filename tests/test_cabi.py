@@ -36,7 +36,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layouts_match_ctypes_mirror():
     lib = be.load_library()
     for which, cls in enumerate([be.Params, be.Cell, be.Task, be.PartsIn, be.PartsOut, be.Counters, be.Timings,
-                                 be.Til]):
+                                 be.Til, be.Integrator, be.StateOut]):
         assert lib.swift_cuda_sizeof(which) == C.sizeof(cls), cls.__name__
     # the oracle's tree structs are layout-compatible (tests memmove between them)
     assert C.sizeof(ol.Cell) == C.sizeof(be.Cell) and C.sizeof(ol.Task) == C.sizeof(be.Task)
