@@ -59,37 +59,6 @@ __device__ __forceinline__ float approx_expf(float x) {
   return __fadd_rn(1.f, __fmul_rn(x, a));
 }
 
-// expf as glibc >= 2.27 computes it (sysdeps/ieee754/flt-32/e_expf.c with the 32-entry table of
-// exp2f_data.c: x * 32 / ln2 = k + r, 2^(k/32) from the table, a cubic in r, all in double, one
-// rounding to float).  The reference calls libm's expf when a drift changes h by more than ~20 %
-// (|w| >= 0.2); CUDA's expf differs from it in the last bit for ~1 argument in 10.
-__device__ const unsigned long long kExp2fTab[32] = {
-      0x3ff0000000000000ULL, 0x3fefd9b0d3158574ULL, 0x3fefb5586cf9890fULL, 0x3fef9301d0125b51ULL,
-      0x3fef72b83c7d517bULL, 0x3fef54873168b9aaULL, 0x3fef387a6e756238ULL, 0x3fef1e9df51fdee1ULL,
-      0x3fef06fe0a31b715ULL, 0x3feef1a7373aa9cbULL, 0x3feedea64c123422ULL, 0x3feece086061892dULL,
-      0x3feebfdad5362a27ULL, 0x3feeb42b569d4f82ULL, 0x3feeab07dd485429ULL, 0x3feea47eb03a5585ULL,
-      0x3feea09e667f3bcdULL, 0x3fee9f75e8ec5f74ULL, 0x3feea11473eb0187ULL, 0x3feea589994cce13ULL,
-      0x3feeace5422aa0dbULL, 0x3feeb737b0cdc5e5ULL, 0x3feec49182a3f090ULL, 0x3feed503b23e255dULL,
-      0x3feee89f995ad3adULL, 0x3feeff76f2fb5e47ULL, 0x3fef199bdd85529cULL, 0x3fef3720dcef9069ULL,
-      0x3fef5818dcfba487ULL, 0x3fef7c97337b9b5fULL, 0x3fefa4afa2a490daULL, 0x3fefd0765b6e4540ULL};
-__device__ float expf_glibc(float x) {
-  if (!(fabsf(x) < 88.f)) return expf(x);  // overflow, underflow, inf, nan: not reached by a drift
-  const double inv_ln2_n = 0x1.71547652b82fep+0 * 32.0, shift = 0x1.8p+52;
-  const double c0 = 0x1.c6af84b912394p-5 / 32.0 / 32.0 / 32.0, c1 = 0x1.ebfce50fac4f3p-3 / 32.0 / 32.0,
-               c2 = 0x1.62e42ff0c52d6p-1 / 32.0;
-  const double z = __dmul_rn(inv_ln2_n, (double)x);
-  double kd = __dadd_rn(z, shift);
-  const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
-  kd = __dsub_rn(kd, shift);
-  const double r = __dsub_rn(z, kd);
-  const double s = __longlong_as_double((long long)(kExp2fTab[ki & 31] + (ki << 47)));
-  const double zz = __dadd_rn(__dmul_rn(c0, r), c1);
-  const double r2 = __dmul_rn(r, r);
-  double y = __dadd_rn(__dmul_rn(c2, r), 1.0);
-  y = __dadd_rn(__dmul_rn(zz, r2), y);
-  return (float)__dmul_rn(y, s);
-}
-
 // v += a * dt with a float accumulator and a double dt: (float)((double)v + (double)a * dt)
 __device__ __forceinline__ float kick_f(float v, float a, double dt) {
   return (float)__dadd_rn((double)v, __dmul_rn((double)a, dt));

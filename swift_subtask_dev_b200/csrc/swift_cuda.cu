@@ -393,7 +393,9 @@ int swift_cuda_build_from_particles(swift_cuda_ctx *c, const swift_cuda_parts_in
   build_tasks(c->prm, c->tree);
   std::vector<uint8_t> act;
   cells_active(c, in, act);
-  c->all_cells_active = std::find(act.begin(), act.end(), (uint8_t)0) == act.end();
+  c->all_cells_active = true;  // empty cells have nothing to contribute either way
+  for (size_t k = 0; k < act.size(); k++)
+    if (!act[k] && c->tree.cells[k].count > 0) c->all_cells_active = false;
   c->integ_on = false;
   build_worklists(c->prm, c->tree, act, c->wl);
   assign_lanes(c->tree, in->x, c->wl);
@@ -414,7 +416,9 @@ int swift_cuda_build_from_cells(swift_cuda_ctx *c, const swift_cuda_parts_in *in
   compute_cell_hmax(c->tree, in->h);
   std::vector<uint8_t> act;
   cells_active(c, in, act);
-  c->all_cells_active = std::find(act.begin(), act.end(), (uint8_t)0) == act.end();
+  c->all_cells_active = true;  // empty cells have nothing to contribute either way
+  for (size_t k = 0; k < act.size(); k++)
+    if (!act[k] && c->tree.cells[k].count > 0) c->all_cells_active = false;
   c->integ_on = false;
   build_worklists(c->prm, c->tree, act, c->wl);
   assign_lanes(c->tree, in->x, c->wl);
