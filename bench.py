@@ -130,6 +130,59 @@ def cpu_arm(sample_side, nproc, reps=1):
                           "wall_s": wall, "interactions": total}
 
 
+def resident_leg(args, ic, hbm_peak):
+    """the particles go to the device ONCE and stay there; per engine step only scalars
+    (ti_end_min, dx_max) come back.  Step 0 has every particle active; the following ones the particles whose
+    time bin ends (individual time steps), all particles drifted at every step (engine_policy_drift_all).
+    Times are CUDA events on the library's stream.  DRIFT_BYTES: what k_drift reads + writes per particle."""
+    from swift_subtask_dev_b200 import HydroBackend, make_params
+    DRIFT_BYTES = 160 + 124
+    n = len(ic["h"])
+    ic = dict(ic)
+    ic["time_bin"] = np.zeros(n, dtype=np.int8)   # hydro_first_init_part
+    be = HydroBackend(make_params())
+    be.build(ic)
+    lmhc = float(np.log(np.float32(np.float32(1.4) ** np.float32(1.0 / 3.0)), dtype=np.float32))
+    be.integrator_init(cfl_condition=0.1, log_max_h_change=lmhc, minimal_internal_energy=0.0, dt_min=1e-12,
+                       dt_max=1e-2, time_base=1.0 / float(1 << 57))
+    steps = []
+    ti_current, ti_old = 0, 0
+    for k in range(args.resident_steps + 1):
+        mab = 56
+        if ti_current:
+            mab = 1
+            while not ((1 << (mab + 1)) & ti_current):
+                mab += 1
+        be.set_time(ti_current, mab)
+        if k > 0:
+            be.drift(ti_old)
+        be.step(do_sort=True)
+        cnt, t = be.counters(), be.timings()
+        if k > 0:
+            be.kick(2)
+        ti_end_min, updated = be.timestep()
+        be.kick(1)
+        it = be.integrator_timings()
+        integ_ms = (it["drift_ms"] if k > 0 else 0.0) + (it["kick2_ms"] if k > 0 else 0.0) + it["kick1_ms"] + \
+            it["timestep_ms"]
+        steps.append({"active": updated, "interactions": cnt["n_density"] + cnt["n_density_redo"] + cnt["n_force"],
+                      "loops_ms": t["total_ms"], "integrator_ms": integ_ms,
+                      "phase_ms": [round(t[q], 3) for q in ("sort_ms", "density_ms", "ghost_ms", "force_ms")],
+                      "drift_gbs": DRIFT_BYTES * n / (it["drift_ms"] * 1e-3) / 1e9 if k > 0 else None})
+        ti_old, ti_current = ti_current, ti_end_min
+    be.close()
+    later = steps[1:]
+    tot_ms = sum(s["loops_ms"] + s["integrator_ms"] for s in steps)
+    out = {"steps": steps, "value": sum(s["interactions"] for s in steps) / (tot_ms * 1e-3), "unit": UNIT,
+           "host_bytes_per_step": 24, "note": "whole engine steps with the particles resident in HBM; value = "
+           "interactions of all steps / device time of all steps (loops + drift + kicks + time-step)"}
+    if later:
+        g = [s["drift_gbs"] for s in later]
+        out["drift_kernel"] = {"bound": "hbm", "achieved": float(np.mean(g)), "peak": hbm_peak, "unit": "GB/s",
+                               "frac": float(np.mean(g)) / hbm_peak, "bytes_per_particle": DRIFT_BYTES}
+    return out
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -150,6 +203,8 @@ def main():
     ap.add_argument("--workload", default="uniform", choices=["uniform", "clustered"],
                     help="uniform: BASELINE configs[1] / [3] (default, the metric's config); clustered: configs[4] "
                          "shape, side^3 particles in TOTAL over ~10^3 clumps + background")
+    ap.add_argument("--resident-steps", type=int, default=3,
+                    help="engine steps of the device-resident leg (drift/kick/time-step kernels, SURVEY 8(f) N3); 0: skip")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -302,6 +357,9 @@ def main():
                        "n_density_redo": cnt["n_density_redo"], "n_force": cnt["n_force"],
                        "ghost_sweeps": cnt["ghost_sweeps"], "phase_ms": {k: v / args.steps for k, v in phase.items()},
                        "wall_ms_per_step": wall_ms, "build_s": build_s, "leaf_interactions": cnt["n_leaf_interactions"]}}
+    if args.resident_steps > 0:
+        be.close()
+        line["resident"] = resident_leg(args, ic, hbm_peak)
     if not args.no_cpu:
         nproc = host_cores()
         v, desc = cpu_arm(args.cpu_side, nproc)

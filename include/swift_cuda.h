@@ -301,6 +301,8 @@ int swift_cuda_timestep(swift_cuda_ctx *ctx, long long *ti_end_min, long long *u
 /* Zeroes x_diff_sort (after a re-sort) and/or x_diff (after a rebuild): what = 1 sort, 2 both. */
 int swift_cuda_reset_offsets(swift_cuda_ctx *ctx, int what);
 int swift_cuda_get_state(swift_cuda_ctx *ctx, const swift_cuda_state_out *out);
+/* Device time (CUDA events on the context's stream) of the last drift, kick1, kick2, timestep, ms. */
+int swift_cuda_get_integrator_timings(swift_cuda_ctx *ctx, float ms[4]);
 
 #ifdef __cplusplus
 }

@@ -123,7 +123,8 @@ EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error
            "swift_cuda_get_touched", "swift_cuda_refresh_cell_hmax",
            "swift_cuda_host_plan", "swift_cuda_host_free",
            "swift_cuda_integrator_init", "swift_cuda_set_time", "swift_cuda_drift", "swift_cuda_kick",
-           "swift_cuda_timestep", "swift_cuda_reset_offsets", "swift_cuda_get_state"]
+           "swift_cuda_timestep", "swift_cuda_reset_offsets", "swift_cuda_get_state",
+           "swift_cuda_get_integrator_timings"]
 
 _lib = None
 
@@ -345,6 +346,11 @@ class HydroBackend:
         t, u = C.c_longlong(0), C.c_longlong(0)
         self._check(self.lib.swift_cuda_timestep(self.ctx, C.byref(t), C.byref(u)))
         return t.value, u.value
+
+    def integrator_timings(self):
+        ms = (C.c_float * 4)()
+        self._check(self.lib.swift_cuda_get_integrator_timings(self.ctx, ms))
+        return {"drift_ms": ms[0], "kick1_ms": ms[1], "kick2_ms": ms[2], "timestep_ms": ms[3]}
 
     def reset_offsets(self, what=1):
         self._check(self.lib.swift_cuda_reset_offsets(self.ctx, what))

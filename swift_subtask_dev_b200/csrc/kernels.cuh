@@ -218,13 +218,38 @@ __device__ __forceinline__ float ordered_to_float(uint32_t u) {
   return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
 }
 
+// Which sorted lists does this step read?  The reference sorts a cell along an axis only when an
+// ACTIVE pair task needs it (cell_activate_hydro_sorts, src/cell_unskip.c); with individual time steps
+// most steps have few active particles.  One warp per leaf: if one of its particles is active, every
+// (cell, axis) list its interactions walk is marked (both sides of a pair).
+__global__ void k_mark_sorts(Dev d) {
+  const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (slot >= d.n_leaves) return;
+  const CellDev c = d.cells[d.leaves[slot]];
+  bool act = false;
+  for (int k = lane; k < c.count; k += 32) act |= d.time_bin[c.first + k] <= kc.max_active_bin;
+  if (!__any_sync(0xffffffffu, act)) return;
+  for (int pass = 0; pass < 2; pass++) {
+    const int32_t *begin = pass == 0 ? d.item_begin : d.redo_begin;
+    const Item *items = pass == 0 ? d.items : d.redo_items;
+    for (int k = begin[slot] + lane; k < begin[slot + 1]; k += 32) {
+      const Item it = items[k];
+      if (it.kind == kSelf || it.kind == kSubSelf) continue;
+      d.sort_need[(int64_t)it.partner * 13 + it.sid] = 1;
+      d.sort_need[(int64_t)it.own * 13 + it.sid] = 1;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) k_sort(Dev d, const int32_t *seg_cell, const int32_t *seg_sid,
                                               const int64_t *seg_off, unsigned long long *scratch,
                                               const int64_t *scratch_off) {
   __shared__ unsigned long long skeys[kSortSmem];
   const int seg = blockIdx.x;
-  const CellDev c = d.cells[seg_cell[seg]];
   const int sid = seg_sid[seg];
+  if (d.sort_need && !d.sort_need[(int64_t)seg_cell[seg] * 13 + sid]) return;
+  const CellDev c = d.cells[seg_cell[seg]];
   const int n = c.count;
   int npad = 1;
   while (npad < n) npad <<= 1;

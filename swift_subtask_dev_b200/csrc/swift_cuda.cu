@@ -64,6 +64,8 @@ struct swift_cuda_ctx {
   bool integ_on = false;
   IntegDev integ = {};
   IntegPrm iprm = {};
+  uint8_t *d_sort_need = nullptr;  // [ncells*13]
+  float integ_ms[4] = {};          // last drift, kick1, kick2, timestep (CUDA events on the stream)
 };
 
 template <typename T>
@@ -502,6 +504,14 @@ double swift_cuda_measure_fp32_peak(swift_cuda_ctx *c) {
 
 // ---- phases ----------------------------------------------------------------
 static int launch_sort(swift_cuda_ctx *c) {
+  Dev &d = c->dev;
+  // time-integration mode: the active set changes per step; rebuild only the lists this step reads
+  d.sort_need = c->integ_on ? c->d_sort_need : nullptr;
+  if (d.sort_need && d.n_leaves > 0) {
+    CK(cudaMemsetAsync(d.sort_need, 0, (size_t)d.ncells * 13, c->stream));
+    k_mark_sorts<<<(d.n_leaves * 32 + 255) / 256, 256, 0, c->stream>>>(d);
+    c->counters.n_kernel_launches += 1;
+  }
   if (c->n_seg > 0)
     k_sort<<<c->n_seg, 256, 0, c->stream>>>(c->dev, c->d_seg_cell, c->d_seg_sid, c->d_seg_off, c->d_scratch,
                                             c->d_scratch_off);
@@ -1005,7 +1015,7 @@ int swift_cuda_integrator_init(swift_cuda_ctx *c, const swift_cuda_integrator *p
   const int64_t n = c->n;
   if (dmalloc(c, &g.vu_full, (size_t)n) || dmalloc(c, &g.xdiff, (size_t)n) || dmalloc(c, &g.xdiff_sort, (size_t)n) ||
       dmalloc(c, &g.dx2_max, 2) || dmalloc(c, &g.ti_end_min, 1) || dmalloc(c, &g.updated, 1) ||
-      dmalloc(c, &g.too_small, 1))
+      dmalloc(c, &g.too_small, 1) || dmalloc(c, &c->d_sort_need, (size_t)c->dev.ncells * 13))
     return 1;
   c->iprm.cfl = p->cfl_condition;
   c->iprm.log_max_h_change = p->log_max_h_change;
@@ -1037,15 +1047,18 @@ int swift_cuda_drift(swift_cuda_ctx *c, long long ti_old, float dx_max[2]) {
   Dev &d = c->dev;
   const double dt = (double)(c->iprm.ti_current - ti_old) * c->iprm.time_base;
   CK(cudaMemsetAsync(c->integ.dx2_max, 0, 2 * sizeof(unsigned), c->stream));
+  CK(cudaEventRecord(c->ev[0], c->stream));
   if (c->n > 0) k_drift<<<(int)((c->n + 255) / 256), 256, 0, c->stream>>>(d, c->integ, c->iprm, dt);
   // c->hydro.h_max follows the particles (cell_drift.c:318, 367)
   if (d.ncells > 0)
     k_cell_hmax_init<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d, d.cell_hmax,
                                                                          const_cast<float *>(d.cell_hmax_old));
   CK(cudaGetLastError());
+  CK(cudaEventRecord(c->ev[5], c->stream));
   float dx2[2] = {0.f, 0.f};
   CK(cudaMemcpyAsync(dx2, c->integ.dx2_max, sizeof(dx2), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
+  CK(cudaEventElapsedTime(&c->integ_ms[0], c->ev[0], c->ev[5]));
   if (dx_max) {
     dx_max[0] = sqrtf(dx2[0]);  // cell_drift.c:359-360
     dx_max[1] = sqrtf(dx2[1]);
@@ -1056,9 +1069,12 @@ int swift_cuda_drift(swift_cuda_ctx *c, long long ti_old, float dx_max[2]) {
 int swift_cuda_kick(swift_cuda_ctx *c, int which) {
   NEED_INTEG(c);
   if (which != 1 && which != 2) return fail("kick: which must be 1 (kick1) or 2 (kick2)");
+  CK(cudaEventRecord(c->ev[0], c->stream));
   if (c->n > 0) k_kick<<<(int)((c->n + 255) / 256), 256, 0, c->stream>>>(c->dev, c->integ, c->iprm, which);
   CK(cudaGetLastError());
+  CK(cudaEventRecord(c->ev[5], c->stream));
   CK(cudaStreamSynchronize(c->stream));
+  CK(cudaEventElapsedTime(&c->integ_ms[which], c->ev[0], c->ev[5]));
   return 0;
 }
 
@@ -1068,19 +1084,29 @@ int swift_cuda_timestep(swift_cuda_ctx *c, long long *ti_end_min, long long *upd
   CK(cudaMemcpyAsync(c->integ.ti_end_min, &big, sizeof(big), cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemsetAsync(c->integ.updated, 0, sizeof(unsigned long long), c->stream));
   CK(cudaMemsetAsync(c->integ.too_small, 0, sizeof(int), c->stream));
+  CK(cudaEventRecord(c->ev[0], c->stream));
   if (c->n > 0) k_timestep<<<(int)((c->n + 255) / 256), 256, 0, c->stream>>>(c->dev, c->integ, c->iprm);
   CK(cudaGetLastError());
+  CK(cudaEventRecord(c->ev[5], c->stream));
   unsigned long long t = 0, u = 0;
   int small = 0;
   CK(cudaMemcpyAsync(&t, c->integ.ti_end_min, sizeof(t), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaMemcpyAsync(&u, c->integ.updated, sizeof(u), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaMemcpyAsync(&small, c->integ.too_small, sizeof(small), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
+  CK(cudaEventElapsedTime(&c->integ_ms[3], c->ev[0], c->ev[5]));
   if (ti_end_min) *ti_end_min = (long long)t;
   if (updated) *updated = (long long)u;
   if (small > 0)
     return fail(std::to_string(small) + " particle(s) want a time-step below dt_min (" +
                 std::to_string(c->iprm.dt_min) + ")");
+  return 0;
+}
+
+int swift_cuda_get_integrator_timings(swift_cuda_ctx *c, float ms[4]) {
+  NEED_INTEG(c);
+  if (!ms) return fail("get_integrator_timings: null argument");
+  for (int k = 0; k < 4; k++) ms[k] = c->integ_ms[k];
   return 0;
 }
 
