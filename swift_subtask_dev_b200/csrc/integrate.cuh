@@ -76,7 +76,7 @@ __global__ void k_integ_init(Dev d, IntegDev g) {
 
 // Every particle from ti_old to ti_current (engine_policy_drift_all).  dt = (ti_current - ti_old) *
 // time_base is at once dt_drift, dt_kick_hydro and dt_therm (cell_drift.c:232-236, no cosmology).
-__global__ void k_drift(Dev d, IntegDev g, IntegPrm ip, double dt) {
+__global__ void __launch_bounds__(256, 4) k_drift(Dev d, IntegDev g, IntegPrm ip, double dt) {
   const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   float dx2 = 0.f, dx2s = 0.f;
   if (p < d.n) {

@@ -242,13 +242,9 @@ __global__ void k_mark_sorts(Dev d) {
   }
 }
 
-__global__ void __launch_bounds__(256) k_sort(Dev d, const int32_t *seg_cell, const int32_t *seg_sid,
-                                              const int64_t *seg_off, unsigned long long *scratch,
-                                              const int64_t *scratch_off) {
-  __shared__ unsigned long long skeys[kSortSmem];
-  const int seg = blockIdx.x;
-  const int sid = seg_sid[seg];
-  if (d.sort_need && !d.sort_need[(int64_t)seg_cell[seg] * 13 + sid]) return;
+__device__ __forceinline__ void sort_segment(const Dev &d, int seg, const int32_t *seg_cell, int sid,
+                                             const int64_t *seg_off, unsigned long long *scratch,
+                                             const int64_t *scratch_off, unsigned long long *skeys) {
   const CellDev c = d.cells[seg_cell[seg]];
   const int n = c.count;
   int npad = 1;
@@ -319,6 +315,34 @@ __global__ void __launch_bounds__(256) k_sort(Dev d, const int32_t *seg_cell, co
     se.d = ordered_to_float((uint32_t)(key >> 32));
     se.i = (int32_t)(key & 0xffffffffu);
     d.sort[off + k] = se;
+  }
+}
+
+// One CTA per (cell, axis) segment when every list is rebuilt; in time-integration mode (sort_need
+// set) a small grid strides over the segments and sorts only the marked ones, so that a step with a
+// handful of active particles does not pay for 13 launches' worth of empty CTAs per cell.
+__global__ void __launch_bounds__(256) k_sort(Dev d, int n_seg, const int32_t *seg_cell, const int32_t *seg_sid,
+                                              const int64_t *seg_off, unsigned long long *scratch,
+                                              const int64_t *scratch_off) {
+  __shared__ unsigned long long skeys[kSortSmem];
+  if (!d.sort_need) {
+    sort_segment(d, blockIdx.x, seg_cell, seg_sid[blockIdx.x], seg_off, scratch, scratch_off, skeys);
+    return;
+  }
+  __shared__ int list[256];
+  __shared__ int cnt;
+  for (int base = blockIdx.x * 256; base < n_seg; base += gridDim.x * 256) {
+    if (threadIdx.x == 0) cnt = 0;
+    __syncthreads();
+    const int mine = base + threadIdx.x;  // 256 flags checked at once, the marked ones sorted in turn
+    if (mine < n_seg && d.sort_need[(int64_t)seg_cell[mine] * 13 + seg_sid[mine]]) list[atomicAdd(&cnt, 1)] = mine;
+    __syncthreads();
+    const int m = cnt;
+    for (int k = 0; k < m; k++) {
+      const int seg = list[k];
+      sort_segment(d, seg, seg_cell, seg_sid[seg], seg_off, scratch, scratch_off, skeys);
+      __syncthreads();  // skeys is reused by the next segment
+    }
   }
 }
 
@@ -993,10 +1017,17 @@ __device__ float cbrtf_glibc(float x) {
   return ldexpf(x > 0.f ? ym : -ym, xe / 3);
 }
 
+__device__ __forceinline__ void ghost_particle(const Dev &d, int sweep, int64_t p);
+
+// Grid-stride: the launch sequence of a step always holds max_smoothing_iterations of these, and
+// all but the first few find nothing pending; a small grid makes those launches free.
 __global__ void k_ghost(Dev d, int sweep) {
   if (sweep > 0 && d.redo_count[sweep - 1] == 0) return;
-  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (p >= d.n) return;
+  for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < d.n; p += (int64_t)gridDim.x * blockDim.x)
+    ghost_particle(d, sweep, p);
+}
+
+__device__ __forceinline__ void ghost_particle(const Dev &d, int sweep, int64_t p) {
   const uint8_t st = d.gstate[p];
   if (st != 1 && st != 2) return;
   const bool planetary = kc.scheme == SWIFT_CUDA_SCHEME_PLANETARY;

@@ -512,9 +512,11 @@ static int launch_sort(swift_cuda_ctx *c) {
     k_mark_sorts<<<(d.n_leaves * 32 + 255) / 256, 256, 0, c->stream>>>(d);
     c->counters.n_kernel_launches += 1;
   }
-  if (c->n_seg > 0)
-    k_sort<<<c->n_seg, 256, 0, c->stream>>>(c->dev, c->d_seg_cell, c->d_seg_sid, c->d_seg_off, c->d_scratch,
-                                            c->d_scratch_off);
+  if (c->n_seg > 0) {
+    const int grid = d.sort_need ? (c->n_seg + 255) / 256 : c->n_seg;
+    k_sort<<<grid, 256, 0, c->stream>>>(c->dev, c->n_seg, c->d_seg_cell, c->d_seg_sid, c->d_seg_off, c->d_scratch,
+                                        c->d_scratch_off);
+  }
   c->counters.n_kernel_launches += 1;
   CK(cudaGetLastError());
   return 0;
@@ -553,7 +555,7 @@ static int launch_density(swift_cuda_ctx *c) {
 
 static int launch_ghost(swift_cuda_ctx *c) {
   Dev &d = c->dev;
-  const int nb = (int)((c->n + 255) / 256);
+  const int nb = (int)std::min<int64_t>((c->n + 255) / 256, 148 * 16);  // grid-stride kernel
   // Fixed launch sequence, no host round trip: every kernel looks at the device-side
   // redo counter of the sweep before and leaves at once when nothing is pending.
   for (int sweep = 0; sweep < c->prm.max_smoothing_iterations; sweep++) {
