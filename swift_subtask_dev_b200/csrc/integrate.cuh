@@ -248,7 +248,9 @@ __global__ void k_timestep(Dev d, IntegDev g, IntegPrm ip) {
   }
   const unsigned b = __ballot_sync(0xffffffffu, upd);
   if ((threadIdx.x & 31) == 0) {
-    atomicMin(g.ti_end_min, (unsigned long long)t_end);
+    // most warps cannot lower the minimum any more: look before the atomic (one address for 5e5 warps)
+    if ((unsigned long long)t_end < *(volatile unsigned long long *)g.ti_end_min)
+      atomicMin(g.ti_end_min, (unsigned long long)t_end);
     if (b) atomicAdd(g.updated, (unsigned long long)__popc(b));
   }
 }

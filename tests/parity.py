@@ -25,7 +25,6 @@ FIELD_MAP = [("d_rho", "d_rho"), ("d_rho_dh", "d_rho_dh"), ("d_wcount", "d_wcoun
              ("balsara", "g_balsara"),
              ("a", "f_a"), ("u_dt", "f_u_dt"), ("h_dt", "f_h_dt"), ("v_sig", "f_v_sig"),
              ("min_ngb_time_bin", "f_min_ngb_time_bin")]
-EOS_DEPENDENT = {"pressure", "soundspeed", "balsara", "a", "u_dt", "h_dt", "v_sig"}
 
 
 def rel_err(a, b, floor):
