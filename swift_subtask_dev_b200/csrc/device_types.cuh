@@ -96,6 +96,11 @@ struct Dev {
   const int32_t *unit_leaf;    // [n_units] warp unit -> leaf slot
   const int32_t *unit_begin;   // [n_leaves+1] first unit of a leaf
   const int32_t *lane_part;    // [n_units*32] particle of each lane, or -1
+  // sparse redo sweeps: the leaves that hold a particle flagged in this sweep, pushed by k_ghost
+  const int32_t *part_slot;    // [n] leaf slot of a particle (-1: its leaf has no work)
+  int *leaf_mark;              // [n_leaves] sweep + 1 of the last push
+  int *leaf_list;              // [n_leaves]
+  int *leaf_count;             // [max_iter + 2] entries of leaf_list per sweep
   // sorts
   const int64_t *sort_lookup;  // [ncells*13]
   SortEnt *sort;           // struct sort_entry (src/sort_part.h:34-41): key d, index i inside the cell

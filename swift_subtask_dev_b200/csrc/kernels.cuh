@@ -535,7 +535,10 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
   // unit as the first pass does (5x more leaves in flight would not fit the L2); once the flagged
   // particles are few, a warp takes a whole leaf and compacts them into full groups of 32
   const bool by_unit = MODE == 0 || (long long)d.redo_count[sweep] * 2 > d.n;
-  const int total = by_unit ? d.n_units : d.n_leaves;
+  // few leaves with a flagged particle: walk the list k_ghost pushed; otherwise all leaves in tree order
+  // (spatially coherent, the unflagged ones are skipped after one look)
+  const bool by_list = MODE == 1 && !by_unit && (long long)d.leaf_count[sweep] * 4 < d.n_leaves;
+  const int total = by_unit ? d.n_units : (by_list ? d.leaf_count[sweep] : d.n_leaves);
   int *const work = d.work_ctr + (MODE == 0 ? 0 : 1 + sweep);
   const Item *__restrict__ items = MODE == 0 ? d.items : d.redo_items;
   const bool rec = d.rec_capacity > 0;
@@ -547,7 +550,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
     if (lane == 0) wid = atomicAdd(work, 1);
     wid = __shfl_sync(kFull, wid, 0);
     if (wid >= total) break;
-    const int slot = by_unit ? d.unit_leaf[wid] : wid;
+    const int slot = by_unit ? d.unit_leaf[wid] : (by_list ? d.leaf_list[wid] : wid);
     const CellDev cL = d.cells[d.leaves[slot]];
     const int ib = (MODE == 0 ? d.item_begin : d.redo_begin)[slot];
     const int ie = (MODE == 0 ? d.item_begin : d.redo_begin)[slot + 1];
@@ -1097,6 +1100,9 @@ __device__ __forceinline__ void ghost_particle(const Dev &d, int sweep, int64_t 
       d.dens1[p] = make_float4(0.f, 0.f, 0.f, 0.f);
       d.gstate[p] = 2;
       atomicAdd(&d.redo_count[sweep], 1);
+      const int slot = d.part_slot[p];
+      if (slot >= 0 && atomicExch(&d.leaf_mark[slot], sweep + 1) != sweep + 1)
+        d.leaf_list[atomicAdd(&d.leaf_count[sweep], 1)] = slot;
       return;
     } else if (h <= kc.h_min) {
       h = kc.h_min;
