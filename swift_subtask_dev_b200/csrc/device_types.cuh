@@ -105,6 +105,8 @@ struct Dev {
   const int64_t *sort_lookup;  // [ncells*13]
   SortEnt *sort;           // struct sort_entry (src/sort_part.h:34-41): key d, index i inside the cell
   uint8_t *sort_need;      // [ncells*13] or null: only these (cell, axis) lists are rebuilt (k_mark_sorts)
+  int *unit_list;          // [n_units] or null: the units with an active lane, pushed by k_mark_sorts
+  int *unit_count;         // [1]
   // persistent kernels: per-warp FIFO of deferred hits [n_qwarps][kQD][32], unit counters
   // [0] first density pass, [1 + sweep] redo sweeps, [1 + max_iter] force
   float4 *gq;

@@ -230,6 +230,11 @@ __global__ void k_mark_sorts(Dev d) {
   bool act = false;
   for (int k = lane; k < c.count; k += 32) act |= d.time_bin[c.first + k] <= kc.max_active_bin;
   if (!__any_sync(0xffffffffu, act)) return;
+  for (int u = d.unit_begin[slot]; u < d.unit_begin[slot + 1]; u++) {
+    const int q = d.lane_part[(int64_t)u * 32 + lane];
+    const bool a = q >= 0 && d.time_bin[q] <= kc.max_active_bin;
+    if (__any_sync(0xffffffffu, a) && lane == 0) d.unit_list[atomicAdd(d.unit_count, 1)] = u;
+  }
   for (int pass = 0; pass < 2; pass++) {
     const int32_t *begin = pass == 0 ? d.item_begin : d.redo_begin;
     const Item *items = pass == 0 ? d.items : d.redo_items;
@@ -538,7 +543,9 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
   // few leaves with a flagged particle: walk the list k_ghost pushed; otherwise all leaves in tree order
   // (spatially coherent, the unflagged ones are skipped after one look)
   const bool by_list = MODE == 1 && !by_unit && (long long)d.leaf_count[sweep] * 4 < d.n_leaves;
-  const int total = by_unit ? d.n_units : (by_list ? d.leaf_count[sweep] : d.n_leaves);
+  // first pass with few active units (time-integration mode): walk the list k_mark_sorts pushed
+  const bool by_ulist = MODE == 0 && d.unit_list != nullptr && (long long)*d.unit_count * 4 < d.n_units;
+  const int total = by_ulist ? *d.unit_count : (by_unit ? d.n_units : (by_list ? d.leaf_count[sweep] : d.n_leaves));
   int *const work = d.work_ctr + (MODE == 0 ? 0 : 1 + sweep);
   const Item *__restrict__ items = MODE == 0 ? d.items : d.redo_items;
   const bool rec = d.rec_capacity > 0;
@@ -550,6 +557,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
     if (lane == 0) wid = atomicAdd(work, 1);
     wid = __shfl_sync(kFull, wid, 0);
     if (wid >= total) break;
+    if (by_ulist) wid = d.unit_list[wid];
     const int slot = by_unit ? d.unit_leaf[wid] : (by_list ? d.leaf_list[wid] : wid);
     const CellDev cL = d.cells[d.leaves[slot]];
     const int ib = (MODE == 0 ? d.item_begin : d.redo_begin)[slot];
@@ -1245,12 +1253,15 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
   const bool rec = d.rec_capacity > 0;
   const float qnan = __int_as_float(0x7fc00000);
   unsigned long long nhits = 0;
+  const bool by_ulist = d.unit_list != nullptr && (long long)*d.unit_count * 4 < d.n_units;
+  const int total = by_ulist ? *d.unit_count : d.n_units;
 
   while (true) {
     int wid = 0;
     if (lane == 0) wid = atomicAdd(work, 1);
     wid = __shfl_sync(kFull, wid, 0);
-    if (wid >= d.n_units) break;
+    if (wid >= total) break;
+    if (by_ulist) wid = d.unit_list[wid];
     const int slot = d.unit_leaf[wid];
     const CellDev cL = d.cells[d.leaves[slot]];
     const int ib = d.item_begin[slot], ie = d.item_begin[slot + 1];

@@ -65,6 +65,8 @@ struct swift_cuda_ctx {
   IntegDev integ = {};
   IntegPrm iprm = {};
   uint8_t *d_sort_need = nullptr;  // [ncells*13]
+  int *d_unit_list = nullptr, *d_unit_count = nullptr;
+  bool marks_fresh = false;        // k_mark_sorts has run for the current active set
   float integ_ms[4] = {};          // last drift, kick1, kick2, timestep (CUDA events on the stream)
 };
 
@@ -179,6 +181,7 @@ static int upload_consts(swift_cuda_ctx *c) {
 // Copies the caller's arrays to the device as they are and permutes them into the cell-ordered
 // SoA layout there (k_pack).  with_static: also mat_id / id / the order table (build only).
 static int upload_and_pack(swift_cuda_ctx *c, const swift_cuda_parts_in *in, bool with_static) {
+  c->marks_fresh = false;  // time bins may change
   const int64_t n = c->n;
   const int64_t m = (with_static || c->n_io < 0) ? n : c->n_io;  // particles on the bus
   Dev &d = c->dev;
@@ -413,6 +416,7 @@ int swift_cuda_build_from_particles(swift_cuda_ctx *c, const swift_cuda_parts_in
   for (size_t k = 0; k < act.size(); k++)
     if (!act[k] && c->tree.cells[k].count > 0) c->all_cells_active = false;
   c->integ_on = false;
+  c->marks_fresh = false;
   build_worklists(c->prm, c->tree, act, c->wl);
   assign_lanes(c->tree, in->x, c->wl);
   return pack_and_upload(c, in);
@@ -436,6 +440,7 @@ int swift_cuda_build_from_cells(swift_cuda_ctx *c, const swift_cuda_parts_in *in
   for (size_t k = 0; k < act.size(); k++)
     if (!act[k] && c->tree.cells[k].count > 0) c->all_cells_active = false;
   c->integ_on = false;
+  c->marks_fresh = false;
   build_worklists(c->prm, c->tree, act, c->wl);
   assign_lanes(c->tree, in->x, c->wl);
   return pack_and_upload(c, in);
@@ -517,15 +522,34 @@ double swift_cuda_measure_fp32_peak(swift_cuda_ctx *c) {
 }
 
 // ---- phases ----------------------------------------------------------------
-static int launch_sort(swift_cuda_ctx *c) {
+// Time-integration mode: the active set changes per step on the device.  k_mark_sorts flags the sorted
+// lists this step reads and lists the units that hold an active particle; both stay valid until the
+// active set changes (set_time, timestep, a build).
+static int launch_mark(swift_cuda_ctx *c) {
   Dev &d = c->dev;
-  // time-integration mode: the active set changes per step; rebuild only the lists this step reads
-  d.sort_need = c->integ_on ? c->d_sort_need : nullptr;
-  if (d.sort_need && d.n_leaves > 0) {
-    CK(cudaMemsetAsync(d.sort_need, 0, (size_t)d.ncells * 13, c->stream));
+  if (!c->integ_on) {
+    d.sort_need = nullptr;
+    d.unit_list = nullptr;
+    return 0;
+  }
+  if (c->marks_fresh) return 0;
+  d.sort_need = c->d_sort_need;
+  d.unit_list = c->d_unit_list;
+  d.unit_count = c->d_unit_count;
+  CK(cudaMemsetAsync(d.sort_need, 0, (size_t)d.ncells * 13, c->stream));
+  CK(cudaMemsetAsync(d.unit_count, 0, sizeof(int), c->stream));
+  if (d.n_leaves > 0) {
     k_mark_sorts<<<(d.n_leaves * 32 + 255) / 256, 256, 0, c->stream>>>(d);
     c->counters.n_kernel_launches += 1;
   }
+  CK(cudaGetLastError());
+  c->marks_fresh = true;
+  return 0;
+}
+
+static int launch_sort(swift_cuda_ctx *c) {
+  Dev &d = c->dev;
+  if (launch_mark(c)) return 1;
   if (c->n_seg > 0) {
     const int grid = d.sort_need ? (c->n_seg + 255) / 256 : c->n_seg;
     k_sort<<<grid, 256, 0, c->stream>>>(c->dev, c->n_seg, c->d_seg_cell, c->d_seg_sid, c->d_seg_off, c->d_scratch,
@@ -550,6 +574,7 @@ static int launch_cell_box(swift_cuda_ctx *c) {
 
 static int launch_density(swift_cuda_ctx *c) {
   Dev &d = c->dev;
+  if (launch_mark(c)) return 1;
   const int nb = (int)((c->n + 255) / 256);
   CK(cudaMemsetAsync(d.hits, 0, 3 * sizeof(unsigned long long), c->stream));
   CK(cudaMemsetAsync(d.redo_count, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
@@ -1043,7 +1068,8 @@ int swift_cuda_integrator_init(swift_cuda_ctx *c, const swift_cuda_integrator *p
   const int64_t n = c->n;
   if (dmalloc(c, &g.vu_full, (size_t)n) || dmalloc(c, &g.xdiff, (size_t)n) || dmalloc(c, &g.xdiff_sort, (size_t)n) ||
       dmalloc(c, &g.dx2_max, 2) || dmalloc(c, &g.ti_end_min, 1) || dmalloc(c, &g.updated, 1) ||
-      dmalloc(c, &g.too_small, 1) || dmalloc(c, &c->d_sort_need, (size_t)c->dev.ncells * 13))
+      dmalloc(c, &g.too_small, 1) || dmalloc(c, &c->d_sort_need, (size_t)c->dev.ncells * 13) ||
+      dmalloc(c, &c->d_unit_list, (size_t)std::max(c->dev.n_units, 1)) || dmalloc(c, &c->d_unit_count, 1))
     return 1;
   c->iprm.cfl = p->cfl_condition;
   c->iprm.log_max_h_change = p->log_max_h_change;
@@ -1057,6 +1083,7 @@ int swift_cuda_integrator_init(swift_cuda_ctx *c, const swift_cuda_integrator *p
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(c->stream));
   c->integ_on = true;
+  c->marks_fresh = false;
   return 0;
 }
 
@@ -1064,6 +1091,7 @@ int swift_cuda_set_time(swift_cuda_ctx *c, long long ti_current, int max_active_
   NEED_INTEG(c);
   c->iprm.ti_current = ti_current;
   c->prm.max_active_bin = max_active_bin;
+  c->marks_fresh = false;
   if (upload_consts(c)) return 1;
   CK(cudaStreamSynchronize(c->stream));
   return 0;
@@ -1113,6 +1141,7 @@ int swift_cuda_timestep(swift_cuda_ctx *c, long long *ti_end_min, long long *upd
   CK(cudaMemsetAsync(c->integ.updated, 0, sizeof(unsigned long long), c->stream));
   CK(cudaMemsetAsync(c->integ.too_small, 0, sizeof(int), c->stream));
   CK(cudaEventRecord(c->ev[0], c->stream));
+  c->marks_fresh = false;  // time bins change
   if (c->n > 0) k_timestep<<<(int)((c->n + 255) / 256), 256, 0, c->stream>>>(c->dev, c->integ, c->iprm);
   CK(cudaGetLastError());
   CK(cudaEventRecord(c->ev[5], c->stream));
