@@ -186,6 +186,16 @@ def test_gpu_resident_loop_matches_oracle_and_golden(name):
         _assert_state_equal(g, ref_states[step], "%s step %d" % (name, step))
 
     sg, lg = il.run_loop_gpu(be, icc, ip, tree, nsteps, on_step=check)
+    t = be.integrator_timings()
+    assert all(t[k] > 0.0 for k in ("drift_ms", "kick1_ms", "kick2_ms", "timestep_ms"))
+    # after a re-sort the host zeroes x_diff_sort only (runner_do_hydro_sort: xp->x_diff_sort = 0), after a
+    # rebuild both (space_rebuild)
+    assert np.abs(sg["x_diff_sort"]).max() > 0
+    be.reset_offsets(1)
+    s1 = be.state()
+    assert not s1["x_diff_sort"].any() and np.array_equal(s1["x_diff"], sg["x_diff"])
+    be.reset_offsets(2)
+    assert not be.state()["x_diff"].any()
     be.close()
     assert [l[:3] + l[5:] for l in lg] == [l[:3] + l[5:] for l in lo], "active counts / sync points differ"
     assert np.array_equal(np.array(lg, dtype=np.float32), np.array(lo, dtype=np.float32)), "dx_max differ"
