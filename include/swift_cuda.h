@@ -265,7 +265,8 @@ int swift_cuda_refresh_cell_hmax(swift_cuda_ctx *ctx, int after_ghost);
  * (engine_policy_drift_all):
  *   set_time(ti_current, get_max_active_bin(ti_current)); drift(ti_old); step(SORT); kick(2); timestep; kick(1)
  * The context must have been built with every cell in the work lists (max_active_bin = 56 at the build:
- * which particles are active then changes per step on the device only). */
+ * which particles are active then changes per step on the device only).  In this mode the raw first-pass
+ * sums (swift_cuda_parts_out.d_*) are not kept. */
 typedef struct {
   float cfl_condition;           /* hydro_props->CFL_condition */
   float log_max_h_change;        /* hydro_props->log_max_h_change */

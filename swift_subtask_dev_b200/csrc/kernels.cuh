@@ -357,10 +357,13 @@ __global__ void __launch_bounds__(256) k_sort(Dev d, int n_seg, const int32_t *s
 __global__ void k_init_step(Dev d) {
   const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (p >= d.n) return;
-  d.dens0[p] = make_float4(0.f, 0.f, 0.f, 0.f);
-  d.dens1[p] = make_float4(0.f, 0.f, 0.f, 0.f);
   const bool active = d.time_bin[p] <= kc.max_active_bin;
   d.gstate[p] = active ? 1 : 0;
+  // time-integration mode (unit_list set): most steps have few active particles and nothing below is
+  // read for the others, so their 45 bytes are not written
+  if (!active && d.unit_list != nullptr) return;
+  d.dens0[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+  d.dens1[p] = make_float4(0.f, 0.f, 0.f, 0.f);
   d.left[p] = 0.f;
   d.right[p] = kc.h_max;
   d.min_bin[p] = kNumTimeBins + 1;

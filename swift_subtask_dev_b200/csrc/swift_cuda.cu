@@ -89,6 +89,13 @@ static void free_device(swift_cuda_ctx *c) {
   for (void *p : c->allocs) cudaFree(p);
   c->allocs.clear();
   c->built = false;
+  // the time-integration state lived in those allocations
+  c->integ_on = false;
+  c->marks_fresh = false;
+  c->integ = IntegDev{};
+  c->d_sort_need = nullptr;
+  c->d_unit_list = nullptr;
+  c->d_unit_count = nullptr;
 }
 
 extern "C" {
@@ -588,9 +595,12 @@ static int launch_density(swift_cuda_ctx *c) {
   if (d.n_units > 0) k_density<0><<<c->grid_density, kBlock, 0, c->stream>>>(d, 0);
   c->counters.n_kernel_launches += 2;
   CK(cudaGetLastError());
-  // keep the raw first-pass sums for inspection (parity tests)
-  CK(cudaMemcpyAsync(c->d_dens0_first, d.dens0, c->n * sizeof(float4), cudaMemcpyDeviceToDevice, c->stream));
-  CK(cudaMemcpyAsync(c->d_dens1_first, d.dens1, c->n * sizeof(float4), cudaMemcpyDeviceToDevice, c->stream));
+  // keep the raw first-pass sums for inspection (parity tests); not in time-integration mode, where a
+  // step may touch a handful of particles and two O(n) copies would be a third of it
+  if (!c->integ_on) {
+    CK(cudaMemcpyAsync(c->d_dens0_first, d.dens0, c->n * sizeof(float4), cudaMemcpyDeviceToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->d_dens1_first, d.dens1, c->n * sizeof(float4), cudaMemcpyDeviceToDevice, c->stream));
+  }
   return 0;
 }
 
@@ -1066,10 +1076,11 @@ int swift_cuda_integrator_init(swift_cuda_ctx *c, const swift_cuda_integrator *p
   if (!(p->time_base > 0.0)) return fail("integrator_init: time_base must be positive");
   IntegDev &g = c->integ;
   const int64_t n = c->n;
-  if (dmalloc(c, &g.vu_full, (size_t)n) || dmalloc(c, &g.xdiff, (size_t)n) || dmalloc(c, &g.xdiff_sort, (size_t)n) ||
+  if (g.vu_full == nullptr &&  // a second call on the same build re-initialises in place
+      (dmalloc(c, &g.vu_full, (size_t)n) || dmalloc(c, &g.xdiff, (size_t)n) || dmalloc(c, &g.xdiff_sort, (size_t)n) ||
       dmalloc(c, &g.dx2_max, 2) || dmalloc(c, &g.ti_end_min, 1) || dmalloc(c, &g.updated, 1) ||
       dmalloc(c, &g.too_small, 1) || dmalloc(c, &c->d_sort_need, (size_t)c->dev.ncells * 13) ||
-      dmalloc(c, &c->d_unit_list, (size_t)std::max(c->dev.n_units, 1)) || dmalloc(c, &c->d_unit_count, 1))
+      dmalloc(c, &c->d_unit_list, (size_t)std::max(c->dev.n_units, 1)) || dmalloc(c, &c->d_unit_count, 1)))
     return 1;
   c->iprm.cfl = p->cfl_condition;
   c->iprm.log_max_h_change = p->log_max_h_change;

@@ -204,6 +204,20 @@ def test_gpu_resident_loop_matches_oracle_and_golden(name):
 
 
 @pytest.mark.gpu
+def test_gpu_rebuild_and_reinit_reproduce_the_run():
+    """A rebuild frees the integrator's device state with everything else; building and initialising again on
+    the same context (what a host does after space_rebuild) gives the same run, bit for bit."""
+    icc, tree, kw, ip, variant, nsteps, eos = _case("clustered4k_bins")
+    be = _gpu_backend(kw, eos)
+    s1, l1 = il.run_loop_gpu(be, icc, ip, tree, 3)
+    s2, l2 = il.run_loop_gpu(be, icc, ip, tree, 3)     # build_from_cells + integrator_init again
+    be.integrator_init(**ip)                            # a second init on the same build is allowed
+    be.close()
+    assert l1 == l2
+    _assert_state_equal(s1, s2, "second run on the same context")
+
+
+@pytest.mark.gpu
 def test_gpu_integrator_needs_all_cells_in_the_work_lists():
     """A context built with part of the particles inactive has dropped their cells from the work lists."""
     import parity
