@@ -96,6 +96,9 @@ struct Dev {
   const int32_t *unit_leaf;    // [n_units] warp unit -> leaf slot
   const int32_t *unit_begin;   // [n_leaves+1] first unit of a leaf
   const int32_t *lane_part;    // [n_units*32] particle of each lane, or -1
+  // leaf-resident kernels (leaf_kernels.cuh): groups of up to kLW consecutive units of one leaf
+  const int4 *groups;          // [n_groups] {leaf slot, first unit, units, 0}
+  int n_groups;
   // sparse redo sweeps: the leaves that hold a particle flagged in this sweep, pushed by k_ghost
   const int32_t *part_slot;    // [n] leaf slot of a particle (-1: its leaf has no work)
   int *leaf_mark;              // [n_leaves] sweep + 1 of the last push

@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "kernels.cuh"
+#include "leaf_kernels.cuh"
 #include "pack.cuh"
 #include "integrate.cuh"
 
@@ -68,7 +69,17 @@ struct swift_cuda_ctx {
   int *d_unit_list = nullptr, *d_unit_count = nullptr;
   bool marks_fresh = false;        // k_mark_sorts has run for the current active set
   float integ_ms[4] = {};          // last drift, kick1, kick2, timestep (CUDA events on the stream)
+  // which neighbour-loop kernels run: bit 0 leaf-resident first density pass, bit 1 fused ghost + redo,
+  // bit 2 leaf-resident force (FAST field arithmetic).  0: the first-generation warp-per-unit kernels.
+  int path = 0;
+  int force_slow = 0;  // test hook (SWIFT_CUDA_SLOW=1): every hit takes the exact sorted-axis-cut path
 };
+
+// leaf-resident kernel configurations (shared-memory tile capacity, queue depth)
+constexpr int kDensCap = 960, kDensQD = 80;
+typedef LeafTile<kDensCap, kDensQD, 1> DensTileT;
+constexpr int kGhostCap = 1152, kGhostQD = 112;
+typedef LeafTile<kGhostCap, kGhostQD, 2> GhostTileT;
 
 template <typename T>
 static int dmalloc(swift_cuda_ctx *c, T **p, size_t count) {
@@ -133,6 +144,12 @@ int swift_cuda_create(const swift_cuda_params *params, int device, swift_cuda_ct
   CK(cudaStreamCreateWithFlags(&c->io, cudaStreamNonBlocking));
   for (auto &e : c->io_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   std::memset(&c->dev, 0, sizeof(Dev));
+  if (const char *e = getenv("SWIFT_CUDA_PATH")) c->path = atoi(e);
+  if (const char *e = getenv("SWIFT_CUDA_SLOW")) c->force_slow = atoi(e);
+  CK(cudaFuncSetAttribute(k_density_leaf<kDensCap, kDensQD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                          (int)sizeof(DensTileT)));
+  CK(cudaFuncSetAttribute(k_ghost_leaf<kGhostCap, kGhostQD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                          (int)sizeof(GhostTileT)));
   *out = c;
   return 0;
 }
@@ -319,6 +336,17 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
     return 1;
   d.leaves = dlv; d.item_begin = dib; d.items = dit; d.redo_begin = drb; d.redo_items = drt;
   d.unit_leaf = dul; d.unit_begin = duo; d.lane_part = dlp; d.sort_lookup = dsl;
+  {
+    std::vector<int4> groups;
+    for (size_t sl = 0; sl < wl.leaves.size(); sl++)
+      for (int u = wl.unit_begin[sl]; u < wl.unit_begin[sl + 1]; u += kLW)
+        groups.push_back(make_int4((int)sl, u, std::min(kLW, wl.unit_begin[sl + 1] - u), 0));
+    int4 *dg;
+    if (upload(c, &dg, groups.data(), groups.size())) return 1;
+    d.groups = dg;
+    d.n_groups = (int)groups.size();
+    CK(cudaStreamSynchronize(c->stream));  // groups goes out of scope
+  }
   {
     std::vector<int32_t> slot_of((size_t)c->n, -1);
     for (size_t sl = 0; sl < wl.leaves.size(); sl++) {
@@ -592,7 +620,12 @@ static int launch_density(swift_cuda_ctx *c) {
   CK(cudaMemsetAsync(d.work_ctr, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
   if (launch_cell_box(c)) return 1;
   k_init_step<<<nb, 256, 0, c->stream>>>(d);
-  if (d.n_units > 0) k_density<0><<<c->grid_density, kBlock, 0, c->stream>>>(d, 0);
+  if ((c->path & 1) && !c->integ_on) {
+    if (d.n_groups > 0)
+      k_density_leaf<kDensCap, kDensQD><<<d.n_groups, kLT, sizeof(DensTileT), c->stream>>>(d, c->force_slow);
+  } else if (d.n_units > 0) {
+    k_density<0><<<c->grid_density, kBlock, 0, c->stream>>>(d, 0);
+  }
   c->counters.n_kernel_launches += 2;
   CK(cudaGetLastError());
   // keep the raw first-pass sums for inspection (parity tests); not in time-integration mode, where a
@@ -606,6 +639,15 @@ static int launch_density(swift_cuda_ctx *c) {
 
 static int launch_ghost(swift_cuda_ctx *c) {
   Dev &d = c->dev;
+  if ((c->path & 2) && !c->integ_on) {
+    // the whole smoothing-length iteration of a leaf inside one CTA (leaf_kernels.cuh)
+    if (d.n_groups > 0)
+      k_ghost_leaf<kGhostCap, kGhostQD><<<d.n_groups, kLT, sizeof(GhostTileT), c->stream>>>(d, c->force_slow);
+    k_cell_hmax<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d);
+    c->counters.n_kernel_launches += 2;
+    CK(cudaGetLastError());
+    return 0;
+  }
   const int nb = (int)std::min<int64_t>((c->n + 255) / 256, 148 * 16);  // grid-stride kernel
   // Fixed launch sequence, no host round trip: every kernel looks at the device-side
   // redo counter of the sweep before and leaves at once when nothing is pending.
@@ -653,6 +695,13 @@ static int finish_counters(swift_cuda_ctx *c) {
   CK(cudaMemcpyAsync(hits, d.hits, sizeof(hits), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaMemcpyAsync(redo.data(), d.redo_count, redo.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
+#ifdef SWIFT_CUDA_GHOST_STATS
+  {
+    int st[12];
+    CK(cudaMemcpy(st, d.work_ctr, sizeof(st), cudaMemcpyDeviceToHost));
+    fprintf(stderr, "ghost stats: rebuilds %d cta-sweeps %d multichunk %d overflow %d groups %d | kcycles(thread0) stage %d filter %d drain %d | tile used avg %.0f q0 avg %.1f\n", st[4], st[5], st[2], st[3], d.n_groups, st[6] / 16, st[7] / 16, st[8] / 16, st[9] / (double)std::max(st[4], 1), st[10] / (double)std::max(st[4], 1));
+  }
+#endif
   c->counters.n_density = (long long)hits[0];
   c->counters.n_density_redo = (long long)hits[1];
   c->counters.n_force = (long long)hits[2];
