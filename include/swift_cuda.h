@@ -31,9 +31,18 @@
 extern "C" {
 #endif
 
-#define SWIFT_CUDA_ABI_VERSION 1
+#define SWIFT_CUDA_ABI_VERSION 2
 
 enum { SWIFT_CUDA_SCHEME_MINIMAL = 0, SWIFT_CUDA_SCHEME_PLANETARY = 1 };
+
+/* How the per-particle FIELDS are computed.  Which pairs interact -- the neighbour lists and
+ * counts of every loop, and therefore h -- is bit-exact in both modes.
+ *   EXACT  every field bit-identical to the single-threaded reference built without FMA
+ *          contraction: reference operand order, IEEE division, hits consumed in task order;
+ *   FAST   the force loop's arithmetic uses FMA contraction and MUFU reciprocals / rsqrt:
+ *          a, u_dt, h_dt, v_sig agree with the reference within the tolerances of the project
+ *          (<= 1e-4 relative, max over particles); h, rho, P, c, f, balsara stay bit-identical. */
+enum { SWIFT_CUDA_FIELDS_EXACT = 0, SWIFT_CUDA_FIELDS_FAST = 1 };
 
 /* Tillotson material, INTERNAL units -- a copy of the reference's
  * struct Til_params after convert_units_Til
@@ -63,6 +72,7 @@ typedef struct {
   int n_til;
   swift_cuda_til til[8];
   float idg_gamma[4]; /* planetary ideal-gas gammas for mat_id 0..3 */
+  int fields_mode;    /* SWIFT_CUDA_FIELDS_* */
 } swift_cuda_params;
 
 /* One cell of the caller's tree: struct cell {loc, width, hydro.parts - parts,

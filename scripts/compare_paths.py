@@ -15,8 +15,9 @@ import numpy as np
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 
 
-def run(ic, path, prm_kw, reps=1):
+def run(ic, path, prm_kw, reps=1, fields=0):
     os.environ["SWIFT_CUDA_PATH"] = str(path)
+    os.environ["SWIFT_CUDA_FIELDS"] = str(fields)
     from swift_subtask_dev_b200 import HydroBackend, make_params
     be = HydroBackend(make_params(**prm_kw))
     be.build(ic)
@@ -39,6 +40,7 @@ def main():
     ap.add_argument("--workload", default="uniform")
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--open", action="store_true")
+    ap.add_argument("--fast", action="store_true")
     a = ap.parse_args()
     from swift_subtask_dev_b200 import ics
     n = a.side ** 3
@@ -50,13 +52,13 @@ def main():
         ic = ics.lattice(a.side, jitter=0.1, seed=1234)
     kw = dict(periodic=not a.open)
     o0, c0, t0 = run(ic, 0, kw, a.reps)
-    o1, c1, t1 = run(ic, a.path, kw, a.reps)
+    o1, c1, t1 = run(ic, a.path, kw, a.reps, 1 if a.fast else 0)
     res = {"n": n, "path": a.path, "t_old": t0, "t_new": t1}
     ok = True
     for k in ("n_density", "n_density_redo", "n_force", "ghost_sweeps"):
         res[k] = (c0[k], c1[k])
         ok &= c0[k] == c1[k]
-    soft = {"a", "u_dt", "h_dt", "v_sig"} if (a.path & 4) else set()
+    soft = {"a", "u_dt", "h_dt", "v_sig"} if ((a.path & 4) or a.fast) else set()
     for k in o0:
         x, y = np.asarray(o0[k]), np.asarray(o1[k])
         nbad = int(np.count_nonzero((x != y) & ~(np.isnan(x.astype(np.float64)) & np.isnan(y.astype(np.float64)))))

@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(_HERE, "libswiftcuda.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 SCHEME_MINIMAL, SCHEME_PLANETARY = 0, 1
+FIELDS_EXACT, FIELDS_FAST = 0, 1
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared", "-fmad=false"]
@@ -26,7 +27,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 def build_library(verbose=False, force=False):
     """Compiles the CUDA backend in-tree with nvcc for sm_100a."""
     srcs = [os.path.join(CSRC, f) for f in ("swift_cuda.cu", "host_tree.cpp")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.cuh", "leaf_kernels.cuh", "integrate.cuh", "pack.cuh", "device_types.cuh", "host_tree.hpp")] + \
+    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.cuh", "leaf_kernels.cuh", "list_kernels.cuh", "integrate.cuh", "pack.cuh", "device_types.cuh", "host_tree.hpp")] + \
         [os.path.join(ROOT, "include", "swift_cuda.h")]
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
         return LIB_PATH
@@ -51,7 +52,7 @@ class Params(C.Structure):
                 ("h_tolerance", C.c_float), ("h_max", C.c_float), ("h_min", C.c_float),
                 ("max_smoothing_iterations", C.c_int), ("viscosity_alpha", C.c_float),
                 ("max_active_bin", C.c_int), ("scheme", C.c_int), ("cosmo_a", C.c_float), ("cosmo_H", C.c_float),
-                ("n_til", C.c_int), ("til", Til * 8), ("idg_gamma", C.c_float * 4)]
+                ("n_til", C.c_int), ("til", Til * 8), ("idg_gamma", C.c_float * 4), ("fields_mode", C.c_int)]
 
 
 class Cell(C.Structure):
@@ -188,7 +189,8 @@ def host_plan(params, ic):
 
 
 def make_params(dim=(1.0, 1.0, 1.0), periodic=True, eta=1.2348, h_tolerance=1e-4, h_max=1e10, h_min=0.0,
-                max_iter=30, alpha=0.8, max_active_bin=56, scheme=SCHEME_MINIMAL, til=(), idg_gamma=(5. / 3.,) * 4):
+                max_iter=30, alpha=0.8, max_active_bin=56, scheme=SCHEME_MINIMAL, til=(), idg_gamma=(5. / 3.,) * 4,
+                fields_mode=0):
     p = Params()
     p.dim[:] = dim
     p.periodic = int(periodic)
@@ -206,6 +208,7 @@ def make_params(dim=(1.0, 1.0, 1.0), periodic=True, eta=1.2348, h_tolerance=1e-4
     for k, t in enumerate(til):
         p.til[k] = t
     p.idg_gamma[:] = idg_gamma
+    p.fields_mode = fields_mode
     return p
 
 

@@ -117,6 +117,12 @@ struct Dev {
   // counters: [0] density, [1] redo, [2] force
   unsigned long long *hits;
   int *redo_count;         // [max_iter+1]
+  // neighbour lists of the ghost iteration (null: not recorded): [n_units][kLD][32] (dx, dy, dz, j)
+  float4 *nl;
+  unsigned short *nl_cnt;      // [n_units*32] entries of a lane's list, 0xffff: none / overflowed
+  float *nl_R;                 // [n_units*32] (h gamma)^2 the list covers
+  float nl_grow;               // the recording sweep covers nl_grow x the search radius
+  const int32_t *part_lane;    // [n] unit * 32 + lane of a particle, -1: none
   // pair recording (test hook)
   long long *rec_pairs[3];
   unsigned long long *rec_count;  // [3]

@@ -30,6 +30,13 @@ constexpr int kBlock = 32 * kWarps;
 constexpr int kNumTimeBins = 56;
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int kDpFlag = 0x40000000;  // queue entry: dx must be recomputed from the f64 positions
+constexpr int kInWin = 0x20000000;   // queue entry (list-recording redo sweep): inside the sorted-axis cut of the CURRENT h
+constexpr int kIdxMask = kInWin - 1;
+// Neighbour lists of the ghost iteration: the redo sweep that walks the cells also records, per lane,
+// every candidate within nl_grow x the search radius as (dx, dy, dz, j) exactly as the reference forms
+// dx; the following sweeps re-test that list against the new h (k_density_list) instead of walking.
+constexpr int kLD = 96;              // list entries per lane
+
 
 // ---------------------------------------------------------------------------
 // small helpers
@@ -117,6 +124,7 @@ struct ForceAcc {
 struct ForceI {  // per-i quantities hoisted out of the neighbour loop
   float h, hi_inv, hid_inv, m, rho, P, f, c, bal, vx, vy, vz;
   float Pr2;  // P / rho^2
+  float m_inv;  // FAST form: 1 / m
 };
 struct ForceJ {
   float h, m, rho, P, f, c, bal, vx, vy, vz;
@@ -176,6 +184,75 @@ __device__ __forceinline__ void iact_force(ForceAcc &a, float r2, float dx, floa
     a.h_dt -= pj.m * dvdr * r_inv / pj.rho * wi_dr;
   else
     a.h_dt -= pj.m * dvdr * r_inv / pj.rho * wi_dr * f_ij;
+  a.v_sig = fmaxf(a.v_sig, v_sig);
+  if (pj.bin > 0) a.min_bin = min(a.min_bin, pj.bin);
+}
+
+// FAST form of runner_iact_nonsym_force (swift_cuda_params.fields_mode = SWIFT_CUDA_FIELDS_FAST): the same
+// expressions with FMA contraction and the reciprocals / square root by MUFU (rcp.approx, rsqrt.approx:
+// ~1 ulp) instead of IEEE division sequences.  Which pairs interact is decided elsewhere, exactly; the
+// accelerations, du/dt, dh/dt and v_sig agree with the reference to ~1e-6 of the summed terms.
+__device__ __forceinline__ float fast_rcp(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void kernel_deval_fast(float u, float &W, float &dW) {
+  const float x = u * kc.gamma_inv;
+  const int t = (int)(x * 2.f);
+  float c0, c1, c2, c3;
+  if (t <= 0) {
+    c0 = 3.f; c1 = -3.f; c2 = 0.f; c3 = 0.5f;
+  } else if (t == 1) {
+    c0 = -1.f; c1 = 3.f; c2 = -3.f; c3 = 1.f;
+  } else {
+    c0 = 0.f; c1 = 0.f; c2 = 0.f; c3 = 0.f;
+  }
+  float w = __fmaf_rn(c0, x, c1);
+  float dw = __fmaf_rn(c0, x, w);
+  w = __fmaf_rn(x, w, c2);
+  dw = __fmaf_rn(dw, x, w);
+  w = __fmaf_rn(x, w, c3);
+  w = fmaxf(w, 0.f);
+  dw = fminf(dw, 0.f);
+  W = w * (kc.kconst * kc.ginv_dim);
+  dW = dw * (kc.kconst * kc.ginv_dim_p1);
+}
+template <int SCHEME>
+__device__ __forceinline__ void iact_force_fast(ForceAcc &a, float r2, float dx, float dy, float dz, const ForceI &pi,
+                                                const ForceJ &pj) {
+  const float a2_Hubble = kc.a * kc.a * kc.H;
+  const float r_inv = r2 > 0.f ? rsqrtf(r2) : 0.f;
+  const float r = r2 * r_inv;
+  float wi, wi_dx, wj, wj_dx;
+  kernel_deval_fast(r * pi.hi_inv, wi, wi_dx);
+  const float wi_dr = pi.hid_inv * wi_dx;
+  const float hj_inv = fast_rcp(pj.h);
+  const float hj2 = hj_inv * hj_inv;
+  kernel_deval_fast(r * hj_inv, wj, wj_dx);
+  const float wj_dr = hj2 * hj2 * wj_dx;
+  const float f_ij = __fmaf_rn(-pi.f, fast_rcp(pj.m), 1.f);
+  const float f_ji = __fmaf_rn(-pj.f, pi.m_inv, 1.f);
+  const float P_over_rho2_i = pi.Pr2 * f_ij;
+  const float P_over_rho2_j = pj.Pr2 * f_ji;
+  float dvdr = __fmaf_rn(pi.vz - pj.vz, dz, __fmaf_rn(pi.vy - pj.vy, dy, (pi.vx - pj.vx) * dx));
+  const float dvdr_H = __fmaf_rn(a2_Hubble, r2, dvdr);
+  if (SCHEME == SWIFT_CUDA_SCHEME_PLANETARY) dvdr = dvdr_H;
+  const float mu_ij = r_inv * fminf(dvdr_H, 0.f);
+  const float v_sig = __fmaf_rn(-kc.beta, mu_ij, pi.c + pj.c);
+  const float rho_ij_inv = fast_rcp(0.5f * (pi.rho + pj.rho));
+  const float visc = -0.25f * v_sig * mu_ij * (pi.bal + pj.bal) * rho_ij_inv;
+  const float visc_acc_term = 0.5f * visc * __fmaf_rn(wi_dr, f_ij, wj_dr * f_ji) * r_inv;
+  const float sph_acc_term = __fmaf_rn(P_over_rho2_i, wi_dr, P_over_rho2_j * wj_dr) * r_inv;
+  const float macc = pj.m * (sph_acc_term + visc_acc_term);
+  a.ax = __fmaf_rn(-macc, dx, a.ax);
+  a.ay = __fmaf_rn(-macc, dy, a.ay);
+  a.az = __fmaf_rn(-macc, dz, a.az);
+  const float sph_du_term_i = P_over_rho2_i * dvdr * r_inv * wi_dr;
+  a.u_dt = __fmaf_rn(__fmaf_rn(0.5f * visc_acc_term, dvdr_H, sph_du_term_i), pj.m, a.u_dt);
+  float hterm = pj.m * dvdr * r_inv * fast_rcp(pj.rho) * wi_dr;
+  if (SCHEME != SWIFT_CUDA_SCHEME_PLANETARY) hterm *= f_ij;
+  a.h_dt -= hterm;
   a.v_sig = fmaxf(a.v_sig, v_sig);
   if (pj.bin > 0) a.min_bin = min(a.min_bin, pj.bin);
 }
@@ -523,6 +600,70 @@ __device__ __forceinline__ bool box_reaches_cell(const StageBox &b, const float 
   return r;
 }
 
+// delta of the safe zone: a hit with r < H - delta passes every sorted-axis cut of the reference
+// whatever the rounding of the keys (|key| <= sqrt(3) max|x|, f32)
+__device__ __forceinline__ float cut_delta(const Dev &d) {
+  return 6e-7f * (float)(fabs(d.dim[0]) + fabs(d.dim[1]) + fabs(d.dim[2]));
+}
+__device__ __forceinline__ float safe_r2(float H, float delta, bool force_slow) {
+  const float rs = H - delta;
+  return (force_slow || !(rs > 0.f)) ? -1.f : rs * rs * 0.999999f;
+}
+
+// Exact sorted-axis cuts of the density loops for one (lane, candidate): the slow path of hits
+// within delta of the search radius.  key: sort key of the candidate.
+// What the exact-cut slow paths read of Dev (a __noinline__ function taking Dev itself would force the
+// kernel's copy of it onto the local-memory stack).
+struct CutCtx {
+  const CellDev *cells;
+  const int64_t *sort_lookup;
+  const SortEnt *sort;
+  const float *cell_hmax;
+  double dim[3];
+};
+__device__ __forceinline__ CutCtx cut_ctx(const Dev &d) {
+  CutCtx c;
+  c.cells = d.cells; c.sort_lookup = d.sort_lookup; c.sort = d.sort; c.cell_hmax = d.cell_hmax;
+  c.dim[0] = d.dim[0]; c.dim[1] = d.dim[1]; c.dim[2] = d.dim[2];
+  return c;
+}
+__device__ __noinline__ bool dens_cut_exact(const CutCtx d, const Item item, double xi, double yi, double zi,
+                                            float hig, float key) {
+  const int kind = item.kind, sid = item.sid;
+  if (kind == kSelf || kind == kSubSelf) return true;
+  const CellDev cB = d.cells[item.partner];
+  double sh[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) sh[k] = (double)item_shift_i(item.shift, k) * d.dim[k];
+  const int64_t segB = d.sort_lookup[(int64_t)item.partner * 13 + sid];
+  if (kind == kPairLeft) {
+    // DOPAIR1 loop 1 (:1122-1216)
+    const double rshift = item_rshift(sh, sid);
+    const float d_me = sort_key(xi, yi, zi, sid);
+    const double dj_min = (double)d.sort[segB].d;
+    const double hi_max = __dsub_rn((double)__fmul_rn(d.cell_hmax[item.own], kc.gamma), rshift);
+    const double di = __dsub_rn((double)__fadd_rn(d_me, hig), rshift);
+    if (!((__dadd_rn((double)d_me, hi_max) > dj_min) && !(di < dj_min))) return false;
+    return key <= thr_lt(di);
+  } else if (kind == kPairRight) {
+    // DOPAIR1 loop 2 (:1222-1316)
+    const double rshift = item_rshift(sh, sid);
+    const float d_me = sort_key(xi, yi, zi, sid);
+    const double di_max = __dsub_rn((double)d.sort[segB + cB.count - 1].d, rshift);
+    const double hj_max = (double)__fmul_rn(d.cell_hmax[item.own], kc.gamma);
+    const double dj = __dadd_rn((double)__fsub_rn(d_me, hig), rshift);
+    if (!((__dsub_rn((double)d_me, hj_max) < di_max) && !(__dsub_rn(dj, rshift) > di_max))) return false;
+    return key >= thr_gt(dj);
+  }
+  // DOPAIR_SUBSET (:745-770, 794-838)
+  const double px = __dsub_rn(xi, sh[0]), py = __dsub_rn(yi, sh[1]), pz = __dsub_rn(zi, sh[2]);
+  const float hg = (kind == kSubPair) ? __fadd_rn(hig, 0.f) : __fsub_rn(-hig, 0.f);
+  const double cut = __dadd_rn(__dadd_rn(__dadd_rn((double)hg, __dmul_rn(px, kc.axis[sid][0])),
+                                         __dmul_rn(py, kc.axis[sid][1])),
+                               __dmul_rn(pz, kc.axis[sid][2]));
+  return kind == kSubPair ? (key <= thr_lt(cut)) : (key >= thr_gt(cut));
+}
+
 // ---------------------------------------------------------------------------
 // K3 / K5: density.
 // MODE 0: first pass, DOSELF1 / DOPAIR1 arithmetic, every active particle;
@@ -617,12 +758,23 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
       DensAcc acc;
       acc.zero();
       int qcnt = 0;
+      // list-recording sweep: the walk covers kGrowL x the search radius
+      const bool recl = MODE == 1 && d.nl != nullptr;
+      const float higR = recl ? __fmul_rn(hig, d.nl_grow) : hig;
+      const float hig2R = recl ? __fmul_rn(__fmul_rn(higR, higR), 1.000001f) : hig2;
+      int ln = 0;
+      float4 *nlp = nullptr;
+      int ul = -1;
+      if (recl && mine) {
+        ul = d.part_lane[p];
+        nlp = d.nl + ((size_t)(ul >> 5) * kLD) * 32 + (ul & 31);
+      }
 
       // box of the unit's particles, each grown by its search radius, in the leaf's frame
       float ulo[3], uhi[3];
       {
         const float l[3] = {dsub_f(xi, cL.loc[0]), dsub_f(yi, cL.loc[1]), dsub_f(zi, cL.loc[2])};
-        const float ru = hig * 1.0001f;
+        const float ru = higR * 1.0001f;
 #pragma unroll
         for (int k = 0; k < 3; k++) {
           ulo[k] = warp_min(mine ? l[k] - ru : INFINITY);
@@ -649,10 +801,14 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
           dx = e.x; dy = e.y; dz = e.z;
         }
         const float r2 = dist2(dx, dy, dz);
-        if (r2 < hig2) {
+        if (recl && r2 < hig2R) {
+          if (ln < kLD) nlp[(size_t)ln * 32] = make_float4(dx, dy, dz, __int_as_float(w & kIdxMask));
+          ln++;
+        }
+        if (r2 < hig2 && (!recl || (w & kInWin))) {
           iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, vmj);
           nhits++;
-          if (rec) record_pair(d, MODE, idi, d.id[w & (kDpFlag - 1)]);
+          if (rec) record_pair(d, MODE, idi, d.id[w & kIdxMask]);
         }
       };
       // software pipeline over the FIFO: entry r+2 is being read, the gathers of entry r+1 are in
@@ -663,7 +819,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
         auto gather = [&](const float4 e, bool ok, float4 &v, double &x, double &y, double &z) {
           if (ok) {
             const int w = __float_as_int(e.w);
-            const int j = w & (kDpFlag - 1);
+            const int j = w & kIdxMask;
             v = d.vm[j];
             if (w & kDpFlag) load_pos(d.pos, j, x, y, z);
           }
@@ -737,9 +893,10 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
         const int64_t segB = sorted ? d.sort_lookup[(int64_t)item.partner * 13 + sid] : 0;
         double px = xi, py = yi, pz = zi;
         float lo = INFINITY, hi_cut = -INFINITY;  // lane's window on the candidates' sort keys (empty)
-        float thr = hig2;
+        float loR = INFINITY, hiR = -INFINITY;    // the same for the radius a list-recording sweep covers
+        float thr = hig2R;
         if (kind == kSelf || kind == kSubSelf) {
-          if (mine) { lo = -INFINITY; hi_cut = INFINITY; }
+          if (mine) { lo = loR = -INFINITY; hi_cut = hiR = INFINITY; }
           if (kind == kSelf) thr = cull_thr(hig2, 4e-7f * cA.width);
         } else if (kind == kPairLeft) {
           // this leaf's particles are "pi" of DOPAIR1 loop 1 (:1122-1216): frame cj.loc + shift
@@ -767,7 +924,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
         } else {
           // DOPAIR_SUBSET (:745-770, 794-838): pix = x - shift in f64, dx = (float)(pix - pj.x)
           px = __dsub_rn(xi, sh[0]); py = __dsub_rn(yi, sh[1]); pz = __dsub_rn(zi, sh[2]);
-          thr = cull_thr(hig2, 8e-7f * fmaxf(cA.width, cB.width));
+          thr = cull_thr(hig2R, 8e-7f * fmaxf(cA.width, cB.width));
           if (mine) {
             const float hg = (kind == kSubPair) ? __fadd_rn(hig, 0.f) : __fsub_rn(-hig, 0.f);
             const double cut = __dadd_rn(__dadd_rn(__dadd_rn((double)hg, __dmul_rn(px, kc.axis[sid][0])),
@@ -775,10 +932,18 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
                                          __dmul_rn(pz, kc.axis[sid][2]));
             if (kind == kSubPair) { lo = -INFINITY; hi_cut = thr_lt(cut); }
             else { lo = thr_gt(cut); hi_cut = INFINITY; }
+            loR = lo; hiR = hi_cut;
+            if (recl) {
+              // the cut of the wider radius, generously: the list is a superset, the exact cut of the
+              // current h travels with every entry (kInWin)
+              const float m = (higR - hig) * 1.01f + 4.f * cut_delta(d);
+              if (kind == kSubPair) hiR = hi_cut + m; else loR = lo - m;
+            }
           }
         }
+        if (!recl) { loR = lo; hiR = hi_cut; }
         // union of the lanes' windows: what is worth staging at all
-        const float wlo = warp_min(lo), whi = warp_max(hi_cut);
+        const float wlo = warp_min(loR), whi = warp_max(hiR);
         if (!(wlo <= whi)) continue;  // no lane takes part
         const float pfx = dsub_f(px, fl[0]), pfy = dsub_f(py, fl[1]), pfz = dsub_f(pz, fl[2]);
 
@@ -801,10 +966,11 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
               const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
               const float r2c = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
               const int j = ti[k0 + u];
-              const bool push = c.w >= lo && c.w <= hi_cut && r2c < thr_c && j != pp;
+              const bool push = c.w >= loR && c.w <= hiR && r2c < thr_c && j != pp;
+              const int inwin = (MODE == 1 && c.w >= lo && c.w <= hi_cut) ? kInWin : 0;
               // straight-line: the store and the FIFO advance are predicated, not branched over
-              if (SHIFTED) st_pred(qp, shf[0], shf[1], shf[2], __int_as_float(j | kDpFlag), push);
-              else st_pred(qp, dx, dy, dz, __int_as_float(j | flagbits), push);
+              if (SHIFTED) st_pred(qp, shf[0], shf[1], shf[2], __int_as_float(j | kDpFlag | inwin), push);
+              else st_pred(qp, dx, dy, dz, __int_as_float(j | flagbits | inwin), push);
               qp += push ? 32 : 0;
             }
           }
@@ -880,6 +1046,10 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
       if (mine) {
         d.dens0[p] = make_float4(acc.rho, acc.rho_dh, acc.wcount, acc.wcount_dh);
         d.dens1[p] = make_float4(acc.div_v, acc.rx, acc.ry, acc.rz);
+        if (recl) {
+          d.nl_cnt[ul] = ln <= kLD ? (unsigned short)ln : (unsigned short)0xffff;
+          d.nl_R[ul] = hig2R;
+        }
       }
     }
   }
@@ -1043,7 +1213,7 @@ __global__ void k_ghost(Dev d, int sweep) {
 
 __device__ __forceinline__ void ghost_particle(const Dev &d, int sweep, int64_t p) {
   const uint8_t st = d.gstate[p];
-  if (st != 1 && st != 2) return;
+  if (st != 1 && st != 2 && st != 4) return;
   const bool planetary = kc.scheme == SWIFT_CUDA_SCHEME_PLANETARY;
   float4 s0 = d.dens0[p];  // rho, rho_dh, wcount, wcount_dh
   float4 s1 = d.dens1[p];  // div_v, rot
@@ -1109,8 +1279,15 @@ __device__ __forceinline__ void ghost_particle(const Dev &d, int sweep, int64_t 
       d.right[p] = right;
       d.dens0[p] = make_float4(0.f, 0.f, 0.f, 0.f);
       d.dens1[p] = make_float4(0.f, 0.f, 0.f, 0.f);
-      d.gstate[p] = 2;
+      // 2: the next redo sweep walks the cells for this particle; 4: its recorded neighbour list covers the new h
+      uint8_t ns = 2;
+      if (d.nl != nullptr) {
+        const int ul = d.part_lane[p];
+        if (ul >= 0 && d.nl_cnt[ul] != 0xffff && sq_gamma2(h) < d.nl_R[ul] * 0.999998f) ns = 4;
+      }
+      d.gstate[p] = ns;
       atomicAdd(&d.redo_count[sweep], 1);
+      if (ns == 4) return;
       const int slot = d.part_slot[p];
       if (slot >= 0 && atomicExch(&d.leaf_mark[slot], sweep + 1) != sweep + 1)
         d.leaf_list[atomicAdd(&d.leaf_count[sweep], 1)] = slot;
@@ -1245,7 +1422,7 @@ struct ForceTile {
   float box[12];      // the unit's boxes (leaf frame): u0 lo/hi, uH lo/hi -- warp-uniform, kept out of the registers
 };
 
-template <int SCHEME>
+template <int SCHEME, bool FAST = false>
 __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
   __shared__ ForceTile tiles[kWarps];
   ForceTile &ws = tiles[threadIdx.x >> 5];
@@ -1292,6 +1469,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
       me.rho = fi.x; me.P = fi.y; me.f = fi.z; me.c = fi.w;
       me.bal = hbi.y;
       me.Pr2 = hbi.w;
+      me.m_inv = 1.0f / me.m;
     }
     const float hig2 = sq_gamma2(me.h);
     const float hig = __fmul_rn(me.h, kc.gamma);
@@ -1342,7 +1520,8 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
         pj.h = hbj.x; pj.bal = hbj.y; pj.bin = __float_as_int(hbj.z); pj.Pr2 = hbj.w;
         pj.m = vmj.w; pj.vx = vmj.x; pj.vy = vmj.y; pj.vz = vmj.z;
         pj.rho = fj.x; pj.P = fj.y; pj.f = fj.z; pj.c = fj.w;
-        iact_force<SCHEME>(acc, r2, dx, dy, dz, me, pj);
+        if (FAST) iact_force_fast<SCHEME>(acc, r2, dx, dy, dz, me, pj);
+        else iact_force<SCHEME>(acc, r2, dx, dy, dz, me, pj);
         nhits++;
         if (rec) record_pair(d, 2, idi, d.id[w & (kDpFlag - 1)]);
       }

@@ -501,70 +501,6 @@ __device__ __forceinline__ bool group_geom(const float (*wbox)[13], float extra,
   return true;
 }
 
-// delta of the safe zone: a hit with r < H - delta passes every sorted-axis cut of the reference
-// whatever the rounding of the keys (|key| <= sqrt(3) max|x|, f32)
-__device__ __forceinline__ float cut_delta(const Dev &d) {
-  return 6e-7f * (float)(fabs(d.dim[0]) + fabs(d.dim[1]) + fabs(d.dim[2]));
-}
-__device__ __forceinline__ float safe_r2(float H, float delta, bool force_slow) {
-  const float rs = H - delta;
-  return (force_slow || !(rs > 0.f)) ? -1.f : rs * rs * 0.999999f;
-}
-
-// Exact sorted-axis cuts of the density loops for one (lane, candidate): the slow path of hits
-// within delta of the search radius.  key: sort key of the candidate.
-// What the exact-cut slow paths read of Dev (a __noinline__ function taking Dev itself would force the
-// kernel's copy of it onto the local-memory stack).
-struct CutCtx {
-  const CellDev *cells;
-  const int64_t *sort_lookup;
-  const SortEnt *sort;
-  const float *cell_hmax;
-  double dim[3];
-};
-__device__ __forceinline__ CutCtx cut_ctx(const Dev &d) {
-  CutCtx c;
-  c.cells = d.cells; c.sort_lookup = d.sort_lookup; c.sort = d.sort; c.cell_hmax = d.cell_hmax;
-  c.dim[0] = d.dim[0]; c.dim[1] = d.dim[1]; c.dim[2] = d.dim[2];
-  return c;
-}
-__device__ __noinline__ bool dens_cut_exact(const CutCtx d, const Item item, double xi, double yi, double zi,
-                                            float hig, float key) {
-  const int kind = item.kind, sid = item.sid;
-  if (kind == kSelf || kind == kSubSelf) return true;
-  const CellDev cB = d.cells[item.partner];
-  double sh[3];
-#pragma unroll
-  for (int k = 0; k < 3; k++) sh[k] = (double)item_shift_i(item.shift, k) * d.dim[k];
-  const int64_t segB = d.sort_lookup[(int64_t)item.partner * 13 + sid];
-  if (kind == kPairLeft) {
-    // DOPAIR1 loop 1 (:1122-1216)
-    const double rshift = item_rshift(sh, sid);
-    const float d_me = sort_key(xi, yi, zi, sid);
-    const double dj_min = (double)d.sort[segB].d;
-    const double hi_max = __dsub_rn((double)__fmul_rn(d.cell_hmax[item.own], kc.gamma), rshift);
-    const double di = __dsub_rn((double)__fadd_rn(d_me, hig), rshift);
-    if (!((__dadd_rn((double)d_me, hi_max) > dj_min) && !(di < dj_min))) return false;
-    return key <= thr_lt(di);
-  } else if (kind == kPairRight) {
-    // DOPAIR1 loop 2 (:1222-1316)
-    const double rshift = item_rshift(sh, sid);
-    const float d_me = sort_key(xi, yi, zi, sid);
-    const double di_max = __dsub_rn((double)d.sort[segB + cB.count - 1].d, rshift);
-    const double hj_max = (double)__fmul_rn(d.cell_hmax[item.own], kc.gamma);
-    const double dj = __dadd_rn((double)__fsub_rn(d_me, hig), rshift);
-    if (!((__dsub_rn((double)d_me, hj_max) < di_max) && !(__dsub_rn(dj, rshift) > di_max))) return false;
-    return key >= thr_gt(dj);
-  }
-  // DOPAIR_SUBSET (:745-770, 794-838)
-  const double px = __dsub_rn(xi, sh[0]), py = __dsub_rn(yi, sh[1]), pz = __dsub_rn(zi, sh[2]);
-  const float hg = (kind == kSubPair) ? __fadd_rn(hig, 0.f) : __fsub_rn(-hig, 0.f);
-  const double cut = __dadd_rn(__dadd_rn(__dadd_rn((double)hg, __dmul_rn(px, kc.axis[sid][0])),
-                                         __dmul_rn(py, kc.axis[sid][1])),
-                               __dmul_rn(pz, kc.axis[sid][2]));
-  return kind == kSubPair ? (key <= thr_lt(cut)) : (key >= thr_gt(cut));
-}
-
 // ---------------------------------------------------------------------------
 // K3': first density pass, DOSELF1 / DOPAIR1 arithmetic.  One CTA per group of units of a leaf.
 // ---------------------------------------------------------------------------

@@ -9,6 +9,7 @@
 
 #include "kernels.cuh"
 #include "leaf_kernels.cuh"
+#include "list_kernels.cuh"
 #include "pack.cuh"
 #include "integrate.cuh"
 
@@ -70,7 +71,8 @@ struct swift_cuda_ctx {
   bool marks_fresh = false;        // k_mark_sorts has run for the current active set
   float integ_ms[4] = {};          // last drift, kick1, kick2, timestep (CUDA events on the stream)
   // which neighbour-loop kernels run: bit 0 leaf-resident first density pass, bit 1 fused ghost + redo,
-  // bit 2 leaf-resident force (FAST field arithmetic).  0: the first-generation warp-per-unit kernels.
+  // bit 2 leaf-resident force (FAST field arithmetic), bit 3 ghost redo sweeps from recorded neighbour
+  // lists (list_kernels.cuh).  0: the first-generation warp-per-unit kernels.
   int path = 0;
   int force_slow = 0;  // test hook (SWIFT_CUDA_SLOW=1): every hit takes the exact sorted-axis-cut path
 };
@@ -138,6 +140,11 @@ int swift_cuda_create(const swift_cuda_params *params, int device, swift_cuda_ct
   CK(cudaSetDevice(device));
   swift_cuda_ctx *c = new swift_cuda_ctx();
   c->prm = *params;
+  if (const char *e = getenv("SWIFT_CUDA_FIELDS")) c->prm.fields_mode = atoi(e);
+  if (c->prm.fields_mode != SWIFT_CUDA_FIELDS_EXACT && c->prm.fields_mode != SWIFT_CUDA_FIELDS_FAST) {
+    delete c;
+    return fail("swift_cuda_create: unknown fields_mode");
+  }
   c->device = device;
   CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   for (auto &e : c->ev) CK(cudaEventCreate(&e));
@@ -345,7 +352,21 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
     if (upload(c, &dg, groups.data(), groups.size())) return 1;
     d.groups = dg;
     d.n_groups = (int)groups.size();
-    CK(cudaStreamSynchronize(c->stream));  // groups goes out of scope
+    std::vector<int32_t> part_lane((size_t)c->n, -1);
+    for (size_t k = 0; k < wl.lane_part.size(); k++)
+      if (wl.lane_part[k] >= 0) part_lane[wl.lane_part[k]] = (int32_t)k;
+    int32_t *dpl;
+    if (upload(c, &dpl, part_lane.data(), part_lane.size())) return 1;
+    d.part_lane = dpl;
+    CK(cudaStreamSynchronize(c->stream));  // groups, part_lane go out of scope
+    d.nl = nullptr;
+    d.nl_grow = 1.02f;
+    if (const char *e = getenv("SWIFT_CUDA_GROW")) d.nl_grow = (float)atof(e);
+    if (c->path & 8) {
+      if (dmalloc(c, &d.nl, (size_t)d.n_units * kLD * 32) || dmalloc(c, &d.nl_cnt, (size_t)d.n_units * 32) ||
+          dmalloc(c, &d.nl_R, (size_t)d.n_units * 32))
+        return 1;
+    }
   }
   {
     std::vector<int32_t> slot_of((size_t)c->n, -1);
@@ -619,6 +640,7 @@ static int launch_density(swift_cuda_ctx *c) {
                      c->stream));
   CK(cudaMemsetAsync(d.work_ctr, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
   if (launch_cell_box(c)) return 1;
+  if (d.nl) CK(cudaMemsetAsync(d.nl_cnt, 0xff, (size_t)d.n_units * 32 * sizeof(unsigned short), c->stream));
   k_init_step<<<nb, 256, 0, c->stream>>>(d);
   if ((c->path & 1) && !c->integ_on) {
     if (d.n_groups > 0)
@@ -663,6 +685,10 @@ static int launch_ghost(swift_cuda_ctx *c) {
       CK(cudaStreamSynchronize(c->stream));
       if (pending == 0) break;
     }
+    if (d.nl && sweep > 0 && d.n_units > 0) {
+      k_density_list<<<(d.n_units + kWarps - 1) / kWarps, kBlock, 0, c->stream>>>(d, sweep);
+      c->counters.n_kernel_launches += 1;
+    }
     if (d.n_leaves > 0) k_density<1><<<c->grid_redo, kBlock, 0, c->stream>>>(d, sweep);
     c->counters.n_kernel_launches += 1;
   }
@@ -678,10 +704,14 @@ static int launch_force(swift_cuda_ctx *c) {
   CK(cudaMemsetAsync(d.work_ctr + 1 + c->prm.max_smoothing_iterations, 0, sizeof(int), c->stream));
   if (d.n_units > 0) {
     const int nb = c->grid_force;
-    if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY)
-      k_force<SWIFT_CUDA_SCHEME_PLANETARY><<<nb, kBlock, 0, c->stream>>>(d);
-    else
-      k_force<SWIFT_CUDA_SCHEME_MINIMAL><<<nb, kBlock, 0, c->stream>>>(d);
+    const bool fast = c->prm.fields_mode == SWIFT_CUDA_FIELDS_FAST;
+    if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY) {
+      if (fast) k_force<SWIFT_CUDA_SCHEME_PLANETARY, true><<<nb, kBlock, 0, c->stream>>>(d);
+      else k_force<SWIFT_CUDA_SCHEME_PLANETARY, false><<<nb, kBlock, 0, c->stream>>>(d);
+    } else {
+      if (fast) k_force<SWIFT_CUDA_SCHEME_MINIMAL, true><<<nb, kBlock, 0, c->stream>>>(d);
+      else k_force<SWIFT_CUDA_SCHEME_MINIMAL, false><<<nb, kBlock, 0, c->stream>>>(d);
+    }
   }
   c->counters.n_kernel_launches += 1;
   CK(cudaGetLastError());
