@@ -207,6 +207,58 @@ int swift_cuda_step(swift_cuda_ctx *ctx, int flags);
 int swift_cuda_step_io(swift_cuda_ctx *ctx, const swift_cuda_parts_in *parts, int flags,
                        const swift_cuda_parts_out *out);
 
+/* ---- The caller's AoS particle records (struct part) in, the same records out ------------------
+ * The reference keeps its particles as an array of 128-byte `struct part`
+ * (src/hydro/Minimal/hydro_part.h:98-189, src/hydro/Planetary/hydro_part.h:100-192; the density-loop
+ * fields share a union with the force-loop fields) and its operators update those records IN PLACE.
+ * These entries take the array as it is: the records are copied to the device whole, unpacked there
+ * into the SoA caches (one coalesced read of the record per particle; role of cache_read_particles,
+ * src/cache.h:183) and the results are written back into the device copy of the records and copied
+ * out whole.  The library never sees the struct: the shim compiled against the reference's headers
+ * passes the byte offsets (offsetof).  An offset < 0 means the record has no such field. */
+typedef struct {
+  int stride;                                          /* sizeof(struct part) */
+  int x, v, a_hydro, mass, h, u, u_dt, rho;            /* p->x[3] (double), p->v[3], p->a_hydro[3], ... */
+  int rho_dh, wcount, wcount_dh, div_v, rot_v;         /* p->density.* (union with p->force.*) */
+  int f, pressure, soundspeed, v_sig, h_dt, balsara;   /* p->force.* */
+  int time_bin, min_ngb_time_bin, id, mat_id;          /* p->time_bin, p->limiter_data.min_ngb_time_bin, p->id, p->mat_id */
+} swift_cuda_part_layout;
+
+/* Phases of swift_cuda_step_parts.  With SWIFT_CUDA_PHASE_KEEP the density loop continues the running
+ * sums found in the records (p->rho, p->density.*) instead of starting from hydro_init_part: what a
+ * per-task shim of runner_do{self,pair}1_branch_density needs, which the reference calls once per cell
+ * pair on records that already hold the contributions of the pairs before.  The force loop always
+ * continues p->a_hydro, p->u_dt, p->force.h_dt, p->force.v_sig, p->limiter_data.min_ngb_time_bin as found;
+ * without SWIFT_CUDA_PHASE_GHOST in the same call it takes rho, P, f, c, balsara of every particle from
+ * the records.  SWIFT_CUDA_PHASE_END_FORCE is runner_do_end_hydro_force (hydro_end_force). */
+enum {
+  SWIFT_CUDA_PHASE_SORT = 1,
+  SWIFT_CUDA_PHASE_DENSITY = 2,
+  SWIFT_CUDA_PHASE_GHOST = 4,
+  SWIFT_CUDA_PHASE_FORCE = 8,
+  SWIFT_CUDA_PHASE_END_FORCE = 16,
+  SWIFT_CUDA_PHASE_KEEP = 32,
+  SWIFT_CUDA_PHASE_ALL = 1 | 2 | 4 | 8 | 16
+};
+
+/* As swift_cuda_build_from_cells, from `n` records in cell order. */
+int swift_cuda_build_from_cells_parts(swift_cuda_ctx *ctx, const swift_cuda_part_layout *layout, const void *parts,
+                                      int64_t n, int ncells, const swift_cuda_cell *cells, int ntasks,
+                                      const swift_cuda_task *tasks);
+/* As swift_cuda_build_from_particles (library-built tree), from `n` records in any order. */
+int swift_cuda_build_from_parts(swift_cuda_ctx *ctx, const swift_cuda_part_layout *layout, const void *parts,
+                                int64_t n);
+/* Uploads the records as they are now (drifted x, v, h, u, time_bin and the running sums), runs the
+ * phases, writes what they produce back into the records (active particles only, as the reference):
+ *   DENSITY            p->rho, p->density.{rho_dh, wcount, wcount_dh, div_v, rot_v}   (raw sums)
+ *   GHOST              p->h, p->rho, p->force.{f, pressure, soundspeed, balsara, v_sig, h_dt}, p->a_hydro, p->u_dt
+ *   FORCE / END_FORCE  p->a_hydro, p->u_dt, p->force.{h_dt, v_sig}, p->limiter_data.min_ngb_time_bin
+ * `parts` should be page-locked for the copies to run at full PCIe rate. */
+int swift_cuda_step_parts(swift_cuda_ctx *ctx, void *parts, int phases);
+/* e->max_active_bin of the step that starts (outside the time-integration mode, where
+ * swift_cuda_set_time does it): which particles the operators update. */
+int swift_cuda_set_max_active_bin(swift_cuda_ctx *ctx, int max_active_bin);
+
 /* Operator-level entry points (same phases, separately callable; used by the
  * per-task shims and the parity tests). */
 int swift_cuda_do_sort(swift_cuda_ctx *ctx);

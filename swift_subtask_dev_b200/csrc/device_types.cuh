@@ -123,6 +123,9 @@ struct Dev {
   float *nl_R;                 // [n_units*32] (h gamma)^2 the list covers
   float nl_grow;               // the recording sweep covers nl_grow x the search radius
   const int32_t *part_lane;    // [n] unit * 32 + lane of a particle, -1: none
+  // swift_cuda_step_parts: continue the running density sums / leave hydro_end_force to its own phase
+  int keep_sums;
+  int no_end_force;
   // pair recording (test hook)
   long long *rec_pairs[3];
   unsigned long long *rec_count;  // [3]

@@ -439,10 +439,11 @@ __global__ void k_init_step(Dev d) {
   // time-integration mode (unit_list set): most steps have few active particles and nothing below is
   // read for the others, so their 45 bytes are not written
   if (!active && d.unit_list != nullptr) return;
-  d.dens0[p] = make_float4(0.f, 0.f, 0.f, 0.f);
-  d.dens1[p] = make_float4(0.f, 0.f, 0.f, 0.f);
   d.left[p] = 0.f;
   d.right[p] = kc.h_max;
+  if (d.keep_sums) return;  // per-task shims: the records' running sums were unpacked into the caches
+  d.dens0[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+  d.dens1[p] = make_float4(0.f, 0.f, 0.f, 0.f);
   d.min_bin[p] = kNumTimeBins + 1;
   if (active) {
     d.acc[p] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -757,6 +758,11 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
       const long long idi = rec ? d.id[pp] : 0;
       DensAcc acc;
       acc.zero();
+      if (MODE == 0 && d.keep_sums && mine) {
+        const float4 s0 = d.dens0[p], s1 = d.dens1[p];
+        acc.rho = s0.x; acc.rho_dh = s0.y; acc.wcount = s0.z; acc.wcount_dh = s0.w;
+        acc.div_v = s1.x; acc.rx = s1.y; acc.ry = s1.z; acc.rz = s1.w;
+      }
       int qcnt = 0;
       // list-recording sweep: the walk covers kGrowL x the search radius
       const bool recl = MODE == 1 && d.nl != nullptr;
@@ -1802,13 +1808,20 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
     if (mine) {
       d.acc[p] = make_float4(acc.ax, acc.ay, acc.az, acc.u_dt);
       // hydro_end_force (Minimal/hydro.h:878-882), the whole of runner_do_end_hydro_force for these schemes
-      d.h_dt[p] = acc.h_dt * (me.h * 0.3333333333f);
+      d.h_dt[p] = d.no_end_force ? acc.h_dt : acc.h_dt * (me.h * 0.3333333333f);
       d.v_sig[p] = acc.v_sig;
       d.min_bin[p] = acc.min_bin;
     }
   }
   for (int o = 16; o > 0; o >>= 1) nhits += __shfl_down_sync(kFull, nhits, o);
   if (lane == 0 && nhits) atomicAdd(&d.hits[2], nhits);
+}
+
+// runner_do_end_hydro_force on its own (swift_cuda_step_parts without the force loop in the same call)
+__global__ void k_end_force(Dev d) {
+  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p >= d.n || d.time_bin[p] > kc.max_active_bin) return;
+  d.h_dt[p] = d.h_dt[p] * (d.h[p] * 0.3333333333f);
 }
 
 }  // namespace swiftcuda

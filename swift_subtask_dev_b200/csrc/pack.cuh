@@ -112,6 +112,105 @@ __global__ void k_unpack(Dev d, RawOut o, const float4 *dens0_first, const float
   }
 }
 
+// ---------------------------------------------------------------------------
+// K1' / K7': the caller's AoS records (struct part, 128 B) <-> the SoA caches, on the device.
+// One thread per particle; a warp reads 32 consecutive records (4 KB, fully coalesced: every byte
+// of every sector is a record byte).  order: cell-order slot -> record index (null: identity).
+// ---------------------------------------------------------------------------
+struct AosDst {
+  float4 *dens0, *dens1, *acc;
+  float *h_dt, *v_sig;
+  int *min_bin;
+};
+template <typename T>
+__device__ __forceinline__ T aos_get(const unsigned char *rec, int off) {
+  return *reinterpret_cast<const T *>(rec + off);
+}
+template <typename T>
+__device__ __forceinline__ void aos_put(unsigned char *rec, int off, T v) {
+  *reinterpret_cast<T *>(rec + off) = v;
+}
+// sums: 1 = also the running density sums (KEEP); force: 1 = also a_hydro, u_dt, h_dt, v_sig, min_bin
+__global__ void k_pack_aos(int64_t n, const unsigned char *aos, swift_cuda_part_layout L, const int32_t *order,
+                           PackDst o, AosDst a, int with_static, int sums, int force) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t s = order ? order[k] : k;
+  const unsigned char *r = aos + (size_t)s * L.stride;
+  PosD q;
+  q.x = aos_get<double>(r, L.x); q.y = aos_get<double>(r, L.x + 8); q.z = aos_get<double>(r, L.x + 16); q.pad = 0.0;
+  o.pos[k] = q;
+  o.vm[k] = make_float4(aos_get<float>(r, L.v), aos_get<float>(r, L.v + 4), aos_get<float>(r, L.v + 8),
+                        aos_get<float>(r, L.mass));
+  const float h = aos_get<float>(r, L.h);
+  o.h[k] = h;
+  o.h0[k] = h;
+  o.u[k] = aos_get<float>(r, L.u);
+  const int8_t tb = aos_get<int8_t>(r, L.time_bin);
+  o.time_bin[k] = tb;
+  const float rho = aos_get<float>(r, L.rho);
+  if (sums) {
+    a.dens0[k] = make_float4(rho, aos_get<float>(r, L.rho_dh), aos_get<float>(r, L.wcount), aos_get<float>(r, L.wcount_dh));
+    a.dens1[k] = make_float4(aos_get<float>(r, L.div_v), aos_get<float>(r, L.rot_v), aos_get<float>(r, L.rot_v + 4),
+                             aos_get<float>(r, L.rot_v + 8));
+  } else {
+    // state the force loop reads of particles the ghost does not touch in this call
+    const float P = aos_get<float>(r, L.pressure);
+    o.fin[k] = make_float4(rho, P, aos_get<float>(r, L.f), aos_get<float>(r, L.soundspeed));
+    o.hb[k] = make_float4(h, aos_get<float>(r, L.balsara), __int_as_float((int)tb), P / (rho * rho));
+  }
+  if (force) {
+    a.acc[k] = make_float4(aos_get<float>(r, L.a_hydro), aos_get<float>(r, L.a_hydro + 4),
+                           aos_get<float>(r, L.a_hydro + 8), aos_get<float>(r, L.u_dt));
+    a.h_dt[k] = aos_get<float>(r, L.h_dt);
+    a.v_sig[k] = aos_get<float>(r, L.v_sig);
+    a.min_bin[k] = L.min_ngb_time_bin >= 0 ? (int)aos_get<int8_t>(r, L.min_ngb_time_bin) : 57;
+  }
+  if (with_static) {
+    o.mat_id[k] = L.mat_id >= 0 ? aos_get<int32_t>(r, L.mat_id) : 0;
+    o.id[k] = L.id >= 0 ? aos_get<long long>(r, L.id) : (long long)s;
+  }
+}
+
+// what: last phase that ran -- 2 density (raw sums), 4 ghost, 8 force (16 with the ghost's fields too)
+__global__ void k_unpack_aos(Dev d, unsigned char *aos, swift_cuda_part_layout L, const int32_t *order, int what,
+                             int max_active_bin) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= d.n) return;
+  if (d.time_bin[k] > max_active_bin) return;  // the reference's operators update active particles only
+  const int64_t s = order ? order[k] : k;
+  unsigned char *r = aos + (size_t)s * L.stride;
+  if (what == 2) {
+    const float4 s0 = d.dens0[k], s1 = d.dens1[k];
+    aos_put<float>(r, L.rho, s0.x);
+    aos_put<float>(r, L.rho_dh, s0.y);
+    aos_put<float>(r, L.wcount, s0.z);
+    aos_put<float>(r, L.wcount_dh, s0.w);
+    aos_put<float>(r, L.div_v, s1.x);
+    aos_put<float>(r, L.rot_v, s1.y);
+    aos_put<float>(r, L.rot_v + 4, s1.z);
+    aos_put<float>(r, L.rot_v + 8, s1.w);
+    return;
+  }
+  if (what == 4 || what == 16) {
+    const float4 f = d.fin[k];
+    aos_put<float>(r, L.h, d.h[k]);
+    aos_put<float>(r, L.rho, f.x);
+    aos_put<float>(r, L.pressure, f.y);
+    aos_put<float>(r, L.f, f.z);
+    aos_put<float>(r, L.soundspeed, f.w);
+    aos_put<float>(r, L.balsara, d.hb[k].y);
+  }
+  const float4 a = d.acc[k];
+  aos_put<float>(r, L.a_hydro, a.x);
+  aos_put<float>(r, L.a_hydro + 4, a.y);
+  aos_put<float>(r, L.a_hydro + 8, a.z);
+  aos_put<float>(r, L.u_dt, a.w);
+  aos_put<float>(r, L.h_dt, d.h_dt[k]);
+  aos_put<float>(r, L.v_sig, d.v_sig[k]);
+  if (what != 4 && L.min_ngb_time_bin >= 0) aos_put<int8_t>(r, L.min_ngb_time_bin, (int8_t)d.min_bin[k]);
+}
+
 // c->hydro.h_max of every cell from the particles' h (after a pack): one warp per cell
 __global__ void k_cell_hmax_init(Dev d, float *hmax, float *hmax_old) {
   const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;

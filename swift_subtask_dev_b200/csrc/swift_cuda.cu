@@ -73,6 +73,12 @@ struct swift_cuda_ctx {
   // which neighbour-loop kernels run: bit 0 leaf-resident first density pass, bit 1 fused ghost + redo,
   // bit 2 leaf-resident force (FAST field arithmetic), bit 3 ghost redo sweeps from recorded neighbour
   // lists (list_kernels.cuh).  0: the first-generation warp-per-unit kernels.
+  // swift_cuda_step_parts: the caller's AoS records
+  swift_cuda_part_layout lay = {};
+  bool has_lay = false;
+  unsigned char *d_aos = nullptr;
+  bool no_prune = false;            // build the work lists with every cell, whatever the time bins
+  std::vector<int32_t> slot_of;     // host copy of Dev::part_slot (caller order)
   int path = 0;
   int force_slow = 0;  // test hook (SWIFT_CUDA_SLOW=1): every hit takes the exact sorted-axis-cut path
 };
@@ -374,6 +380,9 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
       const swift_cuda_cell &leaf = c->tree.cells[wl.leaves[sl]];
       std::fill(slot_of.begin() + leaf.first, slot_of.begin() + leaf.first + leaf.count, (int32_t)sl);
     }
+    // caller-order copy for swift_cuda_update_particles' check of the active set
+    c->slot_of.assign((size_t)c->n, -1);
+    for (int64_t k = 0; k < c->n; k++) c->slot_of[c->tree.order.empty() ? k : c->tree.order[k]] = slot_of[k];
     int32_t *dps;
     if (upload(c, &dps, slot_of.data(), slot_of.size()) || dmalloc(c, &d.leaf_mark, wl.leaves.size()) ||
         dmalloc(c, &d.leaf_list, wl.leaves.size()) ||
@@ -439,7 +448,7 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
 static void cells_active(const swift_cuda_ctx *c, const swift_cuda_parts_in *in, std::vector<uint8_t> &act) {
   const size_t nc = c->tree.cells.size();
   act.assign(nc, 1);
-  if (!in->time_bin) return;
+  if (!in->time_bin || c->no_prune) return;
   const std::vector<int32_t> &ord = c->tree.order;
   for (size_t k = 0; k < nc; k++) {
     const swift_cuda_cell &cell = c->tree.cells[k];
@@ -507,6 +516,14 @@ int swift_cuda_update_particles(swift_cuda_ctx *c, const swift_cuda_parts_in *in
   if (!in || in->n != c->n) return fail("update_particles: particle count changed; rebuild");
   if (!in->x || !in->v || !in->mass || !in->h || !in->u) return fail("update_particles: null argument");
   CK(cudaSetDevice(c->device));
+  if (!c->all_cells_active && in->time_bin) {
+    // the work lists were built without the cells that held no active particle at the build
+    const int64_t m = c->n_io < 0 ? c->n : c->n_io;
+    for (int64_t k = 0; k < m; k++)
+      if (in->time_bin[k] <= c->prm.max_active_bin && c->slot_of[k] < 0)
+        return fail("update_particles: particle " + std::to_string(k) +
+                    " is active but its cell was inactive at the build and has no work list; rebuild");
+  }
   if (upload_and_pack(c, in, false)) return 1;
   // cell h_max follows the particles (c->hydro.h_max after a drift)
   Dev &d = c->dev;
@@ -628,7 +645,8 @@ static int launch_cell_box(swift_cuda_ctx *c) {
   return 0;
 }
 
-static int launch_density(swift_cuda_ctx *c) {
+// What every step needs before the first neighbour loop: counters, cell boxes, hydro_init_part.
+static int launch_density_prep(swift_cuda_ctx *c) {
   Dev &d = c->dev;
   if (launch_mark(c)) return 1;
   const int nb = (int)((c->n + 255) / 256);
@@ -642,13 +660,21 @@ static int launch_density(swift_cuda_ctx *c) {
   if (launch_cell_box(c)) return 1;
   if (d.nl) CK(cudaMemsetAsync(d.nl_cnt, 0xff, (size_t)d.n_units * 32 * sizeof(unsigned short), c->stream));
   k_init_step<<<nb, 256, 0, c->stream>>>(d);
+  c->counters.n_kernel_launches += 1;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+static int launch_density(swift_cuda_ctx *c) {
+  Dev &d = c->dev;
+  if (launch_density_prep(c)) return 1;
   if ((c->path & 1) && !c->integ_on) {
     if (d.n_groups > 0)
       k_density_leaf<kDensCap, kDensQD><<<d.n_groups, kLT, sizeof(DensTileT), c->stream>>>(d, c->force_slow);
   } else if (d.n_units > 0) {
     k_density<0><<<c->grid_density, kBlock, 0, c->stream>>>(d, 0);
   }
-  c->counters.n_kernel_launches += 2;
+  c->counters.n_kernel_launches += 1;
   CK(cudaGetLastError());
   // keep the raw first-pass sums for inspection (parity tests); not in time-integration mode, where a
   // step may touch a handful of particles and two O(n) copies would be a third of it
@@ -926,6 +952,187 @@ int swift_cuda_step_io(swift_cuda_ctx *c, const swift_cuda_parts_in *in, int fla
   CK(cudaEventElapsedTime(&c->timings.force_ms, c->ev[3], c->ev[4]));
   CK(cudaEventElapsedTime(&c->timings.total_ms, c->ev[0], c->ev[4]));
   if (c->counters.ghost_unconverged > 0)
+    return fail("Smoothing length failed to converge on " + std::to_string(c->counters.ghost_unconverged) +
+                " particles.");
+  return 0;
+}
+
+}  // extern "C"
+
+// ---- the caller's AoS records (struct part) ---------------------------------------------------
+namespace {
+struct HostSoA {
+  std::vector<double> x;
+  std::vector<float> v, mass, h, u, rho, P, f, cs, bal;
+  std::vector<int8_t> tb;
+  std::vector<int32_t> mat;
+  std::vector<int64_t> id;
+};
+template <typename T>
+static inline T rec_get(const unsigned char *r, int off) {
+  T v;
+  std::memcpy(&v, r + off, sizeof(T));
+  return v;
+}
+static void aos_to_soa(const swift_cuda_part_layout &L, const void *parts, int64_t n, HostSoA &o,
+                       swift_cuda_parts_in &in) {
+  o.x.resize(3 * n); o.v.resize(3 * n); o.mass.resize(n); o.h.resize(n); o.u.resize(n);
+  o.rho.resize(n); o.P.resize(n); o.f.resize(n); o.cs.resize(n); o.bal.resize(n);
+  o.tb.resize(n); o.mat.resize(n); o.id.resize(n);
+  const unsigned char *base = static_cast<const unsigned char *>(parts);
+  for (int64_t k = 0; k < n; k++) {
+    const unsigned char *r = base + (size_t)k * L.stride;
+    for (int a = 0; a < 3; a++) {
+      o.x[3 * k + a] = rec_get<double>(r, L.x + 8 * a);
+      o.v[3 * k + a] = rec_get<float>(r, L.v + 4 * a);
+    }
+    o.mass[k] = rec_get<float>(r, L.mass);
+    o.h[k] = rec_get<float>(r, L.h);
+    o.u[k] = rec_get<float>(r, L.u);
+    o.rho[k] = rec_get<float>(r, L.rho);
+    o.P[k] = rec_get<float>(r, L.pressure);
+    o.f[k] = rec_get<float>(r, L.f);
+    o.cs[k] = rec_get<float>(r, L.soundspeed);
+    o.bal[k] = rec_get<float>(r, L.balsara);
+    o.tb[k] = rec_get<int8_t>(r, L.time_bin);
+    o.mat[k] = L.mat_id >= 0 ? rec_get<int32_t>(r, L.mat_id) : 0;
+    o.id[k] = L.id >= 0 ? rec_get<int64_t>(r, L.id) : k;
+  }
+  std::memset(&in, 0, sizeof(in));
+  in.n = n;
+  in.x = o.x.data(); in.v = o.v.data(); in.mass = o.mass.data(); in.h = o.h.data(); in.u = o.u.data();
+  in.mat_id = o.mat.data(); in.time_bin = o.tb.data(); in.id = o.id.data();
+  in.rho = o.rho.data(); in.pressure = o.P.data(); in.f = o.f.data(); in.soundspeed = o.cs.data();
+  in.balsara = o.bal.data();
+}
+static int check_layout(const swift_cuda_part_layout *L) {
+  if (!L || L->stride <= 0) return fail("parts: bad record layout");
+  const int need[] = {L->x, L->v, L->a_hydro, L->mass, L->h, L->u, L->u_dt, L->rho, L->rho_dh, L->wcount,
+                      L->wcount_dh, L->div_v, L->rot_v, L->f, L->pressure, L->soundspeed, L->v_sig, L->h_dt,
+                      L->balsara, L->time_bin};
+  for (int o : need)
+    if (o < 0 || o >= L->stride) return fail("parts: a required field offset lies outside the record");
+  if (L->x % 8 || L->v % 4) return fail("parts: misaligned field offset");
+  return 0;
+}
+}  // namespace
+
+static int finish_parts_build(swift_cuda_ctx *c, const swift_cuda_part_layout *L) {
+  c->lay = *L;
+  c->has_lay = true;
+  return dmalloc(c, &c->d_aos, (size_t)std::max<int64_t>(c->n, 1) * L->stride);
+}
+
+extern "C" {
+
+int swift_cuda_build_from_cells_parts(swift_cuda_ctx *c, const swift_cuda_part_layout *L, const void *parts, int64_t n,
+                                      int ncells, const swift_cuda_cell *cells, int ntasks,
+                                      const swift_cuda_task *tasks) {
+  if (!c || !parts) return fail("build_from_cells_parts: null argument");
+  if (check_layout(L)) return 1;
+  HostSoA soa;
+  swift_cuda_parts_in in;
+  aos_to_soa(*L, parts, n, soa, in);
+  c->no_prune = true;  // which particles are active is decided per call (swift_cuda_set_max_active_bin)
+  const int rc = swift_cuda_build_from_cells(c, &in, ncells, cells, ntasks, tasks);
+  c->no_prune = false;
+  if (rc) return rc;
+  return finish_parts_build(c, L);
+}
+
+int swift_cuda_build_from_parts(swift_cuda_ctx *c, const swift_cuda_part_layout *L, const void *parts, int64_t n) {
+  if (!c || !parts) return fail("build_from_parts: null argument");
+  if (check_layout(L)) return 1;
+  HostSoA soa;
+  swift_cuda_parts_in in;
+  aos_to_soa(*L, parts, n, soa, in);
+  c->no_prune = true;
+  const int rc = swift_cuda_build_from_particles(c, &in);
+  c->no_prune = false;
+  if (rc) return rc;
+  return finish_parts_build(c, L);
+}
+
+int swift_cuda_set_max_active_bin(swift_cuda_ctx *c, int max_active_bin) {
+  NEED_BUILT(c);
+  if (!c->all_cells_active)
+    return fail("set_max_active_bin: the work lists were built for a fixed active set (cells without an active "
+                "particle were left out); build with max_active_bin = 56 or through the struct part entries");
+  c->prm.max_active_bin = max_active_bin;
+  c->marks_fresh = false;
+  if (upload_consts(c)) return 1;
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int swift_cuda_step_parts(swift_cuda_ctx *c, void *parts, int phases) {
+  NEED_BUILT(c);
+  if (!c->has_lay) return fail("step_parts: the context was not built from struct part records");
+  if (!parts) return fail("step_parts: null argument");
+  if (c->integ_on) return fail("step_parts: not in time-integration mode");
+  const int64_t n = c->n;
+  Dev &d = c->dev;
+  const swift_cuda_part_layout L = c->lay;
+  const bool do_dens = phases & SWIFT_CUDA_PHASE_DENSITY, do_ghost = phases & SWIFT_CUDA_PHASE_GHOST;
+  const bool do_force = phases & SWIFT_CUDA_PHASE_FORCE, do_end = phases & SWIFT_CUDA_PHASE_END_FORCE;
+  const bool keep = (phases & SWIFT_CUDA_PHASE_KEEP) || (do_ghost && !do_dens);
+  c->counters.n_kernel_launches = 0;
+  CK(cudaEventRecord(c->ev[0], c->stream));
+  CK(cudaMemcpyAsync(c->d_aos, parts, (size_t)n * L.stride, cudaMemcpyHostToDevice, c->stream));
+  PackDst o;
+  o.pos = const_cast<PosD *>(d.pos);
+  o.vm = d.vm; o.fin = d.fin; o.hb = d.hb; o.h = d.h; o.h0 = c->d_h0; o.u = const_cast<float *>(d.u);
+  o.time_bin = const_cast<int8_t *>(d.time_bin);
+  o.mat_id = const_cast<int32_t *>(d.mat_id);
+  o.id = const_cast<int64_t *>(d.id);
+  AosDst a;
+  a.dens0 = d.dens0; a.dens1 = d.dens1; a.acc = d.acc; a.h_dt = d.h_dt; a.v_sig = d.v_sig; a.min_bin = d.min_bin;
+  const int32_t *order = c->tree.order.empty() ? nullptr : c->s_order;
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  const int load_force = (!do_dens && !do_ghost) ? 1 : 0;
+  if (n > 0) k_pack_aos<<<nb, 256, 0, c->stream>>>(n, c->d_aos, L, order, o, a, 0, keep ? 1 : 0, load_force);
+  if (d.ncells > 0)
+    k_cell_hmax_init<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d, d.cell_hmax,
+                                                                         const_cast<float *>(d.cell_hmax_old));
+  c->counters.n_kernel_launches += 2;
+  CK(cudaGetLastError());
+  c->marks_fresh = false;
+  // (without density and ghost in this call the running force sums of the records must survive k_init_step too)
+  d.keep_sums = (keep || load_force) ? 1 : 0;
+  d.no_end_force = do_end ? 0 : 1;
+  if ((phases & SWIFT_CUDA_PHASE_SORT) && launch_sort(c)) return 1;
+  CK(cudaEventRecord(c->ev[1], c->stream));
+  if (do_dens) {
+    if (launch_density(c)) return 1;
+  } else if (launch_density_prep(c)) {
+    return 1;
+  }
+  CK(cudaEventRecord(c->ev[2], c->stream));
+  if (do_ghost && launch_ghost(c)) return 1;
+  CK(cudaEventRecord(c->ev[3], c->stream));
+  if (do_force) {
+    if (launch_force(c)) return 1;
+  } else if (do_end && n > 0) {
+    k_end_force<<<nb, 256, 0, c->stream>>>(d);
+    c->counters.n_kernel_launches += 1;
+  }
+  CK(cudaEventRecord(c->ev[4], c->stream));
+  d.keep_sums = 0;
+  d.no_end_force = 0;
+  const int what = (do_force || do_end) ? (do_ghost ? 16 : 8) : (do_ghost ? 4 : (do_dens ? 2 : 0));
+  if (what && n > 0) {
+    k_unpack_aos<<<nb, 256, 0, c->stream>>>(d, c->d_aos, L, order, what, c->prm.max_active_bin);
+    c->counters.n_kernel_launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(parts, c->d_aos, (size_t)n * L.stride, cudaMemcpyDeviceToHost, c->stream));
+  }
+  if (finish_counters(c)) return 1;
+  CK(cudaEventElapsedTime(&c->timings.sort_ms, c->ev[0], c->ev[1]));
+  CK(cudaEventElapsedTime(&c->timings.density_ms, c->ev[1], c->ev[2]));
+  CK(cudaEventElapsedTime(&c->timings.ghost_ms, c->ev[2], c->ev[3]));
+  CK(cudaEventElapsedTime(&c->timings.force_ms, c->ev[3], c->ev[4]));
+  CK(cudaEventElapsedTime(&c->timings.total_ms, c->ev[0], c->ev[4]));
+  if (do_ghost && c->counters.ghost_unconverged > 0)
     return fail("Smoothing length failed to converge on " + std::to_string(c->counters.ghost_unconverged) +
                 " particles.");
   return 0;

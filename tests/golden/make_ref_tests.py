@@ -1,0 +1,23 @@
+"""Runs the UNMODIFIED reference unit tests (tests/test27cells.c, tests/test125cells.c, linked against
+the reference's own runner_doiact_hydro.o by oracle/Makefile.shim, target `cpu`) in this container and
+stores their output tables as fixtures: what tests/test_reference_tests.py compares the same tests,
+linked against the shim + libswiftcuda.so instead, with on the GPU box."""
+import os
+import shutil
+import subprocess
+import tempfile
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF = os.path.join(HERE, "..", "..", "oracle", "_ref")
+RUNS = {
+    "test27cells": (["-n", "4", "-r", "1", "-d", "0", "-f", "standard"], "swift_dopair_27_standard.dat"),
+    "test27cells_perturbed": (["-n", "4", "-r", "1", "-d", "0.1", "-f", "perturbed"], "swift_dopair_27_perturbed.dat"),
+    "test125cells": (["-n", "6", "-r", "1", "-v", "0", "-p", "0", "-f", "standard"], "swift_dopair_125_standard.dat"),
+    "test125cells_v2": (["-n", "6", "-r", "1", "-v", "2", "-p", "1", "-f", "standard"], "swift_dopair_125_standard.dat"),
+}
+for name, (args, out) in RUNS.items():
+    exe = os.path.join(REF, name.split("_")[0] + "_ref")
+    with tempfile.TemporaryDirectory() as tmp:
+        subprocess.run([exe] + args, cwd=tmp, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        shutil.copy(os.path.join(tmp, out), os.path.join(HERE, "ref_tests", name + ".dat"))
+        print(name, "->", out)

@@ -1,0 +1,86 @@
+"""The reference's OWN unit tests (tests/test27cells.c, tests/test125cells.c), compiled from where
+they lie and linked against swift_subtask_dev_b200/shim/swift_cuda_shim.c + libswiftcuda.so instead
+of the reference's runner_doiact_hydro.o (oracle/Makefile.shim).  Their output tables are gated the
+way the reference gates them (tests/difffloat.py:75-130 with tests/tolerance_*.dat: absolute,
+relative and "too small to compare" thresholds per column) against the brute-force table the test
+itself computes, and compared with the table the unmodified reference wrote for the same arguments
+(tests/golden/ref_tests, tests/golden/make_ref_tests.py)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref")
+GOLD = os.path.join(ROOT, "tests", "golden", "ref_tests")
+
+
+def load_table(path):
+    rows = [l.split() for l in open(path) if l.strip() and not l.lstrip().startswith("#")]
+    return np.array(rows, dtype=np.float64)
+
+
+def difffloat(a, b, tol, number_to_check):
+    """The semantics of the reference's tests/difffloat.py:83-127 (the reference's scripts pass
+    number_to_check = 6: only the first n^3 rows, the main cell, are gated); returns the failing
+    (row, column)s."""
+    abs_tol, rel_tol, lim_tol = tol[0], tol[1], tol[2]
+    assert a.shape == b.shape
+    nrows = min(number_to_check ** 3, len(a))
+    a, b = a[:nrows], b[:nrows]
+    diff = np.abs(a - b)
+    s = np.abs(a + b)
+    rel = np.where(s > 0, diff / np.where(s > 0, s, 1.0), 0.0)
+    bad = diff > 1.1 * abs_tol[None, :]
+    small = (np.abs(a) + np.abs(b)) < lim_tol[None, :]
+    bad |= (~small) & (rel > 1.1 * rel_tol[None, :])
+    return np.argwhere(bad)
+
+
+def run_test(exe, args, tmp_path):
+    path = os.path.join(REF, exe)
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/%s not built (make -C oracle -f Makefile.shim needs the reference tree)" % exe)
+    r = subprocess.run([path] + args, cwd=tmp_path, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    return r
+
+
+CASES_27 = [("test27cells", ["-n", "4", "-r", "1", "-d", "0", "-f", "standard"], "standard", "tolerance_27_normal.dat"),
+            ("test27cells_perturbed", ["-n", "4", "-r", "1", "-d", "0.1", "-f", "perturbed"], "perturbed",
+             "tolerance_27_perturbed.dat")]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,args,ext,tolfile", CASES_27)
+def test_test27cells_through_the_shim(name, args, ext, tolfile, tmp_path):
+    run_test("test27cells_cuda", args, tmp_path)
+    ours = load_table(tmp_path / ("swift_dopair_27_%s.dat" % ext))
+    brute = load_table(tmp_path / ("brute_force_27_%s.dat" % ext))
+    tol = load_table(os.path.join(REF, tolfile))
+    bad = difffloat(ours, brute, tol, int(args[1]))
+    assert len(bad) == 0, "difffloat gate: %d entries out of tolerance, first (row, col) %s" % (len(bad), bad[:5])
+    # and against the unmodified reference's own table: the per-pair partial sums are added in the
+    # same order; only the grouping of the additions across calls differs
+    ref = load_table(os.path.join(GOLD, name + ".dat"))
+    bad = difffloat(ours, ref, tol, 10 ** 6)  # the reference's gate on ALL rows (the tables print 7 digits)
+    assert len(bad) == 0, "against the reference's own table: %d entries, first (row, col) %s" % (len(bad), bad[:5])
+
+
+CASES_125 = [("test125cells", ["-n", "6", "-r", "1", "-v", "0", "-p", "0", "-f", "standard"], "tolerance_125_normal.dat"),
+             ("test125cells_v2", ["-n", "6", "-r", "1", "-v", "2", "-p", "1", "-f", "standard"], "tolerance_125_normal.dat")]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,args,tolfile", CASES_125)
+def test_test125cells_through_the_shim(name, args, tolfile, tmp_path):
+    run_test("test125cells_cuda", args, tmp_path)
+    ours = load_table(tmp_path / "swift_dopair_125_standard.dat")
+    brute = load_table(tmp_path / "brute_force_125_standard.dat")
+    tol = load_table(os.path.join(REF, tolfile))
+    bad = difffloat(ours, brute, tol, int(args[1]))
+    assert len(bad) == 0, "difffloat gate: %d entries out of tolerance, first (row, col) %s" % (len(bad), bad[:5])
+    ref = load_table(os.path.join(GOLD, name + ".dat"))
+    bad = difffloat(ours, ref, tol, 10 ** 6)  # the reference's gate on ALL rows (the tables print 7 digits)
+    assert len(bad) == 0, "against the reference's own table: %d entries, first (row, col) %s" % (len(bad), bad[:5])
