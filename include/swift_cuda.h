@@ -155,7 +155,7 @@ typedef struct swift_cuda_ctx swift_cuda_ctx;
 int swift_cuda_abi_version(void);
 /* sizeof of the ABI structs as compiled into the library, for binding checks:
  * 0 params, 1 cell, 2 task, 3 parts_in, 4 parts_out, 5 counters, 6 timings, 7 til, 8 integrator,
- * 9 state_out. */
+ * 9 state_out, 10 part_layout. */
 size_t swift_cuda_sizeof(int which);
 const char *swift_cuda_last_error(void);
 

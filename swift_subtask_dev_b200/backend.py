@@ -125,8 +125,69 @@ EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error
            "swift_cuda_host_plan", "swift_cuda_host_free",
            "swift_cuda_integrator_init", "swift_cuda_set_time", "swift_cuda_drift", "swift_cuda_kick",
            "swift_cuda_timestep", "swift_cuda_reset_offsets", "swift_cuda_get_state",
-           "swift_cuda_get_integrator_timings"]
+           "swift_cuda_get_integrator_timings",
+           "swift_cuda_build_from_cells_parts", "swift_cuda_build_from_parts", "swift_cuda_step_parts",
+           "swift_cuda_set_max_active_bin"]
 
+
+class PartLayout(C.Structure):
+    # field order must match swift_cuda_part_layout
+    _fields_ = [(k, C.c_int) for k in
+                ("stride", "x", "v", "a_hydro", "mass", "h", "u", "u_dt", "rho", "rho_dh", "wcount", "wcount_dh", "div_v",
+                 "rot_v", "f", "pressure", "soundspeed", "v_sig", "h_dt", "balsara", "time_bin", "min_ngb_time_bin", "id",
+                 "mat_id")]
+
+
+# Byte offsets of the reference's `struct part` (src/hydro/Minimal/hydro_part.h:98-189, Planetary :100-192;
+# 128 bytes, all subgrid models NONE), probe-compiled against the reference headers with offsetof(): the C
+# shim (swift_subtask_dev_b200/shim/swift_cuda_shim.c) computes the same numbers at compile time.
+_PART_COMMON = dict(stride=128, x=16, v=40, a_hydro=52, mass=64, h=68, u=72, u_dt=76, rho=80, rho_dh=92, wcount=84,
+                    wcount_dh=88, div_v=96, rot_v=100, f=84, pressure=88, soundspeed=92, v_sig=96, h_dt=100, balsara=104,
+                    id=0)
+PART_LAYOUTS = {SCHEME_MINIMAL: dict(_PART_COMMON, time_bin=113, min_ngb_time_bin=115, mat_id=-1),
+                SCHEME_PLANETARY: dict(_PART_COMMON, time_bin=117, min_ngb_time_bin=119, mat_id=112)}
+PHASE_SORT, PHASE_DENSITY, PHASE_GHOST, PHASE_FORCE, PHASE_END_FORCE, PHASE_KEEP = 1, 2, 4, 8, 16, 32
+PHASE_ALL = 31
+
+
+def part_dtype(scheme=SCHEME_MINIMAL):
+    """numpy record dtype with the reference's struct part layout (the density / force union as two views)."""
+    L = PART_LAYOUTS[scheme]
+    names = ["id", "x", "v", "a_hydro", "mass", "h", "u", "u_dt", "rho", "wcount", "wcount_dh", "rho_dh", "div_v", "rot_v",
+             "f", "pressure", "soundspeed", "v_sig", "h_dt", "balsara", "time_bin", "min_ngb_time_bin"]
+    fmts = {"id": "<i8", "x": ("<f8", 3), "v": ("<f4", 3), "a_hydro": ("<f4", 3), "rot_v": ("<f4", 3), "time_bin": "i1",
+            "min_ngb_time_bin": "i1"}
+    if L["mat_id"] >= 0:
+        names.append("mat_id")
+        fmts["mat_id"] = "<i4"
+    return np.dtype({"names": names, "formats": [fmts.get(k, "<f4") for k in names],
+                     "offsets": [L[k] for k in names], "itemsize": L["stride"]})
+
+
+def parts_from_ic(ic, scheme=SCHEME_MINIMAL, pinned=False):
+    """An array of struct part records from an initial-conditions dict (sums zero: hydro_init_part)."""
+    n = len(ic["h"])
+    dt = part_dtype(scheme)
+    if pinned:
+        import torch
+        t = torch.zeros(n * dt.itemsize, dtype=torch.uint8, pin_memory=True)
+        parts = t.numpy().view(dt)
+        _PINNED_KEEP.append(t)
+    else:
+        parts = np.zeros(n, dtype=dt)
+    parts["id"] = ic["id"] if ic.get("id") is not None else np.arange(n)
+    parts["x"] = ic["x"]
+    parts["v"] = ic["v"]
+    parts["mass"] = ic["mass"]
+    parts["h"] = ic["h"]
+    parts["u"] = ic["u"]
+    parts["time_bin"] = ic["time_bin"] if ic.get("time_bin") is not None else 1
+    if "mat_id" in dt.names:
+        parts["mat_id"] = ic["mat_id"] if ic.get("mat_id") is not None else 0
+    return parts
+
+
+_PINNED_KEEP = []
 _lib = None
 
 
@@ -143,6 +204,11 @@ def load_library():
         lib.swift_cuda_halo_pack.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
         lib.swift_cuda_halo_unpack.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
         lib.swift_cuda_destroy.argtypes = [C.c_void_p]
+        lib.swift_cuda_build_from_parts.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+        lib.swift_cuda_build_from_cells_parts.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int,
+                                                          C.c_void_p, C.c_int, C.c_void_p]
+        lib.swift_cuda_step_parts.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        lib.swift_cuda_set_max_active_bin.argtypes = [C.c_void_p, C.c_int]
         lib.swift_cuda_record_pairs.argtypes = [C.c_void_p, C.c_longlong]
         lib.swift_cuda_fetch_pairs.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_longlong, C.c_void_p]
         lib.swift_cuda_set_time.argtypes = [C.c_void_p, C.c_longlong, C.c_int]
@@ -275,6 +341,35 @@ class HydroBackend:
         self.n = P.n
         nt = len(tasks) if ntasks is None else ntasks
         self._check(self.lib.swift_cuda_build_from_cells(self.ctx, C.byref(P), len(cells), cells, nt, tasks))
+
+    # ---- the caller's struct part records (the drop-in path of the C shim) ----
+    def _layout(self):
+        L = PartLayout()
+        for k, v in PART_LAYOUTS[self.params.scheme].items():
+            setattr(L, k, v)
+        return L
+
+    def build_from_parts(self, parts, cells=None, tasks=None, ntasks=None):
+        """parts: array of part_dtype records.  cells/tasks given: the caller's tree (records in cell
+        order, swift_cuda_build_from_cells_parts); otherwise the library bins them itself."""
+        self.n = len(parts)
+        L = self._layout()
+        assert parts.dtype.itemsize == L.stride and parts.flags["C_CONTIGUOUS"]
+        if cells is None:
+            self._check(self.lib.swift_cuda_build_from_parts(self.ctx, C.byref(L), parts.ctypes.data_as(C.c_void_p),
+                                                             C.c_int64(self.n)))
+        else:
+            nt = len(tasks) if ntasks is None else ntasks
+            self._check(self.lib.swift_cuda_build_from_cells_parts(self.ctx, C.byref(L),
+                                                                   parts.ctypes.data_as(C.c_void_p), C.c_int64(self.n),
+                                                                   len(cells), cells, nt, tasks))
+
+    def step_parts(self, parts, phases=PHASE_ALL):
+        """Uploads the records, runs the phases, writes the results back into the records (in place)."""
+        self._check(self.lib.swift_cuda_step_parts(self.ctx, parts.ctypes.data_as(C.c_void_p), int(phases)))
+
+    def set_max_active_bin(self, max_active_bin):
+        self._check(self.lib.swift_cuda_set_max_active_bin(self.ctx, int(max_active_bin)))
 
     def update_particles(self, ic):
         P, keep = self._parts_in(ic)

@@ -132,6 +132,7 @@ size_t swift_cuda_sizeof(int which) {
     case 7: return sizeof(swift_cuda_til);
     case 8: return sizeof(swift_cuda_integrator);
     case 9: return sizeof(swift_cuda_state_out);
+    case 10: return sizeof(swift_cuda_part_layout);
     default: return 0;
   }
 }

@@ -36,7 +36,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layouts_match_ctypes_mirror():
     lib = be.load_library()
     for which, cls in enumerate([be.Params, be.Cell, be.Task, be.PartsIn, be.PartsOut, be.Counters, be.Timings,
-                                 be.Til, be.Integrator, be.StateOut]):
+                                 be.Til, be.Integrator, be.StateOut, be.PartLayout]):
         assert lib.swift_cuda_sizeof(which) == C.sizeof(cls), cls.__name__
     # the oracle's tree structs are layout-compatible (tests memmove between them)
     assert C.sizeof(ol.Cell) == C.sizeof(be.Cell) and C.sizeof(ol.Task) == C.sizeof(be.Task)
@@ -92,3 +92,19 @@ def test_host_plan_rejects_too_large_h_in_periodic_box():
     ic["h"][:] = 0.3  # 1.1 * gamma * h > box / 3
     with pytest.raises(be.SwiftCudaError):
         be.host_plan(make_params(periodic=True), ic)
+
+
+def test_struct_part_mirror_has_the_reference_layout():
+    """The numpy mirror of struct part: 128-byte records, the density / force union overlapping as in
+    src/hydro/Minimal/hydro_part.h:133-189 (offsets probe-compiled against the reference headers)."""
+    for scheme in (be.SCHEME_MINIMAL, be.SCHEME_PLANETARY):
+        dt = be.part_dtype(scheme)
+        assert dt.itemsize == 128
+        off = {k: dt.fields[k][1] for k in dt.names}
+        assert off["x"] == 16 and off["v"] == 40 and off["a_hydro"] == 52 and off["rho"] == 80
+        assert off["wcount"] == off["f"] == 84 and off["rot_v"] == off["h_dt"] == 100
+        assert off["time_bin"] == (113 if scheme == be.SCHEME_MINIMAL else 117)
+    ic = ics.uniform_random(100, seed=1)
+    parts = be.parts_from_ic(ic)
+    assert np.array_equal(parts["x"], ic["x"]) and np.array_equal(parts["h"], ic["h"])
+    assert (parts["time_bin"] == 1).all() and (parts["rho"] == 0).all()
