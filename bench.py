@@ -4,8 +4,9 @@
 metric : ordered SPH pair interactions per second over one density+ghost+force
          step, whole job.
 value  : device-timed, particles resident in HBM (CUDA events around the step).
-e2e    : the same step through the public C ABI with HOST buffers (swift_cuda_step_io):
-         H2D of the step's particle state and D2H of its results inside the timed region.
+e2e    : the same step through the reference-facing C-ABI entry with HOST buffers
+         (swift_cuda_step_parts: the caller's array of 128-byte struct part records in, the same
+         records out): H2D and D2H of the records inside the timed region.
 --impl reference : the reference's own CPU operators (oracle/_ref, compiled from
          /root/reference; the plain-C oracle port when that is absent) on all
          host cores, on bounded samples of the same workload.
@@ -203,6 +204,10 @@ def main():
     ap.add_argument("--workload", default="uniform", choices=["uniform", "clustered"],
                     help="uniform: BASELINE configs[1] / [3] (default, the metric's config); clustered: configs[4] "
                          "shape, side^3 particles in TOTAL over ~10^3 clumps + background")
+    ap.add_argument("--fields", default="fast", choices=["fast", "exact"],
+                    help="swift_cuda_params.fields_mode of the headline run: fast = FMA / MUFU arithmetic in the force "
+                         "loop (pair lists, counts and h bit-exact, a / u_dt / h_dt / v_sig within 1e-4); exact = every "
+                         "field bit-identical to the reference.  The other mode is timed too (detail.other_mode)")
     ap.add_argument("--resident-steps", type=int, default=3,
                     help="engine steps of the device-resident leg (drift/kick/time-step kernels, SURVEY 8(f) N3); 0: skip")
     args = ap.parse_args()
@@ -246,7 +251,19 @@ def main():
     else:
         ic = ics.uniform_random(args.side ** 3, seed=cfg["seed"])
     n = len(ic["h"])
-    be = HydroBackend(make_params())
+    fast = args.fields == "fast"
+    cfg["fields_mode"] = ("FAST: neighbour lists, counts and h bit-exact; force-loop fields (a, u_dt, h_dt, v_sig) with FMA "
+                          "/ MUFU arithmetic, within 1e-4 of the reference" if fast else
+                          "EXACT: every field bit-identical to the reference")
+    # the other mode first, briefly: its step time goes into detail.other_mode
+    be = HydroBackend(make_params(fields_mode=0 if fast else 1))
+    be.build(ic)
+    for _ in range(2):
+        be.step(restore=True)
+    other_ms = be.timings()["total_ms"]
+    other_cnt = be.counters()
+    be.close()
+    be = HydroBackend(make_params(fields_mode=1 if fast else 0))
     t0 = time.perf_counter()
     be.build(ic)
     build_s = time.perf_counter() - t0
@@ -277,11 +294,34 @@ def main():
     ms = float(np.mean(times))
     value = inter / (ms * 1e-3)
 
-    # ---- end to end through the C ABI with host buffers: H2D of the step's particle state,
-    # the step, D2H of every result field, all inside the timed region
+    # ---- end to end through the reference-facing entry: the caller's array of 128-byte struct part
+    # records (pinned host memory) in, the same records out (swift_cuda_step_parts: H2D of the records,
+    # device-side unpack to the SoA caches, the step, device-side write-back into the records, D2H)
+    from swift_subtask_dev_b200 import backend as be_mod
+    parts = be_mod.parts_from_ic(ic, pinned=True)
+    bp = HydroBackend(make_params(fields_mode=1 if fast else 0))
+    be.close()
+    bp.build_from_parts(parts)
     e2e_times = []
-    h2d = n * (24 + 12 + 4 + 4 + 4)            # x, v, mass, h, u from pinned host memory
-    d2h = n * (4 * (6 + 3 + 3) + 1)            # h, rho, P, c, f, balsara, a[3], u_dt, h_dt, v_sig, min_ngb_time_bin
+    for k in range(max(1, min(args.steps, 3)) + 1):
+        parts["h"] = ic["h"]                   # every step from the initial h (host side, outside the timing)
+        t0 = time.perf_counter()
+        bp.step_parts(parts)
+        dt = time.perf_counter() - t0
+        if k > 0:
+            e2e_times.append(dt)
+    h2d = d2h = n * parts.dtype.itemsize
+    cnt_p = bp.counters()
+    assert cnt_p["n_density"] + cnt_p["n_density_redo"] + cnt_p["n_force"] == inter
+    e2e_value = inter / float(np.mean(e2e_times))
+    bp.close()
+    be = HydroBackend(make_params(fields_mode=1 if fast else 0))
+    be.build(ic)
+    # ---- the same through the SoA entry (swift_cuda_step_io: five field arrays in, result arrays out,
+    # transfers overlapped with the kernels): reported as detail.e2e_soa
+    soa_times = []
+    h2d_soa = n * (24 + 12 + 4 + 4 + 4)        # x, v, mass, h, u from pinned host memory
+    d2h_soa = n * (4 * (6 + 3 + 3) + 1)        # h, rho, P, c, f, balsara, a[3], u_dt, h_dt, v_sig, min_ngb_time_bin
     ic_pin = {}
     keep = []
     for k, a in ic.items():
@@ -297,8 +337,9 @@ def main():
         be.step_io(ic_pin, out_pin)   # upload + sort + density + ghost + force + download, one C-ABI call
         dt = time.perf_counter() - t0
         if k > 0:
-            e2e_times.append(dt)
-    e2e_value = inter / float(np.mean(e2e_times))
+            soa_times.append(dt)
+    e2e_soa = {"value": inter / float(np.mean(soa_times)), "unit": UNIT, "h2d_bytes_per_step": h2d_soa,
+               "d2h_bytes_per_step": d2h_soa, "entry": "swift_cuda_step_io (SoA field arrays)"}
 
     # ---- roofline of the dominant kernel: the single launch that takes longest (k_force; the ghost
     # phase is longer in total but is five launches of k_density<1>).  FP32 CUDA-core bound (SURVEY.md
@@ -351,12 +392,19 @@ def main():
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": cfg, "clocks": clocks, "gpu_launches": launches,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "entry": "swift_cuda_step_parts (the caller's 128-byte struct part records in and out)"},
             "roofline": roofline,
             "detail": {"n_particles": n, "interactions_per_step": inter, "n_density": cnt["n_density"],
                        "n_density_redo": cnt["n_density_redo"], "n_force": cnt["n_force"],
                        "ghost_sweeps": cnt["ghost_sweeps"], "phase_ms": {k: v / args.steps for k, v in phase.items()},
-                       "wall_ms_per_step": wall_ms, "build_s": build_s, "leaf_interactions": cnt["n_leaf_interactions"]}}
+                       "wall_ms_per_step": wall_ms, "build_s": build_s, "leaf_interactions": cnt["n_leaf_interactions"],
+                       "e2e_soa": e2e_soa,
+                       "other_mode": {"fields_mode": "EXACT" if fast else "FAST", "ms_per_step": other_ms,
+                                      "value": inter / (other_ms * 1e-3),
+                                      "same_counts": bool(other_cnt["n_density"] == cnt["n_density"] and
+                                                          other_cnt["n_density_redo"] == cnt["n_density_redo"] and
+                                                          other_cnt["n_force"] == cnt["n_force"])}}}
     if args.resident_steps > 0:
         be.close()
         line["resident"] = resident_leg(args, ic, hbm_peak)

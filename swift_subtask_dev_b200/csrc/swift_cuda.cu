@@ -79,7 +79,7 @@ struct swift_cuda_ctx {
   unsigned char *d_aos = nullptr;
   bool no_prune = false;            // build the work lists with every cell, whatever the time bins
   std::vector<int32_t> slot_of;     // host copy of Dev::part_slot (caller order)
-  int path = 0;
+  int path = 8;                     // default: ghost redo sweeps from recorded neighbour lists
   int force_slow = 0;  // test hook (SWIFT_CUDA_SLOW=1): every hit takes the exact sorted-axis-cut path
 };
 

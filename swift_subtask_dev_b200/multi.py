@@ -346,22 +346,91 @@ def setup_local(nranks, dim, cdim, per_cell, seed=42, periodic=True, params_kw=N
 
 
 # --------------------------------------------------------------------------- torchrun entry
-def step_rank_nccl(state, transport):
-    """One step of this process's rank: xv halo, sort + density + ghost, rho halo, force."""
+PHASES = ("halo_xv", "sort", "density", "ghost", "halo_rho", "force")
+
+
+def step_rank_nccl(state, transport, phase_ms=None):
+    """One step of this process's rank: xv halo, sort + density + ghost, rho halo, force.
+    phase_ms: dict to add the wall time of every phase to (each phase ends synchronised)."""
+    import time
     be = state.be
+    t = [time.perf_counter()]
+
+    def lap(name):
+        if phase_ms is not None:
+            state.torch.cuda.synchronize()
+            t.append(time.perf_counter())
+            phase_ms[name] = phase_ms.get(name, 0.0) + 1e3 * (t[-1] - t[-2])
     be.restore_particles()
     send = state.pack(0)
     _, recv = state.buffers(0)
     transport.exchange(send, recv)
     state.unpack(0)
+    lap("halo_xv")
     be.runner_do_hydro_sort()
+    lap("sort")
     be.runner_do_density()
+    lap("density")
     be.runner_do_ghost()
+    lap("ghost")
     send = state.pack(1)
     _, recv = state.buffers(1)
     transport.exchange(send, recv)
     state.unpack(1)
+    lap("halo_rho")
     be.runner_do_force()
+    lap("force")
+
+
+def nccl_parity_check(tr, world, rank, local, per_cell=150, seed=11):
+    """A small uniform box split over the ranks and stepped through the SAME code the timed loop runs
+    (step_rank_nccl: halo pack, NCCL send/recv, unpack), against one context holding the whole box on
+    rank 0: every owned particle's results and the summed counters must be bit-identical.
+    Role of the reference's tests/testHydroMPIrules.c + engine_maketasks.c:141-324 (send/recv xv, rho).
+    Returns "ok" or raises on every rank."""
+    import torch.distributed as dist
+    grid = grid_for(world)
+    dim = tuple(float(g) for g in grid)
+    cdim = tuple(int(12 * d / max(dim)) for d in dim)
+    h0 = ics.ETA / (per_cell * np.prod(cdim) / np.prod(dim)) ** (1.0 / 3.0)
+    assert ics.top_grid(dim, h0) == cdim
+    part = Partition(cdim, grid, periodic=True)
+    st = RankState(rank, part, dim, per_cell, seed=seed, device=local)
+    st.set_send_lists(tr.all_to_all_objects({p: ids for p, ids in st.recv_ids.items()}))
+    step_rank_nccl(st, tr)
+    mine = st.owned_results()
+    cnt = st.be.counters()
+    mine["_counts"] = (cnt["n_density"], cnt["n_density_redo"], cnt["n_force"])
+    st.be.close()
+    gathered = [None] * world if rank == 0 else None
+    dist.gather_object(mine, gathered, dst=0, group=tr.setup_group)
+    verdict = ["ok"]
+    if rank == 0:
+        ic = ics.cell_block_random(np.arange(int(np.prod(cdim))), cdim, dim, per_cell, seed=seed)
+        be = HydroBackend(make_params(dim=dim, periodic=True), device=local)
+        be.build(ic)
+        be.step()
+        ref, cref = be.results(), be.counters()
+        be.close()
+        pos = {int(v): k for k, v in enumerate(ic["id"])}
+        tot = np.zeros(3, dtype=np.int64)
+        nchecked = 0
+        for r, res in enumerate(gathered):
+            idx = np.array([pos[int(v)] for v in res["id"]])
+            nchecked += len(idx)
+            for k in ref:
+                if not np.array_equal(res[k], ref[k][idx]):
+                    verdict[0] = "rank %d: field %s differs from the single-GPU run" % (r, k)
+            tot += np.array(res["_counts"], dtype=np.int64)
+        if nchecked != len(ic["h"]):
+            verdict[0] = "owned particles of all ranks: %d, box: %d" % (nchecked, len(ic["h"]))
+        if tuple(tot) != (cref["n_density"], cref["n_density_redo"], cref["n_force"]):
+            verdict[0] = "interaction counters differ: %s vs %s" % (tuple(tot), cref)
+    dist.broadcast_object_list(verdict, src=0, group=tr.setup_group)
+    if verdict[0] != "ok":
+        raise RuntimeError("NCCL path parity check failed: " + verdict[0])
+    return "ok (%d ranks, %d particles, every owned field and the counters bit-identical to one GPU)" % (
+        world, per_cell * int(np.prod(cdim)))
 
 
 def bench_multi(args, cfg, metric, unit, sampler_cls=None):
@@ -378,6 +447,8 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     tr = NcclTransport()
+    # correctness of the timed path first: the same halo code on a small box, against one GPU
+    nccl_parity = nccl_parity_check(tr, world, rank, local)
     grid = grid_for(world)
     side = args.side
     clustered = getattr(args, "workload", "uniform") == "clustered"
@@ -428,6 +499,13 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
     ms_dev = e0.elapsed_time(e1) / args.steps
     ms_wall = 1e3 * (time.perf_counter() - t0) / args.steps
     clocks = sampler.stop() if sampler is not None else None
+    # per-phase split (one more step, every phase synchronised: outside the timed region)
+    phase_ms = {}
+    barrier()
+    step_rank_nccl(st, tr, phase_ms)
+    pt = torch.tensor([phase_ms[k] for k in PHASES], dtype=torch.float64, device="cuda")
+    dist.all_reduce(pt, op=dist.ReduceOp.MAX)
+    phase_max = {k: float(v) for k, v in zip(PHASES, pt.tolist())}
     cnt = st.be.counters()
     inter = cnt["n_density"] + cnt["n_density_redo"] + cnt["n_force"]
     # end to end: H2D of this rank's particle state from pinned host memory, the step, D2H of the results
@@ -487,7 +565,8 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
                 "detail": {"n_particles_owned_total": int(tsum[2]), "interactions_per_step": int(tsum[1]),
                            "halo_bytes_per_step_total": int(tsum[3]), "build_s": build_s,
                            "load_imbalance_interactions_max_over_mean": float(tmax[1]) * world / float(tsum[1]),
-                           "ms_device_events_rank0": ms_dev, "ms_wall_rank0": ms_wall}}
+                           "ms_device_events_rank0": ms_dev, "ms_wall_rank0": ms_wall,
+                           "nccl_parity": nccl_parity, "phase_ms": phase_max}}
         print(json.dumps(line))
     dist.barrier()
     dist.destroy_process_group()
