@@ -10,6 +10,11 @@
 
 namespace swiftcuda {
 
+// A time bin with SWIFT_CUDA_FOREIGN_BIN added marks a copy of a particle another rank owns: never
+// active here (every real bin is <= 56 < 64) while its owner's bin still reaches the neighbour-bin
+// limit of the particles that see it (runner_iact_nonsym_timebin reads bin & kBinMask).
+constexpr int kBinMask = 63;
+
 // Raw caller-order inputs on the device.
 struct RawIn {
   const double *x;   // [n][3]
@@ -41,10 +46,13 @@ struct PackDst {  // mutable views of the Dev arrays k_pack fills
 
 // what: 1 = positions, 2 = everything else, 3 = both (the overlapped step uploads and packs the
 // positions first so that the sorts can start while the other fields are still on the bus)
-__global__ void k_pack(int64_t n, RawIn in, PackDst o, int with_static, int what) {
+// m: only caller indices below m were refreshed on the device (swift_cuda_set_transfer_count): the
+// others keep their device state
+__global__ void k_pack(int64_t n, int64_t m, RawIn in, PackDst o, int with_static, int what) {
   const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (k >= n) return;
   const int64_t s = in.order ? in.order[k] : k;
+  if (s >= m) return;
   if (what & 1) {
     PosD q;
     q.x = in.x[3 * s]; q.y = in.x[3 * s + 1]; q.z = in.x[3 * s + 2]; q.pad = 0.0;
@@ -62,7 +70,7 @@ __global__ void k_pack(int64_t n, RawIn in, PackDst o, int with_static, int what
   const float rho = in.rho ? in.rho[s] : 0.f;
   const float P = in.pressure ? in.pressure[s] : 0.f;
   o.fin[k] = make_float4(rho, P, in.f ? in.f[s] : 0.f, in.soundspeed ? in.soundspeed[s] : 0.f);
-  o.hb[k] = make_float4(h, in.balsara ? in.balsara[s] : 0.f, __int_as_float((int)tb), P / (rho * rho));
+  o.hb[k] = make_float4(h, in.balsara ? in.balsara[s] : 0.f, __int_as_float((int)tb & kBinMask), P / (rho * rho));
   if (with_static) {
     o.mat_id[k] = in.mat_id ? in.mat_id[s] : 0;
     o.id[k] = in.id ? in.id[s] : s;
@@ -157,7 +165,7 @@ __global__ void k_pack_aos(int64_t n, const unsigned char *aos, swift_cuda_part_
     // state the force loop reads of particles the ghost does not touch in this call
     const float P = aos_get<float>(r, L.pressure);
     o.fin[k] = make_float4(rho, P, aos_get<float>(r, L.f), aos_get<float>(r, L.soundspeed));
-    o.hb[k] = make_float4(h, aos_get<float>(r, L.balsara), __int_as_float((int)tb), P / (rho * rho));
+    o.hb[k] = make_float4(h, aos_get<float>(r, L.balsara), __int_as_float((int)tb & kBinMask), P / (rho * rho));
   }
   if (force) {
     a.acc[k] = make_float4(aos_get<float>(r, L.a_hydro), aos_get<float>(r, L.a_hydro + 4),

@@ -117,6 +117,8 @@ static void free_device(swift_cuda_ctx *c) {
   c->d_unit_count = nullptr;
 }
 
+extern "C" void swift_cuda_destroy(swift_cuda_ctx *c);
+
 extern "C" {
 
 int swift_cuda_abi_version(void) { return SWIFT_CUDA_ABI_VERSION; }
@@ -138,8 +140,24 @@ size_t swift_cuda_sizeof(int which) {
 }
 const char *swift_cuda_last_error(void) { return g_err.c_str(); }
 
+static int create_resources(swift_cuda_ctx *c) {
+  CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  for (auto &e : c->ev) CK(cudaEventCreate(&e));
+  CK(cudaStreamCreateWithFlags(&c->io, cudaStreamNonBlocking));
+  for (auto &e : c->io_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  CK(cudaFuncSetAttribute(k_density_leaf<kDensCap, kDensQD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                          (int)sizeof(DensTileT)));
+  CK(cudaFuncSetAttribute(k_ghost_leaf<kGhostCap, kGhostQD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                          (int)sizeof(GhostTileT)));
+  return 0;
+}
+
 int swift_cuda_create(const swift_cuda_params *params, int device, swift_cuda_ctx **out) {
   if (!params || !out) return fail("swift_cuda_create: null argument");
+  // a_factor_Balsara_eps, fac_mu and the a^-2 of the curl are not implemented: refuse rather than return
+  // wrong Balsara switches (src/hydro/Minimal/hydro.h:700-720, hydro_iact.h:268-300)
+  if (params->cosmo_a != 1.f || params->cosmo_H != 0.f)
+    return fail("swift_cuda_create: cosmological factors are not supported (needs cosmo_a = 1, cosmo_H = 0)");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
     return fail("swift_cuda_create: no CUDA device (this backend has no CPU fallback)");
@@ -153,17 +171,13 @@ int swift_cuda_create(const swift_cuda_params *params, int device, swift_cuda_ct
     return fail("swift_cuda_create: unknown fields_mode");
   }
   c->device = device;
-  CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-  for (auto &e : c->ev) CK(cudaEventCreate(&e));
-  CK(cudaStreamCreateWithFlags(&c->io, cudaStreamNonBlocking));
-  for (auto &e : c->io_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   std::memset(&c->dev, 0, sizeof(Dev));
   if (const char *e = getenv("SWIFT_CUDA_PATH")) c->path = atoi(e);
   if (const char *e = getenv("SWIFT_CUDA_SLOW")) c->force_slow = atoi(e);
-  CK(cudaFuncSetAttribute(k_density_leaf<kDensCap, kDensQD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                          (int)sizeof(DensTileT)));
-  CK(cudaFuncSetAttribute(k_ghost_leaf<kGhostCap, kGhostQD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                          (int)sizeof(GhostTileT)));
+  if (create_resources(c)) {
+    swift_cuda_destroy(c);  // releases whatever was created; the error text is kept
+    return 1;
+  }
   *out = c;
   return 0;
 }
@@ -263,7 +277,7 @@ static int upload_and_pack(swift_cuda_ctx *c, const swift_cuda_parts_in *in, boo
   o.time_bin = const_cast<int8_t *>(d.time_bin);
   o.mat_id = const_cast<int32_t *>(d.mat_id);
   o.id = const_cast<int64_t *>(d.id);
-  if (n > 0) k_pack<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, r, o, with_static ? 1 : 0, 3);
+  if (n > 0) k_pack<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, m, r, o, with_static ? 1 : 0, 3);
   CK(cudaGetLastError());
   return 0;
 }
@@ -571,7 +585,9 @@ __global__ void k_fma_peak(float *out, int iters) {
 double swift_cuda_measure_fp32_peak(swift_cuda_ctx *c) {
   if (!c) return -1.0;
   if (cudaSetDevice(c->device) != cudaSuccess) return -1.0;
-  const int blocks = 148 * 16, threads = 256, iters = 1 << 16;
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, c->device));
+  const int blocks = prop.multiProcessorCount * 16, threads = 256, iters = 1 << 16;
   float *buf = nullptr;
   if (cudaMalloc(&buf, (size_t)blocks * threads * sizeof(float)) != cudaSuccess) return -1.0;
   cudaEvent_t e0, e1;
@@ -894,6 +910,7 @@ int swift_cuda_step_io(swift_cuda_ctx *c, const swift_cuda_parts_in *in, int fla
   const int64_t m = c->n_io < 0 ? n : c->n_io;  // particles on the bus
   Dev &d = c->dev;
   c->counters.n_kernel_launches = 0;
+  c->marks_fresh = false;  // time bins may change
   RawIn r;
   std::memset(&r, 0, sizeof(r));
   // io stream: positions, then the rest
@@ -928,10 +945,10 @@ int swift_cuda_step_io(swift_cuda_ctx *c, const swift_cuda_parts_in *in, int fla
   // compute stream
   CK(cudaEventRecord(c->ev[0], c->stream));
   CK(cudaStreamWaitEvent(c->stream, c->io_ev[0], 0));
-  if (n > 0) k_pack<<<nb, 256, 0, c->stream>>>(n, r, o, 0, 1);
+  if (n > 0) k_pack<<<nb, 256, 0, c->stream>>>(n, m, r, o, 0, 1);
   if ((flags & SWIFT_CUDA_STEP_SORT) && launch_sort(c)) return 1;
   CK(cudaStreamWaitEvent(c->stream, c->io_ev[1], 0));
-  if (n > 0) k_pack<<<nb, 256, 0, c->stream>>>(n, r, o, 0, 2);
+  if (n > 0) k_pack<<<nb, 256, 0, c->stream>>>(n, m, r, o, 0, 2);
   if (d.ncells > 0)
     k_cell_hmax_init<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d, d.cell_hmax,
                                                                          const_cast<float *>(d.cell_hmax_old));
@@ -1314,7 +1331,7 @@ __global__ void k_halo_unpack_rho(Dev d, const int32_t *idx, int64_t n, const Ha
   const HaloRho r = buf[k];
   d.h[p] = r.h;
   d.fin[p] = make_float4(r.rho, r.P, r.f, r.c);
-  d.hb[p] = make_float4(r.h, r.bal, __int_as_float((int)d.time_bin[p]), r.P / (r.rho * r.rho));
+  d.hb[p] = make_float4(r.h, r.bal, __int_as_float((int)d.time_bin[p] & kBinMask), r.P / (r.rho * r.rho));
 }
 }  // namespace swiftcuda
 

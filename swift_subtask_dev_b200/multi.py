@@ -122,6 +122,9 @@ class Partition:
         return np.array(sorted(out), dtype=np.int64)
 
 
+FOREIGN_BIN = 64   # SWIFT_CUDA_FOREIGN_BIN of the library (csrc/pack.cuh: kBinMask)
+
+
 def grid_for(nranks):
     return {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[nranks]
 
@@ -130,14 +133,15 @@ def local_particles(part, rank, dim, per_cell, seed=42):
     """Owned particles first, then the halo ones; inside each group cell by cell in the order of
     the global cell index (the particles of a cell come in the same relative order on every rank
     and in a single-GPU run; owned-first lets the host move only its own particles over PCIe:
-    swift_cuda_set_transfer_count).  time_bin 1 = owned (active), 2 = halo (inactive with
-    max_active_bin = 1)."""
+    swift_cuda_set_transfer_count).  A halo copy carries its owner's time bin + FOREIGN_BIN: never
+    active here, while the owner's real bin still enters the neighbour-bin limit of the particles that
+    see it (runner_iact_nonsym_timebin)."""
     own = part.owned_cells(rank)
     halo = part.halo_cells(rank)
     cells = np.concatenate([np.sort(own), np.sort(halo)])
     ic = ics.cell_block_random(cells, part.cdim, dim, per_cell, seed=seed)
     is_own = part.owner[ic["cell"]] == rank
-    ic["time_bin"] = np.where(is_own, 1, 2).astype(np.int8)
+    ic["time_bin"] = np.where(is_own, 1, 1 + FOREIGN_BIN).astype(np.int8)
     ic["owner"] = part.owner[ic["cell"]]
     return ic
 
@@ -166,7 +170,8 @@ def local_particles_from(ic, part, rank, dim):
            for k, a in ic.items()}
     out["cell"] = cell[sel]
     out["owner"] = part.owner[out["cell"]]
-    out["time_bin"] = np.where(out["owner"] == rank, 1, 2).astype(np.int8)
+    base = out["time_bin"].astype(np.int64) if out.get("time_bin") is not None else np.ones(len(sel), dtype=np.int64)
+    out["time_bin"] = (base + FOREIGN_BIN * (out["owner"] != rank)).astype(np.int8)
     return out
 
 
@@ -241,7 +246,7 @@ class RankState:
         self.part = part
         self.device = device
         self.ic = local_particles(part, rank, dim, per_cell, seed=seed) if ic is None else ic
-        kw = dict(dim=dim, periodic=part.periodic, max_active_bin=1)
+        kw = dict(dim=dim, periodic=part.periodic, max_active_bin=56)
         kw.update(params_kw or {})
         self.be = HydroBackend(make_params(**kw), device=device)
         self.be.build(self.ic)
@@ -251,7 +256,7 @@ class RankState:
         self.slot_of = np.empty(len(order), dtype=np.int64)   # caller index -> cell-order slot
         self.slot_of[order] = np.arange(len(order))
         touched = self.be.touched_mask()
-        self.is_own = self.ic["time_bin"] == 1
+        self.is_own = self.ic["time_bin"] < FOREIGN_BIN
         need = touched & ~self.is_own
         # what I need from each peer: ids, sorted, and where they live on my device
         self.recv_ids, self.recv_idx = {}, {}

@@ -156,7 +156,7 @@ def test_weighted_partition_balances_a_clustered_box():
     owned = 0
     for r in range(4):
         loc = multi.local_particles_from(ic, part, r, dim)
-        own = loc["time_bin"] == 1
+        own = loc["time_bin"] < multi.FOREIGN_BIN
         n_own = int(own.sum())
         assert own[:n_own].all() and not own[n_own:].any()
         assert (part.owner[loc["cell"]][own] == r).all()
@@ -192,3 +192,40 @@ def test_clustered_ranks_reproduce_single_gpu_run_bit_exactly(nranks, weighted):
         tot += c["n_density"] + c["n_density_redo"] + c["n_force"]
         s.be.close()
     assert tot == cref["n_density"] + cref["n_density_redo"] + cref["n_force"]
+
+
+@pytest.mark.gpu
+def test_mixed_time_bins_across_ranks():
+    """Individual time steps across a rank boundary: halo copies carry their owner's time bin (plus the
+    foreign flag), so min_ngb_time_bin and every other result of the owned ACTIVE particles equal the
+    single-GPU run's (the reference's runner_iact_nonsym_timebin reads pj->time_bin of the real particle)."""
+    from swift_subtask_dev_b200 import HydroBackend, make_params
+    dim = (1.0, 1.0, 1.0)
+    ic = ics.clustered(200000, nclumps=10, seed=6)
+    n = len(ic["h"])
+    ic["id"] = np.arange(1, n + 1, dtype=np.int64)
+    # bins in slabs along x: the rank boundary (x = 0.5) separates bins 2 and 3, so the active bin-3
+    # particles next to it take their minimum from FOREIGN neighbours
+    ic["time_bin"] = (1 + np.minimum((4 * ic["x"][:, 0]).astype(np.int64), 3)).astype(np.int8)
+    for k in ("rho", "pressure", "soundspeed"):   # what inactive particles carry
+        ic["in_" + k] = np.ones(n, dtype=np.float32)
+    kw = dict(dim=dim, periodic=True, max_active_bin=3)
+    be = HydroBackend(make_params(**kw))
+    be.build(ic)
+    cdim = tuple(be.tree()["cdim"])
+    be.step()
+    ref = be.results()
+    be.close()
+    part, states = multi.setup_local(2, dim, cdim, 0, ic=ic, params_kw=dict(max_active_bin=3))
+    multi.step_ranks_local(states)
+    seen = 0
+    for s in states:
+        r = s.owned_results()
+        idx = r["id"] - 1
+        act = ic["time_bin"][idx] <= 3
+        seen += int(act.sum())
+        for k in ref:
+            assert np.array_equal(r[k][act], ref[k][idx][act]), (s.rank, k)
+        s.be.close()
+    assert seen == int((ic["time_bin"] <= 3).sum())
+    assert len(np.unique(ref["min_ngb_time_bin"][ic["time_bin"] <= 3])) > 2
