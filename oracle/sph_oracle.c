@@ -12,7 +12,7 @@
  * sequences are the same IEEE operations the reference build in oracle/_ref
  * executes.
  *
- * Parity pinning: tests/test_oracle_vs_ref.py runs this file and the compiled
+ * Parity pinning: tests/test_oracle.py runs this file and the compiled
  * reference (oracle/_ref/libswiftref_*.so, through ref_harness.c) on the same
  * inputs and requires identical ordered pair lists and fields equal to
  * summation-order round-off; tests/golden/ holds outputs of the reference

@@ -88,6 +88,8 @@ struct Dev {
   float *cell_box;         // [ncells][6] bounding box of the cell's particles relative to loc (lo xyz, hi xyz)
   uint32_t *cell_box_u;    // the same while it is being reduced (order-preserving integer images)
   const float *cell_hmax_old;  // value at build (h_max_old)
+  const float *recurse_limit;  // [ncells] 0.5 * dmin of the cells the work lists recursed through (+inf: none)
+  int *stale;                  // [1] cells whose h_max (+ dx_max) outgrew recurse_limit: the lists need a rebuild
   const int32_t *leaves;       // [n_leaves] cell index
   const int32_t *item_begin;   // [n_leaves+1]
   const Item *items;           // first density pass + force

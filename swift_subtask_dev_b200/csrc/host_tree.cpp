@@ -406,6 +406,7 @@ struct Flattener {
   std::vector<std::vector<SeqItem>> per_cell;
   int64_t n_interactions = 0;
   int64_t seq = 0;
+  std::vector<uint8_t> *recursed = nullptr;  // cells a sub-task recursed THROUGH (the lists depend on their h_max)
 
   // cell_can_recurse_in_{pair,self}_hydro_task, src/cell.h:761-782 (dx_max_part_old = 0 after a rebuild)
   bool recurse_pair(int c) const {
@@ -461,6 +462,7 @@ struct Flattener {
     if (tree.cells[a].count == 0 || tree.cells[b].count == 0) return;
     const PairGeom g = orient_pair(prm, tree.cells, a, b);
     if (recurse_pair(g.ci) && recurse_pair(g.cj)) {
+      if (recursed) (*recursed)[g.ci] = (*recursed)[g.cj] = 1;
       const OctPairs &op = oct_pairs(g.sid);
       for (int k = 0; k < op.n; k++) {
         const int pa = tree.cells[g.ci].progeny[op.pi[k]], pb = tree.cells[g.cj].progeny[op.pj[k]];
@@ -474,6 +476,7 @@ struct Flattener {
   void sub_self(int c) {
     if (tree.cells[c].count == 0 || !active[c]) return;
     if (recurse_self(c)) {
+      if (recursed) (*recursed)[c] = 1;
       const int *pr = tree.cells[c].progeny;
       for (int k = 0; k < 8; k++)
         if (pr[k] >= 0) {
@@ -596,6 +599,10 @@ void build_worklists(const swift_cuda_params &prm, const Tree &tree, const std::
   Flattener f{prm, tree, cell_active, {}, 0, 0};
   const size_t nc = tree.cells.size();
   f.per_cell.resize(nc);
+  wl = WorkLists();
+  wl.recurse_limit.assign(nc, INFINITY);
+  std::vector<uint8_t> recursed(nc, 0);
+  f.recursed = &recursed;
   std::vector<std::vector<int32_t>> cell_tasks(nc);
   for (size_t t = 0; t < tree.tasks.size(); t++) {
     const swift_cuda_task &tk = tree.tasks[t];
@@ -608,8 +615,13 @@ void build_worklists(const swift_cuda_params &prm, const Tree &tree, const std::
       default: f.sub_pair(tk.ci, tk.cj); break;
     }
   }
-  wl = WorkLists();
   wl.n_interactions = f.n_interactions;
+  // the run-time recursion went through these cells because gamma * h_max (+ dx_max_part) was below half
+  // their width (cell_can_recurse_in_{pair,self}_hydro_task, src/cell.h:761-782): the flattened lists are
+  // those of the reference only while that still holds (cell_unskip.c:808-815 refreshes h_max_old and
+  // dx_max_part_old every step)
+  for (size_t c = 0; c < nc; c++)
+    if (recursed[c]) wl.recurse_limit[c] = 0.5f * (float)cell_dmin(tree.cells[c]);
   wl.sort_lookup.assign(nc * 13, -1);
   auto need_sort = [&](int cell, int sid) {
     int64_t &slot = wl.sort_lookup[(size_t)cell * 13 + sid];

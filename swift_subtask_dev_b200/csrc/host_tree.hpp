@@ -70,6 +70,7 @@ struct WorkLists {
   std::vector<int32_t> sort_sids;    //                              sid
   std::vector<int64_t> sort_offset;  // start of each segment in the flat sort arrays
   std::vector<int64_t> sort_lookup;  // [ncells*13] segment start or -1
+  std::vector<float> recurse_limit;  // [ncells] 0.5 * dmin of the cells a sub-task recursed through, else +inf
   int64_t n_sort_entries = 0;
   int64_t n_interactions = 0;        // direct self + pair interactions
 };

@@ -1817,6 +1817,17 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
   if (lane == 0 && nhits) atomicAdd(&d.hits[2], nhits);
 }
 
+// Are the flattened work lists still the reference's?  A sub-task recursed through a cell at the build
+// because gamma * h_max + dx_max_part < dmin / 2 held (src/cell.h:761-782); the reference re-evaluates
+// that every step with the current values (src/cell_unskip.c:808-815) and stops recursing when it fails,
+// which changes the level -- and so the frame and the reach -- at which pairs are evaluated.
+__global__ void k_check_lists(Dev d, float dx_max) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= d.ncells) return;
+  const float lim = d.recurse_limit[c];
+  if (!(kc.gamma * d.cell_hmax_old[c] + dx_max < lim)) atomicAdd(d.stale, 1);
+}
+
 // runner_do_end_hydro_force on its own (swift_cuda_step_parts without the force loop in the same call)
 __global__ void k_end_force(Dev d) {
   const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;

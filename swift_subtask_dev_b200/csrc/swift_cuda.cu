@@ -79,6 +79,7 @@ struct swift_cuda_ctx {
   unsigned char *d_aos = nullptr;
   bool no_prune = false;            // build the work lists with every cell, whatever the time bins
   std::vector<int32_t> slot_of;     // host copy of Dev::part_slot (caller order)
+  float dx_max_part = 0.f;          // largest |x_diff| since the build (swift_cuda_drift), for k_check_lists
   int path = 8;                     // default: ghost redo sweeps from recorded neighbour lists
   int force_slow = 0;  // test hook (SWIFT_CUDA_SLOW=1): every hit takes the exact sorted-axis-cut path
 };
@@ -108,6 +109,7 @@ static void free_device(swift_cuda_ctx *c) {
   for (void *p : c->allocs) cudaFree(p);
   c->allocs.clear();
   c->built = false;
+  c->dx_max_part = 0.f;
   // the time-integration state lived in those allocations
   c->integ_on = false;
   c->marks_fresh = false;
@@ -332,6 +334,11 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
       upload(c, &dhm_old, c->tree.h_max.data(), nc))
     return 1;
   d.cells = dcells; d.cell_hmax_old = dhm_old;
+  {
+    float *drl;
+    if (upload(c, &drl, c->wl.recurse_limit.data(), nc) || dmalloc(c, &d.stale, 1)) return 1;
+    d.recurse_limit = drl;
+  }
   {
     std::vector<int32_t> par(nc);
     std::vector<uint8_t> spl(nc);
@@ -674,6 +681,8 @@ static int launch_density_prep(swift_cuda_ctx *c) {
   CK(cudaMemcpyAsync(d.cell_hmax, d.cell_hmax_old, (size_t)d.ncells * sizeof(float), cudaMemcpyDeviceToDevice,
                      c->stream));
   CK(cudaMemsetAsync(d.work_ctr, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
+  CK(cudaMemsetAsync(d.stale, 0, sizeof(int), c->stream));
+  if (d.ncells > 0) k_check_lists<<<(d.ncells + 255) / 256, 256, 0, c->stream>>>(d, c->dx_max_part);
   if (launch_cell_box(c)) return 1;
   if (d.nl) CK(cudaMemsetAsync(d.nl_cnt, 0xff, (size_t)d.n_units * 32 * sizeof(unsigned short), c->stream));
   k_init_step<<<nb, 256, 0, c->stream>>>(d);
@@ -767,7 +776,13 @@ static int finish_counters(swift_cuda_ctx *c) {
   std::vector<int> redo((size_t)c->prm.max_smoothing_iterations + 2);
   CK(cudaMemcpyAsync(hits, d.hits, sizeof(hits), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaMemcpyAsync(redo.data(), d.redo_count, redo.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  int stale = 0;
+  CK(cudaMemcpyAsync(&stale, d.stale, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
+  if (stale > 0)
+    return fail("work lists are stale: " + std::to_string(stale) + " cell(s) the sub-tasks recursed through now have "
+                "gamma * h_max + dx_max_part >= dmin / 2 (cell_can_recurse_in_*_hydro_task fails: the reference would "
+                "stop recursing there); rebuild the context (swift_cuda_build_*)");
 #ifdef SWIFT_CUDA_GHOST_STATS
   {
     int st[12];
@@ -1430,6 +1445,7 @@ int swift_cuda_drift(swift_cuda_ctx *c, long long ti_old, float dx_max[2]) {
   CK(cudaMemcpyAsync(dx2, c->integ.dx2_max, sizeof(dx2), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   CK(cudaEventElapsedTime(&c->integ_ms[0], c->ev[0], c->ev[5]));
+  c->dx_max_part = sqrtf(dx2[0]);
   if (dx_max) {
     dx_max[0] = sqrtf(dx2[0]);  // cell_drift.c:359-360
     dx_max[1] = sqrtf(dx2[1]);

@@ -43,6 +43,27 @@ def test_golden_dropin_tree(name):
     parity.assert_exact(r)
 
 
+@pytest.mark.parametrize("name", gu.names())
+def test_golden_fast_fields_mode(name):
+    """fields_mode = FAST against the reference's outputs: the pair lists of all three loops, the counts,
+    h, rho and everything else up to the ghost bit-exact; a, u_dt, h_dt, v_sig within 1e-4."""
+    g = gu.load(name)
+    planetary = g["variant"] == "planetary"
+    eos = ol.eos_from_json() if planetary else None
+    cells, tasks, nt = gu.tree_structs(g)
+    n = len(g["h"])
+    out = parity.run_gpu(g["ic"], g["params"], record=True, pair_capacity=n * 400, tree=(cells, tasks, nt), eos=eos,
+                         fields_mode=1)
+    ref = {k: g[k] for _, k in parity.FIELD_MAP}
+    ref["counts"] = [int(v) for v in g["counts"]]
+    act = _active(g["ic"], g["params"])
+    r = parity.compare(out, ref, active=act, verbose=False)
+    for s in range(3):
+        assert gu.pair_digest(out["pairs"][s]) == str(g["digests"][s]), "pair list of loop %d differs" % s
+    worst = parity.assert_fast(out, ref, r, active=act)
+    print(name, "FAST worst relative errors:", worst)
+
+
 # ---------------------------------------------------------------- library-built tree vs oracle
 def _check(ic, kw, pairs=True):
     n = len(ic["h"])

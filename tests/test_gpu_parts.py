@@ -86,3 +86,24 @@ def test_phase_calls_add_up_to_the_step():
     b.close()
     assert np.allclose(twice["wcount"], 2 * once, rtol=1e-5)
     assert (twice["wcount"] > once).all()
+
+
+@pytest.mark.gpu
+def test_stale_work_lists_are_refused():
+    """The flattened lists replay the sub-task recursion with the cells' h_max at the build; the reference
+    re-evaluates cell_can_recurse_in_*_hydro_task every step (src/cell_unskip.c:808-815).  When h grows
+    past gamma * h_max >= dmin / 2 in a cell the lists recursed through, the step must fail loudly
+    instead of silently dropping the neighbours in non-adjacent progeny."""
+    from swift_subtask_dev_b200 import SwiftCudaError
+    ic = ics.uniform_random(96 ** 3, seed=12)   # 512 particles per top-level cell: split, sub-tasks recurse
+    b = HydroBackend(make_params(periodic=True))
+    b.build(ic)
+    b.step()
+    grown = dict(ic, h=(ic["h"] * 2.5).astype(np.float32))
+    b.update_particles(grown)
+    with pytest.raises(SwiftCudaError, match="work lists are stale"):
+        b.step()
+    # a rebuild with the new h is the remedy
+    b.build(grown)
+    b.step()
+    b.close()
