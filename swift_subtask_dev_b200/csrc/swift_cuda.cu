@@ -10,6 +10,7 @@
 #include "kernels.cuh"
 #include "leaf_kernels.cuh"
 #include "list_kernels.cuh"
+#include "force_fast.cuh"
 #include "pack.cuh"
 #include "integrate.cuh"
 
@@ -758,10 +759,10 @@ static int launch_force(swift_cuda_ctx *c) {
     const int nb = c->grid_force;
     const bool fast = c->prm.fields_mode == SWIFT_CUDA_FIELDS_FAST;
     if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY) {
-      if (fast) k_force<SWIFT_CUDA_SCHEME_PLANETARY, true><<<nb, kBlock, 0, c->stream>>>(d);
+      if (fast) k_force_fast<SWIFT_CUDA_SCHEME_PLANETARY><<<nb, kBlock, 0, c->stream>>>(d, c->force_slow);
       else k_force<SWIFT_CUDA_SCHEME_PLANETARY, false><<<nb, kBlock, 0, c->stream>>>(d);
     } else {
-      if (fast) k_force<SWIFT_CUDA_SCHEME_MINIMAL, true><<<nb, kBlock, 0, c->stream>>>(d);
+      if (fast) k_force_fast<SWIFT_CUDA_SCHEME_MINIMAL><<<nb, kBlock, 0, c->stream>>>(d, c->force_slow);
       else k_force<SWIFT_CUDA_SCHEME_MINIMAL, false><<<nb, kBlock, 0, c->stream>>>(d);
     }
   }
