@@ -119,6 +119,7 @@ struct Dev {
   // counters: [0] density, [1] redo, [2] force
   unsigned long long *hits;
   int *redo_count;         // [max_iter+1]
+  int *walk_count;         // [max_iter+2] of those, the particles the walking kernel redoes (the others: k_density_list)
   // neighbour lists of the ghost iteration (null: not recorded): [n_units][kLD][32] (dx, dy, dz, j)
   float4 *nl;
   unsigned short *nl_cnt;      // [n_units*32] entries of a lane's list, 0xffff: none / overflowed

@@ -675,7 +675,7 @@ __device__ __noinline__ bool dens_cut_exact(const CutCtx d, const Item item, dou
 // ---------------------------------------------------------------------------
 template <int MODE>
 __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, int sweep) {
-  if (MODE == 1 && d.redo_count[sweep] == 0) return;
+  if (MODE == 1 && d.walk_count[sweep] == 0) return;
   __shared__ WarpTile tiles[kWarps];
   WarpTile &ws = tiles[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
@@ -684,7 +684,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
   // redo sweeps: while most particles are still flagged (the first sweeps) a warp takes a 32-particle
   // unit as the first pass does (5x more leaves in flight would not fit the L2); once the flagged
   // particles are few, a warp takes a whole leaf and compacts them into full groups of 32
-  const bool by_unit = MODE == 0 || (long long)d.redo_count[sweep] * 2 > d.n;
+  const bool by_unit = MODE == 0 || (long long)d.walk_count[sweep] * 2 > d.n;
   // few leaves with a flagged particle: walk the list k_ghost pushed; otherwise all leaves in tree order
   // (spatially coherent, the unflagged ones are skipped after one look)
   const bool by_list = MODE == 1 && !by_unit && (long long)d.leaf_count[sweep] * 4 < d.n_leaves;
@@ -1294,6 +1294,7 @@ __device__ __forceinline__ void ghost_particle(const Dev &d, int sweep, int64_t 
       d.gstate[p] = ns;
       atomicAdd(&d.redo_count[sweep], 1);
       if (ns == 4) return;
+      atomicAdd(&d.walk_count[sweep], 1);
       const int slot = d.part_slot[p];
       if (slot >= 0 && atomicExch(&d.leaf_mark[slot], sweep + 1) != sweep + 1)
         d.leaf_list[atomicAdd(&d.leaf_count[sweep], 1)] = slot;

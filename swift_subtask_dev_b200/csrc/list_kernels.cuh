@@ -77,6 +77,7 @@ __global__ void __launch_bounds__(kBlock) k_density_list(Dev d, int sweep) {
       d.gstate[q] = 2;
       d.nl_cnt[ul] = 0xffff;
       nhits = 0;
+      atomicAdd(&d.walk_count[sweep], 1);
       const int slot = d.part_slot[q];
       if (slot >= 0 && atomicExch(&d.leaf_mark[slot], sweep + 1) != sweep + 1)
         d.leaf_list[atomicAdd(&d.leaf_count[sweep], 1)] = slot;

@@ -389,7 +389,7 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
     d.part_lane = dpl;
     CK(cudaStreamSynchronize(c->stream));  // groups, part_lane go out of scope
     d.nl = nullptr;
-    d.nl_grow = 1.02f;
+    d.nl_grow = 1.0005f;
     if (const char *e = getenv("SWIFT_CUDA_GROW")) d.nl_grow = (float)atof(e);
     if (c->path & 8) {
       if (dmalloc(c, &d.nl, (size_t)d.n_units * kLD * 32) || dmalloc(c, &d.nl_cnt, (size_t)d.n_units * 32) ||
@@ -434,6 +434,7 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
       dmalloc(c, &c->d_scratch, (size_t)scratch_total))
     return 1;
   if (dmalloc(c, &d.hits, 3) || dmalloc(c, &d.redo_count, (size_t)c->prm.max_smoothing_iterations + 2) ||
+      dmalloc(c, &d.walk_count, (size_t)c->prm.max_smoothing_iterations + 2) ||
       dmalloc(c, &d.rec_count, 3))
     return 1;
   CK(cudaMemsetAsync(d.rec_count, 0, 3 * sizeof(unsigned long long), c->stream));
@@ -677,6 +678,7 @@ static int launch_density_prep(swift_cuda_ctx *c) {
   const int nb = (int)((c->n + 255) / 256);
   CK(cudaMemsetAsync(d.hits, 0, 3 * sizeof(unsigned long long), c->stream));
   CK(cudaMemsetAsync(d.redo_count, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
+  CK(cudaMemsetAsync(d.walk_count, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
   CK(cudaMemsetAsync(d.leaf_count, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
   CK(cudaMemsetAsync(d.leaf_mark, 0, (size_t)std::max(d.n_leaves, 1) * sizeof(int), c->stream));
   CK(cudaMemcpyAsync(d.cell_hmax, d.cell_hmax_old, (size_t)d.ncells * sizeof(float), cudaMemcpyDeviceToDevice,
