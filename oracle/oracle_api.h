@@ -113,6 +113,13 @@ int ref_sizeof_part(void);
  * examples/Planetary/EarthImpact/earth_impact.yml:2-7). Returns 0 when compiled in. */
 int ref_get_eos(oracle_eos *out);
 
+/* The cell tree and the hydro task list of a particle set by the reference's OWN space_regrid,
+ * space_split_recursive, engine_make_hydroloop_tasks_mapper and scheduler_splittasks (oracle/ref_tree.c).
+ * order[k] = input index of the particle at cell-order slot k; arrays are malloc'ed (free()). */
+int ref_build_tree_tasks(const oracle_params *prm, int n, const double *x, const float *h, int *order,
+                         oracle_cell **cells_out, int *ncells_out, int cdim_out[3], oracle_task **tasks_out,
+                         int *ntasks_out);
+
 /* ---- the plain-C restatement (oracle/sph_oracle.c) ---- */
 int oracle_build_tree(const oracle_params *prm, int n, const double *x, const float *h, int *order,
                       oracle_cell **cells_out, int *ncells_out, int cdim_out[3]);
