@@ -124,7 +124,9 @@ struct Dev {
   float4 *nl;
   unsigned short *nl_cnt;      // [n_units*32] entries of a lane's list, 0xffff: none / overflowed
   float *nl_R;                 // [n_units*32] (h gamma)^2 the list covers
-  float nl_grow;               // the recording sweep covers nl_grow x the search radius
+  float nl_grow;               // the recording sweep covers (nl_grow + nl_slope |h / h_before - 1|) x the search radius
+  float nl_slope;
+  float *h_before;             // [n] h before the ghost's last update (how far Newton-Raphson just moved it)
   const int32_t *part_lane;    // [n] unit * 32 + lane of a particle, -1: none
   // swift_cuda_step_parts: continue the running density sums / leave hydro_end_force to its own phase
   int keep_sums;

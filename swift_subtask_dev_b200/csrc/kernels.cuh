@@ -766,7 +766,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
       int qcnt = 0;
       // list-recording sweep: the walk covers kGrowL x the search radius
       const bool recl = MODE == 1 && d.nl != nullptr;
-      const float higR = recl ? __fmul_rn(hig, d.nl_grow) : hig;
+      const float higR = recl ? __fmul_rn(hig, d.nl_grow + d.nl_slope * fabsf(hi / d.h_before[pp] - 1.f)) : hig;
       const float hig2R = recl ? __fmul_rn(__fmul_rn(higR, higR), 1.000001f) : hig2;
       int ln = 0;
       float4 *nlp = nullptr;
@@ -1288,6 +1288,7 @@ __device__ __forceinline__ void ghost_particle(const Dev &d, int sweep, int64_t 
       // 2: the next redo sweep walks the cells for this particle; 4: its recorded neighbour list covers the new h
       uint8_t ns = 2;
       if (d.nl != nullptr) {
+        d.h_before[p] = h_old;
         const int ul = d.part_lane[p];
         if (ul >= 0 && d.nl_cnt[ul] != 0xffff && sq_gamma2(h) < d.nl_R[ul] * 0.999998f) ns = 4;
       }

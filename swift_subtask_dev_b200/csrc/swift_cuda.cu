@@ -390,10 +390,12 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
     CK(cudaStreamSynchronize(c->stream));  // groups, part_lane go out of scope
     d.nl = nullptr;
     d.nl_grow = 1.0005f;
+    d.nl_slope = 0.f;
     if (const char *e = getenv("SWIFT_CUDA_GROW")) d.nl_grow = (float)atof(e);
+    if (const char *e = getenv("SWIFT_CUDA_SLOPE")) d.nl_slope = (float)atof(e);
     if (c->path & 8) {
       if (dmalloc(c, &d.nl, (size_t)d.n_units * kLD * 32) || dmalloc(c, &d.nl_cnt, (size_t)d.n_units * 32) ||
-          dmalloc(c, &d.nl_R, (size_t)d.n_units * 32))
+          dmalloc(c, &d.nl_R, (size_t)d.n_units * 32) || dmalloc(c, &d.h_before, (size_t)c->n))
         return 1;
     }
   }

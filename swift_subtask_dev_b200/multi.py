@@ -457,6 +457,8 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
     grid = grid_for(world)
     side = args.side
     clustered = getattr(args, "workload", "uniform") == "clustered"
+    fast = getattr(args, "fields", "fast") == "fast"
+    pkw = dict(fields_mode=1 if fast else 0)
     t0 = time.perf_counter()
     if clustered:
         # BASELINE configs[4]: ONE clustered box of side^3 particles split over the ranks (strong
@@ -468,7 +470,8 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
         weights = np.bincount(top_cell_of(gic["x"], cdim, dim), minlength=int(np.prod(cdim)))
         part = Partition(cdim, grid, periodic=True, weights=weights)
         per_cell = 0
-        st = RankState(rank, part, dim, per_cell, device=local, ic=local_particles_from(gic, part, rank, dim))
+        st = RankState(rank, part, dim, per_cell, device=local, ic=local_particles_from(gic, part, rank, dim),
+                       params_kw=pkw)
         del gic
     else:
         dim = tuple(float(g) for g in grid)
@@ -476,7 +479,7 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
         cdim = ics.top_grid(dim, h0)
         part = Partition(cdim, grid, periodic=True)
         per_cell = int(round(side ** 3 * world / float(np.prod(cdim))))
-        st = RankState(rank, part, dim, per_cell, seed=cfg["seed"], device=local)
+        st = RankState(rank, part, dim, per_cell, seed=cfg["seed"], device=local, params_kw=pkw)
     wanted = tr.all_to_all_objects({p: ids for p, ids in st.recv_ids.items()})
     st.set_send_lists(wanted)
     build_s = time.perf_counter() - t0
@@ -558,6 +561,9 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
                                "over a %dx%dx%d GPU grid (%d^3 particles per GPU), density+ghost+force, Minimal SPH "
                                "+ ideal gas" % (per_cell, "x".join(map(str, cdim)), grid[0], grid[1], grid[2], side))
         cfg["parallelism"] = "spatial %dx%dx%d, NCCL send/recv halo (xv 48 B, rho 24 B per particle)" % grid
+        cfg["fields_mode"] = ("FAST: neighbour lists, counts and h bit-exact; force-loop fields with FMA / MUFU "
+                              "arithmetic, within 1e-4 of the reference" if fast else
+                              "EXACT: every field bit-identical to the reference")
         nloc_tot = int(tsum[5])
         line = {"metric": metric, "value": float(tsum[1]) / (ms * 1e-3), "unit": unit, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
