@@ -665,6 +665,24 @@ __device__ __noinline__ bool dens_cut_exact(const CutCtx d, const Item item, dou
   return kind == kSubPair ? (key <= thr_lt(cut)) : (key >= thr_gt(cut));
 }
 
+// The same for a neighbour known only by its index (the FILT form of k_density decides when the hit is
+// consumed, where the interaction it came from is no longer at hand): the interaction is found by the
+// cell range j lies in, the neighbour's sort key is formed again from its position (as k_sort does).
+__device__ __noinline__ bool dens_cut_exact_scan(const CutCtx d, const Item *__restrict__ items, int ib, int ie,
+                                                 const PosD *__restrict__ pos, int j, double xi, double yi, double zi,
+                                                 float hig) {
+  for (int it = ib; it < ie; it++) {
+    const Item item = items[it];
+    if (item.kind == kSelf || item.kind == kSubSelf) continue;
+    const CellDev cB = d.cells[item.partner];
+    if (j < cB.first || j >= cB.first + cB.count) continue;
+    double xj, yj, zj;
+    load_pos(pos, j, xj, yj, zj);
+    return dens_cut_exact(d, item, xi, yi, zi, hig, sort_key(xj, yj, zj, item.sid));
+  }
+  return true;  // own cell: no sorted-axis cut
+}
+
 // ---------------------------------------------------------------------------
 // K3 / K5: density.
 // MODE 0: first pass, DOSELF1 / DOPAIR1 arithmetic, every active particle;
@@ -673,8 +691,8 @@ __device__ __noinline__ bool dens_cut_exact(const CutCtx d, const Item item, dou
 //         particles the ghost flagged (gstate == 2); a unit is a leaf, whose
 //         flagged particles the warp first compacts into full groups of 32.
 // ---------------------------------------------------------------------------
-template <int MODE>
-__global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, int sweep) {
+template <int MODE, bool FILT = false>
+__global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, int sweep, int force_slow = 0) {
   if (MODE == 1 && d.walk_count[sweep] == 0) return;
   __shared__ WarpTile tiles[kWarps];
   WarpTile &ws = tiles[threadIdx.x >> 5];
@@ -768,6 +786,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
       const bool recl = MODE == 1 && d.nl != nullptr;
       const float higR = recl ? __fmul_rn(hig, d.nl_grow + d.nl_slope * fabsf(hi / d.h_before[pp] - 1.f)) : hig;
       const float hig2R = recl ? __fmul_rn(__fmul_rn(higR, higR), 1.000001f) : hig2;
+      const float r2safe = FILT ? safe_r2(hig, cut_delta(d), force_slow != 0) : 0.f;
       int ln = 0;
       float4 *nlp = nullptr;
       int ul = -1;
@@ -811,7 +830,11 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
           if (ln < kLD) nlp[(size_t)ln * 32] = make_float4(dx, dy, dz, __int_as_float(w & kIdxMask));
           ln++;
         }
-        if (r2 < hig2 && (!recl || (w & kInWin))) {
+        bool hit = r2 < hig2 && (FILT || !recl || (w & kInWin));
+        // FILT: the sorted-axis cut is implied by r2 < h^2 gamma^2 unless r is within delta of the radius
+        if (FILT && hit && !(r2 < r2safe))
+          hit = dens_cut_exact_scan(cut_ctx(d), items, ib, ie, d.pos, w & kIdxMask, xi, yi, zi, hig);
+        if (hit) {
           iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, vmj);
           nhits++;
           if (rec) record_pair(d, MODE, idi, d.id[w & kIdxMask]);
@@ -904,6 +927,23 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
         if (kind == kSelf || kind == kSubSelf) {
           if (mine) { lo = loR = -INFINITY; hi_cut = hiR = INFINITY; }
           if (kind == kSelf) thr = cull_thr(hig2, 4e-7f * cA.width);
+        } else if (FILT) {
+          // the candidate test is a pure distance filter; what is needed here is only how far along the
+          // sorted axis this lane can reach at all (|key_j - key_i'| <= r): it bounds the staging walk
+          if (kind != kPairLeft && kind != kPairRight) {
+            px = __dsub_rn(xi, sh[0]); py = __dsub_rn(yi, sh[1]); pz = __dsub_rn(zi, sh[2]);
+            thr = cull_thr(hig2R, 8e-7f * fmaxf(cA.width, cB.width));
+          }
+          if (mine) {
+            const double rshift = item_rshift(sh, sid);
+            const float d_me = sort_key(xi, yi, zi, sid);
+            const float kme = (float)(kind == kPairRight ? ((double)d_me + rshift) : ((double)d_me - rshift));
+            const float m = 4e-7f * (fabsf(kme) + fabsf((float)rshift) + fabsf(d_me)) + 1e-30f;
+            const float reach = higR * 1.000002f;
+            if (!desc) { loR = -INFINITY; hiR = kme + reach + m; }
+            else { loR = kme - reach - m; hiR = INFINITY; }
+            lo = loR; hi_cut = hiR;
+          }
         } else if (kind == kPairLeft) {
           // this leaf's particles are "pi" of DOPAIR1 loop 1 (:1122-1216): frame cj.loc + shift
           if (mine) {
@@ -972,8 +1012,9 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
               const float dx = __fsub_rn(pfx, c.x), dy = __fsub_rn(pfy, c.y), dz = __fsub_rn(pfz, c.z);
               const float r2c = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
               const int j = ti[k0 + u];
-              const bool push = c.w >= loR && c.w <= hiR && r2c < thr_c && j != pp;
-              const int inwin = (MODE == 1 && c.w >= lo && c.w <= hi_cut) ? kInWin : 0;
+              const bool push = FILT ? (mine && r2c < thr_c && j != pp)
+                                     : (c.w >= loR && c.w <= hiR && r2c < thr_c && j != pp);
+              const int inwin = (!FILT && MODE == 1 && c.w >= lo && c.w <= hi_cut) ? kInWin : 0;
               // straight-line: the store and the FIFO advance are predicated, not branched over
               if (SHIFTED) st_pred(qp, shf[0], shf[1], shf[2], __int_as_float(j | kDpFlag | inwin), push);
               else st_pred(qp, dx, dy, dz, __int_as_float(j | flagbits | inwin), push);

@@ -81,7 +81,9 @@ struct swift_cuda_ctx {
   bool no_prune = false;            // build the work lists with every cell, whatever the time bins
   std::vector<int32_t> slot_of;     // host copy of Dev::part_slot (caller order)
   float dx_max_part = 0.f;          // largest |x_diff| since the build (swift_cuda_drift), for k_check_lists
-  int path = 8;                     // default: ghost redo sweeps from recorded neighbour lists
+  int path = 8;                     // default: ghost redo sweeps from recorded neighbour lists (8).  Bit 5 (32): the
+                                    // density walks as distance filters with the decision made at consumption --
+                                    // bit-exact, measured 8 % SLOWER than the windowed test (spills), left off
   int force_slow = 0;  // test hook (SWIFT_CUDA_SLOW=1): every hit takes the exact sorted-axis-cut path
 };
 
@@ -703,7 +705,8 @@ static int launch_density(swift_cuda_ctx *c) {
     if (d.n_groups > 0)
       k_density_leaf<kDensCap, kDensQD><<<d.n_groups, kLT, sizeof(DensTileT), c->stream>>>(d, c->force_slow);
   } else if (d.n_units > 0) {
-    k_density<0><<<c->grid_density, kBlock, 0, c->stream>>>(d, 0);
+    if ((c->path & 32) && !c->integ_on) k_density<0, true><<<c->grid_density, kBlock, 0, c->stream>>>(d, 0, c->force_slow);
+    else k_density<0><<<c->grid_density, kBlock, 0, c->stream>>>(d, 0);
   }
   c->counters.n_kernel_launches += 1;
   CK(cudaGetLastError());
@@ -746,7 +749,10 @@ static int launch_ghost(swift_cuda_ctx *c) {
       k_density_list<<<(d.n_units + kWarps - 1) / kWarps, kBlock, 0, c->stream>>>(d, sweep);
       c->counters.n_kernel_launches += 1;
     }
-    if (d.n_leaves > 0) k_density<1><<<c->grid_redo, kBlock, 0, c->stream>>>(d, sweep);
+    if (d.n_leaves > 0) {
+      if ((c->path & 32) && !c->integ_on) k_density<1, true><<<c->grid_redo, kBlock, 0, c->stream>>>(d, sweep, c->force_slow);
+      else k_density<1><<<c->grid_redo, kBlock, 0, c->stream>>>(d, sweep);
+    }
     c->counters.n_kernel_launches += 1;
   }
   k_cell_hmax<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d);
