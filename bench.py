@@ -367,12 +367,13 @@ def main():
     e2e_soa = {"value": inter / float(np.mean(soa_times)), "unit": UNIT, "h2d_bytes_per_step": h2d_soa,
                "d2h_bytes_per_step": d2h_soa, "entry": "swift_cuda_step_io (SoA field arrays)"}
 
-    # ---- roofline of the dominant kernel: the single launch that takes longest (k_force; the ghost
-    # phase is longer in total but is five launches of k_density<1>).  FP32 CUDA-core bound (SURVEY.md
+    # ---- roofline of the dominant kernel: the single launch that takes longest (the force loop; the ghost
+    # phase is longer in total but is a dozen launches of k_density<1> / k_density_list).  FP32 CUDA-core bound (SURVEY.md
     # 8(d)): algorithmic flops = 66 per density interaction, 122 per force interaction; candidate tests
     # that miss are not credited.  kernel_ms = CUDA events on the library's stream around that launch.
+    fname = "k_force_fast" if fast else "k_force"
     per_launch = {"k_density<0>": (phase["density_ms"] / args.steps, FLOP_DENSITY * cnt["n_density"]),
-                  "k_force": (phase["force_ms"] / args.steps, FLOP_FORCE * cnt["n_force"])}
+                  fname: (phase["force_ms"] / args.steps, FLOP_FORCE * cnt["n_force"])}
     dom = max(per_launch, key=lambda k: per_launch[k][0])
     kern_ms, flops = per_launch[dom]
     achieved = flops / (kern_ms * 1e-3) / 1e12
@@ -389,7 +390,7 @@ def main():
     # dram bytes of that kernel per launch, from the committed `ncu --set full` capture of this command
     traffic = None
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
             tj = json.load(f)
         if tj.get("side") == args.side:
             traffic = tj["dram_bytes_per_launch"].get(dom)
@@ -398,8 +399,10 @@ def main():
     redo_ms = phase["ghost_ms"] / args.steps
     roofline = {"bound": "fp32", "kernel": dom,
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "peak_source": "FMA microbenchmark run by this bench on this GPU (MEASURED_PEAKS.json has no FP32 "
-                               "entry); nominal 148 SMs x 128 lanes x 2 x 1965 MHz = %.1f" % peak_nominal,
+                "peak_source": "FALLBACK denominator: FMA microbenchmark run by this bench on this GPU at the clocks in "
+                               "`clocks` (MEASURED_PEAKS.json has no FP32 entry); nominal 148 SMs x 128 lanes x 2 x "
+                               "1965 MHz = %.1f" % peak_nominal,
+                "peak_sm_mhz": clocks.get("sm_mhz"),
                 "kernel_ms": kern_ms, "traffic": traffic,
                 "note": "bound is the FP32 CUDA-core issue rate (SURVEY 8(d): ~40 flop/B, no dense contraction: "
                         "neither 'hbm' nor 'tensor'); achieved counts only the 122 (66) algorithmic flop of "
@@ -407,7 +410,7 @@ def main():
                 "other_kernels": {"k_density<0>": {"ms": per_launch["k_density<0>"][0],
                                                    "tflops": per_launch["k_density<0>"][1] /
                                                    (per_launch["k_density<0>"][0] * 1e-3) / 1e12},
-                                  "k_density<1> x %d sweeps + k_ghost" % cnt["ghost_sweeps"]:
+                                  "ghost: k_density<1> + k_density_list x %d sweeps + k_ghost" % cnt["ghost_sweeps"]:
                                       {"ms": redo_ms,
                                        "tflops": FLOP_DENSITY * cnt["n_density_redo"] / (redo_ms * 1e-3) / 1e12}},
                 "hbm_step": {"achieved_gbs": 223.0 * n / (ms * 1e-3) / 1e9, "peak_gbs": hbm_peak,

@@ -89,6 +89,38 @@ __device__ __noinline__ bool force_cut_exact(const ForceCutCtx d, int ib, int ie
   return true;  // not found among the pair interactions: own cell, DOSELF2 has no sorted-axis cut
 }
 
+// FIFO traffic with L2 eviction priorities: a stored hit should stay in the L2 until it is consumed
+// (evict_last), a consumed one should be the first to go (evict_first).  SWIFT_FIFO_POLICY=0: the
+// streaming st.global.cs / ld.global.cs of the first-generation kernels.
+#ifndef SWIFT_FIFO_POLICY
+#define SWIFT_FIFO_POLICY 1
+#endif
+__device__ __forceinline__ unsigned long long l2_policy_evict_last() {
+  unsigned long long p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ unsigned long long l2_policy_evict_first() {
+  unsigned long long p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void st_pred_pol(float4 *p, float x, float y, float z, float w, bool pred,
+                                            unsigned long long pol) {
+  asm volatile(
+      "{ .reg .pred q; setp.ne.b32 q, %5, 0; @q st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %6; }" ::"l"(p),
+      "f"(x), "f"(y), "f"(z), "f"(w), "r"((int)pred), "l"(pol)
+      : "memory");
+}
+__device__ __forceinline__ float4 ld_pol(const float4 *p, unsigned long long pol) {
+  float4 r;
+  asm volatile("ld.global.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p), "l"(pol)
+               : "memory");
+  return r;
+}
+
 struct FastTile {
   float4 pos[kTile];  // frame position of the candidate; w: its (h gamma)^2 (own cell: its cull threshold)
   int idx[kTile];
@@ -96,16 +128,20 @@ struct FastTile {
 };
 
 template <int SCHEME>
-__global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force_fast(Dev d, int force_slow) {
+__global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force_fast(Dev d, int force_slow, int qd) {
   __shared__ FastTile tiles[kWarps];
   FastTile &ws = tiles[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
   const unsigned lt_mask = (1u << lane) - 1u;
-  float4 *const gq = d.gq + (size_t)(blockIdx.x * kWarps + (threadIdx.x >> 5)) * (kQD * 32) + lane;
+  // qd <= kQD rows of the per-warp FIFO are used: the FAST mode may consume its hits whenever the FIFO
+  // fills up, and a shorter FIFO keeps the hit traffic of all resident warps inside the L2
+  float4 *const gq = d.gq + (size_t)(blockIdx.x * kWarps + (threadIdx.x >> 5)) * (qd * 32) + lane;
   int *const work = d.work_ctr + 1 + kc.max_iter;
   const bool rec = d.rec_capacity > 0;
   const float qnan = __int_as_float(0x7fc00000);
   const float delta = cut_delta(d);
+  const unsigned long long pol_keep = l2_policy_evict_last(), pol_done = l2_policy_evict_first();
+  (void)pol_keep; (void)pol_done;
   unsigned long long nhits = 0;
   const bool by_ulist = d.unit_list != nullptr && (long long)*d.unit_count * 4 < d.n_units;
   const int total = by_ulist ? *d.unit_count : d.n_units;
@@ -223,13 +259,18 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force_fast(Dev d, 
           if (w & kDpFlag) load_pos(d.pos, j, x, y, z);
         }
       };
-      float4 e0 = qcnt > 0 ? __ldcs(&gq[0]) : z4;
-      float4 e1 = qcnt > 1 ? __ldcs(&gq[32]) : z4;
+#if SWIFT_FIFO_POLICY
+#define FIFO_LD(ptr) ld_pol(ptr, pol_done)
+#else
+#define FIFO_LD(ptr) __ldcs(ptr)
+#endif
+      float4 e0 = qcnt > 0 ? FIFO_LD(&gq[0]) : z4;
+      float4 e1 = qcnt > 1 ? FIFO_LD(&gq[32]) : z4;
       float4 hb0 = z4, v0 = z4, f0 = z4;
       double x0 = 0.0, y0 = 0.0, z0 = 0.0;
       gather(e0, qcnt > 0, hb0, v0, f0, x0, y0, z0);
       for (int r = 0; r < m; r++) {
-        const float4 e2 = (r + 2 < qcnt) ? __ldcs(&gq[(r + 2) * 32]) : z4;
+        const float4 e2 = (r + 2 < qcnt) ? FIFO_LD(&gq[(r + 2) * 32]) : z4;
         float4 hb1 = z4, v1 = z4, f1 = z4;
         double x1 = 0.0, y1 = 0.0, z1 = 0.0;
         gather(e1, r + 1 < qcnt, hb1, v1, f1, x1, y1, z1);
@@ -297,7 +338,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force_fast(Dev d, 
       }
 
       auto test = [&](int st, int n) {
-        if (__any_sync(kFull, qcnt > kQD - n)) drain_all();
+        if (__any_sync(kFull, qcnt > qd - n)) drain_all();
         const float4 *__restrict__ tp = ws.pos + st;
         const int *__restrict__ ti = ws.idx + st;
         float4 *qp = gq + qcnt * 32;
@@ -311,7 +352,11 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force_fast(Dev d, 
             const float r2c = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
             // candidate's own radius counts only for lanes that take part (mine) and never for oneself
             const bool push = mine && r2c < fmaxf(thr_me, c.w) && j != pp;
+#if SWIFT_FIFO_POLICY
+            st_pred_pol(qp, dx, dy, dz, __int_as_float(j | flag), push, pol_keep);
+#else
             st_pred(qp, dx, dy, dz, __int_as_float(j | flag), push);
+#endif
             qp += push ? 32 : 0;
           }
         }

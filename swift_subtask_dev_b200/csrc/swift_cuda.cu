@@ -84,6 +84,7 @@ struct swift_cuda_ctx {
   int path = 8;                     // default: ghost redo sweeps from recorded neighbour lists (8).  Bit 5 (32): the
                                     // density walks as distance filters with the decision made at consumption --
                                     // bit-exact, measured 8 % SLOWER than the windowed test (spills), left off
+  int fast_qd = kQD;   // rows of the hit FIFO k_force_fast uses (SWIFT_CUDA_FAST_QD)
   int force_slow = 0;  // test hook (SWIFT_CUDA_SLOW=1): every hit takes the exact sorted-axis-cut path
 };
 
@@ -179,6 +180,7 @@ int swift_cuda_create(const swift_cuda_params *params, int device, swift_cuda_ct
   std::memset(&c->dev, 0, sizeof(Dev));
   if (const char *e = getenv("SWIFT_CUDA_PATH")) c->path = atoi(e);
   if (const char *e = getenv("SWIFT_CUDA_SLOW")) c->force_slow = atoi(e);
+  if (const char *e = getenv("SWIFT_CUDA_FAST_QD")) c->fast_qd = std::min(std::max(atoi(e), 40), kQD);
   if (create_resources(c)) {
     swift_cuda_destroy(c);  // releases whatever was created; the error text is kept
     return 1;
@@ -769,10 +771,10 @@ static int launch_force(swift_cuda_ctx *c) {
     const int nb = c->grid_force;
     const bool fast = c->prm.fields_mode == SWIFT_CUDA_FIELDS_FAST;
     if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY) {
-      if (fast) k_force_fast<SWIFT_CUDA_SCHEME_PLANETARY><<<nb, kBlock, 0, c->stream>>>(d, c->force_slow);
+      if (fast) k_force_fast<SWIFT_CUDA_SCHEME_PLANETARY><<<nb, kBlock, 0, c->stream>>>(d, c->force_slow, c->fast_qd);
       else k_force<SWIFT_CUDA_SCHEME_PLANETARY, false><<<nb, kBlock, 0, c->stream>>>(d);
     } else {
-      if (fast) k_force_fast<SWIFT_CUDA_SCHEME_MINIMAL><<<nb, kBlock, 0, c->stream>>>(d, c->force_slow);
+      if (fast) k_force_fast<SWIFT_CUDA_SCHEME_MINIMAL><<<nb, kBlock, 0, c->stream>>>(d, c->force_slow, c->fast_qd);
       else k_force<SWIFT_CUDA_SCHEME_MINIMAL, false><<<nb, kBlock, 0, c->stream>>>(d);
     }
   }
