@@ -702,7 +702,8 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
   // redo sweeps: while most particles are still flagged (the first sweeps) a warp takes a 32-particle
   // unit as the first pass does (5x more leaves in flight would not fit the L2); once the flagged
   // particles are few, a warp takes a whole leaf and compacts them into full groups of 32
-  const bool by_unit = MODE == 0 || (long long)d.walk_count[sweep] * 2 > d.n;
+  // (against the lanes that hold a particle of an active leaf, not d.n: a rank's halo copies are never flagged)
+  const bool by_unit = MODE == 0 || (long long)d.walk_count[sweep] * 2 > (long long)d.n_units * 27;
   // few leaves with a flagged particle: walk the list k_ghost pushed; otherwise all leaves in tree order
   // (spatially coherent, the unflagged ones are skipped after one look)
   const bool by_list = MODE == 1 && !by_unit && (long long)d.leaf_count[sweep] * 4 < d.n_leaves;

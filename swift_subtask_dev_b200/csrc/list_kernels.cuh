@@ -14,7 +14,7 @@
 
 namespace swiftcuda {
 
-__global__ void __launch_bounds__(kBlock) k_density_list(Dev d, int sweep) {
+__global__ void __launch_bounds__(kBlock) k_density_list(Dev d, int sweep, int force_slow) {
   if (d.redo_count[sweep] == 0) return;
   const int lane = threadIdx.x & 31;
   const int u = blockIdx.x * kWarps + (threadIdx.x >> 5);
@@ -29,7 +29,8 @@ __global__ void __launch_bounds__(kBlock) k_density_list(Dev d, int sweep) {
   const float hig2 = sq_gamma2(hi);
   const float hi_inv = 1.f / hi;
   const float hig = __fmul_rn(hi, kc.gamma);
-  const float r2safe = safe_r2(hig, cut_delta(d), false);
+  // force_slow (test hook): every hit counts as unsafe, i.e. every listed particle goes back to the walk
+  const float r2safe = safe_r2(hig, cut_delta(d), force_slow != 0);
   const float4 vmi = d.vm[pp];
   const int cnt = on ? (int)d.nl_cnt[ul] : 0;
   const float4 *__restrict__ nlp = d.nl + ((size_t)u * kLD) * 32 + lane;

@@ -748,7 +748,7 @@ static int launch_ghost(swift_cuda_ctx *c) {
       if (pending == 0) break;
     }
     if (d.nl && sweep > 0 && d.n_units > 0) {
-      k_density_list<<<(d.n_units + kWarps - 1) / kWarps, kBlock, 0, c->stream>>>(d, sweep);
+      k_density_list<<<(d.n_units + kWarps - 1) / kWarps, kBlock, 0, c->stream>>>(d, sweep, c->force_slow);
       c->counters.n_kernel_launches += 1;
     }
     if (d.n_leaves > 0) {

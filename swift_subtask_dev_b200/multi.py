@@ -220,7 +220,9 @@ class NcclTransport:
         return {src: o for src, o in enumerate(out) if o is not None and src != self.rank}
 
     def exchange(self, send, recv):
-        """send / recv: {peer: cuda uint8 tensor}.  Grouped point-to-point, no collective."""
+        """send / recv: {peer: cuda uint8 tensor}.  Grouped point-to-point, no collective.
+        The NCCL kernels order themselves with torch's CURRENT stream: call this under the stream the
+        pack / unpack kernels are launched on (RankState.stream)."""
         dist = self.dist
         ops = []
         for peer in sorted(set(send) | set(recv)):
@@ -265,6 +267,12 @@ class RankState:
             self.recv_idx[peer] = self._dev_index(self.slot_of[sel])
         self.send_idx = {}
         self.bufs = {}
+        # The halo stream: pack -> NCCL send/recv -> unpack are ordered on it.  It must not be torch's
+        # default stream: its handle is 0, which swift_cuda_halo_pack/unpack read as "the library's own
+        # (non-blocking) stream", and the kernels would then race with the NCCL transfers.
+        with torch.cuda.device(device):
+            self.stream = torch.cuda.Stream(device=device)
+        assert self.stream.cuda_stream != 0
 
     def _dev_index(self, slots):
         return self.torch.as_tensor(np.ascontiguousarray(slots, dtype=np.int32), device="cuda:%d" % self.device)
@@ -287,17 +295,17 @@ class RankState:
 
     def pack(self, phase):
         send, _ = self.buffers(phase)
-        st = self.torch.cuda.current_stream(self.device).cuda_stream
+        st = self.stream.cuda_stream
         for p, ix in self.send_idx.items():
             self.be.halo_pack(phase, ix.data_ptr(), len(ix), send[p].data_ptr(), st)
         return send
 
     def unpack(self, phase):
         _, recv = self.buffers(phase)
-        st = self.torch.cuda.current_stream(self.device).cuda_stream
+        st = self.stream.cuda_stream
         for p, ix in self.recv_idx.items():
             self.be.halo_unpack(phase, ix.data_ptr(), len(ix), recv[p].data_ptr(), st)
-        self.torch.cuda.current_stream(self.device).synchronize()
+        self.stream.synchronize()   # the library's stream reads the halo copies next
         self.be.refresh_cell_hmax(after_ghost=(phase == 1))
 
     def halo_bytes_per_step(self):
@@ -317,11 +325,12 @@ def step_ranks_local(states):
         for s in states:
             s.pack(phase)
         for s in states:
-            s.torch.cuda.current_stream(s.device).synchronize()
+            s.stream.synchronize()
         for s in states:
             _, recv = s.buffers(phase)
-            for peer, buf in recv.items():
-                buf.copy_(states[peer].buffers(phase)[0][s.rank])
+            with s.torch.cuda.stream(s.stream):
+                for peer, buf in recv.items():
+                    buf.copy_(states[peer].buffers(phase)[0][s.rank])
         for s in states:
             s.unpack(phase)
     for s in states:
@@ -369,7 +378,8 @@ def step_rank_nccl(state, transport, phase_ms=None):
     be.restore_particles()
     send = state.pack(0)
     _, recv = state.buffers(0)
-    transport.exchange(send, recv)
+    with state.torch.cuda.stream(state.stream):
+        transport.exchange(send, recv)
     state.unpack(0)
     lap("halo_xv")
     be.runner_do_hydro_sort()
@@ -380,29 +390,49 @@ def step_rank_nccl(state, transport, phase_ms=None):
     lap("ghost")
     send = state.pack(1)
     _, recv = state.buffers(1)
-    transport.exchange(send, recv)
+    with state.torch.cuda.stream(state.stream):
+        transport.exchange(send, recv)
     state.unpack(1)
     lap("halo_rho")
     be.runner_do_force()
     lap("force")
 
 
-def nccl_parity_check(tr, world, rank, local, per_cell=150, seed=11):
-    """A small uniform box split over the ranks and stepped through the SAME code the timed loop runs
-    (step_rank_nccl: halo pack, NCCL send/recv, unpack), against one context holding the whole box on
-    rank 0: every owned particle's results and the summed counters must be bit-identical.
+def nccl_parity_check(tr, world, rank, local, per_cell=150, seed=11, clustered=False):
+    """A small box split over the ranks and stepped through the SAME code the timed loop runs
+    (step_rank_nccl: halo pack, NCCL send/recv, unpack), TWICE (the second step starts from what the
+    first left in the halo copies), against one context holding the whole box on rank 0: every owned
+    particle's results and the summed counters must be bit-identical.  clustered: a clumpy box in
+    cost-weighted blocks (the shape of BASELINE configs[4]) instead of the uniform one.
     Role of the reference's tests/testHydroMPIrules.c + engine_maketasks.c:141-324 (send/recv xv, rho).
-    Returns "ok" or raises on every rank."""
+    Returns "ok ..." or raises on every rank."""
     import torch.distributed as dist
     grid = grid_for(world)
-    dim = tuple(float(g) for g in grid)
-    cdim = tuple(int(12 * d / max(dim)) for d in dim)
-    h0 = ics.ETA / (per_cell * np.prod(cdim) / np.prod(dim)) ** (1.0 / 3.0)
-    assert ics.top_grid(dim, h0) == cdim
-    part = Partition(cdim, grid, periodic=True)
-    st = RankState(rank, part, dim, per_cell, seed=seed, device=local)
+    if clustered:
+        dim = (1.0, 1.0, 1.0)
+        ic = ics.clustered(400000, nclumps=40, seed=seed)
+        ic["id"] = np.arange(1, len(ic["h"]) + 1, dtype=np.int64)
+        cdim = ics.top_grid(dim, float(ic["h"].max()))
+        weights = np.bincount(top_cell_of(ic["x"], cdim, dim), minlength=int(np.prod(cdim)))
+        part = Partition(cdim, grid, periodic=True, weights=weights)
+        st = RankState(rank, part, dim, 0, device=local, ic=local_particles_from(ic, part, rank, dim))
+    else:
+        dim = tuple(float(g) for g in grid)
+        cdim = tuple(int(12 * d / max(dim)) for d in dim)
+        h0 = ics.ETA / (per_cell * np.prod(cdim) / np.prod(dim)) ** (1.0 / 3.0)
+        assert ics.top_grid(dim, h0) == cdim
+        part = Partition(cdim, grid, periodic=True)
+        st = RankState(rank, part, dim, per_cell, seed=seed, device=local)
+        ic = None
     st.set_send_lists(tr.all_to_all_objects({p: ids for p, ids in st.recv_ids.items()}))
-    step_rank_nccl(st, tr)
+    for _ in range(2):
+        # poison the receive buffers: a pack / transfer / unpack ordering bug then shows as NaNs
+        # instead of hiding behind what the previous step left there
+        for phase in (0, 1):
+            with st.torch.cuda.stream(st.stream):
+                for buf in st.buffers(phase)[1].values():
+                    buf.fill_(255)
+        step_rank_nccl(st, tr)
     mine = st.owned_results()
     cnt = st.be.counters()
     mine["_counts"] = (cnt["n_density"], cnt["n_density_redo"], cnt["n_force"])
@@ -410,8 +440,11 @@ def nccl_parity_check(tr, world, rank, local, per_cell=150, seed=11):
     gathered = [None] * world if rank == 0 else None
     dist.gather_object(mine, gathered, dst=0, group=tr.setup_group)
     verdict = ["ok"]
+    npart = 0
     if rank == 0:
-        ic = ics.cell_block_random(np.arange(int(np.prod(cdim))), cdim, dim, per_cell, seed=seed)
+        if ic is None:
+            ic = ics.cell_block_random(np.arange(int(np.prod(cdim))), cdim, dim, per_cell, seed=seed)
+        npart = len(ic["h"])
         be = HydroBackend(make_params(dim=dim, periodic=True), device=local)
         be.build(ic)
         be.step()
@@ -421,21 +454,21 @@ def nccl_parity_check(tr, world, rank, local, per_cell=150, seed=11):
         tot = np.zeros(3, dtype=np.int64)
         nchecked = 0
         for r, res in enumerate(gathered):
-            idx = np.array([pos[int(v)] for v in res["id"]])
+            idx = np.array([pos[int(v)] for v in res["id"]], dtype=np.int64)
             nchecked += len(idx)
             for k in ref:
-                if not np.array_equal(res[k], ref[k][idx]):
+                if len(idx) and not np.array_equal(res[k], ref[k][idx]):
                     verdict[0] = "rank %d: field %s differs from the single-GPU run" % (r, k)
             tot += np.array(res["_counts"], dtype=np.int64)
-        if nchecked != len(ic["h"]):
-            verdict[0] = "owned particles of all ranks: %d, box: %d" % (nchecked, len(ic["h"]))
+        if nchecked != npart:
+            verdict[0] = "owned particles of all ranks: %d, box: %d" % (nchecked, npart)
         if tuple(tot) != (cref["n_density"], cref["n_density_redo"], cref["n_force"]):
             verdict[0] = "interaction counters differ: %s vs %s" % (tuple(tot), cref)
     dist.broadcast_object_list(verdict, src=0, group=tr.setup_group)
     if verdict[0] != "ok":
         raise RuntimeError("NCCL path parity check failed: " + verdict[0])
-    return "ok (%d ranks, %d particles, every owned field and the counters bit-identical to one GPU)" % (
-        world, per_cell * int(np.prod(cdim)))
+    return "ok (%d ranks, %s box, two steps, every owned field and the counters bit-identical to one GPU)" % (
+        world, "clustered" if clustered else "uniform")
 
 
 def bench_multi(args, cfg, metric, unit, sampler_cls=None):
@@ -454,6 +487,8 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
     tr = NcclTransport()
     # correctness of the timed path first: the same halo code on a small box, against one GPU
     nccl_parity = nccl_parity_check(tr, world, rank, local)
+    if getattr(args, "workload", "uniform") == "clustered":
+        nccl_parity += "; " + nccl_parity_check(tr, world, rank, local, clustered=True)
     grid = grid_for(world)
     side = args.side
     clustered = getattr(args, "workload", "uniform") == "clustered"

@@ -107,3 +107,33 @@ def test_stale_work_lists_are_refused():
     b.build(grown)
     b.step()
     b.close()
+
+
+@pytest.mark.gpu
+def test_max_active_bin_can_change_between_steps():
+    """Individual time steps through the struct part entries: the work lists hold every cell, which
+    particles are active is e->max_active_bin of the step (swift_cuda_set_max_active_bin)."""
+    ic = ics.clustered(30000, nclumps=6, seed=14)
+    rng = np.random.default_rng(2)
+    ic["time_bin"] = rng.integers(1, 5, size=len(ic["h"])).astype(np.int8)
+    parts0 = be.parts_from_ic(ic)
+    for k in ("rho", "pressure", "soundspeed"):
+        parts0[k] = 1.0
+
+    def run(build_bin, step_bin):
+        parts = parts0.copy()
+        b = HydroBackend(make_params(periodic=True, max_active_bin=build_bin))
+        b.build_from_parts(parts)
+        if step_bin != build_bin:
+            b.set_max_active_bin(step_bin)
+        b.step_parts(parts)
+        c = b.counters()
+        b.close()
+        return parts, c
+    a, ca = run(2, 2)
+    bb, cb = run(56, 2)      # built for everything, stepped with bin 2
+    for k in ("h", "rho", "a_hydro", "u_dt", "h_dt", "v_sig", "min_ngb_time_bin"):
+        assert np.array_equal(a[k], bb[k]), k
+    assert ca["n_force"] == cb["n_force"] and ca["n_density_redo"] == cb["n_density_redo"]
+    act = parts0["time_bin"] <= 2
+    assert (a["a_hydro"][~act] == 0).all() and (np.abs(a["a_hydro"][act]).sum() > 0)
