@@ -367,6 +367,40 @@ int swift_cuda_get_state(swift_cuda_ctx *ctx, const swift_cuda_state_out *out);
 /* Device time (CUDA events on the context's stream) of the last drift, kick1, kick2, timestep, ms. */
 int swift_cuda_get_integrator_timings(swift_cuda_ctx *ctx, float ms[4]);
 
+/* ---- Allocation-free time-step entry ----------------------------------------------------------
+ * No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * runner_do_timestep (the arithmetic of swift_cuda_timestep / k_timestep) on arrays the CALLER owns,
+ * without a context: no cudaMalloc, cudaFree or allocating library routine is called.  The kernel's
+ * reduction scratch (one 16-byte partial per 256-particle block + a 256-byte header: 1 048 832 bytes)
+ * is a file-scope `static __device__` array of the library; every GPU that loads the library holds it
+ * until exit.  Hence the limit: count <= SWIFT_CUDA_TIMESTEP_STATIC_MAX (65 536 blocks x 256), more is
+ * rejected with an error.  Every call on a device shares that array: calls that overlap on the same
+ * GPU (two streams, two host threads) race; serialise them.
+ *
+ * device: the GPU the arrays live on; it is made current (cudaSetDevice).  All array pointers are
+ * DEVICE pointers of that GPU (checked with cudaPointerGetAttributes).  time_bin is read and written
+ * in place: bins of particles with time_bin <= max_active_bin are replaced by their new bin, the
+ * others are left alone (and count towards ti_end_min with the end of their current step).
+ * stream: a cudaStream_t of that device, NULL = the CUDA default stream.  The call returns after the
+ * stream has been synchronised, with *ti_end_min / *updated as swift_cuda_timestep gives them
+ * (either may be NULL); it fails, like swift_cuda_timestep, when a particle wants a step below dt_min. */
+#define SWIFT_CUDA_TIMESTEP_STATIC_MAX 16777216LL
+typedef struct {
+  int64_t count;
+  const float *h;                   /* [count] p->h */
+  const float *v_sig;               /* [count] p->force.v_sig */
+  const float *h_dt;                /* [count] p->force.h_dt */
+  const int8_t *min_ngb_time_bin;   /* [count] p->limiter_data.min_ngb_time_bin */
+  int8_t *time_bin;                 /* [count] p->time_bin, in and out */
+  long long ti_current;             /* e->ti_current */
+  int max_active_bin;               /* e->max_active_bin */
+  swift_cuda_integrator integ;      /* CFL, log_max_h_change, dt_min, dt_max, time_base */
+} swift_cuda_timestep_static_args;
+int swift_cuda_timestep_static(int device, const swift_cuda_timestep_static_args *args, long long *ti_end_min,
+                               long long *updated, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -103,6 +103,16 @@ class Integrator(C.Structure):
                 ("dt_min", C.c_double), ("dt_max", C.c_double), ("time_base", C.c_double)]
 
 
+class TimestepStaticArgs(C.Structure):
+    # field order must match swift_cuda_timestep_static_args
+    _fields_ = [("count", C.c_int64), ("h", C.c_void_p), ("v_sig", C.c_void_p), ("h_dt", C.c_void_p),
+                ("min_ngb_time_bin", C.c_void_p), ("time_bin", C.c_void_p), ("ti_current", C.c_longlong),
+                ("max_active_bin", C.c_int), ("integ", Integrator)]
+
+
+TIMESTEP_STATIC_MAX = 16777216   # SWIFT_CUDA_TIMESTEP_STATIC_MAX
+
+
 STATE_FIELDS = [("x", 3), ("v", 3), ("v_full", 3), ("u", 1), ("u_full", 1), ("h", 1), ("rho", 1), ("pressure", 1),
                 ("soundspeed", 1), ("v_sig", 1), ("a", 3), ("u_dt", 1), ("h_dt", 1), ("x_diff", 3), ("x_diff_sort", 3)]
 
@@ -127,7 +137,7 @@ EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error
            "swift_cuda_timestep", "swift_cuda_reset_offsets", "swift_cuda_get_state",
            "swift_cuda_get_integrator_timings",
            "swift_cuda_build_from_cells_parts", "swift_cuda_build_from_parts", "swift_cuda_step_parts",
-           "swift_cuda_set_max_active_bin"]
+           "swift_cuda_set_max_active_bin", "swift_cuda_timestep_static"]
 
 
 class PartLayout(C.Structure):
@@ -216,12 +226,26 @@ def load_library():
         lib.swift_cuda_kick.argtypes = [C.c_void_p, C.c_int]
         lib.swift_cuda_timestep.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         lib.swift_cuda_reset_offsets.argtypes = [C.c_void_p, C.c_int]
+        lib.swift_cuda_timestep_static.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = lib
     return _lib
 
 
 class SwiftCudaError(RuntimeError):
     pass
+
+
+def timestep_static(device, count, h, v_sig, h_dt, min_ngb_time_bin, time_bin, ti_current, max_active_bin, integ,
+                    stream=None):
+    """swift_cuda_timestep_static: runner_do_timestep on DEVICE arrays the caller owns (raw device pointers as
+    ints), with the library's static scratch array: nothing is allocated.  integ: an Integrator.
+    Returns (ti_end_min, updated); time_bin is updated in place."""
+    lib = load_library()
+    a = TimestepStaticArgs(count, h, v_sig, h_dt, min_ngb_time_bin, time_bin, ti_current, max_active_bin, integ)
+    t, u = C.c_longlong(0), C.c_longlong(0)
+    if lib.swift_cuda_timestep_static(device, C.byref(a), C.byref(t), C.byref(u), stream):
+        raise SwiftCudaError(lib.swift_cuda_last_error().decode())
+    return t.value, u.value
 
 
 def host_plan(params, ic):

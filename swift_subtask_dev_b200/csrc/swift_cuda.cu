@@ -1577,3 +1577,215 @@ int swift_cuda_get_state(swift_cuda_ctx *c, const swift_cuda_state_out *o) {
 }
 
 }  // extern "C"
+
+// ---- allocation-free time-step entry (include/swift_cuda.h: swift_cuda_timestep_static) --------------
+// No counterpart in the reference.  The arithmetic of
+// k_timestep (integrate.cuh; runner_do_timestep, src/runner_time_integration.c:637-1000, get_part_timestep
+// and make_integer_timestep, src/timestep.h:45-82, 141-222) on the caller's arrays, with a two-level
+// reduction whose scratch lives in a file-scope device array instead of a cudaMalloc'ed buffer.
+#include <mutex>
+
+namespace swiftcuda {
+constexpr int kTsBlock = 256;
+constexpr int kTsMaxBlocks = 65536;
+static_assert((long long)kTsBlock * kTsMaxBlocks == SWIFT_CUDA_TIMESTEP_STATIC_MAX, "header and kernel disagree");
+struct TsPartial {  // one per block
+  unsigned long long ti_end_min;
+  unsigned updated, too_small;
+};
+struct TsHeader {  // the first 256 bytes of the scratch: zeroed before every launch
+  unsigned long long ti_end_min, updated;
+  unsigned too_small, ticket;
+};
+constexpr size_t kTsHeaderBytes = 256;
+constexpr size_t kTsScratchBytes = kTsHeaderBytes + sizeof(TsPartial) * (size_t)kTsMaxBlocks;  // 1 048 832
+// In HOST code this name is a stand-in, not a device address: the entry below asks the runtime for the
+// address (cudaGetSymbolAddress, once per device) and hands that to the kernel.
+static __device__ __align__(256) unsigned char g_ts_scratch[kTsScratchBytes];
+
+struct TsArgs {
+  int64_t n;
+  const float *h, *v_sig, *h_dt;
+  const int8_t *min_bin;
+  int8_t *time_bin;
+  long long ti_current;
+  int max_active_bin;
+  float gamma, cfl, log_max_h_change;
+  double dt_min, dt_max, time_base_inv;
+};
+
+__global__ void __launch_bounds__(kTsBlock) k_timestep_static(TsArgs a, unsigned char *scratch) {
+  TsHeader *const hdr = reinterpret_cast<TsHeader *>(scratch);
+  TsPartial *const part = reinterpret_cast<TsPartial *>(scratch + kTsHeaderBytes);
+  const int64_t p = blockIdx.x * (int64_t)kTsBlock + threadIdx.x;
+  unsigned long long t_end = (unsigned long long)kMaxNrTimesteps;
+  unsigned upd = 0, small = 0;
+  if (p < a.n) {
+    const int old_bin = a.time_bin[p];
+    if (old_bin > a.max_active_bin) {
+      t_end = (unsigned long long)int_time_end(a.ti_current, old_bin);
+    } else {
+      const float h = a.h[p];
+      const float front = __fmul_rn(__fmul_rn(2.f, a.gamma), a.cfl);
+      const float dt_cfl = (float)__ddiv_rn(__dmul_rn((double)front, (double)h), (double)a.v_sig[p]);
+      const float h_dt = a.h_dt[p];
+      const float dt_h_change = (h_dt != 0.0f) ? fabsf(__fmul_rn(a.log_max_h_change, h) / h_dt) : 3.402823466e+38f;
+      float new_dt = dt_cfl < dt_h_change ? dt_cfl : dt_h_change;
+      new_dt = (double)new_dt < a.dt_max ? new_dt : (float)a.dt_max;
+      if ((double)new_dt < a.dt_min) small = 1;
+      long long new_dti = (long long)__dmul_rn((double)new_dt, a.time_base_inv);
+      int new_bin = (signed char)time_bin_of(new_dti);
+      const int ngb = (int)a.min_bin[p] + kMaxDeltaBin;
+      new_bin = (signed char)(new_bin < ngb ? new_bin : ngb);
+      new_dti = int_timestep(new_bin);
+      const long long current_dti = int_timestep(old_bin);
+      const long long ti_end = int_time_end(a.ti_current, old_bin);
+      if (old_bin > 0) new_dti = new_dti < 2 * current_dti ? new_dti : 2 * current_dti;
+      long long dti_timeline = kMaxNrTimesteps;
+      while (new_dti < dti_timeline) dti_timeline /= 2LL;
+      new_dti = dti_timeline;
+      if (new_dti > current_dti) {
+        if ((kMaxNrTimesteps - ti_end) % new_dti > 0) new_dti = current_dti;
+      }
+      a.time_bin[p] = (int8_t)time_bin_of(new_dti);
+      upd = 1;
+      t_end = (unsigned long long)(a.ti_current + new_dti);
+    }
+  }
+  // level 1: the block's minimum and counts -> its slot of the scratch
+  __shared__ unsigned long long s_t[kTsBlock / 32];
+  __shared__ unsigned s_u[kTsBlock / 32], s_s[kTsBlock / 32];
+  __shared__ bool s_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long other = __shfl_xor_sync(0xffffffffu, t_end, o);
+    t_end = other < t_end ? other : t_end;
+  }
+  upd = __popc(__ballot_sync(0xffffffffu, upd));
+  small = __popc(__ballot_sync(0xffffffffu, small));
+  if (lane == 0) { s_t[warp] = t_end; s_u[warp] = upd; s_s[warp] = small; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    TsPartial r = {s_t[0], s_u[0], s_s[0]};
+    for (int w = 1; w < kTsBlock / 32; w++) {
+      r.ti_end_min = s_t[w] < r.ti_end_min ? s_t[w] : r.ti_end_min;
+      r.updated += s_u[w];
+      r.too_small += s_s[w];
+    }
+    part[blockIdx.x] = r;
+    __threadfence();  // the slot is visible before the ticket is taken
+    s_last = atomicAdd(&hdr->ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  // level 2: the last block to finish folds the slots of all blocks
+  __threadfence();
+  unsigned long long tmin = (unsigned long long)kMaxNrTimesteps, nu = 0;
+  unsigned ns = 0;
+  for (unsigned b = threadIdx.x; b < gridDim.x; b += kTsBlock) {
+    const volatile TsPartial *q = part + b;
+    const unsigned long long t = q->ti_end_min;
+    tmin = t < tmin ? t : tmin;
+    nu += q->updated;
+    ns += q->too_small;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long other = __shfl_xor_sync(0xffffffffu, tmin, o);
+    tmin = other < tmin ? other : tmin;
+    nu += __shfl_xor_sync(0xffffffffu, nu, o);
+    ns += __shfl_xor_sync(0xffffffffu, ns, o);
+  }
+  __shared__ unsigned long long s_n[kTsBlock / 32];
+  if (lane == 0) { s_t[warp] = tmin; s_n[warp] = nu; s_s[warp] = ns; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < kTsBlock / 32; w++) {
+      tmin = s_t[w] < tmin ? s_t[w] : tmin;
+      nu += s_n[w];
+      ns += s_s[w];
+    }
+    hdr->ti_end_min = tmin;
+    hdr->updated = nu;
+    hdr->too_small = ns;
+    hdr->ticket = 0;
+  }
+}
+}  // namespace swiftcuda
+
+// Device address of g_ts_scratch, resolved once per device with that device current.
+static std::mutex g_ts_mu;
+static unsigned char *g_ts_ptr[64] = {};
+static int ts_scratch_of(int device, unsigned char **out) {
+  std::lock_guard<std::mutex> lock(g_ts_mu);
+  if (g_ts_ptr[device] == nullptr) {
+    void *p = nullptr;
+    CK(cudaGetSymbolAddress(&p, swiftcuda::g_ts_scratch));
+    if (p == nullptr) return fail("timestep_static: cudaGetSymbolAddress gave a null address");
+    g_ts_ptr[device] = static_cast<unsigned char *>(p);
+  }
+  *out = g_ts_ptr[device];
+  return 0;
+}
+static int ts_check_ptr(const void *p, const char *name, int device) {
+  if (p == nullptr) return fail(std::string("timestep_static: ") + name + " is null");
+  cudaPointerAttributes at;
+  CK(cudaPointerGetAttributes(&at, p));
+  if ((at.type != cudaMemoryTypeDevice && at.type != cudaMemoryTypeManaged) || (at.type == cudaMemoryTypeDevice && at.device != device))
+    return fail(std::string("timestep_static: ") + name + " is not a device pointer of GPU " + std::to_string(device));
+  return 0;
+}
+
+extern "C" int swift_cuda_timestep_static(int device, const swift_cuda_timestep_static_args *a, long long *ti_end_min,
+                                          long long *updated, void *stream) {
+  using namespace swiftcuda;
+  if (!a) return fail("timestep_static: null argument");
+  if (a->count < 0) return fail("timestep_static: negative count");
+  if (a->count > SWIFT_CUDA_TIMESTEP_STATIC_MAX)
+    return fail("timestep_static: count " + std::to_string((long long)a->count) + " exceeds the " +
+                std::to_string((long long)SWIFT_CUDA_TIMESTEP_STATIC_MAX) +
+                " particles the library's static scratch array (" + std::to_string(kTsScratchBytes) +
+                " bytes) covers; use swift_cuda_timestep on a context, or split the call");
+  if (!(a->integ.time_base > 0.0)) return fail("timestep_static: time_base must be positive");
+  if (device < 0 || device >= 64) return fail("timestep_static: device out of range");
+  CK(cudaSetDevice(device));
+  unsigned long long t = (unsigned long long)kMaxNrTimesteps, u = 0;
+  if (a->count > 0) {
+    if (ts_check_ptr(a->h, "h", device) || ts_check_ptr(a->v_sig, "v_sig", device) ||
+        ts_check_ptr(a->h_dt, "h_dt", device) || ts_check_ptr(a->min_ngb_time_bin, "min_ngb_time_bin", device) ||
+        ts_check_ptr(a->time_bin, "time_bin", device))
+      return 1;
+    unsigned char *scratch = nullptr;
+    if (ts_scratch_of(device, &scratch)) return 1;
+    cudaStream_t s = (cudaStream_t)stream;
+    TsArgs k;
+    k.n = a->count;
+    k.h = a->h; k.v_sig = a->v_sig; k.h_dt = a->h_dt;
+    k.min_bin = a->min_ngb_time_bin;
+    k.time_bin = a->time_bin;
+    k.ti_current = a->ti_current;
+    k.max_active_bin = a->max_active_bin;
+    k.gamma = (float)(1.825742);  // kernel_gamma, as upload_consts
+    k.cfl = a->integ.cfl_condition;
+    k.log_max_h_change = a->integ.log_max_h_change;
+    k.dt_min = a->integ.dt_min;
+    k.dt_max = a->integ.dt_max;
+    k.time_base_inv = 1.0 / a->integ.time_base;
+    // the array keeps what the last call left: the header (results, ticket) must start at zero
+    CK(cudaMemsetAsync(scratch, 0, kTsHeaderBytes, s));
+    const int nb = (int)((a->count + kTsBlock - 1) / kTsBlock);
+    k_timestep_static<<<nb, kTsBlock, 0, s>>>(k, scratch);
+    CK(cudaGetLastError());
+    TsHeader hdr;
+    CK(cudaMemcpyAsync(&hdr, scratch, sizeof(hdr), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    if (hdr.ticket != 0) return fail("timestep_static: the reduction did not complete (overlapping calls share the scratch)");
+    t = hdr.ti_end_min;
+    u = hdr.updated;
+    if (hdr.too_small > 0)
+      return fail(std::to_string(hdr.too_small) + " particle(s) want a time-step below dt_min (" +
+                  std::to_string(a->integ.dt_min) + ")");
+  }
+  if (ti_end_min) *ti_end_min = (long long)t;
+  if (updated) *updated = (long long)u;
+  return 0;
+}
