@@ -57,6 +57,7 @@ struct Dev {
   int ncells;
   int n_leaves;
   int n_units;
+  int unit_lo, unit_hi;   // force loop: walk the units [unit_lo, unit_hi) only (unit_hi == 0: all of them)
   double dim[3];
   // particles, cell order
   const PosD *pos;     // x, y, z f64 in one 32-byte record: a gather touches ONE sector

@@ -144,11 +144,12 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force_fast(Dev d, 
   (void)pol_keep; (void)pol_done;
   unsigned long long nhits = 0;
   const bool by_ulist = d.unit_list != nullptr && (long long)*d.unit_count * 4 < d.n_units;
-  const int total = by_ulist ? *d.unit_count : d.n_units;
+  const int total = by_ulist ? *d.unit_count : (d.unit_hi > 0 ? d.unit_hi : d.n_units);
+  const int wid0 = by_ulist ? 0 : d.unit_lo;
 
   while (true) {
     int wid = 0;
-    if (lane == 0) wid = atomicAdd(work, 1);
+    if (lane == 0) wid = atomicAdd(work, 1) + wid0;
     wid = __shfl_sync(kFull, wid, 0);
     if (wid >= total) break;
     if (by_ulist) wid = d.unit_list[wid];

@@ -638,9 +638,18 @@ void build_worklists(const swift_cuda_params &prm, const Tree &tree, const std::
   wl.redo_begin.push_back(0);
   std::vector<const std::vector<SeqItem> *> chain;
   std::vector<SeqItem> merged;
+  // leaves in the order of their particles (`first`): walking the units in order then walks the particle
+  // arrays in order, and a range of units is a range of records (swift_cuda_step_parts hands the force
+  // results back in such ranges)
+  std::vector<int32_t> visit;
   for (size_t c = 0; c < nc; c++) {
     const swift_cuda_cell &cell = tree.cells[c];
-    if (cell.split || cell.count == 0 || !cell_active[c]) continue;
+    if (!(cell.split || cell.count == 0 || !cell_active[c])) visit.push_back((int32_t)c);
+  }
+  std::stable_sort(visit.begin(), visit.end(),
+                   [&](int32_t a, int32_t b) { return tree.cells[a].first < tree.cells[b].first; });
+  for (const int32_t c : visit) {
+    const swift_cuda_cell &cell = tree.cells[c];
     // every interaction that updates this leaf's particles: its own and its ancestors', in execution order
     chain.clear();
     for (int a = (int)c; a >= 0; a = tree.cells[a].parent)

@@ -181,10 +181,12 @@ __global__ void k_pack_aos(int64_t n, const unsigned char *aos, swift_cuda_part_
 }
 
 // what: last phase that ran -- 2 density (raw sums), 4 ghost, 8 force (16 with the ghost's fields too)
+// [lo, hi): the cell-order slots written by this launch (the force loop of swift_cuda_step_parts hands its
+// results back in pieces so that the copy of one piece overlaps the loop over the next)
 __global__ void k_unpack_aos(Dev d, unsigned char *aos, swift_cuda_part_layout L, const int32_t *order, int what,
-                             int max_active_bin) {
-  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (k >= d.n) return;
+                             int max_active_bin, int64_t lo, int64_t hi) {
+  const int64_t k = lo + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= hi) return;
   if (d.time_bin[k] > max_active_bin) return;  // the reference's operators update active particles only
   const int64_t s = order ? order[k] : k;
   unsigned char *r = aos + (size_t)s * L.stride;

@@ -77,6 +77,11 @@ struct swift_cuda_ctx {
   // swift_cuda_step_parts: the caller's AoS records
   swift_cuda_part_layout lay = {};
   bool has_lay = false;
+  // swift_cuda_step_parts hands the force loop's results back in `pieces` pieces (units of consecutive leaves
+  // = consecutive records) when the caller's records are in cell order, as s->parts is after space_rebuild
+  bool records_in_cell_order = false;
+  int pieces = 8;
+  std::vector<cudaEvent_t> piece_ev;
   unsigned char *d_aos = nullptr;
   bool no_prune = false;            // build the work lists with every cell, whatever the time bins
   std::vector<int32_t> slot_of;     // host copy of Dev::part_slot (caller order)
@@ -198,6 +203,7 @@ void swift_cuda_destroy(swift_cuda_ctx *c) {
   if (c->stream) cudaStreamDestroy(c->stream);
   for (auto &e : c->io_ev)
     if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : c->piece_ev) cudaEventDestroy(e);
   if (c->io) cudaStreamDestroy(c->io);
   delete c;
 }
@@ -1066,6 +1072,14 @@ static int check_layout(const swift_cuda_part_layout *L) {
 static int finish_parts_build(swift_cuda_ctx *c, const swift_cuda_part_layout *L) {
   c->lay = *L;
   c->has_lay = true;
+  // records in cell order (always so through the cells entry: a cell's `first` indexes the caller's array)
+  // and leaves in the order of their records?
+  bool ident = true;
+  for (size_t k = 0; k < c->tree.order.size() && ident; k++) ident = c->tree.order[k] == (int32_t)k;
+  for (size_t sl = 1; sl < c->wl.leaves.size() && ident; sl++)
+    ident = c->tree.cells[c->wl.leaves[sl]].first >= c->tree.cells[c->wl.leaves[sl - 1]].first;
+  c->records_in_cell_order = ident;
+  if (const char *e = getenv("SWIFT_CUDA_PIECES")) c->pieces = std::max(1, atoi(e));
   return dmalloc(c, &c->d_aos, (size_t)std::max<int64_t>(c->n, 1) * L->stride);
 }
 
@@ -1133,7 +1147,7 @@ int swift_cuda_step_parts(swift_cuda_ctx *c, void *parts, int phases) {
   o.id = const_cast<int64_t *>(d.id);
   AosDst a;
   a.dens0 = d.dens0; a.dens1 = d.dens1; a.acc = d.acc; a.h_dt = d.h_dt; a.v_sig = d.v_sig; a.min_bin = d.min_bin;
-  const int32_t *order = c->tree.order.empty() ? nullptr : c->s_order;
+  const int32_t *order = (c->tree.order.empty() || c->records_in_cell_order) ? nullptr : c->s_order;
   const unsigned nb = (unsigned)((n + 255) / 256);
   const int load_force = (!do_dens && !do_ghost) ? 1 : 0;
   if (n > 0) k_pack_aos<<<nb, 256, 0, c->stream>>>(n, c->d_aos, L, order, o, a, 0, keep ? 1 : 0, load_force);
@@ -1156,21 +1170,67 @@ int swift_cuda_step_parts(swift_cuda_ctx *c, void *parts, int phases) {
   CK(cudaEventRecord(c->ev[2], c->stream));
   if (do_ghost && launch_ghost(c)) return 1;
   CK(cudaEventRecord(c->ev[3], c->stream));
-  if (do_force) {
-    if (launch_force(c)) return 1;
-  } else if (do_end && n > 0) {
-    k_end_force<<<nb, 256, 0, c->stream>>>(d);
-    c->counters.n_kernel_launches += 1;
-  }
-  CK(cudaEventRecord(c->ev[4], c->stream));
-  d.keep_sums = 0;
-  d.no_end_force = 0;
   const int what = (do_force || do_end) ? (do_ghost ? 16 : 8) : (do_ghost ? 4 : (do_dens ? 2 : 0));
-  if (what && n > 0) {
-    k_unpack_aos<<<nb, 256, 0, c->stream>>>(d, c->d_aos, L, order, what, c->prm.max_active_bin);
-    c->counters.n_kernel_launches += 1;
-    CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(parts, c->d_aos, (size_t)n * L.stride, cudaMemcpyDeviceToHost, c->stream));
+  const WorkLists &wl = c->wl;
+  const int P = c->pieces;
+  const bool in_pieces = do_force && P > 1 && c->records_in_cell_order && n >= (1 << 18) && d.n_units >= 64 * P &&
+                         (int64_t)wl.unit_begin.size() == (int64_t)wl.leaves.size() + 1;
+  if (in_pieces) {
+    // The force loop over the units of consecutive leaves, piece by piece: the records of a finished piece
+    // are written back and copied to the host (copy stream) while the loop runs over the next piece.
+    while ((int)c->piece_ev.size() < P) {
+      cudaEvent_t e;
+      CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      c->piece_ev.push_back(e);
+    }
+    const int nl = (int)wl.leaves.size();
+    int s_prev = 0;
+    int64_t p_prev = 0;
+    for (int k = 0; k < P; k++) {
+      int s_next = nl;
+      if (k < P - 1) {
+        const int32_t want = (int32_t)((int64_t)d.n_units * (k + 1) / P);
+        s_next = (int)(std::lower_bound(wl.unit_begin.begin(), wl.unit_begin.begin() + nl, want) - wl.unit_begin.begin());
+        s_next = std::max(s_next, s_prev);
+      }
+      const int64_t p_next = s_next < nl ? (int64_t)c->tree.cells[wl.leaves[s_next]].first : n;
+      d.unit_lo = wl.unit_begin[s_prev];
+      d.unit_hi = wl.unit_begin[s_next];
+      if (d.unit_hi > d.unit_lo && launch_force(c)) return 1;
+      if (k == P - 1) CK(cudaEventRecord(c->ev[4], c->stream));
+      if (p_next > p_prev) {
+        const unsigned nbp = (unsigned)((p_next - p_prev + 255) / 256);
+        k_unpack_aos<<<nbp, 256, 0, c->stream>>>(d, c->d_aos, L, nullptr, what, c->prm.max_active_bin, p_prev, p_next);
+        c->counters.n_kernel_launches += 1;
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(c->piece_ev[k], c->stream));
+        CK(cudaStreamWaitEvent(c->io, c->piece_ev[k], 0));
+        CK(cudaMemcpyAsync((unsigned char *)parts + (size_t)p_prev * L.stride, c->d_aos + (size_t)p_prev * L.stride,
+                           (size_t)(p_next - p_prev) * L.stride, cudaMemcpyDeviceToHost, c->io));
+      }
+      s_prev = s_next;
+      p_prev = p_next;
+    }
+    d.unit_lo = d.unit_hi = 0;
+    d.keep_sums = 0;
+    d.no_end_force = 0;
+    CK(cudaStreamSynchronize(c->io));
+  } else {
+    if (do_force) {
+      if (launch_force(c)) return 1;
+    } else if (do_end && n > 0) {
+      k_end_force<<<nb, 256, 0, c->stream>>>(d);
+      c->counters.n_kernel_launches += 1;
+    }
+    CK(cudaEventRecord(c->ev[4], c->stream));
+    d.keep_sums = 0;
+    d.no_end_force = 0;
+    if (what && n > 0) {
+      k_unpack_aos<<<nb, 256, 0, c->stream>>>(d, c->d_aos, L, order, what, c->prm.max_active_bin, 0, n);
+      c->counters.n_kernel_launches += 1;
+      CK(cudaGetLastError());
+      CK(cudaMemcpyAsync(parts, c->d_aos, (size_t)n * L.stride, cudaMemcpyDeviceToHost, c->stream));
+    }
   }
   if (finish_counters(c)) return 1;
   CK(cudaEventElapsedTime(&c->timings.sort_ms, c->ev[0], c->ev[1]));

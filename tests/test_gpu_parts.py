@@ -137,3 +137,43 @@ def test_max_active_bin_can_change_between_steps():
     assert ca["n_force"] == cb["n_force"] and ca["n_density_redo"] == cb["n_density_redo"]
     act = parts0["time_bin"] <= 2
     assert (a["a_hydro"][~act] == 0).all() and (np.abs(a["a_hydro"][act]).sum() > 0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fields_mode", [0, 1])
+def test_records_in_cell_order_come_back_in_pieces(fields_mode, monkeypatch):
+    """s->parts after space_rebuild: every cell's records contiguous.  swift_cuda_step_parts then runs the force
+    loop over pieces of consecutive leaves and copies each finished piece back while the next one runs: the
+    same bits as the one-piece path and as the records in arbitrary order."""
+    ic = ics.clustered(300000, nclumps=30, seed=12)
+    kw = dict(periodic=True, fields_mode=fields_mode)
+    order = be.host_plan(make_params(**kw), ic)["order"]
+    ics_sorted = ics.permute(ic, order)
+    out = {}
+    for name, src, pieces in (("shuffled", ic, "8"), ("sorted_1", ics_sorted, "1"), ("sorted_8", ics_sorted, "8"),
+                              ("sorted_5", ics_sorted, "5")):
+        monkeypatch.setenv("SWIFT_CUDA_PIECES", pieces)
+        parts = be.parts_from_ic(src, pinned=(name == "sorted_8"))
+        b = HydroBackend(make_params(**kw))
+        b.build_from_parts(parts)
+        b.step_parts(parts)
+        parts["h"] = src["h"]
+        b.step_parts(parts)            # a second step: the pieces' events and the copy stream are reused
+        out[name] = (np.array(parts, copy=True), b.counters())
+        b.close()
+    inv = np.empty(len(order), dtype=np.int64)
+    inv[order] = np.arange(len(order))
+    base, cbase = out["sorted_1"]
+    # the piece path really ran: P force launches and P write-backs instead of one of each
+    assert out["sorted_8"][1]["n_kernel_launches"] == cbase["n_kernel_launches"] + 14
+    assert out["sorted_5"][1]["n_kernel_launches"] == cbase["n_kernel_launches"] + 8
+    assert out["shuffled"][1]["n_kernel_launches"] == cbase["n_kernel_launches"]
+    for name in ("sorted_8", "sorted_5", "shuffled"):
+        got, cnt = out[name]
+        if name == "shuffled":
+            got = got[order]
+        for k in ("n_density", "n_density_redo", "n_force"):
+            assert cnt[k] == cbase[k], (name, k)
+        for f in base.dtype.names:
+            assert np.array_equal(got[f], base[f], equal_nan=True) if got[f].dtype.kind == "f" else \
+                np.array_equal(got[f], base[f]), (name, f)
