@@ -427,7 +427,7 @@ def main():
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": cfg, "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "entry": "swift_cuda_step_parts (the caller's 128-byte struct part records in and out; records in cell order as s->parts is after space_rebuild, results copied back in 8 pieces under the force loop)"},
+                    "entry": "swift_cuda_step_parts (the caller's 128-byte struct part records in and out; records in cell order as s->parts is after space_rebuild, taken in 12 pieces: unpack, sorts and the first density pass of a piece run under the copy of the next, results are copied back under the force loop)"},
             "roofline": roofline,
             "detail": {"n_particles": n, "interactions_per_step": inter, "n_density": cnt["n_density"],
                        "n_density_redo": cnt["n_density_redo"], "n_force": cnt["n_force"],

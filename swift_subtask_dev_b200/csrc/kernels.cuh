@@ -431,9 +431,9 @@ __global__ void __launch_bounds__(256) k_sort(Dev d, int n_seg, const int32_t *s
 // ---------------------------------------------------------------------------
 // K1b: start of a step: zero sums (hydro_init_part), arm the ghost state
 // ---------------------------------------------------------------------------
-__global__ void k_init_step(Dev d) {
-  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (p >= d.n) return;
+__global__ void k_init_step(Dev d, int64_t lo = 0, int64_t hi = INT64_MAX) {
+  const int64_t p = lo + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p >= d.n || p >= hi) return;
   const bool active = d.time_bin[p] <= kc.max_active_bin;
   d.gstate[p] = active ? 1 : 0;
   // time-integration mode (unit_list set): most steps have few active particles and nothing below is
@@ -709,7 +709,11 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
   const bool by_list = MODE == 1 && !by_unit && (long long)d.leaf_count[sweep] * 4 < d.n_leaves;
   // first pass with few active units (time-integration mode): walk the list k_mark_sorts pushed
   const bool by_ulist = MODE == 0 && d.unit_list != nullptr && (long long)*d.unit_count * 4 < d.n_units;
-  const int total = by_ulist ? *d.unit_count : (by_unit ? d.n_units : (by_list ? d.leaf_count[sweep] : d.n_leaves));
+  // first pass over a range of units only (swift_cuda_step_parts, records arriving in pieces)
+  const bool ranged = MODE == 0 && !by_ulist && d.unit_hi > 0;
+  const int total = by_ulist ? *d.unit_count
+                             : (by_unit ? (ranged ? d.unit_hi : d.n_units) : (by_list ? d.leaf_count[sweep] : d.n_leaves));
+  const int wid0 = ranged ? d.unit_lo : 0;
   int *const work = d.work_ctr + (MODE == 0 ? 0 : 1 + sweep);
   const Item *__restrict__ items = MODE == 0 ? d.items : d.redo_items;
   const bool rec = d.rec_capacity > 0;
@@ -718,7 +722,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
 
   while (true) {
     int wid = 0;
-    if (lane == 0) wid = atomicAdd(work, 1);
+    if (lane == 0) wid = atomicAdd(work, 1) + wid0;
     wid = __shfl_sync(kFull, wid, 0);
     if (wid >= total) break;
     if (by_ulist) wid = d.unit_list[wid];
@@ -1413,12 +1417,13 @@ __global__ void k_cell_box_init(Dev d) {
   if (i >= d.ncells * 6) return;
   d.cell_box_u[i] = float_to_ordered((i % 6) < 3 ? INFINITY : -INFINITY);
 }
-__global__ void k_cell_box(Dev d) {
+// [first_lo, first_hi): only the leaves whose first particle lies in this range of cell-order slots
+__global__ void k_cell_box(Dev d, int64_t first_lo = 0, int64_t first_hi = INT64_MAX) {
   const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (c >= d.ncells || d.cell_split[c]) return;  // leaves only
   const CellDev cell = d.cells[c];
-  if (cell.count == 0) return;
+  if (cell.count == 0 || cell.first < first_lo || cell.first >= first_hi) return;
   double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
   for (int k = lane; k < cell.count; k += 32) {
     double p[3];

@@ -140,8 +140,8 @@ __device__ __forceinline__ void aos_put(unsigned char *rec, int off, T v) {
 }
 // sums: 1 = also the running density sums (KEEP); force: 1 = also a_hydro, u_dt, h_dt, v_sig, min_bin
 __global__ void k_pack_aos(int64_t n, const unsigned char *aos, swift_cuda_part_layout L, const int32_t *order,
-                           PackDst o, AosDst a, int with_static, int sums, int force) {
-  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+                           PackDst o, AosDst a, int with_static, int sums, int force, int64_t lo = 0) {
+  const int64_t k = lo + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;  // n: end of the range of slots
   if (k >= n) return;
   const int64_t s = order ? order[k] : k;
   const unsigned char *r = aos + (size_t)s * L.stride;
@@ -222,11 +222,14 @@ __global__ void k_unpack_aos(Dev d, unsigned char *aos, swift_cuda_part_layout L
 }
 
 // c->hydro.h_max of every cell from the particles' h (after a pack): one warp per cell
-__global__ void k_cell_hmax_init(Dev d, float *hmax, float *hmax_old) {
+// (end_lo, end_hi]: only the cells whose last particle lies in this range of cell-order slots
+__global__ void k_cell_hmax_init(Dev d, float *hmax, float *hmax_old, int64_t end_lo = -1, int64_t end_hi = INT64_MAX) {
   const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (c >= d.ncells) return;
   const CellDev cell = d.cells[c];
+  const int64_t end = (int64_t)cell.first + cell.count;
+  if (end <= end_lo || end > end_hi) return;
   float m = 0.f;
   for (int k = lane; k < cell.count; k += 32) m = fmaxf(m, d.h[cell.first + k]);
   for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));

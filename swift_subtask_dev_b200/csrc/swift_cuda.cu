@@ -80,8 +80,15 @@ struct swift_cuda_ctx {
   // swift_cuda_step_parts hands the force loop's results back in `pieces` pieces (units of consecutive leaves
   // = consecutive records) when the caller's records are in cell order, as s->parts is after space_rebuild
   bool records_in_cell_order = false;
-  int pieces = 8;
+  int pieces = 12;
   std::vector<cudaEvent_t> piece_ev;
+  std::vector<int64_t> seg_end;    // last slot + 1 of every sort segment's cell (segments are kept in this order)
+  struct PiecePlan {               // built on the first step that runs in pieces
+    int P = 0;
+    std::vector<int> leaf;         // [P+1] leaf slots
+    std::vector<int64_t> rec;      // [P+1] cell-order slots (= records)
+    std::vector<int64_t> dep_hi;   // [P] every cell a piece's interactions read ends at or before this slot
+  } plan;
   unsigned char *d_aos = nullptr;
   bool no_prune = false;            // build the work lists with every cell, whatever the time bins
   std::vector<int32_t> slot_of;     // host copy of Dev::part_slot (caller order)
@@ -366,7 +373,7 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
 
 
   // work lists
-  const WorkLists &wl = c->wl;
+  WorkLists &wl = c->wl;
   d.n_leaves = (int)wl.leaves.size();
   d.n_units = (int)wl.unit_leaf.size();
   int32_t *dlv, *dib, *drb, *dul, *duo, *dlp; Item *dit, *drt; int64_t *dsl;
@@ -428,6 +435,30 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
   }
   if (dmalloc(c, &d.sort, (size_t)wl.n_sort_entries)) return 1;
   c->n_seg = (int)wl.sort_cells.size();
+  {
+    // segments in the order their cells are complete when the records arrive front to back
+    // (swift_cuda_step_parts sorts a piece's cells while the next piece is on the bus)
+    std::vector<int32_t> perm(c->n_seg);
+    for (int s = 0; s < c->n_seg; s++) perm[s] = s;
+    auto end_of = [&](int s) {
+      const swift_cuda_cell &cl = c->tree.cells[wl.sort_cells[s]];
+      return (int64_t)cl.first + cl.count;
+    };
+    std::stable_sort(perm.begin(), perm.end(), [&](int a, int b) { return end_of(a) < end_of(b); });
+    std::vector<int32_t> sc(c->n_seg), ss(c->n_seg);
+    std::vector<int64_t> so(c->n_seg);
+    c->seg_end.resize(c->n_seg);
+    for (int s = 0; s < c->n_seg; s++) {
+      sc[s] = wl.sort_cells[perm[s]];
+      ss[s] = wl.sort_sids[perm[s]];
+      so[s] = wl.sort_offset[perm[s]];
+      c->seg_end[s] = end_of(perm[s]);
+    }
+    wl.sort_cells.swap(sc);
+    wl.sort_sids.swap(ss);
+    wl.sort_offset.swap(so);
+    c->plan.P = 0;
+  }
   std::vector<int64_t> scratch_off(c->n_seg, 0);
   int64_t scratch_total = 0;
   for (int s = 0; s < c->n_seg; s++) {
@@ -1083,6 +1114,130 @@ static int finish_parts_build(swift_cuda_ctx *c, const swift_cuda_part_layout *L
   return dmalloc(c, &c->d_aos, (size_t)std::max<int64_t>(c->n, 1) * L->stride);
 }
 
+// Pieces of consecutive leaves (= consecutive units = consecutive records) of about equal unit counts,
+// and for every piece the last record any of its first-pass / force interactions reads.
+static void build_piece_plan(swift_cuda_ctx *c, int P) {
+  const WorkLists &wl = c->wl;
+  swift_cuda_ctx::PiecePlan &pl = c->plan;
+  const int nl = (int)wl.leaves.size();
+  const int64_t n = c->n;
+  pl.P = P;
+  pl.leaf.assign(P + 1, 0);
+  pl.rec.assign(P + 1, 0);
+  pl.dep_hi.assign(P, 0);
+  for (int k = 1; k < P; k++) {
+    const int32_t want = (int32_t)((int64_t)c->dev.n_units * k / P);
+    int sl = (int)(std::lower_bound(wl.unit_begin.begin(), wl.unit_begin.begin() + nl, want) - wl.unit_begin.begin());
+    sl = std::max(sl, pl.leaf[k - 1]);
+    pl.leaf[k] = sl;
+    pl.rec[k] = sl < nl ? (int64_t)c->tree.cells[wl.leaves[sl]].first : n;
+  }
+  pl.leaf[P] = nl;
+  pl.rec[P] = n;
+  auto end_of = [&](int32_t cell) {
+    const swift_cuda_cell &cl = c->tree.cells[cell];
+    return (int64_t)cl.first + cl.count;
+  };
+  for (int k = 0; k < P; k++) {
+    int64_t hi = pl.rec[k + 1];
+    for (int32_t it = wl.item_begin[pl.leaf[k]]; it < wl.item_begin[pl.leaf[k + 1]]; it++) {
+      hi = std::max(hi, end_of(wl.items[it].own));
+      hi = std::max(hi, end_of(wl.items[it].partner));
+    }
+    pl.dep_hi[k] = hi;
+  }
+}
+
+// The front of swift_cuda_step_parts with the records in cell order: the records go up in pieces (copy
+// stream); as a piece lands its records are unpacked, its particles armed, the cells it completes get
+// their h_max, boxes and sorted lists, and the first density pass runs over every piece of units whose
+// interactions read nothing beyond what has landed -- under the copy of the next piece.
+static int parts_front_in_pieces(swift_cuda_ctx *c, const void *parts, const PackDst &o, const AosDst &a) {
+  Dev &d = c->dev;
+  const swift_cuda_part_layout L = c->lay;
+  const swift_cuda_ctx::PiecePlan &pl = c->plan;
+  const int P = pl.P;
+  const int64_t n = c->n;
+  const size_t nit = (size_t)c->prm.max_smoothing_iterations + 2;
+  // events: [0, P) results of a force piece written back, [P, 2P) a piece of records has landed, [2P] start
+  while ((int)c->piece_ev.size() < 2 * P + 1) {
+    cudaEvent_t e;
+    CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    c->piece_ev.push_back(e);
+  }
+  if (launch_mark(c)) return 1;
+  // what launch_density_prep does before any particle is looked at
+  CK(cudaMemsetAsync(d.hits, 0, 3 * sizeof(unsigned long long), c->stream));
+  CK(cudaMemsetAsync(d.redo_count, 0, nit * sizeof(int), c->stream));
+  CK(cudaMemsetAsync(d.walk_count, 0, nit * sizeof(int), c->stream));
+  CK(cudaMemsetAsync(d.leaf_count, 0, nit * sizeof(int), c->stream));
+  CK(cudaMemsetAsync(d.leaf_mark, 0, (size_t)std::max(d.n_leaves, 1) * sizeof(int), c->stream));
+  CK(cudaMemsetAsync(d.work_ctr, 0, nit * sizeof(int), c->stream));
+  CK(cudaMemsetAsync(d.stale, 0, sizeof(int), c->stream));
+  if (d.nl) CK(cudaMemsetAsync(d.nl_cnt, 0xff, (size_t)d.n_units * 32 * sizeof(unsigned short), c->stream));
+  const int nbc = (d.ncells * 32 + 255) / 256, nb6 = (d.ncells * 6 + 255) / 256;
+  k_cell_box_init<<<nb6, 256, 0, c->stream>>>(d);
+  c->counters.n_kernel_launches += 1;
+  // the copy stream: every piece of records, front to back, each with its event
+  CK(cudaEventRecord(c->piece_ev[2 * P], c->stream));
+  CK(cudaStreamWaitEvent(c->io, c->piece_ev[2 * P], 0));
+  for (int j = 0; j < P; j++) {
+    const int64_t r0 = pl.rec[j], r1 = pl.rec[j + 1];
+    if (r1 > r0)
+      CK(cudaMemcpyAsync(c->d_aos + (size_t)r0 * L.stride, (const unsigned char *)parts + (size_t)r0 * L.stride,
+                         (size_t)(r1 - r0) * L.stride, cudaMemcpyHostToDevice, c->io));
+    CK(cudaEventRecord(c->piece_ev[P + j], c->io));
+  }
+  std::vector<char> launched(P, 0);
+  size_t seg_lo = 0;
+  for (int j = 0; j < P; j++) {
+    const int64_t r0 = pl.rec[j], r1 = pl.rec[j + 1];
+    CK(cudaStreamWaitEvent(c->stream, c->piece_ev[P + j], 0));
+    if (r1 > r0) {
+      const unsigned nb = (unsigned)((r1 - r0 + 255) / 256);
+      k_pack_aos<<<nb, 256, 0, c->stream>>>(r1, c->d_aos, L, nullptr, o, a, 0, 0, 0, r0);
+      k_init_step<<<nb, 256, 0, c->stream>>>(d, r0, r1);
+      k_cell_box<<<nbc, 256, 0, c->stream>>>(d, r0, r1);
+      c->counters.n_kernel_launches += 3;
+    }
+    // the cells this piece completes (a parent is complete with its last leaf)
+    k_cell_hmax_init<<<nbc, 256, 0, c->stream>>>(d, d.cell_hmax, const_cast<float *>(d.cell_hmax_old),
+                                                 j == 0 ? (int64_t)-1 : r0, j == P - 1 ? INT64_MAX : r1);
+    k_cell_box_finish<<<nb6, 256, 0, c->stream>>>(d);
+    c->counters.n_kernel_launches += 2;
+    const size_t seg_hi = j == P - 1 ? (size_t)c->n_seg
+                                     : (size_t)(std::upper_bound(c->seg_end.begin(), c->seg_end.end(), r1) - c->seg_end.begin());
+    if (seg_hi > seg_lo) {
+      k_sort<<<(unsigned)(seg_hi - seg_lo), 256, 0, c->stream>>>(d, (int)(seg_hi - seg_lo), c->d_seg_cell + seg_lo,
+                                                                  c->d_seg_sid + seg_lo, c->d_seg_off + seg_lo, c->d_scratch,
+                                                                  c->d_scratch_off + seg_lo);
+      c->counters.n_kernel_launches += 1;
+    }
+    seg_lo = seg_hi;
+    CK(cudaGetLastError());
+    if (j == P - 1) CK(cudaEventRecord(c->ev[1], c->stream));
+    // the first density pass over every piece of units that reads nothing beyond what has landed
+    for (int k = 0; k < P; k++) {
+      if (launched[k] || (pl.dep_hi[k] > r1 && j < P - 1)) continue;
+      launched[k] = 1;
+      d.unit_lo = c->wl.unit_begin[pl.leaf[k]];
+      d.unit_hi = c->wl.unit_begin[pl.leaf[k + 1]];
+      if (d.unit_hi > d.unit_lo) {
+        CK(cudaMemsetAsync(d.work_ctr, 0, sizeof(int), c->stream));
+        k_density<0><<<c->grid_density, kBlock, 0, c->stream>>>(d, 0);
+        c->counters.n_kernel_launches += 1;
+        CK(cudaGetLastError());
+      }
+    }
+  }
+  d.unit_lo = d.unit_hi = 0;
+  if (d.ncells > 0) k_check_lists<<<(d.ncells + 255) / 256, 256, 0, c->stream>>>(d, c->dx_max_part);
+  CK(cudaMemcpyAsync(c->d_dens0_first, d.dens0, n * sizeof(float4), cudaMemcpyDeviceToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->d_dens1_first, d.dens1, n * sizeof(float4), cudaMemcpyDeviceToDevice, c->stream));
+  CK(cudaGetLastError());
+  return 0;
+}
+
 extern "C" {
 
 int swift_cuda_build_from_cells_parts(swift_cuda_ctx *c, const swift_cuda_part_layout *L, const void *parts, int64_t n,
@@ -1137,8 +1292,13 @@ int swift_cuda_step_parts(swift_cuda_ctx *c, void *parts, int phases) {
   const bool do_force = phases & SWIFT_CUDA_PHASE_FORCE, do_end = phases & SWIFT_CUDA_PHASE_END_FORCE;
   const bool keep = (phases & SWIFT_CUDA_PHASE_KEEP) || (do_ghost && !do_dens);
   c->counters.n_kernel_launches = 0;
+  const WorkLists &wl = c->wl;
+  const int P = c->pieces;
+  // records in cell order and enough of them: the step runs in P pieces of consecutive leaves at both ends
+  const bool pieces_ok = P > 1 && c->records_in_cell_order && n >= (1 << 18) && d.n_units >= 64 * P &&
+                         (int64_t)wl.unit_begin.size() == (int64_t)wl.leaves.size() + 1;
+  if (pieces_ok && c->plan.P != P) build_piece_plan(c, P);
   CK(cudaEventRecord(c->ev[0], c->stream));
-  CK(cudaMemcpyAsync(c->d_aos, parts, (size_t)n * L.stride, cudaMemcpyHostToDevice, c->stream));
   PackDst o;
   o.pos = const_cast<PosD *>(d.pos);
   o.vm = d.vm; o.fin = d.fin; o.hb = d.hb; o.h = d.h; o.h0 = c->d_h0; o.u = const_cast<float *>(d.u);
@@ -1150,52 +1310,47 @@ int swift_cuda_step_parts(swift_cuda_ctx *c, void *parts, int phases) {
   const int32_t *order = (c->tree.order.empty() || c->records_in_cell_order) ? nullptr : c->s_order;
   const unsigned nb = (unsigned)((n + 255) / 256);
   const int load_force = (!do_dens && !do_ghost) ? 1 : 0;
-  if (n > 0) k_pack_aos<<<nb, 256, 0, c->stream>>>(n, c->d_aos, L, order, o, a, 0, keep ? 1 : 0, load_force);
-  if (d.ncells > 0)
-    k_cell_hmax_init<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d, d.cell_hmax,
-                                                                         const_cast<float *>(d.cell_hmax_old));
-  c->counters.n_kernel_launches += 2;
-  CK(cudaGetLastError());
   c->marks_fresh = false;
   // (without density and ghost in this call the running force sums of the records must survive k_init_step too)
   d.keep_sums = (keep || load_force) ? 1 : 0;
   d.no_end_force = do_end ? 0 : 1;
-  if ((phases & SWIFT_CUDA_PHASE_SORT) && launch_sort(c)) return 1;
-  CK(cudaEventRecord(c->ev[1], c->stream));
-  if (do_dens) {
-    if (launch_density(c)) return 1;
-  } else if (launch_density_prep(c)) {
-    return 1;
+  const bool front_in_pieces = pieces_ok && (phases & SWIFT_CUDA_PHASE_SORT) && do_dens && !keep && !(c->path & 33);
+  if (front_in_pieces) {
+    if (parts_front_in_pieces(c, parts, o, a)) return 1;   // records ev[1] after the last sort
+  } else {
+    CK(cudaMemcpyAsync(c->d_aos, parts, (size_t)n * L.stride, cudaMemcpyHostToDevice, c->stream));
+    if (n > 0) k_pack_aos<<<nb, 256, 0, c->stream>>>(n, c->d_aos, L, order, o, a, 0, keep ? 1 : 0, load_force);
+    if (d.ncells > 0)
+      k_cell_hmax_init<<<(d.ncells * 32 + 255) / 256, 256, 0, c->stream>>>(d, d.cell_hmax,
+                                                                           const_cast<float *>(d.cell_hmax_old));
+    c->counters.n_kernel_launches += 2;
+    CK(cudaGetLastError());
+    if ((phases & SWIFT_CUDA_PHASE_SORT) && launch_sort(c)) return 1;
+    CK(cudaEventRecord(c->ev[1], c->stream));
+    if (do_dens) {
+      if (launch_density(c)) return 1;
+    } else if (launch_density_prep(c)) {
+      return 1;
+    }
   }
   CK(cudaEventRecord(c->ev[2], c->stream));
   if (do_ghost && launch_ghost(c)) return 1;
   CK(cudaEventRecord(c->ev[3], c->stream));
   const int what = (do_force || do_end) ? (do_ghost ? 16 : 8) : (do_ghost ? 4 : (do_dens ? 2 : 0));
-  const WorkLists &wl = c->wl;
-  const int P = c->pieces;
-  const bool in_pieces = do_force && P > 1 && c->records_in_cell_order && n >= (1 << 18) && d.n_units >= 64 * P &&
-                         (int64_t)wl.unit_begin.size() == (int64_t)wl.leaves.size() + 1;
+  const bool in_pieces = do_force && pieces_ok;
   if (in_pieces) {
     // The force loop over the units of consecutive leaves, piece by piece: the records of a finished piece
     // are written back and copied to the host (copy stream) while the loop runs over the next piece.
-    while ((int)c->piece_ev.size() < P) {
+    const swift_cuda_ctx::PiecePlan &pl = c->plan;
+    while ((int)c->piece_ev.size() < 2 * P + 1) {
       cudaEvent_t e;
       CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
       c->piece_ev.push_back(e);
     }
-    const int nl = (int)wl.leaves.size();
-    int s_prev = 0;
-    int64_t p_prev = 0;
     for (int k = 0; k < P; k++) {
-      int s_next = nl;
-      if (k < P - 1) {
-        const int32_t want = (int32_t)((int64_t)d.n_units * (k + 1) / P);
-        s_next = (int)(std::lower_bound(wl.unit_begin.begin(), wl.unit_begin.begin() + nl, want) - wl.unit_begin.begin());
-        s_next = std::max(s_next, s_prev);
-      }
-      const int64_t p_next = s_next < nl ? (int64_t)c->tree.cells[wl.leaves[s_next]].first : n;
-      d.unit_lo = wl.unit_begin[s_prev];
-      d.unit_hi = wl.unit_begin[s_next];
+      const int64_t p_prev = pl.rec[k], p_next = pl.rec[k + 1];
+      d.unit_lo = wl.unit_begin[pl.leaf[k]];
+      d.unit_hi = wl.unit_begin[pl.leaf[k + 1]];
       if (d.unit_hi > d.unit_lo && launch_force(c)) return 1;
       if (k == P - 1) CK(cudaEventRecord(c->ev[4], c->stream));
       if (p_next > p_prev) {
@@ -1208,8 +1363,6 @@ int swift_cuda_step_parts(swift_cuda_ctx *c, void *parts, int phases) {
         CK(cudaMemcpyAsync((unsigned char *)parts + (size_t)p_prev * L.stride, c->d_aos + (size_t)p_prev * L.stride,
                            (size_t)(p_next - p_prev) * L.stride, cudaMemcpyDeviceToHost, c->io));
       }
-      s_prev = s_next;
-      p_prev = p_next;
     }
     d.unit_lo = d.unit_hi = 0;
     d.keep_sums = 0;

@@ -142,9 +142,10 @@ def test_max_active_bin_can_change_between_steps():
 @pytest.mark.gpu
 @pytest.mark.parametrize("fields_mode", [0, 1])
 def test_records_in_cell_order_come_back_in_pieces(fields_mode, monkeypatch):
-    """s->parts after space_rebuild: every cell's records contiguous.  swift_cuda_step_parts then runs the force
-    loop over pieces of consecutive leaves and copies each finished piece back while the next one runs: the
-    same bits as the one-piece path and as the records in arbitrary order."""
+    """s->parts after space_rebuild: every cell's records contiguous.  swift_cuda_step_parts then takes the
+    records in pieces (unpack, cell h_max / boxes / sorts and the first density pass of a piece under the copy
+    of the next) and runs the force loop over pieces of consecutive leaves, copying each finished piece back
+    while the next one runs: the same bits as the one-piece path and as the records in arbitrary order."""
     ic = ics.clustered(300000, nclumps=30, seed=12)
     kw = dict(periodic=True, fields_mode=fields_mode)
     order = be.host_plan(make_params(**kw), ic)["order"]
@@ -165,8 +166,9 @@ def test_records_in_cell_order_come_back_in_pieces(fields_mode, monkeypatch):
     inv[order] = np.arange(len(order))
     base, cbase = out["sorted_1"]
     # the piece path really ran: P force launches and P write-backs instead of one of each
-    assert out["sorted_8"][1]["n_kernel_launches"] == cbase["n_kernel_launches"] + 14
-    assert out["sorted_5"][1]["n_kernel_launches"] == cbase["n_kernel_launches"] + 8
+    # the piece path really ran: per piece a density and a force launch, the prep kernels and a write-back
+    assert out["sorted_8"][1]["n_kernel_launches"] >= out["sorted_5"][1]["n_kernel_launches"] + 3 * 6
+    assert out["sorted_5"][1]["n_kernel_launches"] >= cbase["n_kernel_launches"] + 4 * 6
     assert out["shuffled"][1]["n_kernel_launches"] == cbase["n_kernel_launches"]
     for name in ("sorted_8", "sorted_5", "shuffled"):
         got, cnt = out[name]
