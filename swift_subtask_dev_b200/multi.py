@@ -571,11 +571,15 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
         barrier()
         t1 = time.perf_counter()
         st.be.update_particles(ic_pin)
+        t2 = time.perf_counter()
         step_rank_nccl(st, tr)
+        torch.cuda.synchronize()
+        t3 = time.perf_counter()
         st.be.results(out=out_pin)
         torch.cuda.synchronize()
         if k > 0:
             e2e_s.append(time.perf_counter() - t1)
+            e2e_split = {"h2d_ms": 1e3 * (t2 - t1), "step_ms": 1e3 * (t3 - t2), "d2h_ms": 1e3 * (time.perf_counter() - t3)}
     e2e_ms = 1e3 * float(np.mean(e2e_s))
     t = torch.tensor([max(ms_dev, ms_wall), float(inter), float(n_own), float(st.halo_bytes_per_step()), e2e_ms,
                       float(nloc)], dtype=torch.float64, device="cuda")
@@ -612,7 +616,7 @@ def bench_multi(args, cfg, metric, unit, sampler_cls=None):
                            "halo_bytes_per_step_total": int(tsum[3]), "build_s": build_s,
                            "load_imbalance_interactions_max_over_mean": float(tmax[1]) * world / float(tsum[1]),
                            "ms_device_events_rank0": ms_dev, "ms_wall_rank0": ms_wall,
-                           "nccl_parity": nccl_parity, "phase_ms": phase_max}}
+                           "nccl_parity": nccl_parity, "phase_ms": phase_max, "e2e_ms_max_over_ranks": float(tmax[4]), "e2e_split_rank0": e2e_split}}
         print(json.dumps(line))
     dist.barrier()
     dist.destroy_process_group()
