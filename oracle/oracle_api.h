@@ -47,7 +47,7 @@ typedef struct {
   int scheme;            /* ORACLE_SCHEME_*; the ref harness ignores it (compile-time there) */
 } oracle_params;
 
-enum { ORACLE_SCHEME_MINIMAL = 0, ORACLE_SCHEME_PLANETARY = 1 };
+enum { ORACLE_SCHEME_MINIMAL = 0, ORACLE_SCHEME_PLANETARY = 1, ORACLE_SCHEME_SPHENIX = 2 };
 
 /* Tillotson material in INTERNAL units (src/equation_of_state/planetary/tillotson.h:43-143) */
 typedef struct {
@@ -120,7 +120,43 @@ int ref_build_tree_tasks(const oracle_params *prm, int n, const double *x, const
                          oracle_cell **cells_out, int *ncells_out, int cdim_out[3], oracle_task **tasks_out,
                          int *ntasks_out);
 
+/* ---- SPHENIX: the three-loop scheme, src/hydro/SPHENIX -------------------
+ * sort -> density -> ghost (hydro_prepare_gradient + hydro_reset_gradient at convergence) ->
+ * GRADIENT loop (runner_do{self,pair}1_branch_gradient, runner_dosub_{self,pair}1_gradient: the
+ * DOSELF1 / DOPAIR1 walks with runner_iact_nonsym_gradient) -> runner_do_extra_ghost
+ * (hydro_end_gradient, hydro_prepare_force, hydro_reset_acceleration) -> force -> end_force.
+ * Everything the two-loop interface above does not carry travels in this struct; the oracle_parts
+ * fields keep their meaning (d_div_v / f_v_sig are p->viscosity.div_v / p->viscosity.v_sig). */
+typedef struct {
+  /* hydro_props->viscosity / ->diffusion (src/hydro/SPHENIX/hydro_parameters.h:105-140) and
+   * e->time_base (dt_alpha = get_timestep(p->time_bin, time_base), src/runner_ghost.c:1045-1046) */
+  float viscosity_alpha_max, viscosity_alpha_min, viscosity_length;
+  float diffusion_beta, diffusion_alpha_max, diffusion_alpha_min;
+  double time_base;
+  /* inputs, every particle: p->viscosity.alpha, p->diffusion.alpha, p->viscosity.div_v_previous_step */
+  const float *in_alpha_visc, *in_alpha_diff, *in_div_v_prev;
+  /* after the ghost: p->viscosity.div_v (hydro_end_density) */
+  float *g_div_v;
+  /* after the gradient loop, before the extra ghost: p->viscosity.v_sig, p->diffusion.laplace_u (raw
+   * sum), p->force.alpha_visc_max_ngb */
+  float *r_v_sig, *r_laplace_u, *r_alpha_visc_max_ngb;
+  /* after the extra ghost: p->diffusion.laplace_u, p->viscosity.{alpha, div_v_previous_step, div_v_dt},
+   * p->diffusion.alpha */
+  float *e_laplace_u, *e_alpha_visc, *e_alpha_diff, *e_div_v_prev, *e_div_v_dt;
+  /* ordered (updated id, neighbour id) pairs of the gradient loop */
+  long long *grad_pairs; /* [grad_capacity][2], may be NULL */
+  long long grad_capacity;
+  long long grad_count;
+} oracle_sphenix;
+
+/* The reference's own operators (libswiftref_sphenix.so only; returns 1 elsewhere). */
+int ref_run_step_sphenix(const oracle_params *params, oracle_parts *parts, int ncells, const oracle_cell *cells,
+                         int ntasks, const oracle_task *tasks, oracle_pairlog *log, oracle_sphenix *sx);
+
 /* ---- the plain-C restatement (oracle/sph_oracle.c) ---- */
+/* params->scheme must be ORACLE_SCHEME_SPHENIX */
+int oracle_run_step_sphenix(const oracle_params *prm, oracle_parts *parts, int ncells, const oracle_cell *cells,
+                            int ntasks, const oracle_task *tasks, oracle_pairlog *log, oracle_sphenix *sx);
 int oracle_build_tree(const oracle_params *prm, int n, const double *x, const float *h, int *order,
                       oracle_cell **cells_out, int *ncells_out, int cdim_out[3]);
 int oracle_build_tasks(const oracle_params *prm, int ncells, const oracle_cell *cells, const int cdim[3],

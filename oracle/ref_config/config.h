@@ -4,6 +4,8 @@
  * under /root/reference, into oracle/_ref/.  Never part of the product.
  *
  * Scheme selection: -DREF_PLANETARY picks PLANETARY_SPH + EOS_PLANETARY,
+ * -DREF_SPHENIX picks SPHENIX_SPH + EOS_IDEAL_GAS (the reference's configure default,
+ * configure.ac:1958-1959; it defines EXTRA_HYDRO_LOOP itself, src/part.h:84-90),
  * default is MINIMAL_SPH + EOS_IDEAL_GAS. */
 #ifndef REF_CONFIG_H
 #define REF_CONFIG_H
@@ -15,6 +17,9 @@
 #ifdef REF_PLANETARY
 #define PLANETARY_SPH 1
 #define EOS_PLANETARY 1
+#elif defined(REF_SPHENIX)
+#define SPHENIX_SPH 1
+#define EOS_IDEAL_GAS 1
 #else
 #define MINIMAL_SPH 1
 #define EOS_IDEAL_GAS 1

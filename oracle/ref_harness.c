@@ -39,7 +39,27 @@ static oracle_pairlog *g_log = NULL;
 static int g_store = 0;
 static int g_stage = 0; /* 0 density, 1 ghost redo, 2 force */
 
+static oracle_sphenix *g_sx = NULL; /* SPHENIX: extra inputs / outputs, the gradient loop's pair log */
+
+/* the fields that moved between the schemes' struct part */
+#ifdef SPHENIX_SPH
+#define PART_DIV_V(p) ((p)->viscosity.div_v)
+#define PART_V_SIG(p) ((p)->viscosity.v_sig)
+#else
+#define PART_DIV_V(p) ((p)->density.div_v)
+#define PART_V_SIG(p) ((p)->force.v_sig)
+#endif
+
 void ref_record_pair(int loop, long long id_updated, long long id_other) {
+  if (loop == 2) { /* gradient loop */
+    if (g_sx == NULL) return;
+    const long long k = g_sx->grad_count++;
+    if (g_store && g_sx->grad_pairs != NULL && k < g_sx->grad_capacity) {
+      g_sx->grad_pairs[2 * k] = id_updated;
+      g_sx->grad_pairs[2 * k + 1] = id_other;
+    }
+    return;
+  }
   if (g_log == NULL) return;
   const int slot = (loop == 1) ? 2 : g_stage;
   const long long k = g_log->count[slot]++;
@@ -69,9 +89,31 @@ static int cell_has_active(const struct cell *c, const struct engine *e) {
   return 0;
 }
 
+static int run_step(const oracle_params *prm, oracle_parts *io, int ncells, const oracle_cell *cd, int ntasks,
+                    const oracle_task *td, oracle_pairlog *log, oracle_sphenix *sx);
+
 int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
                  const oracle_cell *cd, int ntasks, const oracle_task *td,
                  oracle_pairlog *log) {
+#ifdef SPHENIX_SPH
+  return 1; /* this build runs the three-loop scheme: ref_run_step_sphenix */
+#else
+  return run_step(prm, io, ncells, cd, ntasks, td, log, NULL);
+#endif
+}
+
+int ref_run_step_sphenix(const oracle_params *prm, oracle_parts *io, int ncells, const oracle_cell *cd, int ntasks,
+                         const oracle_task *td, oracle_pairlog *log, oracle_sphenix *sx) {
+#ifdef SPHENIX_SPH
+  if (sx == NULL) return 1;
+  return run_step(prm, io, ncells, cd, ntasks, td, log, sx);
+#else
+  return 1;
+#endif
+}
+
+static int run_step(const oracle_params *prm, oracle_parts *io, int ncells, const oracle_cell *cd, int ntasks,
+                    const oracle_task *td, oracle_pairlog *log, oracle_sphenix *sx) {
   const int n = io->n;
   const integertime_t ti_current = 8;
 
@@ -98,6 +140,12 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
     p->id = io->id[k];
     p->time_bin = io->time_bin ? io->time_bin[k] : 1;
     p->limiter_data.min_ngb_time_bin = num_time_bins + 1;
+#ifdef SPHENIX_SPH
+    /* what hydro_convert_quantities / the previous step left in the particle */
+    p->viscosity.alpha = sx->in_alpha_visc ? sx->in_alpha_visc[k] : prm->viscosity_alpha;
+    p->diffusion.alpha = sx->in_alpha_diff ? sx->in_alpha_diff[k] : 0.f;
+    p->viscosity.div_v_previous_step = sx->in_div_v_prev ? sx->in_div_v_prev[k] : 0.f;
+#endif
   }
 
   /* ---- engine & friends (as tests/test125cells.c:566-619) ---- */
@@ -123,6 +171,14 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
   hp.CFL_condition = 0.1f;
   hp.viscosity.alpha = prm->viscosity_alpha;
   hp.use_mass_weighted_num_ngb = 0;
+#ifdef SPHENIX_SPH
+  hp.viscosity.alpha_max = sx->viscosity_alpha_max;
+  hp.viscosity.alpha_min = sx->viscosity_alpha_min;
+  hp.viscosity.length = sx->viscosity_length;
+  hp.diffusion.beta = sx->diffusion_beta;
+  hp.diffusion.alpha_max = sx->diffusion_alpha_max;
+  hp.diffusion.alpha_min = sx->diffusion_alpha_min;
+#endif
 
   struct cosmology cosmo;
   cosmology_init_no_cosmo(&cosmo);
@@ -137,7 +193,7 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
   engine.max_active_bin = prm->max_active_bin;
   engine.nodeID = 0;
   engine.cosmology = &cosmo;
-  engine.time_base = 1e-3;
+  engine.time_base = sx ? sx->time_base : 1e-3;
   engine.policy = engine_policy_hydro;
   struct lightcone_array_props lcp;
   bzero(&lcp, sizeof(lcp));
@@ -213,6 +269,8 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
   ref_planetary_eos_init();
 #endif
   g_log = log;
+  g_sx = sx;
+  if (sx) sx->grad_count = 0;
   g_store = prm->record_pairs;
   if (log) {
     log->count[0] = log->count[1] = log->count[2] = 0;
@@ -255,7 +313,7 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
     if (io->d_rho_dh) io->d_rho_dh[k] = p->density.rho_dh;
     if (io->d_wcount) io->d_wcount[k] = p->density.wcount;
     if (io->d_wcount_dh) io->d_wcount_dh[k] = p->density.wcount_dh;
-    if (io->d_div_v) io->d_div_v[k] = p->density.div_v;
+    if (io->d_div_v) io->d_div_v[k] = PART_DIV_V(p);
     if (io->d_rot_v)
       for (int d = 0; d < 3; d++) io->d_rot_v[3 * k + d] = p->density.rot_v[d];
   }
@@ -272,7 +330,39 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
     if (io->g_pressure) io->g_pressure[k] = p->force.pressure;
     if (io->g_soundspeed) io->g_soundspeed[k] = p->force.soundspeed;
     if (io->g_balsara) io->g_balsara[k] = p->force.balsara;
+#ifdef SPHENIX_SPH
+    if (sx->g_div_v) sx->g_div_v[k] = p->viscosity.div_v;
+#endif
   }
+
+#ifdef EXTRA_HYDRO_LOOP
+  /* ---- gradient loop + extra ghost (src/runner_main.c:199-200, 249-250, 297-298, 343-344, 420-421) ---- */
+  for (int k = 0; k < ntasks; k++) {
+    struct task *t = &tasks[k];
+    switch (t->type) {
+      case task_type_self: runner_doself1_branch_gradient(&runner, t->ci); break;
+      case task_type_pair: runner_dopair1_branch_gradient(&runner, t->ci, t->cj); break;
+      case task_type_sub_self: runner_dosub_self1_gradient(&runner, t->ci, 0); break;
+      default: runner_dosub_pair1_gradient(&runner, t->ci, t->cj, 0); break;
+    }
+  }
+  for (int k = 0; k < n; k++) {
+    const struct part *p = &parts[k];
+    if (sx->r_v_sig) sx->r_v_sig[k] = p->viscosity.v_sig;
+    if (sx->r_laplace_u) sx->r_laplace_u[k] = p->diffusion.laplace_u;
+    if (sx->r_alpha_visc_max_ngb) sx->r_alpha_visc_max_ngb[k] = p->force.alpha_visc_max_ngb;
+  }
+  for (int k = 0; k < ncells; k++)
+    if (cells[k].parent == NULL) runner_do_extra_ghost(&runner, &cells[k], 0);
+  for (int k = 0; k < n; k++) {
+    const struct part *p = &parts[k];
+    if (sx->e_laplace_u) sx->e_laplace_u[k] = p->diffusion.laplace_u;
+    if (sx->e_alpha_visc) sx->e_alpha_visc[k] = p->viscosity.alpha;
+    if (sx->e_alpha_diff) sx->e_alpha_diff[k] = p->diffusion.alpha;
+    if (sx->e_div_v_prev) sx->e_div_v_prev[k] = p->viscosity.div_v_previous_step;
+    if (sx->e_div_v_dt) sx->e_div_v_dt[k] = p->viscosity.div_v_dt;
+  }
+#endif
 
   /* ---- force ---- */
   g_stage = 2;
@@ -293,11 +383,12 @@ int ref_run_step(const oracle_params *prm, oracle_parts *io, int ncells,
       for (int d = 0; d < 3; d++) io->f_a[3 * k + d] = p->a_hydro[d];
     if (io->f_u_dt) io->f_u_dt[k] = p->u_dt;
     if (io->f_h_dt) io->f_h_dt[k] = p->force.h_dt;
-    if (io->f_v_sig) io->f_v_sig[k] = p->force.v_sig;
+    if (io->f_v_sig) io->f_v_sig[k] = PART_V_SIG(p);
     if (io->f_min_ngb_time_bin) io->f_min_ngb_time_bin[k] = p->limiter_data.min_ngb_time_bin;
   }
 
   g_log = NULL;
+  g_sx = NULL;
   for (int k = 0; k < ncells; k++) cell_free_hydro_sorts(&cells[k]);
   free(links);
   free(tasks);
@@ -388,7 +479,7 @@ static ienv *ienv_make(const oracle_iparams *ip, const oracle_istate *s) {
     p->rho = s->rho[k];
     p->force.pressure = s->pressure[k];
     p->force.soundspeed = s->soundspeed[k];
-    p->force.v_sig = s->v_sig[k];
+    PART_V_SIG(p) = s->v_sig[k];
     p->u_dt = s->u_dt[k];
     p->force.h_dt = s->h_dt[k];
     p->time_bin = s->time_bin[k];
@@ -432,7 +523,7 @@ static void ienv_store(ienv *v, oracle_istate *s) {
     s->rho[k] = p->rho;
     s->pressure[k] = p->force.pressure;
     s->soundspeed[k] = p->force.soundspeed;
-    s->v_sig[k] = p->force.v_sig;
+    s->v_sig[k] = PART_V_SIG(p);
     s->u_dt[k] = p->u_dt;
     s->h_dt[k] = p->force.h_dt;
     s->time_bin[k] = p->time_bin;

@@ -46,6 +46,27 @@ __attribute__((always_inline)) static inline void rec_iact_force(
   runner_iact_force(r2, dx, hi, hj, pi, pj, a, H);
 }
 
+#ifdef EXTRA_HYDRO_LOOP
+/* SPHENIX: the gradient loop (loop 2 of the recorder) */
+__attribute__((always_inline)) static inline void rec_iact_nonsym_gradient(
+    const float r2, const float dx[3], const float hi, const float hj,
+    struct part *restrict pi, struct part *restrict pj, const float a,
+    const float H) {
+  ref_record_pair(2, pi->id, pj->id);
+  runner_iact_nonsym_gradient(r2, dx, hi, hj, pi, pj, a, H);
+}
+__attribute__((always_inline)) static inline void rec_iact_gradient(
+    const float r2, const float dx[3], const float hi, const float hj,
+    struct part *restrict pi, struct part *restrict pj, const float a,
+    const float H) {
+  ref_record_pair(2, pi->id, pj->id);
+  ref_record_pair(2, pj->id, pi->id);
+  runner_iact_gradient(r2, dx, hi, hj, pi, pj, a, H);
+}
+#define runner_iact_nonsym_gradient rec_iact_nonsym_gradient
+#define runner_iact_gradient rec_iact_gradient
+#endif
+
 #define runner_iact_nonsym_density rec_iact_nonsym_density
 #define runner_iact_density rec_iact_density
 #define runner_iact_nonsym_force rec_iact_nonsym_force

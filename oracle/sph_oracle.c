@@ -80,6 +80,9 @@ typedef struct {
   float mass, h, u, u_dt, rho;
   float wcount, wcount_dh, rho_dh, div_v, rot_v[3]; /* density sums */
   float f, pressure, soundspeed, v_sig, h_dt, balsara; /* force variables */
+  /* SPHENIX: p->viscosity.{alpha, div_v_previous_step, div_v_dt}, p->diffusion.{alpha, laplace_u},
+   * p->force.alpha_visc_max_ngb (div_v and v_sig above are its p->viscosity.div_v / .v_sig) */
+  float alpha_visc, div_v_prev, div_v_dt, alpha_diff, laplace_u, alpha_visc_max_ngb;
   long long id;
   int mat_id;
   signed char time_bin, min_ngb_time_bin;
@@ -109,9 +112,10 @@ typedef struct {
   const oracle_task *tasks;
   int ntasks;
   oracle_pairlog *log;
-  int stage;
+  int stage; /* 0 density, 1 ghost redo, 2 force, 3 gradient (SPHENIX) */
   float a, H; /* cosmology_init_no_cosmo: a = 1, H = 0 */
   float beta;
+  oracle_sphenix *sx; /* SPHENIX only */
 } octx;
 
 static inline float fmin_f(float a, float b) { return a < b ? a : b; }
@@ -153,7 +157,15 @@ static inline void kernel_eval(float u, float *W, float *dW) {
  * src/hydro/Planetary/hydro_iact.h:136-186 (same arithmetic).  The symmetric
  * runner_iact_density (:52-120) equals this applied in both directions bit
  * for bit (the reference's tests/testSymmetry.c), so only this form exists. */
+static inline void iact_gradient(octx *c, float r2, const float dx[3], float hi, opart *pi, const opart *pj);
+
 static inline void iact_density(octx *c, float r2, const float dx[3], float hi, opart *pi, const opart *pj) {
+  /* the gradient loop of SPHENIX is FUNCTION = gradient pasted into the same DOSELF1 / DOPAIR1 /
+   * DOSUB_*1 walks (src/runner_doiact_hydro.c:47-52): same loops, another interaction */
+  if (c->stage == 3) {
+    iact_gradient(c, r2, dx, hi, pi, pj);
+    return;
+  }
   float wi, wi_dx;
   const float mj = pj->mass;
   const float r = sqrtf(r2);
@@ -181,10 +193,101 @@ static inline void iact_density(octx *c, float r2, const float dx[3], float hi, 
   log_pair(c, c->stage, pi->id, pj->id);
 }
 
+/* runner_iact_nonsym_gradient: src/hydro/SPHENIX/hydro_iact.h:272-329.  The symmetric runner_iact_gradient
+ * (:196-257) is this applied in both directions: the same new_v_sig, and laplace_u of pj with
+ * -(u_i - u_j) = (u_j - u_i) exactly. */
+static inline void iact_gradient(octx *c, float r2, const float dx[3], float hi, opart *pi, const opart *pj) {
+  const float a = c->a, H = c->H;
+  const float r = sqrtf(r2);
+  const float r_inv = r ? 1.0f / r : 0.0f;
+  const float fac_mu = 1.f;
+  const float a2_Hubble = a * a * H;
+  const float dvdr = (pi->v[0] - pj->v[0]) * dx[0] + (pi->v[1] - pj->v[1]) * dx[1] + (pi->v[2] - pj->v[2]) * dx[2];
+  const float dvdr_Hubble = dvdr + a2_Hubble * r2;
+  const float omega_ij = fmin_f(dvdr_Hubble, 0.f);
+  const float mu_ij = fac_mu * r_inv * omega_ij;
+  /* hydro_signal_velocity, SPHENIX/hydro.h:490-498 */
+  const float new_v_sig = pi->soundspeed + pj->soundspeed - c->beta * mu_ij;
+  pi->v_sig = fmax_f(pi->v_sig, new_v_sig);
+  float wi, wi_dx;
+  const float ui = r / hi;
+  kernel_eval(ui, &wi, &wi_dx);
+  const float delta_u_factor = (pi->u - pj->u) * r_inv;
+  pi->laplace_u += pj->mass * delta_u_factor * wi_dx / pj->rho;
+  pi->alpha_visc_max_ngb = fmax_f(pi->alpha_visc_max_ngb, pj->alpha_visc);
+  if (c->sx) {
+    const long long k = c->sx->grad_count++;
+    if (c->prm->record_pairs && c->sx->grad_pairs != NULL && k < c->sx->grad_capacity) {
+      c->sx->grad_pairs[2 * k] = pi->id;
+      c->sx->grad_pairs[2 * k + 1] = pj->id;
+    }
+  }
+}
+
+/* runner_iact_nonsym_force of SPHENIX: src/hydro/SPHENIX/hydro_iact.h:488-609 (+ runner_iact_nonsym_timebin) */
+static inline void iact_force_sphenix(octx *c, float r2, const float dx[3], float hi, float hj, opart *pi,
+                                      const opart *pj) {
+  const float a = c->a, H = c->H;
+  const float fac_mu = 1.f;
+  const float a2_Hubble = a * a * H;
+  const float r = sqrtf(r2);
+  const float r_inv = r ? 1.0f / r : 0.0f;
+  const float mi = pi->mass, mj = pj->mass;
+  const float rhoi = pi->rho, rhoj = pj->rho;
+  const float pressurei = pi->pressure, pressurej = pj->pressure;
+  const float hi_inv = 1.0f / hi;
+  const float hi2 = hi_inv * hi_inv;
+  const float hid_inv = hi2 * hi2;
+  const float xi = r * hi_inv;
+  float wi, wi_dx;
+  kernel_eval(xi, &wi, &wi_dx);
+  const float wi_dr = hid_inv * wi_dx;
+  const float hj_inv = 1.0f / hj;
+  const float hj2 = hj_inv * hj_inv;
+  const float hjd_inv = hj2 * hj2;
+  const float xj = r * hj_inv;
+  float wj, wj_dx;
+  kernel_eval(xj, &wj, &wj_dx);
+  const float wj_dr = hjd_inv * wj_dx;
+  const float dvdr = (pi->v[0] - pj->v[0]) * dx[0] + (pi->v[1] - pj->v[1]) * dx[1] + (pi->v[2] - pj->v[2]) * dx[2];
+  const float dvdr_Hubble = dvdr + a2_Hubble * r2;
+  const float omega_ij = fmin_f(dvdr_Hubble, 0.f);
+  const float mu_ij = fac_mu * r_inv * omega_ij;
+  const float v_sig = pi->soundspeed + pj->soundspeed - c->beta * mu_ij;
+  const float f_ij = 1.f - pi->f / mj;
+  const float f_ji = 1.f - pj->f / mi;
+  const float rho_ij = rhoi + rhoj;
+  const float alpha = pi->alpha_visc + pj->alpha_visc;
+  const float visc = -0.25f * alpha * v_sig * mu_ij * (pi->balsara + pj->balsara) / rho_ij;
+  const float visc_acc_term = 0.5f * visc * (wi_dr * f_ij + wj_dr * f_ji) * r_inv;
+  const float P_over_rho2_i = pressurei / (rhoi * rhoi) * f_ij;
+  const float P_over_rho2_j = pressurej / (rhoj * rhoj) * f_ji;
+  const float sph_acc_term = (P_over_rho2_i * wi_dr + P_over_rho2_j * wj_dr) * r_inv;
+  const float acc = sph_acc_term + visc_acc_term;
+  pi->a[0] -= mj * acc * dx[0];
+  pi->a[1] -= mj * acc * dx[1];
+  pi->a[2] -= mj * acc * dx[2];
+  const float sph_du_term_i = P_over_rho2_i * dvdr * r_inv * wi_dr;
+  const float visc_du_term = 0.5f * visc_acc_term * dvdr_Hubble;
+  const float alpha_diff = (pressurei * pi->alpha_diff + pressurej * pj->alpha_diff) / (pressurei + pressurej);
+  const float v_diff =
+      alpha_diff * 0.5f * (sqrtf(2.f * fabsf(pressurei - pressurej) / rho_ij) + fabsf(fac_mu * r_inv * dvdr_Hubble));
+  const float diff_du_term = v_diff * (pi->u - pj->u) * (f_ij * wi_dr / rhoi + f_ji * wj_dr / rhoj);
+  const float du_dt_i = sph_du_term_i + visc_du_term + diff_du_term;
+  pi->u_dt += du_dt_i * mj;
+  pi->h_dt -= mj * dvdr * r_inv / rhoj * wi_dr;
+  if (pj->time_bin > 0) pi->min_ngb_time_bin = pi->min_ngb_time_bin < pj->time_bin ? pi->min_ngb_time_bin : pj->time_bin;
+  log_pair(c, 2, pi->id, pj->id);
+}
+
 /* runner_iact_nonsym_force: src/hydro/Minimal/hydro_iact.h:370-478,
  * src/hydro/Planetary/hydro_iact.h:369-476; plus runner_iact_nonsym_timebin
  * src/timestep_limiter_iact.h:41-55. */
 static inline void iact_force(octx *c, float r2, const float dx[3], float hi, float hj, opart *pi, const opart *pj) {
+  if (c->prm->scheme == ORACLE_SCHEME_SPHENIX) {
+    iact_force_sphenix(c, r2, dx, hi, hj, pi, pj);
+    return;
+  }
   const float a = c->a, H = c->H;
   const float fac_mu = 1.f; /* pow_three_gamma_minus_five_over_two(a), gamma=5/3: src/adiabatic_index.h:524-526 */
   const float a2_Hubble = a * a * H;
@@ -358,6 +461,7 @@ static inline void init_part(opart *p) {
   p->rho_dh = 0.f;
   p->div_v = 0.f;
   p->rot_v[0] = p->rot_v[1] = p->rot_v[2] = 0.f;
+  p->laplace_u = 0.f; /* SPHENIX/hydro.h:565-566 */
 }
 
 /* hydro_end_density: Minimal/hydro.h:543-575 (a2_inv = 1 without cosmology) */
@@ -393,11 +497,97 @@ static inline void no_neighbours(opart *p) {
   p->wcount_dh = 0.f;
   p->div_v = 0.f;
   p->rot_v[0] = p->rot_v[1] = p->rot_v[2] = 0.f;
+  p->laplace_u = 0.f; /* SPHENIX/hydro.h:789-806 also clears v_sig, which hydro_reset_gradient sets next */
+}
+
+/* SPHENIX: what runner_do_ghost does for a converged particle under EXTRA_HYDRO_LOOP
+ * (src/runner_ghost.c:1249-1264, 1429-1443): hydro_prepare_gradient + hydro_reset_gradient,
+ * SPHENIX/hydro.h:654-733 */
+static void prepare_gradient(const octx *c, opart *p) {
+  const float fac_B = 1.f; /* cosmo->a_factor_Balsara_eps at a = 1 */
+  const float curl_v = sqrtf(p->rot_v[0] * p->rot_v[0] + p->rot_v[1] * p->rot_v[1] + p->rot_v[2] * p->rot_v[2]);
+  const float abs_div_v = fabsf(p->div_v);
+  float pressure, soundspeed;
+  eos_eval(c, p, &pressure, &soundspeed);
+  const float balsara = abs_div_v / (abs_div_v + curl_v + 0.0001f * soundspeed * fac_B / p->h);
+  const float common_factor = p->h * DIM_INV_F / p->wcount;
+  float grad_h_term;
+  if (p->h > 0.9999f * c->prm->h_max) {
+    grad_h_term = 0.f;
+  } else {
+    const float grad_W_term = common_factor * p->wcount_dh;
+    if (grad_W_term < -0.9999f)
+      grad_h_term = 0.f;
+    else
+      grad_h_term = common_factor * p->rho_dh / (1.f + grad_W_term);
+  }
+  p->f = grad_h_term;
+  p->pressure = pressure;
+  p->soundspeed = soundspeed;
+  p->balsara = balsara;
+  /* hydro_reset_gradient */
+  p->v_sig = 2.f * p->soundspeed;
+  p->alpha_visc_max_ngb = p->alpha_visc;
+}
+
+/* SPHENIX: runner_do_extra_ghost for one active particle (src/runner_ghost.c:1027-1063):
+ * hydro_end_gradient (SPHENIX/hydro.h:745-761), hydro_prepare_force (:823-936) with
+ * dt_alpha = get_timestep(p->time_bin, time_base), hydro_reset_acceleration (:944-955).
+ * The cosmology factors (doubles in struct cosmology) are all 1: a product of two floats formed in
+ * double and rounded once is the float product. */
+static void extra_ghost_part(const octx *c, opart *p) {
+  const oracle_sphenix *sx = c->sx;
+  {
+    const float h_inv = 1.0f / p->h;
+    const float h_inv_dim = h_inv * h_inv * h_inv;
+    const float h_inv_dim_plus_one = h_inv_dim * h_inv;
+    p->laplace_u *= 2.f * h_inv_dim_plus_one;
+  }
+  const double dt_d = (p->time_bin <= 0 ? 0.0 : (double)(1LL << (p->time_bin + 1))) * sx->time_base;
+  const float dt_alpha = (float)dt_d;
+  const float kernel_support_physical = p->h * K_GAMMA;
+  const float kernel_support_physical_inv = 1.f / kernel_support_physical;
+  const float v_sig_physical = p->v_sig;
+  float pressure, soundspeed_physical;
+  eos_eval(c, p, &pressure, &soundspeed_physical);
+  const float sound_crossing_time_inverse = soundspeed_physical * kernel_support_physical_inv;
+  const float div_v_dt = dt_alpha == 0.f ? 0.f : (p->div_v - p->div_v_prev) / dt_alpha;
+  const float S = p->div_v < 0.f ? kernel_support_physical * kernel_support_physical * fmax_f(0.f, -1.f * div_v_dt) : 0.f;
+  const float soundspeed_square = soundspeed_physical * soundspeed_physical;
+  const float alpha_loc = sx->viscosity_alpha_max * S / (soundspeed_square + S);
+  if (alpha_loc > p->alpha_visc) {
+    p->alpha_visc = alpha_loc;
+  } else {
+    const float timescale_ratio = dt_alpha * sound_crossing_time_inverse * sx->viscosity_length;
+    p->alpha_visc += alpha_loc * timescale_ratio;
+    p->alpha_visc /= (1.f + timescale_ratio);
+  }
+  p->alpha_visc = fmax_f(p->alpha_visc, sx->viscosity_alpha_min);
+  p->div_v_prev = p->div_v;
+  p->div_v_dt = div_v_dt;
+  const float diffusion_timescale_physical_inverse = v_sig_physical * kernel_support_physical_inv;
+  const float sqrt_u_inv = 1.f / sqrtf(p->u);
+  float alpha_diff_dt = sx->diffusion_beta * kernel_support_physical * p->laplace_u * sqrt_u_inv;
+  alpha_diff_dt -= (p->alpha_diff - sx->diffusion_alpha_min) * diffusion_timescale_physical_inverse;
+  float new_diffusion_alpha = p->alpha_diff;
+  new_diffusion_alpha += alpha_diff_dt * dt_alpha;
+  new_diffusion_alpha = fmax_f(new_diffusion_alpha, sx->diffusion_alpha_min);
+  const float viscous_diffusion_limit =
+      sx->diffusion_alpha_max * (1.f - p->alpha_visc_max_ngb / sx->viscosity_alpha_max);
+  new_diffusion_alpha = fmin_f(new_diffusion_alpha, viscous_diffusion_limit);
+  p->alpha_diff = new_diffusion_alpha;
+  p->a[0] = p->a[1] = p->a[2] = 0.0f;
+  p->u_dt = 0.0f;
+  p->h_dt = 0.0f;
 }
 
 /* hydro_prepare_force + hydro_reset_acceleration:
  * Minimal/hydro.h:669-761, Planetary/hydro.h:667-768 */
 static void prepare_force(const octx *c, opart *p) {
+  if (c->prm->scheme == ORACLE_SCHEME_SPHENIX) {
+    prepare_gradient(c, p);
+    return;
+  }
   const int planetary = c->prm->scheme == ORACLE_SCHEME_PLANETARY;
   const float fac_Balsara_eps = 1.f; /* a_factor_Balsara_eps at a = 1 */
   const float h_inv = 1.f / p->h;
@@ -1053,6 +1243,7 @@ static void ghost(octx *c, ocell *cell) {
           h_new = 2.f * h_old;
         } else {
           end_density(p);
+          if (prm->scheme == ORACLE_SCHEME_SPHENIX) p->div_v += c->H * DIM_F; /* SPHENIX/hydro.h:633-634 */
           const float n_sum = p->wcount * h_old_dim;
           const float n_target = hydro_eta_dim;
           const float f = n_sum - n_target;
@@ -1407,11 +1598,28 @@ static void cell_add_task(ocell *c, int t) {
   c->tasks[c->ntasks++] = t;
 }
 
+static int run_step(const oracle_params *prm, const oracle_eos *eos, oracle_parts *io, int ncells,
+                    const oracle_cell *cd, int ntasks, const oracle_task *td, oracle_pairlog *log, oracle_sphenix *sx);
+
 int oracle_run_step(const oracle_params *prm, const oracle_eos *eos, oracle_parts *io, int ncells,
                     const oracle_cell *cd, int ntasks, const oracle_task *td, oracle_pairlog *log) {
+  if (prm->scheme == ORACLE_SCHEME_SPHENIX) return 4; /* the three-loop scheme: oracle_run_step_sphenix */
+  return run_step(prm, eos, io, ncells, cd, ntasks, td, log, NULL);
+}
+
+int oracle_run_step_sphenix(const oracle_params *prm, oracle_parts *io, int ncells, const oracle_cell *cd, int ntasks,
+                            const oracle_task *td, oracle_pairlog *log, oracle_sphenix *sx) {
+  if (prm->scheme != ORACLE_SCHEME_SPHENIX || sx == NULL) return 4;
+  return run_step(prm, NULL, io, ncells, cd, ntasks, td, log, sx);
+}
+
+static int run_step(const oracle_params *prm, const oracle_eos *eos, oracle_parts *io, int ncells,
+                    const oracle_cell *cd, int ntasks, const oracle_task *td, oracle_pairlog *log, oracle_sphenix *sx) {
   const int n = io->n;
   octx c;
   memset(&c, 0, sizeof(c));
+  c.sx = sx;
+  if (sx) sx->grad_count = 0;
   c.prm = prm;
   c.eos = eos;
   c.tasks = td;
@@ -1441,6 +1649,11 @@ int oracle_run_step(const oracle_params *prm, const oracle_eos *eos, oracle_part
     p->id = io->id[k];
     p->time_bin = io->time_bin ? io->time_bin[k] : 1;
     p->min_ngb_time_bin = NUM_TIME_BINS + 1;
+    if (sx) {
+      p->alpha_visc = sx->in_alpha_visc ? sx->in_alpha_visc[k] : prm->viscosity_alpha;
+      p->alpha_diff = sx->in_alpha_diff ? sx->in_alpha_diff[k] : 0.f;
+      p->div_v_prev = sx->in_div_v_prev ? sx->in_div_v_prev[k] : 0.f;
+    }
     /* only active particles are re-initialised (src/cell_drift.c:342); the others keep
      * what their last active step left in struct part */
     if (part_active(&c, p)) {
@@ -1516,6 +1729,37 @@ int oracle_run_step(const oracle_params *prm, const oracle_eos *eos, oracle_part
     if (io->g_pressure) io->g_pressure[k] = p->pressure;
     if (io->g_soundspeed) io->g_soundspeed[k] = p->soundspeed;
     if (io->g_balsara) io->g_balsara[k] = p->balsara;
+    if (sx && sx->g_div_v) sx->g_div_v[k] = p->div_v;
+  }
+
+  if (sx) {
+    /* gradient loop (the density walks with runner_iact_nonsym_gradient), then runner_do_extra_ghost */
+    c.stage = 3;
+    for (int t = 0; t < ntasks; t++) {
+      ocell *ci = &c.cells[td[t].ci];
+      ocell *cj = td[t].cj >= 0 ? &c.cells[td[t].cj] : NULL;
+      switch (td[t].type) {
+        case ORACLE_TASK_SELF: self_density_branch(&c, ci); break;
+        case ORACLE_TASK_PAIR: pair_density_branch(&c, ci, cj); break;
+        case ORACLE_TASK_SUB_SELF: sub_self(&c, ci, 0); break;
+        default: sub_pair(&c, ci, cj, 0); break;
+      }
+    }
+    for (int k = 0; k < n; k++) {
+      const opart *p = &c.parts[k];
+      if (sx->r_v_sig) sx->r_v_sig[k] = p->v_sig;
+      if (sx->r_laplace_u) sx->r_laplace_u[k] = p->laplace_u;
+      if (sx->r_alpha_visc_max_ngb) sx->r_alpha_visc_max_ngb[k] = p->alpha_visc_max_ngb;
+    }
+    for (int k = 0; k < n; k++) {
+      opart *p = &c.parts[k];
+      if (part_active(&c, p)) extra_ghost_part(&c, p);
+      if (sx->e_laplace_u) sx->e_laplace_u[k] = p->laplace_u;
+      if (sx->e_alpha_visc) sx->e_alpha_visc[k] = p->alpha_visc;
+      if (sx->e_alpha_diff) sx->e_alpha_diff[k] = p->alpha_diff;
+      if (sx->e_div_v_prev) sx->e_div_v_prev[k] = p->div_v_prev;
+      if (sx->e_div_v_dt) sx->e_div_v_dt[k] = p->div_v_dt;
+    }
   }
 
   /* force */

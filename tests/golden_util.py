@@ -28,6 +28,28 @@ def load(name):
     return g
 
 
+SPHENIX_DIR = os.path.join(GOLDEN_DIR, "sphenix")
+
+
+def sphenix_names():
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(SPHENIX_DIR, "*.npz")))
+
+
+def load_sphenix(name):
+    """A fixture of the three-loop scheme (tests/golden/make_golden_sphenix.py): as load(), plus the hydro_props
+    of the scheme (g["props"]) and the viscosity / diffusion state among the inputs."""
+    z = np.load(os.path.join(SPHENIX_DIR, name + ".npz"))
+    g = {k: z[k] for k in z.files}
+    g["params"] = ast.literal_eval(str(g["params"]))
+    g["props"] = ast.literal_eval(str(g["props"]))
+    g["variant"] = str(g["variant"])
+    g["ic"] = {"x": g["x"], "v": g["v"], "mass": g["mass"], "h": g["h"], "u": g["u"], "id": g["id"],
+               "mat_id": None, "time_bin": g.get("time_bin")}
+    for k in ("in_rho", "in_pressure", "in_f", "in_soundspeed", "in_balsara") + tuple(ol.SPHENIX_IN):
+        g["ic"][k] = g.get(k)
+    return g
+
+
 def tree_structs(g, cell_cls=ol.Cell, task_cls=ol.Task):
     """ctypes arrays of the stored tree and task list."""
     n = len(g["cell_ints"])

@@ -58,6 +58,25 @@ class PairLog(C.Structure):
                 ("count", C.c_longlong * 3), ("ghost_sweeps", C.c_int)]
 
 
+class Sphenix(C.Structure):
+    """oracle_sphenix (oracle/oracle_api.h): what the three-loop scheme adds to Params / Parts / PairLog."""
+    _fields_ = [("viscosity_alpha_max", C.c_float), ("viscosity_alpha_min", C.c_float),
+                ("viscosity_length", C.c_float), ("diffusion_beta", C.c_float), ("diffusion_alpha_max", C.c_float),
+                ("diffusion_alpha_min", C.c_float), ("time_base", C.c_double),
+                ("in_alpha_visc", _FP), ("in_alpha_diff", _FP), ("in_div_v_prev", _FP),
+                ("g_div_v", _FP), ("r_v_sig", _FP), ("r_laplace_u", _FP), ("r_alpha_visc_max_ngb", _FP),
+                ("e_laplace_u", _FP), ("e_alpha_visc", _FP), ("e_alpha_diff", _FP), ("e_div_v_prev", _FP),
+                ("e_div_v_dt", _FP),
+                ("grad_pairs", C.POINTER(C.c_longlong)), ("grad_capacity", C.c_longlong), ("grad_count", C.c_longlong)]
+
+
+SPHENIX_OUT = ("g_div_v", "r_v_sig", "r_laplace_u", "r_alpha_visc_max_ngb", "e_laplace_u", "e_alpha_visc",
+               "e_alpha_diff", "e_div_v_prev", "e_div_v_dt")
+SPHENIX_IN = ("in_alpha_visc", "in_alpha_diff", "in_div_v_prev")
+# hydro_props defaults of the scheme (src/hydro/SPHENIX/hydro_parameters.h:53-101) and the harness's time base
+SPHENIX_PROPS = dict(viscosity_alpha=0.1, viscosity_alpha_max=2.0, viscosity_alpha_min=0.0, viscosity_length=0.05,
+                     diffusion_beta=1.0, diffusion_alpha_max=1.0, diffusion_alpha_min=0.0, time_base=1e-3)
+
 OUT_FIELDS = {"d_rho": 1, "d_rho_dh": 1, "d_wcount": 1, "d_wcount_dh": 1, "d_div_v": 1, "d_rot_v": 3,
               "g_h": 1, "g_rho": 1, "g_f": 1, "g_pressure": 1, "g_soundspeed": 1, "g_balsara": 1,
               "f_a": 3, "f_u_dt": 1, "f_h_dt": 1, "f_v_sig": 1}
@@ -78,6 +97,7 @@ def oracle():
         lib.oracle_build_tree.restype = C.c_int
         lib.oracle_build_tasks.restype = C.c_int
         lib.oracle_run_step.restype = C.c_int
+        lib.oracle_run_step_sphenix.restype = C.c_int
         lib.oracle_free.argtypes = [C.c_void_p]
         _libs["oracle"] = lib
     return _libs["oracle"]
@@ -92,6 +112,7 @@ def ref(variant="minimal"):
     if key not in _libs:
         lib = C.CDLL(os.path.join(ORACLE_DIR, "_ref", "libswiftref_%s.so" % variant))
         lib.ref_run_step.restype = C.c_int
+        lib.ref_run_step_sphenix.restype = C.c_int
         lib.ref_get_eos.restype = C.c_int
         _libs[key] = lib
     return _libs[key]
@@ -171,9 +192,13 @@ def build_tree_and_tasks(prm, x, h):
     return order, cells, tuple(cdim), tasks, ntasks.value
 
 
-def run_step(which, prm, ic, cells, tasks, ntasks, record=False, pair_capacity=None, eos=None, variant="minimal"):
+def run_step(which, prm, ic, cells, tasks, ntasks, record=False, pair_capacity=None, eos=None, variant="minimal",
+             sphenix=None):
     """ic: dict with x[n,3] f64, v[n,3], mass, h, u (f32), id (i64), optional mat_id, time_bin -- already in CELL ORDER.
-    which: 'oracle' or 'ref'.  Returns dict of outputs (+ 'pairs', 'counts', 'ghost_sweeps')."""
+    which: 'oracle' or 'ref'.  Returns dict of outputs (+ 'pairs', 'counts', 'ghost_sweeps').
+    sphenix: dict of the SPHENIX hydro_props (SPHENIX_PROPS keys; prm.scheme must be 2): runs the three-loop
+    scheme; ic may hold in_alpha_visc / in_alpha_diff / in_div_v_prev; the outputs gain SPHENIX_OUT,
+    counts[3] and pairs[3] (the gradient loop)."""
     n = len(ic["h"])
     keep = []
 
@@ -217,6 +242,40 @@ def run_step(which, prm, ic, cells, tasks, ntasks, record=False, pair_capacity=N
             log.pairs[s] = b.ctypes.data_as(C.POINTER(C.c_longlong))
             log.capacity[s] = cap
     ncells = len(cells)
+    if sphenix is not None:
+        S = Sphenix()
+        for k in ("viscosity_alpha_max", "viscosity_alpha_min", "viscosity_length", "diffusion_beta",
+                  "diffusion_alpha_max", "diffusion_alpha_min", "time_base"):
+            setattr(S, k, sphenix[k])
+        for k in SPHENIX_IN:
+            if ic.get(k) is not None:
+                setattr(S, k, arr(ic[k], np.float32).ctypes.data_as(_FP))
+        for k in SPHENIX_OUT:
+            out[k] = np.zeros(n, dtype=np.float32)
+            setattr(S, k, out[k].ctypes.data_as(_FP))
+        gb = None
+        if record:
+            gb = np.zeros((pair_capacity or (n * 400), 2), dtype=np.int64)
+            S.grad_pairs = gb.ctypes.data_as(C.POINTER(C.c_longlong))
+            S.grad_capacity = len(gb)
+        if which == "oracle":
+            rc = oracle().oracle_run_step_sphenix(C.byref(prm), C.byref(P), ncells, cells, ntasks, tasks, C.byref(log),
+                                                  C.byref(S))
+        else:
+            rc = ref("sphenix").ref_run_step_sphenix(C.byref(prm), C.byref(P), ncells, cells, ntasks, tasks,
+                                                     C.byref(log), C.byref(S))
+        if rc != 0:
+            raise RuntimeError("%s run_step_sphenix rc=%d" % (which, rc))
+        out["counts"] = [int(log.count[s]) for s in range(3)] + [int(S.grad_count)]
+        out["ghost_sweeps"] = int(log.ghost_sweeps)
+        if record:
+            assert S.grad_count <= S.grad_capacity, "pair buffer too small"
+            out["pairs"] = []
+            for s in range(3):
+                assert log.count[s] <= log.capacity[s], "pair buffer too small"
+                out["pairs"].append(bufs[s][:log.count[s]].copy())
+            out["pairs"].append(gb[:S.grad_count].copy())
+        return out
     if which == "oracle":
         e = eos if eos is not None else Eos()
         rc = oracle().oracle_run_step(C.byref(prm), C.byref(e), C.byref(P), ncells, cells, ntasks, tasks, C.byref(log))
