@@ -31,9 +31,11 @@
 extern "C" {
 #endif
 
-#define SWIFT_CUDA_ABI_VERSION 2
+#define SWIFT_CUDA_ABI_VERSION 3
 
-enum { SWIFT_CUDA_SCHEME_MINIMAL = 0, SWIFT_CUDA_SCHEME_PLANETARY = 1 };
+/* SPHENIX (the reference's configure default, configure.ac:1958-1959) is the three-loop scheme: see the
+ * "SPHENIX" section below for what it adds and which entries support it. */
+enum { SWIFT_CUDA_SCHEME_MINIMAL = 0, SWIFT_CUDA_SCHEME_PLANETARY = 1, SWIFT_CUDA_SCHEME_SPHENIX = 2 };
 
 /* How the per-particle FIELDS are computed.  Which pairs interact -- the neighbour lists and
  * counts of every loop, and therefore h -- is bit-exact in both modes.
@@ -155,7 +157,7 @@ typedef struct swift_cuda_ctx swift_cuda_ctx;
 int swift_cuda_abi_version(void);
 /* sizeof of the ABI structs as compiled into the library, for binding checks:
  * 0 params, 1 cell, 2 task, 3 parts_in, 4 parts_out, 5 counters, 6 timings, 7 til, 8 integrator,
- * 9 state_out, 10 part_layout. */
+ * 9 state_out, 10 part_layout, 11 sphenix_props, 12 sphenix_in, 13 sphenix_out. */
 size_t swift_cuda_sizeof(int which);
 const char *swift_cuda_last_error(void);
 
@@ -366,6 +368,69 @@ int swift_cuda_reset_offsets(swift_cuda_ctx *ctx, int what);
 int swift_cuda_get_state(swift_cuda_ctx *ctx, const swift_cuda_state_out *out);
 /* Device time (CUDA events on the context's stream) of the last drift, kick1, kick2, timestep, ms. */
 int swift_cuda_get_integrator_timings(swift_cuda_ctx *ctx, float ms[4]);
+
+/* ---- SPHENIX: the gradient loop and the extra ghost -------------------------
+ * params.scheme = SWIFT_CUDA_SCHEME_SPHENIX (+ ideal gas) turns the step into the reference's
+ * EXTRA_HYDRO_LOOP subgraph (src/engine_maketasks.c:2306-2317, src/runner_main.c:199-200, 249-250,
+ * 297-298, 343-344, 420-421):
+ *
+ *   sort -> density -> ghost -> GRADIENT (self/pair/sub) -> extra_ghost -> force -> end_force
+ *
+ *   runner_do{self,pair}1_branch_gradient, runner_dosub_{self,pair}1_gradient   src/runner_doiact_hydro.h:168-191
+ *     with runner_iact_nonsym_gradient                                          src/hydro/SPHENIX/hydro_iact.h:272-329
+ *   runner_do_ghost: hydro_prepare_gradient + hydro_reset_gradient at convergence   src/runner_ghost.c:1249-1264
+ *   runner_do_extra_ghost: hydro_end_gradient, hydro_prepare_force (the viscosity and diffusion
+ *     alphas evolve over dt_alpha = get_timestep(p->time_bin, e->time_base)), hydro_reset_acceleration
+ *                                                                               src/runner_ghost.c:992-1075
+ *   runner_iact_nonsym_force of the scheme                                      src/hydro/SPHENIX/hydro_iact.h:488-609
+ *
+ * Supported entries: swift_cuda_build_from_particles / _from_cells, swift_cuda_update_particles,
+ * swift_cuda_step, swift_cuda_do_*, swift_cuda_get_results (v_sig = p->viscosity.v_sig, d_div_v the raw
+ * first-pass sum), the pair recorder (loop 3 = gradient) and the entries below.  fields_mode must be EXACT.
+ * The struct part entries, swift_cuda_step_io, the halo entries and the time-integration entries refuse a
+ * SPHENIX context (the 160-byte record, the wider halo and the scheme's drift / kick are not built). */
+typedef struct {
+  float viscosity_alpha_max;  /* hydro_props->viscosity.alpha_max, SPH:viscosity_alpha_max (2.0) */
+  float viscosity_alpha_min;  /* ->viscosity.alpha_min (0.0) */
+  float viscosity_length;     /* ->viscosity.length (0.05) */
+  float diffusion_alpha;      /* ->diffusion.alpha: initial value of p->diffusion.alpha (0.0) */
+  float diffusion_beta;       /* ->diffusion.beta (1.0) */
+  float diffusion_alpha_max;  /* ->diffusion.alpha_max (1.0) */
+  float diffusion_alpha_min;  /* ->diffusion.alpha_min (0.0) */
+  double time_base;           /* e->time_base */
+} swift_cuda_sphenix_props;
+/* Before the build call.  Without it a SPHENIX context uses the defaults of
+ * src/hydro/SPHENIX/hydro_parameters.h:53-101 and time_base = 1e-3; params.viscosity_alpha is
+ * hydro_props->viscosity.alpha, the initial p->viscosity.alpha. */
+int swift_cuda_sphenix_set_props(swift_cuda_ctx *ctx, const swift_cuda_sphenix_props *props);
+
+/* The state the scheme carries in struct part from step to step, host arrays in the caller's particle
+ * order; NULL: left as it is on the device (after a build: the initial values of the props). */
+typedef struct {
+  const float *alpha_visc;          /* p->viscosity.alpha */
+  const float *alpha_diff;          /* p->diffusion.alpha */
+  const float *div_v_previous_step; /* p->viscosity.div_v_previous_step */
+} swift_cuda_sphenix_in;
+int swift_cuda_sphenix_set_state(swift_cuda_ctx *ctx, const swift_cuda_sphenix_in *in);
+
+/* Results, host arrays in the caller's particle order, any pointer may be NULL. */
+typedef struct {
+  float *div_v;               /* p->viscosity.div_v (after the ghost) */
+  float *laplace_u;           /* p->diffusion.laplace_u: the raw sum after the gradient loop, x 2 / h^(d+1) after the extra ghost */
+  float *alpha_visc_max_ngb;  /* p->force.alpha_visc_max_ngb */
+  float *alpha_visc;          /* p->viscosity.alpha */
+  float *alpha_diff;          /* p->diffusion.alpha */
+  float *div_v_previous_step; /* p->viscosity.div_v_previous_step */
+  float *div_v_dt;            /* p->viscosity.div_v_dt */
+} swift_cuda_sphenix_out;
+int swift_cuda_sphenix_get_results(swift_cuda_ctx *ctx, const swift_cuda_sphenix_out *out);
+
+/* Operator-level entries of the two phases the scheme adds (swift_cuda_step runs them between
+ * swift_cuda_do_ghost and swift_cuda_do_force). */
+int swift_cuda_do_gradient(swift_cuda_ctx *ctx);
+int swift_cuda_do_extra_ghost(swift_cuda_ctx *ctx);
+/* ordered hits of the gradient loop in the last step (swift_cuda_counters keeps its layout) */
+int swift_cuda_sphenix_get_counter(swift_cuda_ctx *ctx, long long *n_gradient);
 
 /* ---- Allocation-free time-step entry ----------------------------------------------------------
  * No counterpart in the reference: added for callers that

@@ -17,7 +17,7 @@ ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "libswiftcuda.so")
 CSRC = os.path.join(_HERE, "csrc")
 
-SCHEME_MINIMAL, SCHEME_PLANETARY = 0, 1
+SCHEME_MINIMAL, SCHEME_PLANETARY, SCHEME_SPHENIX = 0, 1, 2
 FIELDS_EXACT, FIELDS_FAST = 0, 1
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -27,7 +27,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 def build_library(verbose=False, force=False):
     """Compiles the CUDA backend in-tree with nvcc for sm_100a."""
     srcs = [os.path.join(CSRC, f) for f in ("swift_cuda.cu", "host_tree.cpp")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.cuh", "leaf_kernels.cuh", "list_kernels.cuh", "force_fast.cuh", "integrate.cuh", "pack.cuh", "device_types.cuh", "host_tree.hpp")] + \
+    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.cuh", "leaf_kernels.cuh", "list_kernels.cuh", "force_fast.cuh", "integrate.cuh", "pack.cuh", "sphenix.cuh", "device_types.cuh", "host_tree.hpp")] + \
         [os.path.join(ROOT, "include", "swift_cuda.h")]
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
         return LIB_PATH
@@ -137,7 +137,28 @@ EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error
            "swift_cuda_timestep", "swift_cuda_reset_offsets", "swift_cuda_get_state",
            "swift_cuda_get_integrator_timings",
            "swift_cuda_build_from_cells_parts", "swift_cuda_build_from_parts", "swift_cuda_step_parts",
-           "swift_cuda_set_max_active_bin", "swift_cuda_timestep_static"]
+           "swift_cuda_set_max_active_bin", "swift_cuda_timestep_static",
+           "swift_cuda_sphenix_set_props", "swift_cuda_sphenix_set_state", "swift_cuda_sphenix_get_results",
+           "swift_cuda_sphenix_get_counter", "swift_cuda_do_gradient", "swift_cuda_do_extra_ghost"]
+
+
+class SphenixProps(C.Structure):
+    # field order must match swift_cuda_sphenix_props
+    _fields_ = [("viscosity_alpha_max", C.c_float), ("viscosity_alpha_min", C.c_float), ("viscosity_length", C.c_float),
+                ("diffusion_alpha", C.c_float), ("diffusion_beta", C.c_float), ("diffusion_alpha_max", C.c_float),
+                ("diffusion_alpha_min", C.c_float), ("time_base", C.c_double)]
+
+
+class SphenixIn(C.Structure):
+    _fields_ = [("alpha_visc", _FP), ("alpha_diff", _FP), ("div_v_previous_step", _FP)]
+
+
+SPHENIX_OUT_FIELDS = ("div_v", "laplace_u", "alpha_visc_max_ngb", "alpha_visc", "alpha_diff", "div_v_previous_step",
+                      "div_v_dt")
+
+
+class SphenixOut(C.Structure):
+    _fields_ = [(k, _FP) for k in SPHENIX_OUT_FIELDS]
 
 
 class PartLayout(C.Structure):
@@ -227,6 +248,11 @@ def load_library():
         lib.swift_cuda_timestep.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         lib.swift_cuda_reset_offsets.argtypes = [C.c_void_p, C.c_int]
         lib.swift_cuda_timestep_static.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        for name in ("swift_cuda_sphenix_set_props", "swift_cuda_sphenix_set_state", "swift_cuda_sphenix_get_results",
+                     "swift_cuda_sphenix_get_counter"):
+            getattr(lib, name).argtypes = [C.c_void_p, C.c_void_p]
+        lib.swift_cuda_do_gradient.argtypes = [C.c_void_p]
+        lib.swift_cuda_do_extra_ghost.argtypes = [C.c_void_p]
         _lib = lib
     return _lib
 
@@ -442,6 +468,45 @@ class HydroBackend:
     def runner_do_force(self):
         """All runner_do{self,pair}2_branch_force tasks + runner_do_end_hydro_force."""
         self._check(self.lib.swift_cuda_do_force(self.ctx))
+
+    # ---- SPHENIX (SURVEY.md 8(f) N1): the gradient loop and the extra ghost ----
+    def sphenix_set_props(self, viscosity_alpha_max=2.0, viscosity_alpha_min=0.0, viscosity_length=0.05,
+                          diffusion_alpha=0.0, diffusion_beta=1.0, diffusion_alpha_max=1.0, diffusion_alpha_min=0.0,
+                          time_base=1e-3, **_ignored):
+        """hydro_props->viscosity / ->diffusion of the scheme and e->time_base; before the build."""
+        p = SphenixProps(viscosity_alpha_max, viscosity_alpha_min, viscosity_length, diffusion_alpha, diffusion_beta,
+                         diffusion_alpha_max, diffusion_alpha_min, time_base)
+        self._check(self.lib.swift_cuda_sphenix_set_props(self.ctx, C.byref(p)))
+
+    def sphenix_set_state(self, alpha_visc=None, alpha_diff=None, div_v_previous_step=None):
+        """p->viscosity.alpha, p->diffusion.alpha, p->viscosity.div_v_previous_step (caller order); after the build."""
+        S = SphenixIn()
+        keep = []
+        for k, a in (("alpha_visc", alpha_visc), ("alpha_diff", alpha_diff), ("div_v_previous_step", div_v_previous_step)):
+            if a is not None:
+                a = np.ascontiguousarray(a, dtype=np.float32)
+                assert len(a) == self.n
+                keep.append(a)
+                setattr(S, k, a.ctypes.data_as(_FP))
+        self._check(self.lib.swift_cuda_sphenix_set_state(self.ctx, C.byref(S)))
+
+    def sphenix_results(self):
+        out = {k: np.zeros(self.n, dtype=np.float32) for k in SPHENIX_OUT_FIELDS}
+        O = SphenixOut()
+        for k in SPHENIX_OUT_FIELDS:
+            setattr(O, k, out[k].ctypes.data_as(_FP))
+        self._check(self.lib.swift_cuda_sphenix_get_results(self.ctx, C.byref(O)))
+        n = C.c_longlong(0)
+        self._check(self.lib.swift_cuda_sphenix_get_counter(self.ctx, C.byref(n)))
+        out["n_gradient"] = n.value
+        return out
+
+    def runner_do_gradient(self):
+        """All runner_do{self,pair}1_branch_gradient / runner_dosub_*1_gradient tasks."""
+        self._check(self.lib.swift_cuda_do_gradient(self.ctx))
+
+    def runner_do_extra_ghost(self):
+        self._check(self.lib.swift_cuda_do_extra_ghost(self.ctx))
 
     # ---- time integration (SURVEY.md 8(f) N3): the particles stay on the device across steps ----
     def integrator_init(self, cfl_condition, log_max_h_change, minimal_internal_energy, dt_min, dt_max, time_base,

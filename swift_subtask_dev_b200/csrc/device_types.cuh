@@ -32,6 +32,11 @@ struct Consts {
   swift_cuda_til til[8];
   float idg_gamma[4];
   double axis[13][3];   // runner_shift
+  // SPHENIX (appended: the offsets above are what the two-loop kernels were compiled against):
+  // hydro_props->viscosity.{alpha_max, alpha_min, length}, ->diffusion.{beta, alpha_max, alpha_min}, e->time_base
+  float visc_alpha_max, visc_alpha_min, visc_length;
+  float diff_beta, diff_alpha_max, diff_alpha_min;
+  double time_base;
 };
 
 struct CellDev {
@@ -134,8 +139,15 @@ struct Dev {
   int no_end_force;
   // pair recording (test hook)
   long long *rec_pairs[3];
-  unsigned long long *rec_count;  // [3]
+  unsigned long long *rec_count;  // [4]
   long long rec_capacity;
+  // ---- SPHENIX only (null otherwise; appended, see Consts) ----
+  float4 *sph_state;   // p->viscosity.alpha, p->diffusion.alpha, p->viscosity.div_v_previous_step, p->viscosity.div_v_dt
+  float4 *sph_grad;    // p->viscosity.div_v, p->diffusion.laplace_u, p->force.alpha_visc_max_ngb, unused
+  float4 *gin;         // what a gradient-loop neighbour is read for: u, rho, soundspeed, viscosity.alpha
+  float4 *sx;          // the rest of a force-loop neighbour: viscosity.alpha, diffusion.alpha, u, unused
+  long long *rec_grad; // pair recording of the gradient loop (counter: rec_count[3])
+  long long pad_;      // keeps sizeof(Dev) a multiple of 16: kernel arguments after Dev stay 16-byte aligned
 };
 
 }  // namespace swiftcuda

@@ -125,11 +125,13 @@ struct ForceI {  // per-i quantities hoisted out of the neighbour loop
   float h, hi_inv, hid_inv, m, rho, P, f, c, bal, vx, vy, vz;
   float Pr2;  // P / rho^2
   float m_inv;  // FAST form: 1 / m
+  float alpha, adiff, u;  // SPHENIX: p->viscosity.alpha, p->diffusion.alpha, p->u
 };
 struct ForceJ {
   float h, m, rho, P, f, c, bal, vx, vy, vz;
   float Pr2;  // P / rho^2, formed once per particle by the ghost
   int bin;
+  float alpha, adiff, u;  // SPHENIX
 };
 
 // runner_iact_nonsym_force: Minimal/hydro_iact.h:370-478, Planetary/hydro_iact.h:369-476
@@ -257,11 +259,97 @@ __device__ __forceinline__ void iact_force_fast(ForceAcc &a, float r2, float dx,
   if (pj.bin > 0) a.min_bin = min(a.min_bin, pj.bin);
 }
 
+// ---- SPHENIX: the gradient loop's interaction and the scheme's force interaction ----
+struct GradAcc {
+  float v_sig, lap, amax;  // p->viscosity.v_sig, p->diffusion.laplace_u, p->force.alpha_visc_max_ngb
+  float div_v;             // carried through (the record sph_grad holds it next to the two sums)
+};
+
+// runner_iact_nonsym_gradient, src/hydro/SPHENIX/hydro_iact.h:272-329.  gi / gj: the gradient-loop
+// record of a particle {u, rho, soundspeed, viscosity.alpha}.  max() is the reference's macro (a > b ? a : b).
+__device__ __forceinline__ void iact_gradient(GradAcc &a, float r2, float dx, float dy, float dz, float hi,
+                                              const float4 vmi, const float4 gi, const float4 vmj, const float4 gj) {
+  const float r = sqrtf(r2);
+  const float r_inv = r ? 1.0f / r : 0.0f;
+  const float fac_mu = 1.f;
+  const float a2_Hubble = kc.a * kc.a * kc.H;
+  const float dvdr = (vmi.x - vmj.x) * dx + (vmi.y - vmj.y) * dy + (vmi.z - vmj.z) * dz;
+  const float dvdr_Hubble = dvdr + a2_Hubble * r2;
+  const float omega_ij = dvdr_Hubble < 0.f ? dvdr_Hubble : 0.f;
+  const float mu_ij = fac_mu * r_inv * omega_ij;
+  const float new_v_sig = gi.z + gj.z - kc.beta * mu_ij;  // hydro_signal_velocity, SPHENIX/hydro.h:490-498
+  a.v_sig = a.v_sig > new_v_sig ? a.v_sig : new_v_sig;
+  float wi, wi_dx;
+  const float ui = r / hi;
+  kernel_deval(ui, wi, wi_dx);
+  const float delta_u_factor = (gi.x - gj.x) * r_inv;
+  a.lap += vmj.w * delta_u_factor * wi_dx / gj.y;
+  a.amax = a.amax > gj.w ? a.amax : gj.w;
+}
+
+// runner_iact_nonsym_force of SPHENIX, src/hydro/SPHENIX/hydro_iact.h:488-609 (+ runner_iact_nonsym_timebin).
+// v_sig is not touched by this scheme's force loop.
+__device__ __forceinline__ void iact_force_sphenix(ForceAcc &a, float r2, float dx, float dy, float dz,
+                                                   const ForceI &pi, const ForceJ &pj) {
+  const float fac_mu = 1.f;
+  const float a2_Hubble = kc.a * kc.a * kc.H;
+  const float r = sqrtf(r2);
+  const float r_inv = r ? 1.0f / r : 0.0f;
+  const float xi = r * pi.hi_inv;
+  float wi, wi_dx;
+  kernel_deval(xi, wi, wi_dx);
+  const float wi_dr = pi.hid_inv * wi_dx;
+  const float hj_inv = 1.0f / pj.h;
+  const float hj2 = hj_inv * hj_inv;
+  const float hjd_inv = hj2 * hj2;
+  const float xj = r * hj_inv;
+  float wj, wj_dx;
+  kernel_deval(xj, wj, wj_dx);
+  const float wj_dr = hjd_inv * wj_dx;
+  const float dvdr = (pi.vx - pj.vx) * dx + (pi.vy - pj.vy) * dy + (pi.vz - pj.vz) * dz;
+  const float dvdr_Hubble = dvdr + a2_Hubble * r2;
+  const float omega_ij = dvdr_Hubble < 0.f ? dvdr_Hubble : 0.f;
+  const float mu_ij = fac_mu * r_inv * omega_ij;
+  const float v_sig = pi.c + pj.c - kc.beta * mu_ij;
+  const float f_ij = 1.f - pi.f / pj.m;
+  const float f_ji = 1.f - pj.f / pi.m;
+  const float rho_ij = pi.rho + pj.rho;
+  const float alpha = pi.alpha + pj.alpha;
+  const float visc = -0.25f * alpha * v_sig * mu_ij * (pi.bal + pj.bal) / rho_ij;
+  const float visc_acc_term = 0.5f * visc * (wi_dr * f_ij + wj_dr * f_ji) * r_inv;
+  const float P_over_rho2_i = pi.Pr2 * f_ij;  // pressure / (rho * rho) * f
+  const float P_over_rho2_j = pj.Pr2 * f_ji;
+  const float sph_acc_term = (P_over_rho2_i * wi_dr + P_over_rho2_j * wj_dr) * r_inv;
+  const float acc = sph_acc_term + visc_acc_term;
+  a.ax -= pj.m * acc * dx;
+  a.ay -= pj.m * acc * dy;
+  a.az -= pj.m * acc * dz;
+  const float sph_du_term_i = P_over_rho2_i * dvdr * r_inv * wi_dr;
+  const float visc_du_term = 0.5f * visc_acc_term * dvdr_Hubble;
+  const float alpha_diff = (pi.P * pi.adiff + pj.P * pj.adiff) / (pi.P + pj.P);
+  const float v_diff =
+      alpha_diff * 0.5f * (sqrtf(2.f * fabsf(pi.P - pj.P) / rho_ij) + fabsf(fac_mu * r_inv * dvdr_Hubble));
+  const float diff_du_term = v_diff * (pi.u - pj.u) * (f_ij * wi_dr / pi.rho + f_ji * wj_dr / pj.rho);
+  const float du_dt_i = sph_du_term_i + visc_du_term + diff_du_term;
+  a.u_dt += du_dt_i * pj.m;
+  a.h_dt -= pj.m * dvdr * r_inv / pj.rho * wi_dr;
+  if (pj.bin > 0) a.min_bin = min(a.min_bin, pj.bin);
+}
+
 __device__ __forceinline__ void record_pair(const Dev &d, int loop, long long i, long long j) {
   const unsigned long long k = atomicAdd(&d.rec_count[loop], 1ULL);
   if ((long long)k < d.rec_capacity) {
     d.rec_pairs[loop][2 * k] = i;
     d.rec_pairs[loop][2 * k + 1] = j;
+  }
+}
+
+// the gradient loop's pairs (SPHENIX): slot 3 of the counters, its own buffer
+__device__ __forceinline__ void record_pair_grad(const Dev &d, long long i, long long j) {
+  const unsigned long long k = atomicAdd(&d.rec_count[3], 1ULL);
+  if ((long long)k < d.rec_capacity) {
+    d.rec_grad[2 * k] = i;
+    d.rec_grad[2 * k + 1] = j;
   }
 }
 
@@ -690,8 +778,12 @@ __device__ __noinline__ bool dens_cut_exact_scan(const CutCtx d, const Item *__r
 // MODE 1: ghost redo sweep, DOSELF_SUBSET / DOPAIR_SUBSET arithmetic, only the
 //         particles the ghost flagged (gstate == 2); a unit is a leaf, whose
 //         flagged particles the warp first compacts into full groups of 32.
+// LOOP 1 (with MODE 0): the GRADIENT loop of SPHENIX -- the reference pastes FUNCTION = gradient into
+//         the same DOSELF1 / DOPAIR1 / DOSUB_*1 walks (src/runner_doiact_hydro.c:47-52), so this is the
+//         first-pass walk with the converged h, runner_iact_nonsym_gradient as its body and one more
+//         float4 gathered per hit (gin: u, rho, soundspeed, viscosity.alpha of the neighbour).
 // ---------------------------------------------------------------------------
-template <int MODE, bool FILT = false>
+template <int MODE, bool FILT = false, int LOOP = 0>
 __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, int sweep, int force_slow = 0) {
   if (MODE == 1 && d.walk_count[sweep] == 0) return;
   __shared__ WarpTile tiles[kWarps];
@@ -714,7 +806,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
   const int total = by_ulist ? *d.unit_count
                              : (by_unit ? (ranged ? d.unit_hi : d.n_units) : (by_list ? d.leaf_count[sweep] : d.n_leaves));
   const int wid0 = ranged ? d.unit_lo : 0;
-  int *const work = d.work_ctr + (MODE == 0 ? 0 : 1 + sweep);
+  int *const work = d.work_ctr + (LOOP == 1 ? 2 + kc.max_iter : (MODE == 0 ? 0 : 1 + sweep));
   const Item *__restrict__ items = MODE == 0 ? d.items : d.redo_items;
   const bool rec = d.rec_capacity > 0;
   const float qnan = __int_as_float(0x7fc00000);
@@ -786,6 +878,15 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
         acc.rho = s0.x; acc.rho_dh = s0.y; acc.wcount = s0.z; acc.wcount_dh = s0.w;
         acc.div_v = s1.x; acc.rx = s1.y; acc.ry = s1.z; acc.rz = s1.w;
       }
+      GradAcc gacc;
+      float4 gi = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (LOOP == 1) {
+        // hydro_reset_gradient left v_sig = 2 c and alpha_visc_max_ngb = alpha; laplace_u is 0 since hydro_init_part
+        gi = d.gin[pp];
+        const float4 sg = d.sph_grad[pp];
+        gacc.v_sig = d.v_sig[pp];
+        gacc.div_v = sg.x; gacc.lap = sg.y; gacc.amax = sg.z;
+      }
       int qcnt = 0;
       // list-recording sweep: the walk covers kGrowL x the search radius
       const bool recl = MODE == 1 && d.nl != nullptr;
@@ -814,7 +915,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
 
       // one deferred hit -> runner_iact_nonsym_density; vmj (and the f64 position of j when the
       // difference must be taken in f64) were gathered one round ahead
-      auto consume = [&](const float4 e, const float4 vmj, double xj, double yj, double zj) {
+      auto consume = [&](const float4 e, const float4 vmj, const float4 gj, double xj, double yj, double zj) {
         const int w = __float_as_int(e.w);
         float dx, dy, dz;
         if (w & kDpFlag) {
@@ -840,9 +941,13 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
         if (FILT && hit && !(r2 < r2safe))
           hit = dens_cut_exact_scan(cut_ctx(d), items, ib, ie, d.pos, w & kIdxMask, xi, yi, zi, hig);
         if (hit) {
-          iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, vmj);
+          if (LOOP == 1) iact_gradient(gacc, r2, dx, dy, dz, hi, vmi, gi, vmj, gj);
+          else iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, vmj);
           nhits++;
-          if (rec) record_pair(d, MODE, idi, d.id[w & kIdxMask]);
+          if (rec) {
+            if (LOOP == 1) record_pair_grad(d, idi, d.id[w & kIdxMask]);
+            else record_pair(d, MODE, idi, d.id[w & kIdxMask]);
+          }
         }
       };
       // software pipeline over the FIFO: entry r+2 is being read, the gathers of entry r+1 are in
@@ -850,26 +955,27 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
       auto drain_all = [&]() {
         const int m = __reduce_max_sync(kFull, qcnt);
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        auto gather = [&](const float4 e, bool ok, float4 &v, double &x, double &y, double &z) {
+        auto gather = [&](const float4 e, bool ok, float4 &v, float4 &g, double &x, double &y, double &z) {
           if (ok) {
             const int w = __float_as_int(e.w);
             const int j = w & kIdxMask;
             v = d.vm[j];
+            if (LOOP == 1) g = d.gin[j];
             if (w & kDpFlag) load_pos(d.pos, j, x, y, z);
           }
         };
         float4 e0 = qcnt > 0 ? __ldcs(&gq[0]) : z4;
         float4 e1 = qcnt > 1 ? __ldcs(&gq[32]) : z4;
-        float4 v0 = z4;
+        float4 v0 = z4, g0 = z4;
         double x0 = 0.0, y0 = 0.0, z0 = 0.0;
-        gather(e0, qcnt > 0, v0, x0, y0, z0);
+        gather(e0, qcnt > 0, v0, g0, x0, y0, z0);
         for (int r = 0; r < m; r++) {
           const float4 e2 = (r + 2 < qcnt) ? __ldcs(&gq[(r + 2) * 32]) : z4;
-          float4 v1 = z4;
+          float4 v1 = z4, g1 = z4;
           double x1 = 0.0, y1 = 0.0, z1 = 0.0;
-          gather(e1, r + 1 < qcnt, v1, x1, y1, z1);
-          if (r < qcnt) consume(e0, v0, x0, y0, z0);
-          e0 = e1; e1 = e2; v0 = v1; x0 = x1; y0 = y1; z0 = z1;
+          gather(e1, r + 1 < qcnt, v1, g1, x1, y1, z1);
+          if (r < qcnt) consume(e0, v0, g0, x0, y0, z0);
+          e0 = e1; e1 = e2; v0 = v1; g0 = g1; x0 = x1; y0 = y1; z0 = z1;
         }
         qcnt = 0;
       };
@@ -1095,7 +1201,12 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
         __syncwarp();
       }
       drain_all();
-      if (mine) {
+      if (LOOP == 1) {
+        if (mine) {
+          d.v_sig[p] = gacc.v_sig;
+          d.sph_grad[p] = make_float4(gacc.div_v, gacc.lap, gacc.amax, 0.f);
+        }
+      } else if (mine) {
         d.dens0[p] = make_float4(acc.rho, acc.rho_dh, acc.wcount, acc.wcount_dh);
         d.dens1[p] = make_float4(acc.div_v, acc.rx, acc.ry, acc.rz);
         if (recl) {
@@ -1106,7 +1217,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
     }
   }
   for (int o = 16; o > 0; o >>= 1) nhits += __shfl_down_sync(kFull, nhits, o);
-  if (lane == 0 && nhits) atomicAdd(&d.hits[MODE], nhits);
+  if (lane == 0 && nhits) atomicAdd(&d.hits[LOOP == 1 ? 3 : MODE], nhits);
 }
 
 // ---------------------------------------------------------------------------
@@ -1254,6 +1365,8 @@ __device__ float cbrtf_glibc(float x) {
 }
 
 __device__ __forceinline__ void ghost_particle(const Dev &d, int sweep, int64_t p);
+// SPHENIX: what runner_do_ghost does with a converged particle under EXTRA_HYDRO_LOOP (sphenix.cuh)
+__device__ void sphenix_converged(const Dev &d, int64_t p, float h, float4 s0, float4 s1);
 
 // Grid-stride: the launch sequence of a step always holds max_smoothing_iterations of these, and
 // all but the first few find nothing pending; a small grid makes those launches free.
@@ -1361,6 +1474,11 @@ __device__ __forceinline__ void ghost_particle(const Dev &d, int sweep, int64_t 
         s1 = make_float4(0.f, 0.f, 0.f, 0.f);
       }
     }
+  }
+  if (kc.scheme == SWIFT_CUDA_SCHEME_SPHENIX) {
+    // converged: hydro_prepare_gradient + hydro_reset_gradient (src/runner_ghost.c:1249-1264, 1429-1443)
+    sphenix_converged(d, p, h, s0, s1);
+    return;
   }
   // converged: hydro_prepare_force + hydro_reset_acceleration
   // (Minimal/hydro.h:669-761, Planetary/hydro.h:667-768)
@@ -1526,6 +1644,10 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
       me.bal = hbi.y;
       me.Pr2 = hbi.w;
       me.m_inv = 1.0f / me.m;
+      if (SCHEME == SWIFT_CUDA_SCHEME_SPHENIX) {
+        const float4 sxi = d.sx[pp];
+        me.alpha = sxi.x; me.adiff = sxi.y; me.u = sxi.z;
+      }
     }
     const float hig2 = sq_gamma2(me.h);
     const float hig = __fmul_rn(me.h, kc.gamma);
@@ -1558,8 +1680,8 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
 
     // one deferred hit -> runner_iact_nonsym_force; the three float4 of j (and its f64 position for
     // an own-cell pair) were gathered one round ahead
-    auto consume = [&](const float4 e, const float4 hbj, const float4 vmj, const float4 fj, double xj, double yj,
-                       double zj) {
+    auto consume = [&](const float4 e, const float4 hbj, const float4 vmj, const float4 fj, const float4 sxj,
+                       double xj, double yj, double zj) {
       const int w = __float_as_int(e.w);
       float dx, dy, dz;
       bool hit = true;
@@ -1576,8 +1698,14 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
         pj.h = hbj.x; pj.bal = hbj.y; pj.bin = __float_as_int(hbj.z); pj.Pr2 = hbj.w;
         pj.m = vmj.w; pj.vx = vmj.x; pj.vy = vmj.y; pj.vz = vmj.z;
         pj.rho = fj.x; pj.P = fj.y; pj.f = fj.z; pj.c = fj.w;
-        if (FAST) iact_force_fast<SCHEME>(acc, r2, dx, dy, dz, me, pj);
-        else iact_force<SCHEME>(acc, r2, dx, dy, dz, me, pj);
+        if (SCHEME == SWIFT_CUDA_SCHEME_SPHENIX) {
+          pj.alpha = sxj.x; pj.adiff = sxj.y; pj.u = sxj.z;
+          iact_force_sphenix(acc, r2, dx, dy, dz, me, pj);
+        } else if (FAST) {
+          iact_force_fast<SCHEME>(acc, r2, dx, dy, dz, me, pj);
+        } else {
+          iact_force<SCHEME>(acc, r2, dx, dy, dz, me, pj);
+        }
         nhits++;
         if (rec) record_pair(d, 2, idi, d.id[w & (kDpFlag - 1)]);
       }
@@ -1587,28 +1715,30 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force(Dev d) {
     auto drain_all = [&]() {
       const int m = __reduce_max_sync(kFull, qcnt);
       const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-      auto gather = [&](const float4 e, bool ok, float4 &hb, float4 &v, float4 &f, double &x, double &y, double &z) {
+      auto gather = [&](const float4 e, bool ok, float4 &hb, float4 &v, float4 &f, float4 &sxj, double &x, double &y,
+                        double &z) {
         if (ok) {
           const int w = __float_as_int(e.w);
           const int j = w & (kDpFlag - 1);
           hb = d.hb[j];
           v = d.vm[j];
           f = d.fin[j];
+          if (SCHEME == SWIFT_CUDA_SCHEME_SPHENIX) sxj = d.sx[j];
           if (w & kDpFlag) load_pos(d.pos, j, x, y, z);
         }
       };
       float4 e0 = qcnt > 0 ? __ldcs(&gq[0]) : z4;
       float4 e1 = qcnt > 1 ? __ldcs(&gq[32]) : z4;
-      float4 hb0 = z4, v0 = z4, f0 = z4;
+      float4 hb0 = z4, v0 = z4, f0 = z4, s0 = z4;
       double x0 = 0.0, y0 = 0.0, z0 = 0.0;
-      gather(e0, qcnt > 0, hb0, v0, f0, x0, y0, z0);
+      gather(e0, qcnt > 0, hb0, v0, f0, s0, x0, y0, z0);
       for (int r = 0; r < m; r++) {
         const float4 e2 = (r + 2 < qcnt) ? __ldcs(&gq[(r + 2) * 32]) : z4;
-        float4 hb1 = z4, v1 = z4, f1 = z4;
+        float4 hb1 = z4, v1 = z4, f1 = z4, s1 = z4;
         double x1 = 0.0, y1 = 0.0, z1 = 0.0;
-        gather(e1, r + 1 < qcnt, hb1, v1, f1, x1, y1, z1);
-        if (r < qcnt) consume(e0, hb0, v0, f0, x0, y0, z0);
-        e0 = e1; e1 = e2; hb0 = hb1; v0 = v1; f0 = f1; x0 = x1; y0 = y1; z0 = z1;
+        gather(e1, r + 1 < qcnt, hb1, v1, f1, s1, x1, y1, z1);
+        if (r < qcnt) consume(e0, hb0, v0, f0, s0, x0, y0, z0);
+        e0 = e1; e1 = e2; hb0 = hb1; v0 = v1; f0 = f1; s0 = s1; x0 = x1; y0 = y1; z0 = z1;
       }
       qcnt = 0;
     };

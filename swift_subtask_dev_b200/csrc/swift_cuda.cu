@@ -13,6 +13,7 @@
 #include "force_fast.cuh"
 #include "pack.cuh"
 #include "integrate.cuh"
+#include "sphenix.cuh"
 
 using namespace swiftcuda;
 
@@ -96,6 +97,12 @@ struct swift_cuda_ctx {
   int path = 8;                     // default: ghost redo sweeps from recorded neighbour lists (8).  Bit 5 (32): the
                                     // density walks as distance filters with the decision made at consumption --
                                     // bit-exact, measured 8 % SLOWER than the windowed test (spills), left off
+  // SPHENIX (sphenix.cuh): the scheme's hydro_props, staging of its per-particle state, the gradient loop's grid
+  swift_cuda_sphenix_props sprops = {2.0f, 0.0f, 0.05f, 0.0f, 1.0f, 1.0f, 0.0f, 1e-3};
+  float *s_sph_in[3] = {};
+  float *s_sph_out = nullptr;
+  int grid_gradient = 0;
+  long long n_gradient = 0;
   int fast_qd = kQD;   // rows of the hit FIFO k_force_fast uses (SWIFT_CUDA_FAST_QD)
   int force_slow = 0;  // test hook (SWIFT_CUDA_SLOW=1): every hit takes the exact sorted-axis-cut path
 };
@@ -153,6 +160,9 @@ size_t swift_cuda_sizeof(int which) {
     case 8: return sizeof(swift_cuda_integrator);
     case 9: return sizeof(swift_cuda_state_out);
     case 10: return sizeof(swift_cuda_part_layout);
+    case 11: return sizeof(swift_cuda_sphenix_props);
+    case 12: return sizeof(swift_cuda_sphenix_in);
+    case 13: return sizeof(swift_cuda_sphenix_out);
     default: return 0;
   }
 }
@@ -188,9 +198,19 @@ int swift_cuda_create(const swift_cuda_params *params, int device, swift_cuda_ct
     delete c;
     return fail("swift_cuda_create: unknown fields_mode");
   }
+  if (c->prm.scheme < SWIFT_CUDA_SCHEME_MINIMAL || c->prm.scheme > SWIFT_CUDA_SCHEME_SPHENIX) {
+    delete c;
+    return fail("swift_cuda_create: unknown scheme");
+  }
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX && c->prm.fields_mode != SWIFT_CUDA_FIELDS_EXACT) {
+    delete c;
+    return fail("swift_cuda_create: the SPHENIX scheme runs in the EXACT fields mode only");
+  }
   c->device = device;
   std::memset(&c->dev, 0, sizeof(Dev));
   if (const char *e = getenv("SWIFT_CUDA_PATH")) c->path = atoi(e);
+  // the experimental leaf-resident / filter kernels carry their own copies of the two-loop ghost and bodies
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) c->path &= 8;
   if (const char *e = getenv("SWIFT_CUDA_SLOW")) c->force_slow = atoi(e);
   if (const char *e = getenv("SWIFT_CUDA_FAST_QD")) c->fast_qd = std::min(std::max(atoi(e), 40), kQD);
   if (create_resources(c)) {
@@ -246,6 +266,13 @@ static int upload_consts(swift_cuda_ctx *c) {
   for (int i = 0; i < 4; i++) k.idg_gamma[i] = p.idg_gamma[i];
   for (int s = 0; s < 13; s++)
     for (int d = 0; d < 3; d++) k.axis[s][d] = kAxis[s][d];
+  k.visc_alpha_max = c->sprops.viscosity_alpha_max;
+  k.visc_alpha_min = c->sprops.viscosity_alpha_min;
+  k.visc_length = c->sprops.viscosity_length;
+  k.diff_beta = c->sprops.diffusion_beta;
+  k.diff_alpha_max = c->sprops.diffusion_alpha_max;
+  k.diff_alpha_min = c->sprops.diffusion_alpha_min;
+  k.time_base = c->sprops.time_base;
   CK(cudaMemcpyToSymbolAsync(kc, &k, sizeof(k), 0, cudaMemcpyHostToDevice, c->stream));
   return 0;
 }
@@ -334,6 +361,21 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
   CK(cudaMemsetAsync(d.acc, 0, n * sizeof(float4), c->stream));
   CK(cudaMemsetAsync(d.h_dt, 0, n * sizeof(float), c->stream));
   CK(cudaMemsetAsync(d.v_sig, 0, n * sizeof(float), c->stream));
+  // SPHENIX: the state the scheme carries, at the values hydro_convert_quantities gives a fresh particle
+  std::vector<float4> sph_init;
+  d.sph_state = d.sph_grad = d.gin = d.sx = nullptr;
+  d.rec_grad = nullptr;
+  for (int k = 0; k < 3; k++) c->s_sph_in[k] = nullptr;
+  c->s_sph_out = nullptr;
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) {
+    sph_init.assign((size_t)n, make_float4(c->prm.viscosity_alpha, c->sprops.diffusion_alpha, 0.f, 0.f));
+    if (upload(c, &d.sph_state, sph_init.data(), (size_t)n) || dmalloc(c, &d.sph_grad, n) || dmalloc(c, &d.gin, n) ||
+        dmalloc(c, &d.sx, n))
+      return 1;
+    CK(cudaMemsetAsync(d.sph_grad, 0, n * sizeof(float4), c->stream));
+    CK(cudaMemsetAsync(d.gin, 0, n * sizeof(float4), c->stream));
+    CK(cudaMemsetAsync(d.sx, 0, n * sizeof(float4), c->stream));
+  }
 
   // tree
   const size_t nc = c->tree.cells.size();
@@ -476,11 +518,11 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
       upload(c, &c->d_scratch_off, scratch_off.data(), scratch_off.size()) ||
       dmalloc(c, &c->d_scratch, (size_t)scratch_total))
     return 1;
-  if (dmalloc(c, &d.hits, 3) || dmalloc(c, &d.redo_count, (size_t)c->prm.max_smoothing_iterations + 2) ||
+  if (dmalloc(c, &d.hits, 4) || dmalloc(c, &d.redo_count, (size_t)c->prm.max_smoothing_iterations + 2) ||
       dmalloc(c, &d.walk_count, (size_t)c->prm.max_smoothing_iterations + 2) ||
-      dmalloc(c, &d.rec_count, 3))
+      dmalloc(c, &d.rec_count, 4))
     return 1;
-  CK(cudaMemsetAsync(d.rec_count, 0, 3 * sizeof(unsigned long long), c->stream));
+  CK(cudaMemsetAsync(d.rec_count, 0, 4 * sizeof(unsigned long long), c->stream));
   d.rec_capacity = 0;
   {
     // persistent neighbour-loop kernels: one resident wave of CTAs, one hit FIFO per warp
@@ -489,7 +531,11 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
     int o0 = 0, o1 = 0, o2 = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o0, k_density<0>, kBlock, 0));
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, k_density<1>, kBlock, 0));
-    if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY)
+    int o3 = 0;
+    if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) {
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, k_force<SWIFT_CUDA_SCHEME_SPHENIX>, kBlock, 0));
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, k_density<0, false, 1>, kBlock, 0));
+    } else if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY)
       CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, k_force<SWIFT_CUDA_SCHEME_PLANETARY>, kBlock, 0));
     else
       CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, k_force<SWIFT_CUDA_SCHEME_MINIMAL>, kBlock, 0));
@@ -501,8 +547,11 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
     c->grid_density = grid_for(o0, d.n_units);
     c->grid_redo = grid_for(o1, d.n_units);
     c->grid_force = grid_for(o2, d.n_units);
-    const size_t qwarps = (size_t)std::max(c->grid_density, std::max(c->grid_redo, c->grid_force)) * kWarps;
-    if (dmalloc(c, &d.gq, qwarps * kQD * 32) || dmalloc(c, &d.work_ctr, (size_t)c->prm.max_smoothing_iterations + 2))
+    c->grid_gradient = grid_for(o3, d.n_units);
+    const size_t qwarps =
+        (size_t)std::max(std::max(c->grid_density, c->grid_gradient), std::max(c->grid_redo, c->grid_force)) * kWarps;
+    // unit counters: [0] first density pass, [1 + sweep] redo sweeps, [1 + max_iter] force, [2 + max_iter] gradient
+    if (dmalloc(c, &d.gq, qwarps * kQD * 32) || dmalloc(c, &d.work_ctr, (size_t)c->prm.max_smoothing_iterations + 3))
       return 1;
   }
   for (int k = 0; k < 3; k++) d.rec_pairs[k] = nullptr;
@@ -719,20 +768,24 @@ static int launch_density_prep(swift_cuda_ctx *c) {
   Dev &d = c->dev;
   if (launch_mark(c)) return 1;
   const int nb = (int)((c->n + 255) / 256);
-  CK(cudaMemsetAsync(d.hits, 0, 3 * sizeof(unsigned long long), c->stream));
+  CK(cudaMemsetAsync(d.hits, 0, 4 * sizeof(unsigned long long), c->stream));
   CK(cudaMemsetAsync(d.redo_count, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
   CK(cudaMemsetAsync(d.walk_count, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
   CK(cudaMemsetAsync(d.leaf_count, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
   CK(cudaMemsetAsync(d.leaf_mark, 0, (size_t)std::max(d.n_leaves, 1) * sizeof(int), c->stream));
   CK(cudaMemcpyAsync(d.cell_hmax, d.cell_hmax_old, (size_t)d.ncells * sizeof(float), cudaMemcpyDeviceToDevice,
                      c->stream));
-  CK(cudaMemsetAsync(d.work_ctr, 0, ((size_t)c->prm.max_smoothing_iterations + 2) * sizeof(int), c->stream));
+  CK(cudaMemsetAsync(d.work_ctr, 0, ((size_t)c->prm.max_smoothing_iterations + 3) * sizeof(int), c->stream));
   CK(cudaMemsetAsync(d.stale, 0, sizeof(int), c->stream));
   if (d.ncells > 0) k_check_lists<<<(d.ncells + 255) / 256, 256, 0, c->stream>>>(d, c->dx_max_part);
   if (launch_cell_box(c)) return 1;
   if (d.nl) CK(cudaMemsetAsync(d.nl_cnt, 0xff, (size_t)d.n_units * 32 * sizeof(unsigned short), c->stream));
   k_init_step<<<nb, 256, 0, c->stream>>>(d);
   c->counters.n_kernel_launches += 1;
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX && c->n > 0) {
+    k_sphenix_prep<<<nb, 256, 0, c->stream>>>(d);
+    c->counters.n_kernel_launches += 1;
+  }
   CK(cudaGetLastError());
   return 0;
 }
@@ -800,6 +853,27 @@ static int launch_ghost(swift_cuda_ctx *c) {
   return 0;
 }
 
+// SPHENIX: the gradient loop (the first-pass walk with the converged h and runner_iact_nonsym_gradient)
+static int launch_gradient(swift_cuda_ctx *c) {
+  Dev &d = c->dev;
+  if (c->prm.scheme != SWIFT_CUDA_SCHEME_SPHENIX) return fail("the gradient loop exists in the SPHENIX scheme only");
+  CK(cudaMemsetAsync(d.work_ctr + 2 + c->prm.max_smoothing_iterations, 0, sizeof(int), c->stream));
+  CK(cudaMemsetAsync(d.hits + 3, 0, sizeof(unsigned long long), c->stream));
+  if (d.n_units > 0) k_density<0, false, 1><<<c->grid_gradient, kBlock, 0, c->stream>>>(d, 0);
+  c->counters.n_kernel_launches += 1;
+  CK(cudaGetLastError());
+  return 0;
+}
+// SPHENIX: runner_do_extra_ghost
+static int launch_extra_ghost(swift_cuda_ctx *c) {
+  Dev &d = c->dev;
+  if (c->prm.scheme != SWIFT_CUDA_SCHEME_SPHENIX) return fail("the extra ghost exists in the SPHENIX scheme only");
+  if (c->n > 0) k_extra_ghost<<<(unsigned)((c->n + 255) / 256), 256, 0, c->stream>>>(d);
+  c->counters.n_kernel_launches += 1;
+  CK(cudaGetLastError());
+  return 0;
+}
+
 static int launch_force(swift_cuda_ctx *c) {
   Dev &d = c->dev;
   // runner_do_end_hydro_force is the epilogue of the force kernel
@@ -807,7 +881,9 @@ static int launch_force(swift_cuda_ctx *c) {
   if (d.n_units > 0) {
     const int nb = c->grid_force;
     const bool fast = c->prm.fields_mode == SWIFT_CUDA_FIELDS_FAST;
-    if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY) {
+    if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) {
+      k_force<SWIFT_CUDA_SCHEME_SPHENIX, false><<<nb, kBlock, 0, c->stream>>>(d);
+    } else if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY) {
       if (fast) k_force_fast<SWIFT_CUDA_SCHEME_PLANETARY><<<nb, kBlock, 0, c->stream>>>(d, c->force_slow, c->fast_qd);
       else k_force<SWIFT_CUDA_SCHEME_PLANETARY, false><<<nb, kBlock, 0, c->stream>>>(d);
     } else {
@@ -822,7 +898,7 @@ static int launch_force(swift_cuda_ctx *c) {
 
 static int finish_counters(swift_cuda_ctx *c) {
   Dev &d = c->dev;
-  unsigned long long hits[3];
+  unsigned long long hits[4];
   std::vector<int> redo((size_t)c->prm.max_smoothing_iterations + 2);
   CK(cudaMemcpyAsync(hits, d.hits, sizeof(hits), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaMemcpyAsync(redo.data(), d.redo_count, redo.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
@@ -843,6 +919,7 @@ static int finish_counters(swift_cuda_ctx *c) {
   c->counters.n_density = (long long)hits[0];
   c->counters.n_density_redo = (long long)hits[1];
   c->counters.n_force = (long long)hits[2];
+  c->n_gradient = (long long)hits[3];
   int sweeps = 0;
   for (int s = 0; s < c->prm.max_smoothing_iterations; s++)
     if (redo[s] > 0) sweeps = s + 1;
@@ -883,6 +960,17 @@ int swift_cuda_do_force(swift_cuda_ctx *c) {
   if (launch_force(c)) return 1;
   return finish_counters(c);
 }
+int swift_cuda_do_gradient(swift_cuda_ctx *c) {
+  NEED_BUILT(c);
+  if (launch_gradient(c)) return 1;
+  return finish_counters(c);
+}
+int swift_cuda_do_extra_ghost(swift_cuda_ctx *c) {
+  NEED_BUILT(c);
+  if (launch_extra_ghost(c)) return 1;
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
 
 int swift_cuda_step(swift_cuda_ctx *c, int flags) {
   NEED_BUILT(c);
@@ -896,6 +984,8 @@ int swift_cuda_step(swift_cuda_ctx *c, int flags) {
   if (launch_density(c)) return 1;
   CK(cudaEventRecord(c->ev[2], c->stream));
   if (launch_ghost(c)) return 1;
+  // SPHENIX: gradient loop and extra ghost (timed with the ghost phase)
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX && (launch_gradient(c) || launch_extra_ghost(c))) return 1;
   CK(cudaEventRecord(c->ev[3], c->stream));
   if (launch_force(c)) return 1;
   CK(cudaEventRecord(c->ev[4], c->stream));
@@ -968,6 +1058,7 @@ int swift_cuda_get_results(swift_cuda_ctx *c, const swift_cuda_parts_out *out) {
 // ghost leaves (h, rho, P, c, f, balsara) goes down while the force loop runs.
 int swift_cuda_step_io(swift_cuda_ctx *c, const swift_cuda_parts_in *in, int flags, const swift_cuda_parts_out *out) {
   NEED_BUILT(c);
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) return fail("step_io: not built for the SPHENIX scheme (use swift_cuda_step)");
   if (!in || !out) return fail("step_io: null argument");
   if (in->n != c->n) return fail("step_io: particle count changed; rebuild");
   if (!in->x || !in->v || !in->mass || !in->h || !in->u) return fail("step_io: null argument");
@@ -1167,7 +1258,7 @@ static int parts_front_in_pieces(swift_cuda_ctx *c, const void *parts, const Pac
   }
   if (launch_mark(c)) return 1;
   // what launch_density_prep does before any particle is looked at
-  CK(cudaMemsetAsync(d.hits, 0, 3 * sizeof(unsigned long long), c->stream));
+  CK(cudaMemsetAsync(d.hits, 0, 4 * sizeof(unsigned long long), c->stream));
   CK(cudaMemsetAsync(d.redo_count, 0, nit * sizeof(int), c->stream));
   CK(cudaMemsetAsync(d.walk_count, 0, nit * sizeof(int), c->stream));
   CK(cudaMemsetAsync(d.leaf_count, 0, nit * sizeof(int), c->stream));
@@ -1244,6 +1335,8 @@ int swift_cuda_build_from_cells_parts(swift_cuda_ctx *c, const swift_cuda_part_l
                                       int ncells, const swift_cuda_cell *cells, int ntasks,
                                       const swift_cuda_task *tasks) {
   if (!c || !parts) return fail("build_from_cells_parts: null argument");
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX)
+    return fail("build_from_cells_parts: the struct part entries are not built for the SPHENIX scheme (160-byte record)");
   if (check_layout(L)) return 1;
   HostSoA soa;
   swift_cuda_parts_in in;
@@ -1257,6 +1350,8 @@ int swift_cuda_build_from_cells_parts(swift_cuda_ctx *c, const swift_cuda_part_l
 
 int swift_cuda_build_from_parts(swift_cuda_ctx *c, const swift_cuda_part_layout *L, const void *parts, int64_t n) {
   if (!c || !parts) return fail("build_from_parts: null argument");
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX)
+    return fail("build_from_parts: the struct part entries are not built for the SPHENIX scheme (160-byte record)");
   if (check_layout(L)) return 1;
   HostSoA soa;
   swift_cuda_parts_in in;
@@ -1465,24 +1560,28 @@ int swift_cuda_record_pairs(swift_cuda_ctx *c, long long capacity) {
   if (capacity > 0 && d.rec_pairs[0] == nullptr) {
     for (int k = 0; k < 3; k++)
       if (dmalloc(c, &d.rec_pairs[k], (size_t)capacity * 2)) return 1;
+    if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX && dmalloc(c, &d.rec_grad, (size_t)capacity * 2)) return 1;
     c->rec_capacity = capacity;
   }
   d.rec_capacity = capacity > 0 ? c->rec_capacity : 0;
-  CK(cudaMemsetAsync(d.rec_count, 0, 3 * sizeof(unsigned long long), c->stream));
+  CK(cudaMemsetAsync(d.rec_count, 0, 4 * sizeof(unsigned long long), c->stream));
   return 0;
 }
 int swift_cuda_fetch_pairs(swift_cuda_ctx *c, int loop, long long *pairs, long long capacity, long long *count) {
   NEED_BUILT(c);
-  if (loop < 0 || loop > 2) return fail("fetch_pairs: loop must be 0, 1 or 2");
+  if (loop < 0 || loop > 3 || (loop == 3 && c->prm.scheme != SWIFT_CUDA_SCHEME_SPHENIX))
+    return fail("fetch_pairs: loop must be 0, 1 or 2 (3: the gradient loop of the SPHENIX scheme)");
   Dev &d = c->dev;
-  unsigned long long cnt[3];
+  unsigned long long cnt[4];
   CK(cudaStreamSynchronize(c->stream));
   CK(cudaMemcpy(cnt, d.rec_count, sizeof(cnt), cudaMemcpyDeviceToHost));
   if (count) *count = (long long)cnt[loop];
   if ((long long)cnt[loop] > c->rec_capacity) return fail("fetch_pairs: device pair buffer overflowed");
   if (pairs) {
     const long long m = std::min<long long>(capacity, (long long)cnt[loop]);
-    if (m > 0) CK(cudaMemcpy(pairs, d.rec_pairs[loop], (size_t)m * 2 * sizeof(long long), cudaMemcpyDeviceToHost));
+    if (m > 0)
+      CK(cudaMemcpy(pairs, loop == 3 ? d.rec_grad : d.rec_pairs[loop], (size_t)m * 2 * sizeof(long long),
+                    cudaMemcpyDeviceToHost));
   }
   return 0;
 }
@@ -1583,6 +1682,7 @@ size_t swift_cuda_halo_bytes_per_particle(int phase) { return phase == 0 ? sizeo
 int swift_cuda_halo_pack(swift_cuda_ctx *c, int phase, const int32_t *d_index, int64_t count, void *d_buffer,
                          void *stream) {
   NEED_BUILT(c);
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) return fail("halo_pack: not built for the SPHENIX scheme");
   if (count <= 0) return 0;
   cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
   const int nb = (int)((count + 255) / 256);
@@ -1596,6 +1696,7 @@ int swift_cuda_halo_pack(swift_cuda_ctx *c, int phase, const int32_t *d_index, i
 int swift_cuda_halo_unpack(swift_cuda_ctx *c, int phase, const int32_t *d_index, int64_t count,
                            const void *d_buffer, void *stream) {
   NEED_BUILT(c);
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) return fail("halo_unpack: not built for the SPHENIX scheme");
   if (count <= 0) return 0;
   cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
   const int nb = (int)((count + 255) / 256);
@@ -1614,6 +1715,7 @@ int swift_cuda_halo_unpack(swift_cuda_ctx *c, int phase, const int32_t *d_index,
 
 int swift_cuda_integrator_init(swift_cuda_ctx *c, const swift_cuda_integrator *p) {
   NEED_BUILT(c);
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) return fail("integrator_init: not built for the SPHENIX scheme");
   if (!p) return fail("integrator_init: null argument");
   if (!c->all_cells_active)
     return fail("integrator_init: build the context with every particle active (max_active_bin = 56), so that "
@@ -1790,6 +1892,73 @@ int swift_cuda_get_state(swift_cuda_ctx *c, const swift_cuda_state_out *o) {
 }
 
 }  // extern "C"
+
+// ---- SPHENIX: props, carried state, results (include/swift_cuda.h, "SPHENIX") -----------------------
+extern "C" {
+
+int swift_cuda_sphenix_set_props(swift_cuda_ctx *c, const swift_cuda_sphenix_props *p) {
+  if (!c || !p) return fail("sphenix_set_props: null argument");
+  if (c->prm.scheme != SWIFT_CUDA_SCHEME_SPHENIX) return fail("sphenix_set_props: the context's scheme is not SPHENIX");
+  if (!(p->viscosity_alpha_max > 0.f) || !(p->time_base > 0.0))
+    return fail("sphenix_set_props: viscosity_alpha_max and time_base must be positive");
+  CK(cudaSetDevice(c->device));
+  c->sprops = *p;
+  if (c->built) {  // the constants of a built context follow at once; the particles' state is left alone
+    if (upload_consts(c)) return 1;
+    CK(cudaStreamSynchronize(c->stream));
+  }
+  return 0;
+}
+
+int swift_cuda_sphenix_set_state(swift_cuda_ctx *c, const swift_cuda_sphenix_in *in) {
+  NEED_BUILT(c);
+  if (!in) return fail("sphenix_set_state: null argument");
+  if (c->prm.scheme != SWIFT_CUDA_SCHEME_SPHENIX) return fail("sphenix_set_state: the context's scheme is not SPHENIX");
+  const int64_t n = c->n;
+  const float *src[3] = {in->alpha_visc, in->alpha_diff, in->div_v_previous_step};
+  const float *dev[3] = {nullptr, nullptr, nullptr};
+  for (int k = 0; k < 3; k++)
+    if (src[k]) {
+      if (!c->s_sph_in[k] && dmalloc(c, &c->s_sph_in[k], (size_t)n)) return 1;
+      CK(cudaMemcpyAsync(c->s_sph_in[k], src[k], (size_t)n * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+      dev[k] = c->s_sph_in[k];
+    }
+  if (n > 0)
+    k_sphenix_set_state<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(
+        c->dev, c->tree.order.empty() ? nullptr : c->s_order, dev[0], dev[1], dev[2]);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int swift_cuda_sphenix_get_results(swift_cuda_ctx *c, const swift_cuda_sphenix_out *out) {
+  NEED_BUILT(c);
+  if (!out) return fail("sphenix_get_results: null argument");
+  if (c->prm.scheme != SWIFT_CUDA_SCHEME_SPHENIX) return fail("sphenix_get_results: the context's scheme is not SPHENIX");
+  const int64_t n = c->n;
+  if (!c->s_sph_out && dmalloc(c, &c->s_sph_out, (size_t)n * 7)) return 1;
+  if (n > 0)
+    k_sphenix_unpack<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(
+        c->dev, c->tree.order.empty() ? nullptr : c->s_order, c->s_sph_out);
+  CK(cudaGetLastError());
+  float *dst[7] = {out->div_v, out->laplace_u, out->alpha_visc_max_ngb, out->alpha_visc, out->alpha_diff,
+                   out->div_v_previous_step, out->div_v_dt};
+  for (int k = 0; k < 7; k++)
+    if (dst[k])
+      CK(cudaMemcpyAsync(dst[k], c->s_sph_out + (size_t)k * n, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost,
+                         c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int swift_cuda_sphenix_get_counter(swift_cuda_ctx *c, long long *n_gradient) {
+  if (!c || !n_gradient) return fail("sphenix_get_counter: null argument");
+  *n_gradient = c->n_gradient;
+  return 0;
+}
+
+}  // extern "C"
+
 
 // ---- allocation-free time-step entry (include/swift_cuda.h: swift_cuda_timestep_static) --------------
 // No counterpart in the reference.  The arithmetic of

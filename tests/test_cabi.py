@@ -30,13 +30,14 @@ def test_library_exports_every_declared_symbol():
     for name in syms:
         assert hasattr(lib, name), "libswiftcuda.so does not export %s" % name
     assert sorted(be.EXPORTS) == syms, "backend.EXPORTS and include/swift_cuda.h disagree"
-    assert lib.swift_cuda_abi_version() == 2
+    assert lib.swift_cuda_abi_version() == 3
 
 
 def test_struct_layouts_match_ctypes_mirror():
     lib = be.load_library()
     for which, cls in enumerate([be.Params, be.Cell, be.Task, be.PartsIn, be.PartsOut, be.Counters, be.Timings,
-                                 be.Til, be.Integrator, be.StateOut, be.PartLayout]):
+                                 be.Til, be.Integrator, be.StateOut, be.PartLayout, be.SphenixProps, be.SphenixIn,
+                                 be.SphenixOut]):
         assert lib.swift_cuda_sizeof(which) == C.sizeof(cls), cls.__name__
     # the oracle's tree structs are layout-compatible (tests memmove between them)
     assert C.sizeof(ol.Cell) == C.sizeof(be.Cell) and C.sizeof(ol.Task) == C.sizeof(be.Task)

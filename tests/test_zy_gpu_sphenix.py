@@ -1,0 +1,184 @@
+"""GPU parity tests of the three-loop scheme (SPHENIX): the CUDA path through the C ABI --
+density, ghost with hydro_prepare_gradient, the GRADIENT loop (k_density<0, false, 1>), runner_do_extra_ghost
+(k_extra_ghost), the scheme's force loop (k_force<2>) -- against the golden vectors the reference's own compiled
+SPHENIX operators wrote (tests/golden/sphenix) and against the oracle on a library-built tree.
+Bit-exact: counts, the ordered pair sets of all FOUR loops, every field after every stage."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import golden_util as gu
+import oracle_lib as ol
+import parity
+from swift_subtask_dev_b200 import HydroBackend, ics
+from swift_subtask_dev_b200 import backend as B
+
+pytestmark = pytest.mark.gpu
+
+# GPU key -> reference key, by the stage after which the reference value was taken
+AFTER_GHOST = [("h", "g_h"), ("rho", "g_rho"), ("f", "g_f"), ("pressure", "g_pressure"), ("soundspeed", "g_soundspeed"),
+               ("balsara", "g_balsara"), ("d_rho", "d_rho"), ("d_rho_dh", "d_rho_dh"), ("d_wcount", "d_wcount"),
+               ("d_wcount_dh", "d_wcount_dh"), ("d_div_v", "d_div_v"), ("d_rot_v", "d_rot_v"), ("div_v", "g_div_v")]
+AFTER_GRADIENT = [("v_sig", "r_v_sig"), ("laplace_u", "r_laplace_u"), ("alpha_visc_max_ngb", "r_alpha_visc_max_ngb")]
+AFTER_EXTRA_GHOST = [("laplace_u", "e_laplace_u"), ("alpha_visc", "e_alpha_visc"), ("alpha_diff", "e_alpha_diff"),
+                     ("div_v_previous_step", "e_div_v_prev"), ("div_v_dt", "e_div_v_dt")]
+AFTER_FORCE = [("a", "f_a"), ("u_dt", "f_u_dt"), ("h_dt", "f_h_dt"), ("v_sig", "f_v_sig"),
+               ("min_ngb_time_bin", "f_min_ngb_time_bin")]
+
+
+def _backend(kw, props, fields_mode=0):
+    prm = parity.gpu_params(dict(kw, scheme=B.SCHEME_SPHENIX))
+    prm.fields_mode = fields_mode
+    be = HydroBackend(prm)
+    be.sphenix_set_props(**props)
+    return be
+
+
+def _set_state(be, ic):
+    be.sphenix_set_state(ic.get("in_alpha_visc"), ic.get("in_alpha_diff"), ic.get("in_div_v_prev"))
+
+
+def _both(be):
+    out = be.results(first_pass=True)
+    out.update(be.sphenix_results())
+    return out
+
+
+def _assert_fields(got, ref, table, act, stage):
+    for kg, ko in table:
+        a, b = np.asarray(got[kg]), np.asarray(ref[ko])
+        if act is not None:
+            a, b = a[act], b[act]
+        bad = a != b
+        if a.dtype.kind == "f":
+            bad &= ~(np.isnan(a) & np.isnan(b))
+        n = int(np.count_nonzero(bad.reshape(len(a), -1).any(axis=1))) if a.size else 0
+        assert n == 0, "after %s: field %s differs from the reference's %s on %d particles (max abs %g)" % (
+            stage, kg, ko, n, float(np.max(np.abs(a.astype(np.float64) - b.astype(np.float64)))))
+
+
+def _active(g):
+    if g["ic"].get("time_bin") is None:
+        return None
+    return g["ic"]["time_bin"] <= g["params"].get("max_active_bin", 56)
+
+
+def _build_golden(g, record):
+    cells, tasks, nt = gu.tree_structs(g)
+    be = _backend(g["params"], g["props"])
+    gc = (B.Cell * len(cells))()
+    C.memmove(gc, cells, C.sizeof(B.Cell) * len(cells))
+    gt = (B.Task * max(nt, 1))()
+    C.memmove(gt, tasks, C.sizeof(B.Task) * nt)
+    be.build_from_cells(g["ic"], gc, gt, nt)
+    _set_state(be, g["ic"])
+    if record:
+        be.record_pairs(len(g["h"]) * 400)
+    return be
+
+
+@pytest.mark.parametrize("name", gu.sphenix_names())
+def test_sphenix_golden_phase_by_phase(name):
+    """The operator-level entries in the reference's task order, every field compared after every stage."""
+    g = gu.load_sphenix(name)
+    act = _active(g)
+    n = len(g["h"])
+    be = _build_golden(g, record=True)
+    be.runner_do_hydro_sort()
+    be.runner_do_density()
+    be.runner_do_ghost()
+    _assert_fields(_both(be), g, AFTER_GHOST, act, "ghost")
+    be.runner_do_gradient()
+    _assert_fields(_both(be), g, AFTER_GRADIENT, act, "gradient loop")
+    be.runner_do_extra_ghost()
+    _assert_fields(_both(be), g, AFTER_EXTRA_GHOST, act, "extra ghost")
+    be.runner_do_force()
+    out = _both(be)
+    _assert_fields(out, g, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST[:6], act, "force")
+    c = be.counters()
+    assert [c["n_density"], c["n_density_redo"], c["n_force"], out["n_gradient"]] == [int(v) for v in g["counts"]]
+    for s in range(4):  # 0 density, 1 ghost redo, 2 force, 3 gradient
+        p = be.fetch_pairs(s, n * 400)
+        assert gu.pair_digest(p) == str(g["digests"][s]), "pair list of loop %d differs" % s
+        assert np.array_equal(gu.ngb_counts(p, g["id"]), g["ngb%d" % s])
+    be.close()
+
+
+@pytest.mark.parametrize("name", gu.sphenix_names())
+def test_sphenix_golden_whole_step(name):
+    """swift_cuda_step runs the seven phases of the scheme in one call: the same final state."""
+    g = gu.load_sphenix(name)
+    act = _active(g)
+    be = _build_golden(g, record=False)
+    be.step()
+    out = _both(be)
+    _assert_fields(out, g, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST, act, "step")
+    c = be.counters()
+    assert [c["n_density"], c["n_density_redo"], c["n_force"], out["n_gradient"]] == [int(v) for v in g["counts"]]
+    be.close()
+
+
+def test_sphenix_library_tree_against_oracle():
+    """Library-built tree with split cells (sub-tasks flattened to leaves), 30 k particles: the oracle runs on the
+    library's own tree and task list; pair SETS of the four loops and every field identical."""
+    ic = ics.uniform_random(30000, seed=4)
+    rng = np.random.default_rng(11)
+    n = len(ic["h"])
+    ic["u"] = (ic["u"] * (1.0 + 0.5 * rng.random(n))).astype(np.float32)
+    ic["in_alpha_visc"] = (0.1 + rng.random(n)).astype(np.float32)
+    ic["in_alpha_diff"] = (0.5 * rng.random(n)).astype(np.float32)
+    ic["in_div_v_prev"] = rng.standard_normal(n).astype(np.float32)
+    kw = dict(periodic=True, alpha=0.1)
+    be = _backend(kw, ol.SPHENIX_PROPS)
+    be.build(ic)
+    _set_state(be, ic)
+    be.record_pairs(n * 400)
+    be.step()
+    out = _both(be)
+    c = be.counters()
+    tree = be.tree()
+    pairs = [be.fetch_pairs(s, n * 400) for s in range(4)]
+    be.close()
+    assert any(tree["cells"][k].split for k in range(tree["ncells"])), "the case should have split cells"
+    # the oracle on the same cells: inputs permuted into the library's cell order, outputs back
+    order = tree["order"]
+    icc = ics.permute(ic, order)
+    cells = (ol.Cell * tree["ncells"])()
+    C.memmove(cells, tree["cells"], C.sizeof(ol.Cell) * tree["ncells"])
+    tasks = (ol.Task * max(tree["ntasks"], 1))()
+    C.memmove(tasks, tree["tasks"], C.sizeof(ol.Task) * tree["ntasks"])
+    prm = ol.make_params(record=True, scheme=2, **kw)
+    o = ol.run_step("oracle", prm, icc, cells, tasks, tree["ntasks"], record=True, sphenix=ol.SPHENIX_PROPS)
+    inv = np.empty_like(order)
+    inv[order] = np.arange(len(order), dtype=order.dtype)
+    for k in list(o.keys()):
+        if isinstance(o[k], np.ndarray) and len(o[k]) == n:
+            o[k] = o[k][inv]
+    assert [c["n_density"], c["n_density_redo"], c["n_force"], out["n_gradient"]] == o["counts"]
+    for s in range(4):
+        assert parity.pair_set_diff(pairs[s], o["pairs"][s]) == 0, "pair set of loop %d differs" % s
+    _assert_fields(out, o, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST, None, "step")
+
+
+def test_sphenix_refusals():
+    """What is not built for the scheme fails loudly instead of computing something else."""
+    prm = parity.gpu_params(dict(periodic=True, scheme=B.SCHEME_SPHENIX))
+    prm.fields_mode = 1
+    with pytest.raises(B.SwiftCudaError, match="EXACT fields mode only"):
+        HydroBackend(prm)
+    be = _backend(dict(periodic=True, alpha=0.1), ol.SPHENIX_PROPS)
+    ic = ics.uniform_random(1000, seed=1)
+    be.build(ic)
+    with pytest.raises(B.SwiftCudaError, match="not built for the SPHENIX scheme"):
+        be.integrator_init(0.1, 0.25, 0.0, 1e-10, 1e-2, 1e-3)
+    out = be.alloc_results()
+    with pytest.raises(B.SwiftCudaError, match="not built for the SPHENIX scheme"):
+        be.step_io(ic, out)
+    be.close()
+    # and the two new phases exist in that scheme only
+    be = HydroBackend(parity.gpu_params(dict(periodic=True)))
+    be.build(ic)
+    with pytest.raises(B.SwiftCudaError, match="SPHENIX scheme only"):
+        be.runner_do_gradient()
+    be.close()
