@@ -205,6 +205,31 @@ def resident_leg(args, ic, hbm_peak):
     return out
 
 
+def sphenix_leg(side):
+    """one step of the three-loop scheme (sort, density, ghost, GRADIENT loop, extra ghost, force)
+    on a side^3 uniform-random periodic box, CUDA events of the library; EXACT fields (every field bit-identical to
+    the reference compiled with SPHENIX_SPH).  Repetitions restart from the initial h; the viscosity / diffusion
+    alphas carry over, as in a run."""
+    from swift_subtask_dev_b200 import HydroBackend, ics, make_params
+    from swift_subtask_dev_b200 import backend as B
+    be = HydroBackend(make_params(periodic=True, alpha=0.1, scheme=B.SCHEME_SPHENIX))
+    be.build(ics.uniform_random(side ** 3, seed=42))
+    best = None
+    for rep in range(4):  # the first one is the warm-up
+        be.step(do_sort=True, restore=True)
+        t = be.timings()
+        if rep > 0 and (best is None or t["total_ms"] < best["total_ms"]):
+            best = t
+    c = be.counters()
+    ngrad = be.sphenix_results()["n_gradient"]
+    be.close()
+    inter = c["n_density"] + c["n_density_redo"] + c["n_force"] + ngrad
+    return {"workload": "uniform-random periodic box %d^3, SPHENIX + ideal gas, fields EXACT" % side,
+            "ms_per_step": best["total_ms"], "phase_ms": {k: round(v, 3) for k, v in best.items()},
+            "n_gradient": ngrad, "interactions_per_step": inter, "value": inter / (best["total_ms"] * 1e-3), "unit": UNIT,
+            "note": "ghost_ms includes the gradient loop and the extra ghost"}
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -229,6 +254,8 @@ def main():
                     help="swift_cuda_params.fields_mode of the headline run: fast = FMA / MUFU arithmetic in the force "
                          "loop (pair lists, counts and h bit-exact, a / u_dt / h_dt / v_sig within 1e-4); exact = every "
                          "field bit-identical to the reference.  The other mode is timed too (detail.other_mode)")
+    ap.add_argument("--sphenix-side", type=int, default=128,
+                    help="box side of the SPHENIX leg (three-loop scheme, SURVEY 8(f) N1; detail.sphenix); 0: skip")
     ap.add_argument("--resident-steps", type=int, default=3,
                     help="engine steps of the device-resident leg (drift/kick/time-step kernels, SURVEY 8(f) N3); 0: skip")
     args = ap.parse_args()
@@ -439,9 +466,11 @@ def main():
                                       "same_counts": bool(other_cnt["n_density"] == cnt["n_density"] and
                                                           other_cnt["n_density_redo"] == cnt["n_density_redo"] and
                                                           other_cnt["n_force"] == cnt["n_force"])}}}
+    be.close()
     if args.resident_steps > 0:
-        be.close()
         line["resident"] = resident_leg(args, ic, hbm_peak)
+    if args.sphenix_side > 0:
+        line["detail"]["sphenix"] = sphenix_leg(args.sphenix_side)
     if not args.no_cpu:
         nproc = host_cores()
         v, desc = cpu_arm(args.cpu_side, nproc)

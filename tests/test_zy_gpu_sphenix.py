@@ -120,9 +120,9 @@ def test_sphenix_golden_whole_step(name):
 
 
 def test_sphenix_library_tree_against_oracle():
-    """Library-built tree with split cells (sub-tasks flattened to leaves), 30 k particles: the oracle runs on the
+    """Library-built tree with split cells (sub-tasks flattened to leaves), 40 k particles: the oracle runs on the
     library's own tree and task list; pair SETS of the four loops and every field identical."""
-    ic = ics.uniform_random(30000, seed=4)
+    ic = ics.uniform_random(40000, seed=4)
     rng = np.random.default_rng(11)
     n = len(ic["h"])
     ic["u"] = (ic["u"] * (1.0 + 0.5 * rng.random(n))).astype(np.float32)
@@ -159,6 +159,40 @@ def test_sphenix_library_tree_against_oracle():
     for s in range(4):
         assert parity.pair_set_diff(pairs[s], o["pairs"][s]) == 0, "pair set of loop %d differs" % s
     _assert_fields(out, o, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST, None, "step")
+
+
+def test_sphenix_config0_lattice64():
+    """BASELINE.json configs[0]: SedovBlast_3D-style jittered lattice, 64^3 particles, the DEFAULT SPH scheme (which is
+    SPHENIX, configure.ac:1958-1959), one step: every field of every particle against the oracle, bit for bit (the
+    oracle orders equal sort keys by index, as k_sort does; the reference's quicksort leaves that order unspecified and
+    differs from both on a handful of lattice particles by an ulp)."""
+    ic = ics.lattice(64, jitter=0.1, seed=1234)
+    kw = dict(periodic=True, alpha=0.1)
+    n = len(ic["h"])
+    be = _backend(kw, ol.SPHENIX_PROPS)
+    be.build(ic)
+    be.step()
+    out = _both(be)
+    c = be.counters()
+    tree = be.tree()
+    be.close()
+    order = tree["order"]
+    icc = ics.permute(ic, order)
+    cells = (ol.Cell * tree["ncells"])()
+    C.memmove(cells, tree["cells"], C.sizeof(ol.Cell) * tree["ncells"])
+    tasks = (ol.Task * max(tree["ntasks"], 1))()
+    C.memmove(tasks, tree["tasks"], C.sizeof(ol.Task) * tree["ntasks"])
+    prm = ol.make_params(scheme=2, **kw)
+    o = ol.run_step("oracle", prm, icc, cells, tasks, tree["ntasks"], sphenix=ol.SPHENIX_PROPS)
+    inv = np.empty_like(order)
+    inv[order] = np.arange(len(order), dtype=order.dtype)
+    for k in list(o.keys()):
+        if isinstance(o[k], np.ndarray) and len(o[k]) == n:
+            o[k] = o[k][inv]
+    assert [c["n_density"], c["n_density_redo"], c["n_force"], out["n_gradient"]] == o["counts"]
+    _assert_fields(out, o, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST, None, "step")
+    # the Sedov energy spike is what the scheme sees in this configuration (the gas is at rest): del^2 u
+    assert np.abs(out["laplace_u"]).max() > 0 and out["alpha_diff"].max() > 0
 
 
 def test_sphenix_refusals():
