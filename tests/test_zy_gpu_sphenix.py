@@ -119,46 +119,106 @@ def test_sphenix_golden_whole_step(name):
     be.close()
 
 
-def test_sphenix_library_tree_against_oracle():
-    """Library-built tree with split cells (sub-tasks flattened to leaves), 40 k particles: the oracle runs on the
-    library's own tree and task list; pair SETS of the four loops and every field identical."""
-    ic = ics.uniform_random(40000, seed=4)
-    rng = np.random.default_rng(11)
+def _oracle_on_library_tree(ic, tree, kw, record=False):
+    """The oracle on the library's own cells and tasks: inputs permuted into its cell order, outputs back."""
     n = len(ic["h"])
-    ic["u"] = (ic["u"] * (1.0 + 0.5 * rng.random(n))).astype(np.float32)
-    ic["in_alpha_visc"] = (0.1 + rng.random(n)).astype(np.float32)
-    ic["in_alpha_diff"] = (0.5 * rng.random(n)).astype(np.float32)
-    ic["in_div_v_prev"] = rng.standard_normal(n).astype(np.float32)
-    kw = dict(periodic=True, alpha=0.1)
-    be = _backend(kw, ol.SPHENIX_PROPS)
-    be.build(ic)
-    _set_state(be, ic)
-    be.record_pairs(n * 400)
-    be.step()
-    out = _both(be)
-    c = be.counters()
-    tree = be.tree()
-    pairs = [be.fetch_pairs(s, n * 400) for s in range(4)]
-    be.close()
-    assert any(tree["cells"][k].split for k in range(tree["ncells"])), "the case should have split cells"
-    # the oracle on the same cells: inputs permuted into the library's cell order, outputs back
     order = tree["order"]
     icc = ics.permute(ic, order)
     cells = (ol.Cell * tree["ncells"])()
     C.memmove(cells, tree["cells"], C.sizeof(ol.Cell) * tree["ncells"])
     tasks = (ol.Task * max(tree["ntasks"], 1))()
     C.memmove(tasks, tree["tasks"], C.sizeof(ol.Task) * tree["ntasks"])
-    prm = ol.make_params(record=True, scheme=2, **kw)
-    o = ol.run_step("oracle", prm, icc, cells, tasks, tree["ntasks"], record=True, sphenix=ol.SPHENIX_PROPS)
+    prm = ol.make_params(record=record, scheme=2, **kw)
+    o = ol.run_step("oracle", prm, icc, cells, tasks, tree["ntasks"], record=record, sphenix=ol.SPHENIX_PROPS)
     inv = np.empty_like(order)
     inv[order] = np.arange(len(order), dtype=order.dtype)
     for k in list(o.keys()):
         if isinstance(o[k], np.ndarray) and len(o[k]) == n:
             o[k] = o[k][inv]
+    return o
+
+
+def _state(ic, seed):
+    rng = np.random.default_rng(seed)
+    n = len(ic["h"])
+    ic["u"] = (ic["u"] * (1.0 + 0.5 * rng.random(n))).astype(np.float32)
+    ic["in_alpha_visc"] = (0.1 + rng.random(n)).astype(np.float32)
+    ic["in_alpha_diff"] = (0.5 * rng.random(n)).astype(np.float32)
+    ic["in_div_v_prev"] = rng.standard_normal(n).astype(np.float32)
+    return ic
+
+
+def test_sphenix_library_tree_clustered_pairs():
+    """Library-built tree over a clumpy box (split cells, tasks pushed down to the progeny): the oracle runs on
+    the library's own tree and task list; pair SETS of the four loops and every field identical."""
+    ic = _state(ics.clustered(20000, nclumps=8, seed=6), 11)
+    n = len(ic["h"])
+    kw = dict(periodic=True, alpha=0.1)
+    be = _backend(kw, ol.SPHENIX_PROPS)
+    be.build(ic)
+    _set_state(be, ic)
+    be.record_pairs(n * 600)
+    be.step()
+    out = _both(be)
+    c = be.counters()
+    tree = be.tree()
+    pairs = [be.fetch_pairs(s, n * 600) for s in range(4)]
+    be.close()
+    assert any(tree["cells"][k].split for k in range(tree["ncells"])), "the case should have split cells"
+    o = _oracle_on_library_tree(ic, tree, kw, record=True)
     assert [c["n_density"], c["n_density_redo"], c["n_force"], out["n_gradient"]] == o["counts"]
     for s in range(4):
         assert parity.pair_set_diff(pairs[s], o["pairs"][s]) == 0, "pair set of loop %d differs" % s
     _assert_fields(out, o, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST, None, "step")
+
+
+def test_sphenix_library_tree_sub_tasks():
+    """96^3 in 12^3 top-level cells: 512 particles per cell, split once, sub_self / sub_pair tasks that the library
+    flattens to leaf interactions and the oracle recurses through: counts and every field identical."""
+    ic = _state(ics.uniform_random(96 ** 3, seed=5), 12)
+    kw = dict(periodic=True, alpha=0.1)
+    be = _backend(kw, ol.SPHENIX_PROPS)
+    be.build(ic)
+    _set_state(be, ic)
+    be.step()
+    out = _both(be)
+    c = be.counters()
+    tree = be.tree()
+    be.close()
+    assert {2, 3} <= {tree["tasks"][k].type for k in range(tree["ntasks"])}, "the case should have sub tasks"
+    o = _oracle_on_library_tree(ic, tree, kw)
+    assert [c["n_density"], c["n_density_redo"], c["n_force"], out["n_gradient"]] == o["counts"]
+    _assert_fields(out, o, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST, None, "step")
+
+
+def test_sphenix_state_is_carried_on_the_device():
+    """Two steps in a row: the viscosity / diffusion alphas and div_v_previous_step the first step leaves stay in
+    HBM and are what the second step starts from (only x, v, h, u go up again), as p->viscosity / p->diffusion
+    persist in the reference's struct part.  The oracle gets the first step's outputs as the second one's inputs."""
+    ic = _state(ics.uniform_random(16 ** 3, seed=8), 13)
+    ic["v"] = (ic["v"] - 0.3 * (ic["x"] - 0.5)).astype(np.float32)
+    kw = dict(periodic=True, alpha=0.1)
+    be = _backend(kw, ol.SPHENIX_PROPS)
+    be.build(ic)
+    _set_state(be, ic)
+    be.step()
+    r1 = _both(be)
+    tree = be.tree()
+    ic2 = dict(ic)
+    ic2["h"] = r1["h"].copy()
+    be.update_particles(ic2)
+    be.step()
+    r2 = _both(be)
+    c2 = be.counters()
+    be.close()
+    o1 = _oracle_on_library_tree(ic, tree, kw)
+    _assert_fields(r1, o1, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST, None, "step 1")
+    ic2["in_alpha_visc"], ic2["in_alpha_diff"], ic2["in_div_v_prev"] = o1["e_alpha_visc"], o1["e_alpha_diff"], \
+        o1["e_div_v_prev"]
+    o2 = _oracle_on_library_tree(ic2, tree, kw)
+    assert [c2["n_density"], c2["n_density_redo"], c2["n_force"], r2["n_gradient"]] == o2["counts"]
+    _assert_fields(r2, o2, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST, None, "step 2")
+    assert not np.array_equal(r1["alpha_visc"], r2["alpha_visc"]), "the alphas should have moved between the steps"
 
 
 def test_sphenix_config0_lattice64():
@@ -176,19 +236,7 @@ def test_sphenix_config0_lattice64():
     c = be.counters()
     tree = be.tree()
     be.close()
-    order = tree["order"]
-    icc = ics.permute(ic, order)
-    cells = (ol.Cell * tree["ncells"])()
-    C.memmove(cells, tree["cells"], C.sizeof(ol.Cell) * tree["ncells"])
-    tasks = (ol.Task * max(tree["ntasks"], 1))()
-    C.memmove(tasks, tree["tasks"], C.sizeof(ol.Task) * tree["ntasks"])
-    prm = ol.make_params(scheme=2, **kw)
-    o = ol.run_step("oracle", prm, icc, cells, tasks, tree["ntasks"], sphenix=ol.SPHENIX_PROPS)
-    inv = np.empty_like(order)
-    inv[order] = np.arange(len(order), dtype=order.dtype)
-    for k in list(o.keys()):
-        if isinstance(o[k], np.ndarray) and len(o[k]) == n:
-            o[k] = o[k][inv]
+    o = _oracle_on_library_tree(ic, tree, kw)
     assert [c["n_density"], c["n_density_redo"], c["n_force"], out["n_gradient"]] == o["counts"]
     _assert_fields(out, o, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST, None, "step")
     # the Sedov energy spike is what the scheme sees in this configuration (the gas is at rest): del^2 u
