@@ -162,6 +162,18 @@ def cell_block_random(cells, cdim, dim, per_cell, seed=42, h=None):
     return ic
 
 
+def clump_and_strays(n_clump=600, n_stray=40, seed=3, h=0.03):
+    """A clump in one corner of an open unit box and a few stray particles far from everything: with a small
+    h_max the strays end the ghost at h_max without a neighbour (hydro_part_has_no_neighbours)."""
+    rng = np.random.default_rng(seed)
+    n = n_clump + n_stray
+    x = np.concatenate([rng.random((n_clump, 3)) * 0.2 + 0.05, rng.random((n_stray, 3)) * 0.5 + 0.45])
+    return {"x": np.ascontiguousarray(x, dtype=np.float64), "v": rng.uniform(-0.05, 0.05, (n, 3)).astype(np.float32),
+            "mass": np.full(n, 1.0 / n, dtype=np.float32), "h": np.full(n, h, dtype=np.float32),
+            "u": (1.0 + 0.5 * rng.random(n)).astype(np.float32), "id": np.arange(1, n + 1, dtype=np.int64),
+            "mat_id": None, "time_bin": None}
+
+
 def permute(ic, order):
     """Reorders every per-particle array with `order` (cell order)."""
     out = {}

@@ -72,6 +72,15 @@ def cases():
     ic = warm_start(rough(ics.uniform_random(11 ** 3, seed=21), 7), kw)
     ic["time_bin"] = np.random.default_rng(1).integers(1, 4, len(ic["h"])).astype(np.int8)
     c["random11_timebins"] = (ic, dict(periodic=True, alpha=0.1, max_active_bin=2))
+    # strays that reach h_max without a neighbour: hydro_part_has_no_neighbours, then the gradient / force loops
+    # with nothing to sum for them
+    ic = clump = ics.clump_and_strays()
+    n = len(ic["h"])
+    rng = np.random.default_rng(8)
+    ic["in_alpha_visc"] = (0.1 + 0.5 * rng.random(n)).astype(np.float32)
+    ic["in_alpha_diff"] = (0.3 * rng.random(n)).astype(np.float32)
+    ic["in_div_v_prev"] = rng.standard_normal(n).astype(np.float32)
+    c["strays640_open"] = (ic, dict(periodic=False, alpha=0.1, h_max=0.045))
     return c
 
 

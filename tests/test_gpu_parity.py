@@ -103,6 +103,13 @@ def test_non_periodic():
     _check(ics.uniform_random(28 ** 3, seed=9), dict(periodic=False))
 
 
+def test_strays_reach_h_max_without_neighbours():
+    """hydro_part_has_no_neighbours: stray particles whose h doubles up to h_max and still finds nobody."""
+    ic = ics.clump_and_strays()
+    g, o, r = _check(ic, dict(periodic=False, h_max=0.045))
+    assert np.count_nonzero(g["h"] >= np.float32(0.045)) > 10
+
+
 def test_second_step_is_bit_identical():
     """Stepping twice from the same uploaded state gives the same bits (no atomics in the sums)."""
     from swift_subtask_dev_b200 import HydroBackend, make_params
