@@ -386,9 +386,11 @@ int swift_cuda_get_integrator_timings(swift_cuda_ctx *ctx, float ms[4]);
  *
  * Supported entries: swift_cuda_build_from_particles / _from_cells, swift_cuda_update_particles,
  * swift_cuda_step, swift_cuda_do_*, swift_cuda_get_results (v_sig = p->viscosity.v_sig, d_div_v the raw
- * first-pass sum), the pair recorder (loop 3 = gradient) and the entries below.  fields_mode must be EXACT.
- * The struct part entries, swift_cuda_step_io, the halo entries and the time-integration entries refuse a
- * SPHENIX context (the 160-byte record, the wider halo and the scheme's drift / kick are not built). */
+ * first-pass sum), the pair recorder (loop 3 = gradient), the time-integration entries (the scheme's
+ * hydro_predict_extra / hydro_kick_extra / hydro_compute_timestep are Minimal's arithmetic;
+ * swift_cuda_integrator_init makes its time_base the one of the extra ghost's dt_alpha) and the entries
+ * below.  fields_mode must be EXACT.  The struct part entries, swift_cuda_step_io and the halo entries
+ * refuse a SPHENIX context (the 160-byte record and the wider halo are not built). */
 typedef struct {
   float viscosity_alpha_max;  /* hydro_props->viscosity.alpha_max, SPH:viscosity_alpha_max (2.0) */
   float viscosity_alpha_min;  /* ->viscosity.alpha_min (0.0) */

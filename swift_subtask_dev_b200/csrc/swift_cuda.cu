@@ -1715,7 +1715,6 @@ int swift_cuda_halo_unpack(swift_cuda_ctx *c, int phase, const int32_t *d_index,
 
 int swift_cuda_integrator_init(swift_cuda_ctx *c, const swift_cuda_integrator *p) {
   NEED_BUILT(c);
-  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) return fail("integrator_init: not built for the SPHENIX scheme");
   if (!p) return fail("integrator_init: null argument");
   if (!c->all_cells_active)
     return fail("integrator_init: build the context with every particle active (max_active_bin = 56), so that "
@@ -1737,6 +1736,13 @@ int swift_cuda_integrator_init(swift_cuda_ctx *c, const swift_cuda_integrator *p
   c->iprm.time_base = p->time_base;
   c->iprm.time_base_inv = 1.0 / p->time_base;
   c->iprm.ti_current = 0;
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) {
+    // the scheme's drift / kick / time-step hooks are Minimal's arithmetic (src/hydro/SPHENIX/hydro.h:464-480,
+    // 966-1146 with the floors NONE; v_sig lives in p->viscosity); the extra ghost's dt_alpha is
+    // get_timestep(p->time_bin, e->time_base) of the same time line
+    c->sprops.time_base = p->time_base;
+    if (upload_consts(c)) return 1;
+  }
   if (n > 0) k_integ_init<<<(int)((n + 255) / 256), 256, 0, c->stream>>>(c->dev, g);
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(c->stream));

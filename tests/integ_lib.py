@@ -134,8 +134,12 @@ class Checker:
         return ti_end_min.value, updated.value
 
 
+SPHENIX_STATE = (("alpha_visc", "e_alpha_visc"), ("alpha_diff", "e_alpha_diff"), ("div_v_prev", "e_div_v_prev"),
+                 ("div_v_dt", "e_div_v_dt"), ("laplace_u", "e_laplace_u"))
+
+
 def hydro_step(which, s, prm_kwargs, tree, max_active_bin, eos=None, variant="minimal", mass=None, ids=None,
-               h_build=None):
+               h_build=None, sphenix=None):
     """sort + density + ghost + force of the ACTIVE particles through the step checker; the inactive ones keep
     their state (their rho, P, f, c, balsara are what the force loop of the active ones reads)."""
     cells, tasks, ntasks = tree
@@ -147,8 +151,14 @@ def hydro_step(which, s, prm_kwargs, tree, max_active_bin, eos=None, variant="mi
           "in_balsara": s["balsara"], "in_h_build": h_build}
     if s.get("mat_id") is not None:
         ic["mat_id"] = s["mat_id"]
-    o = ol.run_step(which, prm, ic, cells, tasks, ntasks, record=False, variant=variant, eos=eos)
+    if sphenix is not None:
+        # the three-loop scheme: the viscosity / diffusion state travels in the particle from step to step
+        ic["in_alpha_visc"], ic["in_alpha_diff"], ic["in_div_v_prev"] = s["alpha_visc"], s["alpha_diff"], s["div_v_prev"]
+    o = ol.run_step(which, prm, ic, cells, tasks, ntasks, record=False, variant=variant, eos=eos, sphenix=sphenix)
     act = s["time_bin"] <= max_active_bin
+    if sphenix is not None:
+        for ks, ko in SPHENIX_STATE:
+            s[ks][act] = o[ko][act]
     for ks, ko in (("h", "g_h"), ("rho", "g_rho"), ("pressure", "g_pressure"), ("soundspeed", "g_soundspeed"),
                    ("f", "g_f"), ("balsara", "g_balsara"), ("a", "f_a"), ("u_dt", "f_u_dt"), ("h_dt", "f_h_dt"),
                    ("v_sig", "f_v_sig")):
@@ -157,13 +167,20 @@ def hydro_step(which, s, prm_kwargs, tree, max_active_bin, eos=None, variant="mi
     return o
 
 
-def run_loop(which, ic, prm_kwargs, ip, tree, nsteps, eos=None, variant="minimal", on_step=None):
+def run_loop(which, ic, prm_kwargs, ip, tree, nsteps, eos=None, variant="minimal", on_step=None, sphenix=None):
     """The engine-step loop of the module docstring on the checker `which`.  ic is in CELL order (tree built on
     it).  Returns the state dict and the per-step log [(ti_current, max_active_bin, updated, dx_max...)]."""
     s = new_state(ic)
     n = len(s["h"])
     s["f"] = np.zeros(n, dtype=np.float32)
     s["balsara"] = np.zeros(n, dtype=np.float32)
+    if sphenix is not None:
+        # hydro_convert_quantities: the initial alphas of hydro_props; e->time_base is the integrator's
+        sphenix = dict(sphenix, time_base=ip["time_base"])
+        s["alpha_visc"] = np.full(n, prm_kwargs.get("alpha", 0.8), dtype=np.float32)
+        s["alpha_diff"] = np.full(n, sphenix.get("diffusion_alpha", 0.0), dtype=np.float32)
+        for k in ("div_v_prev", "div_v_dt", "laplace_u"):
+            s[k] = np.zeros(n, dtype=np.float32)
     mass = np.array(ic["mass"], dtype=np.float32)
     ids = np.array(ic["id"], dtype=np.int64) if "id" in ic else np.arange(n, dtype=np.int64)
     chk = Checker(which, ip, eos=eos, variant=variant)
@@ -175,7 +192,8 @@ def run_loop(which, ic, prm_kwargs, ip, tree, nsteps, eos=None, variant="minimal
         dx = (0.0, 0.0)
         if step > 0:
             dx = chk.drift(s, ti_old, ti_current)
-        hydro_step(which, s, prm_kwargs, tree, mab, eos=eos, variant=variant, mass=mass, ids=ids, h_build=h_build)
+        hydro_step(which, s, prm_kwargs, tree, mab, eos=eos, variant=variant, mass=mass, ids=ids, h_build=h_build,
+                   sphenix=sphenix)
         if step > 0:
             chk.kick(s, 2, ti_current, mab)
         ti_end_min, updated = chk.timestep(s, ti_current, mab)
@@ -196,7 +214,8 @@ def prepare(ic, prm_kwargs):
     from swift_subtask_dev_b200 import ics
     icc = ics.permute(ic, order)
     eos = ol.eos_from_json() if prm_kwargs.get("scheme", 0) == 1 else None
-    o0 = ol.run_step("oracle", prm, icc, cells, tasks, nt, eos=eos)
+    o0 = ol.run_step("oracle", prm, icc, cells, tasks, nt, eos=eos,
+                     sphenix=ol.SPHENIX_PROPS if prm_kwargs.get("scheme", 0) == 2 else None)
     ic = dict(ic)
     h = np.empty_like(np.asarray(ic["h"], dtype=np.float32))
     h[order] = o0["g_h"]
@@ -205,7 +224,7 @@ def prepare(ic, prm_kwargs):
     return ics.permute(ic, order), (cells, tasks, nt)
 
 
-def run_loop_gpu(be, ic, ip, tree, nsteps, on_step=None):
+def run_loop_gpu(be, ic, ip, tree, nsteps, on_step=None, sphenix=False):
     """The same loop through the C ABI: the particles go up once (build_from_cells) and stay on the
     device; per step only scalars (ti_end_min, dx_max) come back.  `be` is a HydroBackend created with
     max_active_bin = 56."""
@@ -229,6 +248,15 @@ def run_loop_gpu(be, ic, ip, tree, nsteps, on_step=None):
         be.kick(1)
         log.append((ti_current, mab, updated, dx[0], dx[1], ti_end_min))
         if on_step is not None:
-            on_step(step, be.state())
+            on_step(step, _gpu_state(be, sphenix))
         ti_old, ti_current = ti_current, ti_end_min
-    return be.state(), log
+    return _gpu_state(be, sphenix), log
+
+
+def _gpu_state(be, sphenix):
+    st = be.state()
+    if sphenix:
+        r = be.sphenix_results()
+        st.update({"alpha_visc": r["alpha_visc"], "alpha_diff": r["alpha_diff"], "div_v_prev": r["div_v_previous_step"],
+                   "div_v_dt": r["div_v_dt"], "laplace_u": r["laplace_u"]})
+    return st

@@ -69,3 +69,29 @@ def test_oracle_vs_compiled_reference_sphenix(name, make, kw):
         assert gu.pair_digest(o["pairs"][s]) == gu.pair_digest(r["pairs"][s])
     for k in FIELDS:
         assert np.array_equal(o[k], r[k]), k
+
+
+# ---- engine steps with individual time bins (drift, the seven hydro phases, kick2, time-step, kick1) ----
+def _integ_case():
+    import importlib.util
+    import os
+    path = os.path.join(gu.GOLDEN_DIR, "make_golden_sphenix.py")
+    spec = importlib.util.spec_from_file_location("make_golden_sphenix", path)
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    icc, tree, kw, ip, nsteps = m.integ_case()
+    z = np.load(os.path.join(gu.SPHENIX_DIR, "integ", "clustered4k_bins.npz"))
+    return icc, tree, kw, ip, nsteps, z, m.INTEG_KEYS
+
+
+def test_oracle_engine_loop_reproduces_reference_golden_sphenix():
+    """The state the reference's own cell_drift_part / runner_do_kick1,2 / runner_do_timestep and its SPHENIX hydro
+    operators leave after six engine steps (tests/golden/sphenix/integ), alphas included: identical bits."""
+    import integ_lib as il
+    icc, tree, kw, ip, nsteps, z, extra = _integ_case()
+    s, log = il.run_loop("oracle", icc, kw, ip, tree, nsteps, sphenix=ol.SPHENIX_PROPS)
+    for k in il.STATE_KEYS + extra:
+        assert np.array_equal(np.asarray(s[k]).reshape(-1), z[k].reshape(-1)), k
+    assert [[l[0], l[1], l[2], l[5]] for l in log] == z["log_int"].tolist()
+    assert len(np.unique(s["time_bin"])) >= 4, "not a time-bin hierarchy"
+    assert s["alpha_visc"].max() > 1.0, "the viscosity switch should have fired somewhere"

@@ -243,6 +243,32 @@ def test_sphenix_config0_lattice64():
     assert np.abs(out["laplace_u"]).max() > 0 and out["alpha_diff"].max() > 0
 
 
+def test_sphenix_resident_engine_loop():
+    """N3 with the three-loop scheme: the particles go to the device once; drift, the seven hydro phases on the
+    active particles, kick2, time-step, kick1 per engine step with individual time bins.  Every field -- the
+    viscosity / diffusion alphas, div_v_previous_step, div_v_dt, laplace_u included -- against the oracle after
+    EVERY step and against the reference's golden state at the end."""
+    import integ_lib as il
+    import test_sphenix_oracle as cpu
+    icc, tree, kw, ip, nsteps, z, extra = cpu._integ_case()
+    keys = il.STATE_KEYS + extra
+    ref_states = []
+    so, lo = il.run_loop("oracle", icc, kw, ip, tree, nsteps, sphenix=ol.SPHENIX_PROPS,
+                         on_step=lambda step, s: ref_states.append({k: s[k].copy() for k in keys}))
+    be = _backend(dict(kw, max_active_bin=il.NUM_TIME_BINS), ol.SPHENIX_PROPS)
+
+    def check(step, g):
+        for k in keys:
+            assert np.array_equal(np.asarray(g[k]).reshape(-1), ref_states[step][k].reshape(-1)), \
+                "step %d: field %s is not bit-identical" % (step, k)
+
+    sg, lg = il.run_loop_gpu(be, icc, ip, tree, nsteps, on_step=check, sphenix=True)
+    be.close()
+    assert [l[:3] + l[5:] for l in lg] == [l[:3] + l[5:] for l in lo], "active counts / sync points differ"
+    for k in keys:
+        assert np.array_equal(np.asarray(sg[k]).reshape(-1), z[k].reshape(-1)), "%s vs the reference's golden state" % k
+
+
 def test_sphenix_refusals():
     """What is not built for the scheme fails loudly instead of computing something else."""
     prm = parity.gpu_params(dict(periodic=True, scheme=B.SCHEME_SPHENIX))
@@ -252,8 +278,6 @@ def test_sphenix_refusals():
     be = _backend(dict(periodic=True, alpha=0.1), ol.SPHENIX_PROPS)
     ic = ics.uniform_random(1000, seed=1)
     be.build(ic)
-    with pytest.raises(B.SwiftCudaError, match="not built for the SPHENIX scheme"):
-        be.integrator_init(0.1, 0.25, 0.0, 1e-10, 1e-2, 1e-3)
     out = be.alloc_results()
     with pytest.raises(B.SwiftCudaError, match="not built for the SPHENIX scheme"):
         be.step_io(ic, out)
