@@ -389,7 +389,8 @@ int swift_cuda_get_integrator_timings(swift_cuda_ctx *ctx, float ms[4]);
  * first-pass sum), the pair recorder (loop 3 = gradient), the time-integration entries (the scheme's
  * hydro_predict_extra / hydro_kick_extra / hydro_compute_timestep are Minimal's arithmetic;
  * swift_cuda_integrator_init makes its time_base the one of the extra ghost's dt_alpha) and the entries
- * below.  fields_mode must be EXACT.  The struct part entries, swift_cuda_step_io and the halo entries
+ * below; both fields modes (FAST: k_force_fast with the scheme's interaction; the gradient loop and the extra
+ * ghost stay exact, they decide the alphas).  The struct part entries, swift_cuda_step_io and the halo entries
  * refuse a SPHENIX context (the 160-byte record and the wider halo are not built). */
 typedef struct {
   float viscosity_alpha_max;  /* hydro_props->viscosity.alpha_max, SPH:viscosity_alpha_max (2.0) */

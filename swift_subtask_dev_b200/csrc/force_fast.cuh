@@ -181,6 +181,10 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force_fast(Dev d, 
       me.bal = hbi.y;
       me.Pr2 = hbi.w;
       me.m_inv = 1.0f / me.m;
+      if (SCHEME == SWIFT_CUDA_SCHEME_SPHENIX) {
+        const float4 sxi = d.sx[pp];
+        me.alpha = sxi.x; me.adiff = sxi.y; me.u = sxi.z;
+      }
     }
     const float hig2 = sq_gamma2(me.h);
     const float hig = __fmul_rn(me.h, kc.gamma);
@@ -212,8 +216,8 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force_fast(Dev d, 
     __syncwarp();
 
     // one deferred candidate: the reference's decision, then runner_iact_nonsym_force (FAST arithmetic)
-    auto consume = [&](const float4 e, const float4 hbj, const float4 vmj, const float4 fj, double xj, double yj,
-                       double zj) {
+    auto consume = [&](const float4 e, const float4 hbj, const float4 vmj, const float4 fj, const float4 sxj,
+                       double xj, double yj, double zj) {
       const int w = __float_as_int(e.w);
       const int j = w & (kDpFlag - 1);
       float dx, dy, dz;
@@ -242,7 +246,12 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force_fast(Dev d, 
         pj.h = hbj.x; pj.bal = hbj.y; pj.bin = __float_as_int(hbj.z); pj.Pr2 = hbj.w;
         pj.m = vmj.w; pj.vx = vmj.x; pj.vy = vmj.y; pj.vz = vmj.z;
         pj.rho = fj.x; pj.P = fj.y; pj.f = fj.z; pj.c = fj.w;
-        iact_force_fast<SCHEME>(acc, r2, dx, dy, dz, me, pj);
+        if (SCHEME == SWIFT_CUDA_SCHEME_SPHENIX) {
+          pj.alpha = sxj.x; pj.adiff = sxj.y; pj.u = sxj.z;
+          iact_force_sphenix_fast(acc, r2, dx, dy, dz, me, pj);
+        } else {
+          iact_force_fast<SCHEME>(acc, r2, dx, dy, dz, me, pj);
+        }
         nhits++;
         if (rec) record_pair(d, 2, idi, d.id[j]);
       }
@@ -250,13 +259,15 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force_fast(Dev d, 
     auto drain_all = [&]() {
       const int m = __reduce_max_sync(kFull, qcnt);
       const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-      auto gather = [&](const float4 e, bool ok, float4 &hb, float4 &v, float4 &f, double &x, double &y, double &z) {
+      auto gather = [&](const float4 e, bool ok, float4 &hb, float4 &v, float4 &f, float4 &sxj, double &x, double &y,
+                        double &z) {
         if (ok) {
           const int w = __float_as_int(e.w);
           const int j = w & (kDpFlag - 1);
           hb = d.hb[j];
           v = d.vm[j];
           f = d.fin[j];
+          if (SCHEME == SWIFT_CUDA_SCHEME_SPHENIX) sxj = d.sx[j];
           if (w & kDpFlag) load_pos(d.pos, j, x, y, z);
         }
       };
@@ -267,16 +278,16 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_FORCE) k_force_fast(Dev d, 
 #endif
       float4 e0 = qcnt > 0 ? FIFO_LD(&gq[0]) : z4;
       float4 e1 = qcnt > 1 ? FIFO_LD(&gq[32]) : z4;
-      float4 hb0 = z4, v0 = z4, f0 = z4;
+      float4 hb0 = z4, v0 = z4, f0 = z4, s0 = z4;
       double x0 = 0.0, y0 = 0.0, z0 = 0.0;
-      gather(e0, qcnt > 0, hb0, v0, f0, x0, y0, z0);
+      gather(e0, qcnt > 0, hb0, v0, f0, s0, x0, y0, z0);
       for (int r = 0; r < m; r++) {
         const float4 e2 = (r + 2 < qcnt) ? FIFO_LD(&gq[(r + 2) * 32]) : z4;
-        float4 hb1 = z4, v1 = z4, f1 = z4;
+        float4 hb1 = z4, v1 = z4, f1 = z4, s1 = z4;
         double x1 = 0.0, y1 = 0.0, z1 = 0.0;
-        gather(e1, r + 1 < qcnt, hb1, v1, f1, x1, y1, z1);
-        if (r < qcnt) consume(e0, hb0, v0, f0, x0, y0, z0);
-        e0 = e1; e1 = e2; hb0 = hb1; v0 = v1; f0 = f1; x0 = x1; y0 = y1; z0 = z1;
+        gather(e1, r + 1 < qcnt, hb1, v1, f1, s1, x1, y1, z1);
+        if (r < qcnt) consume(e0, hb0, v0, f0, s0, x0, y0, z0);
+        e0 = e1; e1 = e2; hb0 = hb1; v0 = v1; f0 = f1; s0 = s1; x0 = x1; y0 = y1; z0 = z1;
       }
       qcnt = 0;
     };

@@ -344,6 +344,48 @@ __device__ __forceinline__ void record_pair(const Dev &d, int loop, long long i,
   }
 }
 
+// FAST form of the scheme's force interaction (fields_mode FAST): the same expressions with FMA contraction and
+// MUFU reciprocals / rsqrt, as iact_force_fast; which pairs interact is decided elsewhere, exactly.
+__device__ __forceinline__ void iact_force_sphenix_fast(ForceAcc &a, float r2, float dx, float dy, float dz,
+                                                        const ForceI &pi, const ForceJ &pj) {
+  const float a2_Hubble = kc.a * kc.a * kc.H;
+  const float r_inv = r2 > 0.f ? rsqrtf(r2) : 0.f;
+  const float r = r2 * r_inv;
+  float wi, wi_dx, wj, wj_dx;
+  kernel_deval_fast(r * pi.hi_inv, wi, wi_dx);
+  const float wi_dr = pi.hid_inv * wi_dx;
+  const float hj_inv = fast_rcp(pj.h);
+  const float hj2 = hj_inv * hj_inv;
+  kernel_deval_fast(r * hj_inv, wj, wj_dx);
+  const float wj_dr = hj2 * hj2 * wj_dx;
+  const float dvdr = __fmaf_rn(pi.vz - pj.vz, dz, __fmaf_rn(pi.vy - pj.vy, dy, (pi.vx - pj.vx) * dx));
+  const float dvdr_H = __fmaf_rn(a2_Hubble, r2, dvdr);
+  const float mu_ij = r_inv * fminf(dvdr_H, 0.f);
+  const float v_sig = __fmaf_rn(-kc.beta, mu_ij, pi.c + pj.c);
+  const float f_ij = __fmaf_rn(-pi.f, fast_rcp(pj.m), 1.f);
+  const float f_ji = __fmaf_rn(-pj.f, pi.m_inv, 1.f);
+  const float rho_ij_inv = fast_rcp(pi.rho + pj.rho);
+  const float rhoi_inv = fast_rcp(pi.rho), rhoj_inv = fast_rcp(pj.rho);
+  const float visc = -0.25f * (pi.alpha + pj.alpha) * v_sig * mu_ij * (pi.bal + pj.bal) * rho_ij_inv;
+  const float visc_acc_term = 0.5f * visc * __fmaf_rn(wi_dr, f_ij, wj_dr * f_ji) * r_inv;
+  const float P_over_rho2_i = pi.Pr2 * f_ij;
+  const float P_over_rho2_j = pj.Pr2 * f_ji;
+  const float sph_acc_term = __fmaf_rn(P_over_rho2_i, wi_dr, P_over_rho2_j * wj_dr) * r_inv;
+  const float macc = pj.m * (sph_acc_term + visc_acc_term);
+  a.ax = __fmaf_rn(-macc, dx, a.ax);
+  a.ay = __fmaf_rn(-macc, dy, a.ay);
+  a.az = __fmaf_rn(-macc, dz, a.az);
+  const float sph_du_term_i = P_over_rho2_i * dvdr * r_inv * wi_dr;
+  const float alpha_diff = __fmaf_rn(pi.P, pi.adiff, pj.P * pj.adiff) * fast_rcp(pi.P + pj.P);
+  const float dP2 = 2.f * fabsf(pi.P - pj.P) * rho_ij_inv;
+  const float v_diff = alpha_diff * 0.5f * ((dP2 > 0.f ? dP2 * rsqrtf(dP2) : 0.f) + fabsf(r_inv * dvdr_H));
+  const float diff_du_term = v_diff * (pi.u - pj.u) * __fmaf_rn(f_ij * wi_dr, rhoi_inv, f_ji * wj_dr * rhoj_inv);
+  const float du = __fmaf_rn(0.5f * visc_acc_term, dvdr_H, sph_du_term_i) + diff_du_term;
+  a.u_dt = __fmaf_rn(du, pj.m, a.u_dt);
+  a.h_dt -= pj.m * dvdr * r_inv * rhoj_inv * wi_dr;
+  if (pj.bin > 0) a.min_bin = min(a.min_bin, pj.bin);
+}
+
 // the gradient loop's pairs (SPHENIX): slot 3 of the counters, its own buffer
 __device__ __forceinline__ void record_pair_grad(const Dev &d, long long i, long long j) {
   const unsigned long long k = atomicAdd(&d.rec_count[3], 1ULL);

@@ -202,10 +202,6 @@ int swift_cuda_create(const swift_cuda_params *params, int device, swift_cuda_ct
     delete c;
     return fail("swift_cuda_create: unknown scheme");
   }
-  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX && c->prm.fields_mode != SWIFT_CUDA_FIELDS_EXACT) {
-    delete c;
-    return fail("swift_cuda_create: the SPHENIX scheme runs in the EXACT fields mode only");
-  }
   c->device = device;
   std::memset(&c->dev, 0, sizeof(Dev));
   if (const char *e = getenv("SWIFT_CUDA_PATH")) c->path = atoi(e);
@@ -882,7 +878,8 @@ static int launch_force(swift_cuda_ctx *c) {
     const int nb = c->grid_force;
     const bool fast = c->prm.fields_mode == SWIFT_CUDA_FIELDS_FAST;
     if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) {
-      k_force<SWIFT_CUDA_SCHEME_SPHENIX, false><<<nb, kBlock, 0, c->stream>>>(d);
+      if (fast) k_force_fast<SWIFT_CUDA_SCHEME_SPHENIX><<<nb, kBlock, 0, c->stream>>>(d, c->force_slow, c->fast_qd);
+      else k_force<SWIFT_CUDA_SCHEME_SPHENIX, false><<<nb, kBlock, 0, c->stream>>>(d);
     } else if (c->prm.scheme == SWIFT_CUDA_SCHEME_PLANETARY) {
       if (fast) k_force_fast<SWIFT_CUDA_SCHEME_PLANETARY><<<nb, kBlock, 0, c->stream>>>(d, c->force_slow, c->fast_qd);
       else k_force<SWIFT_CUDA_SCHEME_PLANETARY, false><<<nb, kBlock, 0, c->stream>>>(d);

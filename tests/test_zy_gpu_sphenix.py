@@ -64,9 +64,9 @@ def _active(g):
     return g["ic"]["time_bin"] <= g["params"].get("max_active_bin", 56)
 
 
-def _build_golden(g, record):
+def _build_golden(g, record, fields_mode=0):
     cells, tasks, nt = gu.tree_structs(g)
-    be = _backend(g["params"], g["props"])
+    be = _backend(g["params"], g["props"], fields_mode)
     gc = (B.Cell * len(cells))()
     C.memmove(gc, cells, C.sizeof(B.Cell) * len(cells))
     gt = (B.Task * max(nt, 1))()
@@ -117,6 +117,35 @@ def test_sphenix_golden_whole_step(name):
     c = be.counters()
     assert [c["n_density"], c["n_density_redo"], c["n_force"], out["n_gradient"]] == [int(v) for v in g["counts"]]
     be.close()
+
+
+@pytest.mark.parametrize("name", gu.sphenix_names())
+def test_sphenix_golden_fast_fields_mode(name):
+    """fields_mode = FAST (k_force_fast<2>: FMA / MUFU arithmetic in the scheme's force interaction): the pair lists
+    of all four loops, the counts and every field up to and including the extra ghost bit-exact; a, u_dt, h_dt
+    within 1e-4 (BASELINE.json: north_star) relative to max(|reference|, 0.1 x the rms of the field)."""
+    g = gu.load_sphenix(name)
+    act = _active(g)
+    n = len(g["h"])
+    be = _build_golden(g, record=True, fields_mode=1)
+    be.step()
+    out = _both(be)
+    _assert_fields(out, g, AFTER_EXTRA_GHOST + AFTER_GHOST + [("v_sig", "f_v_sig"), ("min_ngb_time_bin", "f_min_ngb_time_bin")],
+                   act, "step (FAST)")
+    c = be.counters()
+    assert [c["n_density"], c["n_density_redo"], c["n_force"], out["n_gradient"]] == [int(v) for v in g["counts"]]
+    for s in range(4):
+        assert gu.pair_digest(be.fetch_pairs(s, n * 400)) == str(g["digests"][s]), "pair list of loop %d differs" % s
+    be.close()
+    worst = {}
+    for kg, ko in (("a", "f_a"), ("u_dt", "f_u_dt"), ("h_dt", "f_h_dt")):
+        a, b = np.asarray(out[kg], dtype=np.float64), np.asarray(g[ko], dtype=np.float64)
+        if act is not None:
+            a, b = a[act], b[act]
+        rms = float(np.sqrt(np.mean(b ** 2)))
+        worst[kg] = float((np.abs(a - b) / np.maximum(np.abs(b), max(0.1 * rms, 1e-30))).max())
+        assert worst[kg] <= parity.TOL_FORCE, "FAST field %s: relative error %g" % (kg, worst[kg])
+    print(name, "SPHENIX FAST worst relative errors:", worst)
 
 
 def _oracle_on_library_tree(ic, tree, kw, record=False):
@@ -194,28 +223,37 @@ def test_sphenix_library_tree_sub_tasks():
 def test_sphenix_state_is_carried_on_the_device():
     """Two steps in a row: the viscosity / diffusion alphas and div_v_previous_step the first step leaves stay in
     HBM and are what the second step starts from (only x, v, h, u go up again), as p->viscosity / p->diffusion
-    persist in the reference's struct part.  The oracle gets the first step's outputs as the second one's inputs."""
-    ic = _state(ics.uniform_random(16 ** 3, seed=8), 13)
+    persist in the reference's struct part.  The oracle gets the first step's outputs as the second one's inputs.
+    (Converged smoothing lengths from the start, as after the reference's engine_init_particles: the top-level
+    grid is then sized for them.)"""
+    import integ_lib as il
+    kw = dict(periodic=True, alpha=0.1, scheme=2)
+    ic = ics.uniform_random(16 ** 3, seed=8)
     ic["v"] = (ic["v"] - 0.3 * (ic["x"] - 0.5)).astype(np.float32)
-    kw = dict(periodic=True, alpha=0.1)
+    icc, (cells, tasks, nt) = il.prepare(ic, kw)
+    icc = _state(icc, 13)
     be = _backend(kw, ol.SPHENIX_PROPS)
-    be.build(ic)
-    _set_state(be, ic)
+    gc = (B.Cell * len(cells))()
+    C.memmove(gc, cells, C.sizeof(B.Cell) * len(cells))
+    gt = (B.Task * max(nt, 1))()
+    C.memmove(gt, tasks, C.sizeof(B.Task) * nt)
+    be.build_from_cells(icc, gc, gt, nt)
+    _set_state(be, icc)
     be.step()
     r1 = _both(be)
-    tree = be.tree()
-    ic2 = dict(ic)
+    ic2 = dict(icc)
     ic2["h"] = r1["h"].copy()
     be.update_particles(ic2)
     be.step()
     r2 = _both(be)
     c2 = be.counters()
     be.close()
-    o1 = _oracle_on_library_tree(ic, tree, kw)
+    prm = ol.make_params(**kw)
+    o1 = ol.run_step("oracle", prm, icc, cells, tasks, nt, sphenix=ol.SPHENIX_PROPS)
     _assert_fields(r1, o1, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST, None, "step 1")
     ic2["in_alpha_visc"], ic2["in_alpha_diff"], ic2["in_div_v_prev"] = o1["e_alpha_visc"], o1["e_alpha_diff"], \
         o1["e_div_v_prev"]
-    o2 = _oracle_on_library_tree(ic2, tree, kw)
+    o2 = ol.run_step("oracle", prm, ic2, cells, tasks, nt, sphenix=ol.SPHENIX_PROPS)
     assert [c2["n_density"], c2["n_density_redo"], c2["n_force"], r2["n_gradient"]] == o2["counts"]
     _assert_fields(r2, o2, AFTER_FORCE + AFTER_EXTRA_GHOST + AFTER_GHOST, None, "step 2")
     assert not np.array_equal(r1["alpha_visc"], r2["alpha_visc"]), "the alphas should have moved between the steps"
@@ -271,10 +309,6 @@ def test_sphenix_resident_engine_loop():
 
 def test_sphenix_refusals():
     """What is not built for the scheme fails loudly instead of computing something else."""
-    prm = parity.gpu_params(dict(periodic=True, scheme=B.SCHEME_SPHENIX))
-    prm.fields_mode = 1
-    with pytest.raises(B.SwiftCudaError, match="EXACT fields mode only"):
-        HydroBackend(prm)
     be = _backend(dict(periodic=True, alpha=0.1), ol.SPHENIX_PROPS)
     ic = ics.uniform_random(1000, seed=1)
     be.build(ic)
