@@ -224,6 +224,11 @@ typedef struct {
   int rho_dh, wcount, wcount_dh, div_v, rot_v;         /* p->density.* (union with p->force.*) */
   int f, pressure, soundspeed, v_sig, h_dt, balsara;   /* p->force.* */
   int time_bin, min_ngb_time_bin, id, mat_id;          /* p->time_bin, p->limiter_data.min_ngb_time_bin, p->id, p->mat_id */
+  /* SPHENIX records (src/hydro/SPHENIX/hydro_part.h, 160 bytes; div_v and v_sig above are then
+   * p->viscosity.div_v / p->viscosity.v_sig); -1 in the two-loop schemes */
+  int alpha_visc, div_v_previous_step, div_v_dt;       /* p->viscosity.{alpha, div_v_previous_step, div_v_dt} */
+  int alpha_diff, laplace_u;                           /* p->diffusion.{alpha, laplace_u} */
+  int alpha_visc_max_ngb;                              /* p->force.alpha_visc_max_ngb */
 } swift_cuda_part_layout;
 
 /* Phases of swift_cuda_step_parts.  With SWIFT_CUDA_PHASE_KEEP the density loop continues the running
@@ -240,7 +245,13 @@ enum {
   SWIFT_CUDA_PHASE_FORCE = 8,
   SWIFT_CUDA_PHASE_END_FORCE = 16,
   SWIFT_CUDA_PHASE_KEEP = 32,
-  SWIFT_CUDA_PHASE_ALL = 1 | 2 | 4 | 8 | 16
+  SWIFT_CUDA_PHASE_ALL = 1 | 2 | 4 | 8 | 16,
+  /* SPHENIX contexts only: the gradient loop (continues p->viscosity.v_sig, p->diffusion.laplace_u,
+   * p->force.alpha_visc_max_ngb as found in the records unless SWIFT_CUDA_PHASE_GHOST runs in the same call)
+   * and runner_do_extra_ghost */
+  SWIFT_CUDA_PHASE_GRADIENT = 64,
+  SWIFT_CUDA_PHASE_EXTRA_GHOST = 128,
+  SWIFT_CUDA_PHASE_ALL_SPHENIX = 1 | 2 | 4 | 8 | 16 | 64 | 128
 };
 
 /* As swift_cuda_build_from_cells, from `n` records in cell order. */
@@ -255,6 +266,13 @@ int swift_cuda_build_from_parts(swift_cuda_ctx *ctx, const swift_cuda_part_layou
  *   DENSITY            p->rho, p->density.{rho_dh, wcount, wcount_dh, div_v, rot_v}   (raw sums)
  *   GHOST              p->h, p->rho, p->force.{f, pressure, soundspeed, balsara, v_sig, h_dt}, p->a_hydro, p->u_dt
  *   FORCE / END_FORCE  p->a_hydro, p->u_dt, p->force.{h_dt, v_sig}, p->limiter_data.min_ngb_time_bin
+ * SPHENIX records (what the reference's operators of that scheme write, no more):
+ *   GHOST              p->h, p->rho, p->force.{f, pressure, soundspeed, balsara, alpha_visc_max_ngb},
+ *                      p->viscosity.{div_v, v_sig}, p->diffusion.laplace_u
+ *   GRADIENT           p->viscosity.v_sig, p->diffusion.laplace_u, p->force.alpha_visc_max_ngb
+ *   EXTRA_GHOST        p->diffusion.{laplace_u, alpha}, p->viscosity.{alpha, div_v_previous_step, div_v_dt},
+ *                      p->a_hydro, p->u_dt, p->force.h_dt
+ *   FORCE / END_FORCE  p->a_hydro, p->u_dt, p->force.h_dt, p->limiter_data.min_ngb_time_bin
  * `parts` should be page-locked for the copies to run at full PCIe rate. */
 int swift_cuda_step_parts(swift_cuda_ctx *ctx, void *parts, int phases);
 /* e->max_active_bin of the step that starts (outside the time-integration mode, where
@@ -390,8 +408,9 @@ int swift_cuda_get_integrator_timings(swift_cuda_ctx *ctx, float ms[4]);
  * hydro_predict_extra / hydro_kick_extra / hydro_compute_timestep are Minimal's arithmetic;
  * swift_cuda_integrator_init makes its time_base the one of the extra ghost's dt_alpha) and the entries
  * below; both fields modes (FAST: k_force_fast with the scheme's interaction; the gradient loop and the extra
- * ghost stay exact, they decide the alphas).  The struct part entries, swift_cuda_step_io and the halo entries
- * refuse a SPHENIX context (the 160-byte record and the wider halo are not built). */
+ * ghost stay exact, they decide the alphas); the struct part entries with the scheme's 160-byte record
+ * (swift_cuda_part_layout's SPHENIX offsets, SWIFT_CUDA_PHASE_GRADIENT / _EXTRA_GHOST).  swift_cuda_step_io
+ * and the halo entries refuse a SPHENIX context (the wider halo is not built). */
 typedef struct {
   float viscosity_alpha_max;  /* hydro_props->viscosity.alpha_max, SPH:viscosity_alpha_max (2.0) */
   float viscosity_alpha_min;  /* ->viscosity.alpha_min (0.0) */

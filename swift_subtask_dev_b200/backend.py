@@ -166,7 +166,8 @@ class PartLayout(C.Structure):
     _fields_ = [(k, C.c_int) for k in
                 ("stride", "x", "v", "a_hydro", "mass", "h", "u", "u_dt", "rho", "rho_dh", "wcount", "wcount_dh", "div_v",
                  "rot_v", "f", "pressure", "soundspeed", "v_sig", "h_dt", "balsara", "time_bin", "min_ngb_time_bin", "id",
-                 "mat_id")]
+                 "mat_id", "alpha_visc", "div_v_previous_step", "div_v_dt", "alpha_diff", "laplace_u",
+                 "alpha_visc_max_ngb")]
 
 
 # Byte offsets of the reference's `struct part` (src/hydro/Minimal/hydro_part.h:98-189, Planetary :100-192;
@@ -175,10 +176,21 @@ class PartLayout(C.Structure):
 _PART_COMMON = dict(stride=128, x=16, v=40, a_hydro=52, mass=64, h=68, u=72, u_dt=76, rho=80, rho_dh=92, wcount=84,
                     wcount_dh=88, div_v=96, rot_v=100, f=84, pressure=88, soundspeed=92, v_sig=96, h_dt=100, balsara=104,
                     id=0)
-PART_LAYOUTS = {SCHEME_MINIMAL: dict(_PART_COMMON, time_bin=113, min_ngb_time_bin=115, mat_id=-1),
-                SCHEME_PLANETARY: dict(_PART_COMMON, time_bin=117, min_ngb_time_bin=119, mat_id=112)}
+_NO_SPHENIX = dict(alpha_visc=-1, div_v_previous_step=-1, div_v_dt=-1, alpha_diff=-1, laplace_u=-1,
+                   alpha_visc_max_ngb=-1)
+# SPHENIX (src/hydro/SPHENIX/hydro_part.h, 160 bytes, probe-compiled the same way): p->viscosity {div_v, div_v_dt,
+# div_v_previous_step, alpha, v_sig} at 84, p->diffusion {laplace_u, alpha} at 104, the density / force union at 112
+_PART_SPHENIX = dict(stride=160, id=0, x=16, v=40, a_hydro=52, mass=64, h=68, u=72, u_dt=76, rho=80, div_v=84,
+                     div_v_dt=88, div_v_previous_step=92, alpha_visc=96, v_sig=100, laplace_u=104, alpha_diff=108,
+                     wcount=112, wcount_dh=116, rho_dh=120, rot_v=124, f=112, pressure=116, soundspeed=120, h_dt=124,
+                     balsara=128, alpha_visc_max_ngb=132, time_bin=137, min_ngb_time_bin=139, mat_id=-1)
+PART_LAYOUTS = {SCHEME_MINIMAL: dict(_PART_COMMON, time_bin=113, min_ngb_time_bin=115, mat_id=-1, **_NO_SPHENIX),
+                SCHEME_PLANETARY: dict(_PART_COMMON, time_bin=117, min_ngb_time_bin=119, mat_id=112, **_NO_SPHENIX),
+                SCHEME_SPHENIX: _PART_SPHENIX}
 PHASE_SORT, PHASE_DENSITY, PHASE_GHOST, PHASE_FORCE, PHASE_END_FORCE, PHASE_KEEP = 1, 2, 4, 8, 16, 32
 PHASE_ALL = 31
+PHASE_GRADIENT, PHASE_EXTRA_GHOST = 64, 128   # SPHENIX only
+PHASE_ALL_SPHENIX = PHASE_ALL | PHASE_GRADIENT | PHASE_EXTRA_GHOST
 
 
 def part_dtype(scheme=SCHEME_MINIMAL):
@@ -191,6 +203,8 @@ def part_dtype(scheme=SCHEME_MINIMAL):
     if L["mat_id"] >= 0:
         names.append("mat_id")
         fmts["mat_id"] = "<i4"
+    if L["alpha_visc"] >= 0:
+        names += ["alpha_visc", "div_v_previous_step", "div_v_dt", "alpha_diff", "laplace_u", "alpha_visc_max_ngb"]
     return np.dtype({"names": names, "formats": [fmts.get(k, "<f4") for k in names],
                      "offsets": [L[k] for k in names], "itemsize": L["stride"]})
 
@@ -215,6 +229,12 @@ def parts_from_ic(ic, scheme=SCHEME_MINIMAL, pinned=False):
     parts["time_bin"] = ic["time_bin"] if ic.get("time_bin") is not None else 1
     if "mat_id" in dt.names:
         parts["mat_id"] = ic["mat_id"] if ic.get("mat_id") is not None else 0
+    if "alpha_visc" in dt.names:
+        # p->viscosity.alpha, p->diffusion.alpha, p->viscosity.div_v_previous_step as a previous step left them
+        for k_rec, k_ic in (("alpha_visc", "in_alpha_visc"), ("alpha_diff", "in_alpha_diff"),
+                            ("div_v_previous_step", "in_div_v_prev")):
+            if ic.get(k_ic) is not None:
+                parts[k_rec] = ic[k_ic]
     return parts
 
 

@@ -129,6 +129,7 @@ struct AosDst {
   float4 *dens0, *dens1, *acc;
   float *h_dt, *v_sig;
   int *min_bin;
+  float4 *sph_state, *sph_grad;  // SPHENIX records only (null otherwise)
 };
 template <typename T>
 __device__ __forceinline__ T aos_get(const unsigned char *rec, int off) {
@@ -173,6 +174,14 @@ __global__ void k_pack_aos(int64_t n, const unsigned char *aos, swift_cuda_part_
     a.h_dt[k] = aos_get<float>(r, L.h_dt);
     a.v_sig[k] = aos_get<float>(r, L.v_sig);
     a.min_bin[k] = L.min_ngb_time_bin >= 0 ? (int)aos_get<int8_t>(r, L.min_ngb_time_bin) : 57;
+  }
+  if (a.sph_state != nullptr) {
+    // SPHENIX: what the scheme carries in the record from step to step, and the gradient loop's running
+    // values (read by active lanes only when the ghost did not run in this call)
+    a.sph_state[k] = make_float4(aos_get<float>(r, L.alpha_visc), aos_get<float>(r, L.alpha_diff),
+                                 aos_get<float>(r, L.div_v_previous_step), aos_get<float>(r, L.div_v_dt));
+    a.sph_grad[k] = make_float4(aos_get<float>(r, L.div_v), aos_get<float>(r, L.laplace_u),
+                                aos_get<float>(r, L.alpha_visc_max_ngb), 0.f);
   }
   if (with_static) {
     o.mat_id[k] = L.mat_id >= 0 ? aos_get<int32_t>(r, L.mat_id) : 0;

@@ -15,6 +15,7 @@
 // floats formed in double and rounded once to float is the float product.
 #pragma once
 #include "kernels.cuh"
+#include "pack.cuh"
 
 namespace swiftcuda {
 
@@ -50,15 +51,19 @@ __device__ void sphenix_converged(const Dev &d, int64_t p, float h, float4 s0, f
 
 // Start of a step: the neighbour records of the INACTIVE particles (their rho, c, alphas persist from their
 // last active step; active particles get theirs from the ghost and the extra ghost).
-__global__ void k_sphenix_prep(Dev d) {
+// mode (swift_cuda_step_parts with phases in separate calls): bit 0 -- the ghost does not run in this call, the
+// ACTIVE particles' gradient-loop record comes from the uploaded state too; bit 1 -- the same for the force-loop
+// record when the extra ghost does not run.
+__global__ void k_sphenix_prep(Dev d, int mode) {
   const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (p >= d.n) return;
-  if (d.time_bin[p] <= kc.max_active_bin) return;
+  const bool active = d.time_bin[p] <= kc.max_active_bin;
+  if (active && mode == 0) return;
   const float4 st = d.sph_state[p];
   const float4 f = d.fin[p];
   const float u = d.u[p];
-  d.gin[p] = make_float4(u, f.x, f.w, st.x);
-  d.sx[p] = make_float4(st.x, st.y, u, 0.f);
+  if (!active || (mode & 1)) d.gin[p] = make_float4(u, f.x, f.w, st.x);
+  if (!active || (mode & 2)) d.sx[p] = make_float4(st.x, st.y, u, 0.f);
 }
 
 // runner_do_extra_ghost, one thread per particle
@@ -149,6 +154,51 @@ __global__ void k_sphenix_unpack(Dev d, const int32_t *order, float *out) {
   out[4 * d.n + s] = st.y;
   out[5 * d.n + s] = st.z;
   out[6 * d.n + s] = st.w;
+}
+
+// struct part write-back of a SPHENIX record (swift_cuda_step_parts): exactly the fields the reference's
+// operators of the phases that ran write, for active particles.  ran: SWIFT_CUDA_PHASE_* bits.
+__global__ void k_unpack_aos_sphenix(Dev d, unsigned char *aos, swift_cuda_part_layout L, const int32_t *order, int ran,
+                                     int max_active_bin, int64_t lo, int64_t hi) {
+  const int64_t k = lo + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= hi) return;
+  if (d.time_bin[k] > max_active_bin) return;
+  const int64_t s = order ? order[k] : k;
+  unsigned char *r = aos + (size_t)s * L.stride;
+  const float4 sg = d.sph_grad[k];
+  if (ran & SWIFT_CUDA_PHASE_GHOST) {
+    const float4 f = d.fin[k];
+    aos_put<float>(r, L.h, d.h[k]);
+    aos_put<float>(r, L.rho, f.x);
+    aos_put<float>(r, L.pressure, f.y);
+    aos_put<float>(r, L.f, f.z);
+    aos_put<float>(r, L.soundspeed, f.w);
+    aos_put<float>(r, L.balsara, d.hb[k].y);
+    aos_put<float>(r, L.div_v, sg.x);
+  }
+  if (ran & (SWIFT_CUDA_PHASE_GHOST | SWIFT_CUDA_PHASE_GRADIENT)) {
+    aos_put<float>(r, L.v_sig, d.v_sig[k]);
+    aos_put<float>(r, L.alpha_visc_max_ngb, sg.z);
+  }
+  if (ran & (SWIFT_CUDA_PHASE_GHOST | SWIFT_CUDA_PHASE_GRADIENT | SWIFT_CUDA_PHASE_EXTRA_GHOST))
+    aos_put<float>(r, L.laplace_u, sg.y);
+  if (ran & SWIFT_CUDA_PHASE_EXTRA_GHOST) {
+    const float4 st = d.sph_state[k];
+    aos_put<float>(r, L.alpha_visc, st.x);
+    aos_put<float>(r, L.alpha_diff, st.y);
+    aos_put<float>(r, L.div_v_previous_step, st.z);
+    aos_put<float>(r, L.div_v_dt, st.w);
+  }
+  if (ran & (SWIFT_CUDA_PHASE_EXTRA_GHOST | SWIFT_CUDA_PHASE_FORCE | SWIFT_CUDA_PHASE_END_FORCE)) {
+    const float4 a = d.acc[k];
+    aos_put<float>(r, L.a_hydro, a.x);
+    aos_put<float>(r, L.a_hydro + 4, a.y);
+    aos_put<float>(r, L.a_hydro + 8, a.z);
+    aos_put<float>(r, L.u_dt, a.w);
+    aos_put<float>(r, L.h_dt, d.h_dt[k]);
+  }
+  if ((ran & SWIFT_CUDA_PHASE_FORCE) && L.min_ngb_time_bin >= 0)
+    aos_put<int8_t>(r, L.min_ngb_time_bin, (int8_t)d.min_bin[k]);
 }
 
 }  // namespace swiftcuda

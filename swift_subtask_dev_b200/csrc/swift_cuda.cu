@@ -103,6 +103,7 @@ struct swift_cuda_ctx {
   float *s_sph_out = nullptr;
   int grid_gradient = 0;
   long long n_gradient = 0;
+  int sph_prep_mode = 0;   // k_sphenix_prep: swift_cuda_step_parts calls that run without the ghost / the extra ghost
   int fast_qd = kQD;   // rows of the hit FIFO k_force_fast uses (SWIFT_CUDA_FAST_QD)
   int force_slow = 0;  // test hook (SWIFT_CUDA_SLOW=1): every hit takes the exact sorted-axis-cut path
 };
@@ -779,7 +780,7 @@ static int launch_density_prep(swift_cuda_ctx *c) {
   k_init_step<<<nb, 256, 0, c->stream>>>(d);
   c->counters.n_kernel_launches += 1;
   if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX && c->n > 0) {
-    k_sphenix_prep<<<nb, 256, 0, c->stream>>>(d);
+    k_sphenix_prep<<<nb, 256, 0, c->stream>>>(d, c->sph_prep_mode);
     c->counters.n_kernel_launches += 1;
   }
   CK(cudaGetLastError());
@@ -1145,6 +1146,19 @@ static inline T rec_get(const unsigned char *r, int off) {
   std::memcpy(&v, r + off, sizeof(T));
   return v;
 }
+// a SPHENIX context needs the scheme's fields in the record, the two-loop schemes must not name them
+static int check_sphenix_layout(const swift_cuda_ctx *c, const swift_cuda_part_layout *L) {
+  if (!c || !L) return fail("parts: null argument");
+  const int sx[] = {L->alpha_visc, L->div_v_previous_step, L->div_v_dt, L->alpha_diff, L->laplace_u,
+                    L->alpha_visc_max_ngb};
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) {
+    for (int o : sx)
+      if (o < 0 || o + 4 > L->stride) return fail("parts: the SPHENIX scheme needs the offsets of p->viscosity / "
+                                                   "p->diffusion / p->force.alpha_visc_max_ngb in the record layout");
+  }
+  return 0;
+}
+
 static void aos_to_soa(const swift_cuda_part_layout &L, const void *parts, int64_t n, HostSoA &o,
                        swift_cuda_parts_in &in) {
   o.x.resize(3 * n); o.v.resize(3 * n); o.mass.resize(n); o.h.resize(n); o.u.resize(n);
@@ -1332,8 +1346,7 @@ int swift_cuda_build_from_cells_parts(swift_cuda_ctx *c, const swift_cuda_part_l
                                       int ncells, const swift_cuda_cell *cells, int ntasks,
                                       const swift_cuda_task *tasks) {
   if (!c || !parts) return fail("build_from_cells_parts: null argument");
-  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX)
-    return fail("build_from_cells_parts: the struct part entries are not built for the SPHENIX scheme (160-byte record)");
+  if (check_sphenix_layout(c, L)) return 1;
   if (check_layout(L)) return 1;
   HostSoA soa;
   swift_cuda_parts_in in;
@@ -1347,8 +1360,7 @@ int swift_cuda_build_from_cells_parts(swift_cuda_ctx *c, const swift_cuda_part_l
 
 int swift_cuda_build_from_parts(swift_cuda_ctx *c, const swift_cuda_part_layout *L, const void *parts, int64_t n) {
   if (!c || !parts) return fail("build_from_parts: null argument");
-  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX)
-    return fail("build_from_parts: the struct part entries are not built for the SPHENIX scheme (160-byte record)");
+  if (check_sphenix_layout(c, L)) return 1;
   if (check_layout(L)) return 1;
   HostSoA soa;
   swift_cuda_parts_in in;
@@ -1382,12 +1394,16 @@ int swift_cuda_step_parts(swift_cuda_ctx *c, void *parts, int phases) {
   const swift_cuda_part_layout L = c->lay;
   const bool do_dens = phases & SWIFT_CUDA_PHASE_DENSITY, do_ghost = phases & SWIFT_CUDA_PHASE_GHOST;
   const bool do_force = phases & SWIFT_CUDA_PHASE_FORCE, do_end = phases & SWIFT_CUDA_PHASE_END_FORCE;
+  const bool sphenix = c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX;
+  const bool do_grad = phases & SWIFT_CUDA_PHASE_GRADIENT, do_extra = phases & SWIFT_CUDA_PHASE_EXTRA_GHOST;
+  if ((do_grad || do_extra) && !sphenix)
+    return fail("step_parts: SWIFT_CUDA_PHASE_GRADIENT / _EXTRA_GHOST exist in the SPHENIX scheme only");
   const bool keep = (phases & SWIFT_CUDA_PHASE_KEEP) || (do_ghost && !do_dens);
   c->counters.n_kernel_launches = 0;
   const WorkLists &wl = c->wl;
   const int P = c->pieces;
   // records in cell order and enough of them: the step runs in P pieces of consecutive leaves at both ends
-  const bool pieces_ok = P > 1 && c->records_in_cell_order && n >= (1 << 18) && d.n_units >= 64 * P &&
+  const bool pieces_ok = !sphenix && P > 1 && c->records_in_cell_order && n >= (1 << 18) && d.n_units >= 64 * P &&
                          (int64_t)wl.unit_begin.size() == (int64_t)wl.leaves.size() + 1;
   if (pieces_ok && c->plan.P != P) build_piece_plan(c, P);
   CK(cudaEventRecord(c->ev[0], c->stream));
@@ -1399,6 +1415,10 @@ int swift_cuda_step_parts(swift_cuda_ctx *c, void *parts, int phases) {
   o.id = const_cast<int64_t *>(d.id);
   AosDst a;
   a.dens0 = d.dens0; a.dens1 = d.dens1; a.acc = d.acc; a.h_dt = d.h_dt; a.v_sig = d.v_sig; a.min_bin = d.min_bin;
+  a.sph_state = d.sph_state; a.sph_grad = d.sph_grad;  // null unless SPHENIX
+  // SPHENIX phases in separate calls: the neighbour records of ACTIVE particles come from the uploaded state when
+  // the phase that would write them does not run here
+  c->sph_prep_mode = sphenix ? ((do_ghost ? 0 : 1) | (do_extra ? 0 : 2)) : 0;
   const int32_t *order = (c->tree.order.empty() || c->records_in_cell_order) ? nullptr : c->s_order;
   const unsigned nb = (unsigned)((n + 255) / 256);
   const int load_force = (!do_dens && !do_ghost) ? 1 : 0;
@@ -1427,8 +1447,14 @@ int swift_cuda_step_parts(swift_cuda_ctx *c, void *parts, int phases) {
   }
   CK(cudaEventRecord(c->ev[2], c->stream));
   if (do_ghost && launch_ghost(c)) return 1;
+  if (do_grad && launch_gradient(c)) return 1;
+  if (do_extra && launch_extra_ghost(c)) return 1;
+  c->sph_prep_mode = 0;
   CK(cudaEventRecord(c->ev[3], c->stream));
   const int what = (do_force || do_end) ? (do_ghost ? 16 : 8) : (do_ghost ? 4 : (do_dens ? 2 : 0));
+  // SPHENIX: density alone leaves the raw sums (the common code below); any later phase writes its own fields
+  const int ran = phases & (SWIFT_CUDA_PHASE_GHOST | SWIFT_CUDA_PHASE_GRADIENT | SWIFT_CUDA_PHASE_EXTRA_GHOST |
+                            SWIFT_CUDA_PHASE_FORCE | SWIFT_CUDA_PHASE_END_FORCE);
   const bool in_pieces = do_force && pieces_ok;
   if (in_pieces) {
     // The force loop over the units of consecutive leaves, piece by piece: the records of a finished piece
@@ -1470,8 +1496,11 @@ int swift_cuda_step_parts(swift_cuda_ctx *c, void *parts, int phases) {
     CK(cudaEventRecord(c->ev[4], c->stream));
     d.keep_sums = 0;
     d.no_end_force = 0;
-    if (what && n > 0) {
-      k_unpack_aos<<<nb, 256, 0, c->stream>>>(d, c->d_aos, L, order, what, c->prm.max_active_bin, 0, n);
+    if ((sphenix ? (what | ran) : what) && n > 0) {
+      if (sphenix && ran)
+        k_unpack_aos_sphenix<<<nb, 256, 0, c->stream>>>(d, c->d_aos, L, order, ran, c->prm.max_active_bin, 0, n);
+      else
+        k_unpack_aos<<<nb, 256, 0, c->stream>>>(d, c->d_aos, L, order, what, c->prm.max_active_bin, 0, n);
       c->counters.n_kernel_launches += 1;
       CK(cudaGetLastError());
       CK(cudaMemcpyAsync(parts, c->d_aos, (size_t)n * L.stride, cudaMemcpyDeviceToHost, c->stream));

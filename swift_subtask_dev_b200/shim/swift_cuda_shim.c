@@ -64,12 +64,20 @@ static swift_cuda_part_layout shim_layout(void) {
   L.rho_dh = (int)offsetof(struct part, density.rho_dh);
   L.wcount = (int)offsetof(struct part, density.wcount);
   L.wcount_dh = (int)offsetof(struct part, density.wcount_dh);
+#ifdef SPHENIX_SPH
+  L.div_v = (int)offsetof(struct part, viscosity.div_v);
+#else
   L.div_v = (int)offsetof(struct part, density.div_v);
+#endif
   L.rot_v = (int)offsetof(struct part, density.rot_v);
   L.f = (int)offsetof(struct part, force.f);
   L.pressure = (int)offsetof(struct part, force.pressure);
   L.soundspeed = (int)offsetof(struct part, force.soundspeed);
+#ifdef SPHENIX_SPH
+  L.v_sig = (int)offsetof(struct part, viscosity.v_sig);
+#else
   L.v_sig = (int)offsetof(struct part, force.v_sig);
+#endif
   L.h_dt = (int)offsetof(struct part, force.h_dt);
   L.balsara = (int)offsetof(struct part, force.balsara);
   L.time_bin = (int)offsetof(struct part, time_bin);
@@ -79,6 +87,16 @@ static swift_cuda_part_layout shim_layout(void) {
   L.mat_id = (int)offsetof(struct part, mat_id);
 #else
   L.mat_id = -1;
+#endif
+#ifdef SPHENIX_SPH
+  L.alpha_visc = (int)offsetof(struct part, viscosity.alpha);
+  L.div_v_previous_step = (int)offsetof(struct part, viscosity.div_v_previous_step);
+  L.div_v_dt = (int)offsetof(struct part, viscosity.div_v_dt);
+  L.alpha_diff = (int)offsetof(struct part, diffusion.alpha);
+  L.laplace_u = (int)offsetof(struct part, diffusion.laplace_u);
+  L.alpha_visc_max_ngb = (int)offsetof(struct part, force.alpha_visc_max_ngb);
+#else
+  L.alpha_visc = L.div_v_previous_step = L.div_v_dt = L.alpha_diff = L.laplace_u = L.alpha_visc_max_ngb = -1;
 #endif
   return L;
 }

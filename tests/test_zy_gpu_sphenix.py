@@ -307,6 +307,78 @@ def test_sphenix_resident_engine_loop():
         assert np.array_equal(np.asarray(sg[k]).reshape(-1), z[k].reshape(-1)), "%s vs the reference's golden state" % k
 
 
+# ---- struct part in, struct part out: the scheme's 160-byte record (src/hydro/SPHENIX/hydro_part.h) ----
+REC_AFTER_DENSITY = [("rho", "d_rho"), ("rho_dh", "d_rho_dh"), ("wcount", "d_wcount"), ("wcount_dh", "d_wcount_dh"),
+                     ("div_v", "d_div_v"), ("rot_v", "d_rot_v")]
+REC_AFTER_GHOST = [("h", "g_h"), ("rho", "g_rho"), ("f", "g_f"), ("pressure", "g_pressure"), ("soundspeed", "g_soundspeed"),
+                   ("balsara", "g_balsara"), ("div_v", "g_div_v")]
+REC_AFTER_GRADIENT = [("v_sig", "r_v_sig"), ("laplace_u", "r_laplace_u"), ("alpha_visc_max_ngb", "r_alpha_visc_max_ngb")]
+REC_AFTER_EXTRA = [("laplace_u", "e_laplace_u"), ("alpha_visc", "e_alpha_visc"), ("alpha_diff", "e_alpha_diff"),
+                   ("div_v_previous_step", "e_div_v_prev"), ("div_v_dt", "e_div_v_dt")]
+REC_AFTER_FORCE = [("a_hydro", "f_a"), ("u_dt", "f_u_dt"), ("h_dt", "f_h_dt"), ("v_sig", "f_v_sig"),
+                   ("min_ngb_time_bin", "f_min_ngb_time_bin")]
+
+
+def _records(g):
+    """The caller's array of struct part as it is before the step: inputs, the carried state of the scheme, and
+    for inactive particles what their last active step left in the force union."""
+    parts = B.parts_from_ic(g["ic"], scheme=B.SCHEME_SPHENIX)
+    parts["min_ngb_time_bin"] = 57   # num_time_bins + 1, as the reference's time-step task leaves it
+    for rec, key in (("rho", "in_rho"), ("pressure", "in_pressure"), ("f", "in_f"), ("soundspeed", "in_soundspeed"),
+                     ("balsara", "in_balsara")):
+        if g["ic"].get(key) is not None:
+            parts[rec] = g["ic"][key]
+    return parts
+
+
+def _parts_backend(g, parts):
+    cells, tasks, nt = gu.tree_structs(g, B.Cell, B.Task)
+    be = _backend(g["params"], g["props"])
+    be.build_from_parts(parts, cells, tasks, nt)
+    return be
+
+
+@pytest.mark.parametrize("name", gu.sphenix_names())
+def test_sphenix_struct_part_step(name):
+    """swift_cuda_step_parts on the scheme's records, all seven phases in one call: every field the reference's
+    operators write, in the record, bit for bit; inactive records untouched."""
+    g = gu.load_sphenix(name)
+    act = _active(g)
+    parts = _records(g)
+    before = parts.copy()
+    be = _parts_backend(g, parts)
+    be.step_parts(parts, B.PHASE_ALL_SPHENIX)
+    c = be.counters()
+    ngrad = be.sphenix_results()["n_gradient"]
+    be.close()
+    assert [c["n_density"], c["n_density_redo"], c["n_force"], ngrad] == [int(v) for v in g["counts"]]
+    table = REC_AFTER_GHOST + REC_AFTER_EXTRA + REC_AFTER_FORCE + [("alpha_visc_max_ngb", "r_alpha_visc_max_ngb")]
+    _assert_fields(parts, g, table, act, "step_parts")
+    if act is not None:
+        assert parts[~act].tobytes() == before[~act].tobytes(), "inactive records were written"
+
+
+@pytest.mark.parametrize("name", ["uniform14_periodic", "random11_timebins"])
+def test_sphenix_struct_part_phase_calls(name):
+    """One call per phase on the records, as a per-task shim makes them (each call uploads the records as they are
+    and writes back what its phase produces): the record after every call against the reference's stage values."""
+    g = gu.load_sphenix(name)
+    act = _active(g)
+    parts = _records(g)
+    be = _parts_backend(g, parts)
+    be.step_parts(parts, B.PHASE_SORT | B.PHASE_DENSITY)
+    _assert_fields(parts, g, REC_AFTER_DENSITY, act, "density call")
+    be.step_parts(parts, B.PHASE_GHOST)
+    _assert_fields(parts, g, REC_AFTER_GHOST, act, "ghost call")
+    be.step_parts(parts, B.PHASE_GRADIENT)
+    _assert_fields(parts, g, REC_AFTER_GRADIENT + REC_AFTER_GHOST, act, "gradient call")
+    be.step_parts(parts, B.PHASE_EXTRA_GHOST)
+    _assert_fields(parts, g, REC_AFTER_EXTRA + REC_AFTER_GHOST, act, "extra ghost call")
+    be.step_parts(parts, B.PHASE_FORCE | B.PHASE_END_FORCE)
+    be.close()
+    _assert_fields(parts, g, REC_AFTER_FORCE + REC_AFTER_EXTRA + REC_AFTER_GHOST, act, "force call")
+
+
 def test_sphenix_refusals():
     """What is not built for the scheme fails loudly instead of computing something else."""
     be = _backend(dict(periodic=True, alpha=0.1), ol.SPHENIX_PROPS)
