@@ -132,9 +132,33 @@ static void shim_params(const struct engine *e, swift_cuda_params *p) {
     t->P_min = til[k]->P_min; t->mat_id = til[k]->mat_id;
   }
   for (int k = 0; k < 4; k++) p->idg_gamma[k] = 5.f / 3.f;
+#elif defined(SPHENIX_SPH)
+  p->scheme = SWIFT_CUDA_SCHEME_SPHENIX;
+  for (int k = 0; k < 4; k++) p->idg_gamma[k] = 5.f / 3.f;
 #else
   p->scheme = SWIFT_CUDA_SCHEME_MINIMAL;
   for (int k = 0; k < 4; k++) p->idg_gamma[k] = 5.f / 3.f;
+#endif
+}
+
+/* A context for this engine: swift_cuda_create, and for SPHENIX the scheme's hydro_props and e->time_base
+ * (the extra ghost's dt_alpha is get_timestep(p->time_bin, e->time_base), src/runner_ghost.c:1045-1046). */
+static void shim_create(const struct engine *e, swift_cuda_ctx **ctx) {
+  swift_cuda_params prm;
+  shim_params(e, &prm);
+  CUDA_OK(swift_cuda_create(&prm, 0, ctx));
+#ifdef SPHENIX_SPH
+  const struct hydro_props *hp = e->hydro_properties;
+  swift_cuda_sphenix_props sp;
+  sp.viscosity_alpha_max = hp->viscosity.alpha_max;
+  sp.viscosity_alpha_min = hp->viscosity.alpha_min;
+  sp.viscosity_length = hp->viscosity.length;
+  sp.diffusion_alpha = hp->diffusion.alpha;
+  sp.diffusion_beta = hp->diffusion.beta;
+  sp.diffusion_alpha_max = hp->diffusion.alpha_max;
+  sp.diffusion_alpha_min = hp->diffusion.alpha_min;
+  sp.time_base = e->time_base;
+  CUDA_OK(swift_cuda_sphenix_set_props(*ctx, &sp));
 #endif
 }
 
@@ -226,11 +250,9 @@ static void shim_run_task(struct runner *r, struct cell *ci, struct cell *cj, in
   const int root_j = cj ? flatten_cell(&f, cj, -1, cj->hydro.parts, ni) : -1;
   swift_cuda_task t = {task_type, 0, root_j};
 
-  swift_cuda_params prm;
-  shim_params(e, &prm);
   const swift_cuda_part_layout L = shim_layout();
   swift_cuda_ctx *ctx = NULL;
-  CUDA_OK(swift_cuda_create(&prm, 0, &ctx));
+  shim_create(e, &ctx);
   CUDA_OK(swift_cuda_build_from_cells_parts(ctx, &L, buf, ni + nj, f.n, f.cells, 1, &t));
   CUDA_OK(swift_cuda_step_parts(ctx, buf, phases));
   swift_cuda_destroy(ctx);
@@ -292,17 +314,51 @@ void runner_do_ghost(struct runner *r, struct cell *c, int timer) {
   const struct engine *e = r->e;
   struct flat f = {0};
   flatten_cell(&f, c, -1, c->hydro.parts, 0);
-  swift_cuda_params prm;
-  shim_params(e, &prm);
   const swift_cuda_part_layout L = shim_layout();
   swift_cuda_ctx *ctx = NULL;
-  CUDA_OK(swift_cuda_create(&prm, 0, &ctx));
+  shim_create(e, &ctx);
   CUDA_OK(swift_cuda_build_from_cells_parts(ctx, &L, c->hydro.parts, c->hydro.count, f.n, f.cells, 0, NULL));
   CUDA_OK(swift_cuda_step_parts(ctx, c->hydro.parts, SWIFT_CUDA_PHASE_GHOST | SWIFT_CUDA_PHASE_KEEP));
   swift_cuda_destroy(ctx);
   refresh_hmax(&f, e);
   flat_free(&f);
 }
+
+#ifdef EXTRA_HYDRO_LOOP
+/* ---- SPHENIX: the gradient loop and the extra ghost (src/runner_doiact_hydro.h:168-191 with FUNCTION =
+ * gradient, src/runner_main.c:199-200, 249-250, 297-298, 343-344; src/runner_ghost.c:992-1075) --------- */
+#define GRADIENT_PHASES (SWIFT_CUDA_PHASE_SORT | SWIFT_CUDA_PHASE_GRADIENT)
+void runner_doself1_branch_gradient(struct runner *r, struct cell *c) {
+  if (!cell_is_active_hydro(c, r->e)) return;
+  shim_run_task(r, c, NULL, 0, GRADIENT_PHASES);
+}
+void runner_dopair1_branch_gradient(struct runner *r, struct cell *ci, struct cell *cj) {
+  if (!cell_is_active_hydro(ci, r->e) && !cell_is_active_hydro(cj, r->e)) return;
+  shim_run_task(r, ci, cj, 1, GRADIENT_PHASES);
+}
+void runner_dosub_self1_gradient(struct runner *r, struct cell *ci, int gettimer) {
+  if (!cell_is_active_hydro(ci, r->e)) return;
+  shim_run_task(r, ci, NULL, 2, GRADIENT_PHASES);
+}
+void runner_dosub_pair1_gradient(struct runner *r, struct cell *ci, struct cell *cj, int gettimer) {
+  if (!cell_is_active_hydro(ci, r->e) && !cell_is_active_hydro(cj, r->e)) return;
+  shim_run_task(r, ci, cj, 3, GRADIENT_PHASES);
+}
+/* hydro_end_gradient, hydro_prepare_force, hydro_reset_acceleration for the active particles of one cell */
+void runner_do_extra_ghost(struct runner *r, struct cell *c, int timer) {
+  if (c->hydro.count == 0 || !cell_is_active_hydro(c, r->e)) return;
+  const struct engine *e = r->e;
+  struct flat f = {0};
+  flatten_cell(&f, c, -1, c->hydro.parts, 0);
+  const swift_cuda_part_layout L = shim_layout();
+  swift_cuda_ctx *ctx = NULL;
+  shim_create(e, &ctx);
+  CUDA_OK(swift_cuda_build_from_cells_parts(ctx, &L, c->hydro.parts, c->hydro.count, f.n, f.cells, 0, NULL));
+  CUDA_OK(swift_cuda_step_parts(ctx, c->hydro.parts, SWIFT_CUDA_PHASE_EXTRA_GHOST));
+  swift_cuda_destroy(ctx);
+  flat_free(&f);
+}
+#endif /* EXTRA_HYDRO_LOOP */
 
 /* src/runner_sort.c:201-431.  The sorted lists live on the device and are rebuilt there by every
  * call that walks a pair; what is left for the host is the bookkeeping the callers look at. */
@@ -374,10 +430,8 @@ void swift_cuda_shim_rebuild(struct engine *e) {
     tasks[ntasks].cj = t->cj ? find_flat(&shim_flat, t->cj) : -1;
     ntasks++;
   }
-  swift_cuda_params prm;
-  shim_params(e, &prm);
   const swift_cuda_part_layout L = shim_layout();
-  if (shim_ctx == NULL) CUDA_OK(swift_cuda_create(&prm, 0, &shim_ctx));
+  if (shim_ctx == NULL) shim_create(e, &shim_ctx);
   CUDA_OK(swift_cuda_build_from_cells_parts(shim_ctx, &L, s->parts, (int64_t)s->nr_parts, shim_flat.n,
                                             shim_flat.cells, ntasks, tasks));
   free(tasks);
@@ -388,8 +442,11 @@ void swift_cuda_shim_rebuild(struct engine *e) {
 void swift_cuda_shim_step(struct engine *e, int resort) {
   if (shim_ctx == NULL) error("swift_cuda_shim_step before swift_cuda_shim_rebuild");
   CUDA_OK(swift_cuda_set_max_active_bin(shim_ctx, e->max_active_bin));
-  const int phases = (resort ? SWIFT_CUDA_PHASE_SORT : 0) | SWIFT_CUDA_PHASE_DENSITY | SWIFT_CUDA_PHASE_GHOST |
-                     SWIFT_CUDA_PHASE_FORCE | SWIFT_CUDA_PHASE_END_FORCE;
+  int phases = (resort ? SWIFT_CUDA_PHASE_SORT : 0) | SWIFT_CUDA_PHASE_DENSITY | SWIFT_CUDA_PHASE_GHOST |
+               SWIFT_CUDA_PHASE_FORCE | SWIFT_CUDA_PHASE_END_FORCE;
+#ifdef EXTRA_HYDRO_LOOP
+  phases |= SWIFT_CUDA_PHASE_GRADIENT | SWIFT_CUDA_PHASE_EXTRA_GHOST;
+#endif
   CUDA_OK(swift_cuda_step_parts(shim_ctx, e->s->parts, phases));
   refresh_hmax(&shim_flat, e);
 }

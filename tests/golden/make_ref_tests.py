@@ -15,9 +15,15 @@ RUNS = {
     "test125cells": (["-n", "6", "-r", "1", "-v", "0", "-p", "0", "-f", "standard"], "swift_dopair_125_standard.dat"),
     "test125cells_v2": (["-n", "6", "-r", "1", "-v", "2", "-p", "1", "-f", "standard"], "swift_dopair_125_standard.dat"),
 }
-for name, (args, out) in RUNS.items():
-    exe = os.path.join(REF, name.split("_")[0] + "_ref")
-    with tempfile.TemporaryDirectory() as tmp:
-        subprocess.run([exe] + args, cwd=tmp, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
-        shutil.copy(os.path.join(tmp, out), os.path.join(HERE, "ref_tests", name + ".dat"))
-        print(name, "->", out)
+# the same four runs with the reference compiled as SPHENIX_SPH (make -f Makefile.shim VARIANT=sphenix cpu): the
+# gradient loop and the extra ghost are part of test125cells then (tests/test125cells.c:724-767)
+for variant, suffix, prefix in (("minimal", "", ""), ("sphenix", "_sphenix", "sphenix_")):
+    for name, (args, out) in RUNS.items():
+        exe = os.path.join(REF, name.split("_")[0] + "_ref" + suffix)
+        if not os.path.exists(exe):
+            print("skip", variant, name, "(not built)")
+            continue
+        with tempfile.TemporaryDirectory() as tmp:
+            subprocess.run([exe] + args, cwd=tmp, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            shutil.copy(os.path.join(tmp, out), os.path.join(HERE, "ref_tests", prefix + name + ".dat"))
+            print(variant, name, "->", out)

@@ -52,10 +52,17 @@ CASES_27 = [("test27cells", ["-n", "4", "-r", "1", "-d", "0", "-f", "standard"],
              "tolerance_27_perturbed.dat")]
 
 
+# The same tests with the reference compiled as SPHENIX_SPH, its configure default (Makefile.shim VARIANT=sphenix):
+# test125cells then runs runner_do{self,pair}1_branch_gradient and runner_do_extra_ghost between the ghost and the
+# force loop (tests/test125cells.c:724-767), all of them the shim's; the record is the scheme's 160-byte struct part.
+VARIANTS = [("", ""), ("_sphenix", "sphenix_")]
+
+
 @pytest.mark.gpu
+@pytest.mark.parametrize("suffix,prefix", VARIANTS, ids=["minimal", "sphenix"])
 @pytest.mark.parametrize("name,args,ext,tolfile", CASES_27)
-def test_test27cells_through_the_shim(name, args, ext, tolfile, tmp_path):
-    run_test("test27cells_cuda", args, tmp_path)
+def test_test27cells_through_the_shim(name, args, ext, tolfile, suffix, prefix, tmp_path):
+    run_test("test27cells_cuda" + suffix, args, tmp_path)
     ours = load_table(tmp_path / ("swift_dopair_27_%s.dat" % ext))
     brute = load_table(tmp_path / ("brute_force_27_%s.dat" % ext))
     tol = load_table(os.path.join(REF, tolfile))
@@ -63,7 +70,7 @@ def test_test27cells_through_the_shim(name, args, ext, tolfile, tmp_path):
     assert len(bad) == 0, "difffloat gate: %d entries out of tolerance, first (row, col) %s" % (len(bad), bad[:5])
     # and against the unmodified reference's own table: the per-pair partial sums are added in the
     # same order; only the grouping of the additions across calls differs
-    ref = load_table(os.path.join(GOLD, name + ".dat"))
+    ref = load_table(os.path.join(GOLD, prefix + name + ".dat"))
     bad = difffloat(ours, ref, tol, 10 ** 6)  # the reference's gate on ALL rows (the tables print 7 digits)
     assert len(bad) == 0, "against the reference's own table: %d entries, first (row, col) %s" % (len(bad), bad[:5])
 
@@ -73,14 +80,15 @@ CASES_125 = [("test125cells", ["-n", "6", "-r", "1", "-v", "0", "-p", "0", "-f",
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("suffix,prefix", VARIANTS, ids=["minimal", "sphenix"])
 @pytest.mark.parametrize("name,args,tolfile", CASES_125)
-def test_test125cells_through_the_shim(name, args, tolfile, tmp_path):
-    run_test("test125cells_cuda", args, tmp_path)
+def test_test125cells_through_the_shim(name, args, tolfile, suffix, prefix, tmp_path):
+    run_test("test125cells_cuda" + suffix, args, tmp_path)
     ours = load_table(tmp_path / "swift_dopair_125_standard.dat")
     brute = load_table(tmp_path / "brute_force_125_standard.dat")
     tol = load_table(os.path.join(REF, tolfile))
     bad = difffloat(ours, brute, tol, int(args[1]))
     assert len(bad) == 0, "difffloat gate: %d entries out of tolerance, first (row, col) %s" % (len(bad), bad[:5])
-    ref = load_table(os.path.join(GOLD, name + ".dat"))
+    ref = load_table(os.path.join(GOLD, prefix + name + ".dat"))
     bad = difffloat(ours, ref, tol, 10 ** 6)  # the reference's gate on ALL rows (the tables print 7 digits)
     assert len(bad) == 0, "against the reference's own table: %d entries, first (row, col) %s" % (len(bad), bad[:5])

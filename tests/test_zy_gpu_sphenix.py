@@ -355,7 +355,8 @@ def test_sphenix_struct_part_step(name):
     table = REC_AFTER_GHOST + REC_AFTER_EXTRA + REC_AFTER_FORCE + [("alpha_visc_max_ngb", "r_alpha_visc_max_ngb")]
     _assert_fields(parts, g, table, act, "step_parts")
     if act is not None:
-        assert parts[~act].tobytes() == before[~act].tobytes(), "inactive records were written"
+        for k in parts.dtype.names:  # (field by field: the gaps of the record dtype are not copied by numpy)
+            assert np.array_equal(parts[k][~act], before[k][~act]), "field %s of an inactive record was written" % k
 
 
 @pytest.mark.parametrize("name", ["uniform14_periodic", "random11_timebins"])
