@@ -1931,8 +1931,7 @@ extern "C" {
 int swift_cuda_sphenix_set_props(swift_cuda_ctx *c, const swift_cuda_sphenix_props *p) {
   if (!c || !p) return fail("sphenix_set_props: null argument");
   if (c->prm.scheme != SWIFT_CUDA_SCHEME_SPHENIX) return fail("sphenix_set_props: the context's scheme is not SPHENIX");
-  if (!(p->viscosity_alpha_max > 0.f) || !(p->time_base > 0.0))
-    return fail("sphenix_set_props: viscosity_alpha_max and time_base must be positive");
+  // (no range checks: the reference's own unit tests run with e->time_base = 0, i.e. dt_alpha = 0)
   CK(cudaSetDevice(c->device));
   c->sprops = *p;
   if (c->built) {  // the constants of a built context follow at once; the particles' state is left alone
