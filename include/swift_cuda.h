@@ -315,7 +315,11 @@ int swift_cuda_fetch_pairs(swift_cuda_ctx *ctx, int loop, long long *pairs, long
 
 /* Multi-GPU: device pointers of the packed halo buffers so a
  * host can move them with NCCL send/recv (phase 0: xv before density, phase 1:
- * rho after the ghost).  See swift_subtask_dev_b200/halo.py. */
+ * rho after the ghost).  See swift_subtask_dev_b200/multi.py.
+ * A SPHENIX context has three exchanges, as the reference under EXTRA_HYDRO_LOOP (send_xv, send_rho,
+ * send_gradient, src/engine_maketasks.c:141-324): phase 0 xv; phase 3 after the ghost (h, rho, P, f, c, balsara
+ * and what a gradient-loop neighbour is read for: u, the viscosity alpha of before the extra ghost); phase 2
+ * after the extra ghost (the evolved viscosity / diffusion alphas the force loop reads). */
 int swift_cuda_halo_pack(swift_cuda_ctx *ctx, int phase, const int32_t *d_index, int64_t count, void *d_buffer,
                          void *stream);
 int swift_cuda_halo_unpack(swift_cuda_ctx *ctx, int phase, const int32_t *d_index, int64_t count,
@@ -409,8 +413,8 @@ int swift_cuda_get_integrator_timings(swift_cuda_ctx *ctx, float ms[4]);
  * swift_cuda_integrator_init makes its time_base the one of the extra ghost's dt_alpha) and the entries
  * below; both fields modes (FAST: k_force_fast with the scheme's interaction; the gradient loop and the extra
  * ghost stay exact, they decide the alphas); the struct part entries with the scheme's 160-byte record
- * (swift_cuda_part_layout's SPHENIX offsets, SWIFT_CUDA_PHASE_GRADIENT / _EXTRA_GHOST).  swift_cuda_step_io
- * and the halo entries refuse a SPHENIX context (the wider halo is not built). */
+ * (swift_cuda_part_layout's SPHENIX offsets, SWIFT_CUDA_PHASE_GRADIENT / _EXTRA_GHOST); the halo entries with the
+ * scheme's three exchanges.  swift_cuda_step_io refuses a SPHENIX context. */
 typedef struct {
   float viscosity_alpha_max;  /* hydro_props->viscosity.alpha_max, SPH:viscosity_alpha_max (2.0) */
   float viscosity_alpha_min;  /* ->viscosity.alpha_min (0.0) */

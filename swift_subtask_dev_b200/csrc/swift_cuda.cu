@@ -1699,37 +1699,108 @@ __global__ void k_halo_unpack_rho(Dev d, const int32_t *idx, int64_t n, const Ha
   d.fin[p] = make_float4(r.rho, r.P, r.f, r.c);
   d.hb[p] = make_float4(r.h, r.bal, __int_as_float((int)d.time_bin[p] & kBinMask), r.P / (r.rho * r.rho));
 }
+// SPHENIX: the rho halo also carries what a gradient-loop neighbour is read for (u, the viscosity alpha of
+// BEFORE the extra ghost); a third exchange after the extra ghost carries the evolved alphas the force loop
+// reads (the reference's send_rho / send_gradient, src/engine_maketasks.c:141-324 under EXTRA_HYDRO_LOOP)
+struct HaloRhoS {
+  float h, rho, P, f, c, bal, u, alpha_visc;
+};
+struct HaloGrad {
+  float alpha_visc, alpha_diff;
+};
+__global__ void k_halo_pack_rho_sphenix(Dev d, const int32_t *idx, int64_t n, HaloRhoS *buf) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t p = idx[k];
+  const float4 f = d.fin[p];
+  HaloRhoS r = {d.h[p], f.x, f.y, f.z, f.w, d.hb[p].y, d.u[p], d.sph_state[p].x};
+  buf[k] = r;
+}
+__global__ void k_halo_unpack_rho_sphenix(Dev d, const int32_t *idx, int64_t n, const HaloRhoS *buf) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t p = idx[k];
+  const HaloRhoS r = buf[k];
+  d.h[p] = r.h;
+  d.fin[p] = make_float4(r.rho, r.P, r.f, r.c);
+  d.hb[p] = make_float4(r.h, r.bal, __int_as_float((int)d.time_bin[p] & kBinMask), r.P / (r.rho * r.rho));
+  const_cast<float *>(d.u)[p] = r.u;
+  d.gin[p] = make_float4(r.u, r.rho, r.c, r.alpha_visc);
+}
+__global__ void k_halo_pack_grad(Dev d, const int32_t *idx, int64_t n, HaloGrad *buf) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const float4 st = d.sph_state[idx[k]];
+  HaloGrad r = {st.x, st.y};
+  buf[k] = r;
+}
+__global__ void k_halo_unpack_grad(Dev d, const int32_t *idx, int64_t n, const HaloGrad *buf) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t p = idx[k];
+  const HaloGrad r = buf[k];
+  float4 st = d.sph_state[p];
+  st.x = r.alpha_visc;
+  st.y = r.alpha_diff;
+  d.sph_state[p] = st;
+  d.sx[p] = make_float4(r.alpha_visc, r.alpha_diff, d.u[p], 0.f);
+}
 }  // namespace swiftcuda
+
+// which halo phases a context's scheme has: 0 xv and 1 rho (two-loop schemes); 0 xv, 3 rho and 2 gradient (SPHENIX)
+static int halo_phase_ok(const swift_cuda_ctx *c, int phase) {
+  const bool sphenix = c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX;
+  if (phase == 0 || (sphenix ? (phase == 2 || phase == 3) : phase == 1)) return 0;
+  return fail(sphenix ? "halo: a SPHENIX context exchanges phases 0 (xv), 3 (rho, u, alpha) and 2 (alphas after the "
+                        "extra ghost)"
+                      : "halo: phases 0 (xv) and 1 (rho)");
+}
 
 extern "C" {
 
-size_t swift_cuda_halo_bytes_per_particle(int phase) { return phase == 0 ? sizeof(HaloXV) : sizeof(HaloRho); }
+size_t swift_cuda_halo_bytes_per_particle(int phase) {
+  switch (phase) {
+    case 0: return sizeof(HaloXV);
+    case 1: return sizeof(HaloRho);
+    case 2: return sizeof(HaloGrad);
+    case 3: return sizeof(HaloRhoS);
+    default: return 0;
+  }
+}
 
 int swift_cuda_halo_pack(swift_cuda_ctx *c, int phase, const int32_t *d_index, int64_t count, void *d_buffer,
                          void *stream) {
   NEED_BUILT(c);
-  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) return fail("halo_pack: not built for the SPHENIX scheme");
+  if (halo_phase_ok(c, phase)) return 1;
   if (count <= 0) return 0;
   cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
   const int nb = (int)((count + 255) / 256);
   if (phase == 0)
     k_halo_pack_xv<<<nb, 256, 0, s>>>(c->dev, d_index, count, (HaloXV *)d_buffer);
-  else
+  else if (phase == 1)
     k_halo_pack_rho<<<nb, 256, 0, s>>>(c->dev, d_index, count, (HaloRho *)d_buffer);
+  else if (phase == 2)
+    k_halo_pack_grad<<<nb, 256, 0, s>>>(c->dev, d_index, count, (HaloGrad *)d_buffer);
+  else
+    k_halo_pack_rho_sphenix<<<nb, 256, 0, s>>>(c->dev, d_index, count, (HaloRhoS *)d_buffer);
   CK(cudaGetLastError());
   return 0;
 }
 int swift_cuda_halo_unpack(swift_cuda_ctx *c, int phase, const int32_t *d_index, int64_t count,
                            const void *d_buffer, void *stream) {
   NEED_BUILT(c);
-  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) return fail("halo_unpack: not built for the SPHENIX scheme");
+  if (halo_phase_ok(c, phase)) return 1;
   if (count <= 0) return 0;
   cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
   const int nb = (int)((count + 255) / 256);
   if (phase == 0)
     k_halo_unpack_xv<<<nb, 256, 0, s>>>(c->dev, d_index, count, (const HaloXV *)d_buffer);
-  else
+  else if (phase == 1)
     k_halo_unpack_rho<<<nb, 256, 0, s>>>(c->dev, d_index, count, (const HaloRho *)d_buffer);
+  else if (phase == 2)
+    k_halo_unpack_grad<<<nb, 256, 0, s>>>(c->dev, d_index, count, (const HaloGrad *)d_buffer);
+  else
+    k_halo_unpack_rho_sphenix<<<nb, 256, 0, s>>>(c->dev, d_index, count, (const HaloRhoS *)d_buffer);
   CK(cudaGetLastError());
   return 0;
 }

@@ -250,6 +250,9 @@ class RankState:
         self.ic = local_particles(part, rank, dim, per_cell, seed=seed) if ic is None else ic
         kw = dict(dim=dim, periodic=part.periodic, max_active_bin=56)
         kw.update(params_kw or {})
+        # SPHENIX: three exchanges per step (halo phases 0 xv, 3 rho + u + alpha, 2 the alphas after the extra ghost)
+        self.sphenix = kw.get("scheme", 0) == 2
+        self.rho_phase = 3 if self.sphenix else 1
         self.be = HydroBackend(make_params(**kw), device=device)
         self.be.build(self.ic)
         tree = self.be.tree()
@@ -306,13 +309,17 @@ class RankState:
         for p, ix in self.recv_idx.items():
             self.be.halo_unpack(phase, ix.data_ptr(), len(ix), recv[p].data_ptr(), st)
         self.stream.synchronize()   # the library's stream reads the halo copies next
-        self.be.refresh_cell_hmax(after_ghost=(phase == 1))
+        if phase != 2:              # (the gradient halo carries no smoothing lengths)
+            self.be.refresh_cell_hmax(after_ghost=(phase != 0))
 
     def halo_bytes_per_step(self):
-        return sum(len(ix) for ix in self.send_idx.values()) * (self.be.halo_bytes(0) + self.be.halo_bytes(1))
+        per = self.be.halo_bytes(0) + self.be.halo_bytes(self.rho_phase) + (self.be.halo_bytes(2) if self.sphenix else 0)
+        return sum(len(ix) for ix in self.send_idx.values()) * per
 
     def owned_results(self):
         out = self.be.results()
+        if self.sphenix:
+            out.update({k: v for k, v in self.be.sphenix_results().items() if k != "n_gradient"})
         sel = self.is_own
         res = {k: v[sel] for k, v in out.items()}
         res["id"] = self.ic["id"][sel]
@@ -340,7 +347,12 @@ def step_ranks_local(states):
         s.be.runner_do_hydro_sort()
         s.be.runner_do_density()
         s.be.runner_do_ghost()
-    move(1)
+    move(states[0].rho_phase)
+    if states[0].sphenix:
+        for s in states:
+            s.be.runner_do_gradient()
+            s.be.runner_do_extra_ghost()
+        move(2)
     for s in states:
         s.be.runner_do_force()
 
@@ -388,12 +400,22 @@ def step_rank_nccl(state, transport, phase_ms=None):
     lap("density")
     be.runner_do_ghost()
     lap("ghost")
-    send = state.pack(1)
-    _, recv = state.buffers(1)
+    send = state.pack(state.rho_phase)
+    _, recv = state.buffers(state.rho_phase)
     with state.torch.cuda.stream(state.stream):
         transport.exchange(send, recv)
-    state.unpack(1)
+    state.unpack(state.rho_phase)
     lap("halo_rho")
+    if state.sphenix:
+        be.runner_do_gradient()
+        be.runner_do_extra_ghost()
+        lap("gradient")
+        send = state.pack(2)
+        _, recv = state.buffers(2)
+        with state.torch.cuda.stream(state.stream):
+            transport.exchange(send, recv)
+        state.unpack(2)
+        lap("halo_gradient")
     be.runner_do_force()
     lap("force")
 

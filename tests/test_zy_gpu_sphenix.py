@@ -380,6 +380,51 @@ def test_sphenix_struct_part_phase_calls(name):
     _assert_fields(parts, g, REC_AFTER_FORCE + REC_AFTER_EXTRA + REC_AFTER_GHOST, act, "force call")
 
 
+@pytest.mark.parametrize("nranks", [2, 4])
+def test_sphenix_ranks_reproduce_single_gpu_run(nranks):
+    """Several ranks (all in this process, halos moved device to device) with the scheme's THREE exchanges per step --
+    xv; rho + u + the viscosity alpha of before the extra ghost; the evolved alphas after it -- against one context
+    holding the whole box: every owned particle's every field, the scheme's included, bit-identical."""
+    from swift_subtask_dev_b200 import multi
+    grid = multi.grid_for(nranks)
+    dim = tuple(float(g) for g in grid)
+    per_cell = 400 if nranks == 2 else 150
+    cdim = tuple(int(12 * d / max(dim)) for d in dim)
+    ic = ics.cell_block_random(np.arange(int(np.prod(cdim))), cdim, dim, per_cell, seed=7)
+    ident = ic["id"].astype(np.int64)
+    ic["u"] = (1.0 + 0.3 * (ident % 13) / 13.0).astype(np.float32)
+    kw = dict(scheme=B.SCHEME_SPHENIX, alpha=0.1)
+
+    def carried(ids):
+        return ((0.1 + 0.05 * (ids % 7)).astype(np.float32), (0.02 * (ids % 5)).astype(np.float32),
+                (0.01 * ((ids % 11) - 5)).astype(np.float32))
+
+    part, states = multi.setup_local(nranks, dim, cdim, per_cell, seed=7, params_kw=kw, ic=ic)
+    for st in states:
+        st.be.sphenix_set_state(*carried(st.ic["id"].astype(np.int64)))
+    multi.step_ranks_local(states)
+    be = HydroBackend(B.make_params(dim=dim, periodic=True, **kw))
+    be.build(ic)
+    be.sphenix_set_state(*carried(ident))
+    be.step()
+    ref = _both(be)
+    cref = be.counters()
+    be.close()
+    pos = {int(v): k for k, v in enumerate(ic["id"])}
+    tot = np.zeros(4, dtype=np.int64)
+    for st in states:
+        r = st.owned_results()
+        idx = np.array([pos[int(v)] for v in r["id"]])
+        for k in r:
+            if k != "id":
+                assert np.array_equal(r[k], ref[k][idx]), (st.rank, k)
+        c = st.be.counters()
+        tot += np.array([c["n_density"], c["n_density_redo"], c["n_force"], st.be.sphenix_results()["n_gradient"]])
+        assert st.halo_bytes_per_step() > 0
+        st.be.close()
+    assert tuple(tot) == (cref["n_density"], cref["n_density_redo"], cref["n_force"], ref["n_gradient"])
+
+
 def test_sphenix_refusals():
     """What is not built for the scheme fails loudly instead of computing something else."""
     be = _backend(dict(periodic=True, alpha=0.1), ol.SPHENIX_PROPS)
