@@ -1,6 +1,7 @@
 """The NCCL-path parity check of swift_subtask_dev_b200.multi on its own (bench.py runs the same check before
 the timed loop):  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1
---master-port P scripts/nccl_parity.py u|c|uc   (u: uniform box, c: clustered box in weighted blocks)."""
+--master-port P scripts/nccl_parity.py u|c|uc|s   (u: uniform box, c: clustered box in weighted blocks,
+s: uniform box in the SPHENIX scheme with its three halo exchanges)."""
 import os, sys
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 import torch, torch.distributed as dist
@@ -16,6 +17,8 @@ try:
         print("rank", rank, multi.nccl_parity_check(tr, world, rank, local), flush=True)
     if "c" in which:
         print("rank", rank, multi.nccl_parity_check(tr, world, rank, local, clustered=True), flush=True)
+    if "s" in which:
+        print("rank", rank, multi.nccl_parity_check(tr, world, rank, local, sphenix=True), flush=True)
 except Exception as e:
     print("rank", rank, "ERR", str(e)[:200], flush=True)
     rc = 1

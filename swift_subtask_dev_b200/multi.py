@@ -420,13 +420,15 @@ def step_rank_nccl(state, transport, phase_ms=None):
     lap("force")
 
 
-def nccl_parity_check(tr, world, rank, local, per_cell=150, seed=11, clustered=False):
+def nccl_parity_check(tr, world, rank, local, per_cell=150, seed=11, clustered=False, sphenix=False):
     """A small box split over the ranks and stepped through the SAME code the timed loop runs
     (step_rank_nccl: halo pack, NCCL send/recv, unpack), TWICE (the second step starts from what the
     first left in the halo copies), against one context holding the whole box on rank 0: every owned
     particle's results and the summed counters must be bit-identical.  clustered: a clumpy box in
     cost-weighted blocks (the shape of BASELINE configs[4]) instead of the uniform one.
     Role of the reference's tests/testHydroMPIrules.c + engine_maketasks.c:141-324 (send/recv xv, rho).
+    sphenix: the three-loop scheme with its three exchanges (xv; rho + u + alpha; the alphas after the extra
+    ghost), ONE step (the scheme's alphas evolve from step to step), its own fields compared as well.
     Returns "ok ..." or raises on every rank."""
     import torch.distributed as dist
     grid = grid_for(world)
@@ -437,20 +439,22 @@ def nccl_parity_check(tr, world, rank, local, per_cell=150, seed=11, clustered=F
         cdim = ics.top_grid(dim, float(ic["h"].max()))
         weights = np.bincount(top_cell_of(ic["x"], cdim, dim), minlength=int(np.prod(cdim)))
         part = Partition(cdim, grid, periodic=True, weights=weights)
-        st = RankState(rank, part, dim, 0, device=local, ic=local_particles_from(ic, part, rank, dim))
+        st = RankState(rank, part, dim, 0, device=local, ic=local_particles_from(ic, part, rank, dim),
+                       params_kw=dict(scheme=2, alpha=0.1) if sphenix else None)
     else:
         dim = tuple(float(g) for g in grid)
         cdim = tuple(int(12 * d / max(dim)) for d in dim)
         h0 = ics.ETA / (per_cell * np.prod(cdim) / np.prod(dim)) ** (1.0 / 3.0)
         assert ics.top_grid(dim, h0) == cdim
         part = Partition(cdim, grid, periodic=True)
-        st = RankState(rank, part, dim, per_cell, seed=seed, device=local)
+        st = RankState(rank, part, dim, per_cell, seed=seed, device=local,
+                       params_kw=dict(scheme=2, alpha=0.1) if sphenix else None)
         ic = None
     st.set_send_lists(tr.all_to_all_objects({p: ids for p, ids in st.recv_ids.items()}))
-    for _ in range(2):
+    for _ in range(1 if sphenix else 2):
         # poison the receive buffers: a pack / transfer / unpack ordering bug then shows as NaNs
         # instead of hiding behind what the previous step left there
-        for phase in (0, 1):
+        for phase in ((0, 3, 2) if sphenix else (0, 1)):
             with st.torch.cuda.stream(st.stream):
                 for buf in st.buffers(phase)[1].values():
                     buf.fill_(255)
@@ -458,6 +462,8 @@ def nccl_parity_check(tr, world, rank, local, per_cell=150, seed=11, clustered=F
     mine = st.owned_results()
     cnt = st.be.counters()
     mine["_counts"] = (cnt["n_density"], cnt["n_density_redo"], cnt["n_force"])
+    if sphenix:
+        mine["_counts"] += (st.be.sphenix_results()["n_gradient"],)
     st.be.close()
     gathered = [None] * world if rank == 0 else None
     dist.gather_object(mine, gathered, dst=0, group=tr.setup_group)
@@ -467,13 +473,19 @@ def nccl_parity_check(tr, world, rank, local, per_cell=150, seed=11, clustered=F
         if ic is None:
             ic = ics.cell_block_random(np.arange(int(np.prod(cdim))), cdim, dim, per_cell, seed=seed)
         npart = len(ic["h"])
-        be = HydroBackend(make_params(dim=dim, periodic=True), device=local)
+        be = HydroBackend(make_params(dim=dim, periodic=True, **(dict(scheme=2, alpha=0.1) if sphenix else {})),
+                          device=local)
         be.build(ic)
         be.step()
         ref, cref = be.results(), be.counters()
+        want = (cref["n_density"], cref["n_density_redo"], cref["n_force"])
+        if sphenix:
+            sr = be.sphenix_results()
+            want += (sr.pop("n_gradient"),)
+            ref.update(sr)
         be.close()
         pos = {int(v): k for k, v in enumerate(ic["id"])}
-        tot = np.zeros(3, dtype=np.int64)
+        tot = np.zeros(len(want), dtype=np.int64)
         nchecked = 0
         for r, res in enumerate(gathered):
             idx = np.array([pos[int(v)] for v in res["id"]], dtype=np.int64)
@@ -484,13 +496,14 @@ def nccl_parity_check(tr, world, rank, local, per_cell=150, seed=11, clustered=F
             tot += np.array(res["_counts"], dtype=np.int64)
         if nchecked != npart:
             verdict[0] = "owned particles of all ranks: %d, box: %d" % (nchecked, npart)
-        if tuple(tot) != (cref["n_density"], cref["n_density_redo"], cref["n_force"]):
-            verdict[0] = "interaction counters differ: %s vs %s" % (tuple(tot), cref)
+        if tuple(tot) != want:
+            verdict[0] = "interaction counters differ: %s vs %s" % (tuple(tot), want)
     dist.broadcast_object_list(verdict, src=0, group=tr.setup_group)
     if verdict[0] != "ok":
         raise RuntimeError("NCCL path parity check failed: " + verdict[0])
-    return "ok (%d ranks, %s box, two steps, every owned field and the counters bit-identical to one GPU)" % (
-        world, "clustered" if clustered else "uniform")
+    return "ok (%d ranks, %s box, %s, every owned field and the counters bit-identical to one GPU)" % (
+        world, "clustered" if clustered else "uniform",
+        "SPHENIX with its three exchanges, one step" if sphenix else "two steps")
 
 
 def bench_multi(args, cfg, metric, unit, sampler_cls=None):
