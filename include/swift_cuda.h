@@ -414,7 +414,8 @@ int swift_cuda_get_integrator_timings(swift_cuda_ctx *ctx, float ms[4]);
  * below; both fields modes (FAST: k_force_fast with the scheme's interaction; the gradient loop and the extra
  * ghost stay exact, they decide the alphas); the struct part entries with the scheme's 160-byte record
  * (swift_cuda_part_layout's SPHENIX offsets, SWIFT_CUDA_PHASE_GRADIENT / _EXTRA_GHOST); the halo entries with the
- * scheme's three exchanges.  swift_cuda_step_io refuses a SPHENIX context. */
+ * scheme's three exchanges; swift_cuda_step_io (the scheme's own state goes through swift_cuda_sphenix_set_state /
+ * _get_results around it). */
 typedef struct {
   float viscosity_alpha_max;  /* hydro_props->viscosity.alpha_max, SPH:viscosity_alpha_max (2.0) */
   float viscosity_alpha_min;  /* ->viscosity.alpha_min (0.0) */

@@ -1056,7 +1056,6 @@ int swift_cuda_get_results(swift_cuda_ctx *c, const swift_cuda_parts_out *out) {
 // ghost leaves (h, rho, P, c, f, balsara) goes down while the force loop runs.
 int swift_cuda_step_io(swift_cuda_ctx *c, const swift_cuda_parts_in *in, int flags, const swift_cuda_parts_out *out) {
   NEED_BUILT(c);
-  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX) return fail("step_io: not built for the SPHENIX scheme (use swift_cuda_step)");
   if (!in || !out) return fail("step_io: null argument");
   if (in->n != c->n) return fail("step_io: particle count changed; rebuild");
   if (!in->x || !in->v || !in->mass || !in->h || !in->u) return fail("step_io: null argument");
@@ -1111,7 +1110,10 @@ int swift_cuda_step_io(swift_cuda_ctx *c, const swift_cuda_parts_in *in, int fla
   if (launch_density(c)) return 1;
   CK(cudaEventRecord(c->ev[2], c->stream));
   if (launch_ghost(c)) return 1;
+  // SPHENIX: the gradient loop and the extra ghost leave what the ghost wrote (h, rho, P, c, f, balsara) alone:
+  // those fields still go out under the loops that follow
   if (enqueue_results(c, out, 1, c->stream, c->io, c->io_ev[2])) return 1;
+  if (c->prm.scheme == SWIFT_CUDA_SCHEME_SPHENIX && (launch_gradient(c) || launch_extra_ghost(c))) return 1;
   CK(cudaEventRecord(c->ev[3], c->stream));
   if (launch_force(c)) return 1;
   CK(cudaEventRecord(c->ev[4], c->stream));

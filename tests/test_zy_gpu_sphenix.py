@@ -425,15 +425,27 @@ def test_sphenix_ranks_reproduce_single_gpu_run(nranks):
     assert tuple(tot) == (cref["n_density"], cref["n_density_redo"], cref["n_force"], ref["n_gradient"])
 
 
-def test_sphenix_refusals():
-    """What is not built for the scheme fails loudly instead of computing something else."""
-    be = _backend(dict(periodic=True, alpha=0.1), ol.SPHENIX_PROPS)
-    ic = ics.uniform_random(1000, seed=1)
+def test_sphenix_step_io_and_refusals():
+    """swift_cuda_step_io (upload, the seven phases, download overlapped) gives the bits of the separate calls; the
+    two phases of the scheme are refused in a two-loop context."""
+    ic = _state(ics.uniform_random(20000, seed=21), 3)
+    kw = dict(periodic=True, alpha=0.1)
+    be = _backend(kw, ol.SPHENIX_PROPS)
     be.build(ic)
+    _set_state(be, ic)
+    be.update_particles(ic)
+    be.step()
+    a = _both(be)
+    _set_state(be, ic)   # the first step evolved the alphas
     out = be.alloc_results()
-    with pytest.raises(B.SwiftCudaError, match="not built for the SPHENIX scheme"):
-        be.step_io(ic, out)
+    be.step_io(ic, out)
+    b = be.sphenix_results()
     be.close()
+    for k in out:
+        assert np.array_equal(a[k], out[k]), k
+    for k in b:
+        assert np.array_equal(a[k], b[k]), k
+    ic = ics.uniform_random(1000, seed=1)
     # and the two new phases exist in that scheme only
     be = HydroBackend(parity.gpu_params(dict(periodic=True)))
     be.build(ic)
