@@ -152,6 +152,83 @@ def cpu_arm(sample_side, nproc, reps=1):
                           "wall_s": wall, "interactions": total}
 
 
+# ---- the threaded CPU arm: ONE box shared by all host threads ------------------------------------------------
+_BOX = {}
+
+
+def _box_setup(side):
+    """Particles, the tree and task list, and the interaction count of one side^3 box (cached: the count comes from
+    the reference built with IEEE flags and its pair-recording wrapper, single thread, untimed)."""
+    if side not in _BOX:
+        import oracle_lib as ol
+        from swift_subtask_dev_b200 import ics
+        ic = ics.uniform_random(side ** 3, seed=1000)
+        prm = ol.make_params()
+        order, cells, cdim, tasks, nt = ol.build_tree_and_tasks(prm, ic["x"], ic["h"])
+        icc = ics.permute(ic, order)
+        ol.ref("minimal").ref_set_threads(1)
+        o = ol.run_step("ref", prm, icc, cells, tasks, nt, record=False)
+        _BOX[side] = (prm, icc, cells, tasks, nt, sum(o["counts"]))
+    return _BOX[side]
+
+
+def _threaded_child(side, nthreads, reps, q):
+    try:
+        import ctypes
+        import oracle_lib as ol
+        prm, icc, cells, tasks, nt, inter = _box_setup(side)
+        lib = ol.ref("fast")
+        lib.ref_set_threads.argtypes = [ctypes.c_int]
+        lib.ref_last_step_seconds.restype = ctypes.c_double
+        lib.ref_set_threads(nthreads)
+        secs = []
+        for _ in range(reps + 1):   # the first repetition warms the page cache and the allocator
+            ol.run_step("ref", prm, icc, cells, tasks, nt, record=False, variant="fast")
+            secs.append(lib.ref_last_step_seconds())
+        q.put((inter, secs[1:]))
+    except Exception as e:  # noqa: BLE001
+        q.put(("error", repr(e)))
+
+
+def cpu_arm_threaded(side, nthreads, reps=1, timeout_s=600):
+    """The reference's own runner_* operators (compiled from /root/reference/src with its normal optimisation
+    flags) on ONE side^3 box shared by `nthreads` pthreads -- oracle/ref_harness.c: ref_set_threads: tasks drawn
+    from a shared counter under the locks of the top-level cells they update, the role of the reference's threaded
+    runner (src/engine.c:1692-1736, src/runner_main.c, src/cell_lock.c).  Timed: the operator phases (sort,
+    density, ghost, force, end_force) inside the harness; the tree and task build are outside, as for the GPU
+    arm.  Runs in a child process so that a hang cannot take the bench with it.  Returns (interactions/s per
+    repetition, description) or None when the compiled reference is not there or the child failed."""
+    import multiprocessing as mp
+    import oracle_lib as ol
+    if not (ol.ref_available("minimal") and ol.ref_available("fast")):
+        return None
+    ctx = mp.get_context("fork")
+    q = ctx.Queue()
+    t0 = time.perf_counter()
+    p = ctx.Process(target=_threaded_child, args=(side, nthreads, reps, q))
+    p.start()
+    try:
+        inter, secs = q.get(timeout=timeout_s)
+    except Exception:  # noqa: BLE001
+        p.kill()
+        return None
+    p.join(10)
+    if inter == "error":
+        sys.stderr.write("threaded CPU arm failed: %s\n" % secs)
+        return None
+    vals = [inter / s for s in secs]
+    return vals, {"kind": "reference", "cores": nthreads,
+                  "sample": ("ONE %d^3 uniform-random periodic box (12^3 top-level cells%s), sort + density + ghost + force "
+                             "by the reference's own runner_* operators compiled from /root/reference/src (-O3 -ffast-math "
+                             "-funroll-loops -march=x86-64-v3, the reference's normal flags with a portable -march), shared by "
+                             "%d threads: tasks drawn from a shared counter under the locks of the top-level cells they update "
+                             "(oracle/ref_harness.c ref_set_threads; the reference's own scheduler and engine are not "
+                             "built here); tree and task build outside the timed region"
+                             % (side, ", each split once: sub-tasks" if side >= 96 else "", nthreads)),
+                  "build": "fast", "wall_s": time.perf_counter() - t0, "interactions": inter,
+                  "operator_s": secs}
+
+
 def resident_leg(args, ic, hbm_peak):
     """the particles go to the device ONCE and stay there; per engine step only scalars
     (ti_end_min, dx_max) come back.  Step 0 has every particle active; the following ones the particles whose
@@ -249,7 +326,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--side", type=int, default=256, help="particles per box side (BASELINE configs[1]: 256)")
-    ap.add_argument("--cpu-side", type=int, default=64)
+    ap.add_argument("--cpu-side", type=int, default=64, help="side of the independent boxes of the fallback CPU arm")
+    ap.add_argument("--cpu-box-side", type=int, default=128,
+                    help="side of the ONE box the threaded CPU arm steps with all host threads (0: the independent-boxes arm)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--workload", default="uniform", choices=["uniform", "clustered"],
                     help="uniform: BASELINE configs[1] / [3] (default, the metric's config); clustered: configs[4] "
@@ -271,14 +350,20 @@ def main():
         if rank != 0:
             return 0
         nproc = host_cores()
-        for _ in range(max(args.warmup, 0) and 1):
-            cpu_arm(32, nproc)
         t0 = time.perf_counter()
-        vals = []
-        for _ in range(args.steps):
-            v, desc = cpu_arm(args.cpu_side, nproc)
-            vals.append(v)
-        dt = time.perf_counter() - t0
+        thr = cpu_arm_threaded(args.cpu_box_side, nproc, reps=max(args.steps, 1)) if args.cpu_box_side > 0 else None
+        if thr is not None:
+            vals, desc = thr
+            dt = float(np.sum(desc["operator_s"]))
+        else:
+            for _ in range(max(args.warmup, 0) and 1):
+                cpu_arm(32, nproc)
+            t0 = time.perf_counter()
+            vals = []
+            for _ in range(args.steps):
+                v, desc = cpu_arm(args.cpu_side, nproc)
+                vals.append(v)
+            dt = time.perf_counter() - t0
         v = float(np.mean(vals))
         desc["value"] = v
         desc["unit"] = UNIT
@@ -477,7 +562,14 @@ def main():
         line["detail"]["sphenix"] = sphenix_leg(args.sphenix_side)
     if not args.no_cpu:
         nproc = host_cores()
-        v, desc = cpu_arm(args.cpu_side, nproc)
+        thr = cpu_arm_threaded(args.cpu_box_side, nproc, reps=2) if args.cpu_box_side > 0 else None
+        if thr is not None:
+            v, desc = float(np.mean(thr[0])), thr[1]
+            # the arm of round 1 beside it: one independent single-thread box per core (no shared box, no locks)
+            vi, di = cpu_arm(args.cpu_side, nproc)
+            desc["independent_boxes"] = {"value": vi, "cores": nproc, "sample": di["sample"]}
+        else:
+            v, desc = cpu_arm(args.cpu_side, nproc)
         desc["value"] = v
         desc["unit"] = UNIT
         line["cpu_baseline"] = desc

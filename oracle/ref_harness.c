@@ -70,6 +70,153 @@ void ref_record_pair(int loop, long long id_updated, long long id_other) {
 }
 
 int ref_sizeof_part(void) { return (int)sizeof(struct part); }
+
+/* ---- phases, serial or on a pool of pthreads ---------------------------------------------------
+ * ref_set_threads(1) (the default): every phase runs on the calling thread in creation order -- what the
+ * golden fixtures were made with.  ref_set_threads(T > 1): the TIMED CPU baseline of bench.py -- the
+ * reference's operators on ONE box shared by T threads, the role of its threaded runner
+ * (src/runner_main.c, src/engine.c:1692-1736): each thread has its own struct runner, draws tasks from a
+ * shared counter and takes the locks of the top-level cells a task updates (both cells of a pair; the
+ * reference's cell_locktree, src/cell_lock.c, at the granularity of top-level cells); a task whose cells
+ * are busy is put aside and done when the list is through.  Sums then arrive in another order than in the
+ * serial run (rounding differs), which is why nothing is CHECKED in this mode. */
+#include <pthread.h>
+#include <time.h>
+enum { PH_SORT, PH_DENSITY, PH_GHOST, PH_GRADIENT, PH_EXTRA_GHOST, PH_FORCE, PH_END_FORCE };
+static int g_threads = 1;
+static double g_last_seconds = 0.0;
+void ref_set_threads(int n) { g_threads = n < 1 ? 1 : n; }
+double ref_last_step_seconds(void) { return g_last_seconds; }
+
+struct phase_ctx {
+  int phase;
+  struct engine *e;
+  struct cell *cells;
+  int ncells;
+  struct task *tasks;
+  int ntasks;
+  pthread_mutex_t *locks; /* one per cell slot; only those of top-level cells are used */
+  int next;               /* shared work counter */
+};
+
+static void phase_task(struct runner *r, struct task *t, int phase) {
+  if (phase == PH_DENSITY) {
+    switch (t->type) {
+      case task_type_self: runner_doself1_branch_density(r, t->ci); break;
+      case task_type_pair: runner_dopair1_branch_density(r, t->ci, t->cj); break;
+      case task_type_sub_self: runner_dosub_self1_density(r, t->ci, 0); break;
+      default: runner_dosub_pair1_density(r, t->ci, t->cj, 0); break;
+    }
+#ifdef EXTRA_HYDRO_LOOP
+  } else if (phase == PH_GRADIENT) {
+    switch (t->type) {
+      case task_type_self: runner_doself1_branch_gradient(r, t->ci); break;
+      case task_type_pair: runner_dopair1_branch_gradient(r, t->ci, t->cj); break;
+      case task_type_sub_self: runner_dosub_self1_gradient(r, t->ci, 0); break;
+      default: runner_dosub_pair1_gradient(r, t->ci, t->cj, 0); break;
+    }
+#endif
+  } else {
+    switch (t->type) {
+      case task_type_self: runner_doself2_branch_force(r, t->ci); break;
+      case task_type_pair: runner_dopair2_branch_force(r, t->ci, t->cj); break;
+      case task_type_sub_self: runner_dosub_self2_force(r, t->ci, 0); break;
+      default: runner_dosub_pair2_force(r, t->ci, t->cj, 0); break;
+    }
+  }
+}
+
+static void phase_cell(struct runner *r, struct cell *c, int phase) {
+  if (phase == PH_SORT) {
+    if (c->hydro.count > 0) runner_do_hydro_sort(r, c, 0x1FFF, 0, 0, 0);
+  } else if (phase == PH_GHOST) {
+    runner_do_ghost(r, c, 0);
+#ifdef EXTRA_HYDRO_LOOP
+  } else if (phase == PH_EXTRA_GHOST) {
+    runner_do_extra_ghost(r, c, 0);
+#endif
+  } else {
+    runner_do_end_hydro_force(r, c, 0);
+  }
+}
+
+static int phase_is_tasks(int phase) { return phase == PH_DENSITY || phase == PH_GRADIENT || phase == PH_FORCE; }
+
+static void *phase_worker(void *arg) {
+  struct phase_ctx *x = (struct phase_ctx *)arg;
+  struct runner r;
+  bzero(&r, sizeof(r));
+  r.e = x->e;
+  if (!phase_is_tasks(x->phase)) {
+    for (;;) {
+      const int k = __atomic_fetch_add(&x->next, 1, __ATOMIC_RELAXED);
+      if (k >= x->ncells) break;
+      if (x->cells[k].parent == NULL) phase_cell(&r, &x->cells[k], x->phase);
+    }
+    return NULL;
+  }
+  int *later = (int *)malloc(sizeof(int) * (size_t)(x->ntasks + 1));
+  int nlater = 0;
+  for (;;) {
+    const int k = __atomic_fetch_add(&x->next, 1, __ATOMIC_RELAXED);
+    if (k >= x->ntasks) break;
+    struct task *t = &x->tasks[k];
+    pthread_mutex_t *la = &x->locks[t->ci->top - x->cells];
+    pthread_mutex_t *lb = (t->cj != NULL && t->cj->top != t->ci->top) ? &x->locks[t->cj->top - x->cells] : NULL;
+    if (pthread_mutex_trylock(la) != 0) {
+      later[nlater++] = k;
+      continue;
+    }
+    if (lb != NULL && pthread_mutex_trylock(lb) != 0) {
+      pthread_mutex_unlock(la);
+      later[nlater++] = k;
+      continue;
+    }
+    phase_task(&r, t, x->phase);
+    if (lb != NULL) pthread_mutex_unlock(lb);
+    pthread_mutex_unlock(la);
+  }
+  /* what was busy: now with blocking locks, always in address order */
+  for (int i = 0; i < nlater; i++) {
+    struct task *t = &x->tasks[later[i]];
+    pthread_mutex_t *la = &x->locks[t->ci->top - x->cells];
+    pthread_mutex_t *lb = (t->cj != NULL && t->cj->top != t->ci->top) ? &x->locks[t->cj->top - x->cells] : NULL;
+    if (lb != NULL && lb < la) {
+      pthread_mutex_t *tmp = la;
+      la = lb;
+      lb = tmp;
+    }
+    pthread_mutex_lock(la);
+    if (lb != NULL) pthread_mutex_lock(lb);
+    phase_task(&r, t, x->phase);
+    if (lb != NULL) pthread_mutex_unlock(lb);
+    pthread_mutex_unlock(la);
+  }
+  free(later);
+  return NULL;
+}
+
+static void run_phase(struct phase_ctx *x, struct runner *serial_runner, int phase) {
+  struct timespec t0, t1;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  x->phase = phase;
+  x->next = 0;
+  if (g_threads <= 1) {
+    if (phase_is_tasks(phase)) {
+      for (int k = 0; k < x->ntasks; k++) phase_task(serial_runner, &x->tasks[k], phase);
+    } else {
+      for (int k = 0; k < x->ncells; k++)
+        if (x->cells[k].parent == NULL) phase_cell(serial_runner, &x->cells[k], phase);
+    }
+  } else {
+    pthread_t *th = (pthread_t *)malloc(sizeof(pthread_t) * (size_t)g_threads);
+    for (int k = 0; k < g_threads; k++) pthread_create(&th[k], NULL, phase_worker, x);
+    for (int k = 0; k < g_threads; k++) pthread_join(th[k], NULL);
+    free(th);
+  }
+  clock_gettime(CLOCK_MONOTONIC, &t1);
+  g_last_seconds += (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
+}
 #ifdef PLANETARY_SPH
 static void ref_planetary_eos_init(void);
 #endif
@@ -292,21 +439,22 @@ static int run_step(const oracle_params *prm, oracle_parts *io, int ncells, cons
       p->force.balsara = io->in_balsara ? io->in_balsara[k] : 0.f;
     }
   }
-  for (int k = 0; k < ncells; k++)
-    if (cells[k].parent == NULL && cells[k].hydro.count > 0)
-      runner_do_hydro_sort(&runner, &cells[k], 0x1FFF, 0, 0, 0);
+  struct phase_ctx px;
+  bzero(&px, sizeof(px));
+  px.e = &engine;
+  px.cells = cells;
+  px.ncells = ncells;
+  px.tasks = tasks;
+  px.ntasks = ntasks;
+  px.locks = (pthread_mutex_t *)malloc(sizeof(pthread_mutex_t) * (size_t)(ncells + 1));
+  for (int k = 0; k < ncells; k++) pthread_mutex_init(&px.locks[k], NULL);
+  g_last_seconds = 0.0;
+  if (g_threads > 1) g_log = NULL, g_sx = NULL; /* the pair log is not thread safe: nothing is recorded or counted */
+  run_phase(&px, &runner, PH_SORT);
 
   /* ---- density ---- */
   g_stage = 0;
-  for (int k = 0; k < ntasks; k++) {
-    struct task *t = &tasks[k];
-    switch (t->type) {
-      case task_type_self: runner_doself1_branch_density(&runner, t->ci); break;
-      case task_type_pair: runner_dopair1_branch_density(&runner, t->ci, t->cj); break;
-      case task_type_sub_self: runner_dosub_self1_density(&runner, t->ci, 0); break;
-      default: runner_dosub_pair1_density(&runner, t->ci, t->cj, 0); break;
-    }
-  }
+  run_phase(&px, &runner, PH_DENSITY);
   for (int k = 0; k < n; k++) {
     const struct part *p = &parts[k];
     if (io->d_rho) io->d_rho[k] = p->rho;
@@ -320,8 +468,7 @@ static int run_step(const oracle_params *prm, oracle_parts *io, int ncells, cons
 
   /* ---- ghost ---- */
   g_stage = 1;
-  for (int k = 0; k < ncells; k++)
-    if (cells[k].parent == NULL) runner_do_ghost(&runner, &cells[k], 0);
+  run_phase(&px, &runner, PH_GHOST);
   for (int k = 0; k < n; k++) {
     const struct part *p = &parts[k];
     if (io->g_h) io->g_h[k] = p->h;
@@ -337,23 +484,14 @@ static int run_step(const oracle_params *prm, oracle_parts *io, int ncells, cons
 
 #ifdef EXTRA_HYDRO_LOOP
   /* ---- gradient loop + extra ghost (src/runner_main.c:199-200, 249-250, 297-298, 343-344, 420-421) ---- */
-  for (int k = 0; k < ntasks; k++) {
-    struct task *t = &tasks[k];
-    switch (t->type) {
-      case task_type_self: runner_doself1_branch_gradient(&runner, t->ci); break;
-      case task_type_pair: runner_dopair1_branch_gradient(&runner, t->ci, t->cj); break;
-      case task_type_sub_self: runner_dosub_self1_gradient(&runner, t->ci, 0); break;
-      default: runner_dosub_pair1_gradient(&runner, t->ci, t->cj, 0); break;
-    }
-  }
+  run_phase(&px, &runner, PH_GRADIENT);
   for (int k = 0; k < n; k++) {
     const struct part *p = &parts[k];
     if (sx->r_v_sig) sx->r_v_sig[k] = p->viscosity.v_sig;
     if (sx->r_laplace_u) sx->r_laplace_u[k] = p->diffusion.laplace_u;
     if (sx->r_alpha_visc_max_ngb) sx->r_alpha_visc_max_ngb[k] = p->force.alpha_visc_max_ngb;
   }
-  for (int k = 0; k < ncells; k++)
-    if (cells[k].parent == NULL) runner_do_extra_ghost(&runner, &cells[k], 0);
+  run_phase(&px, &runner, PH_EXTRA_GHOST);
   for (int k = 0; k < n; k++) {
     const struct part *p = &parts[k];
     if (sx->e_laplace_u) sx->e_laplace_u[k] = p->diffusion.laplace_u;
@@ -366,17 +504,10 @@ static int run_step(const oracle_params *prm, oracle_parts *io, int ncells, cons
 
   /* ---- force ---- */
   g_stage = 2;
-  for (int k = 0; k < ntasks; k++) {
-    struct task *t = &tasks[k];
-    switch (t->type) {
-      case task_type_self: runner_doself2_branch_force(&runner, t->ci); break;
-      case task_type_pair: runner_dopair2_branch_force(&runner, t->ci, t->cj); break;
-      case task_type_sub_self: runner_dosub_self2_force(&runner, t->ci, 0); break;
-      default: runner_dosub_pair2_force(&runner, t->ci, t->cj, 0); break;
-    }
-  }
-  for (int k = 0; k < ncells; k++)
-    if (cells[k].parent == NULL) runner_do_end_hydro_force(&runner, &cells[k], 0);
+  run_phase(&px, &runner, PH_FORCE);
+  run_phase(&px, &runner, PH_END_FORCE);
+  for (int k = 0; k < ncells; k++) pthread_mutex_destroy(&px.locks[k]);
+  free(px.locks);
   for (int k = 0; k < n; k++) {
     const struct part *p = &parts[k];
     if (io->f_a)
