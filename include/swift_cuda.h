@@ -306,6 +306,12 @@ int swift_cuda_host_plan(const swift_cuda_params *params, const swift_cuda_parts
                          swift_cuda_cell **cells, int *ncells, swift_cuda_task **tasks, int *ntasks,
                          int32_t *order, int cdim[3], long long *n_interactions, long long *n_items);
 void swift_cuda_host_free(void *p);
+/* A 64-bit digest of everything the host builder would hand to the device for these particles (tree, tasks,
+ * cell order, both item lists, units, lanes, sort segments).  The builder runs on several host threads
+ * (SWIFT_CUDA_HOST_THREADS in the environment, default min(16, cores)); with 1 it is the single-threaded form the
+ * threaded one must reproduce byte for byte. */
+int swift_cuda_host_plan_digest(const swift_cuda_params *params, const swift_cuda_parts_in *parts,
+                                unsigned long long *digest);
 
 /* Test hook: record ordered (updated id, neighbour id) pairs of the next
  * phases into device buffers of `capacity` pairs per loop

@@ -132,7 +132,7 @@ EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error
            "swift_cuda_get_tree_size", "swift_cuda_get_tree", "swift_cuda_record_pairs", "swift_cuda_fetch_pairs",
            "swift_cuda_halo_pack", "swift_cuda_halo_unpack", "swift_cuda_halo_bytes_per_particle",
            "swift_cuda_get_touched", "swift_cuda_refresh_cell_hmax",
-           "swift_cuda_host_plan", "swift_cuda_host_free",
+           "swift_cuda_host_plan", "swift_cuda_host_free", "swift_cuda_host_plan_digest",
            "swift_cuda_integrator_init", "swift_cuda_set_time", "swift_cuda_drift", "swift_cuda_kick",
            "swift_cuda_timestep", "swift_cuda_reset_offsets", "swift_cuda_get_state",
            "swift_cuda_get_integrator_timings",
@@ -322,6 +322,23 @@ def host_plan(params, ic):
     lib.swift_cuda_host_free(tasks_p)
     return {"cells": cells, "ncells": nc.value, "tasks": tasks, "ntasks": nt.value, "cdim": tuple(cdim),
             "order": order, "n_interactions": ni.value, "n_items": nitems.value}
+
+
+def host_plan_digest(params, ic):
+    """Host-only: a digest of everything the host builder makes for `ic` (swift_cuda_host_plan_digest)."""
+    lib = load_library()
+    keep = [np.ascontiguousarray(ic["x"], dtype=np.float64), np.ascontiguousarray(ic["h"], dtype=np.float32)]
+    P = PartsIn()
+    P.n = len(keep[1])
+    P.x = keep[0].ctypes.data_as(C.POINTER(C.c_double))
+    P.h = keep[1].ctypes.data_as(_FP)
+    if ic.get("time_bin") is not None:
+        keep.append(np.ascontiguousarray(ic["time_bin"], dtype=np.int8))
+        P.time_bin = keep[-1].ctypes.data_as(C.POINTER(C.c_int8))
+    d = C.c_ulonglong(0)
+    if lib.swift_cuda_host_plan_digest(C.byref(params), C.byref(P), C.byref(d)) != 0:
+        raise SwiftCudaError(lib.swift_cuda_last_error().decode())
+    return d.value
 
 
 def make_params(dim=(1.0, 1.0, 1.0), periodic=True, eta=1.2348, h_tolerance=1e-4, h_max=1e10, h_min=0.0,

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
 #include <thread>
 
 namespace swiftcuda {
@@ -102,13 +103,14 @@ OctPairs make_oct_pairs(int sid) {
   return o;
 }
 const OctPairs &oct_pairs(int sid) {
-  static OctPairs table[13];
-  static bool init = false;
-  if (!init) {
-    for (int s = 0; s < 13; s++) table[s] = make_oct_pairs(s);
-    init = true;
-  }
-  return table[sid];
+  struct Table {
+    OctPairs t[13];
+    Table() {
+      for (int s = 0; s < 13; s++) t[s] = make_oct_pairs(s);
+    }
+  };
+  static const Table table;  // initialised once, thread safe (the list builder runs on several host threads)
+  return table.t[sid];
 }
 
 inline double cell_dmin(const swift_cuda_cell &c) { return std::min(c.width[0], std::min(c.width[1], c.width[2])); }
@@ -118,6 +120,24 @@ inline double cell_dmin(const swift_cuda_cell &c) { return std::min(c.width[0], 
 // ---------------------------------------------------------------------------
 // Tree
 // ---------------------------------------------------------------------------
+// Host threads of the builders below (SWIFT_CUDA_HOST_THREADS=1: everything on the calling thread, the form the
+// threaded one is checked against, tests/test_cabi.py::test_host_builder_threads_give_the_same_lists).
+static int host_threads() {
+  if (const char *e = std::getenv("SWIFT_CUDA_HOST_THREADS")) return std::max(1, std::atoi(e));
+  return (int)std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+}
+template <typename F>
+static void parallel_chunks(size_t n, size_t min_per_thread, F &&fn) {  // fn(thread, begin, end) on contiguous chunks
+  const size_t nt = std::max<size_t>(1, std::min<size_t>((size_t)host_threads(), n / std::max<size_t>(min_per_thread, 1)));
+  if (nt <= 1) {
+    fn((size_t)0, (size_t)0, n);
+    return;
+  }
+  std::vector<std::thread> th;
+  for (size_t t = 0; t < nt; t++) th.emplace_back([&, t]() { fn(t, n * t / nt, n * (t + 1) / nt); });
+  for (auto &t : th) t.join();
+}
+
 namespace {
 struct SplitCtx {
   const double *x;
@@ -187,7 +207,15 @@ void split_top(const double *x, int32_t *order, int32_t *scratch, std::vector<sw
 
 int build_tree(const swift_cuda_params &prm, int64_t n, const double *x, const float *h, Tree &tree) {
   float h_max = 0.f;
-  for (int64_t k = 0; k < n; k++) h_max = std::max(h_max, h[k]);
+  {
+    std::vector<float> part((size_t)host_threads(), 0.f);
+    parallel_chunks((size_t)n, 1 << 16, [&](size_t t, size_t lo, size_t hi) {
+      float m = 0.f;
+      for (size_t k = lo; k < hi; k++) m = std::max(m, h[k]);
+      part[t] = m;
+    });
+    for (float m : part) h_max = std::max(h_max, m);
+  }
   h_max = std::min(h_max, prm.h_max);
   const double dmax = std::max(prm.dim[0], std::max(prm.dim[1], prm.dim[2]));
   const double cell_min = 0.99 * dmax / kMaxTopCells;  // src/space.c:1160
@@ -203,23 +231,41 @@ int build_tree(const swift_cuda_params &prm, int64_t n, const double *x, const f
   }
   const int ntop = cdim[0] * cdim[1] * cdim[2];
 
-  // counting sort of the particles into the top-level cells
+  // counting sort of the particles into the top-level cells, stable (a cell's particles stay in input order):
+  // every host thread histograms a contiguous range of the particles, then scatters it behind the ranges before
   std::vector<int32_t> top_of(n);
   std::vector<int64_t> start(ntop + 1, 0);
-  for (int64_t k = 0; k < n; k++) {
-    int idx[3];
-    for (int d = 0; d < 3; d++) {
-      idx[d] = (int)(x[3 * k + d] * iwidth[d]);
-      idx[d] = std::min(std::max(idx[d], 0), cdim[d] - 1);
-    }
-    top_of[k] = (idx[0] * cdim[1] + idx[1]) * cdim[2] + idx[2];
-    start[top_of[k] + 1]++;
-  }
-  for (int c = 0; c < ntop; c++) start[c + 1] += start[c];
-  tree.order.resize(n);
   {
-    std::vector<int64_t> fill(start.begin(), start.end() - 1);
-    for (int64_t k = 0; k < n; k++) tree.order[fill[top_of[k]]++] = (int32_t)k;
+    const size_t T = (size_t)host_threads();
+    std::vector<std::vector<int64_t>> hist(T);
+    parallel_chunks((size_t)n, 1 << 16, [&](size_t t, size_t lo, size_t hi) {
+      std::vector<int64_t> &hc = hist[t];
+      hc.assign(ntop, 0);
+      for (size_t k = lo; k < hi; k++) {
+        int idx[3];
+        for (int d = 0; d < 3; d++) {
+          idx[d] = (int)(x[3 * k + d] * iwidth[d]);
+          idx[d] = std::min(std::max(idx[d], 0), cdim[d] - 1);
+        }
+        top_of[k] = (idx[0] * cdim[1] + idx[1]) * cdim[2] + idx[2];
+        hc[top_of[k]]++;
+      }
+    });
+    for (int c = 0; c < ntop; c++) {
+      int64_t cnt = 0;
+      for (size_t t = 0; t < T; t++)
+        if (!hist[t].empty()) {
+          const int64_t mine = hist[t][c];
+          hist[t][c] = cnt;  // offset of this thread's particles inside the cell
+          cnt += mine;
+        }
+      start[c + 1] = start[c] + cnt;
+    }
+    tree.order.resize(n);
+    parallel_chunks((size_t)n, 1 << 16, [&](size_t t, size_t lo, size_t hi) {
+      std::vector<int64_t> &off = hist[t];
+      for (size_t k = lo; k < hi; k++) tree.order[start[top_of[k]] + off[top_of[k]]++] = (int32_t)k;
+    });
   }
   top_of.clear();
   top_of.shrink_to_fit();
@@ -241,7 +287,7 @@ int build_tree(const swift_cuda_params &prm, int64_t n, const double *x, const f
       split_top(x, tree.order.data(), scratch.data(), locals[c]);
     }
   };
-  const int nt = (int)std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+  const int nt = host_threads();
   if (n < 200000 || nt == 1) {
     work(0, 1);
   } else {
@@ -271,25 +317,41 @@ int build_tree(const swift_cuda_params &prm, int64_t n, const double *x, const f
   return 0;
 }
 
+void gather_f32(const float *src, const int32_t *order, int64_t n, float *dst) {
+  parallel_chunks((size_t)n, 1 << 16, [&](size_t, size_t lo, size_t hi) {
+    for (size_t k = lo; k < hi; k++) dst[k] = src[order[k]];
+  });
+}
+
 void compute_cell_hmax(Tree &tree, const float *h) {
   const size_t nc = tree.cells.size();
   tree.h_max.assign(nc, 0.f);
   // leaves from particles, parents from children (children have larger indices than
   // their parent in both the library tree and any top-down numbered tree; fall back
-  // to a direct scan otherwise)
+  // to a direct scan otherwise).  The scans first, shared out over the host threads (a maximum: any
+  // order gives the same bits), then the parents from the last cell to the first.
+  auto from_children = [&](size_t c) {
+    const swift_cuda_cell &cell = tree.cells[c];
+    if (!cell.split) return false;
+    for (int k = 0; k < 8; k++)
+      if (cell.progeny[k] >= 0 && (size_t)cell.progeny[k] <= c) return false;
+    return true;
+  };
+  parallel_chunks(nc, 2048, [&](size_t, size_t lo, size_t hi) {
+    for (size_t c = lo; c < hi; c++) {
+      if (from_children(c)) continue;
+      const swift_cuda_cell &cell = tree.cells[c];
+      float m = 0.f;
+      for (int k = 0; k < cell.count; k++) m = std::max(m, h[cell.first + k]);
+      tree.h_max[c] = m;
+    }
+  });
   for (size_t c = nc; c-- > 0;) {
+    if (!from_children(c)) continue;
     const swift_cuda_cell &cell = tree.cells[c];
     float m = 0.f;
-    bool from_children = cell.split;
-    if (from_children)
-      for (int k = 0; k < 8; k++)
-        if (cell.progeny[k] >= 0 && (size_t)cell.progeny[k] <= c) from_children = false;
-    if (from_children) {
-      for (int k = 0; k < 8; k++)
-        if (cell.progeny[k] >= 0) m = std::max(m, tree.h_max[cell.progeny[k]]);
-    } else {
-      for (int k = 0; k < cell.count; k++) m = std::max(m, h[cell.first + k]);
-    }
+    for (int k = 0; k < 8; k++)
+      if (cell.progeny[k] >= 0) m = std::max(m, tree.h_max[cell.progeny[k]]);
     tree.h_max[c] = m;
   }
 }
@@ -633,11 +695,8 @@ void build_worklists(const swift_cuda_params &prm, const Tree &tree, const std::
       wl.n_sort_entries += tree.cells[cell].count;
     }
   };
-  RedoBuilder rb{prm, tree, cell_active, cell_tasks, f};
   wl.item_begin.push_back(0);
   wl.redo_begin.push_back(0);
-  std::vector<const std::vector<SeqItem> *> chain;
-  std::vector<SeqItem> merged;
   // leaves in the order of their particles (`first`): walking the units in order then walks the particle
   // arrays in order, and a range of units is a range of records (swift_cuda_step_parts hands the force
   // results back in such ranges)
@@ -648,41 +707,82 @@ void build_worklists(const swift_cuda_params &prm, const Tree &tree, const std::
   }
   std::stable_sort(visit.begin(), visit.end(),
                    [&](int32_t a, int32_t b) { return tree.cells[a].first < tree.cells[b].first; });
-  for (const int32_t c : visit) {
-    const swift_cuda_cell &cell = tree.cells[c];
-    // every interaction that updates this leaf's particles: its own and its ancestors', in execution order
-    chain.clear();
-    for (int a = (int)c; a >= 0; a = tree.cells[a].parent)
-      if (!f.per_cell[a].empty()) chain.push_back(&f.per_cell[a]);
-    const size_t before = wl.items.size();
-    if (chain.size() == 1) {
-      for (const SeqItem &si : *chain[0]) wl.items.push_back(si.it);
-    } else if (chain.size() > 1) {
-      merged.clear();
-      for (auto *v : chain) merged.insert(merged.end(), v->begin(), v->end());
-      std::sort(merged.begin(), merged.end(), [](const SeqItem &a, const SeqItem &b) { return a.seq < b.seq; });
-      for (const SeqItem &si : merged) wl.items.push_back(si.it);
-    }
-    const size_t rbefore = wl.redo_items.size();
-    rb.build((int)c, wl.redo_items);
-    if (wl.items.size() == before && wl.redo_items.size() == rbefore) continue;
-    for (size_t k = before; k < wl.items.size(); k++) {
-      const Item &it = wl.items[k];
-      if (it.kind != kSelf) {
-        need_sort(it.own, it.sid);
-        need_sort(it.partner, it.sid);
+  // The lists of a leaf depend on nothing but the flattened interactions (read-only from here on): contiguous
+  // chunks of `visit` go to the host threads, each with its own output vectors, stitched together in order below.
+  struct Chunk {
+    std::vector<Item> items, redo;
+    std::vector<int32_t> n_items, n_redo;  // per visited leaf of the chunk
+  };
+  const size_t nv = visit.size();
+  std::vector<Chunk> chunks((size_t)host_threads());
+  std::vector<std::pair<size_t, size_t>> range(chunks.size(), {0, 0});
+  parallel_chunks(nv, 512, [&](size_t t, size_t lo, size_t hi) {
+    Chunk &ck = chunks[t];
+    range[t] = {lo, hi};
+    RedoBuilder rb{prm, tree, cell_active, cell_tasks, f};
+    std::vector<const std::vector<SeqItem> *> chain;
+    std::vector<SeqItem> merged;
+    ck.n_items.reserve(hi - lo);
+    ck.n_redo.reserve(hi - lo);
+    for (size_t v = lo; v < hi; v++) {
+      const int32_t c = visit[v];
+      // every interaction that updates this leaf's particles: its own and its ancestors', in execution order
+      chain.clear();
+      for (int a = (int)c; a >= 0; a = tree.cells[a].parent)
+        if (!f.per_cell[a].empty()) chain.push_back(&f.per_cell[a]);
+      const size_t before = ck.items.size();
+      if (chain.size() == 1) {
+        for (const SeqItem &si : *chain[0]) ck.items.push_back(si.it);
+      } else if (chain.size() > 1) {
+        merged.clear();
+        for (auto *vv : chain) merged.insert(merged.end(), vv->begin(), vv->end());
+        std::sort(merged.begin(), merged.end(), [](const SeqItem &a, const SeqItem &b) { return a.seq < b.seq; });
+        for (const SeqItem &si : merged) ck.items.push_back(si.it);
       }
+      const size_t rbefore = ck.redo.size();
+      rb.build((int)c, ck.redo);
+      ck.n_items.push_back((int32_t)(ck.items.size() - before));
+      ck.n_redo.push_back((int32_t)(ck.redo.size() - rbefore));
     }
-    for (size_t k = rbefore; k < wl.redo_items.size(); k++) {
-      const Item &it = wl.redo_items[k];
-      if (it.kind != kSubSelf) need_sort(it.partner, it.sid);
+  });
+  size_t tot_items = 0, tot_redo = 0;
+  for (const Chunk &ck : chunks) {
+    tot_items += ck.items.size();
+    tot_redo += ck.redo.size();
+  }
+  wl.items.reserve(tot_items);
+  wl.redo_items.reserve(tot_redo);
+  for (size_t t = 0; t < chunks.size(); t++) {
+    const Chunk &ck = chunks[t];
+    size_t ip = 0, rp = 0;
+    for (size_t v = range[t].first; v < range[t].second; v++) {
+      const size_t q = v - range[t].first;
+      const int ni = ck.n_items[q], nr = ck.n_redo[q];
+      if (ni == 0 && nr == 0) continue;
+      const int32_t c = visit[v];
+      const swift_cuda_cell &cell = tree.cells[c];
+      for (int k = 0; k < ni; k++) {
+        const Item &it = ck.items[ip + k];
+        if (it.kind != kSelf) {
+          need_sort(it.own, it.sid);
+          need_sort(it.partner, it.sid);
+        }
+        wl.items.push_back(it);
+      }
+      for (int k = 0; k < nr; k++) {
+        const Item &it = ck.redo[rp + k];
+        if (it.kind != kSubSelf) need_sort(it.partner, it.sid);
+        wl.redo_items.push_back(it);
+      }
+      ip += ni;
+      rp += nr;
+      const int32_t slot = (int32_t)wl.leaves.size();
+      wl.leaves.push_back((int32_t)c);
+      wl.item_begin.push_back((int32_t)wl.items.size());
+      wl.redo_begin.push_back((int32_t)wl.redo_items.size());
+      wl.unit_begin.push_back((int32_t)wl.unit_leaf.size());
+      for (int off = 0; off < cell.count; off += 32) wl.unit_leaf.push_back(slot);
     }
-    const int32_t slot = (int32_t)wl.leaves.size();
-    wl.leaves.push_back((int32_t)c);
-    wl.item_begin.push_back((int32_t)wl.items.size());
-    wl.redo_begin.push_back((int32_t)wl.redo_items.size());
-    wl.unit_begin.push_back((int32_t)wl.unit_leaf.size());
-    for (int off = 0; off < cell.count; off += 32) wl.unit_leaf.push_back(slot);
   }
   wl.unit_begin.push_back((int32_t)wl.unit_leaf.size());
 }
@@ -741,7 +841,7 @@ void assign_lanes(const Tree &tree, const double *x, WorkLists &wl) {
       split_units(pts.data(), cell.count, nunits, &wl.lane_part[(size_t)wl.unit_begin[s] * 32]);
     }
   };
-  const size_t nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+  const size_t nt = (size_t)host_threads();
   if (nl < 2000 || nt == 1) {
     work(0, 1);
   } else {

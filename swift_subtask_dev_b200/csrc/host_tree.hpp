@@ -81,6 +81,9 @@ extern const double kAxis[13][3];
 // an error code (1: empty grid, 2: periodic box with fewer than 3 cells).
 int build_tree(const swift_cuda_params &prm, int64_t n, const double *x, const float *h, Tree &tree);
 
+// dst[k] = src[order[k]] on the host threads (the particles' h in cell order).
+void gather_f32(const float *src, const int32_t *order, int64_t n, float *dst);
+
 // Computes tree.h_max from particle h (cell order).
 void compute_cell_hmax(Tree &tree, const float *h_cell_order);
 

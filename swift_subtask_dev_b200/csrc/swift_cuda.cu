@@ -585,7 +585,7 @@ int swift_cuda_build_from_particles(swift_cuda_ctx *c, const swift_cuda_parts_in
   if (rc == 1) return fail("build: top-level grid has a zero dimension");
   if (rc == 2) return fail("build: periodic box needs at least 3 top-level cells per dimension (h_max too large)");
   std::vector<float> hs(in->n);
-  for (int64_t k = 0; k < in->n; k++) hs[k] = in->h[c->tree.order[k]];
+  gather_f32(in->h, c->tree.order.data(), in->n, hs.data());
   compute_cell_hmax(c->tree, hs.data());
   build_tasks(c->prm, c->tree);
   std::vector<uint8_t> act;
@@ -1556,7 +1556,7 @@ int swift_cuda_host_plan(const swift_cuda_params *params, const swift_cuda_parts
   const int rc = build_tree(*params, in->n, in->x, in->h, tree);
   if (rc) return fail("host_plan: cannot build the top-level grid (code " + std::to_string(rc) + ")");
   std::vector<float> hs(in->n);
-  for (int64_t k = 0; k < in->n; k++) hs[k] = in->h[tree.order[k]];
+  gather_f32(in->h, tree.order.data(), in->n, hs.data());
   compute_cell_hmax(tree, hs.data());
   build_tasks(*params, tree);
   std::vector<uint8_t> act(tree.cells.size(), 1);
@@ -1580,6 +1580,63 @@ int swift_cuda_host_plan(const swift_cuda_params *params, const swift_cuda_parts
   return 0;
 }
 void swift_cuda_host_free(void *p) { free(p); }
+
+// FNV-1a over everything the host builder hands to the device for these particles (tree, tasks, order, the two
+// item lists, leaves, units, lanes, sort segments, recursion limits): what a test compares between the threaded
+// builder and SWIFT_CUDA_HOST_THREADS=1.
+int swift_cuda_host_plan_digest(const swift_cuda_params *params, const swift_cuda_parts_in *in,
+                                unsigned long long *digest) {
+  if (!params || !in || !digest) return fail("host_plan_digest: null argument");
+  Tree tree;
+  const int rc = build_tree(*params, in->n, in->x, in->h, tree);
+  if (rc) return fail("host_plan_digest: cannot build the top-level grid (code " + std::to_string(rc) + ")");
+  std::vector<float> hs(in->n);
+  gather_f32(in->h, tree.order.data(), in->n, hs.data());
+  compute_cell_hmax(tree, hs.data());
+  build_tasks(*params, tree);
+  std::vector<uint8_t> act;
+  {
+    swift_cuda_ctx tmp;
+    tmp.prm = *params;
+    tmp.tree = tree;
+    cells_active(&tmp, in, act);
+  }
+  WorkLists wl;
+  build_worklists(*params, tree, act, wl);
+  assign_lanes(tree, in->x, wl);
+  unsigned long long hsh = 1469598103934665603ULL;
+  auto mix = [&](const void *p, size_t bytes) {
+    const unsigned char *b = static_cast<const unsigned char *>(p);
+    for (size_t k = 0; k < bytes; k++) hsh = (hsh ^ b[k]) * 1099511628211ULL;
+  };
+  auto mixv = [&](const auto &v) {
+    const unsigned long long n = v.size();
+    mix(&n, sizeof(n));
+    if (n) mix(v.data(), n * sizeof(v[0]));
+  };
+  for (const swift_cuda_cell &c : tree.cells) {  // field by field: the struct has padding
+    mix(c.loc, sizeof(c.loc)); mix(c.width, sizeof(c.width));
+    const int ints[5] = {c.first, c.count, c.parent, c.depth, c.split};
+    mix(ints, sizeof(ints)); mix(c.progeny, sizeof(c.progeny));
+  }
+  for (const swift_cuda_task &t : tree.tasks) {
+    const int ints[3] = {t.type, t.ci, t.cj};
+    mix(ints, sizeof(ints));
+  }
+  mixv(tree.order); mixv(tree.h_max);
+  for (const std::vector<Item> *lst : {&wl.items, &wl.redo_items})
+    for (const Item &it : *lst) {
+      const int v[5] = {it.partner, it.own, it.kind, it.sid, it.shift};
+      mix(v, sizeof(v));
+    }
+  mixv(wl.leaves); mixv(wl.item_begin); mixv(wl.redo_begin); mixv(wl.unit_leaf); mixv(wl.unit_begin);
+  mixv(wl.lane_part); mixv(wl.sort_cells); mixv(wl.sort_sids); mixv(wl.sort_offset); mixv(wl.sort_lookup);
+  mixv(wl.recurse_limit);
+  mix(&wl.n_sort_entries, sizeof(wl.n_sort_entries));
+  mix(&wl.n_interactions, sizeof(wl.n_interactions));
+  *digest = hsh;
+  return 0;
+}
 
 // ---- pair recording (test hook) ---------------------------------------------
 int swift_cuda_record_pairs(swift_cuda_ctx *c, long long capacity) {

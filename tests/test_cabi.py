@@ -109,3 +109,29 @@ def test_struct_part_mirror_has_the_reference_layout():
     parts = be.parts_from_ic(ic)
     assert np.array_equal(parts["x"], ic["x"]) and np.array_equal(parts["h"], ic["h"])
     assert (parts["time_bin"] == 1).all() and (parts["rho"] == 0).all()
+
+
+DIGEST_CASES = [
+    ("uniform_split", lambda: ics.uniform_random(96 ** 3, seed=5), dict(periodic=True)),
+    ("clustered", lambda: ics.clustered(60000, nclumps=16, seed=3), dict(periodic=True)),
+    ("open_small", lambda: ics.uniform_random(20 ** 3, seed=7), dict(periodic=False)),
+    ("timebins", lambda: dict(ics.uniform_random(48 ** 3, seed=9),
+                              time_bin=np.random.default_rng(2).integers(1, 5, 48 ** 3).astype(np.int8)),
+     dict(periodic=True, max_active_bin=2)),
+]
+
+
+@pytest.mark.parametrize("name,make,kw", DIGEST_CASES, ids=[c[0] for c in DIGEST_CASES])
+def test_host_builder_threads_give_the_same_lists(name, make, kw, monkeypatch):
+    """The host builder shares its counting sort, the octree split, the per-leaf interaction lists and the lane
+    assignment out over host threads; the tree, the task list, the cell order, both item lists, units, lanes and
+    sort segments must come out byte for byte as from the single-threaded form (SWIFT_CUDA_HOST_THREADS=1)."""
+    ic = make()
+    prm = make_params(**kw)
+    monkeypatch.setenv("SWIFT_CUDA_HOST_THREADS", "1")
+    serial = be.host_plan_digest(prm, ic)
+    for nthreads in ("2", "5", "16"):
+        monkeypatch.setenv("SWIFT_CUDA_HOST_THREADS", nthreads)
+        assert be.host_plan_digest(prm, ic) == serial, "%s host threads" % nthreads
+    monkeypatch.delenv("SWIFT_CUDA_HOST_THREADS")
+    assert be.host_plan_digest(prm, ic) == serial
