@@ -1,4 +1,4 @@
-"""Runs the UNMODIFIED reference unit tests (tests/test27cells.c, tests/test125cells.c, linked against
+"""Runs the UNMODIFIED reference unit tests (tests/test27cells.c, tests/test125cells.c, tests/testPeriodicBC.c, linked against
 the reference's own runner_doiact_hydro.o by oracle/Makefile.shim, target `cpu`) in this container and
 stores their output tables as fixtures: what tests/test_reference_tests.py compares the same tests,
 linked against the shim + libswiftcuda.so instead, with on the GPU box."""
@@ -27,3 +27,21 @@ for variant, suffix, prefix in (("minimal", "", ""), ("sphenix", "_sphenix", "sp
             subprocess.run([exe] + args, cwd=tmp, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
             shutil.copy(os.path.join(tmp, out), os.path.join(HERE, "ref_tests", prefix + name + ".dat"))
             print(variant, name, "->", out)
+
+# tests/testPeriodicBC.c (26 boundary cells of an 8^3 periodic grid, each against its 26 wrapped neighbours; the
+# reference's script runs -v 0..3, tests/testPeriodicBC.sh.in:3-11): the 1 MB tables are kept as compressed arrays
+import numpy as np  # noqa: E402
+PBC = {"testPeriodicBC_v0": ["-n", "6", "-r", "1", "-d", "0", "-f", "standard", "-v", "0"],
+       "testPeriodicBC_v2": ["-n", "6", "-r", "1", "-d", "0", "-f", "standard", "-v", "2"]}
+for variant, suffix, prefix in (("minimal", "", ""), ("sphenix", "_sphenix", "sphenix_")):
+    for name, args in PBC.items():
+        exe = os.path.join(REF, "testPeriodicBC_ref" + suffix)
+        if not os.path.exists(exe):
+            print("skip", variant, name, "(not built)")
+            continue
+        with tempfile.TemporaryDirectory() as tmp:
+            subprocess.run([exe] + args, cwd=tmp, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            rows = [l.split() for l in open(os.path.join(tmp, "swift_periodic_BC_standard.dat"))
+                    if l.strip() and not l.lstrip().startswith("#")]
+            np.savez_compressed(os.path.join(HERE, "ref_tests", prefix + name + ".npz"), table=np.array(rows, dtype=np.float64))
+            print(variant, name, "->", len(rows), "rows")

@@ -1,4 +1,4 @@
-"""The reference's OWN unit tests (tests/test27cells.c, tests/test125cells.c), compiled from where
+"""The reference's OWN unit tests (tests/test27cells.c, tests/test125cells.c, tests/testPeriodicBC.c), compiled from where
 they lie and linked against swift_subtask_dev_b200/shim/swift_cuda_shim.c + libswiftcuda.so instead
 of the reference's runner_doiact_hydro.o (oracle/Makefile.shim).  Their output tables are gated the
 way the reference gates them (tests/difffloat.py:75-130 with tests/tolerance_*.dat: absolute,
@@ -91,4 +91,28 @@ def test_test125cells_through_the_shim(name, args, tolfile, suffix, prefix, tmp_
     assert len(bad) == 0, "difffloat gate: %d entries out of tolerance, first (row, col) %s" % (len(bad), bad[:5])
     ref = load_table(os.path.join(GOLD, prefix + name + ".dat"))
     bad = difffloat(ours, ref, tol, 10 ** 6)  # the reference's gate on ALL rows (the tables print 7 digits)
+    assert len(bad) == 0, "against the reference's own table: %d entries, first (row, col) %s" % (len(bad), bad[:5])
+
+
+# tests/testPeriodicBC.c: an 8^3 grid of cells in a periodic box; for each of 26 boundary cells (corners, face
+# and edge centres) the density pair task against its 26 neighbours THROUGH the box wrap and the self task
+# (tests/testPeriodicBC.c:295-336, 545-627).  The reference's script (tests/testPeriodicBC.sh.in:3-11) gates the
+# first 6^3 rows with tolerance_periodic_BC_normal.dat for -v 0..3; here every row of the table is gated.
+CASES_PBC = [("testPeriodicBC_v0", ["-n", "6", "-r", "1", "-d", "0", "-f", "standard", "-v", "0"]),
+             ("testPeriodicBC_v2", ["-n", "6", "-r", "1", "-d", "0", "-f", "standard", "-v", "2"])]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("suffix,prefix", VARIANTS, ids=["minimal", "sphenix"])
+@pytest.mark.parametrize("name,args", CASES_PBC)
+def test_testPeriodicBC_through_the_shim(name, args, suffix, prefix, tmp_path):
+    run_test("testPeriodicBC_cuda" + suffix, args, tmp_path)
+    ours = load_table(tmp_path / "swift_periodic_BC_standard.dat")
+    brute = load_table(tmp_path / "brute_force_periodic_BC_standard.dat")
+    tol = load_table(os.path.join(REF, "tolerance_periodic_BC_normal.dat"))
+    assert len(ours) == 26 * 6 ** 3
+    bad = difffloat(ours, brute, tol, 10 ** 6)
+    assert len(bad) == 0, "difffloat gate: %d entries out of tolerance, first (row, col) %s" % (len(bad), bad[:5])
+    ref = np.load(os.path.join(GOLD, prefix + name + ".npz"))["table"]
+    bad = difffloat(ours, ref, tol, 10 ** 6)
     assert len(bad) == 0, "against the reference's own table: %d entries, first (row, col) %s" % (len(bad), bad[:5])
