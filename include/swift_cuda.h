@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define SWIFT_CUDA_ABI_VERSION 3
+#define SWIFT_CUDA_ABI_VERSION 4
 
 /* SPHENIX (the reference's configure default, configure.ac:1958-1959) is the three-loop scheme: see the
  * "SPHENIX" section below for what it adds and which entries support it. */
@@ -396,6 +396,42 @@ int swift_cuda_reset_offsets(swift_cuda_ctx *ctx, int what);
 int swift_cuda_get_state(swift_cuda_ctx *ctx, const swift_cuda_state_out *out);
 /* Device time (CUDA events on the context's stream) of the last drift, kick1, kick2, timestep, ms. */
 int swift_cuda_get_integrator_timings(swift_cuda_ctx *ctx, float ms[4]);
+
+/* ---- Time-step limiter (swift --limiter; the remainder of SURVEY.md 8(f) N3) --------------------
+ * Replaces
+ *   runner_do{self,pair}1_branch_limiter,     src/runner_doiact_limiter.h:94-102 = the DOSELF1 / DOPAIR1 /
+ *   runner_dosub_{self,pair}1_limiter         DOSUB_*1 walks of src/runner_doiact_functions_limiter.h:233-828
+ *                                             with runner_iact_nonsym_limiter (src/timestep_limiter_iact.h:
+ *                                             107-117); call sites src/runner_main.c:205-206, 255-256,
+ *                                             303-304, 349-350
+ *   runner_do_limiter                         src/runner_time_integration.c:1324-1467 with
+ *                                             timestep_limit_part (src/timestep_limiter.h:67-217); call
+ *                                             site src/runner_main.c:467-468
+ * Order in a step (src/engine_maketasks.c: kick2 -> timestep -> limiter loop -> timestep_limiter -> kick1):
+ *   ... step; kick(2); timestep; do_limiter_loop; do_limiter; kick(1)
+ * the next ti_current being the smaller of what swift_cuda_timestep and swift_cuda_do_limiter return.
+ *
+ * swift_cuda_do_limiter_loop: for every particle that STARTS a step now (time_bin <= max_active_bin, on the
+ * bins the time-step task has just given) and every neighbour j within its kernel support whose bin is more
+ * than time_bin_neighbour_max_delta_bin (2) above: wakeup[j] = max(wakeup[j], -time_bin_i).  Two starting
+ * particles of the same leaf cell that lie in each other's support do not wake one another (DOSELF1 hands them
+ * to the symmetric runner_iact_limiter, which does nothing); in a pair of cells they do -- as the reference.
+ * Positions, smoothing lengths, sorts and work lists are those of the step just done (kick2 and the time-step
+ * task move neither x nor h).
+ *   time_bin: NULL in the time-integration mode (the bins are on the device).  A caller that runs
+ *             runner_do_timestep itself passes p->time_bin of all n particles (caller order).
+ *   wakeup:   NULL, or n bytes (caller order) that receive p->limiter_data.wakeup (time_bin_not_awake = -56
+ *             where nobody asked) for the caller's own runner_do_limiter.
+ * Single device: a woken halo copy is not sent back to its owner (the reference's limiter pack / unpack
+ * tasks, src/runner_main.c:539-543, have no counterpart in swift_subtask_dev_b200/multi.py). */
+int swift_cuda_do_limiter_loop(swift_cuda_ctx *ctx, const signed char *time_bin, signed char *wakeup);
+/* runner_do_limiter on the device state (time-integration mode): every woken particle takes the bin
+ * -wakeup + 2; an inactive one has the kick1 of its running step undone, is kicked to the beginning of the
+ * new step that contains ti_current and, unless that step starts now, given its first half-kick.
+ * ti_end_min: earliest new end of step (2^57 if nobody was woken); limited: how many were. */
+int swift_cuda_do_limiter(swift_cuda_ctx *ctx, long long *ti_end_min, long long *limited);
+/* Device time of the last limiter loop and the last swift_cuda_do_limiter, ms. */
+int swift_cuda_get_limiter_timings(swift_cuda_ctx *ctx, float ms[2]);
 
 /* ---- SPHENIX: the gradient loop and the extra ghost -------------------------
  * params.scheme = SWIFT_CUDA_SCHEME_SPHENIX (+ ideal gas) turns the step into the reference's

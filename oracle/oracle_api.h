@@ -88,6 +88,16 @@ typedef struct {
    * decides how deep the sub-tasks recurse and stays fixed between rebuilds, src/space_split.c).
    * NULL: the current h (a step right after a rebuild). */
   const float *in_h_build;
+  /* optional, the time-step LIMITER loop (task_subtype_limiter, src/runner_doiact_limiter.c with
+   * runner_iact_nonsym_limiter, src/timestep_limiter_iact.h:107-117): run after end_force on the same
+   * positions and smoothing lengths, with the time bins runner_do_timestep has just given
+   * (l_time_bin, every particle); l_wakeup = p->limiter_data.wakeup afterwards (time_bin_not_awake =
+   * -56 where nobody asked).  Both NULL: the loop is not run. */
+  const signed char *l_time_bin;
+  signed char *l_wakeup;
+  /* != 0: sort and the limiter loop ONLY, on x, h as given (the engine loop of tests/integ_lib.py calls
+   * the step first, then the time-step task, then this: the new bins are not known earlier) */
+  int l_only;
 } oracle_parts;
 
 /* Ordered (updated id, neighbour id) pairs.  loop 0: first density pass,
@@ -169,7 +179,8 @@ void oracle_free(void *p);
  * drift (src/drift.h:143-233 inside the particle loop of src/cell_drift.c:233-340),
  * kick (src/kick.h:215-279 as called by src/runner_time_integration.c:141-180, 412-457),
  * time-step (src/timestep.h:45-82, 141-222; src/runner_time_integration.c:696-745),
- * without cosmology, gravity, cooling, limiter.  All arrays have n entries ([n][3] vectors). */
+ * without cosmology, gravity, cooling; the time-step limiter is ref_limiter / oracle_limiter below and the
+ * l_* fields of oracle_parts.  All arrays have n entries ([n][3] vectors). */
 typedef struct {
   int scheme;                    /* ORACLE_SCHEME_* (the ref harness ignores it) */
   float cfl_condition;           /* hydro_props->CFL_condition */
@@ -209,6 +220,16 @@ int oracle_kick(const oracle_iparams *ip, const oracle_eos *eos, oracle_istate *
  * updated = particles that got a new step.  Returns 2 when a particle wants a step below dt_min. */
 int ref_timestep(const oracle_iparams *ip, oracle_istate *s, long long *ti_end_min, long long *updated);
 int oracle_timestep(const oracle_iparams *ip, oracle_istate *s, long long *ti_end_min, long long *updated);
+/* runner_do_limiter (src/runner_time_integration.c:1324-1467, force = 1) on a cell holding all particles:
+ * timestep_limit_part (src/timestep_limiter.h:67-217) for every particle with wakeup[k] != -56
+ * (time_bin_not_awake) -- an active one only takes the bin -wakeup + 2; an inactive one has its kick1
+ * undone, is kicked to the start of its new, shorter step and, if that bin does not start now, given
+ * the first half-kick of it.  Updates v_full, u_full, u_dt, time_bin; wakeup[k] is reset.  ti_end_min =
+ * the earliest new end of step (max_nr_timesteps if nobody was woken); limited = their number. */
+int ref_limiter(const oracle_iparams *ip, oracle_istate *s, signed char *wakeup, long long *ti_end_min,
+                long long *limited);
+int oracle_limiter(const oracle_iparams *ip, const oracle_eos *eos, oracle_istate *s, signed char *wakeup,
+                   long long *ti_end_min, long long *limited);
 
 #ifdef __cplusplus
 }

@@ -82,7 +82,12 @@ int ref_sizeof_part(void) { return (int)sizeof(struct part); }
  * serial run (rounding differs), which is why nothing is CHECKED in this mode. */
 #include <pthread.h>
 #include <time.h>
-enum { PH_SORT, PH_DENSITY, PH_GHOST, PH_GRADIENT, PH_EXTRA_GHOST, PH_FORCE, PH_END_FORCE };
+enum { PH_SORT, PH_DENSITY, PH_GHOST, PH_GRADIENT, PH_EXTRA_GHOST, PH_FORCE, PH_END_FORCE, PH_LIMITER };
+/* src/runner_doiact_limiter.h:94-102 (FUNCTION = limiter, compiled in src/runner_doiact_limiter.c) */
+void runner_doself1_branch_limiter(struct runner *r, struct cell *c);
+void runner_dopair1_branch_limiter(struct runner *r, struct cell *ci, struct cell *cj);
+void runner_dosub_self1_limiter(struct runner *r, struct cell *ci, int gettimer);
+void runner_dosub_pair1_limiter(struct runner *r, struct cell *ci, struct cell *cj, int gettimer);
 static int g_threads = 1;
 static double g_last_seconds = 0.0;
 void ref_set_threads(int n) { g_threads = n < 1 ? 1 : n; }
@@ -116,6 +121,13 @@ static void phase_task(struct runner *r, struct task *t, int phase) {
       default: runner_dosub_pair1_gradient(r, t->ci, t->cj, 0); break;
     }
 #endif
+  } else if (phase == PH_LIMITER) {
+    switch (t->type) {
+      case task_type_self: runner_doself1_branch_limiter(r, t->ci); break;
+      case task_type_pair: runner_dopair1_branch_limiter(r, t->ci, t->cj); break;
+      case task_type_sub_self: runner_dosub_self1_limiter(r, t->ci, 0); break;
+      default: runner_dosub_pair1_limiter(r, t->ci, t->cj, 0); break;
+    }
   } else {
     switch (t->type) {
       case task_type_self: runner_doself2_branch_force(r, t->ci); break;
@@ -140,7 +152,9 @@ static void phase_cell(struct runner *r, struct cell *c, int phase) {
   }
 }
 
-static int phase_is_tasks(int phase) { return phase == PH_DENSITY || phase == PH_GRADIENT || phase == PH_FORCE; }
+static int phase_is_tasks(int phase) {
+  return phase == PH_DENSITY || phase == PH_GRADIENT || phase == PH_FORCE || phase == PH_LIMITER;
+}
 
 static void *phase_worker(void *arg) {
   struct phase_ctx *x = (struct phase_ctx *)arg;
@@ -451,6 +465,7 @@ static int run_step(const oracle_params *prm, oracle_parts *io, int ncells, cons
   g_last_seconds = 0.0;
   if (g_threads > 1) g_log = NULL, g_sx = NULL; /* the pair log is not thread safe: nothing is recorded or counted */
   run_phase(&px, &runner, PH_SORT);
+  if (io->l_only) goto limiter_loop;
 
   /* ---- density ---- */
   g_stage = 0;
@@ -506,8 +521,6 @@ static int run_step(const oracle_params *prm, oracle_parts *io, int ncells, cons
   g_stage = 2;
   run_phase(&px, &runner, PH_FORCE);
   run_phase(&px, &runner, PH_END_FORCE);
-  for (int k = 0; k < ncells; k++) pthread_mutex_destroy(&px.locks[k]);
-  free(px.locks);
   for (int k = 0; k < n; k++) {
     const struct part *p = &parts[k];
     if (io->f_a)
@@ -517,6 +530,29 @@ static int run_step(const oracle_params *prm, oracle_parts *io, int ncells, cons
     if (io->f_v_sig) io->f_v_sig[k] = PART_V_SIG(p);
     if (io->f_min_ngb_time_bin) io->f_min_ngb_time_bin[k] = p->limiter_data.min_ngb_time_bin;
   }
+
+limiter_loop:
+  /* ---- time-step limiter loop (src/runner_main.c:205-206, 255-256, 303-304, 349-350): the tasks of
+   * subtype limiter sit on the same cells as the density tasks (src/engine_maketasks.c: the limiter
+   * loop is linked next to density / force for every hydro self / pair) and run after the time-step
+   * task, i.e. with the NEW bins; kick2 and the time-step task move neither x nor h ---- */
+  if (io->l_time_bin != NULL && io->l_wakeup != NULL) {
+    for (int k = 0; k < n; k++) {
+      parts[k].time_bin = io->l_time_bin[k];
+      parts[k].limiter_data.wakeup = time_bin_not_awake;
+    }
+    for (int k = 0; k < ncells; k++) {
+      struct cell *c = &cells[k];
+      /* cell_is_starting_hydro (src/active.h:588-601); the flags are what cell_activate_subcell_hydro_tasks
+       * (with_timestep_limiter) and cell_activate_limiter leave on the cells of an active task */
+      c->hydro.ti_beg_max = cell_has_active(c, &engine) ? ti_current : 0;
+      cell_set_flag(c, cell_flag_do_hydro_limiter | cell_flag_do_hydro_sub_limiter);
+    }
+    run_phase(&px, &runner, PH_LIMITER);
+    for (int k = 0; k < n; k++) io->l_wakeup[k] = parts[k].limiter_data.wakeup;
+  }
+  for (int k = 0; k < ncells; k++) pthread_mutex_destroy(&px.locks[k]);
+  free(px.locks);
 
   g_log = NULL;
   g_sx = NULL;
@@ -700,6 +736,27 @@ int ref_timestep(const oracle_iparams *ip, oracle_istate *s, long long *ti_end_m
   runner_do_timestep(&v->runner, &v->cell, 0);
   *ti_end_min = v->cell.hydro.ti_end_min;
   *updated = v->cell.hydro.updated;
+  ienv_store(v, s);
+  return 0;
+}
+
+int ref_limiter(const oracle_iparams *ip, oracle_istate *s, signed char *wakeup, long long *ti_end_min,
+                long long *limited) {
+  ienv *v = ienv_make(ip, s);
+  if (v == NULL) return 1;
+  long long count = 0;
+  for (int k = 0; k < s->n; k++) {
+    v->parts[k].limiter_data.wakeup = wakeup[k];
+    v->parts[k].limiter_data.to_be_synchronized = 0;
+    if (wakeup[k] != time_bin_not_awake) count++;
+  }
+  v->cell.hydro.ti_end_min = max_nr_timesteps;
+  v->cell.hydro.ti_beg_max = 0;
+  v->space.periodic = 0; /* as in ref_kick: no mesh */
+  runner_do_limiter(&v->runner, &v->cell, /*force=*/1, 0);
+  *ti_end_min = v->cell.hydro.ti_end_min;
+  *limited = count;
+  for (int k = 0; k < s->n; k++) wakeup[k] = v->parts[k].limiter_data.wakeup;
   ienv_store(v, s);
   return 0;
 }

@@ -85,7 +85,7 @@ typedef struct {
   float alpha_visc, div_v_prev, div_v_dt, alpha_diff, laplace_u, alpha_visc_max_ngb;
   long long id;
   int mat_id;
-  signed char time_bin, min_ngb_time_bin;
+  signed char time_bin, min_ngb_time_bin, wakeup; /* wakeup: p->limiter_data.wakeup */
 } opart;
 
 typedef struct {
@@ -112,7 +112,7 @@ typedef struct {
   const oracle_task *tasks;
   int ntasks;
   oracle_pairlog *log;
-  int stage; /* 0 density, 1 ghost redo, 2 force, 3 gradient (SPHENIX) */
+  int stage; /* 0 density, 1 ghost redo, 2 force, 3 gradient (SPHENIX), 4 time-step limiter */
   float a, H; /* cosmology_init_no_cosmo: a = 1, H = 0 */
   float beta;
   oracle_sphenix *sx; /* SPHENIX only */
@@ -164,6 +164,19 @@ static inline void iact_density(octx *c, float r2, const float dx[3], float hi, 
    * DOSUB_*1 walks (src/runner_doiact_hydro.c:47-52): same loops, another interaction */
   if (c->stage == 3) {
     iact_gradient(c, r2, dx, hi, pi, pj);
+    return;
+  }
+  /* likewise the limiter loop: FUNCTION = limiter in walks of the same shape
+   * (src/runner_doiact_functions_limiter.h:233-450, 541-680), with "starting" for "active" -- the same
+   * comparison time_bin <= max_active_bin (src/active.h:698-717), on the bins the time-step task has
+   * just given.  runner_iact_nonsym_limiter, src/timestep_limiter_iact.h:107-117: the NEIGHBOUR is
+   * written (accumulate_max_c). */
+  if (c->stage == 4) {
+    opart *wj = (opart *)pj;
+    if (wj->time_bin > pi->time_bin + 2 /* time_bin_neighbour_max_delta_bin */) {
+      const signed char w = (signed char)(-pi->time_bin);
+      if (w > wj->wakeup) wj->wakeup = w;
+    }
     return;
   }
   float wi, wi_dx;
@@ -791,6 +804,10 @@ static void self_density(octx *c, ocell *cell) {
         }
         const int doj = part_active(c, pj) && (r2 < hj * hj * K_GAMMA2);
         const int doi = (r2 < hig2);
+        /* limiter loop: doi && doj is the symmetric runner_iact_limiter, which does nothing
+         * (src/runner_doiact_functions_limiter.h:655-660, src/timestep_limiter_iact.h:76-102) -- in the
+         * sorted pair walk there is no such case, a starting neighbour is written like any other */
+        if (c->stage == 4 && doi && doj) continue;
         if (doi) iact_density(c, r2, dx, hi, pi, pj);
         if (doj) {
           float mdx[3] = {-dx[0], -dx[1], -dx[2]};
@@ -1695,6 +1712,8 @@ static int run_step(const oracle_params *prm, const oracle_eos *eos, oracle_part
     if (td[t].cj >= 0) cell_add_task(&c.cells[td[t].cj], t);
   }
 
+  if (io->l_only) goto limiter_loop;
+
   /* density */
   c.stage = 0;
   for (int t = 0; t < ntasks; t++) {
@@ -1784,6 +1803,35 @@ static int run_step(const oracle_params *prm, const oracle_eos *eos, oracle_part
     if (io->f_h_dt) io->f_h_dt[k] = p->h_dt;
     if (io->f_v_sig) io->f_v_sig[k] = p->v_sig;
     if (io->f_min_ngb_time_bin) io->f_min_ngb_time_bin[k] = p->min_ngb_time_bin;
+  }
+
+limiter_loop:
+  /* time-step limiter loop: the density-shaped walks once more, after the time-step task (new bins),
+   * positions, h and the sorts as they are (src/runner_main.c:205-206, 255-256, 303-304, 349-350) */
+  if (io->l_time_bin != NULL && io->l_wakeup != NULL) {
+    for (int k = 0; k < n; k++) {
+      c.parts[k].time_bin = io->l_time_bin[k];
+      c.parts[k].wakeup = -NUM_TIME_BINS; /* time_bin_not_awake, src/timeline.h:48 */
+    }
+    for (int k = 0; k < ncells; k++) {
+      ocell *o = &c.cells[k];
+      o->active = 0; /* cell_is_starting_hydro */
+      for (int j = 0; j < o->count; j++)
+        if (part_active(&c, &c.parts[o->first + j])) o->active = 1;
+    }
+    c.stage = 4;
+    c.log = NULL;
+    for (int t = 0; t < ntasks; t++) {
+      ocell *ci = &c.cells[td[t].ci];
+      ocell *cj = td[t].cj >= 0 ? &c.cells[td[t].cj] : NULL;
+      switch (td[t].type) {
+        case ORACLE_TASK_SELF: self_density_branch(&c, ci); break;
+        case ORACLE_TASK_PAIR: pair_density_branch(&c, ci, cj); break;
+        case ORACLE_TASK_SUB_SELF: sub_self(&c, ci, 0); break;
+        default: sub_pair(&c, ci, cj, 0); break;
+      }
+    }
+    for (int k = 0; k < n; k++) io->l_wakeup[k] = c.parts[k].wakeup;
   }
 
   for (int k = 0; k < ncells; k++) {
@@ -1899,6 +1947,71 @@ int oracle_drift(const oracle_iparams *ip, const oracle_eos *eos, oracle_istate 
 /* kick_part (src/kick.h:244-278) with hydro_kick_extra (Minimal/hydro.h:901-930, Planetary/hydro.h:904-925),
  * driven as runner_do_kick1 / runner_do_kick2 do (src/runner_time_integration.c:141-180, 412-457);
  * kick2 ends with hydro_reset_predicted_values (Minimal/hydro.h:771-796, Planetary/hydro.h:778-803). */
+/* one kick_part over dt (all of dt_kick_hydro, dt_kick_therm, dt_kick_corr without cosmology) */
+static void kick_one(const oracle_iparams *ip, oracle_istate *s, int k, double dt) {
+  const int planetary = ip->scheme == ORACLE_SCHEME_PLANETARY;
+  for (int d = 0; d < 3; d++) s->v_full[3 * k + d] += s->a[3 * k + d] * dt;
+  const float dt_therm = dt;
+  const float delta_u = s->u_dt[k] * dt_therm;
+  const float ua = s->u_full[k] + delta_u, ub = 0.5f * s->u_full[k];
+  s->u_full[k] = ua > ub ? ua : ub;
+  const float min_u = ip->minimal_internal_energy / 1.0;
+  const float floor_u = 0.f;
+  const float energy_min = planetary ? min_u : (min_u > floor_u ? min_u : floor_u);
+  if (s->u_full[k] < energy_min) {
+    s->u_full[k] = energy_min;
+    s->u_dt[k] = 0.f;
+  }
+}
+
+/* runner_do_limiter on a leaf (src/runner_time_integration.c:1385-1452) with timestep_limit_part
+ * (src/timestep_limiter.h:67-217); kick_get_*_kick_dt without cosmology = (ti_end - ti_beg) * time_base
+ * (src/kick.h:43-60). */
+int oracle_limiter(const oracle_iparams *ip, const oracle_eos *eos, oracle_istate *s, signed char *wakeup,
+                   long long *ti_end_min_out, long long *limited_out) {
+  (void)eos;
+  const signed char not_awake = -NUM_TIME_BINS;
+  long long ti_end_min = MAX_NR_TIMESTEPS, limited = 0;
+  for (int k = 0; k < s->n; k++) {
+    if (wakeup[k] == not_awake) continue;
+    limited++;
+    long long ti_end_new;
+    if (s->time_bin[k] <= ip->max_active_bin) {
+      /* active: only the length of the step that starts now changes */
+      s->time_bin[k] = (signed char)(-wakeup[k] + 2);
+      ti_end_new = ip->ti_current + int_timestep(s->time_bin[k]);
+    } else {
+      const int old_bin = s->time_bin[k];
+      const int new_bin = (signed char)(-wakeup[k] + 2);
+      const long long ti_beg_old = int_time_begin(ip->ti_current, old_bin);
+      const long long ti_end_old = int_time_end(ip->ti_current, old_bin);
+      const long long dti_old = ti_end_old - ti_beg_old;
+      const long long dti_new = int_timestep(new_bin);
+      int j = 0;
+      while (ti_beg_old + j * dti_new <= ip->ti_current) j++;
+      const long long ti_beg_new = ti_beg_old + (j - 1) * dti_new;
+      const long long ti_end_half_old = ti_beg_old + dti_old / 2;
+      const long long ti_end_half_new = ti_beg_new + dti_new / 2;
+      /* undo the kick1 of the old step, kick to the start of the new one */
+      kick_one(ip, s, k, -((double)(ti_end_half_old - ti_beg_old) * ip->time_base));
+      kick_one(ip, s, k, (double)(ti_beg_new - ti_beg_old) * ip->time_base);
+      s->time_bin[k] = (signed char)new_bin;
+      if (new_bin > ip->max_active_bin) {
+        /* the new step started earlier: its kick1 is due here, the kick task will not see the particle */
+        kick_one(ip, s, k, (double)(ti_end_half_new - ti_beg_new) * ip->time_base);
+        ti_end_new = ti_beg_new + dti_new;
+      } else {
+        ti_end_new = ip->ti_current + int_timestep(new_bin);
+      }
+    }
+    wakeup[k] = not_awake;
+    ti_end_min = ti_end_new < ti_end_min ? ti_end_new : ti_end_min;
+  }
+  *ti_end_min_out = ti_end_min;
+  *limited_out = limited;
+  return 0;
+}
+
 int oracle_kick(const oracle_iparams *ip, const oracle_eos *eos, oracle_istate *s, int which) {
   const int planetary = ip->scheme == ORACLE_SCHEME_PLANETARY;
   for (int k = 0; k < s->n; k++) {

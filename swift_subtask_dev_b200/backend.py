@@ -139,7 +139,8 @@ EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error
            "swift_cuda_build_from_cells_parts", "swift_cuda_build_from_parts", "swift_cuda_step_parts",
            "swift_cuda_set_max_active_bin", "swift_cuda_timestep_static",
            "swift_cuda_sphenix_set_props", "swift_cuda_sphenix_set_state", "swift_cuda_sphenix_get_results",
-           "swift_cuda_sphenix_get_counter", "swift_cuda_do_gradient", "swift_cuda_do_extra_ghost"]
+           "swift_cuda_sphenix_get_counter", "swift_cuda_do_gradient", "swift_cuda_do_extra_ghost",
+           "swift_cuda_do_limiter_loop", "swift_cuda_do_limiter", "swift_cuda_get_limiter_timings"]
 
 
 class SphenixProps(C.Structure):
@@ -273,6 +274,9 @@ def load_library():
             getattr(lib, name).argtypes = [C.c_void_p, C.c_void_p]
         lib.swift_cuda_do_gradient.argtypes = [C.c_void_p]
         lib.swift_cuda_do_extra_ghost.argtypes = [C.c_void_p]
+        lib.swift_cuda_do_limiter_loop.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.swift_cuda_do_limiter.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.swift_cuda_get_limiter_timings.argtypes = [C.c_void_p, C.c_void_p]
         _lib = lib
     return _lib
 
@@ -570,6 +574,32 @@ class HydroBackend:
         t, u = C.c_longlong(0), C.c_longlong(0)
         self._check(self.lib.swift_cuda_timestep(self.ctx, C.byref(t), C.byref(u)))
         return t.value, u.value
+
+    # ---- time-step limiter (swift --limiter) ----
+    def runner_do_limiter_loop(self, time_bin=None, want_wakeup=False):
+        """The tasks of subtype limiter (runner_do{self,pair}1_branch_limiter, runner_dosub_*1_limiter) over the
+        whole box, after the time-step task.  time_bin: the new bins of all particles (caller order) when the
+        caller runs runner_do_timestep itself; None in the time-integration mode.  Returns
+        p->limiter_data.wakeup (int8, -56 = not awake) when want_wakeup."""
+        tb = None
+        if time_bin is not None:
+            tb = np.ascontiguousarray(time_bin, dtype=np.int8)
+            assert len(tb) == self.n
+        wake = np.zeros(self.n, dtype=np.int8) if want_wakeup else None
+        self._check(self.lib.swift_cuda_do_limiter_loop(self.ctx, tb.ctypes.data if tb is not None else None,
+                                                        wake.ctypes.data if wake is not None else None))
+        return wake
+
+    def runner_do_limiter(self):
+        """runner_do_limiter on the device state; returns (earliest new end of step, woken particles)."""
+        t, u = C.c_longlong(0), C.c_longlong(0)
+        self._check(self.lib.swift_cuda_do_limiter(self.ctx, C.byref(t), C.byref(u)))
+        return t.value, u.value
+
+    def limiter_timings(self):
+        ms = (C.c_float * 2)()
+        self._check(self.lib.swift_cuda_get_limiter_timings(self.ctx, ms))
+        return {"limiter_loop_ms": ms[0], "limiter_ms": ms[1]}
 
     def integrator_timings(self):
         ms = (C.c_float * 4)()

@@ -147,7 +147,8 @@ struct Dev {
   float4 *gin;         // what a gradient-loop neighbour is read for: u, rho, soundspeed, viscosity.alpha
   float4 *sx;          // the rest of a force-loop neighbour: viscosity.alpha, diffusion.alpha, u, unused
   long long *rec_grad; // pair recording of the gradient loop (counter: rec_count[3])
-  long long pad_;      // keeps sizeof(Dev) a multiple of 16: kernel arguments after Dev stay 16-byte aligned
+  int *wakeup;         // time-step limiter loop: p->limiter_data.wakeup per particle (null until the loop is used);
+                       // takes the place of the padding that kept sizeof(Dev) a multiple of 16
 };
 
 }  // namespace swiftcuda

@@ -10,7 +10,10 @@
 //                                   (kick2 ends with hydro_reset_predicted_values, Minimal/hydro.h:771-796)
 //   runner_do_timestep              src/runner_time_integration.c:696-745, 790-800 with get_part_timestep and
 //                                   make_integer_timestep (src/timestep.h:45-82, 141-222)
-// without cosmology (a = 1), gravity, cooling or the time-step limiter.  All three are HBM-bound streaming
+//   runner_do_limiter               src/runner_time_integration.c:1324-1467 with timestep_limit_part
+//                                   (src/timestep_limiter.h:67-217): k_limiter, after the limiter LOOP
+//                                   (k_density<0, false, 2>, kernels.cuh) has filled Dev::wakeup
+// without cosmology (a = 1), gravity or cooling.  All of them are HBM-bound streaming
 // kernels (one thread per particle, 16-byte vector accesses); arithmetic is in the reference's types
 // and operand order, products with the double time steps in f64, so the results are bit-identical.
 #pragma once
@@ -253,6 +256,108 @@ __global__ void k_timestep(Dev d, IntegDev g, IntegPrm ip) {
       atomicMin(g.ti_end_min, (unsigned long long)t_end);
     if (b) atomicAdd(g.updated, (unsigned long long)__popc(b));
   }
+}
+
+// One kick_part over dt on registers (the arithmetic of k_kick): xp->v_full, xp->u_full; at the energy floor
+// p->u_dt becomes 0 (dirty: the acceleration record has to be written back).
+__device__ __forceinline__ void kick_regs(float4 &vf, float4 &acc, double dt, float energy_min, bool &dirty) {
+  vf.x = kick_f(vf.x, acc.x, dt);
+  vf.y = kick_f(vf.y, acc.y, dt);
+  vf.z = kick_f(vf.z, acc.z, dt);
+  const float delta_u = __fmul_rn(acc.w, (float)dt);
+  const float ua = __fadd_rn(vf.w, delta_u), ub = __fmul_rn(0.5f, vf.w);
+  vf.w = ua > ub ? ua : ub;
+  if (vf.w < energy_min) {
+    vf.w = energy_min;
+    acc.w = 0.f;
+    dirty = true;
+  }
+}
+
+// runner_do_limiter on every particle the limiter loop woke (Dev::wakeup != time_bin_not_awake):
+// timestep_limit_part, src/timestep_limiter.h:67-217.  An ACTIVE particle only takes the bin -wakeup + 2
+// for the step that starts now.  An INACTIVE one is in the middle of a step of its old bin: its kick1 is
+// undone (negative dt), it is kicked from the old beginning to the beginning of the new, shorter step that
+// contains ti_current, and -- when that bin does not start now, so that the kick task will not see the
+// particle -- given the first half-kick of the new step on the spot.  The reference finds the new beginning
+// with `while (ti_beg_old + k * dti_new <= ti_current) k++` (:112-115); here the quotient is taken.
+__global__ void k_limiter(Dev d, IntegDev g, IntegPrm ip) {
+  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  long long t_end = kMaxNrTimesteps;
+  int lim = 0;
+  if (p < d.n) {
+    const int wake = d.wakeup[p];
+    if (wake != -kNumTimeBins) {
+      lim = 1;
+      const int old_bin = d.time_bin[p];
+      const int new_bin = (signed char)(-wake + 2);
+      if (old_bin <= kc.max_active_bin) {
+        t_end = ip.ti_current + int_timestep(new_bin);
+      } else {
+        const long long ti_beg_old = int_time_begin(ip.ti_current, old_bin);
+        const long long ti_end_old = int_time_end(ip.ti_current, old_bin);
+        const long long dti_old = ti_end_old - ti_beg_old;
+        const long long dti_new = int_timestep(new_bin);
+        const long long ti_beg_new = ti_beg_old + ((ip.ti_current - ti_beg_old) / dti_new) * dti_new;
+        const long long ti_end_half_old = ti_beg_old + dti_old / 2;
+        const long long ti_end_half_new = ti_beg_new + dti_new / 2;
+        const bool planetary = kc.scheme == SWIFT_CUDA_SCHEME_PLANETARY;
+        const float energy_min = planetary ? ip.min_u : (ip.min_u > 0.f ? ip.min_u : 0.f);
+        float4 acc = d.acc[p];
+        float4 vf = g.vu_full[p];
+        bool dirty = false;
+        kick_regs(vf, acc, -__dmul_rn((double)(ti_end_half_old - ti_beg_old), ip.time_base), energy_min, dirty);
+        kick_regs(vf, acc, __dmul_rn((double)(ti_beg_new - ti_beg_old), ip.time_base), energy_min, dirty);
+        if (new_bin > kc.max_active_bin) {
+          kick_regs(vf, acc, __dmul_rn((double)(ti_end_half_new - ti_beg_new), ip.time_base), energy_min, dirty);
+          t_end = ti_beg_new + dti_new;
+        } else {
+          t_end = ip.ti_current + int_timestep(new_bin);
+        }
+        g.vu_full[p] = vf;
+        if (dirty) d.acc[p] = acc;
+      }
+      const_cast<int8_t *>(d.time_bin)[p] = (int8_t)new_bin;
+      float4 hb = d.hb[p];
+      hb.z = __int_as_float(new_bin);
+      d.hb[p] = hb;
+      d.wakeup[p] = -kNumTimeBins;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const long long other = __shfl_xor_sync(0xffffffffu, t_end, o);
+    t_end = other < t_end ? other : t_end;
+  }
+  const unsigned b = __ballot_sync(0xffffffffu, lim);
+  if ((threadIdx.x & 31) == 0 && b) {
+    atomicMin(g.ti_end_min, (unsigned long long)t_end);
+    atomicAdd(g.updated, (unsigned long long)__popc(b));
+  }
+}
+
+// The limiter loop's per-particle slate: nobody is awake (time_bin_not_awake = -num_time_bins).
+__global__ void k_wakeup_reset(int64_t n, int *wakeup) {
+  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p < n) wakeup[p] = -kNumTimeBins;
+}
+
+// Time bins handed over by a caller that runs the time-step task itself (caller order -> device slots;
+// the force-loop record of a neighbour carries the bin too).
+__global__ void k_set_bins(int64_t n, const int32_t *order, const int8_t *src, int8_t *time_bin, float4 *hb) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int bin = src[order ? order[k] : k];
+  time_bin[k] = (int8_t)bin;
+  float4 r = hb[k];
+  r.z = __int_as_float(bin);
+  hb[k] = r;
+}
+
+// p->limiter_data.wakeup in caller order
+__global__ void k_scatter_wakeup(int64_t n, const int32_t *order, const int *wakeup, int8_t *dst) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  dst[order ? order[k] : k] = (int8_t)wakeup[k];
 }
 
 // State inspection: scatter `width` floats per particle from a strided source to caller order.

@@ -824,6 +824,12 @@ __device__ __noinline__ bool dens_cut_exact_scan(const CutCtx d, const Item *__r
 //         the same DOSELF1 / DOPAIR1 / DOSUB_*1 walks (src/runner_doiact_hydro.c:47-52), so this is the
 //         first-pass walk with the converged h, runner_iact_nonsym_gradient as its body and one more
 //         float4 gathered per hit (gin: u, rho, soundspeed, viscosity.alpha of the neighbour).
+// LOOP 2 (with MODE 0): the time-step LIMITER loop -- FUNCTION = limiter in walks of the same shape
+//         (src/runner_doiact_functions_limiter.h:233-450, 541-680; "starting" is the same comparison
+//         time_bin <= max_active_bin, src/active.h:698-717, on the bins the time-step task has just
+//         given).  runner_iact_nonsym_limiter (src/timestep_limiter_iact.h:107-117) writes the
+//         NEIGHBOUR: wakeup[j] = max(wakeup[j], -time_bin_i) when time_bin_j > time_bin_i + 2.  No
+//         sums, nothing of the lane's own particle is written.
 // ---------------------------------------------------------------------------
 template <int MODE, bool FILT = false, int LOOP = 0>
 __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, int sweep, int force_slow = 0) {
@@ -848,7 +854,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
   const int total = by_ulist ? *d.unit_count
                              : (by_unit ? (ranged ? d.unit_hi : d.n_units) : (by_list ? d.leaf_count[sweep] : d.n_leaves));
   const int wid0 = ranged ? d.unit_lo : 0;
-  int *const work = d.work_ctr + (LOOP == 1 ? 2 + kc.max_iter : (MODE == 0 ? 0 : 1 + sweep));
+  int *const work = d.work_ctr + (LOOP >= 1 ? 2 + kc.max_iter : (MODE == 0 ? 0 : 1 + sweep));
   const Item *__restrict__ items = MODE == 0 ? d.items : d.redo_items;
   const bool rec = d.rec_capacity > 0;
   const float qnan = __int_as_float(0x7fc00000);
@@ -915,7 +921,8 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
       const long long idi = rec ? d.id[pp] : 0;
       DensAcc acc;
       acc.zero();
-      if (MODE == 0 && d.keep_sums && mine) {
+      const int bin_i = LOOP == 2 ? (int)d.time_bin[pp] : 0;
+      if (MODE == 0 && LOOP != 2 && d.keep_sums && mine) {
         const float4 s0 = d.dens0[p], s1 = d.dens1[p];
         acc.rho = s0.x; acc.rho_dh = s0.y; acc.wcount = s0.z; acc.wcount_dh = s0.w;
         acc.div_v = s1.x; acc.rx = s1.y; acc.ry = s1.z; acc.rz = s1.w;
@@ -982,7 +989,16 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
         // FILT: the sorted-axis cut is implied by r2 < h^2 gamma^2 unless r is within delta of the radius
         if (FILT && hit && !(r2 < r2safe))
           hit = dens_cut_exact_scan(cut_ctx(d), items, ib, ie, d.pos, w & kIdxMask, xi, yi, zi, hig);
-        if (hit) {
+        if (hit && LOOP == 2) {
+          const int j = w & kIdxMask;
+          const int bin_j = (int)d.time_bin[j];
+          bool wake = bin_j > bin_i + 2;  // time_bin_neighbour_max_delta_bin, src/timeline.h:51
+          // DOSELF1 (:641-660): two starting particles in each other's range meet in the symmetric
+          // runner_iact_limiter, which does nothing; the sorted pair walk knows no such case
+          if (wake && (w & kDpFlag) && bin_j <= kc.max_active_bin && r2 < sq_gamma2(d.h[j])) wake = false;
+          if (wake) atomicMax(&d.wakeup[j], -bin_i);
+          nhits++;
+        } else if (hit) {
           if (LOOP == 1) iact_gradient(gacc, r2, dx, dy, dz, hi, vmi, gi, vmj, gj);
           else iact_density(acc, r2, dx, dy, dz, hi_inv, vmi.x, vmi.y, vmi.z, vmj);
           nhits++;
@@ -1001,7 +1017,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
           if (ok) {
             const int w = __float_as_int(e.w);
             const int j = w & kIdxMask;
-            v = d.vm[j];
+            if (LOOP != 2) v = d.vm[j];
             if (LOOP == 1) g = d.gin[j];
             if (w & kDpFlag) load_pos(d.pos, j, x, y, z);
           }
@@ -1248,6 +1264,8 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
           d.v_sig[p] = gacc.v_sig;
           d.sph_grad[p] = make_float4(gacc.div_v, gacc.lap, gacc.amax, 0.f);
         }
+      } else if (LOOP == 2) {
+        // nothing of the lane's own particle changes
       } else if (mine) {
         d.dens0[p] = make_float4(acc.rho, acc.rho_dh, acc.wcount, acc.wcount_dh);
         d.dens1[p] = make_float4(acc.div_v, acc.rx, acc.ry, acc.rz);
@@ -1259,7 +1277,7 @@ __global__ void __launch_bounds__(kBlock, SWIFT_MINB_DENSITY) k_density(Dev d, i
     }
   }
   for (int o = 16; o > 0; o >>= 1) nhits += __shfl_down_sync(kFull, nhits, o);
-  if (lane == 0 && nhits) atomicAdd(&d.hits[LOOP == 1 ? 3 : MODE], nhits);
+  if (lane == 0 && nhits && LOOP != 2) atomicAdd(&d.hits[LOOP == 1 ? 3 : MODE], nhits);
 }
 
 // ---------------------------------------------------------------------------

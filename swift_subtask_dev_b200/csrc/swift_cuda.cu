@@ -102,6 +102,9 @@ struct swift_cuda_ctx {
   float *s_sph_in[3] = {};
   float *s_sph_out = nullptr;
   int grid_gradient = 0;
+  int grid_limiter = 0;        // the time-step limiter loop, k_density<0, false, 2>
+  float limiter_ms[2] = {0.f, 0.f};  // device time of the last limiter loop / k_limiter
+  int8_t *d_lim_tmp = nullptr; // n bytes: time bins in / wakeup out in caller order
   long long n_gradient = 0;
   int sph_prep_mode = 0;   // k_sphenix_prep: swift_cuda_step_parts calls that run without the ghost / the extra ghost
   int fast_qd = kQD;   // rows of the hit FIFO k_force_fast uses (SWIFT_CUDA_FAST_QD)
@@ -141,6 +144,8 @@ static void free_device(swift_cuda_ctx *c) {
   c->d_sort_need = nullptr;
   c->d_unit_list = nullptr;
   c->d_unit_count = nullptr;
+  c->dev.wakeup = nullptr;
+  c->d_lim_tmp = nullptr;
 }
 
 extern "C" void swift_cuda_destroy(swift_cuda_ctx *c);
@@ -545,8 +550,13 @@ static int pack_and_upload(swift_cuda_ctx *c, const swift_cuda_parts_in *in) {
     c->grid_redo = grid_for(o1, d.n_units);
     c->grid_force = grid_for(o2, d.n_units);
     c->grid_gradient = grid_for(o3, d.n_units);
+    int o4 = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o4, k_density<0, false, 2>, kBlock, 0));
+    c->grid_limiter = grid_for(o4, d.n_units);
     const size_t qwarps =
-        (size_t)std::max(std::max(c->grid_density, c->grid_gradient), std::max(c->grid_redo, c->grid_force)) * kWarps;
+        (size_t)std::max(std::max(std::max(c->grid_density, c->grid_gradient), c->grid_limiter),
+                         std::max(c->grid_redo, c->grid_force)) *
+        kWarps;
     // unit counters: [0] first density pass, [1 + sweep] redo sweeps, [1 + max_iter] force, [2 + max_iter] gradient
     if (dmalloc(c, &d.gq, qwarps * kQD * 32) || dmalloc(c, &d.work_ctr, (size_t)c->prm.max_smoothing_iterations + 3))
       return 1;
@@ -1978,6 +1988,75 @@ int swift_cuda_timestep(swift_cuda_ctx *c, long long *ti_end_min, long long *upd
   if (small > 0)
     return fail(std::to_string(small) + " particle(s) want a time-step below dt_min (" +
                 std::to_string(c->iprm.dt_min) + ")");
+  return 0;
+}
+
+// ---- the time-step limiter (swift --limiter): include/swift_cuda.h, "Time-step limiter" ----------------
+int swift_cuda_do_limiter_loop(swift_cuda_ctx *c, const signed char *time_bin, signed char *wakeup) {
+  NEED_BUILT(c);
+  Dev &d = c->dev;
+  const int64_t n = c->n;
+  if (d.wakeup == nullptr && (dmalloc(c, &d.wakeup, (size_t)std::max<int64_t>(n, 1)) ||
+                              dmalloc(c, &c->d_lim_tmp, (size_t)std::max<int64_t>(n, 1))))
+    return 1;
+  const int nb = (int)((n + 255) / 256);
+  const int32_t *order = c->tree.order.empty() ? nullptr : c->s_order;
+  if (time_bin != nullptr) {
+    // a caller that runs the time-step task itself hands the new bins over (caller order, all n)
+    if (c->integ_on) return fail("do_limiter_loop: in the time-integration mode the bins are those of swift_cuda_timestep");
+    if (c->n_io >= 0 && c->n_io < n) return fail("do_limiter_loop: not with a reduced transfer count (halo copies)");
+    CK(cudaMemcpyAsync(c->d_lim_tmp, time_bin, (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    if (n > 0) k_set_bins<<<nb, 256, 0, c->stream>>>(n, order, c->d_lim_tmp, const_cast<int8_t *>(d.time_bin), d.hb);
+    c->marks_fresh = false;
+  }
+  // the units that hold a starting particle: those that held an active one (a particle that was active gets a
+  // bin that starts now, make_integer_timestep; the others keep theirs); after swift_cuda_timestep the marks
+  // are taken again on the new bins
+  if (launch_mark(c)) return 1;
+  if (n > 0) k_wakeup_reset<<<nb, 256, 0, c->stream>>>(n, d.wakeup);
+  CK(cudaMemsetAsync(d.work_ctr + 2 + c->prm.max_smoothing_iterations, 0, sizeof(int), c->stream));
+  CK(cudaEventRecord(c->ev[0], c->stream));
+  if (d.n_units > 0) k_density<0, false, 2><<<c->grid_limiter, kBlock, 0, c->stream>>>(d, 0);
+  CK(cudaEventRecord(c->ev[5], c->stream));
+  c->counters.n_kernel_launches += 1;
+  CK(cudaGetLastError());
+  if (wakeup != nullptr) {
+    if (n > 0) k_scatter_wakeup<<<nb, 256, 0, c->stream>>>(n, order, d.wakeup, c->d_lim_tmp);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(wakeup, c->d_lim_tmp, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaEventElapsedTime(&c->limiter_ms[0], c->ev[0], c->ev[5]));
+  return 0;
+}
+
+int swift_cuda_do_limiter(swift_cuda_ctx *c, long long *ti_end_min, long long *limited) {
+  NEED_INTEG(c);
+  Dev &d = c->dev;
+  if (d.wakeup == nullptr) return fail("do_limiter: swift_cuda_do_limiter_loop has not run");
+  const unsigned long long big = (unsigned long long)kMaxNrTimesteps;
+  CK(cudaMemcpyAsync(c->integ.ti_end_min, &big, sizeof(big), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemsetAsync(c->integ.updated, 0, sizeof(unsigned long long), c->stream));
+  CK(cudaEventRecord(c->ev[0], c->stream));
+  c->marks_fresh = false;  // time bins change
+  if (c->n > 0) k_limiter<<<(int)((c->n + 255) / 256), 256, 0, c->stream>>>(d, c->integ, c->iprm);
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(c->ev[5], c->stream));
+  unsigned long long t = 0, u = 0;
+  CK(cudaMemcpyAsync(&t, c->integ.ti_end_min, sizeof(t), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(&u, c->integ.updated, sizeof(u), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaEventElapsedTime(&c->limiter_ms[1], c->ev[0], c->ev[5]));
+  if (ti_end_min) *ti_end_min = (long long)t;
+  if (limited) *limited = (long long)u;
+  return 0;
+}
+
+int swift_cuda_get_limiter_timings(swift_cuda_ctx *c, float ms[2]) {
+  NEED_BUILT(c);
+  if (!ms) return fail("get_limiter_timings: null argument");
+  ms[0] = c->limiter_ms[0];
+  ms[1] = c->limiter_ms[1];
   return 0;
 }
 

@@ -133,6 +133,20 @@ class Checker:
         assert rc == 0, "a particle wants a time-step below dt_min"
         return ti_end_min.value, updated.value
 
+    def limiter(self, s, wakeup, ti_current, max_active_bin):
+        """runner_do_limiter: timestep_limit_part for every particle with wakeup != -56; wakeup is reset in place.
+        Returns (earliest new end of step or max_nr_timesteps, number of limited particles)."""
+        assert wakeup.dtype == np.int8 and wakeup.flags["C_CONTIGUOUS"]
+        ti_end_min, limited = C.c_longlong(0), C.c_longlong(0)
+        fn = getattr(self.lib, self.pre + "limiter")
+        fn.restype = C.c_int
+        args = [C.byref(_ciparams(self.ip, ti_current, max_active_bin))]
+        if self.which == "oracle":
+            args.append(C.byref(self.eos))
+        rc = fn(*args, C.byref(_cstate(s)), wakeup.ctypes.data_as(_BP), C.byref(ti_end_min), C.byref(limited))
+        assert rc == 0
+        return ti_end_min.value, limited.value
+
 
 SPHENIX_STATE = (("alpha_visc", "e_alpha_visc"), ("alpha_diff", "e_alpha_diff"), ("div_v_prev", "e_div_v_prev"),
                  ("div_v_dt", "e_div_v_dt"), ("laplace_u", "e_laplace_u"))
@@ -167,9 +181,41 @@ def hydro_step(which, s, prm_kwargs, tree, max_active_bin, eos=None, variant="mi
     return o
 
 
-def run_loop(which, ic, prm_kwargs, ip, tree, nsteps, eos=None, variant="minimal", on_step=None, sphenix=None):
+NOT_AWAKE = -NUM_TIME_BINS   # time_bin_not_awake, src/timeline.h:48
+
+
+def limiter_loop(which, s, prm_kwargs, tree, max_active_bin, variant="minimal", mass=None, ids=None, h_build=None,
+                 sphenix=None):
+    """The tasks of subtype limiter (runner_do{self,pair}1_branch_limiter, runner_dosub_*1_limiter) on the state
+    after the time-step task: p->limiter_data.wakeup of every particle."""
+    cells, tasks, ntasks = tree
+    kw = dict(prm_kwargs)
+    kw["max_active_bin"] = max_active_bin
+    prm = ol.make_params(**kw)
+    ic = {"x": s["x"], "v": s["v"], "mass": mass, "h": s["h"], "u": s["u"], "id": ids, "time_bin": s["time_bin"],
+          "in_h_build": h_build, "l_time_bin": s["time_bin"], "l_only": True}
+    if s.get("mat_id") is not None:
+        ic["mat_id"] = s["mat_id"]
+    o = ol.run_step(which, prm, ic, cells, tasks, ntasks, record=False, variant=variant, sphenix=sphenix)
+    return o["l_wakeup"]
+
+
+def limiter_census(wake, time_bin, max_active_bin):
+    """(woken particles, of them inactive ones -- kick1 undone, src/timestep_limiter.h:87-215 --, of those the ones
+    whose new bin does not start now and that get their new kick1 on the spot, :188-207)."""
+    woken = wake != NOT_AWAKE
+    inactive = woken & (time_bin > max_active_bin)
+    rekicked = inactive & ((2 - wake.astype(np.int32)) > max_active_bin)
+    return int(woken.sum()), int(inactive.sum()), int(rekicked.sum())
+
+
+def run_loop(which, ic, prm_kwargs, ip, tree, nsteps, eos=None, variant="minimal", on_step=None, sphenix=None,
+             limiter=False):
     """The engine-step loop of the module docstring on the checker `which`.  ic is in CELL order (tree built on
-    it).  Returns the state dict and the per-step log [(ti_current, max_active_bin, updated, dx_max...)]."""
+    it).  Returns the state dict and the per-step log [(ti_current, max_active_bin, updated, dx_max...)].
+    limiter: the time-step limiter (swift --limiter) -- after the time-step task the limiter loop, then
+    runner_do_limiter, then kick1 (engine_maketasks.c: timestep -> limiter tasks -> timestep_limiter -> kick1);
+    the log entries gain limiter_census."""
     s = new_state(ic)
     n = len(s["h"])
     s["f"] = np.zeros(n, dtype=np.float32)
@@ -197,8 +243,15 @@ def run_loop(which, ic, prm_kwargs, ip, tree, nsteps, eos=None, variant="minimal
         if step > 0:
             chk.kick(s, 2, ti_current, mab)
         ti_end_min, updated = chk.timestep(s, ti_current, mab)
+        if limiter:
+            wake = limiter_loop(which, s, prm_kwargs, tree, mab, variant=variant, mass=mass, ids=ids, h_build=h_build,
+                                sphenix=sphenix)
+            lim = limiter_census(wake, s["time_bin"], mab)
+            t_lim, nlim = chk.limiter(s, wake, ti_current, mab)
+            assert nlim == lim[0]
+            ti_end_min = min(ti_end_min, t_lim)
         chk.kick(s, 1, ti_current, mab)
-        log.append((ti_current, mab, updated, dx[0], dx[1], ti_end_min))
+        log.append((ti_current, mab, updated, dx[0], dx[1], ti_end_min) + (lim if limiter else ()))
         if on_step is not None:
             on_step(step, s)
         ti_old, ti_current = ti_current, ti_end_min
@@ -224,7 +277,7 @@ def prepare(ic, prm_kwargs):
     return ics.permute(ic, order), (cells, tasks, nt)
 
 
-def run_loop_gpu(be, ic, ip, tree, nsteps, on_step=None, sphenix=False):
+def run_loop_gpu(be, ic, ip, tree, nsteps, on_step=None, sphenix=False, limiter=False):
     """The same loop through the C ABI: the particles go up once (build_from_cells) and stay on the
     device; per step only scalars (ti_end_min, dx_max) come back.  `be` is a HydroBackend created with
     max_active_bin = 56."""
@@ -245,8 +298,17 @@ def run_loop_gpu(be, ic, ip, tree, nsteps, on_step=None, sphenix=False):
         if step > 0:
             be.kick(2)
         ti_end_min, updated = be.timestep()
+        lim = ()
+        if limiter:
+            # the wake-up flags come back only for the census of the log; the device keeps its own
+            tb = be.state()["time_bin"]
+            wake = be.runner_do_limiter_loop(want_wakeup=True)
+            lim = limiter_census(wake, tb, mab)
+            t_lim, nlim = be.runner_do_limiter()
+            assert nlim == lim[0]
+            ti_end_min = min(ti_end_min, t_lim)
         be.kick(1)
-        log.append((ti_current, mab, updated, dx[0], dx[1], ti_end_min))
+        log.append((ti_current, mab, updated, dx[0], dx[1], ti_end_min) + lim)
         if on_step is not None:
             on_step(step, _gpu_state(be, sphenix))
         ti_old, ti_current = ti_current, ti_end_min

@@ -50,7 +50,8 @@ class Parts(C.Structure):
                 ("f_a", _FP), ("f_u_dt", _FP), ("f_h_dt", _FP), ("f_v_sig", _FP),
                 ("f_min_ngb_time_bin", C.POINTER(C.c_byte)),
                 ("in_rho", _FP), ("in_pressure", _FP), ("in_f", _FP), ("in_soundspeed", _FP), ("in_balsara", _FP),
-                ("in_h_build", _FP)]
+                ("in_h_build", _FP),
+                ("l_time_bin", C.POINTER(C.c_byte)), ("l_wakeup", C.POINTER(C.c_byte)), ("l_only", C.c_int)]
 
 
 class PairLog(C.Structure):
@@ -196,6 +197,8 @@ def run_step(which, prm, ic, cells, tasks, ntasks, record=False, pair_capacity=N
              sphenix=None):
     """ic: dict with x[n,3] f64, v[n,3], mass, h, u (f32), id (i64), optional mat_id, time_bin -- already in CELL ORDER.
     which: 'oracle' or 'ref'.  Returns dict of outputs (+ 'pairs', 'counts', 'ghost_sweeps').
+    ic["l_time_bin"] (int8, the bins after the time-step task): the time-step limiter loop runs after end_force and
+    out["l_wakeup"] is p->limiter_data.wakeup of every particle; with ic["l_only"] nothing but sort + that loop runs.
     sphenix: dict of the SPHENIX hydro_props (SPHENIX_PROPS keys; prm.scheme must be 2): runs the three-loop
     scheme; ic may hold in_alpha_visc / in_alpha_diff / in_div_v_prev; the outputs gain SPHENIX_OUT,
     counts[3] and pairs[3] (the gradient loop)."""
@@ -226,6 +229,11 @@ def run_step(which, prm, ic, cells, tasks, ntasks, record=False, pair_capacity=N
         if ic.get(k) is not None:
             setattr(P, k, arr(ic[k], np.float32).ctypes.data_as(_FP))
     out = {}
+    if ic.get("l_time_bin") is not None:
+        P.l_time_bin = arr(ic["l_time_bin"], np.int8).ctypes.data_as(C.POINTER(C.c_byte))
+        out["l_wakeup"] = np.zeros(n, dtype=np.int8)
+        P.l_wakeup = out["l_wakeup"].ctypes.data_as(C.POINTER(C.c_byte))
+        P.l_only = int(bool(ic.get("l_only")))
     for k, w in OUT_FIELDS.items():
         out[k] = np.zeros((n, w) if w > 1 else n, dtype=np.float32)
         setattr(P, k, out[k].ctypes.data_as(_FP))

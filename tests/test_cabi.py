@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
     for name in syms:
         assert hasattr(lib, name), "libswiftcuda.so does not export %s" % name
     assert sorted(be.EXPORTS) == syms, "backend.EXPORTS and include/swift_cuda.h disagree"
-    assert lib.swift_cuda_abi_version() == 3
+    assert lib.swift_cuda_abi_version() == 4
 
 
 def test_struct_layouts_match_ctypes_mirror():
