@@ -6,10 +6,11 @@ The CPU side of the same fixtures: tests/test_limiter_oracle.py.
 Each group of checks runs scripts/limiter_gpu_check.py in a process of its own, so that a device fault in this
 code cannot take the CUDA context of the remaining GPU tests with it.
 
-STATUS: this device code was written after the round's GPU budget had been spent; it compiles for sm_100a and
-the SASS of every kernel that existed before is unchanged, but at the time of the commit it
-had not run on hardware once.  The tests are therefore marked xfail(strict=False): the first run on a B200 reports
-XPASS where the device matches the reference bit for bit and XFAIL (with the script's output) where it does not,
+STATUS: this device code was written when the round's GPU budget was all but spent.  The last 19 seconds of it
+went to the "loop" group, which passed on a B200 at the first attempt (profiles/r02_limiter_loop_gpu.txt): that
+test is a plain test.  The other two groups (k_limiter inside the resident run, the refusals) had NOT run on
+hardware at the time of the commit; they are marked xfail(strict=False): their first run on a B200 reports XPASS
+where the device matches the reference bit for bit and XFAIL (with the script's output) where it does not,
 without stopping the tests collected after this file."""
 import os
 import subprocess
@@ -31,7 +32,6 @@ def _run(section):
 
 
 @pytest.mark.gpu
-@pytest.mark.xfail(strict=False, reason=FIRST_RUN)
 def test_limiter_loop_matches_reference_wakeup_flags():
     """swift_cuda_do_limiter_loop on three particle sets (deep tree with sub tasks, periodic wrap, everybody
     starting): p->limiter_data.wakeup of every particle equal to the reference's, with the bins on the device and
