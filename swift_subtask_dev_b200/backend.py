@@ -27,7 +27,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 def build_library(verbose=False, force=False):
     """Compiles the CUDA backend in-tree with nvcc for sm_100a."""
     srcs = [os.path.join(CSRC, f) for f in ("swift_cuda.cu", "host_tree.cpp")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.cuh", "leaf_kernels.cuh", "list_kernels.cuh", "force_fast.cuh", "integrate.cuh", "pack.cuh", "sphenix.cuh", "device_types.cuh", "host_tree.hpp")] + \
+    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.cuh", "leaf_kernels.cuh", "list_kernels.cuh", "force_fast.cuh", "integrate.cuh", "pack.cuh", "sphenix.cuh", "device_types.cuh", "limit_part.h", "host_tree.hpp")] + \
         [os.path.join(ROOT, "include", "swift_cuda.h")]
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
         return LIB_PATH

@@ -18,6 +18,7 @@
 // and operand order, products with the double time steps in f64, so the results are bit-identical.
 #pragma once
 #include "kernels.cuh"
+#include "limit_part.h"
 
 namespace swiftcuda {
 
@@ -258,70 +259,52 @@ __global__ void k_timestep(Dev d, IntegDev g, IntegPrm ip) {
   }
 }
 
-// One kick_part over dt on registers (the arithmetic of k_kick): xp->v_full, xp->u_full; at the energy floor
-// p->u_dt becomes 0 (dirty: the acceleration record has to be written back).
-__device__ __forceinline__ void kick_regs(float4 &vf, float4 &acc, double dt, float energy_min, bool &dirty) {
-  vf.x = kick_f(vf.x, acc.x, dt);
-  vf.y = kick_f(vf.y, acc.y, dt);
-  vf.z = kick_f(vf.z, acc.z, dt);
-  const float delta_u = __fmul_rn(acc.w, (float)dt);
-  const float ua = __fadd_rn(vf.w, delta_u), ub = __fmul_rn(0.5f, vf.w);
-  vf.w = ua > ub ? ua : ub;
-  if (vf.w < energy_min) {
-    vf.w = energy_min;
-    acc.w = 0.f;
-    dirty = true;
-  }
-}
-
 // runner_do_limiter on every particle the limiter loop woke (Dev::wakeup != time_bin_not_awake):
-// timestep_limit_part, src/timestep_limiter.h:67-217.  An ACTIVE particle only takes the bin -wakeup + 2
-// for the step that starts now.  An INACTIVE one is in the middle of a step of its old bin: its kick1 is
-// undone (negative dt), it is kicked from the old beginning to the beginning of the new, shorter step that
-// contains ti_current, and -- when that bin does not start now, so that the kick task will not see the
-// particle -- given the first half-kick of the new step on the spot.  The reference finds the new beginning
-// with `while (ti_beg_old + k * dti_new <= ti_current) k++` (:112-115); here the quotient is taken.
+// timestep_limit_part, src/timestep_limiter.h:67-217, whose arithmetic is limit_part() of limit_part.h -- plain
+// C++ on scalars, so that the same source also compiles for the host, where tests/test_limiter_oracle.py holds
+// it against the reference's fixture.  An ACTIVE particle only takes the bin -wakeup + 2 for the step that
+// starts now.  An INACTIVE one is in the middle of a step of its old bin: its kick1 is undone (negative dt), it
+// is kicked from the old beginning to the beginning of the new, shorter step that contains ti_current, and --
+// when that bin does not start now, so that the kick task will not see the particle -- given the first
+// half-kick of the new step on the spot.  One thread per particle, HBM-bound like k_kick.
 __global__ void k_limiter(Dev d, IntegDev g, IntegPrm ip) {
   const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   long long t_end = kMaxNrTimesteps;
   int lim = 0;
   if (p < d.n) {
     const int wake = d.wakeup[p];
-    if (wake != -kNumTimeBins) {
+    if (wake != kLpNotAwake) {
       lim = 1;
-      const int old_bin = d.time_bin[p];
-      const int new_bin = (signed char)(-wake + 2);
-      if (old_bin <= kc.max_active_bin) {
-        t_end = ip.ti_current + int_timestep(new_bin);
-      } else {
-        const long long ti_beg_old = int_time_begin(ip.ti_current, old_bin);
-        const long long ti_end_old = int_time_end(ip.ti_current, old_bin);
-        const long long dti_old = ti_end_old - ti_beg_old;
-        const long long dti_new = int_timestep(new_bin);
-        const long long ti_beg_new = ti_beg_old + ((ip.ti_current - ti_beg_old) / dti_new) * dti_new;
-        const long long ti_end_half_old = ti_beg_old + dti_old / 2;
-        const long long ti_end_half_new = ti_beg_new + dti_new / 2;
-        const bool planetary = kc.scheme == SWIFT_CUDA_SCHEME_PLANETARY;
-        const float energy_min = planetary ? ip.min_u : (ip.min_u > 0.f ? ip.min_u : 0.f);
-        float4 acc = d.acc[p];
-        float4 vf = g.vu_full[p];
-        bool dirty = false;
-        kick_regs(vf, acc, -__dmul_rn((double)(ti_end_half_old - ti_beg_old), ip.time_base), energy_min, dirty);
-        kick_regs(vf, acc, __dmul_rn((double)(ti_beg_new - ti_beg_old), ip.time_base), energy_min, dirty);
-        if (new_bin > kc.max_active_bin) {
-          kick_regs(vf, acc, __dmul_rn((double)(ti_end_half_new - ti_beg_new), ip.time_base), energy_min, dirty);
-          t_end = ti_beg_new + dti_new;
-        } else {
-          t_end = ip.ti_current + int_timestep(new_bin);
-        }
-        g.vu_full[p] = vf;
-        if (dirty) d.acc[p] = acc;
+      LimitEnv e;
+      e.ti_current = ip.ti_current;
+      e.time_base = ip.time_base;
+      e.max_active_bin = kc.max_active_bin;
+      const bool planetary = kc.scheme == SWIFT_CUDA_SCHEME_PLANETARY;
+      e.energy_min = planetary ? ip.min_u : (ip.min_u > 0.f ? ip.min_u : 0.f);
+      int bin = d.time_bin[p];
+      const bool inactive = bin > kc.max_active_bin;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f), vf4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (inactive) {
+        acc = d.acc[p];
+        vf4 = g.vu_full[p];
       }
-      const_cast<int8_t *>(d.time_bin)[p] = (int8_t)new_bin;
+      float vf[4] = {vf4.x, vf4.y, vf4.z, vf4.w};
+      const float a[3] = {acc.x, acc.y, acc.z};
+      float u_dt = acc.w;
+      bool dirty = false;
+      t_end = limit_part(e, wake, bin, vf, a, u_dt, dirty);
+      if (inactive) {
+        g.vu_full[p] = make_float4(vf[0], vf[1], vf[2], vf[3]);
+        if (dirty) {
+          acc.w = u_dt;
+          d.acc[p] = acc;
+        }
+      }
+      const_cast<int8_t *>(d.time_bin)[p] = (int8_t)bin;
       float4 hb = d.hb[p];
-      hb.z = __int_as_float(new_bin);
+      hb.z = __int_as_float(bin);
       d.hb[p] = hb;
-      d.wakeup[p] = -kNumTimeBins;
+      d.wakeup[p] = kLpNotAwake;
     }
   }
   for (int o = 16; o > 0; o >>= 1) {

@@ -226,3 +226,75 @@ def test_oracle_run_with_limiter_vs_compiled_reference_live():
     assert sum(l[6] for l in lr) > 0, "nobody was woken: the case does not exercise the limiter"
     for k in il.STATE_KEYS:
         assert np.array_equal(sr[k], so[k]), k
+
+
+# ---- the body of the device kernel k_limiter, compiled for the host ---------------------------------------
+@pytest.fixture(scope="module")
+def kernel_body(tmp_path_factory):
+    """swift_subtask_dev_b200/csrc/limit_part.h -- the source nvcc compiles into k_limiter -- built by g++ without
+    contraction behind tests/host_kernels/limit_part_host.cpp."""
+    import ctypes as C
+    import subprocess
+    here = os.path.dirname(os.path.abspath(__file__))
+    so = str(tmp_path_factory.mktemp("host_kernels") / "liblimitpart.so")
+    subprocess.run(["g++", "-O2", "-ffp-contract=off", "-fno-fast-math", "-shared", "-fPIC", "-o", so,
+                    os.path.join(here, "host_kernels", "limit_part_host.cpp")], check=True)
+    lib = C.CDLL(so)
+    lib.limit_parts_host.argtypes = [C.c_int, C.c_longlong, C.c_double, C.c_int, C.c_float] + [C.c_void_p] * 8
+    lib.limit_parts_host.restype = C.c_int
+
+    def run(s, wake, ti_current, mab, ip):
+        import ctypes as C
+        t, u = C.c_longlong(0), C.c_longlong(0)
+        energy_min = max(np.float32(ip["minimal_internal_energy"]), np.float32(0.0))
+        rc = lib.limit_parts_host(len(s["h"]), ti_current, ip["time_base"], mab, float(energy_min), wake.ctypes.data,
+                                  s["time_bin"].ctypes.data, s["v_full"].ctypes.data, s["u_full"].ctypes.data,
+                                  s["a"].ctypes.data, s["u_dt"].ctypes.data, C.addressof(t), C.addressof(u))
+        assert rc == 0
+        return t.value, u.value
+    return run
+
+
+def test_kernel_body_on_the_host_reproduces_reference_golden(kernel_body):
+    z = np.load(os.path.join(GOLD, "apply_sedov14.npz"))
+    ti_current, mab, t_end, nlim = (int(v) for v in z["scalars"])
+    ip = gen().RUN_CASES["run_sedov14"][2]
+    s = {k: np.ascontiguousarray(z["before_" + k]).copy() for k in il.STATE_KEYS}
+    wake = z["wake"].copy()
+    assert kernel_body(s, wake, ti_current, mab, ip) == (t_end, nlim)
+    assert (wake == il.NOT_AWAKE).all()
+    for k in il.STATE_KEYS:
+        assert np.array_equal(s[k], z["after_" + k]), k
+
+
+def test_kernel_body_on_the_host_vs_oracle_at_the_energy_floor(kernel_body):
+    """Strongly cooling particles: undoing a kick cannot take u_full below half (hydro_kick_extra), and with a
+    minimal internal energy u_dt is zeroed on the way -- the later kicks of the same call then see u_dt = 0."""
+    z = np.load(os.path.join(GOLD, "apply_sedov14.npz"))
+    ti_current, mab = int(z["scalars"][0]), int(z["scalars"][1])
+    ip = dict(gen().RUN_CASES["run_sedov14"][2])
+    rng = np.random.default_rng(3)
+    base = {k: np.ascontiguousarray(z["before_" + k]).copy() for k in il.STATE_KEYS}
+    n = len(base["h"])
+    dt_old = (1 << (base["time_bin"].astype(np.int64) + 1)) * ip["time_base"]
+    # |u_dt| * dt comparable with u_full, either sign
+    base["u_dt"] = (rng.uniform(-4.0, 4.0, n) * base["u_full"] / dt_old).astype(np.float32)
+    ip["minimal_internal_energy"] = float(np.median(base["u_full"]))
+    a = {k: v.copy() for k, v in base.items()}
+    b = {k: v.copy() for k, v in base.items()}
+    b["min_ngb_time_bin"] = np.full(n, il.NUM_TIME_BINS + 1, dtype=np.int8)
+    b["mat_id"] = None
+    wa, wb = z["wake"].copy(), z["wake"].copy()
+    ra = kernel_body(a, wa, ti_current, mab, ip)
+    rb = il.Checker("oracle", ip).limiter(b, wb, ti_current, mab)
+    assert ra == rb
+    for k in il.STATE_KEYS:
+        assert np.array_equal(a[k], b[k]), k
+    assert (a["u_dt"] == 0).sum() > (base["u_dt"] == 0).sum() + 50, "the floor was not reached"
+    if ol.ref_available("minimal"):
+        c = {k: v.copy() for k, v in base.items()}
+        c["min_ngb_time_bin"], c["mat_id"] = b["min_ngb_time_bin"], None
+        wc = z["wake"].copy()
+        assert il.Checker("ref", ip).limiter(c, wc, ti_current, mab) == ra
+        for k in il.STATE_KEYS:
+            assert np.array_equal(a[k], c[k]), k + " (compiled reference)"
