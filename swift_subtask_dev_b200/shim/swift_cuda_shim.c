@@ -451,6 +451,27 @@ void swift_cuda_shim_step(struct engine *e, int resort) {
   refresh_hmax(&shim_flat, e);
 }
 
+/* With engine_policy_timestep_limiter (swift --limiter): once per step AFTER the time-step tasks, in place of the
+ * tasks of subtype limiter (runner_do{self,pair}1_branch_limiter, runner_dosub_{self,pair}1_limiter,
+ * src/runner_main.c:205-206, 255-256, 303-304, 349-350), which the scheduler leaves skipped like the other
+ * loops.  The new time bins go up (1 byte per particle), the limiter loop runs on the positions, smoothing
+ * lengths and sorts swift_cuda_shim_step left on the device, and p->limiter_data.wakeup comes back (1 byte per
+ * particle) for the reference's own runner_do_limiter tasks (src/runner_time_integration.c:1324), which stay
+ * where they are. */
+void swift_cuda_shim_limiter(struct engine *e) {
+  if (shim_ctx == NULL) error("swift_cuda_shim_limiter before swift_cuda_shim_rebuild");
+  struct space *s = e->s;
+  const size_t n = s->nr_parts;
+  signed char *bins = (signed char *)malloc(2 * n + 2);
+  if (bins == NULL) error("Can't allocate the time-bin buffer.");
+  signed char *wake = bins + n;
+  for (size_t k = 0; k < n; k++) bins[k] = s->parts[k].time_bin;
+  CUDA_OK(swift_cuda_do_limiter_loop(shim_ctx, bins, wake));
+  for (size_t k = 0; k < n; k++)
+    if (wake[k] > s->parts[k].limiter_data.wakeup) s->parts[k].limiter_data.wakeup = wake[k]; /* accumulate_max_c */
+  free(bins);
+}
+
 void swift_cuda_shim_clean(void) {
   if (shim_ctx != NULL) swift_cuda_destroy(shim_ctx);
   shim_ctx = NULL;
