@@ -433,6 +433,58 @@ int swift_cuda_do_limiter(swift_cuda_ctx *ctx, long long *ti_end_min, long long 
 /* Device time of the last limiter loop and the last swift_cuda_do_limiter, ms. */
 int swift_cuda_get_limiter_timings(swift_cuda_ctx *ctx, float ms[2]);
 
+/* ---- Table equations of state of the Planetary scheme -----------------------
+ * Replaces, for materials that live in tables,
+ *   load_table_SESAME / prepare_table_SESAME / convert_units_SESAME   src/equation_of_state/planetary/sesame.h:149-352
+ *   load_table_HM80 / prepare_table_HM80 / convert_units_HM80         planetary/hm80.h:76-178
+ *   SESAME_{pressure,soundspeed}_from_internal_energy                 sesame.h:480-594, 605-721
+ *   HM80_{pressure,soundspeed}_from_internal_energy                   hm80.h:224-300
+ * as called by gas_pressure_from_internal_energy / gas_soundspeed_from_internal_energy of the planetary
+ * dispatcher (planetary/equation_of_state.h:910-1146, 1305-1457) from hydro_prepare_force, the drift and kick2.
+ * SESAME-style tables serve SESAME iron / basalt / water (mat_id 300-302), SS08 water (303), ANEOS forsterite /
+ * iron / Fe85Si15 (400-402) and custom materials (900-909); HM80 tables HHe / ice / rock (200-202).
+ * The reference's table FILES are not part of its tree (examples/Planetary/EoSTables/get_eos_tables.sh downloads
+ * them): parity is pinned on synthetic tables in the reference's file formats, read by the reference's own
+ * loaders and evaluated by its own functions (tests/test_eos_tables.py). */
+typedef struct {
+  int kind;              /* 1 SESAME-style, 2 HM80 */
+  int mat_id;            /* enum eos_planetary_material_id */
+  int num_rho, num_T;    /* SESAME: without the rho = 0 / T = 0 entries of the file; HM80: num_rho, num_u */
+  float *log_rho;        /* SESAME [num_rho]: log(rho), internal units */
+  float *log_u;          /* SESAME [num_rho][num_T]: log(u) */
+  float *P;              /* SESAME [num_rho][num_T]: P; HM80 [num_rho][num_u]: log(P) */
+  float *c;              /* SESAME [num_rho][num_T]: sound speed */
+  float P_tiny, c_tiny;  /* SESAME */
+  float log_rho_min, log_rho_step, inv_log_rho_step; /* HM80 */
+  float log_u_min, log_u_step, inv_log_u_step;       /* HM80 */
+  float bulk_mod, P_min_for_c_min;                   /* HM80 */
+} swift_cuda_eos_table;
+
+/* units_cgs_conversion_factor(&si, X) / units_cgs_conversion_factor(us, X) for X = UNIT_CONV_DENSITY,
+ * _ENERGY_PER_UNIT_MASS, _PRESSURE, _SPEED, as the caller's unit system gives them (doubles: the tables are
+ * scaled in the reference's operand order, float *= double and float += logf(double)). */
+typedef struct {
+  double density, energy_per_unit_mass, pressure, speed;
+} swift_cuda_eos_units;
+
+/* Host only (no GPU needed).  Read a table file in the reference's text format and make it what the reference
+ * holds after load + prepare + convert_units.  version_date: what set_<material> expects (20220714 for the
+ * SESAME / ANEOS materials, 0 = any for custom ones; 20201003 for HM80, whose bulk modulus and P_min_for_c_min
+ * follow from mat_id as in set_HM80_*).  The arrays belong to the table: swift_cuda_eos_table_free. */
+int swift_cuda_eos_table_load_sesame(const char *path, int mat_id, int version_date, const swift_cuda_eos_units *units,
+                                     swift_cuda_eos_table *out);
+int swift_cuda_eos_table_load_hm80(const char *path, int mat_id, const swift_cuda_eos_units *units,
+                                   swift_cuda_eos_table *out);
+/* The same table as one flat little-endian binary file (64-byte header, then the float arrays): what a
+ * production run reads instead of parsing 1e6 numbers of text at every start. */
+int swift_cuda_eos_table_write_bin(const char *path, const swift_cuda_eos_table *table);
+int swift_cuda_eos_table_read_bin(const char *path, swift_cuda_eos_table *out);
+void swift_cuda_eos_table_free(swift_cuda_eos_table *table);
+/* Copies the table to the context's device (at most 8 tables per context, Planetary scheme only); particles
+ * whose mat_id equals the table's are evaluated from it from then on.  A particle whose material is neither
+ * an ideal gas, a Tillotson material of swift_cuda_params nor a table set here makes the step fail. */
+int swift_cuda_set_eos_table(swift_cuda_ctx *ctx, const swift_cuda_eos_table *table);
+
 /* ---- SPHENIX: the gradient loop and the extra ghost -------------------------
  * params.scheme = SWIFT_CUDA_SCHEME_SPHENIX (+ ideal gas) turns the step into the reference's
  * EXTRA_HYDRO_LOOP subgraph (src/engine_maketasks.c:2306-2317, src/runner_main.c:199-200, 249-250,

@@ -123,6 +123,32 @@ int ref_sizeof_part(void);
  * examples/Planetary/EarthImpact/earth_impact.yml:2-7). Returns 0 when compiled in. */
 int ref_get_eos(oracle_eos *out);
 
+/* ---- table equations of state of the Planetary scheme (libswiftref_planetary.so only) ----
+ * One material's table as the reference holds it after load_table_* + prepare_table_* + convert_units_*
+ * (src/equation_of_state/planetary/sesame.h:149-352, hm80.h:76-178), internal units of ref_get_eos.  Pointers
+ * are into the reference's own arrays. */
+typedef struct {
+  int kind;                 /* 1 SESAME-style (SESAME, SS08, ANEOS, custom), 2 HM80 */
+  int mat_id;
+  int num_rho, num_T;       /* HM80: num_rho, num_u */
+  const float *log_rho;     /* SESAME [num_rho] */
+  const float *log_u;       /* SESAME [num_rho][num_T] */
+  const float *P;           /* SESAME P [num_rho][num_T]; HM80 log P [num_rho][num_u] */
+  const float *c;           /* SESAME [num_rho][num_T] */
+  float P_tiny, c_tiny;
+  float log_rho_min, log_rho_step, inv_log_rho_step, log_u_min, log_u_step, inv_log_u_step;
+  float bulk_mod, P_min_for_c_min;
+} oracle_eos_table;
+/* what eos_init does for EoS:planetary_use_<material> = 1 with EoS:planetary_<material>_table_file = path
+ * (src/equation_of_state/planetary/equation_of_state.h:1629-1745); mat_id: 200-202, 300-303, 400-402, 900-909 */
+int ref_eos_table_load(int mat_id, const char *path);
+/* units_cgs_conversion_factor(&si, X) / units_cgs_conversion_factor(us, X) for X = density, energy per unit mass,
+ * pressure, speed in the harness' unit system: what convert_units_* scale the tables with */
+int ref_eos_unit_ratios(double out[4]);
+int ref_eos_table_get(int mat_id, oracle_eos_table *out);
+/* gas_pressure_from_internal_energy / gas_soundspeed_from_internal_energy (rho[k], u[k], mat_id) */
+int ref_eos_table_eval(int mat_id, int n, const float *rho, const float *u, float *P, float *c);
+
 /* The cell tree and the hydro task list of a particle set by the reference's OWN space_regrid,
  * space_split_recursive, engine_make_hydroloop_tasks_mapper and scheduler_splittasks (oracle/ref_tree.c).
  * order[k] = input index of the particle at cell-order slot k; arrays are malloc'ed (free()). */

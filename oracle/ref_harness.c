@@ -807,9 +807,126 @@ int ref_get_eos(oracle_eos *out) {
   for (int k = 0; k < 4; k++) out->idg_gamma[k] = eos.idg_def.gamma;
   return 0;
 }
+
+/* ---- table materials: the reference's own loaders and interpolation ---- */
+static struct SESAME_params *sesame_slot(int mat_id) {
+  switch (mat_id) {
+    case eos_planetary_id_SESAME_iron: return &eos.SESAME_iron;
+    case eos_planetary_id_SESAME_basalt: return &eos.SESAME_basalt;
+    case eos_planetary_id_SESAME_water: return &eos.SESAME_water;
+    case eos_planetary_id_SS08_water: return &eos.SS08_water;
+    case eos_planetary_id_ANEOS_forsterite: return &eos.ANEOS_forsterite;
+    case eos_planetary_id_ANEOS_iron: return &eos.ANEOS_iron;
+    case eos_planetary_id_ANEOS_Fe85Si15: return &eos.ANEOS_Fe85Si15;
+    default:
+      if (mat_id >= 900 && mat_id < 910) return &eos.custom[mat_id - 900];
+      return NULL;
+  }
+}
+static struct HM80_params *hm80_slot(int mat_id) {
+  switch (mat_id) {
+    case eos_planetary_id_HM80_HHe: return &eos.HM80_HHe;
+    case eos_planetary_id_HM80_ice: return &eos.HM80_ice;
+    case eos_planetary_id_HM80_rock: return &eos.HM80_rock;
+    default: return NULL;
+  }
+}
+
+int ref_eos_table_load(int mat_id, const char *path) {
+  ref_planetary_eos_init();
+  struct unit_system us;
+  units_init(&us, 1e27, 1e8, 1.0, 1.0, 1.0);
+  char file[1024];
+  strncpy(file, path, sizeof(file) - 1);
+  file[sizeof(file) - 1] = 0;
+  struct HM80_params *h = hm80_slot(mat_id);
+  if (h != NULL) {
+    if (mat_id == eos_planetary_id_HM80_HHe) set_HM80_HHe(h, mat_id);
+    else if (mat_id == eos_planetary_id_HM80_ice) set_HM80_ice(h, mat_id);
+    else set_HM80_rock(h, mat_id);
+    load_table_HM80(h, file);
+    prepare_table_HM80(h);
+    convert_units_HM80(h, &us);
+    return 0;
+  }
+  struct SESAME_params *m = sesame_slot(mat_id);
+  if (m == NULL) return 1;
+  switch (mat_id) {
+    case eos_planetary_id_SESAME_iron: set_SESAME_iron(m, mat_id); break;
+    case eos_planetary_id_SESAME_basalt: set_SESAME_basalt(m, mat_id); break;
+    case eos_planetary_id_SESAME_water: set_SESAME_water(m, mat_id); break;
+    case eos_planetary_id_SS08_water: set_SS08_water(m, mat_id); break;
+    case eos_planetary_id_ANEOS_forsterite: set_ANEOS_forsterite(m, mat_id); break;
+    case eos_planetary_id_ANEOS_iron: set_ANEOS_iron(m, mat_id); break;
+    case eos_planetary_id_ANEOS_Fe85Si15: set_ANEOS_Fe85Si15(m, mat_id); break;
+    default: set_custom(m, mat_id); break;
+  }
+  load_table_SESAME(m, file);
+  prepare_table_SESAME(m);
+  convert_units_SESAME(m, &us);
+  return 0;
+}
+
+int ref_eos_unit_ratios(double out[4]) {
+  struct unit_system us, si;
+  units_init(&us, 1e27, 1e8, 1.0, 1.0, 1.0);
+  units_init_si(&si);
+  out[0] = units_cgs_conversion_factor(&si, UNIT_CONV_DENSITY) / units_cgs_conversion_factor(&us, UNIT_CONV_DENSITY);
+  out[1] = units_cgs_conversion_factor(&si, UNIT_CONV_ENERGY_PER_UNIT_MASS) /
+           units_cgs_conversion_factor(&us, UNIT_CONV_ENERGY_PER_UNIT_MASS);
+  out[2] = units_cgs_conversion_factor(&si, UNIT_CONV_PRESSURE) / units_cgs_conversion_factor(&us, UNIT_CONV_PRESSURE);
+  out[3] = units_cgs_conversion_factor(&si, UNIT_CONV_SPEED) / units_cgs_conversion_factor(&us, UNIT_CONV_SPEED);
+  return 0;
+}
+
+int ref_eos_table_get(int mat_id, oracle_eos_table *o) {
+  bzero(o, sizeof(*o));
+  o->mat_id = mat_id;
+  const struct HM80_params *h = hm80_slot(mat_id);
+  if (h != NULL) {
+    if (h->table_log_P_rho_u == NULL) return 2;
+    o->kind = 2;
+    o->num_rho = h->num_rho;
+    o->num_T = h->num_u;
+    o->P = h->table_log_P_rho_u;
+    o->log_rho_min = h->log_rho_min; o->log_rho_step = h->log_rho_step; o->inv_log_rho_step = h->inv_log_rho_step;
+    o->log_u_min = h->log_u_min; o->log_u_step = h->log_u_step; o->inv_log_u_step = h->inv_log_u_step;
+    o->bulk_mod = h->bulk_mod; o->P_min_for_c_min = h->P_min_for_c_min;
+    return 0;
+  }
+  const struct SESAME_params *m = sesame_slot(mat_id);
+  if (m == NULL) return 1;
+  if (m->table_log_rho == NULL) return 2;
+  o->kind = 1;
+  o->num_rho = m->num_rho;
+  o->num_T = m->num_T;
+  o->log_rho = m->table_log_rho;
+  o->log_u = m->table_log_u_rho_T;
+  o->P = m->table_P_rho_T;
+  o->c = m->table_c_rho_T;
+  o->P_tiny = m->P_tiny;
+  o->c_tiny = m->c_tiny;
+  return 0;
+}
+
+int ref_eos_table_eval(int mat_id, int n, const float *rho, const float *u, float *P, float *c) {
+  ref_planetary_eos_init();
+  for (int k = 0; k < n; k++) {
+    P[k] = gas_pressure_from_internal_energy(rho[k], u[k], (enum eos_planetary_material_id)mat_id);
+    c[k] = gas_soundspeed_from_internal_energy(rho[k], u[k], (enum eos_planetary_material_id)mat_id);
+  }
+  return 0;
+}
 #else
 int ref_get_eos(oracle_eos *out) {
   (void)out;
+  return 1;
+}
+int ref_eos_table_load(int mat_id, const char *path) { (void)mat_id; (void)path; return 1; }
+int ref_eos_unit_ratios(double out[4]) { (void)out; return 1; }
+int ref_eos_table_get(int mat_id, oracle_eos_table *o) { (void)mat_id; (void)o; return 1; }
+int ref_eos_table_eval(int mat_id, int n, const float *rho, const float *u, float *P, float *c) {
+  (void)mat_id; (void)n; (void)rho; (void)u; (void)P; (void)c;
   return 1;
 }
 #endif

@@ -26,8 +26,8 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 def build_library(verbose=False, force=False):
     """Compiles the CUDA backend in-tree with nvcc for sm_100a."""
-    srcs = [os.path.join(CSRC, f) for f in ("swift_cuda.cu", "host_tree.cpp")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.cuh", "leaf_kernels.cuh", "list_kernels.cuh", "force_fast.cuh", "integrate.cuh", "pack.cuh", "sphenix.cuh", "device_types.cuh", "limit_part.h", "host_tree.hpp")] + \
+    srcs = [os.path.join(CSRC, f) for f in ("swift_cuda.cu", "host_tree.cpp", "eos_loader.cpp")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.cuh", "leaf_kernels.cuh", "list_kernels.cuh", "force_fast.cuh", "integrate.cuh", "pack.cuh", "sphenix.cuh", "device_types.cuh", "limit_part.h", "eos_table.h", "host_tree.hpp")] + \
         [os.path.join(ROOT, "include", "swift_cuda.h")]
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
         return LIB_PATH
@@ -140,7 +140,51 @@ EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error
            "swift_cuda_set_max_active_bin", "swift_cuda_timestep_static",
            "swift_cuda_sphenix_set_props", "swift_cuda_sphenix_set_state", "swift_cuda_sphenix_get_results",
            "swift_cuda_sphenix_get_counter", "swift_cuda_do_gradient", "swift_cuda_do_extra_ghost",
-           "swift_cuda_do_limiter_loop", "swift_cuda_do_limiter", "swift_cuda_get_limiter_timings"]
+           "swift_cuda_do_limiter_loop", "swift_cuda_do_limiter", "swift_cuda_get_limiter_timings",
+           "swift_cuda_eos_table_load_sesame", "swift_cuda_eos_table_load_hm80", "swift_cuda_eos_table_write_bin",
+           "swift_cuda_eos_table_read_bin", "swift_cuda_eos_table_free", "swift_cuda_set_eos_table"]
+
+
+class EosTable(C.Structure):
+    # field order must match swift_cuda_eos_table
+    _fields_ = [("kind", C.c_int), ("mat_id", C.c_int), ("num_rho", C.c_int), ("num_T", C.c_int),
+                ("log_rho", C.POINTER(C.c_float)), ("log_u", C.POINTER(C.c_float)), ("P", C.POINTER(C.c_float)),
+                ("c", C.POINTER(C.c_float)), ("P_tiny", C.c_float), ("c_tiny", C.c_float),
+                ("log_rho_min", C.c_float), ("log_rho_step", C.c_float), ("inv_log_rho_step", C.c_float),
+                ("log_u_min", C.c_float), ("log_u_step", C.c_float), ("inv_log_u_step", C.c_float),
+                ("bulk_mod", C.c_float), ("P_min_for_c_min", C.c_float)]
+
+
+class EosUnits(C.Structure):
+    # field order must match swift_cuda_eos_units
+    _fields_ = [("density", C.c_double), ("energy_per_unit_mass", C.c_double), ("pressure", C.c_double),
+                ("speed", C.c_double)]
+
+
+def load_eos_table(path, mat_id, units, version_date=None):
+    """Host only.  Reads a table file in the reference's text format (HM80 for mat_id 200-202, SESAME-style
+    otherwise) or, for a path ending in .bin, the library's flat binary form.  units: EosUnits or a 4-tuple
+    (density, energy per unit mass, pressure, speed: SI value / internal value).  Returns an EosTable whose arrays
+    belong to the library (free_eos_table)."""
+    lib = load_library()
+    t = EosTable()
+    if not isinstance(units, EosUnits):
+        units = EosUnits(*[float(v) for v in units])
+    if path.endswith(".bin"):
+        rc = lib.swift_cuda_eos_table_read_bin(path.encode(), C.byref(t))
+    elif 200 <= mat_id < 300:
+        rc = lib.swift_cuda_eos_table_load_hm80(path.encode(), mat_id, C.byref(units), C.byref(t))
+    else:
+        if version_date is None:
+            version_date = 0 if mat_id >= 900 else 20220714   # set_custom / set_SESAME_*, set_ANEOS_* (sesame.h:56-106)
+        rc = lib.swift_cuda_eos_table_load_sesame(path.encode(), mat_id, version_date, C.byref(units), C.byref(t))
+    if rc != 0:
+        raise SwiftCudaError(lib.swift_cuda_last_error().decode())
+    return t
+
+
+def free_eos_table(t):
+    load_library().swift_cuda_eos_table_free(C.byref(t))
 
 
 class SphenixProps(C.Structure):
@@ -274,6 +318,13 @@ def load_library():
             getattr(lib, name).argtypes = [C.c_void_p, C.c_void_p]
         lib.swift_cuda_do_gradient.argtypes = [C.c_void_p]
         lib.swift_cuda_do_extra_ghost.argtypes = [C.c_void_p]
+        lib.swift_cuda_eos_table_load_sesame.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        lib.swift_cuda_eos_table_load_hm80.argtypes = [C.c_char_p, C.c_int, C.c_void_p, C.c_void_p]
+        lib.swift_cuda_eos_table_write_bin.argtypes = [C.c_char_p, C.c_void_p]
+        lib.swift_cuda_eos_table_read_bin.argtypes = [C.c_char_p, C.c_void_p]
+        lib.swift_cuda_eos_table_free.argtypes = [C.c_void_p]
+        lib.swift_cuda_eos_table_free.restype = None
+        lib.swift_cuda_set_eos_table.argtypes = [C.c_void_p, C.c_void_p]
         lib.swift_cuda_do_limiter_loop.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         lib.swift_cuda_do_limiter.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         lib.swift_cuda_get_limiter_timings.argtypes = [C.c_void_p, C.c_void_p]
@@ -574,6 +625,11 @@ class HydroBackend:
         t, u = C.c_longlong(0), C.c_longlong(0)
         self._check(self.lib.swift_cuda_timestep(self.ctx, C.byref(t), C.byref(u)))
         return t.value, u.value
+
+    # ---- table equations of state (Planetary scheme) ----
+    def set_eos_table(self, table):
+        """Copies an EosTable (load_eos_table) to the device: particles of its mat_id are evaluated from it."""
+        self._check(self.lib.swift_cuda_set_eos_table(self.ctx, C.byref(table)))
 
     # ---- time-step limiter (swift --limiter) ----
     def runner_do_limiter_loop(self, time_bin=None, want_wakeup=False):

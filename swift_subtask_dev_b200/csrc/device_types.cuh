@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include "../../include/swift_cuda.h"
+#include "eos_table.h"
 #include "host_tree.hpp"
 
 namespace swiftcuda {
@@ -37,6 +38,10 @@ struct Consts {
   float visc_alpha_max, visc_alpha_min, visc_length;
   float diff_beta, diff_alpha_max, diff_alpha_min;
   double time_base;
+  // table equations of state of the Planetary scheme (appended; eos_table.h): device arrays
+  int n_tab;
+  int pad_tab_;
+  EosTable tab[8];
 };
 
 struct CellDev {

@@ -1398,6 +1398,14 @@ __device__ __forceinline__ void eos_eval(float rho, float u, int mat_id, float &
     cs = sqrtf(u * g * (g - 1.f));  // planetary/ideal_gas.h:161-165
     return;
   }
+  if (mat_id >= 200) {
+    // a material that lives in a table (HM80 200-202, SESAME 300-303, ANEOS 400-402, custom 900-909): eos_table.h
+    for (int k = 0; k < kc.n_tab; k++)
+      if (kc.tab[k].mat_id == mat_id) {
+        et_eval(kc.tab[k], rho, u, P, cs);
+        return;
+      }
+  }
   int m = 0;
   for (int k = 0; k < kc.n_til; k++)
     if (kc.til[k].mat_id == mat_id) m = k;

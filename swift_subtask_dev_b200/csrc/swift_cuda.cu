@@ -22,6 +22,9 @@ static int fail(const std::string &m) {
   g_err = m;
   return 1;
 }
+namespace swiftcuda {
+int set_error(const std::string &m) { return fail(m); }  // for the host-only sources (eos_loader.cpp)
+}
 #define CK(call)                                                                              \
   do {                                                                                        \
     cudaError_t e_ = (call);                                                                  \
@@ -105,6 +108,10 @@ struct swift_cuda_ctx {
   int grid_limiter = 0;        // the time-step limiter loop, k_density<0, false, 2>
   float limiter_ms[2] = {0.f, 0.f};  // device time of the last limiter loop / k_limiter
   int8_t *d_lim_tmp = nullptr; // n bytes: time bins in / wakeup out in caller order
+  // table equations of state (swift_cuda_set_eos_table): device arrays that outlive rebuilds
+  EosTable tabs[8] = {};
+  int n_tab = 0;
+  std::vector<void *> eos_allocs;
   long long n_gradient = 0;
   int sph_prep_mode = 0;   // k_sphenix_prep: swift_cuda_step_parts calls that run without the ghost / the extra ghost
   int fast_qd = kQD;   // rows of the hit FIFO k_force_fast uses (SWIFT_CUDA_FAST_QD)
@@ -227,6 +234,7 @@ void swift_cuda_destroy(swift_cuda_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
   free_device(c);
+  for (void *q : c->eos_allocs) cudaFree(q);
   for (auto &e : c->ev)
     if (e) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -275,6 +283,8 @@ static int upload_consts(swift_cuda_ctx *c) {
   k.diff_alpha_max = c->sprops.diffusion_alpha_max;
   k.diff_alpha_min = c->sprops.diffusion_alpha_min;
   k.time_base = c->sprops.time_base;
+  k.n_tab = c->n_tab;
+  for (int i = 0; i < 8; i++) k.tab[i] = c->tabs[i];
   CK(cudaMemcpyToSymbolAsync(kc, &k, sizeof(k), 0, cudaMemcpyHostToDevice, c->stream));
   return 0;
 }
@@ -1988,6 +1998,55 @@ int swift_cuda_timestep(swift_cuda_ctx *c, long long *ti_end_min, long long *upd
   if (small > 0)
     return fail(std::to_string(small) + " particle(s) want a time-step below dt_min (" +
                 std::to_string(c->iprm.dt_min) + ")");
+  return 0;
+}
+
+// ---- table equations of state: include/swift_cuda.h, "Table equations of state" (loaders: eos_loader.cpp) ----
+int swift_cuda_set_eos_table(swift_cuda_ctx *c, const swift_cuda_eos_table *t) {
+  if (!c || !t) return fail("set_eos_table: null argument");
+  if (c->prm.scheme != SWIFT_CUDA_SCHEME_PLANETARY) return fail("set_eos_table: table materials exist in the Planetary scheme only");
+  if (t->kind != kEosTableSesame && t->kind != kEosTableHM80) return fail("set_eos_table: kind must be 1 (SESAME-style) or 2 (HM80)");
+  if (t->mat_id < 200) return fail("set_eos_table: mat_id below 200 is an ideal gas or a Tillotson material");
+  if (t->num_rho < 2 || t->num_T < 2) return fail("set_eos_table: fewer than two densities or energies");
+  if (!t->P || (t->kind == kEosTableSesame && (!t->log_rho || !t->log_u || !t->c))) return fail("set_eos_table: null array");
+  CK(cudaSetDevice(c->device));
+  int slot = c->n_tab;
+  for (int k = 0; k < c->n_tab; k++)
+    if (c->tabs[k].mat_id == t->mat_id) slot = k;  // a second table for a material replaces the first
+  if (slot >= 8) return fail("set_eos_table: at most 8 tables per context");
+  const size_t n2 = (size_t)t->num_rho * t->num_T;
+  auto up = [&](const float *src, size_t count, const float **dst) -> int {
+    float *p = nullptr;
+    if (cudaMalloc(&p, count * sizeof(float)) != cudaSuccess) return fail("set_eos_table: out of device memory");
+    c->eos_allocs.push_back(p);
+    if (cudaMemcpy(p, src, count * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess)
+      return fail("set_eos_table: copy to the device failed");
+    *dst = p;
+    return 0;
+  };
+  EosTable e = {};
+  e.kind = t->kind;
+  e.mat_id = t->mat_id;
+  e.num_rho = t->num_rho;
+  e.num_T = t->num_T;
+  if (up(t->P, n2, &e.P)) return 1;
+  if (t->kind == kEosTableSesame) {
+    if (up(t->log_rho, (size_t)t->num_rho, &e.log_rho) || up(t->log_u, n2, &e.log_u) || up(t->c, n2, &e.c)) return 1;
+  }
+  e.P_tiny = t->P_tiny;
+  e.c_tiny = t->c_tiny;
+  e.log_rho_min = t->log_rho_min;
+  e.log_rho_step = t->log_rho_step;
+  e.inv_log_rho_step = t->inv_log_rho_step;
+  e.log_u_min = t->log_u_min;
+  e.log_u_step = t->log_u_step;
+  e.inv_log_u_step = t->inv_log_u_step;
+  e.bulk_mod = t->bulk_mod;
+  e.P_min_for_c_min = t->P_min_for_c_min;
+  c->tabs[slot] = e;
+  if (slot == c->n_tab) c->n_tab++;
+  if (upload_consts(c)) return 1;
+  CK(cudaStreamSynchronize(c->stream));
   return 0;
 }
 
