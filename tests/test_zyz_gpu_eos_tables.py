@@ -1,0 +1,43 @@
+"""GPU tests of the table equations of state: a whole step and a resident run of a two-body
+impact whose materials live in five synthetic tables, against the fixtures the REFERENCE's own compiled operators,
+table loaders and interpolation wrote (tests/golden/eos_tables/impact3k_tables*.npz).  The CPU side -- loaders and
+the device's interpolation source built for the host, bit for bit against the reference -- is
+tests/test_eos_tables.py.
+
+The checks run scripts/eos_tables_gpu_check.py in a process of its own.
+
+STATUS: this device path (eos_eval's table branch, swift_cuda_set_eos_table) was written after the round's GPU
+budget had been spent; it had NOT run on hardware at the time of the commit.  What is known: the interpolation is
+the same source file that passes on the host, and the SASS of every kernel that does not evaluate an equation of
+state is unchanged.  The tests are marked xfail(strict=False): their first run on a B200
+reports XPASS where the device matches the reference bit for bit and XFAIL (with the script's output) where it
+does not, without stopping the tests collected after this file."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SCRIPT = os.path.join(ROOT, "scripts", "eos_tables_gpu_check.py")
+FIRST_RUN = "first run on hardware (written after the round's GPU budget was spent)"
+
+
+def _run(section):
+    r = subprocess.run([sys.executable, SCRIPT, section], cwd=ROOT, capture_output=True, text=True, timeout=900)
+    sys.stdout.write(r.stdout[-6000:])
+    sys.stderr.write(r.stderr[-3000:])
+    assert r.returncode == 0, "eos_tables_gpu_check.py %s:\n%s\n%s" % (section, r.stdout[-3000:], r.stderr[-2000:])
+    assert "all ok" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason=FIRST_RUN)
+def test_step_with_table_materials_matches_the_reference():
+    _run("step")
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason=FIRST_RUN)
+def test_resident_run_with_table_materials_matches_the_reference():
+    _run("run")
