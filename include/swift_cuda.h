@@ -485,6 +485,42 @@ void swift_cuda_eos_table_free(swift_cuda_eos_table *table);
  * an ideal gas, a Tillotson material of swift_cuda_params nor a table set here makes the step fail. */
 int swift_cuda_set_eos_table(swift_cuda_ctx *ctx, const swift_cuda_eos_table *table);
 
+/* ---- Flat binary particle files (the other half of SURVEY.md 8(f) N4) ---------------------------
+ * The field set, names and types of the reference's HDF5 initial conditions and snapshots for gas
+ * (hydro_read_particles / hydro_write_particles, src/hydro/Planetary/hydro_io.h:55-84, 190-228; the other
+ * schemes lack MaterialIDs), as one little-endian file: a 128-byte header (magic "SWCUPRT1", n, the box, a mask
+ * of the fields present), then the arrays in the order below, each padded to 16 bytes.  HDF5 is not needed
+ * (nor present here): a converter from the reference's files is a dozen lines of h5py on a machine that has it.
+ * Values are in internal units; nothing is converted.  Host only. */
+#define SWIFT_CUDA_FIELD_COORDINATES 1       /* double [n][3]   p->x          compulsory */
+#define SWIFT_CUDA_FIELD_VELOCITIES 2        /* float  [n][3]   p->v          compulsory */
+#define SWIFT_CUDA_FIELD_MASSES 4            /* float  [n]      p->mass       compulsory */
+#define SWIFT_CUDA_FIELD_SMOOTHING_LENGTHS 8 /* float  [n]      p->h          compulsory */
+#define SWIFT_CUDA_FIELD_INTERNAL_ENERGIES 16 /* float [n]      p->u          compulsory */
+#define SWIFT_CUDA_FIELD_PARTICLE_IDS 32     /* int64  [n]      p->id         compulsory */
+#define SWIFT_CUDA_FIELD_MATERIAL_IDS 64     /* int32  [n]      p->mat_id     Planetary */
+#define SWIFT_CUDA_FIELD_DENSITIES 128       /* float  [n]      p->rho        optional (snapshots) */
+#define SWIFT_CUDA_FIELD_ACCELERATIONS 256   /* float  [n][3]   p->a_hydro    optional */
+#define SWIFT_CUDA_FIELD_PRESSURES 512       /* float  [n]      convert_P     optional (snapshots) */
+#define SWIFT_CUDA_FIELDS_COMPULSORY 63
+typedef struct {
+  int64_t n;
+  double dim[3];          /* box size (Header/BoxSize) */
+  double time;            /* Header/Time */
+  int fields;             /* SWIFT_CUDA_FIELD_* present; absent arrays are NULL */
+  double *coordinates;
+  float *velocities, *masses, *smoothing_lengths, *internal_energies;
+  long long *particle_ids;
+  int *material_ids;
+  float *densities, *accelerations, *pressures;
+} swift_cuda_particle_file;
+/* Writes the arrays whose bit is set in `fields` (the compulsory ones must be). */
+int swift_cuda_particles_write_bin(const char *path, const swift_cuda_particle_file *p);
+/* Reads a file written by the above; the arrays belong to the struct (swift_cuda_particles_free).  The arrays
+ * of a read file can go straight into swift_cuda_parts_in. */
+int swift_cuda_particles_read_bin(const char *path, swift_cuda_particle_file *out);
+void swift_cuda_particles_free(swift_cuda_particle_file *p);
+
 /* ---- SPHENIX: the gradient loop and the extra ghost -------------------------
  * params.scheme = SWIFT_CUDA_SCHEME_SPHENIX (+ ideal gas) turns the step into the reference's
  * EXTRA_HYDRO_LOOP subgraph (src/engine_maketasks.c:2306-2317, src/runner_main.c:199-200, 249-250,

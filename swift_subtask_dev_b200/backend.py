@@ -26,7 +26,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 def build_library(verbose=False, force=False):
     """Compiles the CUDA backend in-tree with nvcc for sm_100a."""
-    srcs = [os.path.join(CSRC, f) for f in ("swift_cuda.cu", "host_tree.cpp", "eos_loader.cpp")]
+    srcs = [os.path.join(CSRC, f) for f in ("swift_cuda.cu", "host_tree.cpp", "eos_loader.cpp", "particle_io.cpp")]
     deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.cuh", "leaf_kernels.cuh", "list_kernels.cuh", "force_fast.cuh", "integrate.cuh", "pack.cuh", "sphenix.cuh", "device_types.cuh", "limit_part.h", "eos_table.h", "host_tree.hpp")] + \
         [os.path.join(ROOT, "include", "swift_cuda.h")]
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
@@ -142,7 +142,8 @@ EXPORTS = ["swift_cuda_abi_version", "swift_cuda_sizeof", "swift_cuda_last_error
            "swift_cuda_sphenix_get_counter", "swift_cuda_do_gradient", "swift_cuda_do_extra_ghost",
            "swift_cuda_do_limiter_loop", "swift_cuda_do_limiter", "swift_cuda_get_limiter_timings",
            "swift_cuda_eos_table_load_sesame", "swift_cuda_eos_table_load_hm80", "swift_cuda_eos_table_write_bin",
-           "swift_cuda_eos_table_read_bin", "swift_cuda_eos_table_free", "swift_cuda_set_eos_table"]
+           "swift_cuda_eos_table_read_bin", "swift_cuda_eos_table_free", "swift_cuda_set_eos_table",
+           "swift_cuda_particles_write_bin", "swift_cuda_particles_read_bin", "swift_cuda_particles_free"]
 
 
 class EosTable(C.Structure):
@@ -185,6 +186,64 @@ def load_eos_table(path, mat_id, units, version_date=None):
 
 def free_eos_table(t):
     load_library().swift_cuda_eos_table_free(C.byref(t))
+
+
+class ParticleFile(C.Structure):
+    # field order must match swift_cuda_particle_file
+    _fields_ = [("n", C.c_int64), ("dim", C.c_double * 3), ("time", C.c_double), ("fields", C.c_int),
+                ("coordinates", C.POINTER(C.c_double)), ("velocities", C.POINTER(C.c_float)),
+                ("masses", C.POINTER(C.c_float)), ("smoothing_lengths", C.POINTER(C.c_float)),
+                ("internal_energies", C.POINTER(C.c_float)), ("particle_ids", C.POINTER(C.c_longlong)),
+                ("material_ids", C.POINTER(C.c_int)), ("densities", C.POINTER(C.c_float)),
+                ("accelerations", C.POINTER(C.c_float)), ("pressures", C.POINTER(C.c_float))]
+
+
+# (member of swift_cuda_particle_file, SWIFT_CUDA_FIELD_* bit, key of the particle dicts used here, dtype, width)
+PARTICLE_FIELDS = [("coordinates", 1, "x", np.float64, 3), ("velocities", 2, "v", np.float32, 3),
+                   ("masses", 4, "mass", np.float32, 1), ("smoothing_lengths", 8, "h", np.float32, 1),
+                   ("internal_energies", 16, "u", np.float32, 1), ("particle_ids", 32, "id", np.int64, 1),
+                   ("material_ids", 64, "mat_id", np.int32, 1), ("densities", 128, "rho", np.float32, 1),
+                   ("accelerations", 256, "a", np.float32, 3), ("pressures", 512, "pressure", np.float32, 1)]
+
+
+def write_particles(path, ic, dim, time=0.0):
+    """Host only.  Writes the particle dict ic (x, v, mass, h, u, id; optional mat_id, rho, a, pressure) as a flat
+    binary file with the field set of the reference's HDF5 files (src/hydro/Planetary/hydro_io.h)."""
+    lib = load_library()
+    f = ParticleFile()
+    f.n = len(ic["h"])
+    f.dim[:] = [float(v) for v in dim]
+    f.time = float(time)
+    keep = []
+    for member, bit, key, dt, w in PARTICLE_FIELDS:
+        if ic.get(key) is None:
+            continue
+        a = np.ascontiguousarray(ic[key], dtype=dt)
+        assert a.size == f.n * w, key
+        keep.append(a)
+        f.fields |= bit
+        setattr(f, member, a.ctypes.data_as(dict(ParticleFile._fields_)[member]))
+    if lib.swift_cuda_particles_write_bin(path.encode(), C.byref(f)) != 0:
+        raise SwiftCudaError(lib.swift_cuda_last_error().decode())
+
+
+def read_particles(path):
+    """Host only.  Returns (particle dict, dim, time) of a file written by write_particles / the C entry."""
+    lib = load_library()
+    f = ParticleFile()
+    if lib.swift_cuda_particles_read_bin(path.encode(), C.byref(f)) != 0:
+        raise SwiftCudaError(lib.swift_cuda_last_error().decode())
+    ic = {"time_bin": None}
+    n = int(f.n)
+    for member, bit, key, dt, w in PARTICLE_FIELDS:
+        if not (f.fields & bit):
+            ic[key] = None
+            continue
+        a = np.ctypeslib.as_array(getattr(f, member), shape=(n * w,)).astype(dt, copy=True) if n else np.zeros(0, dt)
+        ic[key] = a.reshape(n, 3) if w == 3 else a
+    out = (ic, tuple(f.dim), float(f.time))
+    lib.swift_cuda_particles_free(C.byref(f))
+    return out
 
 
 class SphenixProps(C.Structure):
@@ -324,6 +383,10 @@ def load_library():
         lib.swift_cuda_eos_table_read_bin.argtypes = [C.c_char_p, C.c_void_p]
         lib.swift_cuda_eos_table_free.argtypes = [C.c_void_p]
         lib.swift_cuda_eos_table_free.restype = None
+        lib.swift_cuda_particles_write_bin.argtypes = [C.c_char_p, C.c_void_p]
+        lib.swift_cuda_particles_read_bin.argtypes = [C.c_char_p, C.c_void_p]
+        lib.swift_cuda_particles_free.argtypes = [C.c_void_p]
+        lib.swift_cuda_particles_free.restype = None
         lib.swift_cuda_set_eos_table.argtypes = [C.c_void_p, C.c_void_p]
         lib.swift_cuda_do_limiter_loop.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         lib.swift_cuda_do_limiter.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
