@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <chrono>
 #include <string>
 #include <vector>
 
@@ -1607,13 +1608,26 @@ void swift_cuda_host_free(void *p) { free(p); }
 int swift_cuda_host_plan_digest(const swift_cuda_params *params, const swift_cuda_parts_in *in,
                                 unsigned long long *digest) {
   if (!params || !in || !digest) return fail("host_plan_digest: null argument");
+  // SWIFT_CUDA_HOST_TIMING=1: the stages' wall-clock times on stderr (what scripts/host_plan_time.py reads)
+  const bool timing = getenv("SWIFT_CUDA_HOST_TIMING") != nullptr;
+  auto now = [] { return std::chrono::steady_clock::now(); };
+  auto t_last = now();
+  auto lap = [&](const char *what) {
+    if (!timing) return;
+    const auto t = now();
+    fprintf(stderr, "host_plan %-16s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(t - t_last).count());
+    t_last = t;
+  };
   Tree tree;
   const int rc = build_tree(*params, in->n, in->x, in->h, tree);
   if (rc) return fail("host_plan_digest: cannot build the top-level grid (code " + std::to_string(rc) + ")");
+  lap("build_tree");
   std::vector<float> hs(in->n);
   gather_f32(in->h, tree.order.data(), in->n, hs.data());
   compute_cell_hmax(tree, hs.data());
+  lap("cell_hmax");
   build_tasks(*params, tree);
+  lap("build_tasks");
   std::vector<uint8_t> act;
   {
     swift_cuda_ctx tmp;
@@ -1621,9 +1635,12 @@ int swift_cuda_host_plan_digest(const swift_cuda_params *params, const swift_cud
     tmp.tree = tree;
     cells_active(&tmp, in, act);
   }
+  lap("cells_active");
   WorkLists wl;
   build_worklists(*params, tree, act, wl);
+  lap("build_worklists");
   assign_lanes(tree, in->x, wl);
+  lap("assign_lanes");
   unsigned long long hsh = 1469598103934665603ULL;
   auto mix = [&](const void *p, size_t bytes) {
     const unsigned char *b = static_cast<const unsigned char *>(p);
