@@ -55,10 +55,31 @@ typedef struct {
   int mat_id;
 } oracle_til;
 
+/* ---- table equations of state of the Planetary scheme ----
+ * One material's table as the reference holds it after load_table_* + prepare_table_* + convert_units_*
+ * (src/equation_of_state/planetary/sesame.h:149-352, hm80.h:76-178), internal units of ref_get_eos.  Pointers
+ * are into the reference's own arrays. */
+typedef struct {
+  int kind;                 /* 1 SESAME-style (SESAME, SS08, ANEOS, custom), 2 HM80 */
+  int mat_id;
+  int num_rho, num_T;       /* HM80: num_rho, num_u */
+  const float *log_rho;     /* SESAME [num_rho] */
+  const float *log_u;       /* SESAME [num_rho][num_T] */
+  const float *P;           /* SESAME P [num_rho][num_T]; HM80 log P [num_rho][num_u] */
+  const float *c;           /* SESAME [num_rho][num_T] */
+  float P_tiny, c_tiny;
+  float log_rho_min, log_rho_step, inv_log_rho_step, log_u_min, log_u_step, inv_log_u_step;
+  float bulk_mod, P_min_for_c_min;
+} oracle_eos_table;
+
 typedef struct {
   int n_til;
   oracle_til til[8];
   float idg_gamma[4]; /* planetary ideal gas gammas, mat_id 0..2 (planetary/ideal_gas.h) */
+  /* materials that live in tables (mat_id >= 200): prepared tables, e.g. those of ref_eos_table_get or of
+   * the fixture tests/golden/eos_tables/reference_results.npz.  n_tab = 0: none. */
+  int n_tab;
+  const oracle_eos_table *tab;
 } oracle_eos;
 
 /* Particle arrays (SoA, n entries; vectors are [n][3] row-major). */
@@ -123,22 +144,7 @@ int ref_sizeof_part(void);
  * examples/Planetary/EarthImpact/earth_impact.yml:2-7). Returns 0 when compiled in. */
 int ref_get_eos(oracle_eos *out);
 
-/* ---- table equations of state of the Planetary scheme (libswiftref_planetary.so only) ----
- * One material's table as the reference holds it after load_table_* + prepare_table_* + convert_units_*
- * (src/equation_of_state/planetary/sesame.h:149-352, hm80.h:76-178), internal units of ref_get_eos.  Pointers
- * are into the reference's own arrays. */
-typedef struct {
-  int kind;                 /* 1 SESAME-style (SESAME, SS08, ANEOS, custom), 2 HM80 */
-  int mat_id;
-  int num_rho, num_T;       /* HM80: num_rho, num_u */
-  const float *log_rho;     /* SESAME [num_rho] */
-  const float *log_u;       /* SESAME [num_rho][num_T] */
-  const float *P;           /* SESAME P [num_rho][num_T]; HM80 log P [num_rho][num_u] */
-  const float *c;           /* SESAME [num_rho][num_T] */
-  float P_tiny, c_tiny;
-  float log_rho_min, log_rho_step, inv_log_rho_step, log_u_min, log_u_step, inv_log_u_step;
-  float bulk_mod, P_min_for_c_min;
-} oracle_eos_table;
+/* ---- table equations of state: the reference's own loaders and functions (libswiftref_planetary.so only) ---- */
 /* what eos_init does for EoS:planetary_use_<material> = 1 with EoS:planetary_<material>_table_file = path
  * (src/equation_of_state/planetary/equation_of_state.h:1629-1745); mat_id: 200-202, 300-303, 400-402, 900-909 */
 int ref_eos_table_load(int mat_id, const char *path);

@@ -434,6 +434,122 @@ static float til_soundspeed(float density, float u, const oracle_til *m) {
   return sqrtf(c_sq);
 }
 
+/* ---- materials that live in tables --------------------------------------------------
+ * find_value_in_monot_incr_array, src/utilities.h:33-57 */
+static int tab_find(float x, const float *array, int n) {
+  int lo = 0, hi = n;
+  while (hi - lo > 1) {
+    const int mid = (hi + lo) / 2;
+    if (array[mid] <= x) lo = mid; else hi = mid;
+  }
+  if (x < array[0]) return -1;
+  if (array[n - 1] <= x) return n;
+  return lo;
+}
+
+/* What SESAME_pressure_from_internal_energy and SESAME_soundspeed_from_internal_energy share
+ * (src/equation_of_state/planetary/sesame.h:488-544, 613-669).  which = 0: pressure (:546-593), 1: sound speed
+ * (:671-720); they differ in the table, in what a non-positive node does, and in whether the "below the minimum u"
+ * clamp looks at the raw or at the logged node values.  The u slices are searched in rows clamped into the table
+ * (the reference reads rows -1 / num_rho + 1 for a density outside it: undefined). */
+static float tab_sesame(const oracle_eos_table *m, float density, float u, int which) {
+  if (u <= 0.f) return 0.f;
+  const int nT = m->num_T;
+  const float log_rho = logf(density);
+  const float log_u = logf(u);
+  int idx_rho = tab_find(log_rho, m->log_rho, m->num_rho);
+  const int r1 = idx_rho < 0 ? 0 : (idx_rho > m->num_rho - 1 ? m->num_rho - 1 : idx_rho);
+  const int r2 = idx_rho + 1 < 0 ? 0 : (idx_rho + 1 > m->num_rho - 1 ? m->num_rho - 1 : idx_rho + 1);
+  int idx_u_1 = tab_find(log_u, m->log_u + (size_t)r1 * nT, nT);
+  int idx_u_2 = tab_find(log_u, m->log_u + (size_t)r2 * nT, nT);
+  if (idx_rho <= -1) idx_rho = 0; else if (idx_rho >= m->num_rho) idx_rho = m->num_rho - 2;
+  if (idx_u_1 <= -1) idx_u_1 = 0; else if (idx_u_1 >= nT) idx_u_1 = nT - 2;
+  if (idx_u_2 <= -1) idx_u_2 = 0; else if (idx_u_2 >= nT) idx_u_2 = nT - 2;
+  float intp_rho, intp_u_1, intp_u_2;
+  if (m->log_rho[idx_rho + 1] != m->log_rho[idx_rho])
+    intp_rho = (log_rho - m->log_rho[idx_rho]) / (m->log_rho[idx_rho + 1] - m->log_rho[idx_rho]);
+  else
+    intp_rho = 1.f;
+  const float *ua = m->log_u + (size_t)idx_rho * nT, *ub = m->log_u + (size_t)(idx_rho + 1) * nT;
+  if (ua[idx_u_1 + 1] != ua[idx_u_1]) intp_u_1 = (log_u - ua[idx_u_1]) / (ua[idx_u_1 + 1] - ua[idx_u_1]);
+  else intp_u_1 = 1.f;
+  if (ub[idx_u_2 + 1] != ub[idx_u_2]) intp_u_2 = (log_u - ub[idx_u_2]) / (ub[idx_u_2 + 1] - ub[idx_u_2]);
+  else intp_u_2 = 1.f;
+  const float *tab = which == 0 ? m->P : m->c;
+  float v1 = tab[(size_t)idx_rho * nT + idx_u_1], v2 = tab[(size_t)idx_rho * nT + idx_u_1 + 1];
+  float v3 = tab[(size_t)(idx_rho + 1) * nT + idx_u_2], v4 = tab[(size_t)(idx_rho + 1) * nT + idx_u_2 + 1];
+  if (which == 0 && (idx_rho > 0.f) && ((intp_u_1 < 0.f) || (intp_u_2 < 0.f) || (v1 > v2) || (v3 > v4))) {
+    intp_u_1 = 0;
+    intp_u_2 = 0;
+  }
+  const int npos = (v1 <= 0.f) + (v2 <= 0.f) + (v3 <= 0.f) + (v4 <= 0.f);
+  const float tiny = which == 0 ? m->P_tiny : m->c_tiny;
+  if (which == 0) {
+    if (npos > 0) {
+      if ((npos > 2) || (m->P_tiny == 0.f) || (intp_rho < 0.f) || (intp_u_1 < 0.f) || (intp_u_2 < 0.f)) return 0.f;
+    }
+  } else {
+    if (npos > 2) return m->c_tiny;
+    if (npos > 0 && ((intp_rho < 0.f) || (intp_u_1 < 0.f) || (intp_u_2 < 0.f))) return m->c_tiny;
+  }
+  if (npos > 0) {
+    if (v1 <= 0.f) v1 = tiny;
+    if (v2 <= 0.f) v2 = tiny;
+    if (v3 <= 0.f) v3 = tiny;
+    if (v4 <= 0.f) v4 = tiny;
+  }
+  v1 = logf(v1); v2 = logf(v2); v3 = logf(v3); v4 = logf(v4);
+  if (which == 1 && (idx_rho > 0.f) && ((intp_u_1 < 0.f) || (intp_u_2 < 0.f) || (v1 > v2) || (v3 > v4))) {
+    intp_u_1 = 0;
+    intp_u_2 = 0;
+  }
+  const float v = (1.f - intp_rho) * ((1.f - intp_u_1) * v1 + intp_u_1 * v2) +
+                  intp_rho * ((1.f - intp_u_2) * v3 + intp_u_2 * v4);
+  return expf(v);
+}
+
+/* HM80_pressure_from_internal_energy, src/equation_of_state/planetary/hm80.h:224-268 */
+static float tab_hm80_pressure(const oracle_eos_table *m, float density, float u) {
+  if (u <= 0.f) return 0.f;
+  const float log_rho = logf(density);
+  const float log_u = logf(u);
+  int idx_rho = floor((log_rho - m->log_rho_min) * m->inv_log_rho_step);
+  int idx_u = floor((log_u - m->log_u_min) * m->inv_log_u_step);
+  if (idx_rho <= -1) idx_rho = 0; else if (idx_rho >= m->num_rho - 1) idx_rho = m->num_rho - 2;
+  if (idx_u <= -1) idx_u = 0; else if (idx_u >= m->num_T - 1) idx_u = m->num_T - 2;
+  const float intp_rho = (log_rho - m->log_rho_min - idx_rho * m->log_rho_step) * m->inv_log_rho_step;
+  const float intp_u = (log_u - m->log_u_min - idx_u * m->log_u_step) * m->inv_log_u_step;
+  const int nu = m->num_T;
+  const float p1 = m->P[(size_t)idx_rho * nu + idx_u], p2 = m->P[(size_t)idx_rho * nu + idx_u + 1];
+  const float p3 = m->P[(size_t)(idx_rho + 1) * nu + idx_u], p4 = m->P[(size_t)(idx_rho + 1) * nu + idx_u + 1];
+  const float log_P = (1.f - intp_rho) * ((1.f - intp_u) * p1 + intp_u * p2) +
+                      intp_rho * ((1.f - intp_u) * p3 + intp_u * p4);
+  return expf(log_P);
+}
+
+/* the table branch of the planetary dispatcher; returns 0 when mat_id has no table */
+static int tab_eval(const oracle_eos *eos, int mat_id, float rho, float u, float *P, float *cs) {
+  for (int k = 0; k < eos->n_tab; k++) {
+    const oracle_eos_table *m = &eos->tab[k];
+    if (m->mat_id != mat_id) continue;
+    if (m->kind == 2) {
+      *P = tab_hm80_pressure(m, rho, u);
+      /* HM80_soundspeed_from_internal_energy, hm80.h:281-300 */
+      if (m->bulk_mod != 0) {
+        *cs = sqrtf(m->bulk_mod / rho);
+      } else {
+        *cs = sqrtf(GAMMA_F * (*P) / rho);
+        if (*cs <= 0) *cs = sqrtf(GAMMA_F * m->P_min_for_c_min / rho);
+      }
+    } else {
+      *P = tab_sesame(m, rho, u, 0);
+      *cs = tab_sesame(m, rho, u, 1);
+    }
+    return 1;
+  }
+  return 0;
+}
+
 /* Dispatcher: src/equation_of_state/planetary/equation_of_state.h:910-1146
  * (pressure) and :1305-1457 (sound speed): type = mat_id / 100; type 0 is
  * the planetary ideal gas (planetary/ideal_gas.h), type 1 Tillotson. */
@@ -452,6 +568,8 @@ static void eos_eval(const octx *c, const opart *p, float *P, float *cs) {
     *cs = sqrtf(p->u * g * (g - 1.f));
     return;
   }
+  /* types 2 (HM80), 3 (SESAME), 4 (ANEOS), 9 (custom): tables */
+  if (type >= 2 && tab_eval(c->eos, p->mat_id, p->rho, p->u, P, cs)) return;
   const oracle_til *m = NULL;
   for (int k = 0; k < c->eos->n_til; k++)
     if (c->eos->til[k].mat_id == p->mat_id) m = &c->eos->til[k];

@@ -12,13 +12,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 _FP = C.POINTER(C.c_float)
 
 
-class Table(C.Structure):
-    # oracle_eos_table == swift_cuda_eos_table, field for field
-    _fields_ = [("kind", C.c_int), ("mat_id", C.c_int), ("num_rho", C.c_int), ("num_T", C.c_int),
-                ("log_rho", _FP), ("log_u", _FP), ("P", _FP), ("c", _FP), ("P_tiny", C.c_float), ("c_tiny", C.c_float),
-                ("log_rho_min", C.c_float), ("log_rho_step", C.c_float), ("inv_log_rho_step", C.c_float),
-                ("log_u_min", C.c_float), ("log_u_step", C.c_float), ("inv_log_u_step", C.c_float),
-                ("bulk_mod", C.c_float), ("P_min_for_c_min", C.c_float)]
+from oracle_lib import EosTable as Table  # noqa: E402  oracle_eos_table == swift_cuda_eos_table, field for field
 
 
 class Units(C.Structure):
@@ -149,3 +143,31 @@ def sample_points(a, units_density, seed=1, n=4000):
     u[200:220] = 0.0
     u[220:230] = -1.0
     return rho.astype(np.float32), u.astype(np.float32)
+
+
+def eos_with_tables(eos, tables):
+    """An oracle_lib.Eos (ideal gas + Tillotson, e.g. ol.eos_from_json()) that also knows the given prepared tables
+    (dicts as table_arrays / the fixture's "<name>/table/*" entries).  Returns (eos, keep-alive list)."""
+    keep = []
+    arr = (Table * max(len(tables), 1))()
+    for k, a in enumerate(tables):
+        t, kp = table_from_arrays(a)
+        keep.append(kp)
+        C.memmove(C.byref(arr, k * C.sizeof(Table)), C.byref(t), C.sizeof(Table))
+    keep.append(arr)
+    eos.n_tab = len(tables)
+    eos.tab = C.cast(arr, C.POINTER(Table))
+    return eos, keep
+
+
+def fixture_tables(gold=None):
+    """The prepared tables of tests/golden/eos_tables/reference_results.npz, one dict per table."""
+    if gold is None:
+        z = np.load(os.path.join(ROOT, "tests", "golden", "eos_tables", "reference_results.npz"))
+        gold = {k: z[k] for k in z.files}
+    names = sorted({k.split("/")[0] for k in gold if "/table/" in k})
+    out = []
+    for name in names:
+        pre = name + "/table/"
+        out.append({k[len(pre):]: gold[k] for k in gold if k.startswith(pre)})
+    return out

@@ -33,8 +33,19 @@ class Til(C.Structure):
         + [("mat_id", C.c_int)]
 
 
+class EosTable(C.Structure):
+    # oracle_eos_table (oracle/oracle_api.h) == swift_cuda_eos_table, field for field
+    _fields_ = [("kind", C.c_int), ("mat_id", C.c_int), ("num_rho", C.c_int), ("num_T", C.c_int),
+                ("log_rho", C.POINTER(C.c_float)), ("log_u", C.POINTER(C.c_float)), ("P", C.POINTER(C.c_float)),
+                ("c", C.POINTER(C.c_float)), ("P_tiny", C.c_float), ("c_tiny", C.c_float),
+                ("log_rho_min", C.c_float), ("log_rho_step", C.c_float), ("inv_log_rho_step", C.c_float),
+                ("log_u_min", C.c_float), ("log_u_step", C.c_float), ("inv_log_u_step", C.c_float),
+                ("bulk_mod", C.c_float), ("P_min_for_c_min", C.c_float)]
+
+
 class Eos(C.Structure):
-    _fields_ = [("n_til", C.c_int), ("til", Til * 8), ("idg_gamma", C.c_float * 4)]
+    _fields_ = [("n_til", C.c_int), ("til", Til * 8), ("idg_gamma", C.c_float * 4),
+                ("n_tab", C.c_int), ("tab", C.POINTER(EosTable))]
 
 
 _FP = C.POINTER(C.c_float)

@@ -10,7 +10,9 @@ oracle/ref_harness.c; results in tests/golden/eos_tables/reference_results.npz):
     eos_eval), built for the host by g++ without contraction, gives the reference's P and c bit for bit on 4000
     points per table -- inside, below and above the table in u, on table nodes, at u <= 0;
   * its logf / expf agree with this machine's libm (what the reference calls);
-  * live against the compiled reference where oracle/_ref is present.
+  * live against the compiled reference where oracle/_ref is present;
+  * the C oracle (oracle/sph_oracle.c, its own restatement of the table functions) reproduces the whole step and
+    the three-step run the compiled reference made with table materials (impact3k_tables*.npz).
 
 GPU tests of the same tables: tests/test_zyz_gpu_eos_tables.py."""
 import ctypes as C
@@ -159,3 +161,54 @@ def test_live_against_the_compiled_reference(gold):
         assert np.array_equal(P.view(np.uint32), rP.view(np.uint32)), name
         assert np.array_equal(c.view(np.uint32), rc.view(np.uint32)), name
         lib.swift_cuda_eos_table_free(C.byref(t))
+
+
+# ---- the C oracle (oracle/sph_oracle.c: tab_sesame, tab_hm80_pressure, tab_eval) ------------------------------
+def _oracle_eos(gold):
+    eos, keep = el.eos_with_tables(ol.eos_from_json(), el.fixture_tables(gold))
+    return eos, keep
+
+
+def test_oracle_step_with_table_materials_reproduces_reference_golden(gold):
+    """One whole step of the two-body impact whose materials live in the five tables (+ Tillotson iron), by the
+    oracle with its own restatement of the table functions, against what the compiled reference wrote
+    (tests/golden/make_golden_eos_step.py): pair lists, counts, every field."""
+    import ast
+    import golden_util as gu
+    import parity
+    z = np.load(os.path.join(DIR, "impact3k_tables.npz"))
+    g = {k: z[k] for k in z.files}
+    kw = ast.literal_eval(str(g["params"]))
+    ic = {"x": g["x"], "v": g["v"], "mass": g["mass"], "h": g["h"], "u": g["u"], "id": g["id"], "mat_id": g["mat_id"]}
+    cells, tasks, nt = gu.tree_structs(g)
+    eos, keep = _oracle_eos(gold)
+    prm = ol.make_params(record=True, **kw)
+    r = ol.run_step("oracle", prm, ic, cells, tasks, nt, record=True, eos=eos)
+    assert r["counts"] == [int(v) for v in g["counts"]]
+    for s in range(3):
+        assert gu.pair_digest(r["pairs"][s]) == str(g["digests"][s])
+    for k in list(ol.OUT_FIELDS) + ["f_min_ngb_time_bin"]:
+        a, b = np.asarray(r[k]), g[k]
+        assert np.array_equal(a, b) or np.array_equal(a.view(np.uint32), b.view(np.uint32)), k
+    assert (g["mat_id"] >= 200).sum() > 2900
+
+
+def test_oracle_run_with_table_materials_reproduces_reference_golden(gold):
+    """Three engine steps: the drift (hydro_predict_extra) and kick2 (hydro_reset_predicted_values) evaluate the
+    tables too."""
+    import sys
+    sys.path.insert(0, os.path.dirname(DIR))
+    import make_golden_eos_step as gen
+    icc, tree, kw, ip = gen.case()
+    z = np.load(os.path.join(DIR, "impact3k_tables_run.npz"))
+    eos, keep = _oracle_eos(gold)
+    s, log = il_run(icc, kw, ip, tree, len(z["log_int"]) - 1, eos)
+    import integ_lib as il
+    for k in il.STATE_KEYS:
+        assert np.array_equal(np.asarray(s[k]).reshape(-1), z[k].reshape(-1)), k
+    assert [[l[0], l[1], l[2], l[5]] for l in log] == z["log_int"].tolist()
+
+
+def il_run(icc, kw, ip, tree, nsteps, eos):
+    import integ_lib as il
+    return il.run_loop("oracle", icc, kw, ip, tree, nsteps, eos=eos, variant="planetary")
