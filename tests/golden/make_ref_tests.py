@@ -45,3 +45,24 @@ for variant, suffix, prefix in (("minimal", "", ""), ("sphenix", "_sphenix", "sp
                     if l.strip() and not l.lstrip().startswith("#")]
             np.savez_compressed(os.path.join(HERE, "ref_tests", prefix + name + ".npz"), table=np.array(rows, dtype=np.float64))
             print(variant, name, "->", len(rows), "rows")
+
+# tests/testActivePair.c: two neighbouring cells with every mix of active and inactive particles (one particle per
+# cell, all active, half, none, 10 %, one cell active and one not, ...), the density pair task and the force pair
+# task against the brute force of tests/tools.c; the reference's script (tests/testActivePair.sh.in) runs a random
+# seed and the seed 1506434777 "that triggered a bug"; fixed seeds here
+ACTIVE_PAIR = {"testActivePair_s1506434777": "1506434777", "testActivePair_s12345": "12345"}
+for variant, suffix, prefix in (("minimal", "", ""), ("sphenix", "_sphenix", "sphenix_")):
+    exe = os.path.join(REF, "testActivePair_ref" + suffix)
+    if not os.path.exists(exe):
+        print("skip", variant, "testActivePair (not built)")
+        continue
+    for name, seed in ACTIVE_PAIR.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            subprocess.run([exe, "-n", "6", "-r", "1", "-d", "0", "-f", "active", "-s", seed], cwd=tmp, check=True,
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            z = {}
+            for key, fname in (("density", "swift_dopair_active.dat"), ("force", "swift_dopair2_force_active.dat")):
+                rows = [l.split() for l in open(os.path.join(tmp, fname)) if l.strip() and not l.lstrip().startswith("#")]
+                z[key] = np.array(rows, dtype=np.float64)
+            np.savez_compressed(os.path.join(HERE, "ref_tests", prefix + name + ".npz"), **z)
+            print(variant, name, "->", {k: v.shape for k, v in z.items()})

@@ -1,4 +1,4 @@
-"""The reference's OWN unit tests (tests/test27cells.c, tests/test125cells.c, tests/testPeriodicBC.c), compiled from where
+"""The reference's OWN unit tests (tests/test27cells.c, tests/test125cells.c, tests/testPeriodicBC.c, tests/testActivePair.c), compiled from where
 they lie and linked against swift_subtask_dev_b200/shim/swift_cuda_shim.c + libswiftcuda.so instead
 of the reference's runner_doiact_hydro.o (oracle/Makefile.shim).  Their output tables are gated the
 way the reference gates them (tests/difffloat.py:75-130 with tests/tolerance_*.dat: absolute,
@@ -38,11 +38,11 @@ def difffloat(a, b, tol, number_to_check):
     return np.argwhere(bad)
 
 
-def run_test(exe, args, tmp_path):
+def run_test(exe, args, tmp_path, timeout=900):
     path = os.path.join(REF, exe)
     if not os.path.exists(path):
         pytest.skip("oracle/_ref/%s not built (make -C oracle -f Makefile.shim needs the reference tree)" % exe)
-    r = subprocess.run([path] + args, cwd=tmp_path, capture_output=True, text=True, timeout=900)
+    r = subprocess.run([path] + args, cwd=tmp_path, capture_output=True, text=True, timeout=timeout)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     return r
 
@@ -116,3 +116,34 @@ def test_testPeriodicBC_through_the_shim(name, args, suffix, prefix, tmp_path):
     ref = np.load(os.path.join(GOLD, prefix + name + ".npz"))["table"]
     bad = difffloat(ours, ref, tol, 10 ** 6)
     assert len(bad) == 0, "against the reference's own table: %d entries, first (row, col) %s" % (len(bad), bad[:5])
+
+
+# tests/testActivePair.c: two neighbouring cells in every mix of active and inactive particles (one particle per cell;
+# all active; half; none; 10 %; one cell active, the other not; ...), first the density pair task, then the force pair
+# task, each against the brute force of tests/tools.c (tests/testActivePair.c:343-560).  The reference's script
+# (tests/testActivePair.sh.in) gates every row with tolerance_pair_active.dat and tolerance_pair_force_active.dat, for
+# a random seed and for the seed 1506434777 "that triggered a bug"; fixed seeds here.
+# NOT YET RUN ON HARDWARE (linked after the round's GPU budget was spent; the per-task entries it calls are the ones
+# test27cells / test125cells / testPeriodicBC pass through, the mixes of inactive particles are new): xfail until seen.
+CASES_ACTIVE_PAIR = [("testActivePair_s1506434777", "1506434777"), ("testActivePair_s12345", "12345")]
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason="first run on hardware (linked after the round's GPU budget was spent)")
+@pytest.mark.parametrize("suffix,prefix", VARIANTS, ids=["minimal", "sphenix"])
+@pytest.mark.parametrize("name,seed", CASES_ACTIVE_PAIR)
+def test_testActivePair_through_the_shim(name, seed, suffix, prefix, tmp_path):
+    run_test("testActivePair_cuda" + suffix, ["-n", "6", "-r", "1", "-d", "0", "-f", "active", "-s", seed], tmp_path,
+             timeout=180)
+    ref = np.load(os.path.join(GOLD, prefix + name + ".npz"))
+    for key, ours_f, brute_f, tol_f in (
+            ("density", "swift_dopair_active.dat", "brute_force_pair_active.dat", "tolerance_pair_active.dat"),
+            ("force", "swift_dopair2_force_active.dat", "brute_force_dopair2_active.dat",
+             "tolerance_pair_force_active.dat")):
+        ours = load_table(tmp_path / ours_f)
+        brute = load_table(tmp_path / brute_f)
+        tol = load_table(os.path.join(REF, tol_f))
+        bad = difffloat(ours, brute, tol, 10 ** 6)
+        assert len(bad) == 0, "%s, difffloat gate: %d entries out of tolerance, first (row, col) %s" % (key, len(bad), bad[:5])
+        bad = difffloat(ours, ref[key], tol, 10 ** 6)
+        assert len(bad) == 0, "%s, against the reference's own table: %d entries, first %s" % (key, len(bad), bad[:5])
