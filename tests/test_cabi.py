@@ -135,3 +135,30 @@ def test_host_builder_threads_give_the_same_lists(name, make, kw, monkeypatch):
         assert be.host_plan_digest(prm, ic) == serial, "%s host threads" % nthreads
     monkeypatch.delenv("SWIFT_CUDA_HOST_THREADS")
     assert be.host_plan_digest(prm, ic) == serial
+
+
+def test_host_builder_takes_degenerate_inputs():
+    """No particle, one, two, and sets without a single active particle (what the reference's testActivePair hands to
+    the pair tasks): the host builder returns a plan, the same with one host thread and with all."""
+    import parity
+    from swift_subtask_dev_b200 import backend as be
+
+    def ic_n(n, tb=None):
+        rng = np.random.default_rng(1)
+        ic = {"x": rng.random((n, 3)) * 3.0, "v": np.zeros((n, 3), np.float32), "mass": np.ones(n, np.float32),
+              "h": np.full(n, 0.2, np.float32), "u": np.ones(n, np.float32), "id": np.arange(n, dtype=np.int64)}
+        if tb is not None:
+            ic["time_bin"] = np.full(n, tb, np.int8)
+        return ic
+
+    prm = parity.gpu_params(dict(periodic=False, dim=(3.0, 3.0, 3.0), max_active_bin=56))
+    seen = set()
+    for n, tb in ((0, None), (1, None), (2, None), (2, 57), (500, 57), (500, None)):
+        d = be.host_plan_digest(prm, ic_n(n, tb))
+        os.environ["SWIFT_CUDA_HOST_THREADS"] = "1"
+        try:
+            assert be.host_plan_digest(prm, ic_n(n, tb)) == d
+        finally:
+            del os.environ["SWIFT_CUDA_HOST_THREADS"]
+        seen.add(d)
+    assert len(seen) == 6
