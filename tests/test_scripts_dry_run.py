@@ -108,3 +108,40 @@ def test_eos_tables_check_script_flow_with_a_mock_backend(monkeypatch, capsys):
     E.step_checks()
     E.run_checks()
     assert E.FAILED == [], capsys.readouterr().out
+
+
+def test_edge_cases_check_script_flow_with_a_mock_backend(monkeypatch, capsys):
+    """scripts/edge_cases_gpu_check.py with the GPU run replaced by the oracle on the tree the library's HOST builder
+    makes (swift_cuda_host_plan, no GPU): the script's flow, and that the oracle itself takes one particle, two,
+    nobody active, one in a hundred active without aborting."""
+    import edge_cases_gpu_check as E
+    from swift_subtask_dev_b200 import backend as B
+
+    def mock_run_gpu(ic, kw, record=False, pair_capacity=0, tree=None, eos=None, fields_mode=0):
+        t = B.host_plan(parity.gpu_params(kw), ic)
+        o = parity.run_oracle_on_tree(ic, t, kw, record=True)
+        out = {kg: o[ko] for kg, ko in parity.FIELD_MAP}
+        out["counters"] = {"n_density": o["counts"][0], "n_density_redo": o["counts"][1], "n_force": o["counts"][2]}
+        out["tree"], out["pairs"] = t, o["pairs"]
+        return out
+
+    class EmptyMock:
+        def __init__(self, prm):
+            pass
+
+        def build(self, ic):
+            assert len(ic["h"]) == 0
+
+        def step(self):
+            pass
+
+        def counters(self):
+            return {"n_density": 0, "n_force": 0}
+
+        def close(self):
+            pass
+
+    monkeypatch.setattr(parity, "run_gpu", mock_run_gpu)
+    monkeypatch.setattr(E, "HydroBackend", EmptyMock)
+    monkeypatch.setattr(E, "FAILED", [])
+    assert E.main() == 0, capsys.readouterr().out
