@@ -141,12 +141,71 @@ static void shim_params(const struct engine *e, swift_cuda_params *p) {
 #endif
 }
 
+#ifdef PLANETARY_SPH
+/* Materials that live in tables: eos_init has read the files into the reference's global `eos`
+ * (src/equation_of_state/planetary/equation_of_state.h:1629-1745: load_table_*, prepare_table_*, convert_units_*);
+ * the prepared arrays are handed to the library as they are, which copies them to the device.  A material whose
+ * table was not loaded (its arrays are NULL) is skipped. */
+static void shim_set_sesame(swift_cuda_ctx *ctx, const struct SESAME_params *m) {
+  if (m->table_log_rho == NULL || m->table_P_rho_T == NULL) return;
+  swift_cuda_eos_table t;
+  memset(&t, 0, sizeof(t));
+  t.kind = 1;
+  t.mat_id = (int)m->mat_id;
+  t.num_rho = m->num_rho;
+  t.num_T = m->num_T;
+  t.log_rho = m->table_log_rho;
+  t.log_u = m->table_log_u_rho_T;
+  t.P = m->table_P_rho_T;
+  t.c = m->table_c_rho_T;
+  t.P_tiny = m->P_tiny;
+  t.c_tiny = m->c_tiny;
+  CUDA_OK(swift_cuda_set_eos_table(ctx, &t));
+}
+static void shim_set_hm80(swift_cuda_ctx *ctx, const struct HM80_params *m) {
+  if (m->table_log_P_rho_u == NULL) return;
+  swift_cuda_eos_table t;
+  memset(&t, 0, sizeof(t));
+  t.kind = 2;
+  t.mat_id = (int)m->mat_id;
+  t.num_rho = m->num_rho;
+  t.num_T = m->num_u;
+  t.P = m->table_log_P_rho_u;
+  t.log_rho_min = m->log_rho_min;
+  t.log_rho_step = m->log_rho_step;
+  t.inv_log_rho_step = m->inv_log_rho_step;
+  t.log_u_min = m->log_u_min;
+  t.log_u_step = m->log_u_step;
+  t.inv_log_u_step = m->inv_log_u_step;
+  t.bulk_mod = m->bulk_mod;
+  t.P_min_for_c_min = m->P_min_for_c_min;
+  CUDA_OK(swift_cuda_set_eos_table(ctx, &t));
+}
+static void shim_set_tables(swift_cuda_ctx *ctx) {
+  /* at most 8 tables per context: the materials of one run */
+  shim_set_hm80(ctx, &eos.HM80_HHe);
+  shim_set_hm80(ctx, &eos.HM80_ice);
+  shim_set_hm80(ctx, &eos.HM80_rock);
+  shim_set_sesame(ctx, &eos.SESAME_iron);
+  shim_set_sesame(ctx, &eos.SESAME_basalt);
+  shim_set_sesame(ctx, &eos.SESAME_water);
+  shim_set_sesame(ctx, &eos.SS08_water);
+  shim_set_sesame(ctx, &eos.ANEOS_forsterite);
+  shim_set_sesame(ctx, &eos.ANEOS_iron);
+  shim_set_sesame(ctx, &eos.ANEOS_Fe85Si15);
+  for (int k = 0; k < 10; k++) shim_set_sesame(ctx, &eos.custom[k]);
+}
+#endif
+
 /* A context for this engine: swift_cuda_create, and for SPHENIX the scheme's hydro_props and e->time_base
  * (the extra ghost's dt_alpha is get_timestep(p->time_bin, e->time_base), src/runner_ghost.c:1045-1046). */
 static void shim_create(const struct engine *e, swift_cuda_ctx **ctx) {
   swift_cuda_params prm;
   shim_params(e, &prm);
   CUDA_OK(swift_cuda_create(&prm, 0, ctx));
+#ifdef PLANETARY_SPH
+  shim_set_tables(*ctx);
+#endif
 #ifdef SPHENIX_SPH
   const struct hydro_props *hp = e->hydro_properties;
   swift_cuda_sphenix_props sp;
