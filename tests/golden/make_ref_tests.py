@@ -66,3 +66,30 @@ for variant, suffix, prefix in (("minimal", "", ""), ("sphenix", "_sphenix", "sp
                 z[key] = np.array(rows, dtype=np.float64)
             np.savez_compressed(os.path.join(HERE, "ref_tests", prefix + name + ".npz"), **z)
             print(variant, name, "->", {k: v.shape for k, v in z.items()})
+
+# The reference's PERTURBED runs with its scripts' own arguments (tests/test27cellsPerturbed.sh.in,
+# test125cellsPerturbed.sh.in, testPeriodicBCPerturbed.sh.in): positions jittered by 0.1 spacings, smoothing lengths
+# spread by up to 10 % / 30 % (-p 1.1 / 1.3).  Tables as compressed arrays (first table each run writes).
+PERTURBED = {
+    "test27cells_n6_perturbed": ("test27cells", ["-n", "6", "-r", "1", "-d", "0.1", "-f", "perturbed", "-v", "2"],
+                                 "swift_dopair_27_perturbed.dat"),
+    "test27cells_n6_perturbed_h": ("test27cells", ["-n", "6", "-r", "1", "-d", "0.1", "-f", "perturbed", "-v", "1", "-p", "1.1"],
+                                   "swift_dopair_27_perturbed.dat"),
+    "test27cells_n6_perturbed_h2": ("test27cells", ["-n", "6", "-r", "1", "-d", "0.1", "-f", "perturbed", "-v", "3", "-p", "1.3"],
+                                    "swift_dopair_27_perturbed.dat"),
+    "test125cells_perturbed": ("test125cells", ["-n", "6", "-r", "1", "-d", "0.1", "-v", "1", "-p", "2", "-f", "perturbed"],
+                               "swift_dopair_125_perturbed.dat"),
+    "testPeriodicBC_perturbed": ("testPeriodicBC", ["-n", "6", "-r", "1", "-d", "0.1", "-f", "perturbed", "-v", "1"],
+                                 "swift_periodic_BC_perturbed.dat"),
+}
+for variant, suffix, prefix in (("minimal", "", ""), ("sphenix", "_sphenix", "sphenix_")):
+    for name, (exe_name, args, out) in PERTURBED.items():
+        exe = os.path.join(REF, exe_name + "_ref" + suffix)
+        if not os.path.exists(exe):
+            print("skip", variant, name, "(not built)")
+            continue
+        with tempfile.TemporaryDirectory() as tmp:
+            subprocess.run([exe] + args, cwd=tmp, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            rows = [l.split() for l in open(os.path.join(tmp, out)) if l.strip() and not l.lstrip().startswith("#")]
+            np.savez_compressed(os.path.join(HERE, "ref_tests", prefix + name + ".npz"), table=np.array(rows, dtype=np.float64))
+            print(variant, name, "->", len(rows), "rows")

@@ -147,3 +147,41 @@ def test_testActivePair_through_the_shim(name, seed, suffix, prefix, tmp_path):
         assert len(bad) == 0, "%s, difffloat gate: %d entries out of tolerance, first (row, col) %s" % (key, len(bad), bad[:5])
         bad = difffloat(ours, ref[key], tol, 10 ** 6)
         assert len(bad) == 0, "%s, against the reference's own table: %d entries, first %s" % (key, len(bad), bad[:5])
+
+
+# The reference's PERTURBED runs with its scripts' own arguments (tests/test27cellsPerturbed.sh.in,
+# test125cellsPerturbed.sh.in, testPeriodicBCPerturbed.sh.in): positions jittered by 0.1 spacings; smoothing lengths
+# spread by up to 10 % and 30 % (-p 1.1 / 1.3, gated with tolerance_27_perturbed_h / _h2.dat).
+# NOT YET RUN ON HARDWARE with these arguments (added after the round's GPU budget was spent; the binaries and the
+# entries are those of the tests above): xfail until seen.
+CASES_PERTURBED = [
+    ("test27cells_n6_perturbed", "test27cells", ["-n", "6", "-r", "1", "-d", "0.1", "-f", "perturbed", "-v", "2"],
+     "swift_dopair_27_perturbed.dat", "brute_force_27_perturbed.dat", "tolerance_27_perturbed.dat", 6),
+    ("test27cells_n6_perturbed_h", "test27cells",
+     ["-n", "6", "-r", "1", "-d", "0.1", "-f", "perturbed", "-v", "1", "-p", "1.1"],
+     "swift_dopair_27_perturbed.dat", "brute_force_27_perturbed.dat", "tolerance_27_perturbed_h.dat", 6),
+    ("test27cells_n6_perturbed_h2", "test27cells",
+     ["-n", "6", "-r", "1", "-d", "0.1", "-f", "perturbed", "-v", "3", "-p", "1.3"],
+     "swift_dopair_27_perturbed.dat", "brute_force_27_perturbed.dat", "tolerance_27_perturbed_h2.dat", 6),
+    ("test125cells_perturbed", "test125cells", ["-n", "6", "-r", "1", "-d", "0.1", "-v", "1", "-p", "2", "-f", "perturbed"],
+     "swift_dopair_125_perturbed.dat", "brute_force_125_perturbed.dat", "tolerance_125_perturbed.dat", 6),
+    ("testPeriodicBC_perturbed", "testPeriodicBC", ["-n", "6", "-r", "1", "-d", "0.1", "-f", "perturbed", "-v", "1"],
+     "swift_periodic_BC_perturbed.dat", "brute_force_periodic_BC_perturbed.dat", "tolerance_periodic_BC_perturbed.dat",
+     10 ** 6),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason="first run on hardware with these arguments (added after the round's GPU budget was spent)")
+@pytest.mark.parametrize("suffix,prefix", VARIANTS, ids=["minimal", "sphenix"])
+@pytest.mark.parametrize("name,exe,args,ours_f,brute_f,tol_f,nrows", CASES_PERTURBED, ids=[c[0] for c in CASES_PERTURBED])
+def test_perturbed_runs_through_the_shim(name, exe, args, ours_f, brute_f, tol_f, nrows, suffix, prefix, tmp_path):
+    run_test(exe + "_cuda" + suffix, args, tmp_path, timeout=300)
+    ours = load_table(tmp_path / ours_f)
+    brute = load_table(tmp_path / brute_f)
+    tol = load_table(os.path.join(REF, tol_f))
+    bad = difffloat(ours, brute, tol, nrows)     # the reference's gate: the main cell's n^3 rows (all for the periodic test)
+    assert len(bad) == 0, "difffloat gate: %d entries out of tolerance, first (row, col) %s" % (len(bad), bad[:5])
+    ref = np.load(os.path.join(GOLD, prefix + name + ".npz"))["table"]
+    bad = difffloat(ours, ref, tol, 10 ** 6)
+    assert len(bad) == 0, "against the reference's own table: %d entries, first (row, col) %s" % (len(bad), bad[:5])
