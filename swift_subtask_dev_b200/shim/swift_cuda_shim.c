@@ -294,7 +294,10 @@ static void refresh_hmax(const struct flat *f, const struct engine *e) {
 
 /* ---- (1) per-task entries ---------------------------------------------------------------------- */
 /* One task on one or two cells: records of ci then cj in a scratch array, one context, one phase. */
-static void shim_run_task(struct runner *r, struct cell *ci, struct cell *cj, int task_type, int phases) {
+/* subset != NULL: only the `count` particles ci->hydro.parts[subset[k]] are updated (the *_subset_* entries below):
+ * in the scratch copy they alone carry an active time bin; the bins of the records that go back are the caller's. */
+static void shim_run_task_subset(struct runner *r, struct cell *ci, struct cell *cj, int task_type, int phases,
+                                 const int *subset, int count) {
   const struct engine *e = r->e;
   if (ci->hydro.count == 0 || (cj != NULL && cj->hydro.count == 0)) return;
   const int ni = ci->hydro.count, nj = cj ? cj->hydro.count : 0;
@@ -303,6 +306,16 @@ static void shim_run_task(struct runner *r, struct cell *ci, struct cell *cj, in
     error("Can't allocate the scratch particle array.");
   memcpy(buf, ci->hydro.parts, sizeof(struct part) * ni);
   if (cj) memcpy(buf + ni, cj->hydro.parts, sizeof(struct part) * nj);
+  timebin_t *saved_bins = NULL;
+  if (subset != NULL) {
+    if ((saved_bins = (timebin_t *)malloc(sizeof(timebin_t) * (size_t)(ni + nj))) == NULL)
+      error("Can't allocate the time-bin scratch array.");
+    for (int k = 0; k < ni + nj; k++) {
+      saved_bins[k] = buf[k].time_bin;
+      buf[k].time_bin = (timebin_t)(e->max_active_bin + 1); /* inactive */
+    }
+    for (int k = 0; k < count; k++) buf[subset[k]].time_bin = (timebin_t)e->max_active_bin;
+  }
 
   struct flat f = {0};
   flatten_cell(&f, ci, -1, ci->hydro.parts, 0);
@@ -316,10 +329,18 @@ static void shim_run_task(struct runner *r, struct cell *ci, struct cell *cj, in
   CUDA_OK(swift_cuda_step_parts(ctx, buf, phases));
   swift_cuda_destroy(ctx);
 
+  if (saved_bins != NULL) {
+    for (int k = 0; k < ni + nj; k++) buf[k].time_bin = saved_bins[k];
+    free(saved_bins);
+  }
   memcpy(ci->hydro.parts, buf, sizeof(struct part) * ni);
   if (cj) memcpy(cj->hydro.parts, buf + ni, sizeof(struct part) * nj);
   flat_free(&f);
   free(buf);
+}
+
+static void shim_run_task(struct runner *r, struct cell *ci, struct cell *cj, int task_type, int phases) {
+  shim_run_task_subset(r, ci, cj, task_type, phases, NULL, 0);
 }
 
 #define DENSITY_PHASES (SWIFT_CUDA_PHASE_SORT | SWIFT_CUDA_PHASE_DENSITY | SWIFT_CUDA_PHASE_KEEP)
@@ -334,6 +355,24 @@ void runner_doself1_branch_density(struct runner *r, struct cell *c) {
 void runner_dopair1_branch_density(struct runner *r, struct cell *ci, struct cell *cj) {
   if (!cell_is_active_hydro(ci, r->e) && !cell_is_active_hydro(cj, r->e)) return;
   shim_run_task(r, ci, cj, 1, DENSITY_PHASES);
+}
+/* runner_do{self,pair}_subset_branch_density (src/runner_doiact_functions_hydro.h:884-937, 1047-1057; the entries
+ * runner_do_ghost calls for the particles whose h has not converged, and tests/test27cells.c built as
+ * test27cells_subset calls directly): only parts[ind[0..count)] of ci are updated, from ALL particles of ci (self)
+ * or of cj (pair).  That is the density task with nobody but the subset active -- DOSELF1 / DOPAIR1 update an active
+ * particle from every neighbour, active or not -- so the scratch copy carries an active bin for the subset alone.
+ * `parts` must be ci->hydro.parts, as at every call site of the reference. */
+void runner_doself_subset_branch_density(struct runner *r, struct cell *restrict ci, struct part *restrict parts,
+                                         int *restrict ind, int count) {
+  if (parts != ci->hydro.parts) error("runner_doself_subset_branch_density: parts is not ci->hydro.parts");
+  if (count == 0) return;
+  shim_run_task_subset(r, ci, NULL, 0, DENSITY_PHASES, ind, count);
+}
+void runner_dopair_subset_branch_density(struct runner *r, struct cell *restrict ci, struct part *restrict parts_i,
+                                         int *restrict ind, int count, struct cell *restrict cj) {
+  if (parts_i != ci->hydro.parts) error("runner_dopair_subset_branch_density: parts_i is not ci->hydro.parts");
+  if (count == 0) return;
+  shim_run_task_subset(r, ci, cj, 1, DENSITY_PHASES, ind, count);
 }
 void runner_doself2_branch_force(struct runner *r, struct cell *c) {
   if (!cell_is_active_hydro(c, r->e)) return;

@@ -81,6 +81,12 @@ PERTURBED = {
                                "swift_dopair_125_perturbed.dat"),
     "testPeriodicBC_perturbed": ("testPeriodicBC", ["-n", "6", "-r", "1", "-d", "0.1", "-f", "perturbed", "-v", "1"],
                                  "swift_periodic_BC_perturbed.dat"),
+    # test27cells_subset (tests/Makefile.am:97-99): the same test with runner_do{self,pair}_subset_branch_density in
+    # the place of the density tasks (tests/test27cells.sh.in runs both binaries with the same arguments)
+    "test27cells_subset_n6": ("test27cells_subset", ["-n", "6", "-r", "1", "-d", "0", "-f", "standard", "-v", "2"],
+                              "swift_dopair_27_standard.dat"),
+    "test27cells_subset_n6_h": ("test27cells_subset", ["-n", "6", "-r", "1", "-d", "0", "-f", "standard", "-v", "1", "-p", "1.1"],
+                                "swift_dopair_27_standard.dat"),
 }
 for variant, suffix, prefix in (("minimal", "", ""), ("sphenix", "_sphenix", "sphenix_")):
     for name, (exe_name, args, out) in PERTURBED.items():

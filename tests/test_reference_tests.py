@@ -168,6 +168,14 @@ CASES_PERTURBED = [
     ("testPeriodicBC_perturbed", "testPeriodicBC", ["-n", "6", "-r", "1", "-d", "0.1", "-f", "perturbed", "-v", "1"],
      "swift_periodic_BC_perturbed.dat", "brute_force_periodic_BC_perturbed.dat", "tolerance_periodic_BC_perturbed.dat",
      10 ** 6),
+    # test27cells_subset (tests/Makefile.am:97-99, tests/test27cells.sh.in): test27cells.c with
+    # runner_do{self,pair}_subset_branch_density in the place of the density tasks; the shim runs them as the density
+    # task with nobody but the subset active
+    ("test27cells_subset_n6", "test27cells_subset", ["-n", "6", "-r", "1", "-d", "0", "-f", "standard", "-v", "2"],
+     "swift_dopair_27_standard.dat", "brute_force_27_standard.dat", "tolerance_27_normal.dat", 6),
+    ("test27cells_subset_n6_h", "test27cells_subset",
+     ["-n", "6", "-r", "1", "-d", "0", "-f", "standard", "-v", "1", "-p", "1.1"],
+     "swift_dopair_27_standard.dat", "brute_force_27_standard.dat", "tolerance_27_perturbed_h.dat", 6),
 ]
 
 
