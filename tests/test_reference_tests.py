@@ -134,7 +134,7 @@ CASES_ACTIVE_PAIR = [("testActivePair_s1506434777", "1506434777"), ("testActiveP
 @pytest.mark.parametrize("name,seed", CASES_ACTIVE_PAIR)
 def test_testActivePair_through_the_shim(name, seed, suffix, prefix, tmp_path):
     run_test("testActivePair_cuda" + suffix, ["-n", "6", "-r", "1", "-d", "0", "-f", "active", "-s", seed], tmp_path,
-             timeout=180)
+             timeout=90)
     ref = np.load(os.path.join(GOLD, prefix + name + ".npz"))
     for key, ours_f, brute_f, tol_f in (
             ("density", "swift_dopair_active.dat", "brute_force_pair_active.dat", "tolerance_pair_active.dat"),
@@ -184,7 +184,7 @@ CASES_PERTURBED = [
 @pytest.mark.parametrize("suffix,prefix", VARIANTS, ids=["minimal", "sphenix"])
 @pytest.mark.parametrize("name,exe,args,ours_f,brute_f,tol_f,nrows", CASES_PERTURBED, ids=[c[0] for c in CASES_PERTURBED])
 def test_perturbed_runs_through_the_shim(name, exe, args, ours_f, brute_f, tol_f, nrows, suffix, prefix, tmp_path):
-    run_test(exe + "_cuda" + suffix, args, tmp_path, timeout=300)
+    run_test(exe + "_cuda" + suffix, args, tmp_path, timeout=90)
     ours = load_table(tmp_path / ours_f)
     brute = load_table(tmp_path / brute_f)
     tol = load_table(os.path.join(REF, tol_f))

@@ -24,7 +24,7 @@ FIRST_RUN = "first run on hardware (written after the round's GPU budget was spe
 
 
 def _run(section):
-    r = subprocess.run([sys.executable, SCRIPT, section], cwd=ROOT, capture_output=True, text=True, timeout=900)
+    r = subprocess.run([sys.executable, SCRIPT, section], cwd=ROOT, capture_output=True, text=True, timeout=300)
     sys.stdout.write(r.stdout[-6000:])
     sys.stderr.write(r.stderr[-3000:])
     assert r.returncode == 0, "limiter_gpu_check.py %s:\n%s\n%s" % (section, r.stdout[-3000:], r.stderr[-2000:])
