@@ -298,3 +298,25 @@ def test_kernel_body_on_the_host_vs_oracle_at_the_energy_floor(kernel_body):
         assert il.Checker("ref", ip).limiter(c, wc, ti_current, mab) == ra
         for k in il.STATE_KEYS:
             assert np.array_equal(a[k], c[k]), k + " (compiled reference)"
+
+
+@pytest.mark.skipif(not ol.ref_available("planetary"), reason="oracle/_ref not built (needs the reference tree)")
+def test_oracle_run_with_limiter_planetary_vs_compiled_reference_live():
+    """The Planetary scheme (Tillotson): kick_part's energy floor is the scheme's own (hydro_kick_extra,
+    src/hydro/Planetary/hydro.h:904-925), and the undone / redone kicks of a woken particle go through it."""
+    from swift_subtask_dev_b200 import ics
+    ic = ics.two_body_impact(3000, seed=5)
+    kw = dict(periodic=False, dim=tuple(float(v) for v in ic["dim"]), scheme=1, alpha=1.5, h_max=float(ic["h_max"]))
+    ip = il.default_iparams(scheme=1, h_max=float(ic["h_max"]), dt_max=1e3, time_end=1e5)
+    # a hot spot on the impactor's surface: its neighbours fall more than two bins behind
+    hot = np.argsort(ic["x"][:, 0])[-12:]
+    ic["u"] = ic["u"].copy()
+    ic["u"][hot] *= 400.0
+    eos = ol.eos_from_json()
+    icc, tree = il.prepare(ic, kw)
+    sr, lr = il.run_loop("ref", icc, kw, ip, tree, 6, eos=eos, variant="planetary", limiter=True)
+    so, lo = il.run_loop("oracle", icc, kw, ip, tree, 6, eos=eos, variant="planetary", limiter=True)
+    assert lr == lo
+    assert sum(l[6] for l in lr) > 0, "nobody was woken: the case does not exercise the limiter"
+    for k in il.STATE_KEYS:
+        assert np.array_equal(sr[k], so[k]), k
