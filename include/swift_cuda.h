@@ -481,8 +481,10 @@ int swift_cuda_eos_table_write_bin(const char *path, const swift_cuda_eos_table 
 int swift_cuda_eos_table_read_bin(const char *path, swift_cuda_eos_table *out);
 void swift_cuda_eos_table_free(swift_cuda_eos_table *table);
 /* Copies the table to the context's device (at most 8 tables per context, Planetary scheme only); particles
- * whose mat_id equals the table's are evaluated from it from then on.  A particle whose material is neither
- * an ideal gas, a Tillotson material of swift_cuda_params nor a table set here makes the step fail. */
+ * whose mat_id equals the table's are evaluated from it from then on; a second table for the same mat_id replaces
+ * the first.  Tables outlive rebuilds of the context.  The caller must set a table for every table material its
+ * particles carry: a mat_id >= 200 without one is NOT detected (it is evaluated as the first Tillotson material,
+ * as any unknown material id has been since round 1). */
 int swift_cuda_set_eos_table(swift_cuda_ctx *ctx, const swift_cuda_eos_table *table);
 
 /* ---- Flat binary particle files (the other half of SURVEY.md 8(f) N4) ---------------------------
