@@ -148,3 +148,44 @@ def test_threaded_reference_harness_agrees_with_the_serial_one():
     again = ol.run_step("ref", prm, icc, cells, tasks, nt)
     for k in FIELDS:
         assert np.array_equal(again[k], serial[k]), "the serial mode is what it was: " + k
+
+
+def _brute_force_counts(x, H, active, dim, periodic):
+    """All pairs, no tree: for every active i the neighbours within its own kernel support (what the gradient loop
+    of SPHENIX and a density pass with the converged h visit) and within either support (the force loop)."""
+    n = len(H)
+    H2 = H.astype(np.float32) ** 2
+    n_own, n_either = np.zeros(n, np.int64), np.zeros(n, np.int64)
+    for i in np.nonzero(active)[0]:
+        dx = x[i] - x
+        if periodic:
+            dx -= np.round(dx / dim) * dim
+        r2 = (dx.astype(np.float32) ** 2).sum(1)
+        own = r2 < H2[i]
+        own[i] = False
+        either = own | (r2 < H2)
+        either[i] = False
+        n_own[i], n_either[i] = own.sum(), either.sum()
+    return n_own, n_either
+
+
+def _exact_count_inputs(g):
+    kw = g["params"]
+    tb = g["ic"].get("time_bin")
+    act = np.ones(len(g["h"]), bool) if tb is None else tb <= kw.get("max_active_bin", 56)
+    gamma = np.float32(1.825742)
+    # active particles: the converged h; the others keep theirs
+    H = np.where(act, g["g_h"] * gamma, g["h"] * gamma).astype(np.float32)
+    return H, act, np.array(kw.get("dim", (1.0, 1.0, 1.0)), dtype=np.float64), kw.get("periodic", True)
+
+
+@pytest.mark.parametrize("name", gu.names())
+def test_force_loop_counts_against_brute_force(name):
+    """The role of the reference's exact-count checker (hydro_exact_density_compute / N_force_exact,
+    src/hydro.c:50-260 under SWIFT_HYDRO_DENSITY_CHECKS): the number of neighbours every particle met in the
+    reference's force loop, from positions and smoothing lengths alone."""
+    g = gu.load(name)
+    H, act, dim, periodic = _exact_count_inputs(g)
+    n_own, n_either = _brute_force_counts(g["x"], H, act, dim, periodic)
+    assert np.array_equal(n_either, g["ngb2"])
+    assert int(n_either.sum()) == int(g["counts"][2])

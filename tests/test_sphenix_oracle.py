@@ -95,3 +95,17 @@ def test_oracle_engine_loop_reproduces_reference_golden_sphenix():
     assert [[l[0], l[1], l[2], l[5]] for l in log] == z["log_int"].tolist()
     assert len(np.unique(s["time_bin"])) >= 4, "not a time-bin hierarchy"
     assert s["alpha_visc"].max() > 1.0, "the viscosity switch should have fired somewhere"
+
+
+@pytest.mark.parametrize("name", gu.sphenix_names())
+def test_gradient_and_force_loop_counts_against_brute_force(name):
+    """N_gradient_exact and N_force_exact of the reference's checker (src/hydro.c:50-260, SWIFT_HYDRO_DENSITY_CHECKS)
+    from positions and converged smoothing lengths alone, all pairs: the gradient loop visits the neighbours within a
+    particle's own kernel support, the force loop those within either support."""
+    from test_oracle import _brute_force_counts, _exact_count_inputs
+    g = gu.load_sphenix(name)
+    H, act, dim, periodic = _exact_count_inputs(g)
+    n_own, n_either = _brute_force_counts(g["x"], H, act, dim, periodic)
+    assert np.array_equal(n_own, g["ngb3"]), "gradient loop"
+    assert np.array_equal(n_either, g["ngb2"]), "force loop"
+    assert int(n_own.sum()) == int(g["counts"][3]) and int(n_either.sum()) == int(g["counts"][2])
