@@ -311,6 +311,22 @@ def sphenix_leg(side):
     return out
 
 
+def limiter_leg(side, timeout_s=150):
+    """The time-step limiter's device times on a resident run (scripts/limiter_bench.py), in a process of its own:
+    its kernels were written after the last GPU session of the round, so nothing they do -- a refusal, a device
+    fault, a hang -- may touch this process or its JSON line.  Returns the script's line, or why there is none."""
+    import subprocess
+    try:
+        r = subprocess.run([sys.executable, os.path.join(os.path.dirname(os.path.abspath(__file__)), "scripts",
+                                                         "limiter_bench.py"), str(side)],
+                           capture_output=True, text=True, timeout=timeout_s)
+        if r.returncode != 0:
+            return {"unavailable": "limiter_bench.py exited %d: %s" % (r.returncode, (r.stderr or r.stdout)[-300:])}
+        return json.loads(r.stdout.strip().splitlines()[-1])
+    except Exception as e:  # noqa: BLE001  (a timeout, no output, bad JSON: the bench line goes out regardless)
+        return {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:300])}
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -339,6 +355,9 @@ def main():
                          "field bit-identical to the reference.  The other mode is timed too (detail.other_mode)")
     ap.add_argument("--sphenix-side", type=int, default=128,
                     help="box side of the SPHENIX leg (three-loop scheme, SURVEY 8(f) N1; detail.sphenix); 0: skip")
+    ap.add_argument("--limiter-side", type=int, default=96,
+                    help="lattice side of the time-step limiter leg (resident engine steps with the limiter on, in a "
+                         "process of its own; detail.limiter); 0: skip")
     ap.add_argument("--resident-steps", type=int, default=3,
                     help="engine steps of the device-resident leg (drift/kick/time-step kernels, SURVEY 8(f) N3); 0: skip")
     args = ap.parse_args()
@@ -560,6 +579,8 @@ def main():
         line["resident"] = resident_leg(args, ic, hbm_peak)
     if args.sphenix_side > 0:
         line["detail"]["sphenix"] = sphenix_leg(args.sphenix_side)
+    if args.limiter_side > 0:
+        line["detail"]["limiter"] = limiter_leg(args.limiter_side)
     if not args.no_cpu:
         nproc = host_cores()
         thr = cpu_arm_threaded(args.cpu_box_side, nproc, reps=2) if args.cpu_box_side > 0 else None
