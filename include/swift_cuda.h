@@ -345,8 +345,8 @@ int swift_cuda_refresh_cell_hmax(swift_cuda_ctx *ctx, int after_ghost);
 
 /* ---- Time integration on the device -------------------
  * The step either side of the neighbour loops, so that the particles stay resident in HBM across
- * steps and only snapshots cross the bus.  Replaces, for gas particles without gravity, cosmology,
- * cooling or the time-step limiter:
+ * steps and only snapshots cross the bus.  Replaces, for gas particles without gravity, cosmology or
+ * cooling (the time-step limiter has a section of its own below):
  *   runner_do_drift_part -> cell_drift_part   src/cell_drift.c:145-380  (drift_part, src/drift.h:143-233,
  *                                             hydro_predict_extra, src/hydro/<scheme>/hydro.h)
  *   runner_do_kick1 / runner_do_kick2         src/runner_time_integration.c:87-220, 359-500 (kick_part,
